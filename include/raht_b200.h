@@ -1,0 +1,227 @@
+/*
+ * raht_b200.h -- C ABI of libraht_b200.so: the B200 (sm_100a) implementation of the RAHT-3DGS
+ * encode/decode hot path of Daaohame/RAHT-3DGS-codec (reference commit ef45e2e).
+ *
+ * This is the drop-in boundary.  Everything the reference's Python operator layer needs for the
+ * path  voxelise -> merge -> RAHT_param -> RAHT -> quantise -> reorder -> RLGR  (and the inverse)
+ * is reachable through the entry points below: plain pointers and sizes, no torch types.
+ * The reference has no C FFI of its own for this path (its natives are a torch-extension and a
+ * pybind11 module); each entry point cites the reference interface it replaces (file:line relative
+ * to the reference repository) so a maintainer can bind it with ctypes.
+ *
+ * Conventions
+ *   - every pointer is a DEVICE pointer owned by the caller unless its name ends in _host;
+ *   - every call is stream-ordered on `stream` (a cudaStream_t passed as void*); only the calls
+ *     documented as "synchronises" wait for the stream (they must learn a size on the host);
+ *   - scratch memory is caller-provided: ask raht_*_workspace_bytes() first (the transform plan is
+ *     the one library-owned object: raht_plan_create / raht_plan_destroy);
+ *   - return value: 0 on success, a negative RAHT_E_* code otherwise; raht_last_error() returns
+ *     a thread-local message for the last failing call;
+ *   - inputs are never modified; outputs must not alias inputs.
+ */
+#ifndef RAHT_B200_H
+#define RAHT_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define RAHT_B200_ABI_VERSION 2
+
+enum {
+    RAHT_OK = 0,
+    RAHT_E_INVALID = -1,   /* bad argument (null pointer, size, depth, alignment)          */
+    RAHT_E_WORKSPACE = -2, /* workspace too small                                          */
+    RAHT_E_CUDA = -3,      /* a CUDA runtime call or launch failed                         */
+    RAHT_E_NODEVICE = -4,  /* no sm_100 device / wrong architecture                        */
+    RAHT_E_INPUT = -5      /* device-side validation failed (see status bits)              */
+};
+
+/* dtype tags for attribute matrices */
+enum { RAHT_F32 = 0, RAHT_F64 = 1 };
+
+/* device-side status bits (written with atomicOr into a caller-zeroed int32 word) */
+enum {
+    RAHT_ST_OUT_OF_BOUNDS = 1,     /* RAHT_param.py:26-27 ValueError("RAHT_param:OutOfBounds")  */
+    RAHT_ST_NOT_SORTED_UNIQUE = 2, /* rows not Morton-sorted/unique (undefined in the reference) */
+    RAHT_ST_INT32_OVERFLOW = 4,    /* |q| >= 2^31 on the int32 cast, encode_3dgs.py:215         */
+    RAHT_ST_STREAM_OVERFLOW = 8,   /* RLGR stream did not fit its slot                          */
+    RAHT_ST_SORT_STALL = 16        /* radix-sort look-back gave up (internal error)             */
+};
+
+int raht_abi_version(void);
+const char *raht_last_error(void);
+/* number of SMs / compute capability of the current device (major*10+minor); <0 on error */
+int raht_device_info(int *sm_count, int *cc);
+
+/* ------------------------------------------------------------------------------------------------
+ * (a1,a2) Voxelisation front end.   Replaces python/voxelize_pc.py:25-59 (get_morton_code) and
+ * :62-172 (voxelize_pc_batched): min / max, fp32 quantisation, Morton keys, torch.sort (:101),
+ * boundary detection (:114-120).
+ * ------------------------------------------------------------------------------------------------ */
+
+/* bounds6[0..2] = min over rows of V[:,0..2], bounds6[3..5] = max.  V is (n, ld) fp32, ld >= 3.
+ * voxelize_pc.py:87-95 (vmin = V.min(0); width = (V - vmin).max()).  bounds6 needs no init.     */
+int raht_bounds3_f32(const float *V, int64_t n, int64_t ld, float *bounds6, void *stream);
+
+/* Device-side completion of voxelize_pc.py:87-97 from bounds6: if use_given_* != 0 the caller's
+ * vmin_host[3] / width_host are used instead of the data's.  Writes params4 = {vmin x,y,z,
+ * (float)voxel_size} and params_d2 = {width, voxel_size} (doubles).                               */
+int raht_voxel_params(const float *bounds6, int J, int use_given_vmin, const float *vmin_host,
+                      int use_given_width, double width_host, float *params4, double *params_d2,
+                      void *stream);
+
+/* keys[i] = Morton( clamp(floor((V[i]-vmin)/voxel_size), 0, 2^J-1) ), fp32 arithmetic exactly as
+ * torch does for a float32 tensor (voxelize_pc.py:90,98,100).  params4 from raht_voxel_params.
+ * vint (n,3) int64 optional: the clamped integer coordinates (V0_integer).                        */
+int raht_morton_keys_f32(const float *V, int64_t n, int64_t ld, const float *params4, int J,
+                         uint64_t *keys, int64_t *vint, void *stream);
+
+/* get_morton_code(V int64 (n,3), J)  voxelize_pc.py:25-59 */
+int raht_morton_keys_i64(const int64_t *V, int64_t n, int J, int64_t *keys, void *stream);
+
+/* RAHT_param.py:21-36 / :201-212: Vint = floor((V - minV)/Q), Q = width/2^depth, fp64; sets
+ * RAHT_ST_OUT_OF_BOUNDS in *status when an index leaves [0, 2^depth-1].                           */
+int raht_morton_keys_f64(const double *V, int64_t n, const double *minV_host, double width, int depth,
+                         int64_t *keys, int32_t *status, void *stream);
+
+/* inverse of the Morton interleave: coords (n,3) as fp32 (PCvox, voxelize_pc.py:158-160) */
+int raht_morton_decode_f32(const uint64_t *keys, int64_t n, int J, float *coords, void *stream);
+
+/* Onesweep LSD radix sort of (key, payload) pairs, stable, bits [begin_bit, end_bit) of the key.
+ * vals_in == NULL sorts the identity permutation (payload = original index).  Replaces
+ * torch.sort at voxelize_pc.py:101 (stable: ties keep original order).  status: caller-zeroed
+ * int32 word (RAHT_ST_SORT_STALL).                                                                 */
+size_t raht_radix_sort_workspace_bytes(int64_t n, int begin_bit, int end_bit);
+int raht_radix_sort_pairs(const uint64_t *keys_in, uint64_t *keys_out, const uint32_t *vals_in,
+                          uint32_t *vals_out, int64_t n, int begin_bit, int end_bit, int32_t *status,
+                          void *workspace, size_t workspace_bytes, void *stream);
+
+/* voxel_indices[v] = first sorted position of voxel v (voxelize_pc.py:114-118); *nvox (device).
+ * Also writes cluster_offsets int32 (nvox+1 entries, test_voxelize_3dgs.py:225-233) when non-NULL
+ * and the unique keys (nvox) when non-NULL.                                                        */
+size_t raht_voxel_segments_workspace_bytes(int64_t n);
+int raht_voxel_segments(const uint64_t *sorted_keys, int64_t n, int64_t *voxel_indices,
+                        int32_t *cluster_offsets, uint64_t *unique_keys, int64_t *nvox,
+                        void *workspace, size_t workspace_bytes, void *stream);
+
+/* Row gather + voxelisation residual: PCsorted = PC[idx], DeltaV = V0 - voxel_size*floor(V0/voxel_size)
+ * (voxelize_pc.py:103-111).  Either output may be NULL.  PC is (n, ld) fp32; PCsorted (n, ld);
+ * DeltaV (n, ld_delta) columns 0..2.                                                              */
+int raht_gather_rows_f32(const float *PC, int64_t n, int64_t ld, const uint32_t *idx,
+                         const float *params4, float *PCsorted, float *DeltaV, int64_t ld_delta,
+                         void *stream);
+
+/* Per-voxel attribute mean (voxelize_pc.py:122-153): Cvox[v] = sum of C[idx[s..e)] in sorted order
+ * / count; PC is (n, ld) fp32 with the d attributes in columns 3..3+d.  Cvox (nvox, ld_out) written
+ * at columns col_out..col_out+d.  DeltaC (n, ld_delta) at columns 3..3+d optional.                 */
+int raht_voxel_attr_mean_f32(const float *PC, int64_t n, int64_t ld, int d, const uint32_t *idx,
+                             const int64_t *voxel_indices, int64_t nvox, float *Cvox, int64_t ld_out,
+                             int col_out, float *DeltaC, int64_t ld_delta, void *stream);
+
+/* ------------------------------------------------------------------------------------------------
+ * (a4) Segmented Gaussian merge.  Replaces cuda/merge_cluster.cu:2-111 and its host wrapper
+ * cuda/merge_cluster_wrapper.cu:11-116 (merge_clusters_cuda).  fp32, IEEE (no fast-math).
+ * Any of the five outputs may be NULL.  packed (optional): row-major (num_clusters, 11+color_dim)
+ * matrix [means3|quats4|scales3|opacity1|colors] in packed_dtype, the layout the transform eats.
+ * Empty segments produce zero rows (the reference leaves torch::zeros, merge_cluster.cu:27-29).
+ * ------------------------------------------------------------------------------------------------ */
+int raht_merge_segments(const int32_t *cluster_indices, const int32_t *cluster_offsets,
+                        int64_t num_clusters, const float *means, const float *quats,
+                        const float *scales, const float *opacities, const float *colors,
+                        int color_dim, int weight_by_opacity, float *m_means, float *m_quats,
+                        float *m_scales, float *m_opacities, float *m_colors, void *packed,
+                        int packed_dtype, void *stream);
+
+/* ------------------------------------------------------------------------------------------------
+ * (a5,a6) Tree construction.  Replaces python/RAHT_param.py:6-83 (RAHT_param) and :191-279
+ * (RAHT_param_reorder_fast).
+ *
+ * Compact device tree: for every row i of the Morton-sorted unique codes, level[i] = bit level at
+ * which row i is merged as a right sibling = index of the highest bit in which MC[i-1] and MC[i]
+ * differ; level[0] = 255 (root).  Everything the reference returns (List/Flags/weights per level,
+ * order_RAGFT, w) is a function of level[] alone.
+ * ------------------------------------------------------------------------------------------------ */
+int raht_tree_levels(const int64_t *MC, int64_t n, uint8_t *level, int32_t *status, void *stream);
+
+/* List[l] / Flags[l] / weights[l] of RAHT_param.py:226-277 for one level; *count (device int64). */
+size_t raht_tree_level_workspace_bytes(int64_t n);
+int raht_tree_level(const uint8_t *level, int64_t n, int l, int64_t *list, uint8_t *flags,
+                    int64_t *weights, int64_t *count, void *workspace, size_t workspace_bytes,
+                    void *stream);
+
+/* max over rows>=1 of level[] (-1 when n<=1) -> *max_level (device int32): len(List) = max+1.     */
+int raht_tree_max_level(const uint8_t *level, int64_t n, int32_t *max_level, void *stream);
+
+/* order_RAGFT (RAHT_param.py:219-274): row 0, then rows by descending octree level (level/3),
+ * ascending row index inside a group.  order (n x int64, optional); position (n x int32, optional)
+ * is the inverse permutation (the argsort of encode_3dgs.py:267).                                  */
+size_t raht_order_ragft_workspace_bytes(int64_t n);
+int raht_order_ragft(const uint8_t *level, int64_t n, int64_t *order, int32_t *position,
+                     void *workspace, size_t workspace_bytes, void *stream);
+
+/* Transform plan: the butterflies of the tree scheduled for the fused shared-memory kernels.
+ * Stage 1 cuts the rows into tiles of tile_rows Morton-contiguous rows; every butterfly whose
+ * row span lies inside one tile runs there, the others ("deferred") are compacted into stage 2,
+ * which is tiled again, and so on until one tile remains.  tile_rows in [128, 1024], even.
+ * w (n doubles, optional): the second output of RAHT2_optimized (RAHT.py:286,325-328).
+ * SYNCHRONISES `stream` once per stage (a handful of times).                                       */
+typedef struct raht_plan raht_plan;
+int raht_plan_create(const uint8_t *level, int64_t n, int tile_rows, double *w, raht_plan **plan,
+                     void *stream);
+void raht_plan_destroy(raht_plan *plan);
+/* info[0]=n, [1]=tile_rows, [2]=stages, [3]=device bytes held, [4+k]=rows in stage k          */
+int raht_plan_info(const raht_plan *plan, int64_t *info_host, int cap);
+
+/* ------------------------------------------------------------------------------------------------
+ * (a7,a8) Transform.  Replaces python/RAHT.py:253-336 (RAHT2_optimized) and python/iRAHT.py:40-114
+ * (inverse_RAHT_optimized).  With t_dtype = RAHT_F64: IEEE fp64, no FMA contraction, bit-exact with
+ * the reference on CPU.  t_dtype = RAHT_F32 is the build-specific fast mode.
+ * C is (n, D) row-major of c_dtype; T (n, D) row-major of t_dtype.  flags: bit 0 = do not use TMA.
+ * ------------------------------------------------------------------------------------------------ */
+int raht_forward(const raht_plan *plan, const void *C, int c_dtype, int D, void *T, int t_dtype,
+                 int flags, void *stream);
+int raht_inverse(const raht_plan *plan, const void *T, int t_dtype, int D, void *C, int flags,
+                 void *stream);
+
+/* ------------------------------------------------------------------------------------------------
+ * (a9,a10,a11) Quantise + reorder + channel marshalling.  Replaces encode_3dgs.py:204 (floor(T/step
+ * +0.5)), :210 (index_select(order_RAGFT)), :215-222 (int32 cast, per-channel sequences) and the
+ * mirror :255-268.  steps: D doubles (device) -- one per channel (encode_3dgs_debug.py:376-381);
+ * q is channel-major int32: q[c*ld + p] = quantised T[order[p], c].  order == NULL = identity.
+ * ------------------------------------------------------------------------------------------------ */
+int raht_quant_reorder(const void *T, int t_dtype, int64_t n, int D, const int64_t *order,
+                       const double *steps, int32_t *q, int64_t ld, int32_t *status, void *stream);
+int raht_dequant_unreorder(const int32_t *q, int64_t ld, int64_t n, int D, const int64_t *order,
+                           const double *steps, void *T, int t_dtype, void *stream);
+/* row-major variants without marshalling: Coeff_enc = floor(T/step+0.5) (fp64 out), and q*step */
+int raht_quantize_f64(const double *T, int64_t count, double step, double *q, void *stream);
+int raht_dequantize_f64(const double *q, int64_t count, double step, double *T, void *stream);
+
+/* ------------------------------------------------------------------------------------------------
+ * (a12) RLGR entropy coder.  Replaces python/PyRLGR/src/libs/rlgr/membuf.cpp:340-423 (rlgrWrite),
+ * :258-338 (rlgrRead), :46-56 (close), :59-62 (get_buffer) as bound by bindings.cpp:34-57.
+ * One independent stream per channel, byte-identical to the reference's.
+ * q: channel-major int32 (nch, ld); streams: nch slots of slot_bytes (multiple of 8) bytes;
+ * nbytes[c]: closed stream length.  A stream that does not fit sets RAHT_ST_STREAM_OVERFLOW.
+ * ------------------------------------------------------------------------------------------------ */
+size_t raht_rlgr_encode_workspace_bytes(int64_t n, int nch);
+int raht_rlgr_encode(const int32_t *q, int64_t n, int64_t ld, int nch, int flag_signed,
+                     uint8_t *streams, int64_t slot_bytes, int64_t *nbytes, int32_t *status,
+                     void *workspace, size_t workspace_bytes, void *stream);
+int raht_rlgr_decode(const uint8_t *streams, int64_t slot_bytes, const int64_t *nbytes, int64_t n,
+                     int64_t ld, int nch, int flag_signed, int32_t *q, void *stream);
+
+/* (a13) sum over rows of (A-B)^2 in fp64 for columns [c0,c1) of two (n, D) matrices -> *sse
+ * (device double, overwritten), encode_3dgs.py:298-310.                                            */
+int raht_sse_f64(const double *A, const double *B, int64_t n, int D, int c0, int c1, double *sse,
+                 void *workspace, size_t workspace_bytes, void *stream);
+size_t raht_sse_workspace_bytes(int64_t n, int D);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* RAHT_B200_H */

@@ -1,0 +1,109 @@
+// merge.cu -- segmented Gaussian merge.
+// Replaces cuda/merge_cluster.cu:2-111 (merge_weighted_mean_kernel, one thread per voxel with
+// strided gathers and a 48x re-read of the opacities) and cuda/merge_cluster_wrapper.cu:11-116.
+//
+// Mapping: one thread per (voxel, output channel); the 11+color_dim channels of a voxel sit in
+// consecutive lanes, so the gathers of a member's colour row are coalesced and the packed output row
+// [means3|quats4|scales3|opacity1|colors] is written contiguously.  Every channel sums its members in
+// segment order with separately rounded multiply and add, so the result is a deterministic function
+// of the inputs (the reference's --use_fast_math build is not).
+#include "common.cuh"
+#include <math.h>
+
+namespace {
+
+template <typename OutT>
+__global__ void __launch_bounds__(256)
+merge_kernel(const int32_t *__restrict__ cidx, const int32_t *__restrict__ coff, int64_t nclu,
+             const float *__restrict__ means, const float *__restrict__ quats, const float *__restrict__ scales,
+             const float *__restrict__ opac, const float *__restrict__ colors, int color_dim, int by_opacity,
+             float *__restrict__ m_means, float *__restrict__ m_quats, float *__restrict__ m_scales,
+             float *__restrict__ m_opac, float *__restrict__ m_colors, OutT *__restrict__ packed)
+{
+    const int OC = 11 + color_dim;
+    const int64_t total = nclu * OC;
+    for (int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; e < total; e += (int64_t)gridDim.x * blockDim.x) {
+        const int64_t v = e / OC;
+        const int c = (int)(e - v * OC);
+        const int s = coff[v], t = coff[v + 1];
+        float out = 0.0f;
+        if (t > s) {                                                     // merge_cluster.cu:27-29
+            if (c >= 3 && c < 7) {
+                // quaternion: all four weighted sums are needed for the norm (:74-87)
+                float q[4] = {0.f, 0.f, 0.f, 0.f};
+                for (int i = s; i < t; ++i) {
+                    int g = cidx[i];
+                    float w = by_opacity ? opac[g] : 1.0f;               // :42
+                    const float4 qq = *reinterpret_cast<const float4 *>(quats + (size_t)g * 4);
+                    q[0] = __fadd_rn(q[0], __fmul_rn(qq.x, w));
+                    q[1] = __fadd_rn(q[1], __fmul_rn(qq.y, w));
+                    q[2] = __fadd_rn(q[2], __fmul_rn(qq.z, w));
+                    q[3] = __fadd_rn(q[3], __fmul_rn(qq.w, w));
+                }
+                float nn = __fadd_rn(__fadd_rn(__fadd_rn(__fmul_rn(q[0], q[0]), __fmul_rn(q[1], q[1])), __fmul_rn(q[2], q[2])),
+                                     __fmul_rn(q[3], q[3]));
+                float qn = __fsqrt_rn(nn);                               // :75-76
+                if (qn > 0.0f) out = __fdiv_rn(q[c - 3], qn);
+                else out = (c == 6) ? 1.0f : 0.0f;                       // fallback (0,0,0,1) :82-86
+            } else if (c == 10) {
+                float acc = 0.0f;
+                for (int i = s; i < t; ++i) acc = __fadd_rn(acc, opac[cidx[i]]);
+                out = fminf(acc, 1.0f);                                  // :94
+            } else {
+                const float *src;
+                int ld, col;
+                if (c < 3) { src = means; ld = 3; col = c; }
+                else if (c < 10) { src = scales; ld = 3; col = c - 7; }
+                else { src = colors; ld = color_dim; col = c - 11; }
+                float acc = 0.0f, wsum = 0.0f;
+                for (int i = s; i < t; ++i) {
+                    int g = cidx[i];
+                    float w = by_opacity ? opac[g] : 1.0f;
+                    acc = __fadd_rn(acc, __fmul_rn(src[(size_t)g * ld + col], w));
+                    wsum = __fadd_rn(wsum, w);
+                }
+                if (c < 10) {
+                    if (wsum == 0.0f) wsum = 1.0f;                       // :65-67
+                    out = __fdiv_rn(acc, wsum);
+                } else {
+                    out = (wsum > 0.0f) ? __fdiv_rn(acc, wsum) : 0.0f;   // :108-109
+                }
+            }
+        }
+        if (c < 3) { if (m_means) m_means[v * 3 + c] = out; }
+        else if (c < 7) { if (m_quats) m_quats[v * 4 + (c - 3)] = out; }
+        else if (c < 10) { if (m_scales) m_scales[v * 3 + (c - 7)] = out; }
+        else if (c == 10) { if (m_opac) m_opac[v] = out; }
+        else { if (m_colors) m_colors[v * (int64_t)color_dim + (c - 11)] = out; }
+        if (packed) packed[e] = (OutT)out;
+    }
+}
+
+}  // namespace
+
+RAHT_API int raht_merge_segments(const int32_t *cluster_indices, const int32_t *cluster_offsets, int64_t num_clusters,
+                                 const float *means, const float *quats, const float *scales, const float *opacities,
+                                 const float *colors, int color_dim, int weight_by_opacity, float *m_means,
+                                 float *m_quats, float *m_scales, float *m_opacities, float *m_colors, void *packed,
+                                 int packed_dtype, void *stream)
+{
+    RAHT_REQUIRE(num_clusters >= 0 && color_dim >= 0, "raht_merge_segments: bad sizes");
+    if (num_clusters == 0) return RAHT_OK;
+    RAHT_REQUIRE(cluster_indices && cluster_offsets && means && quats && scales && opacities && (colors || color_dim == 0),
+                 "raht_merge_segments: null input pointer");
+    RAHT_REQUIRE(((uintptr_t)quats & 15) == 0, "raht_merge_segments: quats must be 16-byte aligned");
+    RAHT_REQUIRE(packed_dtype == RAHT_F32 || packed_dtype == RAHT_F64, "raht_merge_segments: bad packed_dtype");
+    cudaStream_t st = (cudaStream_t)stream;
+    int64_t total = num_clusters * (11 + color_dim);
+    int grid = grid_for(total, 256, 8);
+    if (packed && packed_dtype == RAHT_F64)
+        merge_kernel<double><<<grid, 256, 0, st>>>(cluster_indices, cluster_offsets, num_clusters, means, quats, scales,
+                                                   opacities, colors, color_dim, weight_by_opacity, m_means, m_quats,
+                                                   m_scales, m_opacities, m_colors, (double *)packed);
+    else
+        merge_kernel<float><<<grid, 256, 0, st>>>(cluster_indices, cluster_offsets, num_clusters, means, quats, scales,
+                                                  opacities, colors, color_dim, weight_by_opacity, m_means, m_quats,
+                                                  m_scales, m_opacities, m_colors, (float *)packed);
+    RAHT_LAUNCH_CHECK();
+    return RAHT_OK;
+}

@@ -1,0 +1,224 @@
+// quant.cu -- uniform quantisation, coefficient reorder and channel marshalling (SURVEY 8a rows
+// a9-a11, a13).  Replaces python/encode_3dgs.py:204 (floor(Coeff/step+0.5)), :210
+// (index_select(order_RAGFT)), :215-222 (int32 cast + one Python list per channel), the mirror
+// :255-268 (stack, *step, argsort(order) gather) and the PSNR reduction :298-310.
+//
+// One kernel each way: rows are gathered by order_RAGFT (whole 8*D-byte rows, coalesced), quantised
+// in fp64 exactly as torch does (true division, add 0.5, floor), transposed through shared memory
+// and written channel-major so that each channel is one contiguous int32 sequence for the entropy
+// coder.  Algorithmic traffic: D*e + 8 B read, 4*D B written per row.
+#include "common.cuh"
+#include <math.h>
+
+namespace {
+
+constexpr int QR_THREADS = 256;
+constexpr int QR_WARPS = QR_THREADS / 32;
+constexpr int QR_P = 128;              // positions per CTA
+constexpr int QR_PITCH = QR_P + 1;     // odd pitch: conflict-free transposition
+
+template <typename Tel>
+__global__ void __launch_bounds__(QR_THREADS)
+quant_reorder_kernel(const Tel *__restrict__ T, int64_t n, int D, const int64_t *__restrict__ order,
+                     const double *__restrict__ steps, int32_t *__restrict__ q, int64_t ld, int32_t *status)
+{
+    extern __shared__ __align__(16) unsigned char qr_smem[];
+    int32_t *s_q = (int32_t *)qr_smem;                       // [D][QR_PITCH]
+    double *s_step = (double *)(s_q + (size_t)D * QR_PITCH + ((D * QR_PITCH) & 1));
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int64_t p0 = (int64_t)blockIdx.x * QR_P;
+    const int np = (int)min((int64_t)QR_P, n - p0);
+    for (int c = tid; c < D; c += QR_THREADS) s_step[c] = steps[c];
+    __syncthreads();
+    bool ovf = false;
+    for (int j = warp; j < np; j += QR_WARPS) {
+        const int64_t row = order ? order[p0 + j] : (p0 + j);
+        const Tel *src = T + (size_t)row * D;
+        for (int c = lane; c < D; c += 32) {
+            double v = (double)src[c];
+            double qq = floor(__dadd_rn(__ddiv_rn(v, s_step[c]), 0.5));       // encode_3dgs.py:204
+            ovf |= !(qq >= -2147483648.0 && qq <= 2147483647.0);
+            s_q[c * QR_PITCH + j] = (int32_t)qq;                              // :215 .to(torch.int32)
+        }
+    }
+    if (__any_sync(~0u, ovf) && lane == 0 && status) atomicOr(status, RAHT_ST_INT32_OVERFLOW);
+    __syncthreads();
+    const int total = D * QR_P;
+    for (int i = tid; i < total; i += QR_THREADS) {
+        int c = i / QR_P, j = i - c * QR_P;
+        if (j < np) q[(size_t)c * ld + p0 + j] = s_q[c * QR_PITCH + j];
+    }
+}
+
+template <typename Tel>
+__global__ void __launch_bounds__(QR_THREADS)
+dequant_unreorder_kernel(const int32_t *__restrict__ q, int64_t ld, int64_t n, int D, const int64_t *__restrict__ order,
+                         const double *__restrict__ steps, Tel *__restrict__ T)
+{
+    extern __shared__ __align__(16) unsigned char qr_smem[];
+    int32_t *s_q = (int32_t *)qr_smem;
+    double *s_step = (double *)(s_q + (size_t)D * QR_PITCH + ((D * QR_PITCH) & 1));
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int64_t p0 = (int64_t)blockIdx.x * QR_P;
+    const int np = (int)min((int64_t)QR_P, n - p0);
+    for (int c = tid; c < D; c += QR_THREADS) s_step[c] = steps[c];
+    const int total = D * QR_P;
+    for (int i = tid; i < total; i += QR_THREADS) {
+        int c = i / QR_P, j = i - c * QR_P;
+        if (j < np) s_q[c * QR_PITCH + j] = q[(size_t)c * ld + p0 + j];
+    }
+    __syncthreads();
+    for (int j = warp; j < np; j += QR_WARPS) {
+        const int64_t row = order ? order[p0 + j] : (p0 + j);
+        Tel *dst = T + (size_t)row * D;
+        for (int c = lane; c < D; c += 32)
+            dst[c] = (Tel)__dmul_rn((double)s_q[c * QR_PITCH + j], s_step[c]);    // encode_3dgs.py:261
+    }
+}
+
+__global__ void __launch_bounds__(256) quantize_kernel(const double *__restrict__ T, int64_t count, double step,
+                                                       double *__restrict__ q)
+{
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < count; i += (int64_t)gridDim.x * blockDim.x)
+        q[i] = floor(__dadd_rn(__ddiv_rn(T[i], step), 0.5));
+}
+__global__ void __launch_bounds__(256) dequantize_kernel(const double *__restrict__ q, int64_t count, double step,
+                                                         double *__restrict__ T)
+{
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < count; i += (int64_t)gridDim.x * blockDim.x)
+        T[i] = __dmul_rn(q[i], step);
+}
+
+// ---- sum of squared differences -----------------------------------------------------------------
+constexpr int SSE_BLOCKS_MAX = 1184;      // 148 SMs x 8
+
+__global__ void __launch_bounds__(256) sse_partial_kernel(const double *__restrict__ A, const double *__restrict__ B,
+                                                          int64_t n, int D, int c0, int c1, double *partial)
+{
+    const int wc = c1 - c0;
+    const int64_t total = n * wc;
+    double acc = 0.0;
+    for (int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; e < total; e += (int64_t)gridDim.x * blockDim.x) {
+        int64_t r = e / wc;
+        int c = c0 + (int)(e - r * wc);
+        double d = A[r * D + c] - B[r * D + c];
+        acc += d * d;
+    }
+    __shared__ double s[8];
+    for (int o = 16; o; o >>= 1) acc += __shfl_xor_sync(~0u, acc, o);
+    if (lane_id() == 0) s[threadIdx.x >> 5] = acc;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        double t = 0.0;
+        for (int w = 0; w < 8; ++w) t += s[w];
+        partial[blockIdx.x] = t;
+    }
+}
+__global__ void __launch_bounds__(256) sse_final_kernel(const double *partial, int nb, double *out)
+{
+    double acc = 0.0;
+    for (int i = threadIdx.x; i < nb; i += 256) acc += partial[i];
+    __shared__ double s[8];
+    for (int o = 16; o; o >>= 1) acc += __shfl_xor_sync(~0u, acc, o);
+    if (lane_id() == 0) s[threadIdx.x >> 5] = acc;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        double t = 0.0;
+        for (int w = 0; w < 8; ++w) t += s[w];
+        *out = t;
+    }
+}
+
+size_t qr_smem_bytes(int D) { return ((size_t)D * QR_PITCH + 1) * 4 + (size_t)D * 8 + 16; }
+
+}  // namespace
+
+RAHT_API int raht_quant_reorder(const void *T, int t_dtype, int64_t n, int D, const int64_t *order, const double *steps,
+                                int32_t *q, int64_t ld, int32_t *status, void *stream)
+{
+    RAHT_REQUIRE(n >= 0 && D >= 1 && ld >= n && steps, "raht_quant_reorder: bad arguments");
+    if (n == 0) return RAHT_OK;
+    RAHT_REQUIRE(T && q, "raht_quant_reorder: null pointer");
+    size_t smem = qr_smem_bytes(D);
+    RAHT_REQUIRE(smem <= 227 * 1024, "raht_quant_reorder: D too large");
+    cudaStream_t st = (cudaStream_t)stream;
+    unsigned grid = (unsigned)((n + QR_P - 1) / QR_P);
+    if (t_dtype == RAHT_F64) {
+        RAHT_CUDA(cudaFuncSetAttribute(quant_reorder_kernel<double>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        quant_reorder_kernel<double><<<grid, QR_THREADS, smem, st>>>((const double *)T, n, D, order, steps, q, ld, status);
+    } else if (t_dtype == RAHT_F32) {
+        RAHT_CUDA(cudaFuncSetAttribute(quant_reorder_kernel<float>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        quant_reorder_kernel<float><<<grid, QR_THREADS, smem, st>>>((const float *)T, n, D, order, steps, q, ld, status);
+    } else {
+        raht_set_error("raht_quant_reorder: bad dtype");
+        return RAHT_E_INVALID;
+    }
+    RAHT_LAUNCH_CHECK();
+    return RAHT_OK;
+}
+
+RAHT_API int raht_dequant_unreorder(const int32_t *q, int64_t ld, int64_t n, int D, const int64_t *order,
+                                    const double *steps, void *T, int t_dtype, void *stream)
+{
+    RAHT_REQUIRE(n >= 0 && D >= 1 && ld >= n && steps, "raht_dequant_unreorder: bad arguments");
+    if (n == 0) return RAHT_OK;
+    RAHT_REQUIRE(T && q, "raht_dequant_unreorder: null pointer");
+    size_t smem = qr_smem_bytes(D);
+    RAHT_REQUIRE(smem <= 227 * 1024, "raht_dequant_unreorder: D too large");
+    cudaStream_t st = (cudaStream_t)stream;
+    unsigned grid = (unsigned)((n + QR_P - 1) / QR_P);
+    if (t_dtype == RAHT_F64) {
+        RAHT_CUDA(cudaFuncSetAttribute(dequant_unreorder_kernel<double>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        dequant_unreorder_kernel<double><<<grid, QR_THREADS, smem, st>>>(q, ld, n, D, order, steps, (double *)T);
+    } else if (t_dtype == RAHT_F32) {
+        RAHT_CUDA(cudaFuncSetAttribute(dequant_unreorder_kernel<float>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        dequant_unreorder_kernel<float><<<grid, QR_THREADS, smem, st>>>(q, ld, n, D, order, steps, (float *)T);
+    } else {
+        raht_set_error("raht_dequant_unreorder: bad dtype");
+        return RAHT_E_INVALID;
+    }
+    RAHT_LAUNCH_CHECK();
+    return RAHT_OK;
+}
+
+RAHT_API int raht_quantize_f64(const double *T, int64_t count, double step, double *q, void *stream)
+{
+    RAHT_REQUIRE(count >= 0 && (count == 0 || (T && q)), "raht_quantize_f64: bad arguments");
+    if (count == 0) return RAHT_OK;
+    quantize_kernel<<<grid_for(count, 256, 8), 256, 0, (cudaStream_t)stream>>>(T, count, step, q);
+    RAHT_LAUNCH_CHECK();
+    return RAHT_OK;
+}
+
+RAHT_API int raht_dequantize_f64(const double *q, int64_t count, double step, double *T, void *stream)
+{
+    RAHT_REQUIRE(count >= 0 && (count == 0 || (T && q)), "raht_dequantize_f64: bad arguments");
+    if (count == 0) return RAHT_OK;
+    dequantize_kernel<<<grid_for(count, 256, 8), 256, 0, (cudaStream_t)stream>>>(q, count, step, T);
+    RAHT_LAUNCH_CHECK();
+    return RAHT_OK;
+}
+
+RAHT_API size_t raht_sse_workspace_bytes(int64_t n, int D)
+{
+    (void)n; (void)D;
+    return (size_t)SSE_BLOCKS_MAX * 8 + 256;
+}
+
+RAHT_API int raht_sse_f64(const double *A, const double *B, int64_t n, int D, int c0, int c1, double *sse, void *workspace,
+                          size_t workspace_bytes, void *stream)
+{
+    RAHT_REQUIRE(n >= 0 && D >= 1 && c0 >= 0 && c1 <= D && c0 < c1 && sse && workspace, "raht_sse_f64: bad arguments");
+    if (workspace_bytes < raht_sse_workspace_bytes(n, D)) {
+        raht_set_error("raht_sse_f64: workspace too small");
+        return RAHT_E_WORKSPACE;
+    }
+    cudaStream_t st = (cudaStream_t)stream;
+    int nb = grid_for(n * (c1 - c0), 256, 8);
+    if (nb > SSE_BLOCKS_MAX) nb = SSE_BLOCKS_MAX;
+    if (n == 0) nb = 1;
+    sse_partial_kernel<<<nb, 256, 0, st>>>(A, B, n, D, c0, c1, (double *)workspace);
+    sse_final_kernel<<<1, 256, 0, st>>>((const double *)workspace, nb, sse);
+    RAHT_LAUNCH_CHECK();
+    return RAHT_OK;
+}

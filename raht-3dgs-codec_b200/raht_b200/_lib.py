@@ -1,0 +1,108 @@
+"""ctypes binding of libraht_b200.so (the C ABI declared in include/raht_b200.h).
+
+This is the only place the package touches the native library.  There is no CPU fallback and no
+alternative backend: if the library is missing, importing any operator module fails loudly.
+PyTorch is used for device memory, streams and (multi-GPU) torch.distributed only.
+"""
+import ctypes as C
+import os
+
+import torch
+
+_HERE = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+LIB_PATH = os.path.join(_HERE, "libraht_b200.so")
+
+RAHT_F32, RAHT_F64 = 0, 1
+ST_OUT_OF_BOUNDS, ST_NOT_SORTED_UNIQUE, ST_INT32_OVERFLOW, ST_STREAM_OVERFLOW, ST_SORT_STALL = 1, 2, 4, 8, 16
+FLAG_NO_TMA = 1
+
+if not os.path.exists(LIB_PATH):
+    raise ImportError(
+        f"{LIB_PATH} not found: build it with `make -C {_HERE} -j` (or __graft_entry__.build()). "
+        "raht-3dgs-codec_b200 has no CPU fallback."
+    )
+
+lib = C.CDLL(LIB_PATH)
+
+_p, _i, _i64, _sz, _d = C.c_void_p, C.c_int, C.c_int64, C.c_size_t, C.c_double
+
+# name -> (restype, argtypes); mirrors include/raht_b200.h exactly (tests check every symbol resolves)
+SIGNATURES = {
+    "raht_abi_version": (_i, []),
+    "raht_last_error": (C.c_char_p, []),
+    "raht_device_info": (_i, [C.POINTER(_i), C.POINTER(_i)]),
+    "raht_bounds3_f32": (_i, [_p, _i64, _i64, _p, _p]),
+    "raht_voxel_params": (_i, [_p, _i, _i, C.POINTER(C.c_float), _i, _d, _p, _p, _p]),
+    "raht_morton_keys_f32": (_i, [_p, _i64, _i64, _p, _i, _p, _p, _p]),
+    "raht_morton_keys_i64": (_i, [_p, _i64, _i, _p, _p]),
+    "raht_morton_keys_f64": (_i, [_p, _i64, C.POINTER(_d), _d, _i, _p, _p, _p]),
+    "raht_morton_decode_f32": (_i, [_p, _i64, _i, _p, _p]),
+    "raht_radix_sort_workspace_bytes": (_sz, [_i64, _i, _i]),
+    "raht_radix_sort_pairs": (_i, [_p, _p, _p, _p, _i64, _i, _i, _p, _p, _sz, _p]),
+    "raht_voxel_segments_workspace_bytes": (_sz, [_i64]),
+    "raht_voxel_segments": (_i, [_p, _i64, _p, _p, _p, _p, _p, _sz, _p]),
+    "raht_gather_rows_f32": (_i, [_p, _i64, _i64, _p, _p, _p, _p, _i64, _p]),
+    "raht_voxel_attr_mean_f32": (_i, [_p, _i64, _i64, _i, _p, _p, _i64, _p, _i64, _i, _p, _i64, _p]),
+    "raht_merge_segments": (_i, [_p, _p, _i64, _p, _p, _p, _p, _p, _i, _i, _p, _p, _p, _p, _p, _p, _i, _p]),
+    "raht_tree_levels": (_i, [_p, _i64, _p, _p, _p]),
+    "raht_tree_level_workspace_bytes": (_sz, [_i64]),
+    "raht_tree_level": (_i, [_p, _i64, _i, _p, _p, _p, _p, _p, _sz, _p]),
+    "raht_tree_max_level": (_i, [_p, _i64, _p, _p]),
+    "raht_order_ragft_workspace_bytes": (_sz, [_i64]),
+    "raht_order_ragft": (_i, [_p, _i64, _p, _p, _p, _sz, _p]),
+    "raht_plan_create": (_i, [_p, _i64, _i, _p, C.POINTER(_p), _p]),
+    "raht_plan_destroy": (None, [_p]),
+    "raht_plan_info": (_i, [_p, C.POINTER(_i64), _i]),
+    "raht_forward": (_i, [_p, _p, _i, _i, _p, _i, _i, _p]),
+    "raht_inverse": (_i, [_p, _p, _i, _i, _p, _i, _p]),
+    "raht_quant_reorder": (_i, [_p, _i, _i64, _i, _p, _p, _p, _i64, _p, _p]),
+    "raht_dequant_unreorder": (_i, [_p, _i64, _i64, _i, _p, _p, _p, _i, _p]),
+    "raht_quantize_f64": (_i, [_p, _i64, _d, _p, _p]),
+    "raht_dequantize_f64": (_i, [_p, _i64, _d, _p, _p]),
+    "raht_rlgr_encode_workspace_bytes": (_sz, [_i64, _i]),
+    "raht_rlgr_encode": (_i, [_p, _i64, _i64, _i, _i, _p, _i64, _p, _p, _p, _sz, _p]),
+    "raht_rlgr_decode": (_i, [_p, _i64, _p, _i64, _i64, _i, _i, _p, _p]),
+    "raht_sse_workspace_bytes": (_sz, [_i64, _i]),
+    "raht_sse_f64": (_i, [_p, _p, _i64, _i, _i, _i, _p, _p, _sz, _p]),
+}
+
+for _name, (_res, _args) in SIGNATURES.items():
+    _f = getattr(lib, _name)          # AttributeError here = header and library out of sync
+    _f.restype = _res
+    _f.argtypes = _args
+
+
+class RahtError(RuntimeError):
+    pass
+
+
+def check(rc: int, what: str = ""):
+    if rc != 0:
+        msg = lib.raht_last_error().decode("utf-8", "replace")
+        raise RahtError(f"{what or 'libraht_b200'} failed ({rc}): {msg}")
+
+
+def ptr(t):
+    """Device pointer of a tensor (None -> NULL)."""
+    return None if t is None else C.c_void_p(t.data_ptr())
+
+
+def stream():
+    return C.c_void_p(torch.cuda.current_stream().cuda_stream)
+
+
+def require_cuda(t: torch.Tensor, name: str):
+    if not isinstance(t, torch.Tensor) or not t.is_cuda:
+        raise RuntimeError(f"{name} must be a CUDA tensor (raht-3dgs-codec_b200 has no CPU path)")
+
+
+def workspace(nbytes: int, device) -> torch.Tensor:
+    return torch.empty(max(int(nbytes), 256), dtype=torch.uint8, device=device)
+
+
+def dtype_tag(dt: torch.dtype) -> int:
+    if dt == torch.float64:
+        return RAHT_F64
+    if dt == torch.float32:
+        return RAHT_F32
+    raise TypeError(f"unsupported dtype {dt}")

@@ -1,0 +1,157 @@
+"""End-to-end RAHT-3DGS encode / decode on one GPU: the call sequence of the reference drivers
+(python/test_voxelize_3dgs.py:198-265 for voxelise+merge, python/encode_3dgs.py:144-276 for
+RAHT_param -> RAHT -> quantise -> reorder -> RLGR and back) with every step on the device.
+
+Channel layout of the coded matrix (D = 11 + color_dim, 59 for 3DGS with 48 SH coefficients):
+[merged_means 3 | quats 4 | scales 3 | opacity 1 | colors].
+"""
+from dataclasses import dataclass, field
+from typing import Optional
+
+import torch
+
+from . import ops
+from . import _lib as L
+from ._lib import lib, check, ptr, stream
+
+
+@dataclass
+class EncodedScene:
+    J: int
+    n_in: int
+    nvox: int
+    D: int
+    step: object                      # scalar or per-channel steps
+    vmin: torch.Tensor                # (3,) fp32
+    voxel_size: float
+    width: float
+    keys: torch.Tensor                # (nvox,) int64 Morton codes of the occupied voxels (geometry side info)
+    streams: ops.RlgrStreams          # D closed RLGR streams
+    transform_dtype: torch.dtype = torch.float64
+    tree: Optional[ops.RahtTree] = field(default=None, repr=False)   # encoder-side cache (decoder rebuilds from keys)
+
+    def payload_bytes(self) -> int:
+        return self.streams.total_bytes()
+
+
+class StageTimer:
+    """CUDA-event timer per pipeline stage (events on the current stream)."""
+
+    def __init__(self, enabled=False):
+        self.enabled = enabled
+        self.marks = []
+
+    def mark(self, name):
+        if self.enabled:
+            e = torch.cuda.Event(enable_timing=True)
+            e.record()
+            self.marks.append((name, e))
+
+    def result(self):
+        if not self.enabled or len(self.marks) < 2:
+            return {}
+        torch.cuda.synchronize()
+        out = {}
+        for (_, e0), (name, e1) in zip(self.marks[:-1], self.marks[1:]):
+            out[name] = out.get(name, 0.0) + e0.elapsed_time(e1)
+        return out
+
+
+@torch.no_grad()
+def voxelize_merge(means, quats, scales, opacities, colors, J, packed_dtype=torch.float32, timer=None):
+    """Voxelise the Gaussian centres and merge the Gaussians of each voxel.
+    Returns (packed (nvox, D), unique_keys int64 (nvox), info dict)."""
+    timer = timer or StageTimer(False)
+    dev = means.device
+    N = means.shape[0]
+    st = stream()
+    means = means.contiguous().float()
+    bounds = torch.empty(6, dtype=torch.float32, device=dev)
+    params4 = torch.empty(4, dtype=torch.float32, device=dev)
+    params_d2 = torch.empty(2, dtype=torch.float64, device=dev)
+    check(lib.raht_bounds3_f32(ptr(means), N, 3, ptr(bounds), st), "raht_bounds3_f32")
+    check(lib.raht_voxel_params(ptr(bounds), J, 0, None, 0, 0.0, ptr(params4), ptr(params_d2), st), "raht_voxel_params")
+    keys = torch.empty(N, dtype=torch.int64, device=dev)
+    check(lib.raht_morton_keys_f32(ptr(means), N, 3, ptr(params4), J, ptr(keys), None, st), "raht_morton_keys_f32")
+    timer.mark("morton")
+    keys_sorted, idx32, status = ops.radix_sort_pairs(keys, 3 * J)
+    timer.mark("sort")
+    _, offsets, unique_keys, nvox = ops.voxel_segments(keys_sorted)
+    timer.mark("segments")
+    if int(status.item()) & L.ST_SORT_STALL:
+        raise RuntimeError("radix sort look-back stalled (internal error)")
+    _, packed = ops.merge_segments(idx32, offsets, means, quats.contiguous().float(), scales.contiguous().float(),
+                                   opacities.contiguous().float(), colors.contiguous().float(), True, separate=False,
+                                   packed_dtype=packed_dtype)
+    timer.mark("merge")
+    pd = params_d2.cpu().tolist()
+    info = {"Nvox": nvox, "N": N, "vmin": params4[:3].clone(), "width": pd[0], "voxel_size": pd[1], "sort_idx": idx32}
+    return packed, unique_keys.clone(), info
+
+
+@torch.no_grad()
+def encode_attributes(keys, Cmat, step, transform_dtype=torch.float64, tile_rows=None, timer=None, flags=0):
+    """RAHT_param -> RAHT -> quantise -> reorder -> RLGR for rows that are Morton-sorted unique voxels."""
+    timer = timer or StageTimer(False)
+    tree = ops.tree_from_keys(keys, validate=True)
+    order, _ = tree.order(want_position=True)
+    tree.plan(tile_rows)
+    timer.mark("raht_param")
+    T = ops.forward(tree, Cmat, transform_dtype, tile_rows, flags)
+    timer.mark("raht")
+    q = ops.quant_reorder(T, order, step)
+    timer.mark("quant_reorder")
+    streams = ops.rlgr_encode(q, 1)
+    timer.mark("rlgr_encode")
+    return tree, streams
+
+
+@torch.no_grad()
+def decode_attributes(keys, streams, D, step, transform_dtype=torch.float64, tree=None, tile_rows=None, timer=None, flags=0):
+    """RLGR^-1 -> dequantise -> inverse reorder -> iRAHT."""
+    timer = timer or StageTimer(False)
+    if tree is None:
+        tree = ops.tree_from_keys(keys, validate=True)
+        tree.plan(tile_rows)
+        timer.mark("raht_param_dec")
+    order = tree.order()
+    q = ops.rlgr_decode(streams, 1)
+    timer.mark("rlgr_decode")
+    T = ops.dequant_unreorder(q, order, step, transform_dtype)
+    timer.mark("dequant_unreorder")
+    Crec = ops.inverse(tree, T, tile_rows, flags)
+    timer.mark("iraht")
+    return Crec
+
+
+@torch.no_grad()
+def encode_scene(means, quats, scales, opacities, colors, J, step, transform_dtype=torch.float64, tile_rows=None,
+                 timer=None, flags=0) -> EncodedScene:
+    timer = timer or StageTimer(False)
+    timer.mark("start")
+    packed, keys, info = voxelize_merge(means, quats, scales, opacities, colors, J, torch.float32, timer)
+    tree, streams = encode_attributes(keys, packed, step, transform_dtype, tile_rows, timer, flags)
+    return EncodedScene(J=J, n_in=info["N"], nvox=info["Nvox"], D=packed.shape[1], step=step, vmin=info["vmin"],
+                        voxel_size=info["voxel_size"], width=info["width"], keys=keys, streams=streams,
+                        transform_dtype=transform_dtype, tree=tree)
+
+
+@torch.no_grad()
+def decode_scene(enc: EncodedScene, reuse_tree=False, tile_rows=None, timer=None, flags=0):
+    """Returns (voxel coordinates (nvox,3) fp32 integer-valued, attributes (nvox, D))."""
+    timer = timer or StageTimer(False)
+    timer.mark("start_dec")
+    Crec = decode_attributes(enc.keys, enc.streams, enc.D, enc.step, enc.transform_dtype,
+                             enc.tree if reuse_tree else None, tile_rows, timer, flags)
+    coords = torch.empty(enc.nvox, 3, dtype=torch.float32, device=enc.keys.device)
+    check(lib.raht_morton_decode_f32(ptr(enc.keys), enc.nvox, enc.J, ptr(coords), stream()), "raht_morton_decode_f32")
+    timer.mark("geometry")
+    return coords, Crec
+
+
+def psnr(Cref: torch.Tensor, Crec: torch.Tensor, c0=0, c1=None) -> float:
+    """-10 log10(mean((C - C_rec)^2) + 1e-10)   (encode_3dgs.py:298-299)."""
+    import math
+    c1 = Cref.shape[1] if c1 is None else c1
+    s = float(ops.sse(Cref.to(torch.float64), Crec.to(torch.float64), c0, c1).item())
+    return -10.0 * math.log10(s / (Cref.shape[0] * (c1 - c0)) + 1e-10)

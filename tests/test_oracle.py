@@ -1,0 +1,159 @@
+"""CPU tests (-m "not gpu"): the C oracle against the golden fixtures generated from the reference
+(tests/golden/make_golden.py) and against the known-answer vectors of SURVEY App. B.
+When /root/reference is present the oracle is additionally checked against the reference run live."""
+import os
+
+import numpy as np
+import pytest
+
+import helpers
+from oracle import oracle_ctypes as orc
+
+
+@pytest.mark.parametrize("name", helpers.RAHT_CASES)
+def test_oracle_tree_transform_vs_golden(name):
+    g = helpers.load(name)
+    V, J = g["V"], int(g["J"])
+    MC = orc.morton(V, J)
+    assert np.array_equal(MC, helpers.morton_np(V))
+    assert np.all(np.diff(MC) > 0)
+    MCf, rc = orc.morton_from_f64(V.astype(np.float64), np.zeros(3), 2 ** J, J)
+    assert rc == 0 and np.array_equal(MCf, MC)
+    t = orc.Tree(MC, J)
+    levels = helpers.split_levels(g)
+    assert t.nlevels == int(g["nlevels"]) == len(levels)
+    for l, (lst, fl, w) in enumerate(levels):
+        a, b, c = t.level(l)
+        assert np.array_equal(a, lst) and np.array_equal(b, fl) and np.array_equal(c, w), f"level {l}"
+    assert np.array_equal(t.order(), g["order"])
+    T, w = t.forward(g["C"])
+    assert np.array_equal(T, g["T"]), "forward RAHT must be bit-exact with RAHT2_optimized"
+    assert np.array_equal(w, g["w"])
+    assert np.array_equal(t.inverse(T), g["C_lossless"])
+    for s in g["steps"]:
+        s = int(s)
+        q = orc.quantize(T, s)[t.order()].T.astype(np.int32)
+        assert np.array_equal(q, g[f"q_step{s}"])
+        streams = helpers.split_streams(g, s)
+        for ch in range(q.shape[0]):
+            buf = orc.rlgr_encode(q[ch].astype(np.int64), 1)
+            assert buf == streams[ch], f"step {s} channel {ch}"
+            assert np.array_equal(orc.rlgr_decode(buf, q.shape[1], 1), q[ch])
+        inv = np.argsort(t.order(), kind="stable")
+        Tdec = orc.dequantize(q.T.astype(np.float64), s)[inv]
+        assert np.array_equal(t.inverse(Tdec), g[f"C_rec_step{s}"])
+
+
+def test_oracle_rlgr_kats():
+    for seq, out, fs in helpers.rlgr_kats():
+        assert orc.rlgr_encode(seq, fs) == out
+        assert np.array_equal(orc.rlgr_decode(out, len(seq), fs), seq)
+
+
+def test_survey_appendix_b_hex():
+    kat = {(0,): "00", (1,): "40", (-1,): "20", tuple([0] * 16): "0740", tuple([0] * 100): "07f900",
+           (-4, -3, -2, -1, 0, 1, 2, 3, 4): "b969bdcc00", (0, 0, 0, 0, 1): "0420", (0, 0, 0, 0, -1): "0400",
+           (0, 0, 0, 0, 2): "0450", (0, 0, 0, 5, -3, 0, 0, 0, 0, 0, 0, 0, 1, 0, 0): "03e99b30",
+           (100000, -100000, 2147483647, -2147483648): "ffffffff00030d400001869fdfffffffafffffffe0"}
+    for seq, hx in kat.items():
+        assert orc.rlgr_encode(np.array(seq, dtype=np.int64), 1).hex() == hx
+    assert orc.rlgr_encode(np.array([0, 3, 0, 0, 20, 1], dtype=np.int64), 0).hex() == "147fe800"
+
+
+@pytest.mark.parametrize("name", helpers.VOX_CASES)
+def test_oracle_voxelize_vs_golden(name):
+    g = helpers.load(name)
+    PC, J = g["PC"], int(g["J"])
+    vmin = g["vmin_in"] if g["vmin_in"].size else None
+    width = float(g["width_in"][0]) if g["width_in"].size else None
+    r = orc.voxelize(PC[:, :3], J, vmin, width)
+    assert r["Nvox"] == int(g["Nvox"])
+    assert np.array_equal(r["sort_idx"], g["sort_idx"])
+    assert np.array_equal(r["voxel_indices"], g["voxel_indices"])
+    assert r["voxel_size"] == float(g["voxel_size"]) and r["width"] == float(g["width"])
+    assert np.array_equal(r["vmin"], g["vmin"])
+    Vvox = r["Vint"][r["sort_idx"]][r["voxel_indices"]].astype(np.float32)
+    assert np.array_equal(Vvox, g["PCvox"][:, :3])
+    assert np.array_equal(r["DeltaV"], g["DeltaPC"][:, :3])
+    assert np.array_equal(PC[r["sort_idx"]], g["PCsorted"])
+    if PC.shape[1] > 3:
+        Cvox = orc.voxel_attr_mean(PC[:, 3:], r["sort_idx"], r["voxel_indices"])
+        assert np.array_equal(Cvox, g["PCvox"][:, 3:])
+
+
+def test_oracle_rgb_to_yuv():
+    g = helpers.load("rgb_to_yuv")
+    np.testing.assert_allclose(orc.rgb_to_yuv(g["rgb"]), g["yuv"], rtol=0, atol=1e-10)
+
+
+def test_oracle_properties():
+    """Invariants the reference asserts or prints: perfect reconstruction, orthonormality,
+    DC = sqrt(N) * mean, order is a permutation."""
+    P, MC = helpers.unique_sorted_voxels(20000, 10, 7)
+    rng = np.random.default_rng(3)
+    Cm = rng.normal(size=(len(MC), 4))
+    t = orc.Tree(MC, 10)
+    T, w = t.forward(Cm)
+    np.testing.assert_allclose(t.inverse(T), Cm, rtol=0, atol=1e-10)
+    np.testing.assert_allclose(np.linalg.norm(T, axis=0), np.linalg.norm(Cm, axis=0), rtol=1e-12)
+    np.testing.assert_allclose(T[0], np.sqrt(len(MC)) * Cm.mean(0), rtol=1e-10)
+    assert np.array_equal(np.sort(t.order()), np.arange(len(MC)))
+    assert w[0] == len(MC)
+
+
+def test_oracle_rlgr_vs_reference_coder_random():
+    if not orc.ref_rlgr_available():
+        pytest.skip("oracle/_ref/librlgr_ref.so not built")
+    rng = np.random.default_rng(11)
+    for zfrac, scale in [(0.0, 2.0), (0.5, 10.0), (0.9, 3.0), (0.99, 1.0), (0.2, 1e6)]:
+        x = np.rint(rng.laplace(0, scale, size=5000)).astype(np.int64)
+        x[rng.random(5000) < zfrac] = 0
+        ref, _ = orc.ref_rlgr_encode(x, 1)
+        assert orc.rlgr_encode(x, 1) == ref
+        dec, _ = orc.ref_rlgr_decode(ref, len(x), 1)
+        assert np.array_equal(dec, x)
+
+
+@pytest.mark.skipif(not os.path.isdir("/root/reference/python"), reason="reference checkout absent")
+def test_oracle_vs_reference_live():
+    """Run the reference's Python operators here (torch CPU) on a fresh seeded cloud."""
+    import sys
+    import importlib
+    import torch
+    sys.path.insert(0, "/root/reference/python")
+    try:
+        for m in ("RAHT_param", "RAHT", "iRAHT"):
+            sys.modules.pop(m, None)
+        ref_param = importlib.import_module("RAHT_param")
+        ref_raht = importlib.import_module("RAHT")
+        ref_iraht = importlib.import_module("iRAHT")
+        assert ref_param.__file__.startswith("/root/reference")
+        P, MC = helpers.unique_sorted_voxels(6000, 9, 99)
+        Cm = np.random.default_rng(5).normal(size=(len(MC), 7))
+        Vt = torch.from_numpy(P.astype(np.float64))
+        List, Flags, weights, order = ref_param.RAHT_param_reorder_fast(Vt, torch.zeros(3, dtype=torch.float64), 2 ** 9, 9)
+        # as shipped: torch-CPU sqrt (MKL VML) is 1 ulp off for ~0.7 % of inputs -> compare with the
+        # tolerance the reference's own crosscheck.compare_RAHT_outputs uses (rtol = atol = 1e-12)
+        T_raw, _ = ref_raht.RAHT2_optimized(torch.from_numpy(Cm), List, Flags, weights)
+        # with the IEEE-754 square root (what torch computes on CUDA, the reference's production device)
+        orig_sqrt = torch.sqrt
+        torch.sqrt = lambda x: torch.from_numpy(np.sqrt(x.numpy()))
+        try:
+            T, w = ref_raht.RAHT2_optimized(torch.from_numpy(Cm), List, Flags, weights)
+            Crec = ref_iraht.inverse_RAHT_optimized(T, List, Flags, weights)
+        finally:
+            torch.sqrt = orig_sqrt
+        t = orc.Tree(MC, 9)
+        assert t.nlevels == len(Flags)
+        for l in range(t.nlevels):
+            a, b, c = t.level(l)
+            assert np.array_equal(a, List[l].numpy()) and np.array_equal(b, Flags[l].numpy()) and np.array_equal(c, weights[l].numpy())
+        assert np.array_equal(t.order(), order.numpy())
+        To, wo = t.forward(Cm)
+        assert np.array_equal(To, T.numpy()) and np.array_equal(wo, w.numpy().reshape(-1))
+        np.testing.assert_allclose(To, T_raw.numpy(), rtol=1e-12, atol=1e-12)
+        assert np.array_equal(t.inverse(To), Crec.numpy())
+    finally:
+        sys.path.remove("/root/reference/python")
+        for m in ("RAHT_param", "RAHT", "iRAHT"):
+            sys.modules.pop(m, None)
