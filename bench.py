@@ -1,0 +1,359 @@
+#!/usr/bin/env python
+"""bench.py -- Gaussians/s of the full RAHT-3DGS encode + decode (59 channels) on B200.
+
+One "step" = one pass of the hot path over one synthetic scene:
+    encode: voxelise (Morton, radix sort, segments) -> merge -> RAHT_param (tree, plan, order) ->
+            RAHT (fp64) -> quantise + reorder -> RLGR encode (59 streams)
+    decode: RAHT_param from the voxel keys -> RLGR decode -> dequantise + inverse reorder -> iRAHT
+`value`  : Gaussians/s with the scene already resident in HBM (CUDA events, max over ranks).
+`e2e`    : the same through the public Python API from pinned HOST buffers, H2D of the scene and D2H
+           of the bitstreams and of the decoded attributes inside the timed region.
+`roofline`: the dominant kernel family of the step, algorithmic bytes / measured duration vs the
+           measured HBM peak of MEASURED_PEAKS.json.
+`cpu_baseline` / --impl reference: the CPU restatement of the reference path (oracle/, plus the
+           reference's own RLGR coder from oracle/_ref when built) on the host cores.
+N > 1 ranks (torchrun): every rank codes its own scene (scene-per-GPU, BASELINE config 5) -- weak scaling,
+no data-path collective.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+for p in (ROOT, os.path.join(ROOT, "raht-3dgs-codec_b200"), os.path.join(ROOT, "tests")):
+    if p not in sys.path:
+        sys.path.insert(0, p)
+
+import numpy as np  # noqa: E402
+
+WORKLOADS = {
+    # name: (n_gaussians, depth, description)          BASELINE.json configs[1] / configs[2]
+    "c2": (1_000_000, 12, "3DGS scene 1M Gaussians, 59 channels, depth 12 (BASELINE configs[1])"),
+    "c3": (6_000_000, 16, "3DGS scene 6M Gaussians, 59 channels, depth 16 (BASELINE configs[2])"),
+    "tiny": (50_000, 10, "smoke-sized scene"),
+}
+STEP = 1.0 / 64          # uniform quantisation step applied to all 59 channels
+D = 59
+
+
+def load_peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        return float(json.load(open(p))["hbm_gbs"]), "measured (MEASURED_PEAKS.json)"
+    return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+# ---------------------------------------------------------------------------------------------------
+# CPU path (oracle): used for cpu_baseline and for --impl reference
+# ---------------------------------------------------------------------------------------------------
+def cpu_pipeline(scene, J, step, use_ref_rlgr):
+    """Full encode + decode on the host with the CPU restatement of the reference (oracle/)."""
+    from oracle import oracle_ctypes as orc
+    means, quats, scales, opac, colors = scene
+    n = means.shape[0]
+    r = orc.voxelize(means, J, want_delta=False)
+    coff = np.concatenate([r["voxel_indices"], [n]]).astype(np.int32)
+    mm, mq, ms, mo, mc = orc.merge_clusters(r["sort_idx"].astype(np.int32), coff, means, quats, scales, opac, colors, True)
+    packed = np.concatenate([mm, mq, ms, mo[:, None], mc], 1).astype(np.float64)
+    keys = r["MC_sorted"][r["voxel_indices"]]
+    t = orc.Tree(keys, J)
+    T, _ = t.forward(packed)
+    order = t.order()
+    q = np.ascontiguousarray(orc.quantize(T, step)[order].T.astype(np.int32))
+    nvox = q.shape[1]
+    if use_ref_rlgr:
+        streams = [orc.ref_rlgr_encode(q[c].astype(np.int64), 1)[0] for c in range(q.shape[0])]
+        qd = np.stack([orc.ref_rlgr_decode(streams[c], nvox, 1)[0] for c in range(q.shape[0])]).astype(np.int32)
+    else:
+        _, out, cap, nb = orc.rlgr_encode_channels(q, 1)
+        qd = orc.rlgr_decode_channels(out, cap, nb, nvox, q.shape[0], 1)
+    # decoder side: tree again from the keys, dequantise, inverse reorder, iRAHT
+    t2 = orc.Tree(keys, J)
+    inv = np.argsort(t2.order(), kind="stable")
+    Tdec = orc.dequantize(qd.T.astype(np.float64), step)[inv]
+    Crec = t2.inverse(Tdec)
+    return nvox, Crec
+
+
+def time_cpu(scene, J, step, sample_n, reps, use_ref_rlgr):
+    sample = tuple(a[:sample_n] for a in scene)
+    best = None
+    for _ in range(reps):
+        t0 = time.perf_counter()
+        cpu_pipeline(sample, J, step, use_ref_rlgr)
+        dt = time.perf_counter() - t0
+        best = dt if best is None else min(best, dt)
+    return sample_n / best, best
+
+
+# ---------------------------------------------------------------------------------------------------
+class ClockSampler:
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, gpu_index):
+        self.idx = gpu_index
+        self.rows = []
+        self.proc = None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "100",
+                                          "-i", str(self.idx)], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.thread = threading.Thread(target=self._read, daemon=True)
+            self.thread.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append(line.strip())
+
+    def stop(self):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=2)
+        except Exception:
+            self.proc.kill()
+        sm, mx, reasons = [], None, set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for r in self.rows:
+            f = [x.strip() for x in r.split(",")]
+            if len(f) < 8:
+                continue
+            try:
+                sm.append(float(f[1])); mx = float(f[2])
+            except ValueError:
+                continue
+            for nm, v in zip(names, f[4:8]):
+                if v.lower().startswith("active"):
+                    reasons.add(nm)
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": mx, "reasons": sorted(reasons), "samples": len(sm)}
+
+
+def stage_bytes(nvox, n_in, payload, J):
+    """Algorithmic (compulsory) bytes per stage for one step, SURVEY 8(d)."""
+    passes = (3 * J + 7) // 8
+    return {
+        "morton": n_in * 24, "sort": n_in * 24 * passes, "segments": n_in * 8 + nvox * 20,
+        "merge": n_in * (12 + 236) + nvox * 236,
+        "raht_param": nvox * 21, "raht_param_dec": nvox * 21,
+        "raht": nvox * (D * 4 + D * 8 + 13),            # fp32 packed rows in, fp64 coefficients out
+        "quant_reorder": nvox * (D * 8 + 8 + D * 4),
+        "rlgr_encode": nvox * D * 4 + payload,
+        "rlgr_decode": payload + nvox * D * 4,
+        "dequant_unreorder": nvox * (D * 4 + 8 + D * 8),
+        "iraht": nvox * (2 * D * 8 + 13),
+        "geometry": nvox * 20,
+    }
+
+
+def run_gpu(args):
+    import torch
+    import torch.distributed as dist
+    import helpers
+    from raht_b200 import codec, ops
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    n, J, desc = WORKLOADS[args.workload]
+    if args.n:
+        n = args.n
+    tdtype = torch.float64 if args.dtype == "f64" else torch.float32
+
+    scene = helpers.synthetic_gaussians(n, 2001 + rank)
+    host = [torch.from_numpy(a).pin_memory() for a in scene]
+    devt = [h.to(dev) for h in host]
+    h2d_bytes = sum(h.numel() * h.element_size() for h in host)
+
+    def step_resident(timer=None):
+        enc = codec.encode_scene(*devt, J=J, step=STEP, transform_dtype=tdtype, tile_rows=args.tile_rows, timer=timer)
+        coords, Crec = codec.decode_scene(enc, reuse_tree=False, tile_rows=args.tile_rows, timer=timer)
+        return enc, Crec
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    for _ in range(args.warmup):
+        enc, Crec = step_resident()
+    barrier()
+    nvox, payload = enc.nvox, enc.payload_bytes()
+
+    # ---- timed region: device-resident inputs ------------------------------------------------------
+    clocks = ClockSampler(local)
+    clocks.start()
+    timers = []
+    launches0 = ops.lib.raht_launch_count()
+    barrier()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(args.steps):
+        tm = codec.StageTimer(True)
+        step_resident(tm)
+        timers.append(tm)
+    e1.record()
+    barrier()
+    ms_total = e0.elapsed_time(e1)
+    launches = (ops.lib.raht_launch_count() - launches0) // max(args.steps, 1)
+    clk = clocks.stop()
+    t = torch.tensor([ms_total], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms_step = float(t.item()) / args.steps
+    value = n * world / (ms_step / 1e3)
+
+    stages = {}
+    for tm in timers:
+        for k, v in tm.result().items():
+            stages[k] = stages.get(k, 0.0) + v / len(timers)
+
+    # ---- end to end from host buffers ------------------------------------------------------------
+    def step_e2e():
+        dv = [h.to(dev, non_blocking=True) for h in host]
+        enc = codec.encode_scene(*dv, J=J, step=STEP, transform_dtype=tdtype, tile_rows=args.tile_rows)
+        sizes = enc.streams.nbytes.cpu()
+        slot = enc.streams.slot_bytes
+        compact = torch.cat([enc.streams.buf[c * slot: c * slot + int(sizes[c])] for c in range(enc.D)])
+        out_host = compact.cpu()                                   # the bitstreams leave the device
+        keys_host = enc.keys.cpu()                                 # geometry side information
+        coords, Crec = codec.decode_scene(enc, reuse_tree=False, tile_rows=args.tile_rows)
+        rec_host = Crec.cpu()                                      # decoded attributes back on the host
+        return out_host.numel() + keys_host.numel() * 8 + sizes.numel() * 8 + rec_host.numel() * rec_host.element_size()
+
+    d2h = step_e2e()
+    barrier()
+    t0 = time.perf_counter()
+    e0.record()
+    for _ in range(args.steps):
+        d2h = step_e2e()
+    e1.record()
+    barrier()
+    ms_e2e = e0.elapsed_time(e1)
+    t = torch.tensor([ms_e2e], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    e2e_value = n * world / (float(t.item()) / args.steps / 1e3)
+    wall_e2e = time.perf_counter() - t0
+
+    if rank != 0:
+        if world > 1:
+            dist.destroy_process_group()
+        return
+
+    peak, peak_src = load_peaks()
+    sb = stage_bytes(nvox, n, payload, J)
+    dom = max(stages, key=stages.get) if stages else None
+    roofline = None
+    if dom:
+        achieved = sb.get(dom, 0) / (stages[dom] / 1e3) / 1e9
+        roofline = {"bound": "hbm", "kernel": dom, "achieved": round(achieved, 2), "peak": peak, "unit": "GB/s",
+                    "frac": round(achieved / peak, 4), "traffic": None, "peak_source": peak_src,
+                    "algorithmic_bytes_per_launch": sb.get(dom, 0), "ms_per_launch": round(stages[dom], 4)}
+    per_stage = {k: {"ms": round(v, 4), "GBps": round(sb.get(k, 0) / (v / 1e3) / 1e9, 1) if v > 0 else None,
+                     "frac_of_peak": round(sb.get(k, 0) / (v / 1e3) / 1e9 / peak, 4) if v > 0 else None}
+                 for k, v in stages.items()}
+
+    cpu = None
+    if world == 1 and not args.no_cpu_baseline:
+        from oracle import oracle_ctypes as orc
+        sample = min(n, args.cpu_sample)
+        v, secs = time_cpu(scene, J, STEP, sample, 1, False)
+        cpu = {"value": round(v, 1), "unit": "Gaussians/s", "cores": orc.num_threads(), "kind": "port",
+               "sample": f"first {sample} Gaussians of the same scene, full encode+decode once ({secs:.1f} s), oracle/raht_oracle.c with OpenMP"}
+
+    line = {
+        "metric": "Gaussians/s full RAHT encode+decode (59 ch)", "value": round(value, 1), "unit": "Gaussians/s",
+        "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": round(ms_step, 4),
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": args.dtype, "data": "synthetic",
+        "config": {"workload": desc, "n_gaussians_per_gpu": n, "nvox": nvox, "depth": J, "channels": D, "quant_step": STEP,
+                   "tile_rows": args.tile_rows or ops.DEFAULT_TILE_ROWS, "payload_bytes": payload,
+                   "bits_per_voxel": round(payload * 8 / nvox, 3),
+                   "l2": "inputs (236 MB per scene) and every intermediate exceed the 126 MB L2; no explicit flush",
+                   "parallelism": "scene-per-GPU (no collective)" if world > 1 else "single GPU",
+                   "decoder": "rebuilds the tree from the voxel keys (no encoder state reused)"},
+        "clocks": clk,
+        "e2e": {"value": round(e2e_value, 1), "unit": "Gaussians/s", "h2d_bytes_per_step": h2d_bytes, "d2h_bytes_per_step": int(d2h),
+                "wall_s": round(wall_e2e, 3)},
+        "gpu_launches": int(launches),
+        "roofline": roofline,
+        "stages": per_stage,
+        "cpu_baseline": cpu,
+    }
+    print(json.dumps(line))
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def run_reference(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    import helpers
+    from oracle import oracle_ctypes as orc
+    n, J, desc = WORKLOADS[args.workload]
+    if args.n:
+        n = args.n
+    sample = min(n, args.cpu_sample)
+    scene = helpers.synthetic_gaussians(n, 2001)
+    use_ref = orc.ref_rlgr_available() and not args.port_rlgr
+    sub = tuple(a[:sample] for a in scene)
+    for _ in range(args.warmup):
+        cpu_pipeline(sub, J, STEP, use_ref)
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        nvox, _ = cpu_pipeline(sub, J, STEP, use_ref)
+    secs = (time.perf_counter() - t0) / args.steps
+    v = sample / secs
+    kind = "port"   # the transform/voxeliser are the C restatement; only the entropy coder is the reference's own object code
+    cpu = {"value": round(v, 1), "unit": "Gaussians/s", "cores": orc.num_threads(), "kind": kind,
+           "sample": f"first {sample} Gaussians of the scene per step; oracle/raht_oracle.c (OpenMP) + "
+                     + ("reference RLGR coder oracle/_ref/librlgr_ref.so (1 thread, as the reference)" if use_ref else "oracle RLGR (1 thread per channel)")}
+    line = {
+        "impl": "reference", "metric": "Gaussians/s full RAHT encode+decode (59 ch)", "value": round(v, 1), "unit": "Gaussians/s",
+        "n_gpus": int(os.environ.get("WORLD_SIZE", "1")), "steps": args.steps, "warmup": args.warmup, "ms_per_step": round(secs * 1e3, 2),
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+        "config": {"workload": desc, "n_gaussians_per_gpu": n, "nvox": int(nvox), "depth": J, "channels": D, "quant_step": STEP},
+        "cpu_baseline": cpu,
+        "e2e": {"value": round(v, 1), "unit": "Gaussians/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+    }
+    print(json.dumps(line))
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--workload", default="c2", choices=sorted(WORKLOADS))
+    ap.add_argument("--n", type=int, default=0, help="override the number of Gaussians")
+    ap.add_argument("--dtype", default="f64", choices=["f64", "f32"], help="transform arithmetic (f64 = bit-exact mode)")
+    ap.add_argument("--tile-rows", type=int, default=0)
+    ap.add_argument("--cpu-sample", type=int, default=250_000)
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--port-rlgr", action="store_true", help="reference arm: use the oracle RLGR port instead of oracle/_ref")
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 3) if args.impl == "b200" else args.warmup
+    args.tile_rows = args.tile_rows or None
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_gpu(args)
+
+
+if __name__ == "__main__":
+    main()

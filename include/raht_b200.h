@@ -53,6 +53,8 @@ enum {
 };
 
 int raht_abi_version(void);
+/* kernels launched by this process through the library so far (bench.py reports the per-step delta) */
+long long raht_launch_count(void);
 const char *raht_last_error(void);
 /* number of SMs / compute capability of the current device (major*10+minor); <0 on error */
 int raht_device_info(int *sm_count, int *cc);

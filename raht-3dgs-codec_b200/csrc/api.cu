@@ -3,6 +3,10 @@
 #include <string.h>
 
 static thread_local char g_err[512] = "";
+static long long g_launches = 0;
+
+void raht_count_launches(int n) { __atomic_fetch_add(&g_launches, (long long)n, __ATOMIC_RELAXED); }
+RAHT_API long long raht_launch_count(void) { return __atomic_load_n(&g_launches, __ATOMIC_RELAXED); }
 
 void raht_set_error(const char *fmt, ...)
 {

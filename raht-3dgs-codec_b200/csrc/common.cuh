@@ -9,6 +9,7 @@
 #define RAHT_API extern "C" __attribute__((visibility("default")))
 
 void raht_set_error(const char *fmt, ...);
+void raht_count_launches(int n);   // bookkeeping for raht_launch_count() (bench.py reports it)
 
 #define RAHT_REQUIRE(cond, ...)                                                                    \
     do {                                                                                           \
@@ -189,13 +190,14 @@ template <typename Pred, typename Emit>
 static inline int device_select(int64_t n, Pred pred, Emit emit, int64_t *count_out, void *ws, cudaStream_t st)
 {
     int64_t nb = sel_num_blocks(n);
+    raht_count_launches(n ? 2 : 0);
     unsigned long long *counts = (unsigned long long *)ws;
     if (n == 0) {
-        scan_counts_kernel<<<1, 1024, 0, st>>>(counts, 0, count_out);
+        (raht_count_launches(1), scan_counts_kernel)<<<1, 1024, 0, st>>>(counts, 0, count_out);
         return 0;
     }
     sel_count_kernel<<<(unsigned)nb, SEL_THREADS, 0, st>>>(n, pred, counts);
-    scan_counts_kernel<<<1, 1024, 0, st>>>(counts, nb, count_out);
+    (raht_count_launches(1), scan_counts_kernel)<<<1, 1024, 0, st>>>(counts, nb, count_out);
     sel_scatter_kernel<<<(unsigned)nb, SEL_THREADS, 0, st>>>(n, pred, emit, counts);
     return 0;
 }

@@ -96,6 +96,7 @@ RAHT_API int raht_merge_segments(const int32_t *cluster_indices, const int32_t *
     cudaStream_t st = (cudaStream_t)stream;
     int64_t total = num_clusters * (11 + color_dim);
     int grid = grid_for(total, 256, 8);
+    raht_count_launches(1);
     if (packed && packed_dtype == RAHT_F64)
         merge_kernel<double><<<grid, 256, 0, st>>>(cluster_indices, cluster_offsets, num_clusters, means, quats, scales,
                                                    opacities, colors, color_dim, weight_by_opacity, m_means, m_quats,

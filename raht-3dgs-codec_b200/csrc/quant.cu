@@ -143,6 +143,7 @@ RAHT_API int raht_quant_reorder(const void *T, int t_dtype, int64_t n, int D, co
     RAHT_REQUIRE(smem <= 227 * 1024, "raht_quant_reorder: D too large");
     cudaStream_t st = (cudaStream_t)stream;
     unsigned grid = (unsigned)((n + QR_P - 1) / QR_P);
+    raht_count_launches(1);
     if (t_dtype == RAHT_F64) {
         RAHT_CUDA(cudaFuncSetAttribute(quant_reorder_kernel<double>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         quant_reorder_kernel<double><<<grid, QR_THREADS, smem, st>>>((const double *)T, n, D, order, steps, q, ld, status);
@@ -167,6 +168,7 @@ RAHT_API int raht_dequant_unreorder(const int32_t *q, int64_t ld, int64_t n, int
     RAHT_REQUIRE(smem <= 227 * 1024, "raht_dequant_unreorder: D too large");
     cudaStream_t st = (cudaStream_t)stream;
     unsigned grid = (unsigned)((n + QR_P - 1) / QR_P);
+    raht_count_launches(1);
     if (t_dtype == RAHT_F64) {
         RAHT_CUDA(cudaFuncSetAttribute(dequant_unreorder_kernel<double>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         dequant_unreorder_kernel<double><<<grid, QR_THREADS, smem, st>>>(q, ld, n, D, order, steps, (double *)T);
@@ -185,7 +187,7 @@ RAHT_API int raht_quantize_f64(const double *T, int64_t count, double step, doub
 {
     RAHT_REQUIRE(count >= 0 && (count == 0 || (T && q)), "raht_quantize_f64: bad arguments");
     if (count == 0) return RAHT_OK;
-    quantize_kernel<<<grid_for(count, 256, 8), 256, 0, (cudaStream_t)stream>>>(T, count, step, q);
+    (raht_count_launches(1), quantize_kernel)<<<grid_for(count, 256, 8), 256, 0, (cudaStream_t)stream>>>(T, count, step, q);
     RAHT_LAUNCH_CHECK();
     return RAHT_OK;
 }
@@ -194,7 +196,7 @@ RAHT_API int raht_dequantize_f64(const double *q, int64_t count, double step, do
 {
     RAHT_REQUIRE(count >= 0 && (count == 0 || (T && q)), "raht_dequantize_f64: bad arguments");
     if (count == 0) return RAHT_OK;
-    dequantize_kernel<<<grid_for(count, 256, 8), 256, 0, (cudaStream_t)stream>>>(q, count, step, T);
+    (raht_count_launches(1), dequantize_kernel)<<<grid_for(count, 256, 8), 256, 0, (cudaStream_t)stream>>>(q, count, step, T);
     RAHT_LAUNCH_CHECK();
     return RAHT_OK;
 }
@@ -217,8 +219,8 @@ RAHT_API int raht_sse_f64(const double *A, const double *B, int64_t n, int D, in
     int nb = grid_for(n * (c1 - c0), 256, 8);
     if (nb > SSE_BLOCKS_MAX) nb = SSE_BLOCKS_MAX;
     if (n == 0) nb = 1;
-    sse_partial_kernel<<<nb, 256, 0, st>>>(A, B, n, D, c0, c1, (double *)workspace);
-    sse_final_kernel<<<1, 256, 0, st>>>((const double *)workspace, nb, sse);
+    (raht_count_launches(1), sse_partial_kernel)<<<nb, 256, 0, st>>>(A, B, n, D, c0, c1, (double *)workspace);
+    (raht_count_launches(1), sse_final_kernel)<<<1, 256, 0, st>>>((const double *)workspace, nb, sse);
     RAHT_LAUNCH_CHECK();
     return RAHT_OK;
 }

@@ -255,8 +255,8 @@ RAHT_API int raht_radix_sort_pairs(const uint64_t *keys_in, uint64_t *keys_out, 
 
     // zero histograms, tickets (one per pass) and tile states in one memset
     RAHT_CUDA(cudaMemsetAsync(ws, 0, L.off_keys, st));
-    rs_hist_kernel<<<grid_for(n, RS_THREADS * 8, 4), RS_THREADS, 0, st>>>(keys_in, n, begin_bit, L.passes, end_bit, ghist);
-    rs_scan_kernel<<<L.passes, RS_RADIX, 0, st>>>(ghist);
+    (raht_count_launches(1), rs_hist_kernel)<<<grid_for(n, RS_THREADS * 8, 4), RS_THREADS, 0, st>>>(keys_in, n, begin_bit, L.passes, end_bit, ghist);
+    (raht_count_launches(1), rs_scan_kernel)<<<L.passes, RS_RADIX, 0, st>>>(ghist);
     RAHT_LAUNCH_CHECK();
 
     // ping-pong so that the last pass lands in keys_out / vals_out
@@ -268,7 +268,7 @@ RAHT_API int raht_radix_sort_pairs(const uint64_t *keys_in, uint64_t *keys_out, 
         uint32_t *dst_v = to_out ? vals_out : tmp_vals;
         int sh = begin_bit + p * RS_BITS;
         int nb = end_bit - sh < RS_BITS ? end_bit - sh : RS_BITS;
-        rs_onesweep_kernel<<<(unsigned)L.tiles, RS_THREADS, 0, st>>>(
+        (raht_count_launches(1), rs_onesweep_kernel)<<<(unsigned)L.tiles, RS_THREADS, 0, st>>>(
             src_k, dst_k, src_v, dst_v, n, sh, (1u << nb) - 1u, ghist + (size_t)p * RS_RADIX,
             state + (size_t)p * (size_t)L.tiles * RS_RADIX, ticket + p, status);
         RAHT_LAUNCH_CHECK();

@@ -215,7 +215,7 @@ RAHT_API int raht_rlgr_encode(const int32_t *q, int64_t n, int64_t ld, int nch, 
     if (nch == 0) return RAHT_OK;
     RAHT_REQUIRE((q || n == 0) && streams && nbytes, "raht_rlgr_encode: null pointer");
     RAHT_REQUIRE(((uintptr_t)streams & 7) == 0, "raht_rlgr_encode: streams must be 8-byte aligned");
-    rlgr_encode_serial_kernel<<<nch, 32, 0, (cudaStream_t)stream>>>(q, n, ld, flag_signed, streams, slot_bytes, nbytes, status);
+    (raht_count_launches(1), rlgr_encode_serial_kernel)<<<nch, 32, 0, (cudaStream_t)stream>>>(q, n, ld, flag_signed, streams, slot_bytes, nbytes, status);
     RAHT_LAUNCH_CHECK();
     return RAHT_OK;
 }
@@ -228,7 +228,7 @@ RAHT_API int raht_rlgr_decode(const uint8_t *streams, int64_t slot_bytes, const 
     if (nch == 0 || n == 0) return RAHT_OK;
     RAHT_REQUIRE(streams && q, "raht_rlgr_decode: null pointer");
     RAHT_REQUIRE(((uintptr_t)streams & 7) == 0, "raht_rlgr_decode: streams must be 8-byte aligned");
-    rlgr_decode_serial_kernel<<<nch, 32, 0, (cudaStream_t)stream>>>(streams, slot_bytes, nbytes, n, ld, flag_signed, q);
+    (raht_count_launches(1), rlgr_decode_serial_kernel)<<<nch, 32, 0, (cudaStream_t)stream>>>(streams, slot_bytes, nbytes, n, ld, flag_signed, q);
     RAHT_LAUNCH_CHECK();
     return RAHT_OK;
 }

@@ -218,7 +218,7 @@ int launch_stage(const raht_plan *P, int k, const Tin *A, const Tel *B, const ui
     }
     RAHT_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)L.total));
     StageArgs a{S.rows, S.to_next, S.sched, S.ab, S.hdr};
-    kern<<<(unsigned)S.n_tiles, TR_THREADS, L.total, st>>>(a, A, B, sel, O, D, R, use_tma);
+    (raht_count_launches(1), kern)<<<(unsigned)S.n_tiles, TR_THREADS, L.total, st>>>(a, A, B, sel, O, D, R, use_tma);
     RAHT_LAUNCH_CHECK();
     return RAHT_OK;
 }

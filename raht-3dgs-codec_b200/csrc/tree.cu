@@ -245,7 +245,7 @@ RAHT_API int raht_tree_levels(const int64_t *MC, int64_t n, uint8_t *level, int3
 {
     RAHT_REQUIRE(n >= 0 && (n == 0 || (MC && level)), "raht_tree_levels: bad arguments");
     if (n == 0) return RAHT_OK;
-    levels_kernel<<<grid_for(n, 256, 8), 256, 0, (cudaStream_t)stream>>>(MC, n, level, status);
+    (raht_count_launches(1), levels_kernel)<<<grid_for(n, 256, 8), 256, 0, (cudaStream_t)stream>>>(MC, n, level, status);
     RAHT_LAUNCH_CHECK();
     return RAHT_OK;
 }
@@ -264,7 +264,7 @@ RAHT_API int raht_tree_level(const uint8_t *level, int64_t n, int l, int64_t *li
     LevelPred pred{level, l};
     LevelEmit emit{list};
     device_select(n, pred, emit, count, workspace, st);
-    level_fill_kernel<<<grid_for(n, 256, 8), 256, 0, st>>>(level, n, l, list, count, flags, weights);
+    (raht_count_launches(1), level_fill_kernel)<<<grid_for(n, 256, 8), 256, 0, st>>>(level, n, l, list, count, flags, weights);
     RAHT_LAUNCH_CHECK();
     return RAHT_OK;
 }
@@ -273,8 +273,8 @@ RAHT_API int raht_tree_max_level(const uint8_t *level, int64_t n, int32_t *max_l
 {
     RAHT_REQUIRE(n >= 0 && max_level && (n == 0 || level), "raht_tree_max_level: bad arguments");
     cudaStream_t st = (cudaStream_t)stream;
-    max_level_init<<<1, 1, 0, st>>>(max_level);
-    if (n > 1) max_level_kernel<<<grid_for(n, 256, 8), 256, 0, st>>>(level, n, max_level);
+    (raht_count_launches(1), max_level_init)<<<1, 1, 0, st>>>(max_level);
+    if (n > 1) (raht_count_launches(1), max_level_kernel)<<<grid_for(n, 256, 8), 256, 0, st>>>(level, n, max_level);
     RAHT_LAUNCH_CHECK();
     return RAHT_OK;
 }
@@ -298,9 +298,9 @@ RAHT_API int raht_order_ragft(const uint8_t *level, int64_t n, int64_t *order, i
     cudaStream_t st = (cudaStream_t)stream;
     int64_t nb = (n + OR_TILE - 1) / OR_TILE;
     unsigned long long *counts = (unsigned long long *)workspace;
-    order_count_kernel<<<(unsigned)nb, OR_THREADS, 0, st>>>(level, n, nb, counts);
-    scan_counts_kernel<<<1, 1024, 0, st>>>(counts, nb * OR_BUCKETS, nullptr);
-    order_scatter_kernel<<<(unsigned)nb, OR_THREADS, 0, st>>>(level, n, nb, counts, order, position);
+    (raht_count_launches(1), order_count_kernel)<<<(unsigned)nb, OR_THREADS, 0, st>>>(level, n, nb, counts);
+    (raht_count_launches(1), scan_counts_kernel)<<<1, 1024, 0, st>>>(counts, nb * OR_BUCKETS, nullptr);
+    (raht_count_launches(1), order_scatter_kernel)<<<(unsigned)nb, OR_THREADS, 0, st>>>(level, n, nb, counts, order, position);
     RAHT_LAUNCH_CHECK();
     return RAHT_OK;
 }
@@ -382,7 +382,7 @@ RAHT_API int raht_plan_create(const uint8_t *level, int64_t n, int tile_rows, do
         PLAN_CUDA(cudaMalloc(&S.ab, slots * sizeof(double2)));
         PLAN_CUDA(cudaMalloc(&S.hdr, (size_t)S.n_tiles * sizeof(TileHdr)));
         P->bytes += (size_t)n_cur + slots * 20 + (size_t)S.n_tiles * sizeof(TileHdr) + (S.rows ? (size_t)n_cur * 4 : 0);
-        plan_stage_kernel<<<(unsigned)S.n_tiles, PB_THREADS, plan_smem_bytes(R), st>>>(
+        (raht_count_launches(1), plan_stage_kernel)<<<(unsigned)S.n_tiles, PB_THREADS, plan_smem_bytes(R), st>>>(
             S.rows, lev_cur, n_cur, n, R, S.to_next, S.sched, S.ab, S.hdr, w);
         PLAN_CUDA(cudaGetLastError());
         if (S.n_tiles == 1) break;

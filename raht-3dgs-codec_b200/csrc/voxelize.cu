@@ -84,8 +84,8 @@ RAHT_API int raht_bounds3_f32(const float *V, int64_t n, int64_t ld, float *boun
 {
     RAHT_REQUIRE(bounds6 && (V || n == 0) && ld >= 3 && n >= 0, "raht_bounds3_f32: bad arguments");
     cudaStream_t st = (cudaStream_t)stream;
-    bounds_init_kernel<<<1, 32, 0, st>>>(bounds6);
-    if (n) bounds3_kernel<<<grid_for(n, 256, 8), 256, 0, st>>>(V, n, ld, bounds6);
+    (raht_count_launches(1), bounds_init_kernel)<<<1, 32, 0, st>>>(bounds6);
+    if (n) (raht_count_launches(1), bounds3_kernel)<<<grid_for(n, 256, 8), 256, 0, st>>>(V, n, ld, bounds6);
     RAHT_LAUNCH_CHECK();
     return RAHT_OK;
 }
@@ -123,7 +123,7 @@ RAHT_API int raht_voxel_params(const float *bounds6, int J, int use_given_vmin, 
     RAHT_REQUIRE(!use_given_vmin || vmin_host, "raht_voxel_params: vmin_host required");
     F3 vm = {{0, 0, 0}};
     if (use_given_vmin) { vm.v[0] = vmin_host[0]; vm.v[1] = vmin_host[1]; vm.v[2] = vmin_host[2]; }
-    voxel_params_kernel<<<1, 32, 0, (cudaStream_t)stream>>>(bounds6, J, use_given_vmin, vm, use_given_width, width_host,
+    (raht_count_launches(1), voxel_params_kernel)<<<1, 32, 0, (cudaStream_t)stream>>>(bounds6, J, use_given_vmin, vm, use_given_width, width_host,
                                                             params4, params_d2);
     RAHT_LAUNCH_CHECK();
     return RAHT_OK;
@@ -156,7 +156,7 @@ RAHT_API int raht_morton_keys_f32(const float *V, int64_t n, int64_t ld, const f
     RAHT_REQUIRE(n >= 0 && ld >= 3 && J >= 1 && J <= 21 && params4 && (n == 0 || (V && keys)),
                  "raht_morton_keys_f32: bad arguments");
     if (n == 0) return RAHT_OK;
-    morton_f32_kernel<<<grid_for(n, 256, 8), 256, 0, (cudaStream_t)stream>>>(V, n, ld, params4, J, keys, vint);
+    (raht_count_launches(1), morton_f32_kernel)<<<grid_for(n, 256, 8), 256, 0, (cudaStream_t)stream>>>(V, n, ld, params4, J, keys, vint);
     RAHT_LAUNCH_CHECK();
     return RAHT_OK;
 }
@@ -172,7 +172,7 @@ RAHT_API int raht_morton_keys_i64(const int64_t *V, int64_t n, int J, int64_t *k
 {
     RAHT_REQUIRE(n >= 0 && J >= 1 && J <= 21 && (n == 0 || (V && keys)), "raht_morton_keys_i64: bad arguments");
     if (n == 0) return RAHT_OK;
-    morton_i64_kernel<<<grid_for(n, 256, 8), 256, 0, (cudaStream_t)stream>>>(V, n, J, keys);
+    (raht_count_launches(1), morton_i64_kernel)<<<grid_for(n, 256, 8), 256, 0, (cudaStream_t)stream>>>(V, n, J, keys);
     RAHT_LAUNCH_CHECK();
     return RAHT_OK;
 }
@@ -204,7 +204,7 @@ RAHT_API int raht_morton_keys_f64(const double *V, int64_t n, const double *minV
     if (n == 0) return RAHT_OK;
     D3 mv = {{minV_host[0], minV_host[1], minV_host[2]}};
     double Q = width / (double)((int64_t)1 << depth);                                     // :21, :204
-    morton_f64_kernel<<<grid_for(n, 256, 8), 256, 0, (cudaStream_t)stream>>>(V, n, mv, Q, depth, keys, status);
+    (raht_count_launches(1), morton_f64_kernel)<<<grid_for(n, 256, 8), 256, 0, (cudaStream_t)stream>>>(V, n, mv, Q, depth, keys, status);
     RAHT_LAUNCH_CHECK();
     return RAHT_OK;
 }
@@ -225,7 +225,7 @@ RAHT_API int raht_morton_decode_f32(const uint64_t *keys, int64_t n, int J, floa
     (void)J;
     RAHT_REQUIRE(n >= 0 && (n == 0 || (keys && coords)), "raht_morton_decode_f32: bad arguments");
     if (n == 0) return RAHT_OK;
-    morton_decode_kernel<<<grid_for(n, 256, 8), 256, 0, (cudaStream_t)stream>>>(keys, n, coords);
+    (raht_count_launches(1), morton_decode_kernel)<<<grid_for(n, 256, 8), 256, 0, (cudaStream_t)stream>>>(keys, n, coords);
     RAHT_LAUNCH_CHECK();
     return RAHT_OK;
 }
@@ -271,7 +271,7 @@ RAHT_API int raht_voxel_segments(const uint64_t *sorted_keys, int64_t n, int64_t
     BoundaryPred pred{sorted_keys};
     BoundaryEmit emit{sorted_keys, voxel_indices, cluster_offsets, unique_keys};
     device_select(n, pred, emit, count, sel_ws, st);
-    segments_tail_kernel<<<1, 1, 0, st>>>(count, nvox, cluster_offsets, n);
+    (raht_count_launches(1), segments_tail_kernel)<<<1, 1, 0, st>>>(count, nvox, cluster_offsets, n);
     RAHT_LAUNCH_CHECK();
     return RAHT_OK;
 }
@@ -304,7 +304,7 @@ RAHT_API int raht_gather_rows_f32(const float *PC, int64_t n, int64_t ld, const 
     RAHT_REQUIRE(n >= 0 && ld >= 1 && (n == 0 || (PC && idx)) && (!DeltaV || (params4 && ld >= 3 && ld_delta >= 3)),
                  "raht_gather_rows_f32: bad arguments");
     if (n == 0) return RAHT_OK;
-    gather_rows_kernel<<<grid_for(n * ld, 256, 8), 256, 0, (cudaStream_t)stream>>>(PC, n, ld, idx, params4, PCsorted,
+    (raht_count_launches(1), gather_rows_kernel)<<<grid_for(n * ld, 256, 8), 256, 0, (cudaStream_t)stream>>>(PC, n, ld, idx, params4, PCsorted,
                                                                                   DeltaV, ld_delta);
     RAHT_LAUNCH_CHECK();
     return RAHT_OK;
@@ -339,7 +339,7 @@ RAHT_API int raht_voxel_attr_mean_f32(const float *PC, int64_t n, int64_t ld, in
     RAHT_REQUIRE(n >= 0 && nvox >= 0 && d >= 0 && ld >= 3 + d, "raht_voxel_attr_mean_f32: bad arguments");
     if (nvox == 0 || d == 0) return RAHT_OK;
     RAHT_REQUIRE(PC && idx && voxel_indices && Cvox, "raht_voxel_attr_mean_f32: null pointer");
-    attr_mean_kernel<<<grid_for(nvox * d, 256, 8), 256, 0, (cudaStream_t)stream>>>(
+    (raht_count_launches(1), attr_mean_kernel)<<<grid_for(nvox * d, 256, 8), 256, 0, (cudaStream_t)stream>>>(
         PC, n, ld, d, idx, voxel_indices, nvox, Cvox, ld_out, col_out, DeltaC, ld_delta);
     RAHT_LAUNCH_CHECK();
     return RAHT_OK;

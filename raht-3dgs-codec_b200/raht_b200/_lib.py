@@ -30,6 +30,7 @@ _p, _i, _i64, _sz, _d = C.c_void_p, C.c_int, C.c_int64, C.c_size_t, C.c_double
 SIGNATURES = {
     "raht_abi_version": (_i, []),
     "raht_last_error": (C.c_char_p, []),
+    "raht_launch_count": (C.c_longlong, []),
     "raht_device_info": (_i, [C.POINTER(_i), C.POINTER(_i)]),
     "raht_bounds3_f32": (_i, [_p, _i64, _i64, _p, _p]),
     "raht_voxel_params": (_i, [_p, _i, _i, C.POINTER(C.c_float), _i, _d, _p, _p, _p]),

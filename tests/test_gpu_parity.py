@@ -1,0 +1,344 @@
+"""GPU parity tests (-m gpu): the CUDA path, called through the C ABI / the reference-named Python
+shims, against (i) the golden fixtures generated from the reference and (ii) the CPU oracle on seeded
+inputs.  Integer / index / byte results and fp64 coefficients must be bit-exact."""
+import numpy as np
+import pytest
+import torch
+
+import helpers
+from oracle import oracle_ctypes as orc
+
+pytestmark = pytest.mark.gpu
+DEV = "cuda:0"
+
+
+def cu(a, dtype=None):
+    t = torch.from_numpy(np.ascontiguousarray(a)).to(DEV)
+    return t if dtype is None else t.to(dtype)
+
+
+def test_pinning_assumption_cuda_sqrt_is_ieee():
+    """The fixtures assume torch on CUDA (the reference's production device) rounds sqrt correctly."""
+    x = np.random.default_rng(0).random(200000)
+    assert np.array_equal(torch.sqrt(cu(x)).cpu().numpy(), np.sqrt(x))
+    a = np.random.default_rng(1).integers(1, 10**6, size=200000).astype(np.float64)
+    b = np.random.default_rng(2).integers(1, 10**6, size=200000).astype(np.float64)
+    assert np.array_equal((cu(a) / (cu(a) + cu(b))).cpu().numpy(), a / (a + b))
+
+
+# ---------------------------------------------------------------------------------------------------
+# tree + transform + quantisation + RLGR against the golden fixtures (reference outputs)
+# ---------------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("name", helpers.RAHT_CASES)
+@pytest.mark.parametrize("tile_rows", [128, 256])
+def test_golden_raht_pipeline(name, tile_rows):
+    import RAHT_param as P
+    import RAHT as R
+    import iRAHT as IR
+    from raht_b200 import ops
+    g = helpers.load(name)
+    J = int(g["J"])
+    V = cu(g["V"], torch.float64)
+    origin = torch.zeros(3, dtype=torch.float64, device=DEV)
+    List, Flags, weights, order = P.RAHT_param_reorder_fast(V, origin, 2 ** J, J)
+    levels = helpers.split_levels(g)
+    assert len(List) == len(Flags) == len(weights) == int(g["nlevels"])
+    for l, (lst, fl, w) in enumerate(levels):
+        assert List[l].dtype == torch.int64 and Flags[l].dtype == torch.bool and weights[l].dtype == torch.int64
+        assert np.array_equal(List[l].cpu().numpy(), lst), f"List[{l}]"
+        assert np.array_equal(Flags[l].cpu().numpy(), fl), f"Flags[{l}]"
+        assert np.array_equal(weights[l].cpu().numpy(), w), f"weights[{l}]"
+    assert np.array_equal(order.cpu().numpy(), g["order"])
+
+    tree = ops.tree_of(List)
+    C = cu(g["C"])
+    T = ops.forward(tree, C, torch.float64, tile_rows)
+    assert np.array_equal(T.cpu().numpy(), g["T"]), "T must be bit-exact with RAHT2_optimized"
+    T2, w = R.RAHT2_optimized(C, List, Flags, weights)
+    assert np.array_equal(T2.cpu().numpy(), g["T"]) and w.shape == (C.shape[0], 1)
+    assert np.array_equal(w.cpu().numpy().reshape(-1), g["w"])
+    # TMA and plain-load paths agree
+    assert torch.equal(ops.forward(tree, C, torch.float64, tile_rows, flags=1), T)
+    Cl = ops.inverse(tree, T, tile_rows)
+    assert np.array_equal(Cl.cpu().numpy(), g["C_lossless"])
+    assert torch.equal(ops.inverse(tree, T, tile_rows, flags=1), Cl)
+    assert np.array_equal(IR.inverse_RAHT_optimized(T, List, Flags, weights).cpu().numpy(), g["C_lossless"])
+    # fp32 input is widened exactly
+    T32in = ops.forward(tree, C.float(), torch.float64, tile_rows)
+    assert np.array_equal(T32in.cpu().numpy(), orc.Tree(helpers.morton_np(g["V"]), J).forward(g["C"].astype(np.float32).astype(np.float64))[0])
+
+    for s in g["steps"]:
+        s = int(s)
+        q = ops.quant_reorder(T, order, s)
+        assert np.array_equal(q.cpu().numpy(), g[f"q_step{s}"])
+        streams = ops.rlgr_encode(q, 1)
+        got = streams.to_bytes()
+        exp = helpers.split_streams(g, s)
+        for ch in range(len(exp)):
+            assert got[ch] == exp[ch], f"step {s}: RLGR bytes of channel {ch} differ"
+        qd = ops.rlgr_decode(streams, 1)
+        assert torch.equal(qd, q)
+        Td = ops.dequant_unreorder(qd, order, s)
+        Crec = ops.inverse(tree, Td, tile_rows)
+        assert np.array_equal(Crec.cpu().numpy(), g[f"C_rec_step{s}"])
+
+
+def test_plain_lists_are_accepted():
+    """encode_3dgs.py:152-154 rebuilds the lists with [t.to(device) for t in List]; also lists that did
+    not come from this package (here: from the golden file) must work."""
+    import RAHT_param as P
+    import RAHT as R
+    g = helpers.load("raht_clustered_J7_D5")
+    J = int(g["J"])
+    V = cu(g["V"], torch.float64)
+    List, Flags, weights, _ = P.RAHT_param_reorder_fast(V, torch.zeros(3, device=DEV, dtype=torch.float64), 2 ** J, J)
+    L2 = [t.to(device=DEV, non_blocking=True) for t in List]
+    F2 = [t.to(device=DEV, non_blocking=True) for t in Flags]
+    W2 = [t.to(device=DEV, non_blocking=True) for t in weights]
+    T, _ = R.RAHT2_optimized(cu(g["C"]), L2, F2, W2)
+    assert np.array_equal(T.cpu().numpy(), g["T"])
+    lv = helpers.split_levels(g)
+    L3, F3, W3 = [cu(a) for a, _, _ in lv], [cu(b) for _, b, _ in lv], [cu(c) for _, _, c in lv]
+    T3, w3 = R.RAHT2_optimized(cu(g["C"]), L3, F3, W3)
+    assert np.array_equal(T3.cpu().numpy(), g["T"]) and np.array_equal(w3.cpu().numpy().reshape(-1), g["w"])
+    L1 = [a + 1 for a in L3]
+    T4, _ = R.RAHT2_optimized(cu(g["C"]), L1, F3, W3, one_based=True)
+    assert np.array_equal(T4.cpu().numpy(), g["T"])
+
+
+def test_raht_param_errors():
+    import RAHT_param as P
+    V = torch.tensor([[0, 0, 0], [0, 0, 1], [4, 0, 0]], dtype=torch.float64, device=DEV)
+    with pytest.raises(ValueError, match="OutOfBounds"):
+        P.RAHT_param(V, torch.zeros(3, device=DEV), 4, 2)
+    V = torch.tensor([[0, 0, 1], [0, 0, 0]], dtype=torch.float64, device=DEV)
+    with pytest.raises(ValueError, match="sorted"):
+        P.RAHT_param_reorder_fast(V, torch.zeros(3, device=DEV), 4, 2)
+    V = torch.tensor([[0, 0, 1], [0, 0, 1]], dtype=torch.float64, device=DEV)
+    with pytest.raises(ValueError):
+        P.RAHT_param_reorder_fast(V, torch.zeros(3, device=DEV), 4, 2)
+    # N == 1 (RAHT_param.py:233-236): one level, order None
+    V = torch.tensor([[1, 2, 3]], dtype=torch.float64, device=DEV)
+    Ls, Fs, Ws, order = P.RAHT_param_reorder_fast(V, torch.zeros(3, device=DEV), 4, 2)
+    assert len(Ls) == 1 and order is None and Ws[0].tolist() == [1] and Fs[0].tolist() == [False]
+    import RAHT as R
+    T, w = R.RAHT2_optimized(torch.tensor([[5.0, 6.0]], device=DEV), Ls, Fs, Ws)
+    assert T.tolist() == [[5.0, 6.0]] and w.tolist() == [[1.0]]
+
+
+# ---------------------------------------------------------------------------------------------------
+# the same pipeline against the CPU oracle at sizes the oracle finishes in seconds
+# ---------------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("n,J,D,clustered,seed", [(60000, 10, 59, True, 1), (150000, 12, 59, False, 2), (300000, 16, 3, True, 3),
+                                                  (200001, 21, 8, False, 4), (129, 4, 59, False, 5), (2, 3, 4, False, 6)])
+def test_oracle_raht_pipeline(n, J, D, clustered, seed):
+    from raht_b200 import ops
+    import RAHT_param as P
+    Pts, MC = helpers.unique_sorted_voxels(n, J, seed, clustered)
+    N = len(MC)
+    rng = np.random.default_rng(seed)
+    C = (rng.normal(size=(N, D)) * np.linspace(0.5, 40, D)[None, :]).astype(np.float64)
+    t = orc.Tree(MC, J)
+    List, Flags, weights, order = P.RAHT_param_reorder_fast(cu(Pts, torch.float64), torch.zeros(3, device=DEV), 2 ** J, J)
+    assert len(List) == t.nlevels
+    for l in sorted(set([0, 1, t.nlevels // 2, t.nlevels - 1])):
+        a, b, c = t.level(l)
+        assert np.array_equal(List[l].cpu().numpy(), a) and np.array_equal(Flags[l].cpu().numpy(), b)
+        assert np.array_equal(weights[l].cpu().numpy(), c)
+    o_ref = t.order()
+    if N > 4:
+        assert np.array_equal(order.cpu().numpy(), o_ref)
+    tree = ops.tree_of(List)
+    To, wo = t.forward(C)
+    for R_ in (128, 512):
+        T = ops.forward(tree, cu(C), torch.float64, R_)
+        assert np.array_equal(T.cpu().numpy(), To), f"tile_rows={R_}"
+        assert np.array_equal(tree.w.cpu().numpy(), wo)
+        assert np.array_equal(ops.inverse(tree, T, R_).cpu().numpy(), t.inverse(To))
+    info = tree.plan_info(128)
+    assert info["stage_rows"][0] == N and info["stages"] >= 1
+    for s in (1, 12):
+        q = ops.quant_reorder(T, order, s)
+        q_ref = orc.quantize(To, s)[order.cpu().numpy()].T.astype(np.int32)
+        assert np.array_equal(q.cpu().numpy(), q_ref)
+        streams = ops.rlgr_encode(q, 1)
+        got = streams.to_bytes()
+        exp, _, _, _ = orc.rlgr_encode_channels(q_ref, 1)
+        assert got == exp
+        assert torch.equal(ops.rlgr_decode(streams, 1), q)
+
+
+def test_fp32_mode_tolerance():
+    """Build-specific fp32 transform: <= 1e-5 relative error on coefficients, PSNR within 0.01 dB."""
+    from raht_b200 import ops, codec
+    Pts, MC = helpers.unique_sorted_voxels(100000, 12, 21, True)
+    N = len(MC)
+    C = np.random.default_rng(21).normal(size=(N, 59)).astype(np.float32)
+    tree = ops.tree_from_keys(cu(MC))
+    T64 = ops.forward(tree, cu(C), torch.float64)
+    T32 = ops.forward(tree, cu(C), torch.float32)
+    scale = T64.abs().max(dim=0).values
+    err = ((T32.double() - T64).abs().max(dim=0).values / scale).max().item()
+    assert err <= 1e-5, err
+    order = tree.order()
+    ps = []
+    for T in (T64, T32):
+        q = ops.quant_reorder(T, order, 0.05)
+        Td = ops.dequant_unreorder(q, order, 0.05, T.dtype)
+        Crec = ops.inverse(tree, Td)
+        ps.append(codec.psnr(cu(C).double(), Crec.double()))
+    assert abs(ps[0] - ps[1]) <= 0.01, ps
+
+
+# ---------------------------------------------------------------------------------------------------
+# voxelisation front end
+# ---------------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("name", helpers.VOX_CASES)
+def test_golden_voxelize(name):
+    import voxelize_pc as VX
+    g = helpers.load(name)
+    PC, J = g["PC"], int(g["J"])
+    vmin = torch.from_numpy(g["vmin_in"]) if g["vmin_in"].size else None
+    width = float(g["width_in"][0]) if g["width_in"].size else None
+    PCvox, PCsorted, vi, DeltaPC, info = VX.voxelize_pc_batched(cu(PC), vmin=vmin, width=width, J=J, device=DEV)
+    assert info["Nvox"] == int(g["Nvox"]) and info["N"] == PC.shape[0]
+    assert info["voxel_size"] == float(g["voxel_size"]) and info["width"] == float(g["width"])
+    assert np.array_equal(info["vmin"].cpu().numpy(), g["vmin"])
+    assert info["sort_idx"].dtype == torch.int64 and np.array_equal(info["sort_idx"].cpu().numpy(), g["sort_idx"])
+    assert vi.dtype == torch.int64 and np.array_equal(vi.cpu().numpy(), g["voxel_indices"])
+    assert np.array_equal(PCsorted.cpu().numpy(), g["PCsorted"])
+    assert np.array_equal(PCvox.cpu().numpy(), g["PCvox"])
+    assert np.array_equal(DeltaPC.cpu().numpy(), g["DeltaPC"])
+    out4 = VX.voxelize_pc(cu(PC), {"J": J, "vmin": None if vmin is None else vmin.tolist(), "width": width})
+    assert torch.equal(out4[0], PCvox) and torch.equal(out4[2], vi)
+    V0i = cu(g["PCvox"][:, :3].astype(np.int64))
+    assert np.array_equal(VX.get_morton_code(V0i, J).cpu().numpy(), helpers.morton_np(g["PCvox"][:, :3].astype(np.int64)))
+
+
+@pytest.mark.parametrize("n,bits,seed", [(1, 8, 0), (1000, 5, 1), (3072, 17, 2), (3073, 36, 3), (200000, 48, 4), (1500000, 63, 5),
+                                         (777777, 9, 6)])
+def test_radix_sort_stable(n, bits, seed):
+    from raht_b200 import ops
+    rng = np.random.default_rng(seed)
+    keys = rng.integers(0, 2 ** bits, size=n, dtype=np.int64)
+    ks, idx, status = ops.radix_sort_pairs(cu(keys), bits)
+    order = np.argsort(keys, kind="stable")
+    assert int(status.item()) == 0
+    assert np.array_equal(ks.cpu().numpy(), keys[order])
+    assert np.array_equal(idx.cpu().numpy().astype(np.int64), order)
+    vals = rng.integers(0, 2 ** 31, size=n).astype(np.int32)
+    ks2, v2, _ = ops.radix_sort_pairs(cu(keys), bits, cu(vals))
+    assert np.array_equal(v2.cpu().numpy(), vals[order])
+
+
+@pytest.mark.parametrize("n,J,seed", [(200000, 6, 1), (300000, 12, 2), (50000, 16, 3)])
+def test_oracle_voxelize_merge(n, J, seed):
+    import voxelize_pc as VX
+    import merge_cluster_cuda as MG
+    from raht_b200 import codec
+    means, quats, scales, opac, colors = helpers.synthetic_gaussians(n, seed)
+    r = orc.voxelize(means, J, want_delta=False)
+    PCvox, PCsorted, vi, DeltaPC, info = VX.voxelize_pc_batched(cu(means), J=J, device=DEV)
+    assert info["Nvox"] == r["Nvox"]
+    assert np.array_equal(info["sort_idx"].cpu().numpy(), r["sort_idx"])
+    assert np.array_equal(vi.cpu().numpy(), r["voxel_indices"])
+    Vvox = r["Vint"][r["sort_idx"]][r["voxel_indices"]].astype(np.float32)
+    assert np.array_equal(PCvox.cpu().numpy(), Vvox)
+    # test_voxelize_3dgs.py:225-247
+    cidx = info["sort_idx"].int()
+    coff = torch.cat([vi, torch.tensor([n], device=DEV)]).int()
+    exp = orc.merge_clusters(r["sort_idx"].astype(np.int32), np.concatenate([r["voxel_indices"], [n]]).astype(np.int32),
+                             means, quats, scales, opac, colors, True)
+    got = MG.merge_gaussian_clusters_with_indices(cu(means), cu(quats), cu(scales), cu(opac), cu(colors), cidx, coff, True)
+    for a, b, nm in zip(got, exp, ("means", "quats", "scales", "opacities", "colors")):
+        assert np.array_equal(a.cpu().numpy(), b), nm
+    got_u = MG.merge_gaussian_clusters_with_indices(cu(means), cu(quats), cu(scales), cu(opac), cu(colors), cidx, coff, False)
+    exp_u = orc.merge_clusters(r["sort_idx"].astype(np.int32), np.concatenate([r["voxel_indices"], [n]]).astype(np.int32),
+                               means, quats, scales, opac, colors, False)
+    for a, b in zip(got_u, exp_u):
+        assert np.array_equal(a.cpu().numpy(), b)
+    packed, keys, info2 = codec.voxelize_merge(cu(means), cu(quats), cu(scales), cu(opac), cu(colors), J)
+    assert np.array_equal(keys.cpu().numpy(), r["MC_sorted"][r["voxel_indices"]])
+    assert np.array_equal(packed.cpu().numpy(), np.concatenate([exp[0], exp[1], exp[2], exp[3][:, None], exp[4]], 1))
+    # label interface
+    labels = cu(r["MC"])
+    got_l = MG.merge_gaussian_clusters(cu(means), cu(quats), cu(scales), cu(opac), cu(colors), labels, True)
+    for a, b in zip(got_l, exp):
+        assert np.array_equal(a.cpu().numpy(), b)
+
+
+def test_merge_errors_and_empty_clusters():
+    import merge_cluster_cuda as MG
+    m = torch.zeros(4, 3, device=DEV); q = torch.zeros(4, 4, device=DEV); s = torch.zeros(4, 3, device=DEV)
+    o = torch.ones(4, device=DEV); c = torch.ones(4, 6, device=DEV)
+    idx = torch.arange(4, device=DEV).int()
+    off = torch.tensor([0, 2, 2, 4], device=DEV).int()          # middle cluster empty -> zeros (merge_cluster.cu:27-29)
+    out = MG.merge_gaussian_clusters_with_indices(m, q, s, o, c, idx, off)
+    assert out[3].tolist() == [1.0, 0.0, 1.0] and out[1][0].tolist() == [0.0, 0.0, 0.0, 1.0] and out[1][1].tolist() == [0.0] * 4
+    with pytest.raises(RuntimeError):
+        MG.merge_gaussian_clusters_with_indices(m.cpu(), q, s, o, c, idx, off)
+    with pytest.raises(RuntimeError):
+        MG.merge_gaussian_clusters_with_indices(m, q[:, :3], s, o, c, idx, off)
+
+
+# ---------------------------------------------------------------------------------------------------
+# RLGR
+# ---------------------------------------------------------------------------------------------------
+def test_rlgr_kats_membuf_interface():
+    import rlgr
+    for seq, out, fs in helpers.rlgr_kats():
+        m = rlgr.membuf()
+        m.rlgrWrite(seq.tolist(), fs)
+        m.close()
+        assert bytes(m.get_buffer()) == out, seq[:8]
+        r = rlgr.membuf(list(out))
+        _, dec = r.rlgrRead(len(seq), fs)
+        assert dec == seq.tolist()
+
+
+@pytest.mark.parametrize("zfrac,scale,n", [(0.0, 3.0, 70000), (0.3, 50.0, 70000), (0.85, 2.0, 90000), (0.97, 5.0, 120000),
+                                           (0.9995, 1.0, 300000), (0.5, 3e8, 20000)])
+def test_rlgr_random_vs_oracle(zfrac, scale, n):
+    from raht_b200 import ops
+    rng = np.random.default_rng(int(scale) + n)
+    nch = 5
+    x = np.clip(np.rint(rng.laplace(0, scale, size=(nch, n))), -2**31, 2**31 - 1).astype(np.int32)
+    x[rng.random((nch, n)) < zfrac] = 0
+    x[1, -300:] = 0            # trailing zero run (tail rule)
+    x[2, -1] = -1              # tail quirk: u-1 == 0 in run mode
+    x[3, :] = 0
+    streams = ops.rlgr_encode(cu(x), 1)
+    exp, _, _, _ = orc.rlgr_encode_channels(x, 1)
+    assert streams.to_bytes() == exp
+    assert np.array_equal(ops.rlgr_decode(streams, 1).cpu().numpy(), x)
+
+
+# ---------------------------------------------------------------------------------------------------
+# whole scene, size-independent properties at a BASELINE-sized input
+# ---------------------------------------------------------------------------------------------------
+def test_scene_roundtrip_properties_1m():
+    from raht_b200 import codec, ops
+    n, J = 1_000_000, 12
+    means, quats, scales, opac, colors = helpers.synthetic_gaussians(n, 2001)
+    args = [cu(a) for a in (means, quats, scales, opac, colors)]
+    enc = codec.encode_scene(*args, J=J, step=1.0 / 256)
+    assert enc.D == 59 and 0.9 * n < enc.nvox <= n
+    keys = enc.keys.cpu().numpy()
+    assert np.all(np.diff(keys) > 0)                                     # sorted, unique
+    coords, Crec = codec.decode_scene(enc)
+    packed, keys2, _ = codec.voxelize_merge(*args, J=J)
+    assert torch.equal(keys2, enc.keys)
+    # quantisation error bound: orthonormal transform => per-coefficient error <= step/2, so RMSE <= step/2
+    err = (Crec - packed.double())
+    assert err.abs().max().item() < 1.0 and (err ** 2).mean().sqrt().item() <= 0.5 / 256
+    # lossless path: iRAHT(RAHT(C)) == C to rounding; energy preserved; DC = sqrt(N) mean
+    tree = enc.tree
+    T = ops.forward(tree, packed, torch.float64)
+    assert torch.allclose(ops.inverse(tree, T), packed.double(), rtol=0, atol=1e-9)
+    assert torch.allclose(T.norm(dim=0), packed.double().norm(dim=0), rtol=1e-12)
+    assert torch.allclose(T[0], packed.double().mean(0) * np.sqrt(enc.nvox), rtol=1e-9, atol=1e-9)
+    order = tree.order()
+    assert torch.equal(torch.sort(order).values, torch.arange(enc.nvox, device=DEV))
+    # decode without the encoder-side tree gives the same result
+    _, Crec2 = codec.decode_scene(enc, reuse_tree=False)
+    assert torch.equal(Crec, Crec2)
