@@ -150,7 +150,7 @@ def test_oracle_raht_pipeline(n, J, D, clustered, seed):
         assert np.array_equal(order.cpu().numpy(), o_ref)
     tree = ops.tree_of(List)
     To, wo = t.forward(C)
-    for R_ in (128, 512):
+    for R_ in (128, 256 if D > 30 else 512):      # 512 rows x 59 fp64 channels exceed 227 KB of shared memory
         T = ops.forward(tree, cu(C), torch.float64, R_)
         assert np.array_equal(T.cpu().numpy(), To), f"tile_rows={R_}"
         assert np.array_equal(tree.w.cpu().numpy(), wo)
