@@ -29,7 +29,7 @@
 extern "C" {
 #endif
 
-#define RAHT_B200_ABI_VERSION 2
+#define RAHT_B200_ABI_VERSION 3
 
 enum {
     RAHT_OK = 0,
@@ -208,14 +208,27 @@ int raht_dequantize_f64(const double *q, int64_t count, double step, double *T, 
  * :258-338 (rlgrRead), :46-56 (close), :59-62 (get_buffer) as bound by bindings.cpp:34-57.
  * One independent stream per channel, byte-identical to the reference's.
  * q: channel-major int32 (nch, ld); streams: nch slots of slot_bytes (multiple of 8) bytes;
- * nbytes[c]: closed stream length.  A stream that does not fit sets RAHT_ST_STREAM_OVERFLOW.
+ * nbytes[c]: closed stream length (exact even when the stream did not fit: RAHT_ST_STREAM_OVERFLOW).
+ *
+ * sync_index (optional, device, nch * raht_rlgr_sync_entries(n) entries of 16 bytes): side
+ * information the encoder can emit next to the reference bitstream -- for every chunk of 3968
+ * symbols the bit offset, first symbol and coder state (k_P, k_RP) at an event boundary.  The
+ * streams do not depend on it.  raht_rlgr_decode with the index decodes every chunk in parallel;
+ * with sync_index == NULL (a stream written by the reference coder) it decodes one channel per
+ * thread, as the format forces.
  * ------------------------------------------------------------------------------------------------ */
+int64_t raht_rlgr_sync_entries(int64_t n);
 size_t raht_rlgr_encode_workspace_bytes(int64_t n, int nch);
 int raht_rlgr_encode(const int32_t *q, int64_t n, int64_t ld, int nch, int flag_signed,
-                     uint8_t *streams, int64_t slot_bytes, int64_t *nbytes, int32_t *status,
-                     void *workspace, size_t workspace_bytes, void *stream);
-int raht_rlgr_decode(const uint8_t *streams, int64_t slot_bytes, const int64_t *nbytes, int64_t n,
-                     int64_t ld, int nch, int flag_signed, int32_t *q, void *stream);
+                     uint8_t *streams, int64_t slot_bytes, int64_t *nbytes, void *sync_index,
+                     int32_t *status, void *workspace, size_t workspace_bytes, void *stream);
+/* diagnostics of the last encode on `workspace`: out3_host = {chunk solves in the speculation sweeps,
+ * their fixed-point rounds, chunks re-solved by the resolve pass}.  Synchronises `stream`.          */
+int raht_rlgr_encode_stats(const void *workspace, int64_t n, int nch, unsigned long long *out3_host,
+                           void *stream);
+int raht_rlgr_decode(const uint8_t *streams, int64_t slot_bytes, const int64_t *nbytes,
+                     const void *sync_index, int64_t n, int64_t ld, int nch, int flag_signed,
+                     int32_t *q, void *stream);
 
 /* (a13) sum over rows of (A-B)^2 in fp64 for columns [c0,c1) of two (n, D) matrices -> *sse
  * (device double, overwritten), encode_3dgs.py:298-310.                                            */

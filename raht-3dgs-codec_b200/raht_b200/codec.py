@@ -31,7 +31,12 @@ class EncodedScene:
     tree: Optional[ops.RahtTree] = field(default=None, repr=False)   # encoder-side cache (decoder rebuilds from keys)
 
     def payload_bytes(self) -> int:
+        """Bytes of the D reference-format RLGR streams."""
         return self.streams.total_bytes()
+
+    def index_bytes(self) -> int:
+        """Bytes of the optional sync index (side information for chunk-parallel decoding)."""
+        return self.streams.index_bytes()
 
 
 class StageTimer:

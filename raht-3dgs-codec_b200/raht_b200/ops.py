@@ -342,16 +342,25 @@ def dequant_unreorder(q: torch.Tensor, order, step, out_dtype=torch.float64) -> 
 
 
 class RlgrStreams:
-    """nch closed RLGR streams in one device buffer (slot per channel)."""
+    """nch closed RLGR streams in one device buffer (slot per channel).
 
-    def __init__(self, buf, slot_bytes, nbytes, n, nch):
+    sync_index (optional): the encoder's side information for chunk-parallel decoding -- 16 bytes per
+    chunk of 3968 symbols (bit offset, first symbol, coder state); the streams themselves are the
+    reference bitstreams and do not depend on it."""
+
+    def __init__(self, buf, slot_bytes, nbytes, n, nch, sync_index=None):
         self.buf, self.slot_bytes, self.nbytes, self.n, self.nch = buf, slot_bytes, nbytes, n, nch
+        self.sync_index = sync_index
+        self.stats = None
 
     def sizes(self):
         return self.nbytes.cpu().tolist()
 
     def total_bytes(self):
         return int(self.nbytes.sum().item())
+
+    def index_bytes(self):
+        return 0 if self.sync_index is None else self.sync_index.numel() * self.sync_index.element_size()
 
     def to_bytes(self):
         """list[bytes], one per channel (D2H)."""
@@ -360,7 +369,7 @@ class RlgrStreams:
         return [host[c * self.slot_bytes: c * self.slot_bytes + sizes[c]].tobytes() for c in range(self.nch)]
 
 
-def rlgr_encode(q: torch.Tensor, flag_signed=1, slot_bytes=None) -> RlgrStreams:
+def rlgr_encode(q: torch.Tensor, flag_signed=1, slot_bytes=None, with_index=True, want_stats=False) -> RlgrStreams:
     """q: (nch, n) int32 channel-major (row stride >= n)."""
     L.require_cuda(q, "q")
     nch, n = q.shape
@@ -369,27 +378,36 @@ def rlgr_encode(q: torch.Tensor, flag_signed=1, slot_bytes=None) -> RlgrStreams:
         q = q.to(torch.int32).contiguous()
     ld = q.stride(0) if nch > 1 else max(n, 1)
     slot = slot_bytes or ((n * 4 + 64 + 7) // 8 * 8)
+    entries = int(lib.raht_rlgr_sync_entries(n))
+    ws_bytes = lib.raht_rlgr_encode_workspace_bytes(n, nch)
+    ws = workspace(ws_bytes, dev)
     while True:
         buf = torch.empty(nch * slot, dtype=torch.uint8, device=dev)
         nbytes = torch.zeros(nch, dtype=torch.int64, device=dev)
+        index = torch.empty(nch * entries, 4, dtype=torch.int32, device=dev) if with_index else None
         status = _status_word(dev)
-        ws_bytes = lib.raht_rlgr_encode_workspace_bytes(n, nch)
-        ws = workspace(ws_bytes, dev)
-        check(lib.raht_rlgr_encode(ptr(q), n, ld, nch, flag_signed, ptr(buf), slot, ptr(nbytes), ptr(status), ptr(ws),
-                                   ws_bytes, stream()), "raht_rlgr_encode")
+        check(lib.raht_rlgr_encode(ptr(q), n, ld, nch, flag_signed, ptr(buf), slot, ptr(nbytes), ptr(index), ptr(status),
+                                   ptr(ws), ws_bytes, stream()), "raht_rlgr_encode")
         if int(status.item()) & L.ST_STREAM_OVERFLOW:
             slot = (int(nbytes.max().item()) + 64 + 7) // 8 * 8       # exact size is known even on overflow
             continue
-        return RlgrStreams(buf, slot, nbytes, n, nch)
+        out = RlgrStreams(buf, slot, nbytes, n, nch, index)
+        if want_stats and n > 0 and nch > 0:
+            st = (C.c_ulonglong * 3)()
+            check(lib.raht_rlgr_encode_stats(ptr(ws), n, nch, st, stream()), "raht_rlgr_encode_stats")
+            out.stats = {"solves": int(st[0]), "rounds": int(st[1]), "repairs": int(st[2]), "chunks": nch * entries}
+        return out
 
 
-def rlgr_decode(streams: RlgrStreams, flag_signed=1) -> torch.Tensor:
+def rlgr_decode(streams: RlgrStreams, flag_signed=1, use_index=True) -> torch.Tensor:
+    """Chunk-parallel with the encoder's sync index, else one channel per thread (reference streams)."""
     dev = streams.buf.device
     n, nch = streams.n, streams.nch
     ld = (n + 3) // 4 * 4
     q = torch.empty(nch, max(ld, 1), dtype=torch.int32, device=dev)
-    check(lib.raht_rlgr_decode(ptr(streams.buf), streams.slot_bytes, ptr(streams.nbytes), n, max(ld, 1), nch, flag_signed,
-                               ptr(q), stream()), "raht_rlgr_decode")
+    index = streams.sync_index if use_index else None
+    check(lib.raht_rlgr_decode(ptr(streams.buf), streams.slot_bytes, ptr(streams.nbytes), ptr(index), n, max(ld, 1), nch,
+                               flag_signed, ptr(q), stream()), "raht_rlgr_decode")
     return q[:, :n]
 
 

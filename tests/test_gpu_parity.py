@@ -78,6 +78,7 @@ def test_golden_raht_pipeline(name, tile_rows):
             assert got[ch] == exp[ch], f"step {s}: RLGR bytes of channel {ch} differ"
         qd = ops.rlgr_decode(streams, 1)
         assert torch.equal(qd, q)
+        assert torch.equal(ops.rlgr_decode(streams, 1, use_index=False), q)      # channel-serial path (no sync index)
         Td = ops.dequant_unreorder(qd, order, s)
         Crec = ops.inverse(tree, Td, tile_rows)
         assert np.array_equal(Crec.cpu().numpy(), g[f"C_rec_step{s}"])
@@ -166,6 +167,7 @@ def test_oracle_raht_pipeline(n, J, D, clustered, seed):
         exp, _, _, _ = orc.rlgr_encode_channels(q_ref, 1)
         assert got == exp
         assert torch.equal(ops.rlgr_decode(streams, 1), q)
+        assert torch.equal(ops.rlgr_decode(streams, 1, use_index=False), q)
 
 
 def test_fp32_mode_tolerance():
@@ -307,10 +309,41 @@ def test_rlgr_random_vs_oracle(zfrac, scale, n):
     x[1, -300:] = 0            # trailing zero run (tail rule)
     x[2, -1] = -1              # tail quirk: u-1 == 0 in run mode
     x[3, :] = 0
-    streams = ops.rlgr_encode(cu(x), 1)
+    streams = ops.rlgr_encode(cu(x), 1, want_stats=True)
+    exp, _, _, _ = orc.rlgr_encode_channels(x, 1)
+    assert streams.to_bytes() == exp
+    assert np.array_equal(ops.rlgr_decode(streams, 1).cpu().numpy(), x)                       # chunk-parallel, sync index
+    assert np.array_equal(ops.rlgr_decode(streams, 1, use_index=False).cpu().numpy(), x)      # channel-serial
+    assert streams.stats["chunks"] == nch * ((n + 127) // 128 + 30) // 31
+    no_index = ops.rlgr_encode(cu(x), 1, with_index=False)
+    assert no_index.sync_index is None and no_index.to_bytes() == exp
+
+
+def test_rlgr_regime_changes_and_unsigned():
+    """Dense / sparse / empty stretches inside one channel (speculation must be repaired exactly), lengths
+    around the block (128) and chunk (3968) sizes, and the unsigned mapping (flagSigned = 0)."""
+    from raht_b200 import ops
+    rng = np.random.default_rng(99)
+    parts = [np.rint(rng.laplace(0, s, 30000)) for s in (0.05, 5, 0.3, 0.01, 50, 0.0, 1, 0.002, 300)]
+    x = np.concatenate(parts).astype(np.int32)[None, :]
+    streams = ops.rlgr_encode(cu(x), 1, want_stats=True)
     exp, _, _, _ = orc.rlgr_encode_channels(x, 1)
     assert streams.to_bytes() == exp
     assert np.array_equal(ops.rlgr_decode(streams, 1).cpu().numpy(), x)
+    for n in (1, 2, 127, 128, 129, 3967, 3968, 3969, 7936, 7937, 12001):
+        for last in (None, 0, -1, 7):
+            y = np.rint(rng.laplace(0, 0.7, size=(3, n))).astype(np.int32)
+            y[1] = np.abs(y[1])
+            y[2, n // 3:] = 0
+            if last is not None:
+                y[0, -1] = last
+            for fs in (1, 0):
+                z = np.abs(y) if fs == 0 else y
+                st = ops.rlgr_encode(cu(z), fs)
+                e, _, _, _ = orc.rlgr_encode_channels(z, fs)
+                assert st.to_bytes() == e, (n, last, fs)
+                assert np.array_equal(ops.rlgr_decode(st, fs).cpu().numpy(), z), (n, last, fs)
+                assert np.array_equal(ops.rlgr_decode(st, fs, use_index=False).cpu().numpy(), z), (n, last, fs)
 
 
 # ---------------------------------------------------------------------------------------------------

@@ -1,0 +1,92 @@
+"""CPU tests of the chunk-parallel RLGR ALGORITHM (event blocks, speculation sweeps, resolve, emit)
+through the host warp emulation tests/emu/rlgr_emu.cpp, which compiles the same arithmetic header as
+the CUDA kernels (csrc/rlgr_core.cuh).  Checked against the oracle restatement of membuf.cpp, against
+the reference's own coder (oracle/_ref) when built, and against the golden KATs."""
+import ctypes as C
+import os
+import subprocess
+
+import numpy as np
+import pytest
+
+import helpers
+from oracle import oracle_ctypes as orc
+
+EMU_DIR = os.path.join(os.path.dirname(os.path.abspath(__file__)), "emu")
+
+
+@pytest.fixture(scope="module")
+def emu():
+    subprocess.run(["make", "-C", EMU_DIR], check=True, capture_output=True)
+    lib = C.CDLL(os.path.join(EMU_DIR, "_build", "librlgr_emu.so"))
+    lib.emu_rlgr_encode.restype = C.c_int64
+    lib.emu_rlgr_encode.argtypes = [C.c_void_p, C.c_int64, C.c_int, C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p, C.c_int, C.c_int]
+
+    def encode(q, flag_signed=1, sweeps=2, c1_kp=9):
+        q = np.ascontiguousarray(q, dtype=np.int32)
+        cap = q.size * 12 + 64
+        out = np.zeros(cap, dtype=np.uint8)
+        stats = np.zeros(4, dtype=np.uint64)
+        nchunks = ((q.size + 127) // 128 + 30) // 31
+        sync = np.zeros((max(nchunks, 1), 4), dtype=np.uint32)
+        nb = lib.emu_rlgr_encode(q.ctypes.data, q.size, flag_signed, out.ctypes.data, cap, stats.ctypes.data, sync.ctypes.data,
+                                 sweeps, c1_kp)
+        assert nb >= 0, nb
+        return out[:nb].tobytes(), stats, sync[:nchunks]
+    return encode
+
+
+def test_emu_golden_kats(emu):
+    for seq, out, fs in helpers.rlgr_kats():
+        got, _, _ = emu(seq, fs)
+        assert got == out, seq[:8]
+
+
+@pytest.mark.parametrize("sigma", [0.0, 0.02, 0.2, 0.5, 1.0, 3.0, 40.0, 1e6])
+def test_emu_matches_oracle_over_densities(emu, sigma):
+    rng = np.random.default_rng(int(sigma * 100) + 1)
+    q = np.rint(rng.laplace(0, sigma, 150000)) if sigma > 0 else np.zeros(150000)
+    q = np.clip(q, -2**31 + 1, 2**31 - 1).astype(np.int64)
+    for sweeps in (1, 2, 3):
+        got, stats, _ = emu(q, 1, sweeps=sweeps)
+        assert got == orc.rlgr_encode(q, 1), (sigma, sweeps)
+    if orc.ref_rlgr_available():
+        assert got == orc.ref_rlgr_encode(q, 1)[0]
+
+
+def test_emu_regime_changes_edges_and_unsigned(emu):
+    rng = np.random.default_rng(5)
+    parts = [np.rint(rng.laplace(0, s, 20000)) for s in (0.05, 5, 0.3, 0.01, 50, 0.0, 1, 0.002, 300)]
+    q = np.concatenate(parts).astype(np.int64)
+    got, stats, sync = emu(q, 1)
+    assert got == orc.rlgr_encode(q, 1)
+    assert stats[3] == len(sync)
+    for n in (1, 2, 127, 128, 129, 3967, 3968, 3969, 7936, 7937, 12001):
+        for last in (None, 0, -1, 7):
+            y = np.rint(rng.laplace(0, 0.7, n)).astype(np.int64)
+            if last is not None:
+                y[-1] = last
+            for fs in (1, 0):
+                z = np.abs(y) if fs == 0 else y
+                assert emu(z, fs)[0] == orc.rlgr_encode(z, fs), (n, last, fs)
+    z = np.zeros(50000, dtype=np.int64)
+    z[0] = 5
+    assert emu(z, 1)[0] == orc.rlgr_encode(z, 1)
+    z[:] = 0
+    z[-1] = -1
+    assert emu(z, 1)[0] == orc.rlgr_encode(z, 1)
+
+
+def test_emu_sync_index_points_at_event_boundaries(emu):
+    """Every sync entry (bit offset, first symbol, state) must let a sequential decoder resume there."""
+    rng = np.random.default_rng(11)
+    q = np.rint(rng.laplace(0, 0.6, 40000)).astype(np.int64)
+    q[9000:21000] = 0
+    buf, _, sync = emu(q, 1)
+    assert np.array_equal(orc.rlgr_decode(buf, len(q), 1), q)
+    first = sync[:, 2].astype(np.int64)
+    assert first[0] == 0 and np.all(np.diff(first) >= 0) and np.all(first <= np.arange(len(sync)) * 3968)
+    for w in range(1, len(sync)):
+        s = int(first[w])
+        assert s == 0 or q[s - 1] != 0            # an event boundary: right after a non-zero symbol
+        assert np.all(q[s: w * 3968] == 0)        # everything up to the nominal chunk start is the run of zeros
