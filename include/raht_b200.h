@@ -29,7 +29,7 @@
 extern "C" {
 #endif
 
-#define RAHT_B200_ABI_VERSION 3
+#define RAHT_B200_ABI_VERSION 4
 
 enum {
     RAHT_OK = 0,
@@ -166,16 +166,20 @@ int raht_order_ragft(const uint8_t *level, int64_t n, int64_t *order, int32_t *p
                      void *workspace, size_t workspace_bytes, void *stream);
 
 /* Transform plan: the butterflies of the tree scheduled for the fused shared-memory kernels.
- * Stage 1 cuts the rows into tiles of tile_rows Morton-contiguous rows; every butterfly whose
- * row span lies inside one tile runs there, the others ("deferred") are compacted into stage 2,
- * which is tiled again, and so on until one tile remains.  tile_rows in [128, 1024], even.
- * w (n doubles, optional): the second output of RAHT2_optimized (RAHT.py:286,325-328).
- * SYNCHRONISES `stream` once per stage (a handful of times).                                       */
+ * Stage 0 cuts the rows into tiles of tile_rows Morton-contiguous rows; every butterfly whose
+ * row span lies inside one tile runs there, the others ("deferred", at most 129 per tile) go, 8
+ * tiles' worth at a time, into a tile of the next stage, and so on until one tile remains.  The
+ * hierarchy is static: stage count, grids and buffer sizes depend on (n, tile_rows) only, so the
+ * call neither synchronises nor allocates on the device -- the plan lives in the caller's
+ * workspace (256-byte aligned, raht_plan_workspace_bytes), which must outlive it.
+ * tile_rows in [32, 1024], even.  w (n doubles, optional): the second output of RAHT2_optimized
+ * (RAHT.py:286,325-328).                                                                         */
 typedef struct raht_plan raht_plan;
-int raht_plan_create(const uint8_t *level, int64_t n, int tile_rows, double *w, raht_plan **plan,
-                     void *stream);
-void raht_plan_destroy(raht_plan *plan);
-/* info[0]=n, [1]=tile_rows, [2]=stages, [3]=device bytes held, [4+k]=rows in stage k          */
+size_t raht_plan_workspace_bytes(int64_t n, int tile_rows);
+int raht_plan_create(const uint8_t *level, int64_t n, int tile_rows, double *w, void *workspace,
+                     size_t workspace_bytes, raht_plan **plan, void *stream);
+void raht_plan_destroy(raht_plan *plan);   /* frees the host handle only */
+/* info[0]=n, [1]=tile_rows, [2]=stages, [3]=workspace bytes used, [4+k]=tiles in stage k      */
 int raht_plan_info(const raht_plan *plan, int64_t *info_host, int cap);
 
 /* ------------------------------------------------------------------------------------------------

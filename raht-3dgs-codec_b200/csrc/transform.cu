@@ -29,23 +29,14 @@ template <> struct Arith<float> {
     static __device__ __forceinline__ float sub(float a, float b) { return __fsub_rn(a, b); }
 };
 
-struct StageArgs {
-    const uint32_t *rows;      // nullptr: entries are the rows themselves (stage 0, contiguous tiles)
-    const uint8_t *to_next;
-    const uint32_t *sched;
-    const double2 *ab;
-    const TileHdr *hdr;
-};
-
 template <typename Tel> struct SmemLayout {
-    size_t off_ab, off_sched, off_rowid, off_hdr, off_flag, off_bar, total;
+    size_t off_ab, off_sched, off_hdr, off_flag, off_bar, total;
     __host__ __device__ SmemLayout(int R, int D)
     {
         size_t o = (size_t)R * D * sizeof(Tel);
         o = (o + 15) & ~(size_t)15;
         off_ab = o; o += (size_t)R * 2 * sizeof(Tel);
         off_sched = o; o += (size_t)R * 4;
-        off_rowid = o; o += (size_t)R * 4;
         off_hdr = o; o += sizeof(TileHdr);
         off_bar = o; o += 8;
         off_flag = o; o += (size_t)R;
@@ -53,21 +44,21 @@ template <typename Tel> struct SmemLayout {
     }
 };
 
-// A: primary source (row-major, Tin).  B: secondary source for rows flagged in sel (inverse: rows the
-// upper stages already wrote), may be nullptr.  O: destination.  FWD: forward butterflies in schedule
-// order, else inverse butterflies in reverse order.
+// ---- stage 0: tiles of consecutive rows ------------------------------------------------------------------
+// A: source rows (row-major, Tin).  B: second source for the rows this tile deferred (inverse only: the
+// upper stages have already rewritten them in the output), may be nullptr.  O: destination.
+// FWD: forward butterflies in schedule order, else inverse butterflies in reverse order.
 template <typename Tin, typename Tel, int DT, bool FWD>
 __global__ void __launch_bounds__(TR_THREADS)
-transform_stage_kernel(StageArgs a, const Tin *__restrict__ A, const Tel *B, const uint8_t *__restrict__ sel, Tel *O,
-                       int D_rt, int R, int use_tma)
+transform_stage0_kernel(PlanDev P, const Tin *__restrict__ A, const Tel *B, Tel *O, int D_rt, int use_tma)
 {
     extern __shared__ __align__(128) unsigned char tr_smem[];
     const int D = DT ? DT : D_rt;
+    const int R = P.tile_rows;
     const SmemLayout<Tel> L(R, D);
     Tel *s_rows = (Tel *)tr_smem;
     Tel *s_ab = (Tel *)(tr_smem + L.off_ab);
     uint32_t *s_sched = (uint32_t *)(tr_smem + L.off_sched);
-    uint32_t *s_rowid = (uint32_t *)(tr_smem + L.off_rowid);
     TileHdr *s_hdr = (TileHdr *)(tr_smem + L.off_hdr);
     uint64_t *s_bar = (uint64_t *)(tr_smem + L.off_bar);
     uint8_t *s_flag = tr_smem + L.off_flag;
@@ -75,19 +66,19 @@ transform_stage_kernel(StageArgs a, const Tin *__restrict__ A, const Tel *B, con
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int64_t tile = blockIdx.x;
     const int64_t base = tile * R;
-    const bool contiguous = (a.rows == nullptr);
 
-    if (tid < (int)(sizeof(TileHdr) / 4)) ((uint32_t *)s_hdr)[tid] = ((const uint32_t *)(a.hdr + tile))[tid];
+    if (tid < (int)(sizeof(TileHdr) / 4)) ((uint32_t *)s_hdr)[tid] = ((const uint32_t *)(P.hdr + tile))[tid];
     __syncthreads();
     const int n_rows = s_hdr->n_rows;
     const int n_bf = s_hdr->n_bf;
     const int n_rounds = s_hdr->n_rounds;
+    const size_t bf_off = s_hdr->bf_off;
     const size_t tile_bytes = (size_t)n_rows * D * sizeof(Tel);
 
     // bulk copies need 16-byte granularity; tiles that do not qualify (ragged last tile) use plain loads
     bool tma_in = false, tma_out = false;
     if constexpr (sizeof(Tin) == sizeof(Tel)) {
-        if (contiguous && use_tma && (tile_bytes % 16) == 0) {
+        if (use_tma && (tile_bytes % 16) == 0) {
             tma_in = (((uintptr_t)(A + base * D)) % 16) == 0;
             tma_out = (((uintptr_t)(O + base * D)) % 16) == 0;
         }
@@ -106,47 +97,36 @@ transform_stage_kernel(StageArgs a, const Tin *__restrict__ A, const Tel *B, con
         }
     }
 
-    // schedule, coefficients, row ids and source flags (overlaps the bulk copy)
+    // schedule and coefficients (overlaps the bulk copy)
     for (int j = tid; j < n_bf; j += TR_THREADS) {
-        s_sched[j] = a.sched[base + j];
-        double2 c = a.ab[base + j];
+        s_sched[j] = P.sched[bf_off + j];
+        double2 c = P.ab[bf_off + j];
         s_ab[2 * j] = (Tel)c.x;
         s_ab[2 * j + 1] = (Tel)c.y;
     }
-    const bool patch = (B != nullptr) && (sel != nullptr);
-    for (int j = tid; j < n_rows; j += TR_THREADS) {
-        s_rowid[j] = contiguous ? (uint32_t)(base + j) : a.rows[base + j];
-        s_flag[j] = patch ? sel[base + j] : (uint8_t)0;
+    const bool patch = (B != nullptr);
+    if (patch) {
+        for (int j = tid; j < n_rows; j += TR_THREADS) s_flag[j] = 0;
+        __syncthreads();
+        const int n_def = s_hdr->n_def;
+        for (int j = tid; j < n_def; j += TR_THREADS) s_flag[P.def_local[(size_t)tile * PLAN_DEFER_MAX + j]] = 1;
     }
     __syncthreads();
 
-    if (contiguous) {
-        if (tma_in) {
-            mbar_wait(s_bar, 0);
-        } else {
-            const Tin *src = A + base * D;
-            const int n_el = n_rows * D;
-            for (int i = tid; i < n_el; i += TR_THREADS) s_rows[i] = (Tel)src[i];
-        }
-        if (patch) {
-            if (!tma_in) __syncthreads();
-            for (int j = warp; j < n_rows; j += TR_WARPS)
-                if (s_flag[j]) {
-                    const Tel *src = B + (size_t)(base + j) * D;
-                    for (int c = lane; c < D; c += 32) s_rows[j * D + c] = src[c];
-                }
-        }
+    if (tma_in) {
+        mbar_wait(s_bar, 0);
     } else {
-        for (int j = warp; j < n_rows; j += TR_WARPS) {
-            const size_t row = s_rowid[j];
+        const Tin *src = A + base * D;
+        const int n_el = n_rows * D;
+        for (int i = tid; i < n_el; i += TR_THREADS) s_rows[i] = (Tel)src[i];
+        __syncthreads();
+    }
+    if (patch) {
+        for (int j = warp; j < n_rows; j += TR_WARPS)
             if (s_flag[j]) {
-                const Tel *src = B + row * D;
+                const Tel *src = B + (size_t)(base + j) * D;
                 for (int c = lane; c < D; c += 32) s_rows[j * D + c] = src[c];
-            } else {
-                const Tin *src = A + row * D;
-                for (int c = lane; c < D; c += 32) s_rows[j * D + c] = (Tel)src[c];
             }
-        }
     }
     __syncthreads();
 
@@ -161,7 +141,7 @@ transform_stage_kernel(StageArgs a, const Tin *__restrict__ A, const Tel *B, con
             const int e = lo + idx / D;
             const int c = idx - (idx / D) * D;
             const uint32_t ent = s_sched[e];
-            const int r = ent & 1023, s = (ent >> 10) & 1023;
+            const int r = ent & 4095, s = (ent >> 12) & 4095;
             const Tel ca = s_ab[2 * e], cb = s_ab[2 * e + 1];
             Tel *p0 = s_rows + s * D + c, *p1 = s_rows + r * D + c;
             const Tel x0 = *p0, x1 = *p1;
@@ -177,71 +157,173 @@ transform_stage_kernel(StageArgs a, const Tin *__restrict__ A, const Tel *B, con
     }
 
     // write back
-    if (contiguous) {
-        if (tma_out) {
-            fence_proxy_async();
-            __syncthreads();
-            if (tid == 0) {
-                char *dst = (char *)(O + base * D);
-                const char *src = (const char *)s_rows;
-                for (size_t off = 0; off < tile_bytes; off += TMA_CHUNK) {
-                    unsigned sz = (unsigned)((tile_bytes - off) < TMA_CHUNK ? (tile_bytes - off) : TMA_CHUNK);
-                    bulk_s2g(dst + off, src + off, sz);
-                }
-                bulk_commit();
-                bulk_wait_read0();
+    if (tma_out) {
+        fence_proxy_async();
+        __syncthreads();
+        if (tid == 0) {
+            char *dst = (char *)(O + base * D);
+            const char *src = (const char *)s_rows;
+            for (size_t off = 0; off < tile_bytes; off += TMA_CHUNK) {
+                unsigned sz = (unsigned)((tile_bytes - off) < TMA_CHUNK ? (tile_bytes - off) : TMA_CHUNK);
+                bulk_s2g(dst + off, src + off, sz);
             }
-        } else {
-            Tel *dst = O + base * D;
-            const int n_el = n_rows * D;
-            for (int i = tid; i < n_el; i += TR_THREADS) dst[i] = s_rows[i];
+            bulk_commit();
+            bulk_wait_read0();
         }
     } else {
-        for (int j = warp; j < n_rows; j += TR_WARPS) {
-            Tel *dst = O + (size_t)s_rowid[j] * D;
-            for (int c = lane; c < D; c += 32) dst[c] = s_rows[j * D + c];
+        Tel *dst = O + base * D;
+        const int n_el = n_rows * D;
+        for (int i = tid; i < n_el; i += TR_THREADS) dst[i] = s_rows[i];
+    }
+}
+
+// ---- stages >= 1: tiles of gathered rows -------------------------------------------------------------------
+// The entries of tile j are the rows its (up to) 8 child tiles deferred, at most 1032.  The channels are
+// processed in passes of DS = min(D, UP_ELEMS / n_rows) so that any tile fits the same shared-memory
+// budget; a typical tile (100-300 rows) takes one pass.  A: source of a row unless this tile deferred
+// it and B is given (inverse: then B, which the upper stage already wrote).  O: destination.
+constexpr int UP_ELEMS = 8192;     // row elements staged per pass
+
+template <typename Tel, bool FWD>
+__global__ void __launch_bounds__(TR_THREADS)
+transform_upper_kernel(PlanDev P, int stage, const Tel *A, const Tel *B, Tel *O, int D)
+{
+    extern __shared__ __align__(128) unsigned char tr_smem[];
+    Tel *s_rows = (Tel *)tr_smem;                                          // UP_ELEMS
+    Tel *s_ab = s_rows + UP_ELEMS;                                         // 2 * PLAN_UP_CAP
+    uint32_t *s_sched = (uint32_t *)(s_ab + 2 * PLAN_UP_CAP);              // PLAN_UP_CAP
+    uint32_t *s_rowid = s_sched + PLAN_UP_CAP;                             // PLAN_UP_CAP
+    uint8_t *s_flag = (uint8_t *)(s_rowid + PLAN_UP_CAP);                  // PLAN_UP_CAP
+    __shared__ TileHdr s_hdr;
+    __shared__ int s_off[PLAN_FANIN + 1];
+
+    const int tid = threadIdx.x;
+    const int64_t tile = blockIdx.x;
+    const int64_t gt = P.tile_base[stage] + tile;
+    if (tid < (int)(sizeof(TileHdr) / 4)) ((uint32_t *)&s_hdr)[tid] = ((const uint32_t *)(P.hdr + gt))[tid];
+    const int64_t c0 = tile * PLAN_FANIN;
+    const int64_t cbase = P.tile_base[stage - 1];
+    if (tid == 0) {
+        int run = 0;
+        for (int c = 0; c < PLAN_FANIN; ++c) {
+            s_off[c] = run;
+            if (c0 + c < P.tiles[stage - 1]) run += min((int)P.hdr[cbase + c0 + c].n_def, PLAN_DEFER_MAX);
         }
+        s_off[PLAN_FANIN] = run;
+    }
+    __syncthreads();
+    const int n_rows = s_hdr.n_rows;
+    const int n_bf = s_hdr.n_bf;
+    const int n_rounds = s_hdr.n_rounds;
+    const size_t bf_off = s_hdr.bf_off;
+    if (n_bf == 0) return;                                   // nothing scheduled: every row stays as it is
+    for (int c = 0; c < PLAN_FANIN; ++c) {
+        const int cnt = s_off[c + 1] - s_off[c];
+        const size_t src = (size_t)(cbase + c0 + c) * PLAN_DEFER_MAX;
+        for (int j = tid; j < cnt; j += TR_THREADS) s_rowid[s_off[c] + j] = P.def_rows[src + j];
+    }
+    for (int j = tid; j < n_rows; j += TR_THREADS) s_flag[j] = 0;
+    for (int j = tid; j < n_bf; j += TR_THREADS) {
+        s_sched[j] = P.sched[bf_off + j];
+        double2 c = P.ab[bf_off + j];
+        s_ab[2 * j] = (Tel)c.x;
+        s_ab[2 * j + 1] = (Tel)c.y;
+    }
+    __syncthreads();
+    if (B) {
+        const int n_def = s_hdr.n_def;
+        for (int j = tid; j < n_def; j += TR_THREADS) s_flag[P.def_local[(size_t)gt * PLAN_DEFER_MAX + j]] = 1;
+    }
+    __syncthreads();
+
+    using AR = Arith<Tel>;
+    int DS = UP_ELEMS / n_rows;
+    if (DS > D) DS = D;
+    for (int d0 = 0; d0 < D; d0 += DS) {
+        const int dn = min(DS, D - d0);
+        const int n_el = n_rows * dn;
+        for (int i = tid; i < n_el; i += TR_THREADS) {
+            const int j = i / dn, c = i - j * dn;
+            const Tel *src = (B && s_flag[j]) ? B : A;
+            s_rows[j * dn + c] = src[(size_t)s_rowid[j] * D + d0 + c];
+        }
+        __syncthreads();
+        for (int kk = 0; kk < n_rounds; ++kk) {
+            const int k = FWD ? kk : n_rounds - 1 - kk;
+            const int lo = k ? s_hdr.round_end[k - 1] : 0;
+            const int hi = s_hdr.round_end[k];
+            const int work = (hi - lo) * dn;
+            for (int idx = tid; idx < work; idx += TR_THREADS) {
+                const int e = lo + idx / dn;
+                const int c = idx - (idx / dn) * dn;
+                const uint32_t ent = s_sched[e];
+                const int r = ent & 4095, s = (ent >> 12) & 4095;
+                const Tel ca = s_ab[2 * e], cb = s_ab[2 * e + 1];
+                Tel *p0 = s_rows + s * dn + c, *p1 = s_rows + r * dn + c;
+                const Tel x0 = *p0, x1 = *p1;
+                if (FWD) {
+                    *p0 = AR::add(AR::mul(ca, x0), AR::mul(cb, x1));
+                    *p1 = AR::add(AR::mul(-cb, x0), AR::mul(ca, x1));
+                } else {
+                    *p0 = AR::sub(AR::mul(ca, x0), AR::mul(cb, x1));
+                    *p1 = AR::add(AR::mul(cb, x0), AR::mul(ca, x1));
+                }
+            }
+            __syncthreads();
+        }
+        for (int i = tid; i < n_el; i += TR_THREADS) {
+            const int j = i / dn, c = i - j * dn;
+            O[(size_t)s_rowid[j] * D + d0 + c] = s_rows[j * dn + c];
+        }
+        __syncthreads();
     }
 }
 
 template <typename Tin, typename Tel, int DT, bool FWD>
-int launch_stage(const raht_plan *P, int k, const Tin *A, const Tel *B, const uint8_t *sel, Tel *O, int D, int use_tma,
-                 cudaStream_t st)
+int launch_stage0(const raht_plan *P, const Tin *A, const Tel *B, Tel *O, int D, int use_tma, cudaStream_t st)
 {
-    const PlanStage &S = P->st[k];
-    const int R = P->tile_rows;
+    const int R = P->d.tile_rows;
     SmemLayout<Tel> L(R, D);
-    auto kern = transform_stage_kernel<Tin, Tel, DT, FWD>;
+    auto kern = transform_stage0_kernel<Tin, Tel, DT, FWD>;
     if (L.total > 227 * 1024) {
         raht_set_error("transform: tile of %d rows x %d channels needs %zu bytes of shared memory (> 227 KB)", R, D, L.total);
         return RAHT_E_INVALID;
     }
     RAHT_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)L.total));
-    StageArgs a{S.rows, S.to_next, S.sched, S.ab, S.hdr};
-    (raht_count_launches(1), kern)<<<(unsigned)S.n_tiles, TR_THREADS, L.total, st>>>(a, A, B, sel, O, D, R, use_tma);
+    (raht_count_launches(1), kern)<<<(unsigned)P->d.tiles[0], TR_THREADS, L.total, st>>>(P->d, A, B, O, D, use_tma);
     RAHT_LAUNCH_CHECK();
     return RAHT_OK;
 }
 
 template <typename Tin, typename Tel, bool FWD>
-int launch_stage_d(const raht_plan *P, int k, const Tin *A, const Tel *B, const uint8_t *sel, Tel *O, int D, int use_tma,
-                   cudaStream_t st)
+int launch_stage0_d(const raht_plan *P, const Tin *A, const Tel *B, Tel *O, int D, int use_tma, cudaStream_t st)
 {
     switch (D) {
-    case 3: return launch_stage<Tin, Tel, 3, FWD>(P, k, A, B, sel, O, D, use_tma, st);
-    case 56: return launch_stage<Tin, Tel, 56, FWD>(P, k, A, B, sel, O, D, use_tma, st);
-    case 59: return launch_stage<Tin, Tel, 59, FWD>(P, k, A, B, sel, O, D, use_tma, st);
-    default: return launch_stage<Tin, Tel, 0, FWD>(P, k, A, B, sel, O, D, use_tma, st);
+    case 3: return launch_stage0<Tin, Tel, 3, FWD>(P, A, B, O, D, use_tma, st);
+    case 56: return launch_stage0<Tin, Tel, 56, FWD>(P, A, B, O, D, use_tma, st);
+    case 59: return launch_stage0<Tin, Tel, 59, FWD>(P, A, B, O, D, use_tma, st);
+    default: return launch_stage0<Tin, Tel, 0, FWD>(P, A, B, O, D, use_tma, st);
     }
+}
+
+template <typename Tel, bool FWD>
+int launch_upper(const raht_plan *P, int k, const Tel *A, const Tel *B, Tel *O, int D, cudaStream_t st)
+{
+    const size_t smem = (size_t)(UP_ELEMS + 2 * PLAN_UP_CAP) * sizeof(Tel) + (size_t)PLAN_UP_CAP * 9 + 16;
+    auto kern = transform_upper_kernel<Tel, FWD>;
+    RAHT_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    (raht_count_launches(1), kern)<<<(unsigned)P->d.tiles[k], TR_THREADS, smem, st>>>(P->d, k, A, B, O, D);
+    RAHT_LAUNCH_CHECK();
+    return RAHT_OK;
 }
 
 template <typename Tin, typename Tel>
 int forward_impl(const raht_plan *P, const Tin *C, Tel *T, int D, int use_tma, cudaStream_t st)
 {
     // stage 0: C -> T (every row); stages >= 1: in place on T
-    int rc = launch_stage_d<Tin, Tel, true>(P, 0, C, (const Tel *)nullptr, nullptr, T, D, use_tma, st);
-    for (int k = 1; k < P->n_stages && rc == RAHT_OK; ++k)
-        rc = launch_stage_d<Tel, Tel, true>(P, k, (const Tel *)T, (const Tel *)nullptr, nullptr, T, D, use_tma, st);
+    int rc = launch_stage0_d<Tin, Tel, true>(P, C, (const Tel *)nullptr, T, D, use_tma, st);
+    for (int k = 1; k < P->d.n_stages && rc == RAHT_OK; ++k)
+        rc = launch_upper<Tel, true>(P, k, (const Tel *)T, (const Tel *)nullptr, T, D, st);
     return rc;
 }
 
@@ -249,13 +331,12 @@ template <typename Tel>
 int inverse_impl(const raht_plan *P, const Tel *T, Tel *C, int D, int use_tma, cudaStream_t st)
 {
     // top stage first.  A row is read from C when an upper stage has already rewritten it (the rows a
-    // stage carries into the next one), else from T; every row of a stage is written to C.
+    // tile defers to the next stage), else from T; every row of a tile that ran is written to C.
     int rc = RAHT_OK;
-    for (int k = P->n_stages - 1; k >= 0 && rc == RAHT_OK; --k) {
-        const bool top = (k == P->n_stages - 1);
-        rc = launch_stage_d<Tel, Tel, false>(P, k, T, top ? (const Tel *)nullptr : (const Tel *)C,
-                                             top ? nullptr : P->st[k].to_next, C, D, use_tma, st);
-    }
+    const int S = P->d.n_stages;
+    for (int k = S - 1; k >= 1 && rc == RAHT_OK; --k)
+        rc = launch_upper<Tel, false>(P, k, T, k == S - 1 ? (const Tel *)nullptr : (const Tel *)C, C, D, st);
+    if (rc == RAHT_OK) rc = launch_stage0_d<Tel, Tel, false>(P, T, S > 1 ? (const Tel *)C : (const Tel *)nullptr, C, D, use_tma, st);
     return rc;
 }
 
@@ -265,7 +346,7 @@ RAHT_API int raht_forward(const raht_plan *plan, const void *C, int c_dtype, int
                           void *stream)
 {
     RAHT_REQUIRE(plan && D >= 1, "raht_forward: bad arguments");
-    if (plan->n == 0) return RAHT_OK;
+    if (plan->d.n == 0) return RAHT_OK;
     RAHT_REQUIRE(C && T && C != T, "raht_forward: C and T must be distinct non-null device pointers");
     cudaStream_t st = (cudaStream_t)stream;
     const int use_tma = (flags & 1) ? 0 : 1;
@@ -280,7 +361,7 @@ RAHT_API int raht_forward(const raht_plan *plan, const void *C, int c_dtype, int
 RAHT_API int raht_inverse(const raht_plan *plan, const void *T, int t_dtype, int D, void *C, int flags, void *stream)
 {
     RAHT_REQUIRE(plan && D >= 1, "raht_inverse: bad arguments");
-    if (plan->n == 0) return RAHT_OK;
+    if (plan->d.n == 0) return RAHT_OK;
     RAHT_REQUIRE(C && T && C != T, "raht_inverse: T and C must be distinct non-null device pointers");
     cudaStream_t st = (cudaStream_t)stream;
     const int use_tma = (flags & 1) ? 0 : 1;

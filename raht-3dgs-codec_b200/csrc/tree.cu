@@ -130,43 +130,72 @@ __global__ void __launch_bounds__(OR_THREADS) order_scatter_kernel(const uint8_t
     }
 }
 
-// ---- transform plan: one stage ------------------------------------------------------------------
+// ---- transform plan: one tile of one stage (plan.cuh) ------------------------------------------------
 constexpr int PB_THREADS = 256;
+constexpr int PB_WARPS = PB_THREADS / 32;
+
+__global__ void plan_init_kernel(PlanDev P) { *P.bump = (unsigned int)P.slots0; }
 
 __global__ void __launch_bounds__(PB_THREADS)
-plan_stage_kernel(const uint32_t *__restrict__ rows, const uint8_t *__restrict__ lev, int64_t n_entries, int64_t n_total,
-                  int R, uint8_t *__restrict__ to_next, uint32_t *__restrict__ sched, double2 *__restrict__ ab,
-                  TileHdr *__restrict__ hdr, double *__restrict__ w)
+plan_tile_kernel(PlanDev P, int stage, const uint8_t *__restrict__ level, double *__restrict__ w)
 {
-    extern __shared__ __align__(16) unsigned char pb_smem[];
-    uint32_t *s_orig = (uint32_t *)pb_smem;          // R + 1
-    uint16_t *s_s = (uint16_t *)(s_orig + R + 1);    // R   local index of the left row, 0xffff = not in tile
-    uint16_t *s_t = s_s + R;                         // R   local index of the right boundary
-    uint8_t *s_lev = (uint8_t *)(s_t + R);           // R + 1
+    __shared__ uint32_t s_orig[PLAN_UP_CAP + 1];   // original row of each entry (+ virtual end of the cloud)
+    __shared__ uint16_t s_s[PLAN_UP_CAP];          // local index of the left row, 0xffff = not schedulable here
+    __shared__ uint16_t s_t[PLAN_UP_CAP];          // local index of the right boundary
+    __shared__ uint8_t s_lev[PLAN_UP_CAP + 1];
     __shared__ int hist[PLAN_MAX_ROUNDS], offs[PLAN_MAX_ROUNDS], cur[PLAN_MAX_ROUNDS];
-    __shared__ int s_nbf, s_nr;
+    __shared__ int s_off[PLAN_FANIN + 1];
+    __shared__ int wsum[PB_WARPS];
+    __shared__ int s_nbf, s_nr, s_bfoff, s_run;
 
-    const int tid = threadIdx.x;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int64_t tile = blockIdx.x;
-    const int64_t base = tile * R;
-    const int n_rows = (int)min((int64_t)R, n_entries - base);
-    const bool last = (tile == (int64_t)gridDim.x - 1);
-    const bool multi = gridDim.x > 1;
+    const int64_t gt = P.tile_base[stage] + tile;
+    const bool last = tile == P.tiles[stage] - 1;
+    const bool multi = P.tiles[stage] > 1;
+    const int64_t n_total = P.n;
 
     if (tid < PLAN_MAX_ROUNDS) { hist[tid] = 0; cur[tid] = 0; }
-    for (int j = tid; j < n_rows; j += PB_THREADS) {
-        s_lev[j] = lev[base + j];
-        s_orig[j] = rows ? rows[base + j] : (uint32_t)(base + j);
+    int n_rows;
+    if (stage == 0) {
+        const int64_t base = tile * P.tile_rows;
+        n_rows = (int)min((int64_t)P.tile_rows, n_total - base);
+        for (int j = tid; j < n_rows; j += PB_THREADS) {
+            s_lev[j] = level[base + j];
+            s_orig[j] = (uint32_t)(base + j);
+        }
+    } else {
+        const int64_t c0 = tile * PLAN_FANIN;
+        const int64_t cbase = P.tile_base[stage - 1];
+        if (tid == 0) {
+            int run = 0;
+            for (int c = 0; c < PLAN_FANIN; ++c) {
+                s_off[c] = run;
+                if (c0 + c < P.tiles[stage - 1]) run += min((int)P.hdr[cbase + c0 + c].n_def, PLAN_DEFER_MAX);
+            }
+            s_off[PLAN_FANIN] = run;
+        }
+        __syncthreads();
+        n_rows = s_off[PLAN_FANIN];
+        for (int c = 0; c < PLAN_FANIN; ++c) {
+            const int cnt = s_off[c + 1] - s_off[c];
+            const size_t src = (size_t)(cbase + c0 + c) * PLAN_DEFER_MAX;
+            for (int j = tid; j < cnt; j += PB_THREADS) {
+                s_orig[s_off[c] + j] = P.def_rows[src + j];
+                s_lev[s_off[c] + j] = P.def_lev[src + j];
+            }
+        }
     }
     if (tid == 0 && last) { s_lev[n_rows] = 255; s_orig[n_rows] = (uint32_t)n_total; }   // virtual end of the cloud
     __syncthreads();
 
+    // partner search: s = nearest earlier entry with a higher level, t = nearest later one
     const int lim = last ? n_rows + 1 : n_rows;
     for (int j = tid; j < n_rows; j += PB_THREADS) {
         const int l = s_lev[j];
         if (l == 255) {                                   // the root: never a right sibling
             s_s[j] = 0xffff;
-            to_next[base + j] = multi ? 1 : 0;
+            s_t[j] = multi ? 1 : 0;                       // s_t doubles as the "deferred" flag for unschedulable entries
             if (!multi && w) w[s_orig[j]] = (double)n_total;
             continue;
         }
@@ -178,11 +207,37 @@ plan_stage_kernel(const uint32_t *__restrict__ rows, const uint8_t *__restrict__
                 if (s_lev[i] > l) { t = i; break; }
         const bool in_tile = (s >= 0) && (t >= 0);
         s_s[j] = in_tile ? (uint16_t)s : (uint16_t)0xffff;
-        s_t[j] = (uint16_t)(t >= 0 ? t : 0);
-        to_next[base + j] = in_tile ? 0 : 1;
+        s_t[j] = in_tile ? (uint16_t)t : (uint16_t)1;
         if (in_tile) atomicAdd(&hist[min(l, PLAN_MAX_ROUNDS - 1)], 1);
     }
+    if (tid == 0) s_run = 0;
     __syncthreads();
+
+    // deferred entries, in order, into this tile's slot of the next stage's input
+    for (int base = 0; base < n_rows; base += PB_THREADS) {
+        const int j = base + tid;
+        const bool p = j < n_rows && s_s[j] == 0xffff && s_t[j] == 1;
+        const unsigned b = __ballot_sync(~0u, p);
+        if (lane == 0) wsum[warp] = __popc(b);
+        __syncthreads();
+        int woff = 0, tot = 0;
+        for (int x = 0; x < PB_WARPS; ++x) {
+            if (x < warp) woff += wsum[x];
+            tot += wsum[x];
+        }
+        const int pos = s_run + woff + __popc(b & lanemask_lt());
+        if (p && pos < PLAN_DEFER_MAX) {
+            const size_t dst = (size_t)gt * PLAN_DEFER_MAX + pos;
+            P.def_rows[dst] = s_orig[j];
+            P.def_lev[dst] = s_lev[j];
+            P.def_local[dst] = (uint16_t)j;
+        }
+        __syncthreads();
+        if (tid == 0) s_run += tot;
+        __syncthreads();
+    }
+
+    TileHdr *H = P.hdr + gt;
     if (tid < 32) {                                       // scan of the 64-bin level histogram by one warp
         int h0 = hist[tid], h1 = hist[tid + 32];
         int x0 = h0, x1 = h1;
@@ -194,12 +249,16 @@ plan_stage_kernel(const uint32_t *__restrict__ rows, const uint8_t *__restrict__
         offs[tid] = x0 - h0;
         offs[tid + 32] = tot0 + x1 - h1;
         unsigned m0 = __ballot_sync(~0u, h0 > 0), m1 = __ballot_sync(~0u, h1 > 0);
-        TileHdr *H = hdr + tile;
         if (h0 > 0) H->round_end[__popc(m0 & lanemask_lt())] = (uint16_t)x0;
         if (h1 > 0) H->round_end[__popc(m0) + __popc(m1 & lanemask_lt())] = (uint16_t)(tot0 + x1);
-        if (tid == 31) { s_nbf = tot0 + x1; s_nr = __popc(m0) + __popc(m1); }
+        if (tid == 31) {
+            s_nbf = tot0 + x1;
+            s_nr = __popc(m0) + __popc(m1);
+            s_bfoff = stage == 0 ? (int)(tile * P.tile_rows) : (int)atomicAdd(P.bump, (unsigned int)(tot0 + x1));
+        }
     }
     __syncthreads();
+    const size_t bf_off = (size_t)(unsigned int)s_bfoff;
     for (int j = tid; j < n_rows; j += PB_THREADS) {
         const int s = s_s[j];
         if (s == 0xffff) continue;
@@ -208,36 +267,56 @@ plan_stage_kernel(const uint32_t *__restrict__ rows, const uint8_t *__restrict__
         const double w0 = (double)(s_orig[j] - s_orig[s]);
         const double w1 = (double)(s_orig[t] - s_orig[j]);
         const double den = __dadd_rn(w0, w1);                           // RAHT.py:317
-        sched[base + p] = (uint32_t)j | ((uint32_t)s << 10) | ((uint32_t)l << 20);
-        ab[base + p] = make_double2(__dsqrt_rn(__ddiv_rn(w0, den)), __dsqrt_rn(__ddiv_rn(w1, den)));   // :321-322
+        P.sched[bf_off + p] = sched_pack(j, s, l);
+        P.ab[bf_off + p] = make_double2(__dsqrt_rn(__ddiv_rn(w0, den)), __dsqrt_rn(__ddiv_rn(w1, den)));   // :321-322
         if (w) w[s_orig[j]] = den;                                      // :325-328 (final value of w[i1])
     }
     if (tid == 0) {
-        TileHdr *H = hdr + tile;
         H->n_rows = (uint16_t)n_rows;
         H->n_bf = (uint16_t)s_nbf;
         H->n_rounds = (uint16_t)s_nr;
+        H->n_def = (uint16_t)min(s_run, PLAN_DEFER_MAX);
+        H->bf_off = (uint32_t)s_bfoff;
         H->pad = 0;
     }
 }
 
-struct CarryPred {
-    const uint8_t *flag;
-    __device__ bool operator()(int64_t i) const { return flag[i] != 0; }
-};
-struct CarryEmit {
-    const uint32_t *rows;
-    const uint8_t *lev;
-    uint32_t *rows_out;
-    uint8_t *lev_out;
-    __device__ void operator()(unsigned long long pos, int64_t i) const
-    {
-        rows_out[pos] = rows ? rows[i] : (uint32_t)i;
-        lev_out[pos] = lev[i];
-    }
+struct PlanLayout {
+    PlanDev d;          // sizes and stage table filled in; pointers as byte offsets from the workspace start
+    size_t off_hdr, off_def_rows, off_def_local, off_def_lev, off_sched, off_ab, off_bump, total;
 };
 
-size_t plan_smem_bytes(int R) { return (size_t)(R + 1) * 4 + (size_t)R * 4 + (size_t)(R + 1) + 16; }
+PlanLayout plan_layout(int64_t n, int tile_rows)
+{
+    PlanLayout L;
+    PlanDev &d = L.d;
+    d = PlanDev();
+    d.n = n;
+    d.tile_rows = tile_rows;
+    int k = 0;
+    int64_t t = n > 0 ? (n + tile_rows - 1) / tile_rows : 0, base = 0;
+    while (t > 0) {
+        d.tiles[k] = t;
+        d.tile_base[k] = base;
+        base += t;
+        ++k;
+        if (t == 1 || k >= PLAN_MAX_STAGES) break;
+        t = (t + PLAN_FANIN - 1) / PLAN_FANIN;
+    }
+    d.n_stages = k;
+    d.tiles_total = base;
+    d.slots0 = k ? d.tiles[0] * tile_rows : 0;
+    size_t o = 0;
+    L.off_hdr = o; o += align_up((size_t)base * sizeof(TileHdr), 256);
+    L.off_def_rows = o; o += align_up((size_t)base * PLAN_DEFER_MAX * 4, 256);
+    L.off_def_local = o; o += align_up((size_t)base * PLAN_DEFER_MAX * 2, 256);
+    L.off_def_lev = o; o += align_up((size_t)base * PLAN_DEFER_MAX, 256);
+    L.off_sched = o; o += align_up((size_t)(d.slots0 + n) * 4, 256);
+    L.off_ab = o; o += align_up((size_t)(d.slots0 + n) * 16, 256);
+    L.off_bump = o; o += 256;
+    L.total = o;
+    return L;
+}
 
 }  // namespace
 
@@ -306,123 +385,54 @@ RAHT_API int raht_order_ragft(const uint8_t *level, int64_t n, int64_t *order, i
 }
 
 // ---- plan create / destroy -------------------------------------------------------------------------
-RAHT_API void raht_plan_destroy(raht_plan *plan)
+RAHT_API void raht_plan_destroy(raht_plan *plan) { delete plan; }
+
+RAHT_API size_t raht_plan_workspace_bytes(int64_t n, int tile_rows)
 {
-    if (!plan) return;
-    for (int k = 0; k < plan->n_stages; ++k) {
-        PlanStage &S = plan->st[k];
-        cudaFree(S.rows);
-        cudaFree(S.to_next);
-        cudaFree(S.sched);
-        cudaFree(S.ab);
-        cudaFree(S.hdr);
-    }
-    delete plan;
+    if (n < 0 || tile_rows < 32 || tile_rows > 1024) return 0;
+    return plan_layout(n, tile_rows).total + 256;
 }
 
-#define PLAN_CUDA(call)                                                                            \
-    do {                                                                                           \
-        cudaError_t e__ = (call);                                                                  \
-        if (e__ != cudaSuccess) {                                                                  \
-            raht_set_error("%s:%d %s: %s", __FILE__, __LINE__, #call, cudaGetErrorString(e__));    \
-            cudaFree(lev_cur_owned);                                                               \
-            cudaFree(sel_ws);                                                                      \
-            cudaFree(d_count);                                                                     \
-            raht_plan_destroy(P);                                                                  \
-            return RAHT_E_CUDA;                                                                    \
-        }                                                                                          \
-    } while (0)
-
-RAHT_API int raht_plan_create(const uint8_t *level, int64_t n, int tile_rows, double *w, raht_plan **plan, void *stream)
+RAHT_API int raht_plan_create(const uint8_t *level, int64_t n, int tile_rows, double *w, void *workspace,
+                              size_t workspace_bytes, raht_plan **plan, void *stream)
 {
     RAHT_REQUIRE(plan, "raht_plan_create: plan is null");
     *plan = nullptr;
     RAHT_REQUIRE(n >= 0 && n < ((int64_t)1 << 32) - 1, "raht_plan_create: n out of range");
-    RAHT_REQUIRE(tile_rows >= 128 && tile_rows <= 1024 && (tile_rows % 2) == 0,
-                 "raht_plan_create: tile_rows must be even and in [128, 1024]");
+    RAHT_REQUIRE(tile_rows >= 32 && tile_rows <= 1024 && (tile_rows % 2) == 0,
+                 "raht_plan_create: tile_rows must be even and in [32, 1024]");
     RAHT_REQUIRE(n == 0 || level, "raht_plan_create: level is null");
-    cudaStream_t st = (cudaStream_t)stream;
+    PlanLayout L = plan_layout(n, tile_rows);
+    RAHT_REQUIRE(L.d.n_stages < PLAN_MAX_STAGES, "raht_plan_create: too many stages");
+    RAHT_REQUIRE((uint64_t)(L.d.slots0 + n) < ((uint64_t)1 << 32), "raht_plan_create: schedule does not fit 32-bit slots");
+    if (n > 0 && (!workspace || workspace_bytes < L.total || ((uintptr_t)workspace & 255) != 0)) {
+        raht_set_error("raht_plan_create: workspace too small or not 256-byte aligned (%zu < %zu)", workspace_bytes, L.total);
+        return RAHT_E_WORKSPACE;
+    }
     raht_plan *P = new (std::nothrow) raht_plan();
     RAHT_REQUIRE(P, "raht_plan_create: out of host memory");
-    P->n = n;
-    P->tile_rows = tile_rows;
-    P->n_stages = 0;
-    P->bytes = 0;
-    const int R = tile_rows;
-    uint8_t *lev_cur_owned = nullptr;     // level array of the current stage when it is ours
-    void *sel_ws = nullptr;
-    int64_t *d_count = nullptr;
-    if (n == 0) { *plan = P; return RAHT_OK; }
-
-    PLAN_CUDA(cudaMalloc(&sel_ws, sel_workspace_bytes(n)));
-    PLAN_CUDA(cudaMalloc(&d_count, 256));
-    if (plan_smem_bytes(R) > 48 * 1024)
-        PLAN_CUDA(cudaFuncSetAttribute(plan_stage_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)plan_smem_bytes(R)));
-
-    const uint8_t *lev_cur = level;
-    uint32_t *rows_cur = nullptr;
-    int64_t n_cur = n;
-    for (int k = 0;; ++k) {
-        if (k >= PLAN_MAX_STAGES) {
-            raht_set_error("raht_plan_create: too many stages");
-            cudaFree(lev_cur_owned); cudaFree(sel_ws); cudaFree(d_count);
-            raht_plan_destroy(P);
-            return RAHT_E_INVALID;
+    char *ws = (char *)workspace;
+    P->d = L.d;
+    P->bytes = L.total;
+    P->d.hdr = (TileHdr *)(ws + L.off_hdr);
+    P->d.def_rows = (uint32_t *)(ws + L.off_def_rows);
+    P->d.def_local = (uint16_t *)(ws + L.off_def_local);
+    P->d.def_lev = (uint8_t *)(ws + L.off_def_lev);
+    P->d.sched = (uint32_t *)(ws + L.off_sched);
+    P->d.ab = (double2 *)(ws + L.off_ab);
+    P->d.bump = (unsigned int *)(ws + L.off_bump);
+    if (n > 0) {
+        cudaStream_t st = (cudaStream_t)stream;
+        (raht_count_launches(1), plan_init_kernel)<<<1, 1, 0, st>>>(P->d);
+        for (int k = 0; k < P->d.n_stages; ++k)
+            (raht_count_launches(1), plan_tile_kernel)<<<(unsigned)P->d.tiles[k], PB_THREADS, 0, st>>>(P->d, k, level, w);
+        cudaError_t e = cudaGetLastError();
+        if (e != cudaSuccess) {
+            raht_set_error("raht_plan_create: launch: %s", cudaGetErrorString(e));
+            delete P;
+            return RAHT_E_CUDA;
         }
-        PlanStage &S = P->st[k];
-        S = PlanStage();
-        P->n_stages = k + 1;
-        S.n_entries = n_cur;
-        S.n_tiles = (n_cur + R - 1) / R;
-        S.rows = rows_cur;                                    // ownership moves into the plan
-        rows_cur = nullptr;
-        size_t slots = (size_t)S.n_tiles * R;
-        PLAN_CUDA(cudaMalloc(&S.to_next, (size_t)n_cur));
-        PLAN_CUDA(cudaMalloc(&S.sched, slots * sizeof(uint32_t)));
-        PLAN_CUDA(cudaMalloc(&S.ab, slots * sizeof(double2)));
-        PLAN_CUDA(cudaMalloc(&S.hdr, (size_t)S.n_tiles * sizeof(TileHdr)));
-        P->bytes += (size_t)n_cur + slots * 20 + (size_t)S.n_tiles * sizeof(TileHdr) + (S.rows ? (size_t)n_cur * 4 : 0);
-        (raht_count_launches(1), plan_stage_kernel)<<<(unsigned)S.n_tiles, PB_THREADS, plan_smem_bytes(R), st>>>(
-            S.rows, lev_cur, n_cur, n, R, S.to_next, S.sched, S.ab, S.hdr, w);
-        PLAN_CUDA(cudaGetLastError());
-        if (S.n_tiles == 1) break;
-
-        // compact the carried entries into the next stage (order preserved)
-        size_t cap = (size_t)S.n_tiles * 128;                 // <= 63 prefix + 63 suffix records + root per tile
-        if (cap > (size_t)n_cur) cap = (size_t)n_cur;
-        uint32_t *rows_next = nullptr;
-        uint8_t *lev_next = nullptr;
-        PLAN_CUDA(cudaMalloc(&rows_next, cap * sizeof(uint32_t)));
-        rows_cur = rows_next;
-        cudaError_t e2 = cudaMalloc(&lev_next, cap);
-        if (e2 != cudaSuccess) { cudaFree(rows_next); rows_cur = nullptr; PLAN_CUDA(e2); }
-        CarryPred pred{S.to_next};
-        CarryEmit emit{S.rows, lev_cur, rows_next, lev_next};
-        device_select(n_cur, pred, emit, d_count, sel_ws, st);
-        int64_t h_count = 0;
-        cudaError_t e3 = cudaMemcpyAsync(&h_count, d_count, 8, cudaMemcpyDeviceToHost, st);
-        if (e3 == cudaSuccess) e3 = cudaStreamSynchronize(st);
-        if (e3 != cudaSuccess) { cudaFree(rows_next); cudaFree(lev_next); rows_cur = nullptr; PLAN_CUDA(e3); }
-        cudaFree(lev_cur_owned);
-        lev_cur_owned = lev_next;
-        lev_cur = lev_next;
-        if (h_count <= 0 || h_count >= n_cur) {
-            raht_set_error("raht_plan_create: stage %d did not shrink (%lld -> %lld); is level[] from raht_tree_levels?", k,
-                           (long long)n_cur, (long long)h_count);
-            cudaFree(rows_next); cudaFree(lev_cur_owned); cudaFree(sel_ws); cudaFree(d_count);
-            raht_plan_destroy(P);
-            return RAHT_E_INPUT;
-        }
-        n_cur = h_count;
     }
-    cudaError_t e4 = cudaStreamSynchronize(st);
-    cudaFree(lev_cur_owned);
-    lev_cur_owned = nullptr;
-    cudaFree(sel_ws);
-    sel_ws = nullptr;
-    cudaFree(d_count);
-    d_count = nullptr;
-    PLAN_CUDA(e4);
     *plan = P;
     return RAHT_OK;
 }
@@ -430,10 +440,10 @@ RAHT_API int raht_plan_create(const uint8_t *level, int64_t n, int tile_rows, do
 RAHT_API int raht_plan_info(const raht_plan *plan, int64_t *info_host, int cap)
 {
     RAHT_REQUIRE(plan && info_host && cap >= 4, "raht_plan_info: bad arguments");
-    info_host[0] = plan->n;
-    info_host[1] = plan->tile_rows;
-    info_host[2] = plan->n_stages;
+    info_host[0] = plan->d.n;
+    info_host[1] = plan->d.tile_rows;
+    info_host[2] = plan->d.n_stages;
     info_host[3] = (int64_t)plan->bytes;
-    for (int k = 0; k < plan->n_stages && 4 + k < cap; ++k) info_host[4 + k] = plan->st[k].n_entries;
+    for (int k = 0; k < plan->d.n_stages && 4 + k < cap; ++k) info_host[4 + k] = plan->d.tiles[k];
     return RAHT_OK;
 }

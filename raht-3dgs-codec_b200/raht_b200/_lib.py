@@ -51,7 +51,8 @@ SIGNATURES = {
     "raht_tree_max_level": (_i, [_p, _i64, _p, _p]),
     "raht_order_ragft_workspace_bytes": (_sz, [_i64]),
     "raht_order_ragft": (_i, [_p, _i64, _p, _p, _p, _sz, _p]),
-    "raht_plan_create": (_i, [_p, _i64, _i, _p, C.POINTER(_p), _p]),
+    "raht_plan_workspace_bytes": (_sz, [_i64, _i]),
+    "raht_plan_create": (_i, [_p, _i64, _i, _p, _p, _sz, C.POINTER(_p), _p]),
     "raht_plan_destroy": (None, [_p]),
     "raht_plan_info": (_i, [_p, C.POINTER(_i64), _i]),
     "raht_forward": (_i, [_p, _p, _i, _i, _p, _i, _i, _p]),

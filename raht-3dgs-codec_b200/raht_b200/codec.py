@@ -63,9 +63,10 @@ class StageTimer:
 
 
 @torch.no_grad()
-def voxelize_merge(means, quats, scales, opacities, colors, J, packed_dtype=torch.float32, timer=None):
+def voxelize_merge(means, quats, scales, opacities, colors, J, packed_dtype=torch.float32, timer=None, status=None):
     """Voxelise the Gaussian centres and merge the Gaussians of each voxel.
-    Returns (packed (nvox, D), unique_keys int64 (nvox), info dict)."""
+    Returns (packed (nvox, D), unique_keys int64 (nvox), info dict).  One synchronisation (the voxel
+    count must reach the host); with a shared `status` word the sort status is left to the caller."""
     timer = timer or StageTimer(False)
     dev = means.device
     N = means.shape[0]
@@ -79,34 +80,37 @@ def voxelize_merge(means, quats, scales, opacities, colors, J, packed_dtype=torc
     keys = torch.empty(N, dtype=torch.int64, device=dev)
     check(lib.raht_morton_keys_f32(ptr(means), N, 3, ptr(params4), J, ptr(keys), None, st), "raht_morton_keys_f32")
     timer.mark("morton")
-    keys_sorted, idx32, status = ops.radix_sort_pairs(keys, 3 * J)
+    deferred = status is not None
+    keys_sorted, idx32, status = ops.radix_sort_pairs(keys, 3 * J, status=status)
     timer.mark("sort")
     _, offsets, unique_keys, nvox = ops.voxel_segments(keys_sorted)
     timer.mark("segments")
-    if int(status.item()) & L.ST_SORT_STALL:
-        raise RuntimeError("radix sort look-back stalled (internal error)")
+    if not deferred:
+        ops.raise_for_status(int(status.item()))
     _, packed = ops.merge_segments(idx32, offsets, means, quats.contiguous().float(), scales.contiguous().float(),
                                    opacities.contiguous().float(), colors.contiguous().float(), True, separate=False,
                                    packed_dtype=packed_dtype)
     timer.mark("merge")
-    pd = params_d2.cpu().tolist()
-    info = {"Nvox": nvox, "N": N, "vmin": params4[:3].clone(), "width": pd[0], "voxel_size": pd[1], "sort_idx": idx32}
-    return packed, unique_keys.clone(), info
+    info = {"Nvox": nvox, "N": N, "vmin": params4[:3], "params_d2": params_d2, "sort_idx": idx32}   # params_d2 = (width, voxel_size), device
+    return packed, unique_keys, info
 
 
 @torch.no_grad()
-def encode_attributes(keys, Cmat, step, transform_dtype=torch.float64, tile_rows=None, timer=None, flags=0):
-    """RAHT_param -> RAHT -> quantise -> reorder -> RLGR for rows that are Morton-sorted unique voxels."""
+def encode_attributes(keys, Cmat, step, transform_dtype=torch.float64, tile_rows=None, timer=None, flags=0, status=None):
+    """RAHT_param -> RAHT -> quantise -> reorder -> RLGR for rows that are Morton-sorted unique voxels.
+    Device-side validation (sorted/unique keys, int32 overflow, sort stall) accumulates in one status
+    word that is read once, after the entropy coder."""
     timer = timer or StageTimer(False)
-    tree = ops.tree_from_keys(keys, validate=True)
+    status = ops._status_word(keys.device) if status is None else status
+    tree = ops.tree_from_keys(keys, validate=True, status=status)
     order, _ = tree.order(want_position=True)
     tree.plan(tile_rows)
     timer.mark("raht_param")
     T = ops.forward(tree, Cmat, transform_dtype, tile_rows, flags)
     timer.mark("raht")
-    q = ops.quant_reorder(T, order, step)
+    q = ops.quant_reorder(T, order, step, status=status)
     timer.mark("quant_reorder")
-    streams = ops.rlgr_encode(q, 1)
+    streams = ops.rlgr_encode(q, 1, status=status)
     timer.mark("rlgr_encode")
     return tree, streams
 
@@ -115,8 +119,10 @@ def encode_attributes(keys, Cmat, step, transform_dtype=torch.float64, tile_rows
 def decode_attributes(keys, streams, D, step, transform_dtype=torch.float64, tree=None, tile_rows=None, timer=None, flags=0):
     """RLGR^-1 -> dequantise -> inverse reorder -> iRAHT."""
     timer = timer or StageTimer(False)
+    status = None
     if tree is None:
-        tree = ops.tree_from_keys(keys, validate=True)
+        status = ops._status_word(keys.device)
+        tree = ops.tree_from_keys(keys, validate=True, status=status)
         tree.plan(tile_rows)
         timer.mark("raht_param_dec")
     order = tree.order()
@@ -126,6 +132,8 @@ def decode_attributes(keys, streams, D, step, transform_dtype=torch.float64, tre
     timer.mark("dequant_unreorder")
     Crec = ops.inverse(tree, T, tile_rows, flags)
     timer.mark("iraht")
+    if status is not None:
+        ops.raise_for_status(int(status.item()))      # the decoder's one synchronisation: were the keys a valid voxel list?
     return Crec
 
 
@@ -134,10 +142,12 @@ def encode_scene(means, quats, scales, opacities, colors, J, step, transform_dty
                  timer=None, flags=0) -> EncodedScene:
     timer = timer or StageTimer(False)
     timer.mark("start")
-    packed, keys, info = voxelize_merge(means, quats, scales, opacities, colors, J, torch.float32, timer)
-    tree, streams = encode_attributes(keys, packed, step, transform_dtype, tile_rows, timer, flags)
+    status = ops._status_word(means.device)
+    packed, keys, info = voxelize_merge(means, quats, scales, opacities, colors, J, torch.float32, timer, status)
+    tree, streams = encode_attributes(keys, packed, step, transform_dtype, tile_rows, timer, flags, status)
+    width, voxel_size = info["params_d2"].cpu().tolist()          # after the coder's synchronisation: no extra wait
     return EncodedScene(J=J, n_in=info["N"], nvox=info["Nvox"], D=packed.shape[1], step=step, vmin=info["vmin"],
-                        voxel_size=info["voxel_size"], width=info["width"], keys=keys, streams=streams,
+                        voxel_size=voxel_size, width=width, keys=keys, streams=streams,
                         transform_dtype=transform_dtype, tree=tree)
 
 

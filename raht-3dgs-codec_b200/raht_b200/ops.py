@@ -19,6 +19,18 @@ def _status_word(device):
     return torch.zeros(1, dtype=torch.int32, device=device)
 
 
+def raise_for_status(bits: int):
+    """Map the device-side status bits (include/raht_b200.h RAHT_ST_*) to the reference's exceptions."""
+    if bits & L.ST_SORT_STALL:
+        raise RuntimeError("radix sort look-back stalled (internal error)")
+    if bits & L.ST_OUT_OF_BOUNDS:
+        raise ValueError("RAHT_param:OutOfBounds: voxel index out of [0, 2^depth - 1]")
+    if bits & L.ST_NOT_SORTED_UNIQUE:
+        raise ValueError("RAHT_param: rows must be Morton-sorted and unique (duplicate or unsorted voxels)")
+    if bits & L.ST_INT32_OVERFLOW:
+        raise OverflowError("quantised coefficient does not fit int32 (encode_3dgs.py:215 would truncate)")
+
+
 # ------------------------------------------------------------------------------------------------
 # voxelisation front end
 # ------------------------------------------------------------------------------------------------
@@ -44,14 +56,14 @@ def morton_keys_f64(V: torch.Tensor, minV, width: float, depth: int):
     return keys, status
 
 
-def radix_sort_pairs(keys: torch.Tensor, end_bit: int, vals: torch.Tensor = None, begin_bit: int = 0):
+def radix_sort_pairs(keys: torch.Tensor, end_bit: int, vals: torch.Tensor = None, begin_bit: int = 0, status=None):
     """Stable LSD radix sort of 64-bit keys with 32-bit payloads (identity when vals is None)."""
     L.require_cuda(keys, "keys")
     n = keys.shape[0]
     dev = keys.device
     keys_out = torch.empty_like(keys)
     vals_out = torch.empty(n, dtype=torch.int32, device=dev)
-    status = _status_word(dev)
+    status = _status_word(dev) if status is None else status
     if n == 0:
         return keys_out, vals_out, status
     ws_bytes = lib.raht_radix_sort_workspace_bytes(n, begin_bit, end_bit)
@@ -105,8 +117,9 @@ def merge_segments(cluster_indices, cluster_offsets, means, quats, scales, opaci
 # tree
 # ------------------------------------------------------------------------------------------------
 class _PlanHandle:
-    def __init__(self, handle):
+    def __init__(self, handle, ws):
         self.handle = handle
+        self.ws = ws            # the plan lives in this workspace tensor
 
     def __del__(self):
         h, self.handle = self.handle, None
@@ -152,9 +165,11 @@ class RahtTree:
         if tile_rows not in self._plans:
             w = torch.empty(self.n, dtype=torch.float64, device=self.device)
             h = C.c_void_p()
-            check(lib.raht_plan_create(ptr(self.level), self.n, tile_rows, ptr(w), C.byref(h), stream()),
+            ws_bytes = lib.raht_plan_workspace_bytes(self.n, tile_rows)
+            ws = workspace(ws_bytes, self.device)
+            check(lib.raht_plan_create(ptr(self.level), self.n, tile_rows, ptr(w), ptr(ws), ws_bytes, C.byref(h), stream()),
                   "raht_plan_create")
-            self._plans[tile_rows] = _PlanHandle(h)
+            self._plans[tile_rows] = _PlanHandle(h, ws)
             self._w = w
         return self._plans[tile_rows].handle
 
@@ -164,7 +179,7 @@ class RahtTree:
         check(lib.raht_plan_info(h, buf, 48), "raht_plan_info")
         st = int(buf[2])
         return {"n": int(buf[0]), "tile_rows": int(buf[1]), "stages": st, "bytes": int(buf[3]),
-                "stage_rows": [int(buf[4 + k]) for k in range(st)]}
+                "stage_tiles": [int(buf[4 + k]) for k in range(st)]}
 
     @property
     def w(self) -> torch.Tensor:
@@ -200,12 +215,15 @@ class RahtTree:
         return (self._order, self._position) if want_position else self._order
 
 
-def tree_from_keys(MC: torch.Tensor, validate=True) -> RahtTree:
+def tree_from_keys(MC: torch.Tensor, validate=True, status=None) -> RahtTree:
+    """status: a shared device status word; when given the sorted/unique check is left to the caller
+    (raise_for_status at its next synchronisation point) and this call does not synchronise."""
     n = MC.shape[0]
     level = torch.empty(n, dtype=torch.uint8, device=MC.device)
-    status = _status_word(MC.device)
+    deferred = status is not None
+    status = _status_word(MC.device) if status is None else status
     check(lib.raht_tree_levels(ptr(MC), n, ptr(level), ptr(status), stream()), "raht_tree_levels")
-    if validate:
+    if validate and not deferred:
         s = int(status.item())
         if s & L.ST_NOT_SORTED_UNIQUE:
             raise ValueError("RAHT_param: rows must be Morton-sorted and unique (duplicate or unsorted voxels)")
@@ -311,18 +329,20 @@ def _steps_tensor(step, D, device):
     return torch.tensor([float(x) for x in step], dtype=torch.float64, device=device)
 
 
-def quant_reorder(T: torch.Tensor, order, step, check_overflow=True) -> torch.Tensor:
-    """q[c, p] = int32(floor(T[order[p], c] / step_c + 0.5)), channel-major (D, n)."""
+def quant_reorder(T: torch.Tensor, order, step, check_overflow=True, status=None) -> torch.Tensor:
+    """q[c, p] = int32(floor(T[order[p], c] / step_c + 0.5)), channel-major (D, n).
+    status: shared device status word (no synchronisation here; the caller checks it later)."""
     n, D = T.shape
     dev = T.device
     T = T.contiguous()
     steps = _steps_tensor(step, D, dev)
     ld = (n + 3) // 4 * 4
     q = torch.empty(D, ld, dtype=torch.int32, device=dev)
-    status = _status_word(dev)
+    deferred = status is not None
+    status = _status_word(dev) if status is None else status
     check(lib.raht_quant_reorder(ptr(T), L.dtype_tag(T.dtype), n, D, ptr(order), ptr(steps), ptr(q), ld, ptr(status),
                                  stream()), "raht_quant_reorder")
-    if check_overflow and int(status.item()) & L.ST_INT32_OVERFLOW:
+    if check_overflow and not deferred and int(status.item()) & L.ST_INT32_OVERFLOW:
         raise OverflowError("quantised coefficient does not fit int32 (encode_3dgs.py:215 would truncate)")
     return q[:, :n]
 
@@ -369,8 +389,10 @@ class RlgrStreams:
         return [host[c * self.slot_bytes: c * self.slot_bytes + sizes[c]].tobytes() for c in range(self.nch)]
 
 
-def rlgr_encode(q: torch.Tensor, flag_signed=1, slot_bytes=None, with_index=True, want_stats=False) -> RlgrStreams:
-    """q: (nch, n) int32 channel-major (row stride >= n)."""
+def rlgr_encode(q: torch.Tensor, flag_signed=1, slot_bytes=None, with_index=True, want_stats=False, status=None) -> RlgrStreams:
+    """q: (nch, n) int32 channel-major (row stride >= n).
+    status: shared device status word of the preceding pipeline steps; it is read here (the one
+    synchronisation of the encoder after the voxel count) and any earlier failure is raised."""
     L.require_cuda(q, "q")
     nch, n = q.shape
     dev = q.device
@@ -385,11 +407,14 @@ def rlgr_encode(q: torch.Tensor, flag_signed=1, slot_bytes=None, with_index=True
         buf = torch.empty(nch * slot, dtype=torch.uint8, device=dev)
         nbytes = torch.zeros(nch, dtype=torch.int64, device=dev)
         index = torch.empty(nch * entries, 4, dtype=torch.int32, device=dev) if with_index else None
-        status = _status_word(dev)
+        status = _status_word(dev) if status is None else status
         check(lib.raht_rlgr_encode(ptr(q), n, ld, nch, flag_signed, ptr(buf), slot, ptr(nbytes), ptr(index), ptr(status),
                                    ptr(ws), ws_bytes, stream()), "raht_rlgr_encode")
-        if int(status.item()) & L.ST_STREAM_OVERFLOW:
+        bits = int(status.item())
+        raise_for_status(bits)
+        if bits & L.ST_STREAM_OVERFLOW:
             slot = (int(nbytes.max().item()) + 64 + 7) // 8 * 8       # exact size is known even on overflow
+            status.zero_()
             continue
         out = RlgrStreams(buf, slot, nbytes, n, nch, index)
         if want_stats and n > 0 and nch > 0:

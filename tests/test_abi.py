@@ -30,13 +30,13 @@ def test_library_exports_every_declared_symbol():
 def test_ctypes_signatures_cover_header():
     from raht_b200 import _lib
     assert sorted(_lib.SIGNATURES) == declared_symbols()
-    assert _lib.lib.raht_abi_version() == 3
+    assert _lib.lib.raht_abi_version() == 4
 
 
 def test_argument_validation_without_gpu():
     """Host-side validation returns RAHT_E_INVALID and a message before any CUDA call."""
     from raht_b200 import _lib
-    rc = _lib.lib.raht_plan_create(None, 10, 100, None, ctypes.byref(ctypes.c_void_p()), None)   # tile_rows too small
+    rc = _lib.lib.raht_plan_create(None, 10, 30, None, None, 0, ctypes.byref(ctypes.c_void_p()), None)   # tile_rows too small
     assert rc == -1
     assert b"tile_rows" in _lib.lib.raht_last_error()
     rc = _lib.lib.raht_rlgr_encode(None, 10, 10, 1, 1, None, 12, None, None, None, None, 0, None)        # slot not multiple of 8

@@ -157,7 +157,7 @@ def test_oracle_raht_pipeline(n, J, D, clustered, seed):
         assert np.array_equal(tree.w.cpu().numpy(), wo)
         assert np.array_equal(ops.inverse(tree, T, R_).cpu().numpy(), t.inverse(To))
     info = tree.plan_info(128)
-    assert info["stage_rows"][0] == N and info["stages"] >= 1
+    assert info["stage_tiles"][0] == (N + 127) // 128 and info["stage_tiles"][-1] == 1 and info["stages"] >= 1
     for s in (1, 12):
         q = ops.quant_reorder(T, order, s)
         q_ref = orc.quantize(To, s)[order.cpu().numpy()].T.astype(np.int32)
