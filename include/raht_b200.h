@@ -29,7 +29,7 @@
 extern "C" {
 #endif
 
-#define RAHT_B200_ABI_VERSION 4
+#define RAHT_B200_ABI_VERSION 5
 
 enum {
     RAHT_OK = 0,
@@ -214,12 +214,15 @@ int raht_dequantize_f64(const double *q, int64_t count, double step, double *T, 
  * q: channel-major int32 (nch, ld); streams: nch slots of slot_bytes (multiple of 8) bytes;
  * nbytes[c]: closed stream length (exact even when the stream did not fit: RAHT_ST_STREAM_OVERFLOW).
  *
- * sync_index (optional, device, nch * raht_rlgr_sync_entries(n) entries of 16 bytes): side
- * information the encoder can emit next to the reference bitstream -- for every chunk of 3968
- * symbols the bit offset, first symbol and coder state (k_P, k_RP) at an event boundary.  The
- * streams do not depend on it.  raht_rlgr_decode with the index decodes every chunk in parallel;
- * with sync_index == NULL (a stream written by the reference coder) it decodes one channel per
- * thread, as the format forces.
+ * sync_index (optional, device, nch * raht_rlgr_sync_entries(n) entries of 8 bytes): side
+ * information the encoder can emit next to the reference bitstream -- for every range of 512
+ * symbols (4 blocks of 128; 8 ranges per chunk of 31 blocks) the bit offset and coder state
+ * (k_P, k_RP) before the range's first event and the position of that event's non-zero symbol:
+ *   word 0 = bit offset (low 32), word 1 = offset bits 32..38 | k_P << 7 | k_RP << 14 | first << 22
+ *   (first = 1023: the range holds only zeros).
+ * The streams do not depend on it.  raht_rlgr_decode with the index decodes every range in
+ * parallel; with sync_index == NULL (a stream written by the reference coder) it decodes one
+ * channel per thread, as the format forces.  q is fully written either way.
  * ------------------------------------------------------------------------------------------------ */
 int64_t raht_rlgr_sync_entries(int64_t n);
 size_t raht_rlgr_encode_workspace_bytes(int64_t n, int nch);

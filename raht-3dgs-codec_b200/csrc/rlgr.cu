@@ -29,6 +29,9 @@ namespace {
 
 using namespace rlgr;
 
+constexpr int SYNC_STRIDE = 4;                                                // lane blocks per sync entry
+constexpr int SYNC_PER_CHUNK = (CHUNK_LANES + SYNC_STRIDE - 1) / SYNC_STRIDE;     // 8 entries per warp chunk
+constexpr uint32_t SYNC_NONE = 1023;                                          // no non-zero symbol in the entry's range
 constexpr int ROW_PITCH = BLOCK_SYMS + 1;                         // odd pitch: lane-strided reads are conflict-free
 constexpr int CHUNK_SMEM_WORDS = 32 * ROW_PITCH + 32 * MASK_WORDS;
 
@@ -285,8 +288,8 @@ __global__ void __launch_bounds__(32) rlgr_resolve_kernel(const int32_t *__restr
                                                           const int32_t *__restrict__ lastnz, uint4 *__restrict__ rec,
                                                           uint2 *__restrict__ lanerec, unsigned long long *__restrict__ chunkoff,
                                                           int64_t slot_bytes, int64_t *__restrict__ nbytes,
-                                                          unsigned long long *__restrict__ totals, uint4 *__restrict__ sync_index,
-                                                          int32_t *status, unsigned long long *stats)
+                                                          unsigned long long *__restrict__ totals, int32_t *status,
+                                                          unsigned long long *stats)
 {
     extern __shared__ uint32_t rl_smem[];
     const int ch = blockIdx.x;
@@ -301,7 +304,6 @@ __global__ void __launch_bounds__(32) rlgr_resolve_kernel(const int32_t *__restr
         uint4 r = make_uint4(0, 0, 0, 0);
         if (w < G.nchunks) r = rec[ci];
         unsigned long long my_off = 0;
-        uint32_t my_state = 0;
         const int cnt = (int)min((int64_t)32, G.nchunks - base);
         for (int i = 0; i < cnt; ++i) {
             const uint32_t cand = __shfl_sync(~0u, r.x, i);
@@ -309,7 +311,7 @@ __global__ void __launch_bounds__(32) rlgr_resolve_kernel(const int32_t *__restr
             uint32_t b0 = __shfl_sync(~0u, r.z, i), b1 = __shfl_sync(~0u, r.w, i);
             const uint32_t ps = pack_state(s);
             if (b0 & REC_IDENTITY) {                             // nothing coded in this chunk: state and offset pass through
-                if (lane == i) { my_off = off << 1; my_state = ps; }
+                if (lane == i) my_off = off << 1;
                 continue;
             }
             int b = (ps == (cand & 0xffff)) ? 0 : (ps == (cand >> 16)) ? 1 : -1;
@@ -324,18 +326,11 @@ __global__ void __launch_bounds__(32) rlgr_resolve_kernel(const int32_t *__restr
                 b = 0;
                 ++repairs;
             }
-            if (lane == i) { my_off = (off << 1) | (unsigned)b; my_state = ps; }
+            if (lane == i) my_off = (off << 1) | (unsigned)b;
             off += b ? b1 : b0;
             s = unpack_state(b ? (ends >> 16) : (ends & 0xffff));
         }
-        if (w < G.nchunks) {
-            chunkoff[ci] = my_off;
-            if (sync_index) {
-                const int64_t blk = w * CHUNK_LANES;
-                const int64_t first_sym = blk == 0 ? 0 : (int64_t)lastnz_ch[blk - 1] + 1;
-                sync_index[ci] = make_uint4((uint32_t)(my_off >> 1), (uint32_t)(my_off >> 33), (uint32_t)first_sym, my_state);
-            }
-        }
+        if (w < G.nchunks) chunkoff[ci] = my_off;
     }
     if (lane == 0) {
         const int64_t nb = (int64_t)((off + 7) >> 3);
@@ -409,7 +404,8 @@ struct BitSink {
 __global__ void __launch_bounds__(32) rlgr_emit_kernel(const int32_t *__restrict__ q, Geometry G,
                                                        const int32_t *__restrict__ lastnz, const uint2 *__restrict__ lanerec,
                                                        const unsigned long long *__restrict__ chunkoff,
-                                                       uint8_t *__restrict__ streams, int64_t slot_bytes, int32_t *status)
+                                                       uint8_t *__restrict__ streams, int64_t slot_bytes,
+                                                       uint2 *__restrict__ sync_index, int32_t *status)
 {
     extern __shared__ uint32_t rl_smem[];
     const int ch = blockIdx.y;
@@ -428,6 +424,25 @@ __global__ void __launch_bounds__(32) rlgr_emit_kernel(const int32_t *__restrict
         if (lane >= o) x += y;
     }
     const unsigned long long begin = (co >> 1) + (x - mybits);
+    if (sync_index) {
+        // sync entry of lanes 1+4k..4+4k: where (bit offset, state) the coder stands before the range's first
+        // event and where that event's non-zero symbol sits.  Lanes without events have no bits and pass the
+        // state through, so the leader lane's (begin, s) are those of the first lane with an event.
+        uint32_t fn = SYNC_NONE;
+        for (int wd = MASK_WORDS - 1; wd >= 0; --wd)
+            if (B.mask[wd]) fn = (uint32_t)(32 * wd + __ffs((int)B.mask[wd]) - 1);
+        uint32_t first = fn;
+        for (int o = 1; o < SYNC_STRIDE; ++o) {                   // nearest lane with an event wins
+            const uint32_t f = __shfl_down_sync(~0u, fn, o);
+            if (first == SYNC_NONE && lane + o < 32 && f != SYNC_NONE) first = (uint32_t)(o * BLOCK_SYMS) + f;
+        }
+        if (lane >= 1 && ((lane - 1) % SYNC_STRIDE) == 0) {
+            const int k = (lane - 1) / SYNC_STRIDE;
+            const uint32_t hi = (uint32_t)((begin >> 32) & 0x7f) | ((uint32_t)(s.kP & 0x7f) << 7) | ((uint32_t)(s.kRP & 0xff) << 14) |
+                                (first << 22);
+            sync_index[ci * SYNC_PER_CHUNK + k] = make_uint2((uint32_t)begin, hi);
+        }
+    }
     if (lane == 0 || mybits == 0) return;
     BitSink sink;
     sink.init(streams + (size_t)ch * slot_bytes, slot_bytes, begin);
@@ -436,98 +451,7 @@ __global__ void __launch_bounds__(32) rlgr_emit_kernel(const int32_t *__restrict
     if (sink.overflow && status) atomicOr(status, RAHT_ST_STREAM_OVERFLOW);
 }
 
-// ---- decoder ---------------------------------------------------------------------------------------------
-// MSB-first reader over big-endian 32-bit words; acc holds the next nbits bits left-aligned.
-struct BitReader {
-    const uint32_t *in;
-    int64_t n_words, pos;
-    uint64_t acc;
-    int nbits;
-    __device__ __forceinline__ void init(const uint8_t *stream, int64_t readable_bytes, unsigned long long begin_bit)
-    {
-        in = (const uint32_t *)stream;
-        n_words = (readable_bytes + 3) >> 2;
-        pos = (int64_t)(begin_bit >> 5);
-        acc = 0;
-        nbits = 0;
-        const unsigned skip = (unsigned)(begin_bit & 31);
-        if (skip) { fill(); acc <<= skip; nbits -= (int)skip; }
-    }
-    __device__ __forceinline__ void fill()                  // afterwards nbits >= 33
-    {
-        if (nbits <= 32) {
-            const uint32_t w = pos < n_words ? __byte_perm(in[pos], 0, 0x0123) : 0u;
-            ++pos;
-            acc |= (uint64_t)w << (32 - nbits);
-            nbits += 32;
-        }
-    }
-    __device__ __forceinline__ unsigned get1()
-    {
-        fill();
-        const unsigned b = (unsigned)(acc >> 63);
-        acc <<= 1;
-        --nbits;
-        return b;
-    }
-    __device__ __forceinline__ uint64_t get(unsigned len)   // len <= 32
-    {
-        if (len == 0) return 0;
-        fill();
-        const uint64_t v = acc >> (64 - len);
-        acc <<= len;
-        nbits -= (int)len;
-        return v;
-    }
-    __device__ __forceinline__ uint64_t gr(unsigned kr)     // membuf.cpp:228-240 (grRead)
-    {
-        fill();
-        const int p = __clzll((long long)~acc);             // leading ones (bits past nbits read as zero)
-        if (p >= 32) {
-            acc <<= 32;
-            nbits -= 32;
-            return get(32);
-        }
-        acc <<= (p + 1);
-        nbits -= p + 1;
-        return (((uint64_t)p) << kr) + get(kr);
-    }
-};
-
-// symbols [pos, stop) of one channel from reader br in state s; dst is pre-zeroed, only non-zeros are stored
-__device__ __forceinline__ void decode_range(BitReader &br, State s, int64_t pos, int64_t stop, int flag_signed,
-                                             int32_t *__restrict__ dst)
-{
-    while (pos < stop) {                                                   // membuf.cpp:266-334
-        int k = s.kP / RL_L;
-        const unsigned kR = (unsigned)(s.kRP / RL_L);
-        if (k) {
-            uint64_t m = 0;
-            while (br.get1()) {                                            // complete runs
-                m += ((uint64_t)1) << k;
-                s.kP += RL_U1;
-                k = s.kP / RL_L;
-                if (m >= (uint64_t)(stop - pos)) break;                    // corrupt stream guard
-            }
-            m += br.get((unsigned)k);
-            pos = (m > (uint64_t)(stop - pos)) ? stop : pos + (int64_t)m;
-            if (pos >= stop) break;
-            const uint64_t u = br.gr(kR);
-            const uint64_t val = u + 1;
-            dst[pos++] = flag_signed ? u2s(val) : (int32_t)val;
-            adapt_krp(s, u >> kR);
-            s.kP = s.kP < RL_D1 ? 0 : s.kP - RL_D1;
-        } else {
-            const uint64_t u = br.gr(kR);
-            if (u) dst[pos] = flag_signed ? u2s(u) : (int32_t)u;
-            ++pos;
-            adapt_krp(s, u >> kR);
-            if (u) s.kP = s.kP < RL_D0 ? 0 : s.kP - RL_D0;
-            else s.kP += RL_U0;
-        }
-    }
-}
-
+// ---- decoder (BitReader and decode_range live in rlgr_core.cuh) ---------------------------------------------
 // without a sync index: one thread per channel
 __global__ void __launch_bounds__(32) rlgr_decode_serial_kernel(const uint8_t *__restrict__ streams, int64_t slot_bytes,
                                                                const int64_t *__restrict__ nbytes, Geometry G,
@@ -539,29 +463,38 @@ __global__ void __launch_bounds__(32) rlgr_decode_serial_kernel(const uint8_t *_
     if (nb > slot_bytes) nb = slot_bytes;
     BitReader br;
     br.init(streams + (size_t)ch * slot_bytes, nb, 0);
-    decode_range(br, initial_state(), 0, G.n, G.flag_signed, q + (size_t)ch * G.ld);
+    decode_range(br, initial_state(), -1, G.n, G.flag_signed, q + (size_t)ch * G.ld);
 }
 
-// with the encoder's sync index: one thread per warp chunk
-constexpr int DEC_THREADS = 64;
+// with the encoder's sync index: one thread per entry (SYNC_STRIDE lane blocks)
+constexpr int DEC_THREADS = 128;
 __global__ void __launch_bounds__(DEC_THREADS) rlgr_decode_indexed_kernel(const uint8_t *__restrict__ streams, int64_t slot_bytes,
                                                                          const int64_t *__restrict__ nbytes,
-                                                                         const uint4 *__restrict__ sync_index, Geometry G,
+                                                                         const uint2 *__restrict__ sync_index, Geometry G,
                                                                          int32_t *__restrict__ q)
 {
     const int ch = blockIdx.y;
-    const int64_t w = (int64_t)blockIdx.x * DEC_THREADS + threadIdx.x;
-    if (w >= G.nchunks) return;
-    const size_t ci = (size_t)ch * G.nchunks + w;
-    const uint4 e = sync_index[ci];
-    const int64_t pos = (int64_t)e.z;
-    const int64_t stop = (w + 1 < G.nchunks) ? (int64_t)sync_index[ci + 1].z : G.n;
-    if (pos >= stop) return;
+    const int64_t e = (int64_t)blockIdx.x * DEC_THREADS + threadIdx.x;
+    const int64_t entries = G.nchunks * SYNC_PER_CHUNK;
+    if (e >= entries) return;
+    const int64_t w = e / SYNC_PER_CHUNK;
+    const int k = (int)(e - w * SYNC_PER_CHUNK);
+    const int64_t start = (w * CHUNK_LANES + (int64_t)k * SYNC_STRIDE) * BLOCK_SYMS;
+    if (start >= G.n) return;
+    const int nblocks = min(SYNC_STRIDE, CHUNK_LANES - k * SYNC_STRIDE);
+    int64_t end = start + (int64_t)nblocks * BLOCK_SYMS;
+    if (end > G.n) end = G.n;
+    const uint2 ent = sync_index[(size_t)ch * entries + e];
+    const uint32_t first = ent.y >> 22;
+    if (first == SYNC_NONE || start + first >= end) return;                // nothing but zeros in this range
+    State s;
+    s.kP = (int)((ent.y >> 7) & 0x7f);
+    s.kRP = (int)((ent.y >> 14) & 0xff);
     int64_t nb = nbytes ? nbytes[ch] : slot_bytes;
     if (nb > slot_bytes) nb = slot_bytes;
     BitReader br;
-    br.init(streams + (size_t)ch * slot_bytes, nb, (unsigned long long)e.x | ((unsigned long long)e.y << 32));
-    decode_range(br, unpack_state(e.w), pos, stop > G.n ? G.n : stop, G.flag_signed, q + (size_t)ch * G.ld);
+    br.init(streams + (size_t)ch * slot_bytes, nb, (unsigned long long)ent.x | ((unsigned long long)(ent.y & 0x7f) << 32));
+    decode_range(br, s, start + first, end, G.flag_signed, q + (size_t)ch * G.ld);
 }
 
 struct EncLayout {
@@ -585,7 +518,7 @@ EncLayout enc_layout(int64_t n, int nch)
 
 }  // namespace
 
-RAHT_API int64_t raht_rlgr_sync_entries(int64_t n) { return n <= 0 ? 0 : chunks_of(n); }
+RAHT_API int64_t raht_rlgr_sync_entries(int64_t n) { return n <= 0 ? 0 : chunks_of(n) * SYNC_PER_CHUNK; }
 
 RAHT_API size_t raht_rlgr_encode_workspace_bytes(int64_t n, int nch) { return enc_layout(n < 0 ? 0 : n, nch).total; }
 
@@ -629,9 +562,10 @@ RAHT_API int raht_rlgr_encode(const int32_t *q, int64_t n, int64_t ld, int nch, 
     (raht_count_launches(1), rlgr_speculate_kernel)<<<cgrid, 32, smem, st>>>(q, G, lastnz, 0, recB, recA, lanerec, stats);
     (raht_count_launches(1), rlgr_speculate_kernel)<<<cgrid, 32, smem, st>>>(q, G, lastnz, 1, recA, recB, lanerec, stats);
     (raht_count_launches(1), rlgr_resolve_kernel)<<<nch, 32, smem, st>>>(q, G, lastnz, recB, lanerec, chunkoff, slot_bytes, nbytes,
-                                                                       totals, (uint4 *)sync_index, status, stats);
+                                                                       totals, status, stats);
     (raht_count_launches(1), rlgr_zero_kernel)<<<dim3(64, nch), 256, 0, st>>>(streams, slot_bytes, totals);
-    (raht_count_launches(1), rlgr_emit_kernel)<<<cgrid, 32, smem, st>>>(q, G, lastnz, lanerec, chunkoff, streams, slot_bytes, status);
+    (raht_count_launches(1), rlgr_emit_kernel)<<<cgrid, 32, smem, st>>>(q, G, lastnz, lanerec, chunkoff, streams, slot_bytes,
+                                                                      (uint2 *)sync_index, status);
     RAHT_LAUNCH_CHECK();
     return RAHT_OK;
 }
@@ -661,9 +595,9 @@ RAHT_API int raht_rlgr_decode(const uint8_t *streams, int64_t slot_bytes, const 
     G.n = n; G.ld = ld; G.nblk = blocks_of(n); G.nchunks = chunks_of(n); G.nch = nch; G.flag_signed = flag_signed;
     RAHT_CUDA(cudaMemsetAsync(q, 0, ((size_t)(nch - 1) * ld + n) * 4, st));      // the decoders store non-zeros only
     if (sync_index) {
-        const dim3 grid((unsigned)((G.nchunks + DEC_THREADS - 1) / DEC_THREADS), nch);
+        const dim3 grid((unsigned)((G.nchunks * SYNC_PER_CHUNK + DEC_THREADS - 1) / DEC_THREADS), nch);
         (raht_count_launches(1), rlgr_decode_indexed_kernel)<<<grid, DEC_THREADS, 0, st>>>(streams, slot_bytes, nbytes,
-                                                                                          (const uint4 *)sync_index, G, q);
+                                                                                          (const uint2 *)sync_index, G, q);
     } else {
         (raht_count_launches(1), rlgr_decode_serial_kernel)<<<nch, 32, 0, st>>>(streams, slot_bytes, nbytes, G, q);
     }

@@ -58,6 +58,23 @@ RL_HD int rl_ctz(uint32_t x)
 #endif
 }
 
+RL_HD uint32_t rl_bswap32(uint32_t x)
+{
+#if defined(__CUDA_ARCH__)
+    return __byte_perm(x, 0, 0x0123);
+#else
+    return __builtin_bswap32(x);
+#endif
+}
+RL_HD int rl_clz64(uint64_t x)           // 64 for x == 0
+{
+#if defined(__CUDA_ARCH__)
+    return __clzll((long long)x);
+#else
+    return x ? __builtin_clzll(x) : 64;
+#endif
+}
+
 // Sink that only counts bits (passes that need code lengths, not codes)
 struct CountSink {
     uint32_t bits;
@@ -182,6 +199,112 @@ RL_HD void code_block(const uint32_t *row, int len, const uint32_t *mask, uint32
     if (is_tail) {
         const uint32_t g = prev < 0 ? zeros_before + (uint32_t)len : (uint32_t)(len - 1 - prev);
         code_tail(s, g, quirk, sink);
+    }
+}
+
+// ---- decoder ---------------------------------------------------------------------------------------------
+// MSB-first reader over big-endian 32-bit words; acc holds the next nbits bits left-aligned.
+struct BitReader {
+    const uint32_t *in;
+    int64_t n_words, pos;
+    uint64_t acc;
+    int nbits;
+    RL_HD void init(const uint8_t *stream, int64_t readable_bytes, unsigned long long begin_bit)
+    {
+        in = (const uint32_t *)stream;
+        n_words = (readable_bytes + 3) >> 2;
+        pos = (int64_t)(begin_bit >> 5);
+        acc = 0;
+        nbits = 0;
+        const unsigned skip = (unsigned)(begin_bit & 31);
+        if (skip) { fill(); acc <<= skip; nbits -= (int)skip; }
+    }
+    RL_HD void fill()                  // afterwards nbits >= 33
+    {
+        if (nbits <= 32) {
+            const uint32_t w = pos < n_words ? rl_bswap32(in[pos]) : 0u;
+            ++pos;
+            acc |= (uint64_t)w << (32 - nbits);
+            nbits += 32;
+        }
+    }
+    RL_HD unsigned get1()
+    {
+        fill();
+        const unsigned b = (unsigned)(acc >> 63);
+        acc <<= 1;
+        --nbits;
+        return b;
+    }
+    RL_HD uint64_t get(unsigned len)   // len <= 32
+    {
+        if (len == 0) return 0;
+        fill();
+        const uint64_t v = acc >> (64 - len);
+        acc <<= len;
+        nbits -= (int)len;
+        return v;
+    }
+    RL_HD uint64_t gr(unsigned kr)     // membuf.cpp:228-240 (grRead)
+    {
+        fill();
+        const int p = rl_clz64(~acc);             // leading ones (bits past nbits read as zero)
+        if (p >= 32) {
+            acc <<= 32;
+            nbits -= 32;
+            return get(32);
+        }
+        acc <<= (p + 1);
+        nbits -= p + 1;
+        return (((uint64_t)p) << kr) + get(kr);
+    }
+};
+
+// Events from reader br in state s.  dst is pre-zeroed: only non-zero symbols are stored, so zero runs cost
+// nothing and the tail of the stream is never read.
+//   first_pos < 0: plain sequential decode of symbols [0, end) (reader at the stream start);
+//   first_pos >= 0: the reader stands before an event whose non-zero symbol is dst[first_pos] (a sync entry);
+//   the zeros in front of it are decoded and dropped, then decoding continues up to `end`.
+RL_HD void decode_range(BitReader &br, State s, int64_t first_pos, int64_t end, int flag_signed,
+                                             int32_t *__restrict__ dst)
+{
+    bool synced = first_pos < 0;
+    int64_t pos = 0;
+    while (pos < end) {                                                    // membuf.cpp:266-334
+        int k = s.kP / RL_L;
+        const unsigned kR = (unsigned)(s.kRP / RL_L);
+        if (k) {
+            uint64_t m = 0;
+            while (br.get1()) {                                            // complete runs
+                m += ((uint64_t)1) << k;
+                s.kP += RL_U1;
+                k = s.kP / RL_L;
+                if (m > (uint64_t)1 << 40) break;                          // corrupt stream guard
+            }
+            m += br.get((unsigned)k);
+            if (synced) {
+                if (m >= (uint64_t)(end - pos)) break;                     // the next non-zero lies past this range
+                pos += (int64_t)m;
+            } else {
+                pos = first_pos;
+                synced = true;
+            }
+            const uint64_t u = br.gr(kR);
+            const uint64_t val = u + 1;
+            dst[pos++] = flag_signed ? u2s(val) : (int32_t)val;
+            adapt_krp(s, u >> kR);
+            s.kP = s.kP < RL_D1 ? 0 : s.kP - RL_D1;
+        } else {
+            const uint64_t u = br.gr(kR);
+            if (u) {
+                if (!synced) { pos = first_pos; synced = true; }
+                dst[pos] = flag_signed ? u2s(u) : (int32_t)u;
+            }
+            if (synced) ++pos;
+            adapt_krp(s, u >> kR);
+            if (u) s.kP = s.kP < RL_D0 ? 0 : s.kP - RL_D0;
+            else s.kP += RL_U0;
+        }
     }
 }
 

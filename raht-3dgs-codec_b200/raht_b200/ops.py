@@ -364,9 +364,9 @@ def dequant_unreorder(q: torch.Tensor, order, step, out_dtype=torch.float64) -> 
 class RlgrStreams:
     """nch closed RLGR streams in one device buffer (slot per channel).
 
-    sync_index (optional): the encoder's side information for chunk-parallel decoding -- 16 bytes per
-    chunk of 3968 symbols (bit offset, first symbol, coder state); the streams themselves are the
-    reference bitstreams and do not depend on it."""
+    sync_index (optional): the encoder's side information for parallel decoding -- 8 bytes per range
+    of 512 symbols (bit offset, coder state, position of the first non-zero); the streams themselves
+    are the reference bitstreams and do not depend on it."""
 
     def __init__(self, buf, slot_bytes, nbytes, n, nch, sync_index=None):
         self.buf, self.slot_bytes, self.nbytes, self.n, self.nch = buf, slot_bytes, nbytes, n, nch
@@ -406,7 +406,7 @@ def rlgr_encode(q: torch.Tensor, flag_signed=1, slot_bytes=None, with_index=True
     while True:
         buf = torch.empty(nch * slot, dtype=torch.uint8, device=dev)
         nbytes = torch.zeros(nch, dtype=torch.int64, device=dev)
-        index = torch.empty(nch * entries, 4, dtype=torch.int32, device=dev) if with_index else None
+        index = torch.empty(nch * entries, 2, dtype=torch.int32, device=dev) if with_index else None
         status = _status_word(dev) if status is None else status
         check(lib.raht_rlgr_encode(ptr(q), n, ld, nch, flag_signed, ptr(buf), slot, ptr(nbytes), ptr(index), ptr(status),
                                    ptr(ws), ws_bytes, stream()), "raht_rlgr_encode")

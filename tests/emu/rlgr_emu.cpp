@@ -14,6 +14,10 @@ using namespace rlgr;
 
 namespace {
 
+constexpr int SYNC_STRIDE = 4;                                                // as in rlgr.cu
+constexpr int SYNC_PER_CHUNK = (CHUNK_LANES + SYNC_STRIDE - 1) / SYNC_STRIDE;
+constexpr uint32_t SYNC_NONE = 1023;
+
 struct Lane {
     std::vector<uint32_t> row;
     uint32_t mask[MASK_WORDS];
@@ -218,13 +222,6 @@ __attribute__((visibility("default"))) int64_t emu_rlgr_encode(const int32_t *q,
             if (stats) stats[2]++;
         }
         chunkoff[w] = (off << 1) | (unsigned)b;
-        if (sync) {
-            const int64_t blk = w * CHUNK_LANES;
-            sync[4 * w + 0] = (uint32_t)off;
-            sync[4 * w + 1] = (uint32_t)(off >> 32);
-            sync[4 * w + 2] = (uint32_t)(blk == 0 ? 0 : (int64_t)C.lastnz[blk - 1] + 1);
-            sync[4 * w + 3] = ps;
-        }
         off += b ? rec[w].bits1 : rec[w].bits0;
         s = unpack_state(b ? (rec[w].ends >> 16) : (rec[w].ends & 0xffff));
     }
@@ -238,6 +235,16 @@ __attribute__((visibility("default"))) int64_t emu_rlgr_encode(const int32_t *q,
             const LaneRec &lr = lanerec[w * 32 + l];
             State st = unpack_state(b ? (lr.starts >> 16) : (lr.starts & 0xffff));
             const uint32_t mybits = b ? (lr.bits >> 16) : (lr.bits & 0xffff);
+            if (sync && (l - 1) % SYNC_STRIDE == 0) {              // sync entry of lanes l .. l+3 (rlgr.cu, emit kernel)
+                uint32_t first = SYNC_NONE;
+                for (int o = 0; o < SYNC_STRIDE && l + o < 32 && first == SYNC_NONE; ++o)
+                    for (int i = 0; i < L[l + o].len; ++i)
+                        if (L[l + o].row[i]) { first = (uint32_t)(o * BLOCK_SYMS + i); break; }
+                const int k = (l - 1) / SYNC_STRIDE;
+                sync[2 * (w * SYNC_PER_CHUNK + k) + 0] = (uint32_t)begin;
+                sync[2 * (w * SYNC_PER_CHUNK + k) + 1] = (uint32_t)((begin >> 32) & 0x7f) | ((uint32_t)(st.kP & 0x7f) << 7) |
+                                                         ((uint32_t)(st.kRP & 0xff) << 14) | (first << 22);
+            }
             sink.pos = begin;
             if (mybits) code_block(L[l].row.data(), L[l].len, L[l].mask, L[l].zeros_before, L[l].is_tail, st, sink);
             if (sink.pos != begin + mybits) return -1000 - l;     // length bookkeeping broken
@@ -246,6 +253,40 @@ __attribute__((visibility("default"))) int64_t emu_rlgr_encode(const int32_t *q,
     }
     const int64_t nb = (int64_t)((off + 7) >> 3);
     return sink.overflow ? -nb : nb;
+}
+
+// Decoder: out must be zero-filled (n int32).  sync == nullptr: sequential decode from the stream start;
+// else every sync entry is decoded on its own, as the threads of rlgr_decode_indexed_kernel do.
+__attribute__((visibility("default"))) void emu_rlgr_decode(const uint8_t *buf, int64_t nbytes, int64_t n, int flag_signed,
+                                                            const uint32_t *sync, int32_t *out)
+{
+    if (n <= 0) return;
+    std::vector<uint8_t> padded((size_t)((nbytes + 3) / 4 * 4 + 8), 0);       // the reader fetches whole words
+    std::memcpy(padded.data(), buf, (size_t)nbytes);
+    if (!sync) {
+        BitReader br;
+        br.init(padded.data(), nbytes, 0);
+        decode_range(br, initial_state(), -1, n, flag_signed, out);
+        return;
+    }
+    const int64_t nblk = (n + BLOCK_SYMS - 1) / BLOCK_SYMS, nchunks = (nblk + CHUNK_LANES - 1) / CHUNK_LANES;
+    for (int64_t e = 0; e < nchunks * SYNC_PER_CHUNK; ++e) {
+        const int64_t w = e / SYNC_PER_CHUNK;
+        const int k = (int)(e - w * SYNC_PER_CHUNK);
+        const int64_t start = (w * CHUNK_LANES + (int64_t)k * SYNC_STRIDE) * BLOCK_SYMS;
+        if (start >= n) continue;
+        const int nblocks = std::min(SYNC_STRIDE, CHUNK_LANES - k * SYNC_STRIDE);
+        const int64_t end = std::min<int64_t>(start + (int64_t)nblocks * BLOCK_SYMS, n);
+        const uint32_t x = sync[2 * e], y = sync[2 * e + 1];
+        const uint32_t first = y >> 22;
+        if (first == SYNC_NONE || start + first >= end) continue;
+        State s;
+        s.kP = (int)((y >> 7) & 0x7f);
+        s.kRP = (int)((y >> 14) & 0xff);
+        BitReader br;
+        br.init(padded.data(), nbytes, (unsigned long long)x | ((unsigned long long)(y & 0x7f) << 32));
+        decode_range(br, s, start + first, end, flag_signed, out);
+    }
 }
 
 }  // extern "C"

@@ -28,11 +28,22 @@ def emu():
         out = np.zeros(cap, dtype=np.uint8)
         stats = np.zeros(4, dtype=np.uint64)
         nchunks = ((q.size + 127) // 128 + 30) // 31
-        sync = np.zeros((max(nchunks, 1), 4), dtype=np.uint32)
+        sync = np.zeros((max(nchunks, 1) * 8, 2), dtype=np.uint32)
         nb = lib.emu_rlgr_encode(q.ctypes.data, q.size, flag_signed, out.ctypes.data, cap, stats.ctypes.data, sync.ctypes.data,
                                  sweeps, c1_kp)
         assert nb >= 0, nb
-        return out[:nb].tobytes(), stats, sync[:nchunks]
+        return out[:nb].tobytes(), stats, sync[:nchunks * 8]
+
+    lib.emu_rlgr_decode.restype = None
+    lib.emu_rlgr_decode.argtypes = [C.c_void_p, C.c_int64, C.c_int64, C.c_int, C.c_void_p, C.c_void_p]
+
+    def decode(buf, n, flag_signed=1, sync=None):
+        out = np.zeros(max(n, 1), dtype=np.int32)
+        b = np.frombuffer(buf, dtype=np.uint8).copy() if len(buf) else np.zeros(1, dtype=np.uint8)
+        sp = None if sync is None else np.ascontiguousarray(sync, dtype=np.uint32).ctypes.data
+        lib.emu_rlgr_decode(b.ctypes.data, len(buf), n, flag_signed, sp, out.ctypes.data)
+        return out[:n]
+    encode.decode = decode
     return encode
 
 
@@ -60,7 +71,7 @@ def test_emu_regime_changes_edges_and_unsigned(emu):
     q = np.concatenate(parts).astype(np.int64)
     got, stats, sync = emu(q, 1)
     assert got == orc.rlgr_encode(q, 1)
-    assert stats[3] == len(sync)
+    assert stats[3] * 8 == len(sync)
     for n in (1, 2, 127, 128, 129, 3967, 3968, 3969, 7936, 7937, 12001):
         for last in (None, 0, -1, 7):
             y = np.rint(rng.laplace(0, 0.7, n)).astype(np.int64)
@@ -77,16 +88,29 @@ def test_emu_regime_changes_edges_and_unsigned(emu):
     assert emu(z, 1)[0] == orc.rlgr_encode(z, 1)
 
 
-def test_emu_sync_index_points_at_event_boundaries(emu):
-    """Every sync entry (bit offset, first symbol, state) must let a sequential decoder resume there."""
+def test_emu_sync_index_decodes_every_range_independently(emu):
+    """Each sync entry (bit offset, state, position of the first non-zero) must let a decoder start there, and
+    the plain sequential decoder (reference streams, no index) must agree."""
     rng = np.random.default_rng(11)
+    cases = []
     q = np.rint(rng.laplace(0, 0.6, 40000)).astype(np.int64)
     q[9000:21000] = 0
-    buf, _, sync = emu(q, 1)
-    assert np.array_equal(orc.rlgr_decode(buf, len(q), 1), q)
-    first = sync[:, 2].astype(np.int64)
-    assert first[0] == 0 and np.all(np.diff(first) >= 0) and np.all(first <= np.arange(len(sync)) * 3968)
-    for w in range(1, len(sync)):
-        s = int(first[w])
-        assert s == 0 or q[s - 1] != 0            # an event boundary: right after a non-zero symbol
-        assert np.all(q[s: w * 3968] == 0)        # everything up to the nominal chunk start is the run of zeros
+    cases.append(q)
+    cases.append(np.rint(rng.laplace(0, 30, 9000)).astype(np.int64))
+    z = np.zeros(30000, dtype=np.int64); z[17] = -3; z[29000] = 1
+    cases.append(z)
+    cases.append(np.zeros(5000, dtype=np.int64))
+    z = np.rint(rng.laplace(0, 0.05, 60000)).astype(np.int64); z[-1] = -1
+    cases.append(z)
+    for q in cases:
+        for fs in (1, 0):
+            x = np.abs(q) if fs == 0 else q
+            buf, stats, sync = emu(x, fs)
+            assert buf == orc.rlgr_encode(x, fs)
+            assert np.array_equal(emu.decode(buf, len(x), fs, sync), x)
+            assert np.array_equal(emu.decode(buf, len(x), fs, None), x)
+            assert np.array_equal(emu.decode(orc.rlgr_encode(x, fs), len(x), fs, None), orc.rlgr_decode(buf, len(x), fs))
+    for n in (1, 2, 127, 128, 129, 511, 512, 513, 3967, 3968, 3969, 7937):
+        y = np.rint(rng.laplace(0, 0.7, n)).astype(np.int64)
+        buf, _, sync = emu(y, 1)
+        assert np.array_equal(emu.decode(buf, n, 1, sync), y), n
