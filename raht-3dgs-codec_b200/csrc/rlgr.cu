@@ -113,6 +113,8 @@ struct LaneBlock {
     int len;                   // symbols of the block inside the channel (0: none)
     uint32_t zeros_before;     // zeros between the previous non-zero of the channel and the block
     bool is_tail;              // block holds the channel's last symbol
+    int last_nz;               // index of the block's last non-zero symbol, -1: none
+    bool dense;                // warp-uniform: the chunk is mostly non-zero -> per-symbol branch-free counting
 };
 
 // Lane l of chunk w holds block 31 w - 1 + l (lane 0: the block before the chunk).
@@ -152,6 +154,15 @@ __device__ __forceinline__ LaneBlock load_chunk(const int32_t *__restrict__ q, c
     B.len = (int)len;
     B.zeros_before = (blk <= 0 || len == 0) ? 0u : (uint32_t)(start - 1 - (int64_t)lastnz_ch[blk - 1]);
     B.is_tail = len > 0 && start + len == G.n;
+    B.last_nz = -1;
+    uint32_t nz = 0;
+    for (int wd = 0; wd < MASK_WORDS; ++wd) {
+        const uint32_t m = B.mask[wd];
+        nz += __popc(m);
+        if (m) B.last_nz = 32 * wd + 31 - __clz((int)m);
+    }
+    for (int o = 16; o; o >>= 1) nz += __shfl_xor_sync(~0u, nz, o);
+    B.dense = nz * 2 >= (uint32_t)(CHUNK_LANES * BLOCK_SYMS);
     return B;
 }
 
@@ -176,13 +187,24 @@ __device__ __forceinline__ bool solve_chunk(const LaneBlock &B, bool pin, const 
     int r = 0;
     for (; r < 34; ++r) {
         if (need) {
-            for (int c = 0; c < NCAND; ++c) {
-                if (c > 0 && in[c] == in[0]) { out[c] = out[0]; bits[c] = bits[0]; continue; }
-                State s = in[c];
-                CountSink k{0};
-                code_block(B.row, B.len, B.mask, B.zeros_before, B.is_tail, s, k);
-                out[c] = s;
-                bits[c] = k.bits;
+            if (B.dense) {
+                for (int c = 0; c < NCAND; ++c) out[c] = in[c];
+                if (in[1] == in[0]) {
+                    count_block_dense<1>(B.row, B.len, B.last_nz, B.zeros_before, B.is_tail, out, bits);
+                    out[1] = out[0];
+                    bits[1] = bits[0];
+                } else {
+                    count_block_dense<NCAND>(B.row, B.len, B.last_nz, B.zeros_before, B.is_tail, out, bits);
+                }
+            } else {
+                for (int c = 0; c < NCAND; ++c) {
+                    if (c > 0 && in[c] == in[0]) { out[c] = out[0]; bits[c] = bits[0]; continue; }
+                    State s = in[c];
+                    CountSink k{0};
+                    code_block(B.row, B.len, B.mask, B.zeros_before, B.is_tail, s, k);
+                    out[c] = s;
+                    bits[c] = k.bits;
+                }
             }
         }
         need = false;

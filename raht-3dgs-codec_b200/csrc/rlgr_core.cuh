@@ -202,6 +202,67 @@ RL_HD void code_block(const uint32_t *row, int len, const uint32_t *mask, uint32
     }
 }
 
+// ---- dense blocks: one branch-free step per SYMBOL (lengths only) -----------------------------------------------
+// Same automaton as the event form, advanced one symbol at a time with selects instead of branches, for NC
+// candidate states side by side (independent chains: instruction-level parallelism instead of divergence).
+// Zeros cost as much as non-zeros here, so callers use it for blocks that are mostly non-zero.
+struct SymState {
+    int kP, kRP;
+    uint32_t m;         // open partial run
+    uint32_t bits;
+};
+
+// one symbol x (already mapped; 0 = zero symbol).  Returns true when the tail rule would fire if this were the
+// channel's last symbol (membuf.cpp:416: k at the top of the iteration != 0 and u, post-decrement, == 0).
+RL_HD bool sym_step(SymState &t, uint32_t x)
+{
+    const int k = t.kP >> 2;
+    const unsigned kR = (unsigned)(t.kRP >> 2);
+    const bool run = k != 0, z = x == 0;
+    const bool coded = !(run && z);                               // a Golomb-Rice code is written for this symbol
+    const uint32_t v = x - ((run && !z) ? 1u : 0u);               // run mode codes u - 1
+    const uint32_t p = kR > 31 ? 0u : v >> kR;
+    const uint32_t grlen = p < 32 ? p + 1 + kR : 64u;
+    const uint32_t m1 = t.m + 1;
+    const bool complete = !coded && m1 == (1u << k);
+    t.bits += coded ? grlen + (run ? (uint32_t)(1 + k) : 0u) : (complete ? 1u : 0u);
+    const int krp_up = t.kRP + (int)(p > 256u ? 256u : p) - 1;
+    const int krp_new = p ? (krp_up > RL_KRP_MAX ? RL_KRP_MAX : krp_up) : (t.kRP < 2 ? 0 : t.kRP - 2);
+    t.kRP = coded ? krp_new : t.kRP;
+    const int kp_coded = z ? t.kP + RL_U0 : (t.kP < 1 ? 0 : t.kP - 1);   // D0 == D1 == 1
+    t.kP = coded ? kp_coded : (complete ? t.kP + RL_U1 : t.kP);
+    t.m = (coded || complete) ? 0u : m1;
+    return run && v == 0;
+}
+
+// The block of code_block(), lengths only, for NC candidate states.  last_nz = index of the block's last non-zero
+// symbol (-1: none).  s[] in/out, bits[] out.
+template <int NC>
+RL_HD void count_block_dense(const uint32_t *row, int len, int last_nz, uint32_t zeros_before, bool is_tail, State *s,
+                             uint32_t *bits)
+{
+    SymState t[NC];
+    for (int c = 0; c < NC; ++c) {
+        CountSink k{0};
+        State st = s[c];
+        uint32_t m = 0;
+        if (zeros_before && (last_nz >= 0 || is_tail)) m = code_zeros(st, zeros_before, k, (bool *)nullptr);
+        t[c].kP = st.kP; t[c].kRP = st.kRP; t[c].m = m; t[c].bits = k.bits;
+    }
+    const int end = is_tail ? len : last_nz + 1;
+    bool fire[NC];
+    for (int c = 0; c < NC; ++c) fire[c] = false;
+    for (int i = 0; i < end; ++i) {
+        const uint32_t x = row[i];
+        for (int c = 0; c < NC; ++c) fire[c] = sym_step(t[c], x);
+    }
+    for (int c = 0; c < NC; ++c) {
+        if (is_tail && end > 0 && fire[c]) t[c].bits += 1 + (uint32_t)(t[c].kP >> 2);     // write(0); write(m, k_P / L)
+        s[c].kP = t[c].kP; s[c].kRP = t[c].kRP;
+        bits[c] = t[c].bits;
+    }
+}
+
 // ---- decoder ---------------------------------------------------------------------------------------------
 // MSB-first reader over big-endian 32-bit words; acc holds the next nbits bits left-aligned.
 struct BitReader {

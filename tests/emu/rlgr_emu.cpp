@@ -24,6 +24,8 @@ struct Lane {
     int len;
     uint32_t zeros_before;
     bool is_tail;
+    int last_nz;
+    bool dense;
 };
 
 struct Chan {
@@ -54,6 +56,13 @@ void load_chunk(const Chan &C, int64_t w, Lane L[32])
         B.zeros_before = (blk <= 0 || len == 0) ? 0u : (uint32_t)(start - 1 - (int64_t)C.lastnz[blk - 1]);
         B.is_tail = len > 0 && start + len == C.n;
     }
+    uint32_t nz = 0;
+    for (int l = 0; l < 32; ++l) {
+        L[l].last_nz = -1;
+        for (int i = 0; i < BLOCK_SYMS; ++i)
+            if (L[l].row[i]) { ++nz; L[l].last_nz = i; }
+    }
+    for (int l = 0; l < 32; ++l) L[l].dense = nz * 2 >= (uint32_t)(CHUNK_LANES * BLOCK_SYMS);
 }
 
 struct LaneRes {
@@ -80,6 +89,12 @@ int solve_chunk(const Lane L[32], bool pin, const State first[NCAND], LaneRes R[
     for (; r < 34; ++r) {
         for (int l = 0; l < 32; ++l) {
             if (!need[l]) continue;
+            if (L[l].dense) {
+                for (int c = 0; c < NCAND; ++c) R[l].out[c] = R[l].in[c];
+                count_block_dense<NCAND>(L[l].row.data(), L[l].len, L[l].last_nz, L[l].zeros_before, L[l].is_tail, R[l].out,
+                                         R[l].bits);
+                continue;
+            }
             for (int c = 0; c < NCAND; ++c) {
                 State s = R[l].in[c];
                 CountSink k{0};
