@@ -24,6 +24,7 @@
 // with the sync index and channel-serial without it (streams written by the reference coder).
 #include "common.cuh"
 #include "rlgr_core.cuh"
+#include <stdlib.h>
 
 namespace {
 
@@ -294,6 +295,8 @@ __global__ void __launch_bounds__(32) rlgr_speculate_kernel(const int32_t *__res
         pin = true;
     }
     const LaneBlock B = load_chunk(q, G, ch, w, lastnz + (size_t)ch * G.nblk, rl_smem);
+    // mostly non-zero chunks re-synchronise through k_P = 0 whatever the parity: one canonical state is enough
+    if (sweep == 0 && B.dense) first[1] = first[0];
     State in[NCAND], out[NCAND];
     uint32_t bits[NCAND];
     int rounds;
@@ -581,8 +584,20 @@ RAHT_API int raht_rlgr_encode(const int32_t *q, int64_t n, int64_t ld, int nch, 
     (raht_count_launches(1), rlgr_lastnz_kernel)<<<dim3(groups, nch), 32 * K0_WARPS, 0, st>>>(q, G, lastnz);
     (raht_count_launches(1), rlgr_lastnz_scan_kernel)<<<nch, 1024, 0, st>>>(G, lastnz);
     const dim3 cgrid((unsigned)G.nchunks, nch);
-    (raht_count_launches(1), rlgr_speculate_kernel)<<<cgrid, 32, smem, st>>>(q, G, lastnz, 0, recB, recA, lanerec, stats);
-    (raht_count_launches(1), rlgr_speculate_kernel)<<<cgrid, 32, smem, st>>>(q, G, lastnz, 1, recA, recB, lanerec, stats);
+    // speculation sweeps: the first from canonical states, later ones from the previous chunk's end states
+    static int sweeps = -1;
+    if (sweeps < 0) {
+        const char *e = getenv("RAHT_RLGR_SWEEPS");
+        sweeps = e ? atoi(e) : 2;
+        if (sweeps < 1) sweeps = 1;
+        if (sweeps > 8) sweeps = 8;
+    }
+    uint4 *rec_cur = recA, *rec_prev = recB;
+    for (int sw = 0; sw < sweeps; ++sw) {
+        (raht_count_launches(1), rlgr_speculate_kernel)<<<cgrid, 32, smem, st>>>(q, G, lastnz, sw, rec_prev, rec_cur, lanerec, stats);
+        uint4 *t = rec_cur; rec_cur = rec_prev; rec_prev = t;
+    }
+    recB = rec_prev;                                          // records of the last sweep
     (raht_count_launches(1), rlgr_resolve_kernel)<<<nch, 32, smem, st>>>(q, G, lastnz, recB, lanerec, chunkoff, slot_bytes, nbytes,
                                                                        totals, status, stats);
     (raht_count_launches(1), rlgr_zero_kernel)<<<dim3(64, nch), 256, 0, st>>>(streams, slot_bytes, totals);

@@ -213,6 +213,7 @@ __attribute__((visibility("default"))) int64_t emu_rlgr_encode(const int32_t *q,
                 pin = true;
             }
             load_chunk(C, w, L);
+            if (sweep == 0 && L[0].dense) first[1] = first[0];
             bool identity = false;
             const int rounds = solve_chunk(L, pin, first, R, &identity);
             cur[w] = finish_chunk(R, identity, &lanerec[w * 32]);
