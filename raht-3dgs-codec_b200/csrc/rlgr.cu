@@ -115,7 +115,8 @@ struct LaneBlock {
     uint32_t zeros_before;     // zeros between the previous non-zero of the channel and the block
     bool is_tail;              // block holds the channel's last symbol
     int last_nz;               // index of the block's last non-zero symbol, -1: none
-    bool dense;                // warp-uniform: the chunk is mostly non-zero -> per-symbol branch-free counting
+    bool dense;                // warp-uniform: >= 25 % non-zero -> per-symbol branch-free counting
+    bool single;               // warp-uniform: >= 50 % non-zero -> one canonical warm-up state is enough
 };
 
 // Lane l of chunk w holds block 31 w - 1 + l (lane 0: the block before the chunk).
@@ -163,7 +164,8 @@ __device__ __forceinline__ LaneBlock load_chunk(const int32_t *__restrict__ q, c
         if (m) B.last_nz = 32 * wd + 31 - __clz((int)m);
     }
     for (int o = 16; o; o >>= 1) nz += __shfl_xor_sync(~0u, nz, o);
-    B.dense = nz * 2 >= (uint32_t)(CHUNK_LANES * BLOCK_SYMS);
+    B.dense = nz * 4 >= (uint32_t)(CHUNK_LANES * BLOCK_SYMS);   // >= 25 % non-zero: the per-symbol form is cheaper
+    B.single = nz * 2 >= (uint32_t)(CHUNK_LANES * BLOCK_SYMS);
     return B;
 }
 
@@ -296,7 +298,7 @@ __global__ void __launch_bounds__(32) rlgr_speculate_kernel(const int32_t *__res
     }
     const LaneBlock B = load_chunk(q, G, ch, w, lastnz + (size_t)ch * G.nblk, rl_smem);
     // mostly non-zero chunks re-synchronise through k_P = 0 whatever the parity: one canonical state is enough
-    if (sweep == 0 && B.dense) first[1] = first[0];
+    if (sweep == 0 && B.single) first[1] = first[0];
     State in[NCAND], out[NCAND];
     uint32_t bits[NCAND];
     int rounds;

@@ -25,7 +25,7 @@ struct Lane {
     uint32_t zeros_before;
     bool is_tail;
     int last_nz;
-    bool dense;
+    bool dense, single;
 };
 
 struct Chan {
@@ -62,7 +62,10 @@ void load_chunk(const Chan &C, int64_t w, Lane L[32])
         for (int i = 0; i < BLOCK_SYMS; ++i)
             if (L[l].row[i]) { ++nz; L[l].last_nz = i; }
     }
-    for (int l = 0; l < 32; ++l) L[l].dense = nz * 2 >= (uint32_t)(CHUNK_LANES * BLOCK_SYMS);
+    for (int l = 0; l < 32; ++l) {
+        L[l].dense = nz * 4 >= (uint32_t)(CHUNK_LANES * BLOCK_SYMS);
+        L[l].single = nz * 2 >= (uint32_t)(CHUNK_LANES * BLOCK_SYMS);
+    }
 }
 
 struct LaneRes {
@@ -213,7 +216,7 @@ __attribute__((visibility("default"))) int64_t emu_rlgr_encode(const int32_t *q,
                 pin = true;
             }
             load_chunk(C, w, L);
-            if (sweep == 0 && L[0].dense) first[1] = first[0];
+            if (sweep == 0 && L[0].single) first[1] = first[0];
             bool identity = false;
             const int rounds = solve_chunk(L, pin, first, R, &identity);
             cur[w] = finish_chunk(R, identity, &lanerec[w * 32]);
