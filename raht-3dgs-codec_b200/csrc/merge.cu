@@ -12,6 +12,61 @@
 
 namespace {
 
+constexpr int MG_UNROLL = 4;      // (voxel, channel) elements per thread, loads batched level by level
+
+// Channel c of voxel [s, t) given its first member g0 (already fetched: opacity o0, and value x0 / quaternion q0).
+// Sums run in segment order with separately rounded multiply and add, starting from 0 as the reference does.
+__device__ __forceinline__ float merge_element(int c, int s, int t, float o0, float x0, float4 q0,
+                                               const int32_t *__restrict__ cidx, const float *__restrict__ means,
+                                               const float *__restrict__ quats, const float *__restrict__ scales,
+                                               const float *__restrict__ opac, const float *__restrict__ colors, int color_dim,
+                                               int by_opacity)
+{
+    if (t <= s) return 0.0f;                                             // merge_cluster.cu:27-29
+    const float w0 = by_opacity ? o0 : 1.0f;                             // :42
+    if (c >= 3 && c < 7) {
+        // quaternion: all four weighted sums are needed for the norm (:74-87)
+        float q[4] = {__fadd_rn(0.f, __fmul_rn(q0.x, w0)), __fadd_rn(0.f, __fmul_rn(q0.y, w0)),
+                      __fadd_rn(0.f, __fmul_rn(q0.z, w0)), __fadd_rn(0.f, __fmul_rn(q0.w, w0))};
+        for (int i = s + 1; i < t; ++i) {
+            const int g = cidx[i];
+            const float w = by_opacity ? opac[g] : 1.0f;
+            const float4 qq = *reinterpret_cast<const float4 *>(quats + (size_t)g * 4);
+            q[0] = __fadd_rn(q[0], __fmul_rn(qq.x, w));
+            q[1] = __fadd_rn(q[1], __fmul_rn(qq.y, w));
+            q[2] = __fadd_rn(q[2], __fmul_rn(qq.z, w));
+            q[3] = __fadd_rn(q[3], __fmul_rn(qq.w, w));
+        }
+        const float nn = __fadd_rn(__fadd_rn(__fadd_rn(__fmul_rn(q[0], q[0]), __fmul_rn(q[1], q[1])), __fmul_rn(q[2], q[2])),
+                                   __fmul_rn(q[3], q[3]));
+        const float qn = __fsqrt_rn(nn);                                 // :75-76
+        if (qn > 0.0f) return __fdiv_rn(q[c - 3], qn);
+        return (c == 6) ? 1.0f : 0.0f;                                   // fallback (0,0,0,1) :82-86
+    }
+    if (c == 10) {
+        float acc = __fadd_rn(0.0f, o0);
+        for (int i = s + 1; i < t; ++i) acc = __fadd_rn(acc, opac[cidx[i]]);
+        return fminf(acc, 1.0f);                                         // :94
+    }
+    const float *src;
+    int ld, col;
+    if (c < 3) { src = means; ld = 3; col = c; }
+    else if (c < 10) { src = scales; ld = 3; col = c - 7; }
+    else { src = colors; ld = color_dim; col = c - 11; }
+    float acc = __fadd_rn(0.0f, __fmul_rn(x0, w0)), wsum = __fadd_rn(0.0f, w0);
+    for (int i = s + 1; i < t; ++i) {
+        const int g = cidx[i];
+        const float w = by_opacity ? opac[g] : 1.0f;
+        acc = __fadd_rn(acc, __fmul_rn(src[(size_t)g * ld + col], w));
+        wsum = __fadd_rn(wsum, w);
+    }
+    if (c < 10) {
+        if (wsum == 0.0f) wsum = 1.0f;                                   // :65-67
+        return __fdiv_rn(acc, wsum);
+    }
+    return (wsum > 0.0f) ? __fdiv_rn(acc, wsum) : 0.0f;                  // :108-109
+}
+
 template <typename OutT>
 __global__ void __launch_bounds__(256)
 merge_kernel(const int32_t *__restrict__ cidx, const int32_t *__restrict__ coff, int64_t nclu,
@@ -22,60 +77,51 @@ merge_kernel(const int32_t *__restrict__ cidx, const int32_t *__restrict__ coff,
 {
     const int OC = 11 + color_dim;
     const int64_t total = nclu * OC;
-    for (int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; e < total; e += (int64_t)gridDim.x * blockDim.x) {
-        const int64_t v = e / OC;
-        const int c = (int)(e - v * OC);
-        const int s = coff[v], t = coff[v + 1];
-        float out = 0.0f;
-        if (t > s) {                                                     // merge_cluster.cu:27-29
-            if (c >= 3 && c < 7) {
-                // quaternion: all four weighted sums are needed for the norm (:74-87)
-                float q[4] = {0.f, 0.f, 0.f, 0.f};
-                for (int i = s; i < t; ++i) {
-                    int g = cidx[i];
-                    float w = by_opacity ? opac[g] : 1.0f;               // :42
-                    const float4 qq = *reinterpret_cast<const float4 *>(quats + (size_t)g * 4);
-                    q[0] = __fadd_rn(q[0], __fmul_rn(qq.x, w));
-                    q[1] = __fadd_rn(q[1], __fmul_rn(qq.y, w));
-                    q[2] = __fadd_rn(q[2], __fmul_rn(qq.z, w));
-                    q[3] = __fadd_rn(q[3], __fmul_rn(qq.w, w));
-                }
-                float nn = __fadd_rn(__fadd_rn(__fadd_rn(__fmul_rn(q[0], q[0]), __fmul_rn(q[1], q[1])), __fmul_rn(q[2], q[2])),
-                                     __fmul_rn(q[3], q[3]));
-                float qn = __fsqrt_rn(nn);                               // :75-76
-                if (qn > 0.0f) out = __fdiv_rn(q[c - 3], qn);
-                else out = (c == 6) ? 1.0f : 0.0f;                       // fallback (0,0,0,1) :82-86
-            } else if (c == 10) {
-                float acc = 0.0f;
-                for (int i = s; i < t; ++i) acc = __fadd_rn(acc, opac[cidx[i]]);
-                out = fminf(acc, 1.0f);                                  // :94
-            } else {
-                const float *src;
-                int ld, col;
-                if (c < 3) { src = means; ld = 3; col = c; }
-                else if (c < 10) { src = scales; ld = 3; col = c - 7; }
-                else { src = colors; ld = color_dim; col = c - 11; }
-                float acc = 0.0f, wsum = 0.0f;
-                for (int i = s; i < t; ++i) {
-                    int g = cidx[i];
-                    float w = by_opacity ? opac[g] : 1.0f;
-                    acc = __fadd_rn(acc, __fmul_rn(src[(size_t)g * ld + col], w));
-                    wsum = __fadd_rn(wsum, w);
-                }
-                if (c < 10) {
-                    if (wsum == 0.0f) wsum = 1.0f;                       // :65-67
-                    out = __fdiv_rn(acc, wsum);
-                } else {
-                    out = (wsum > 0.0f) ? __fdiv_rn(acc, wsum) : 0.0f;   // :108-109
-                }
+    const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+    for (int64_t e0 = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; e0 < total; e0 += MG_UNROLL * stride) {
+        int64_t v[MG_UNROLL];
+        int c[MG_UNROLL], s[MG_UNROLL], t[MG_UNROLL], g[MG_UNROLL];
+        float o0[MG_UNROLL], x0[MG_UNROLL];
+        float4 q0[MG_UNROLL];
+        // the dependent loads (offsets -> member index -> member data) are issued level by level for all elements
+#pragma unroll
+        for (int u = 0; u < MG_UNROLL; ++u) {
+            const int64_t e = e0 + u * stride;
+            const bool ok = e < total;
+            v[u] = ok ? e / OC : 0;
+            c[u] = (int)(e - v[u] * OC);
+            s[u] = ok ? coff[v[u]] : 0;
+            t[u] = ok ? coff[v[u] + 1] : 0;
+        }
+#pragma unroll
+        for (int u = 0; u < MG_UNROLL; ++u) g[u] = t[u] > s[u] ? cidx[s[u]] : -1;
+#pragma unroll
+        for (int u = 0; u < MG_UNROLL; ++u) {
+            o0[u] = 0.f; x0[u] = 0.f; q0[u] = make_float4(0.f, 0.f, 0.f, 0.f);
+            if (g[u] >= 0) {
+                const int cc = c[u];
+                o0[u] = opac[g[u]];
+                if (cc >= 3 && cc < 7) q0[u] = *reinterpret_cast<const float4 *>(quats + (size_t)g[u] * 4);
+                else if (cc < 3) x0[u] = means[(size_t)g[u] * 3 + cc];
+                else if (cc < 10) x0[u] = scales[(size_t)g[u] * 3 + (cc - 7)];
+                else if (cc > 10) x0[u] = colors[(size_t)g[u] * color_dim + (cc - 11)];
             }
         }
-        if (c < 3) { if (m_means) m_means[v * 3 + c] = out; }
-        else if (c < 7) { if (m_quats) m_quats[v * 4 + (c - 3)] = out; }
-        else if (c < 10) { if (m_scales) m_scales[v * 3 + (c - 7)] = out; }
-        else if (c == 10) { if (m_opac) m_opac[v] = out; }
-        else { if (m_colors) m_colors[v * (int64_t)color_dim + (c - 11)] = out; }
-        if (packed) packed[e] = (OutT)out;
+#pragma unroll
+        for (int u = 0; u < MG_UNROLL; ++u) {
+            const int64_t e = e0 + u * stride;
+            if (e >= total) continue;
+            const int cc = c[u];
+            const float out = merge_element(cc, s[u], t[u], o0[u], x0[u], q0[u], cidx, means, quats, scales, opac, colors,
+                                            color_dim, by_opacity);
+            const int64_t vv = v[u];
+            if (cc < 3) { if (m_means) m_means[vv * 3 + cc] = out; }
+            else if (cc < 7) { if (m_quats) m_quats[vv * 4 + (cc - 3)] = out; }
+            else if (cc < 10) { if (m_scales) m_scales[vv * 3 + (cc - 7)] = out; }
+            else if (cc == 10) { if (m_opac) m_opac[vv] = out; }
+            else { if (m_colors) m_colors[vv * (int64_t)color_dim + (cc - 11)] = out; }
+            if (packed) packed[e] = (OutT)out;
+        }
     }
 }
 
@@ -95,7 +141,7 @@ RAHT_API int raht_merge_segments(const int32_t *cluster_indices, const int32_t *
     RAHT_REQUIRE(packed_dtype == RAHT_F32 || packed_dtype == RAHT_F64, "raht_merge_segments: bad packed_dtype");
     cudaStream_t st = (cudaStream_t)stream;
     int64_t total = num_clusters * (11 + color_dim);
-    int grid = grid_for(total, 256, 8);
+    int grid = grid_for((total + MG_UNROLL - 1) / MG_UNROLL, 256, 8);
     raht_count_launches(1);
     if (packed && packed_dtype == RAHT_F64)
         merge_kernel<double><<<grid, 256, 0, st>>>(cluster_indices, cluster_offsets, num_clusters, means, quats, scales,
