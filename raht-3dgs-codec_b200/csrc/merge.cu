@@ -67,8 +67,14 @@ __device__ __forceinline__ float merge_element(int c, int s, int t, float o0, fl
     return (wsum > 0.0f) ? __fdiv_rn(acc, wsum) : 0.0f;                  // :108-109
 }
 
+// Thread (x, y) of a 64 x 4 block: channel c = x (+64, ... when there are more than 64 channels) of voxel
+// blockIdx * 4 + y, MG_UNROLL voxels per thread a grid stride apart.  No integer division anywhere; the offset /
+// member-index / opacity loads of a voxel are the same address for its 59 threads (one broadcast transaction), the
+// colour row and the packed output row are contiguous across x.
+constexpr int MG_TX = 64, MG_TY = 4;
+
 template <typename OutT>
-__global__ void __launch_bounds__(256)
+__global__ void __launch_bounds__(MG_TX *MG_TY)
 merge_kernel(const int32_t *__restrict__ cidx, const int32_t *__restrict__ coff, int64_t nclu,
              const float *__restrict__ means, const float *__restrict__ quats, const float *__restrict__ scales,
              const float *__restrict__ opac, const float *__restrict__ colors, int color_dim, int by_opacity,
@@ -76,51 +82,48 @@ merge_kernel(const int32_t *__restrict__ cidx, const int32_t *__restrict__ coff,
              float *__restrict__ m_opac, float *__restrict__ m_colors, OutT *__restrict__ packed)
 {
     const int OC = 11 + color_dim;
-    const int64_t total = nclu * OC;
-    const int64_t stride = (int64_t)gridDim.x * blockDim.x;
-    for (int64_t e0 = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; e0 < total; e0 += MG_UNROLL * stride) {
-        int64_t v[MG_UNROLL];
-        int c[MG_UNROLL], s[MG_UNROLL], t[MG_UNROLL], g[MG_UNROLL];
-        float o0[MG_UNROLL], x0[MG_UNROLL];
-        float4 q0[MG_UNROLL];
-        // the dependent loads (offsets -> member index -> member data) are issued level by level for all elements
+    const int64_t vstride = (int64_t)gridDim.x * MG_TY;
+    for (int64_t v0 = (int64_t)blockIdx.x * MG_TY + threadIdx.y; v0 < nclu; v0 += MG_UNROLL * vstride) {
+        int s[MG_UNROLL], t[MG_UNROLL], g[MG_UNROLL];
+        float o0[MG_UNROLL];
+        // the dependent loads (offsets -> member index -> member data) are issued level by level for all voxels
 #pragma unroll
         for (int u = 0; u < MG_UNROLL; ++u) {
-            const int64_t e = e0 + u * stride;
-            const bool ok = e < total;
-            v[u] = ok ? e / OC : 0;
-            c[u] = (int)(e - v[u] * OC);
-            s[u] = ok ? coff[v[u]] : 0;
-            t[u] = ok ? coff[v[u] + 1] : 0;
+            const int64_t v = v0 + u * vstride;
+            const bool ok = v < nclu;
+            s[u] = ok ? coff[v] : 0;
+            t[u] = ok ? coff[v + 1] : 0;
         }
 #pragma unroll
         for (int u = 0; u < MG_UNROLL; ++u) g[u] = t[u] > s[u] ? cidx[s[u]] : -1;
 #pragma unroll
-        for (int u = 0; u < MG_UNROLL; ++u) {
-            o0[u] = 0.f; x0[u] = 0.f; q0[u] = make_float4(0.f, 0.f, 0.f, 0.f);
-            if (g[u] >= 0) {
-                const int cc = c[u];
-                o0[u] = opac[g[u]];
-                if (cc >= 3 && cc < 7) q0[u] = *reinterpret_cast<const float4 *>(quats + (size_t)g[u] * 4);
-                else if (cc < 3) x0[u] = means[(size_t)g[u] * 3 + cc];
-                else if (cc < 10) x0[u] = scales[(size_t)g[u] * 3 + (cc - 7)];
-                else if (cc > 10) x0[u] = colors[(size_t)g[u] * color_dim + (cc - 11)];
-            }
-        }
+        for (int u = 0; u < MG_UNROLL; ++u) o0[u] = g[u] >= 0 ? opac[g[u]] : 0.f;
+        for (int cc = threadIdx.x; cc < OC; cc += MG_TX) {
+            float x0[MG_UNROLL];
+            float4 q0[MG_UNROLL];
 #pragma unroll
-        for (int u = 0; u < MG_UNROLL; ++u) {
-            const int64_t e = e0 + u * stride;
-            if (e >= total) continue;
-            const int cc = c[u];
-            const float out = merge_element(cc, s[u], t[u], o0[u], x0[u], q0[u], cidx, means, quats, scales, opac, colors,
-                                            color_dim, by_opacity);
-            const int64_t vv = v[u];
-            if (cc < 3) { if (m_means) m_means[vv * 3 + cc] = out; }
-            else if (cc < 7) { if (m_quats) m_quats[vv * 4 + (cc - 3)] = out; }
-            else if (cc < 10) { if (m_scales) m_scales[vv * 3 + (cc - 7)] = out; }
-            else if (cc == 10) { if (m_opac) m_opac[vv] = out; }
-            else { if (m_colors) m_colors[vv * (int64_t)color_dim + (cc - 11)] = out; }
-            if (packed) packed[e] = (OutT)out;
+            for (int u = 0; u < MG_UNROLL; ++u) {
+                x0[u] = 0.f; q0[u] = make_float4(0.f, 0.f, 0.f, 0.f);
+                if (g[u] >= 0) {
+                    if (cc >= 3 && cc < 7) q0[u] = *reinterpret_cast<const float4 *>(quats + (size_t)g[u] * 4);
+                    else if (cc < 3) x0[u] = means[(size_t)g[u] * 3 + cc];
+                    else if (cc < 10) x0[u] = scales[(size_t)g[u] * 3 + (cc - 7)];
+                    else if (cc > 10) x0[u] = colors[(size_t)g[u] * color_dim + (cc - 11)];
+                }
+            }
+#pragma unroll
+            for (int u = 0; u < MG_UNROLL; ++u) {
+                const int64_t vv = v0 + u * vstride;
+                if (vv >= nclu) continue;
+                const float out = merge_element(cc, s[u], t[u], o0[u], x0[u], q0[u], cidx, means, quats, scales, opac, colors,
+                                                color_dim, by_opacity);
+                if (cc < 3) { if (m_means) m_means[vv * 3 + cc] = out; }
+                else if (cc < 7) { if (m_quats) m_quats[vv * 4 + (cc - 3)] = out; }
+                else if (cc < 10) { if (m_scales) m_scales[vv * 3 + (cc - 7)] = out; }
+                else if (cc == 10) { if (m_opac) m_opac[vv] = out; }
+                else { if (m_colors) m_colors[vv * (int64_t)color_dim + (cc - 11)] = out; }
+                if (packed) packed[vv * OC + cc] = (OutT)out;
+            }
         }
     }
 }
@@ -141,14 +144,15 @@ RAHT_API int raht_merge_segments(const int32_t *cluster_indices, const int32_t *
     RAHT_REQUIRE(packed_dtype == RAHT_F32 || packed_dtype == RAHT_F64, "raht_merge_segments: bad packed_dtype");
     cudaStream_t st = (cudaStream_t)stream;
     int64_t total = num_clusters * (11 + color_dim);
-    int grid = grid_for((total + MG_UNROLL - 1) / MG_UNROLL, 256, 8);
+    int grid = grid_for((num_clusters + MG_UNROLL - 1) / MG_UNROLL, MG_TY, 6);
+    const dim3 block(MG_TX, MG_TY);
     raht_count_launches(1);
     if (packed && packed_dtype == RAHT_F64)
-        merge_kernel<double><<<grid, 256, 0, st>>>(cluster_indices, cluster_offsets, num_clusters, means, quats, scales,
+        merge_kernel<double><<<grid, block, 0, st>>>(cluster_indices, cluster_offsets, num_clusters, means, quats, scales,
                                                    opacities, colors, color_dim, weight_by_opacity, m_means, m_quats,
                                                    m_scales, m_opacities, m_colors, (double *)packed);
     else
-        merge_kernel<float><<<grid, 256, 0, st>>>(cluster_indices, cluster_offsets, num_clusters, means, quats, scales,
+        merge_kernel<float><<<grid, block, 0, st>>>(cluster_indices, cluster_offsets, num_clusters, means, quats, scales,
                                                   opacities, colors, color_dim, weight_by_opacity, m_means, m_quats,
                                                   m_scales, m_opacities, m_colors, (float *)packed);
     RAHT_LAUNCH_CHECK();
