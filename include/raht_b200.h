@@ -29,7 +29,7 @@
 extern "C" {
 #endif
 
-#define RAHT_B200_ABI_VERSION 5
+#define RAHT_B200_ABI_VERSION 6
 
 enum {
     RAHT_OK = 0,
@@ -216,8 +216,9 @@ int raht_dequantize_f64(const double *q, int64_t count, double step, double *T, 
  *
  * sync_index (optional, device, nch * raht_rlgr_sync_entries(n) entries of 8 bytes): side
  * information the encoder can emit next to the reference bitstream -- for every range of 512
- * symbols (4 blocks of 128; 8 ranges per chunk of 31 blocks) the bit offset and coder state
- * (k_P, k_RP) before the range's first event and the position of that event's non-zero symbol:
+ * symbols [512 r, 512 r + 512), raht_rlgr_sync_entries(n) = ceil(n / 512) per channel, the bit offset
+ * and coder state (k_P, k_RP) before the range's first event and the position of that event's
+ * non-zero symbol inside the range:
  *   word 0 = bit offset (low 32), word 1 = offset bits 32..38 | k_P << 7 | k_RP << 14 | first << 22
  *   (first = 1023: the range holds only zeros).
  * The streams do not depend on it.  raht_rlgr_decode with the index decodes every range in
@@ -229,9 +230,10 @@ size_t raht_rlgr_encode_workspace_bytes(int64_t n, int nch);
 int raht_rlgr_encode(const int32_t *q, int64_t n, int64_t ld, int nch, int flag_signed,
                      uint8_t *streams, int64_t slot_bytes, int64_t *nbytes, void *sync_index,
                      int32_t *status, void *workspace, size_t workspace_bytes, void *stream);
-/* diagnostics of the last encode on `workspace`: out3_host = {chunk solves in the speculation sweeps,
- * their fixed-point rounds, chunks re-solved by the resolve pass}.  Synchronises `stream`.          */
-int raht_rlgr_encode_stats(const void *workspace, int64_t n, int nch, unsigned long long *out3_host,
+/* diagnostics of the last encode on `workspace`: out5_host = {chunk solves in the speculation pass,
+ * their fixed-point rounds, chunks re-solved by the resolve pass, slowest chunk of the speculation
+ * pass as SM cycles << 24 | channel << 8 | rounds, rounds spent in the re-solves}.  Synchronises.    */
+int raht_rlgr_encode_stats(const void *workspace, int64_t n, int nch, unsigned long long *out5_host,
                            void *stream);
 int raht_rlgr_decode(const uint8_t *streams, int64_t slot_bytes, const int64_t *nbytes,
                      const void *sync_index, int64_t n, int64_t ld, int nch, int flag_signed,

@@ -5,22 +5,24 @@
 // for bit: MSB-first packing, zero padding to a byte, constants L=4,U0=3,D0=1,U1=2,D1=1
 // (membuf.h:18-22), including the tail rule (:416-419) and the 32-bit escape (:242-256).
 //
-// The reference coder is a sequential state machine per channel.  Here a channel is cut into lane
-// blocks of 128 symbols at EVENT boundaries (rlgr_core.cuh: between events the state is (k_P,k_RP));
-// 31 consecutive blocks form a warp chunk, solved by one warp:
-//   K0  last_nonzero     per block: index of its last non-zero symbol; max-scanned per channel, so every
-//                        block knows how many zeros precede it (its first event's run starts there);
-//   A   speculate        every chunk in parallel.  Each lane codes its block (lengths only) from two
-//                        candidate start states; lane j+1 then restarts from lane j's end states until
-//                        nothing changes (exact inside the chunk after <= 32 rounds, 2 in practice).
-//                        Lane 0 holds the block BEFORE the chunk as warm-up from canonical states;
-//                        later sweeps start from the previous chunk's end states instead;
+// The reference coder is a sequential state machine per channel.  Here every channel is first
+// compacted to its EVENT list (rlgr_core.cuh: event = zero run + the non-zero symbol that ends it;
+// between events the state is (k_P,k_RP)), stored lane-interleaved so that the 32 lanes of a warp
+// stream 32 consecutive blocks of 128 events with fully coalesced loads and no shared memory:
+//   K1  count / scan / scatter   non-zeros per 128-symbol block, exclusive scan per channel, then
+//                        every non-zero symbol writes (gap, u) to its slot of the event store;
+//   A   speculate        every chunk (31 blocks + the block before it as warm-up) in parallel: each
+//                        lane codes its block (lengths only) from two canonical start states; lane
+//                        j+1 then restarts from lane j's end states until nothing changes (exact
+//                        inside the chunk after <= 32 rounds, ~2 in practice);
 //   B   resolve          one warp per channel walks the chunk records: the true start state selects
 //                        the matching candidate (or the chunk is re-solved exactly), giving each chunk
-//                        its start state and bit offset, the channel its byte length and -- optionally
-//                        -- the sync index that lets the decoder start at every chunk;
-//   C   emit             every lane re-codes its block from its now-known state and bit offset.
-// All of it is exact: speculation only decides how much is recomputed.  The decoder is chunk-parallel
+//                        its start state and bit offset and the channel its byte length;
+//   C   emit             every lane re-codes its block from its now-known state at its now-known bit
+//                        offset, and writes the sync index (one entry per 512 symbols) on the way.
+// All of it is exact: speculation only decides how much is recomputed.  Work, warm-up length and the
+// number of chunks are proportional to the number of EVENTS, so zero runs cost nothing and sparse
+// channels (which never re-synchronise) have few chunks to repair.  The decoder is range-parallel
 // with the sync index and channel-serial without it (streams written by the reference coder).
 #include "common.cuh"
 #include "rlgr_core.cuh"
@@ -30,341 +32,531 @@ namespace {
 
 using namespace rlgr;
 
-constexpr int SYNC_STRIDE = 4;                                                // lane blocks per sync entry
-constexpr int SYNC_PER_CHUNK = (CHUNK_LANES + SYNC_STRIDE - 1) / SYNC_STRIDE;     // 8 entries per warp chunk
-constexpr uint32_t SYNC_NONE = 1023;                                          // no non-zero symbol in the entry's range
-constexpr int ROW_PITCH = BLOCK_SYMS + 1;                         // odd pitch: lane-strided reads are conflict-free
-constexpr int CHUNK_SMEM_WORDS = 32 * ROW_PITCH + 32 * MASK_WORDS;
-
 struct Geometry {
     int64_t n, ld;
-    int64_t nblk;        // lane blocks per channel
-    int64_t nchunks;     // warp chunks per channel
+    int64_t nsb;         // 128-symbol blocks per channel (compaction passes)
+    int64_t W;           // chunk slots per channel in the event store (enough for n events)
     int nch, flag_signed;
 };
 
-__host__ __device__ inline int64_t blocks_of(int64_t n) { return (n + BLOCK_SYMS - 1) / BLOCK_SYMS; }
-__host__ __device__ inline int64_t chunks_of(int64_t n) { return (blocks_of(n) + CHUNK_LANES - 1) / CHUNK_LANES; }
+__host__ __device__ inline int64_t sym_blocks_of(int64_t n) { return (n + SYM_BLOCK - 1) / SYM_BLOCK; }
+__host__ __device__ inline int64_t ev_blocks_of(int64_t events) { return events > 0 ? (events + EV_BLOCK - 1) / EV_BLOCK : 1; }
+__host__ __device__ inline int64_t chunks_of_blocks(int64_t nb) { return (nb + CHUNK_LANES - 1) / CHUNK_LANES; }
+__host__ __device__ inline int64_t chunk_slots_of(int64_t n) { return chunks_of_blocks(ev_blocks_of(n)); }
 
-// ---- K0: last non-zero symbol of every lane block ------------------------------------------------------
-constexpr int K0_WARPS = 8;
-__global__ void __launch_bounds__(32 * K0_WARPS) rlgr_lastnz_kernel(const int32_t *__restrict__ q, Geometry G,
-                                                                   int32_t *__restrict__ lastnz)
+// per-channel header written by the scan pass
+struct ChanInfo {
+    uint32_t events;     // non-zero symbols of the channel
+    uint32_t nblocks;    // event blocks (>= 1: the block of an empty channel codes the tail)
+    uint32_t nchunks;
+    uint32_t tail_zeros; // zero symbols after the last event
+};
+
+// ---- K1a: non-zero count and last non-zero symbol of every 128-symbol block -----------------------------
+constexpr int K1_WARPS = 8;
+__global__ void __launch_bounds__(32 * K1_WARPS) rlgr_count_kernel(const int32_t *__restrict__ q, Geometry G,
+                                                                  uint32_t *__restrict__ cnt, int32_t *__restrict__ lastnz)
 {
     const int lane = threadIdx.x & 31;
-    const int64_t group = (int64_t)blockIdx.x * K0_WARPS + (threadIdx.x >> 5);      // 32 lane blocks per warp
+    const int64_t group = (int64_t)blockIdx.x * K1_WARPS + (threadIdx.x >> 5);      // 32 symbol blocks per warp
     const int ch = blockIdx.y;
     const int64_t blk0 = group * 32;
-    if (blk0 >= G.nblk) return;
+    if (blk0 >= G.nsb) return;
     const int32_t *src = q + (size_t)ch * G.ld;
-    int32_t mine = -1;
+    int32_t mine_last = -1;
+    uint32_t mine_cnt = 0;
+#pragma unroll 4
     for (int b = 0; b < 32; ++b) {
-        const int64_t s0 = (blk0 + b) * BLOCK_SYMS;
+        const int64_t s0 = (blk0 + b) * SYM_BLOCK;
         if (s0 >= G.n) break;
-        int32_t v[MASK_WORDS];
+        int32_t v[4];
 #pragma unroll
-        for (int w = 0; w < MASK_WORDS; ++w) {
+        for (int w = 0; w < 4; ++w) {
             const int64_t i = s0 + 32 * w + lane;
             v[w] = i < G.n ? src[i] : 0;
         }
         int32_t last = -1;
+        uint32_t c = 0;
 #pragma unroll
-        for (int w = 0; w < MASK_WORDS; ++w) {
+        for (int w = 0; w < 4; ++w) {
             const unsigned m = __ballot_sync(~0u, v[w] != 0);
+            c += __popc(m);
             if (m) last = (int32_t)(s0 + 32 * w + 31 - __clz((int)m));
         }
-        if (lane == b) mine = last;
+        if (lane == b) { mine_last = last; mine_cnt = c; }
     }
-    if (blk0 + lane < G.nblk) lastnz[(size_t)ch * G.nblk + blk0 + lane] = mine;
+    if (blk0 + lane < G.nsb) {
+        lastnz[(size_t)ch * G.nsb + blk0 + lane] = mine_last;
+        cnt[(size_t)ch * G.nsb + blk0 + lane] = mine_cnt;
+    }
 }
 
-// inclusive max-scan of lastnz per channel: afterwards lastnz[b] = last non-zero symbol at or before
-// the end of block b (-1: none).  One CTA per channel.
-__global__ void __launch_bounds__(1024) rlgr_lastnz_scan_kernel(Geometry G, int32_t *__restrict__ lastnz)
+// ---- K1b: per channel, exclusive sum-scan of cnt (-> index of the block's first event) and inclusive
+// max-scan of lastnz (-> last non-zero symbol at or before the end of the block).  One CTA per channel.
+__global__ void __launch_bounds__(1024) rlgr_scan_kernel(Geometry G, uint32_t *__restrict__ cnt, int32_t *__restrict__ lastnz,
+                                                         ChanInfo *__restrict__ info)
 {
     __shared__ int32_t wmax[32];
-    __shared__ int32_t carry_s;
-    int32_t *a = lastnz + (size_t)blockIdx.x * G.nblk;
+    __shared__ uint32_t wsum[32];
+    __shared__ int32_t carry_max;
+    __shared__ uint32_t carry_sum;
+    int32_t *a = lastnz + (size_t)blockIdx.x * G.nsb;
+    uint32_t *c = cnt + (size_t)blockIdx.x * G.nsb;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    if (threadIdx.x == 0) carry_s = -1;
+    if (threadIdx.x == 0) { carry_max = -1; carry_sum = 0; }
     __syncthreads();
-    for (int64_t base = 0; base < G.nblk; base += 1024) {
+    for (int64_t base = 0; base < G.nsb; base += 1024) {
         const int64_t i = base + threadIdx.x;
-        int32_t x = i < G.nblk ? a[i] : -1;
+        int32_t x = i < G.nsb ? a[i] : -1;
+        const uint32_t own = i < G.nsb ? c[i] : 0u;
+        uint32_t s = own;
         for (int o = 1; o < 32; o <<= 1) {
-            int32_t y = __shfl_up_sync(~0u, x, o);
-            if (lane >= o) x = max(x, y);
+            const int32_t y = __shfl_up_sync(~0u, x, o);
+            const uint32_t t = __shfl_up_sync(~0u, s, o);
+            if (lane >= o) { x = max(x, y); s += t; }
         }
-        if (lane == 31) wmax[warp] = x;
+        if (lane == 31) { wmax[warp] = x; wsum[warp] = s; }
         __syncthreads();
-        int32_t pre = carry_s;
-        for (int w = 0; w < warp; ++w) pre = max(pre, wmax[w]);
+        int32_t pre = carry_max;
+        uint32_t pres = carry_sum;
+        for (int w = 0; w < warp; ++w) { pre = max(pre, wmax[w]); pres += wsum[w]; }
         x = max(x, pre);
-        if (i < G.nblk) a[i] = x;
+        s += pres;
+        if (i < G.nsb) { a[i] = x; c[i] = s - own; }
         __syncthreads();
-        if (threadIdx.x == 1023) carry_s = x;
+        if (threadIdx.x == 1023) { carry_max = x; carry_sum = s; }
         __syncthreads();
+    }
+    if (threadIdx.x == 0) {
+        ChanInfo I;
+        I.events = carry_sum;
+        I.nblocks = (uint32_t)ev_blocks_of(carry_sum);
+        I.nchunks = (uint32_t)chunks_of_blocks(I.nblocks);
+        I.tail_zeros = (uint32_t)(G.n - 1 - (int64_t)carry_max);
+        info[blockIdx.x] = I;
     }
 }
 
-// ---- one warp chunk in shared memory -------------------------------------------------------------------
+// ---- K1c: scatter every non-zero symbol to its slot(s) of the event store ----------------------------------
+// store: uint2 (gap, u) [channel][chunk slot w][unit j = i / 4][lane][i % 4]; block b = 31 w - 1 + lane, so the
+// last block of a chunk is written twice (lane 31 of chunk w and lane 0, the warm-up, of chunk w + 1).
+// blockpos[channel][b] = symbol index of the block's first event.
+__device__ __forceinline__ void store_event(uint2 *__restrict__ evc, uint32_t *__restrict__ bpos, int64_t W, uint32_t e,
+                                            uint32_t gap, uint32_t u, uint32_t pos)
+{
+    const uint32_t b = e / EV_BLOCK;
+    const int i = (int)(e % EV_BLOCK);
+    const uint32_t w = b / CHUNK_LANES;
+    const int l = (int)(b - w * CHUNK_LANES) + 1;
+    evc[(size_t)w * CHUNK_SLOTS + ev_slot(l, i)] = make_uint2(gap, u);
+    if (l == CHUNK_LANES && (int64_t)w + 1 < W) evc[(size_t)(w + 1) * CHUNK_SLOTS + ev_slot(0, i)] = make_uint2(gap, u);
+    if (i == 0) bpos[b] = pos;
+}
+
+__global__ void __launch_bounds__(32 * K1_WARPS) rlgr_scatter_kernel(const int32_t *__restrict__ q, Geometry G,
+                                                                    const uint32_t *__restrict__ evbase,
+                                                                    const int32_t *__restrict__ lastnz, uint2 *__restrict__ ev,
+                                                                    uint32_t *__restrict__ blockpos)
+{
+    const int lane = threadIdx.x & 31;
+    const int64_t group = (int64_t)blockIdx.x * K1_WARPS + (threadIdx.x >> 5);
+    const int ch = blockIdx.y;
+    const int64_t blk0 = group * 32;
+    if (blk0 >= G.nsb) return;
+    const int32_t *src = q + (size_t)ch * G.ld;
+    uint2 *evc = ev + (size_t)ch * G.W * CHUNK_SLOTS;
+    uint32_t *bpos = blockpos + (size_t)ch * G.nsb;
+    uint32_t e = evbase[(size_t)ch * G.nsb + blk0];
+    int64_t last = blk0 ? (int64_t)lastnz[(size_t)ch * G.nsb + blk0 - 1] : -1;          // warp-uniform
+#pragma unroll 2
+    for (int b = 0; b < 32; ++b) {
+        const int64_t s0 = (blk0 + b) * SYM_BLOCK;
+        if (s0 >= G.n) break;
+        int32_t v[4];
+#pragma unroll
+        for (int w = 0; w < 4; ++w) {
+            const int64_t i = s0 + 32 * w + lane;
+            v[w] = i < G.n ? src[i] : 0;
+        }
+#pragma unroll
+        for (int w = 0; w < 4; ++w) {
+            const unsigned m = __ballot_sync(~0u, v[w] != 0);
+            if (!m) continue;
+            const int64_t wbase = s0 + 32 * w;
+            if (v[w] != 0) {
+                const unsigned before = m & lanemask_lt();
+                const int64_t prev = before ? wbase + 31 - __clz((int)before) : last;
+                const int64_t pos = wbase + lane;
+                const uint32_t u = G.flag_signed ? s2u(v[w]) : (uint32_t)v[w];
+                store_event(evc, bpos, G.W, e + __popc(before), (uint32_t)(pos - prev - 1), u, (uint32_t)pos);
+            }
+            e += __popc(m);
+            last = wbase + 31 - __clz((int)m);
+        }
+    }
+}
+
+// ---- one lane block of the event store ---------------------------------------------------------------------
 struct LaneBlock {
-    const uint32_t *row;       // mapped symbols of this lane's block (shared memory)
-    const uint32_t *mask;      // MASK_WORDS non-zero masks
-    int len;                   // symbols of the block inside the channel (0: none)
-    uint32_t zeros_before;     // zeros between the previous non-zero of the channel and the block
-    bool is_tail;              // block holds the channel's last symbol
-    int last_nz;               // index of the block's last non-zero symbol, -1: none
-    bool dense;                // warp-uniform: >= 25 % non-zero -> per-symbol branch-free counting
-    bool single;               // warp-uniform: >= 50 % non-zero -> one canonical warm-up state is enough
+    const uint4 *base;         // the chunk in the store, as 16-byte units: unit j of this lane at base[(j * 32 + lane) * 2 + {0,1}]
+    int cnt;                   // events of this lane's block (0: none)
+    bool is_tail;              // the block holds the channel's last event (or the channel has none): it also codes the tail
+    uint32_t tail_zeros;
 };
 
 // Lane l of chunk w holds block 31 w - 1 + l (lane 0: the block before the chunk).
-__device__ __forceinline__ LaneBlock load_chunk(const int32_t *__restrict__ q, const Geometry &G, int ch, int64_t w,
-                                                const int32_t *__restrict__ lastnz_ch, uint32_t *smem)
+__device__ __forceinline__ LaneBlock lane_block(const uint2 *__restrict__ ev, const Geometry &G, int ch, int64_t w,
+                                                const ChanInfo &I)
 {
     const int lane = threadIdx.x & 31;
-    uint32_t *s_rows = smem;
-    uint32_t *s_mask = smem + 32 * ROW_PITCH;
-    const int32_t *src = q + (size_t)ch * G.ld;
-    const int64_t sym0 = (w * CHUNK_LANES - 1) * BLOCK_SYMS;
-    __syncwarp();
-    for (int b = 0; b < 32; ++b) {
-        const int64_t s0 = sym0 + (int64_t)b * BLOCK_SYMS;
-        uint32_t u[MASK_WORDS];
-#pragma unroll
-        for (int wd = 0; wd < MASK_WORDS; ++wd) {
-            const int64_t i = s0 + 32 * wd + lane;
-            const int32_t v = (i >= 0 && i < G.n) ? src[i] : 0;
-            u[wd] = G.flag_signed ? s2u(v) : (uint32_t)v;
-        }
-#pragma unroll
-        for (int wd = 0; wd < MASK_WORDS; ++wd) {
-            s_rows[b * ROW_PITCH + 32 * wd + lane] = u[wd];
-            const unsigned m = __ballot_sync(~0u, u[wd] != 0);
-            if (lane == wd) s_mask[b * MASK_WORDS + wd] = m;
-        }
-    }
-    __syncwarp();
     LaneBlock B;
-    const int64_t blk = w * CHUNK_LANES - 1 + lane;
-    const int64_t start = blk * BLOCK_SYMS;
-    B.row = s_rows + lane * ROW_PITCH;
-    B.mask = s_mask + lane * MASK_WORDS;
-    int64_t len = (blk < 0) ? 0 : G.n - start;
-    len = len < 0 ? 0 : (len > BLOCK_SYMS ? BLOCK_SYMS : len);
-    B.len = (int)len;
-    B.zeros_before = (blk <= 0 || len == 0) ? 0u : (uint32_t)(start - 1 - (int64_t)lastnz_ch[blk - 1]);
-    B.is_tail = len > 0 && start + len == G.n;
-    B.last_nz = -1;
-    uint32_t nz = 0;
-    for (int wd = 0; wd < MASK_WORDS; ++wd) {
-        const uint32_t m = B.mask[wd];
-        nz += __popc(m);
-        if (m) B.last_nz = 32 * wd + 31 - __clz((int)m);
-    }
-    for (int o = 16; o; o >>= 1) nz += __shfl_xor_sync(~0u, nz, o);
-    B.dense = nz * 4 >= (uint32_t)(CHUNK_LANES * BLOCK_SYMS);   // >= 25 % non-zero: the per-symbol form is cheaper
-    B.single = nz * 2 >= (uint32_t)(CHUNK_LANES * BLOCK_SYMS);
+    B.base = (const uint4 *)(ev + ((size_t)ch * G.W + w) * CHUNK_SLOTS);
+    const int64_t b = w * CHUNK_LANES - 1 + lane;
+    int64_t cnt = (b < 0 || b >= (int64_t)I.nblocks) ? 0 : (int64_t)I.events - b * EV_BLOCK;
+    cnt = cnt < 0 ? 0 : (cnt > EV_BLOCK ? EV_BLOCK : cnt);
+    B.cnt = (int)cnt;
+    B.is_tail = b == (int64_t)I.nblocks - 1;
+    B.tail_zeros = I.tail_zeros;
     return B;
 }
 
-// Exact solution of a chunk given the states at the start of lane 1 (pin == true: lane 0 just forwards
-// `first`) or a warm-up of lane 0's block from `first` (pin == false).  On return, for each candidate c:
-// in[c] = state at the start of this lane's block, out[c] = state after it, bits[c] = code length of it.
-// Blocks without events (and without the tail) leave the state alone, so every lane takes its start
-// state from the nearest earlier lane that has events: a correction crosses empty blocks in one round.
-// Returns true when no lane of the chunk (1..31) codes anything: the chunk is the identity on the state.
-__device__ __forceinline__ bool solve_chunk(const LaneBlock &B, bool pin, const State first[NCAND], State in[NCAND],
-                                            State out[NCAND], uint32_t bits[NCAND], int *rounds)
+// Code lengths of the lane's block for NC candidate start states side by side (independent chains).  s[] in/out.
+template <int NC> __device__ __forceinline__ void count_lane(const LaneBlock &B, State *s, uint32_t *bits)
 {
     const int lane = threadIdx.x & 31;
-    bool has = B.is_tail;
-    for (int w = 0; w < MASK_WORDS; ++w) has |= B.mask[w] != 0;
-    if (lane == 0) has = !pin && has;                       // a pinned lane 0 only forwards `first`
+    bool quirk[NC];
+#pragma unroll
+    for (int c = 0; c < NC; ++c) { bits[c] = 0; quirk[c] = false; }
+    const int units = (B.cnt + EV_GROUP - 1) / EV_GROUP;
+    for (int j = 0; j < units; ++j) {
+        const uint4 a = __ldg(B.base + (j * 32 + lane) * 2);
+        const uint4 b = __ldg(B.base + (j * 32 + lane) * 2 + 1);
+        const uint32_t g[4] = {a.x, a.z, b.x, b.z}, u[4] = {a.y, a.w, b.y, b.w};
+#pragma unroll
+        for (int t = 0; t < 4; ++t)
+            if (j * EV_GROUP + t < B.cnt) {
+#pragma unroll
+                for (int c = 0; c < NC; ++c) quirk[c] = count_event(s[c], g[t], u[t], bits[c]);
+            }
+    }
+    if (B.is_tail) {
+#pragma unroll
+        for (int c = 0; c < NC; ++c) {
+            CountSink k{0};
+            code_tail(s[c], B.tail_zeros, quirk[c], k);
+            bits[c] += k.bits;
+        }
+    }
+}
+
+// ---- one chunk: speculative block states made consistent lane to lane -----------------------------------------
+// Every lane carries NC candidate start states of its block with the end state and code length under each
+// (NC = 1 for channels that are mostly non-zero: they re-synchronise through k_P = 0 within a block; NC = 8 = the
+// state classes of rlgr_core.cuh::expand_classes otherwise).  pin == false (speculation): lane 0 codes the block
+// before the chunk as warm-up; pin == true (chunk 0, repair): lane 0 forwards the known state at the chunk start
+// and lane 1 keeps it.  Round 1: every other lane codes its block from the canonical states.  After round 1 a lane
+// takes the classes around its predecessor's end states as candidates; later, a lane whose predecessor ended in a
+// state that is not among its candidates takes the predecessor's end states (results of states it already knows
+// are kept).  Candidates are LINKED, not index-matched: candidate c of a lane continues in whichever candidate of
+// the next lane equals its end state, so a chain may change slots from lane to lane, and only one chain has to be
+// complete: a candidate of the wrong class never re-synchronises (its chain would need one round per lane), the
+// right one merges with the true trajectory within a few events.  The rounds stop when the pinned chain (pin) /
+// any chain (speculation) reaches the last lane, or after max_rounds; chains that are incomplete then are marked
+// invalid.  With pin the true state advances at least one lane per round: 33 rounds always complete the chain.
+constexpr uint32_t STATE_INVALID = 0xffffu;
+constexpr int SEL_NONE = 15;
+
+template <int NC> struct ChunkSol {
+    uint32_t in[NC], out[NC];       // packed states
+    uint32_t bits[NC];
+    uint32_t sel;                   // nibble c: this lane's candidate on the chain of chunk candidate c (15: broken)
+    unsigned complete;              // warp-uniform mask: chain c reaches the last lane
+    uint32_t end[NC], total[NC];    // warp-uniform: packed state after the chunk / code length of the chunk on chain c
+    int rounds;
+};
+
+template <int NC> __device__ __forceinline__ void recode(const LaneBlock &B, ChunkSol<NC> &S, unsigned dirty)
+{
+    if (!dirty) return;
+    if (NC == 1) {
+        State t[1] = {unpack_state(S.in[0])};
+        uint32_t b[1];
+        count_lane<1>(B, t, b);
+        S.out[0] = pack_state(t[0]);
+        S.bits[0] = b[0];
+        return;
+    }
+    // the distinct states among the dirty candidates, coded side by side
+    uint32_t ds[NC];
+    int rep[NC], m = 0;
+    for (int c = 0; c < NC; ++c) {
+        rep[c] = 0;
+        if (!(dirty >> c & 1)) continue;
+        int k = 0;
+        while (k < m && ds[k] != S.in[c]) ++k;
+        if (k == m) ds[m++] = S.in[c];
+        rep[c] = k;
+    }
+    State t[NC];
+    uint32_t b[NC];
+    for (int k = 0; k < NC; ++k) t[k] = unpack_state(ds[k < m ? k : 0]);
+    if (m == 1) count_lane<1>(B, t, b);
+    else if (m == 2) count_lane<(NC >= 2 ? 2 : 1)>(B, t, b);
+    else if (m <= 4) count_lane<(NC >= 4 ? 4 : 1)>(B, t, b);
+    else count_lane<NC>(B, t, b);
+    for (int c = 0; c < NC; ++c)
+        if (dirty >> c & 1) { S.out[c] = pack_state(t[rep[c]]); S.bits[c] = b[rep[c]]; }
+}
+
+// chains from lane 1's candidates through the lanes in order (src skips the lanes without a block)
+template <int NC> __device__ __forceinline__ void walk_chains(ChunkSol<NC> &S, bool has, int src)
+{
+    const int lane = threadIdx.x & 31;
+    uint32_t from = 0;               // nibble c: my candidate that continues candidate c of my predecessor
+    for (int c = 0; c < NC; ++c) {
+        const uint32_t o = __shfl_sync(~0u, S.out[c], src);
+        int f = SEL_NONE;
+        for (int k = NC - 1; k >= 0; --k) if (S.in[k] == o) f = k;
+        if (!has) f = c;
+        from |= (uint32_t)f << (4 * c);
+    }
+    uint32_t sel = 0;
+    for (int c = 0; c < NC; ++c) sel |= (uint32_t)(lane == 1 ? c : SEL_NONE) << (4 * c);
+    for (int step = 2; step < 32; ++step) {
+        const uint32_t p = __shfl_sync(~0u, sel, src);
+        if (lane == step) {
+            sel = 0;
+            for (int c = 0; c < NC; ++c) {
+                const int pc = (int)(p >> (4 * c)) & 15;
+                sel |= (uint32_t)(pc == SEL_NONE ? SEL_NONE : (int)(from >> (4 * pc)) & 15) << (4 * c);
+            }
+        }
+    }
+    S.sel = sel;
+    S.complete = 0;
+    for (int c = 0; c < NC; ++c) {
+        const int sc = (int)(sel >> (4 * c)) & 15;
+        const unsigned broken = __ballot_sync(~0u, sc == SEL_NONE) & ~1u;          // lanes 1..31
+        if (!broken) S.complete |= 1u << c;
+        uint32_t b = 0, e = 0;
+        for (int k = 0; k < NC; ++k) if (k == sc) { b = S.bits[k]; e = S.out[k]; }
+        if (lane == 0) b = 0;                                                     // the warm-up block belongs to the previous chunk
+        for (int o = 16; o; o >>= 1) b += __shfl_xor_sync(~0u, b, o);
+        S.total[c] = b;
+        S.end[c] = __shfl_sync(~0u, e, 31);
+    }
+}
+
+template <int NC>
+__device__ __forceinline__ void solve_chunk(const LaneBlock &B, bool pin, State pinned, int max_rounds, ChunkSol<NC> &S)
+{
+    const int lane = threadIdx.x & 31;
+    bool has = B.cnt > 0 || B.is_tail;
+    if (lane == 0) has = !pin && has;                       // a pinned lane 0 only forwards the known state
     const unsigned active = __ballot_sync(~0u, has);
     const unsigned before = active & lanemask_lt();
     const int src = before ? 31 - __clz((int)before) : 0;  // nearest earlier lane that changes the state
-    for (int c = 0; c < NCAND; ++c) { in[c] = first[c]; out[c] = first[c]; bits[c] = 0; }
-    bool need = has;
+    State canon[2];
+    canon[0] = initial_state();
+    canon[1].kP = 9;                                        // run mode, the other k_P parity
+    canon[1].kRP = RL_KRP_INIT;
+    for (int c = 0; c < NC; ++c) {
+        S.in[c] = (pin && lane < 2) ? pack_state(pinned) : pack_state(canon[c < NC / 2 ? 0 : 1]);
+        S.out[c] = S.in[c];
+        S.bits[c] = 0;
+    }
+    unsigned dirty = has ? (1u << NC) - 1 : 0u;
     int r = 0;
-    for (; r < 34; ++r) {
-        if (need) {
-            if (B.dense) {
-                for (int c = 0; c < NCAND; ++c) out[c] = in[c];
-                if (in[1] == in[0]) {
-                    count_block_dense<1>(B.row, B.len, B.last_nz, B.zeros_before, B.is_tail, out, bits);
-                    out[1] = out[0];
-                    bits[1] = bits[0];
-                } else {
-                    count_block_dense<NCAND>(B.row, B.len, B.last_nz, B.zeros_before, B.is_tail, out, bits);
+    for (;;) {
+        recode<NC>(B, S, dirty);
+        ++r;
+        dirty = 0;
+        uint32_t o[NC];
+        for (int c = 0; c < NC; ++c) o[c] = __shfl_sync(~0u, S.out[c], src);
+        if (lane > 0 && !has)
+            for (int c = 0; c < NC; ++c) S.in[c] = S.out[c] = o[c];             // no block: pass the states through
+        if (r >= 2) {
+            walk_chains<NC>(S, has, src);
+            if (pin ? (S.complete & 1u) : (S.complete != 0)) break;
+        }
+        if (lane > 0 && has && r < max_rounds && !(pin && lane == 1)) {
+            uint32_t nw[NC];
+            bool replace = false;
+            bool expanded = false;
+            if constexpr (NC == 8) {
+                if (r == 1) {                              // the classes around the predecessor's end states
+                    expand_classes(unpack_state(o[0]), unpack_state(o[NC / 2]), nw);
+                    replace = expanded = true;
                 }
-            } else {
-                for (int c = 0; c < NCAND; ++c) {
-                    if (c > 0 && in[c] == in[0]) { out[c] = out[0]; bits[c] = bits[0]; continue; }
-                    State s = in[c];
-                    CountSink k{0};
-                    code_block(B.row, B.len, B.mask, B.zeros_before, B.is_tail, s, k);
-                    out[c] = s;
-                    bits[c] = k.bits;
+            }
+            if (!expanded && !(NC > 1 && lane == 1)) {           // (lane 1's candidates are the chunk's: fixed after the expansion)
+                for (int c = 0; c < NC; ++c) {
+                    bool cov = false;
+                    for (int k = 0; k < NC; ++k) cov |= o[c] == S.in[k];
+                    replace |= !cov;
+                    nw[c] = o[c];
+                }
+            }
+            if (replace) {
+                uint32_t oin[NC], oout[NC], obits[NC];
+                for (int c = 0; c < NC; ++c) { oin[c] = S.in[c]; oout[c] = S.out[c]; obits[c] = S.bits[c]; }
+                for (int c = 0; c < NC; ++c) {
+                    int m = -1;
+                    for (int k = NC - 1; k >= 0; --k) if (nw[c] == oin[k]) m = k;
+                    S.in[c] = nw[c];
+                    if (m >= 0) { S.out[c] = oout[m]; S.bits[c] = obits[m]; }
+                    else dirty |= 1u << c;
                 }
             }
         }
-        need = false;
-        for (int c = 0; c < NCAND; ++c) {
-            const uint32_t prev = __shfl_sync(~0u, pack_state(out[c]), src);
-            if (lane > 0 && prev != pack_state(in[c])) {
-                in[c] = unpack_state(prev);
-                if (has) need = true;
-                else out[c] = in[c];
-            }
+        if (!__any_sync(~0u, dirty != 0)) {
+            if (r < 2) walk_chains<NC>(S, has, src);
+            break;
         }
-        if (!__any_sync(~0u, need)) break;
     }
-    // lanes without events behind the last correction: forward once more so that in == out == source's out
-    for (int c = 0; c < NCAND; ++c) {
-        const uint32_t prev = __shfl_sync(~0u, pack_state(out[c]), src);
-        if (lane > 0 && !has) { in[c] = unpack_state(prev); out[c] = in[c]; }
-    }
-    if (lane == 0) { bits[0] = 0; bits[1] = 0; }           // the warm-up block belongs to the previous chunk
-    if (rounds) *rounds = r + 1;
-    return (active & ~1u) == 0;
+    S.rounds = r;
 }
 
 // ---- records -----------------------------------------------------------------------------------------------
-// chunk record (uint4): x = cand0 | cand1 << 16 (assumed states at the chunk start), y = end0 | end1 << 16,
-//                       z = bits0, w = bits1 (code length of the chunk under each candidate)
-// lane record  (uint2): x = start0 | start1 << 16, y = bits0 | bits1 << 16      (bits of a block < 2^16)
-// chunk offset (u64)  : bit offset of the chunk in its stream << 1 | chosen candidate
-// sync index   (uint4): x,y = bit offset (lo, hi), z = first symbol coded at that offset, w = packed state
-__device__ __forceinline__ uint32_t warp_sum(uint32_t v)
-{
-    for (int o = 16; o; o >>= 1) v += __shfl_xor_sync(~0u, v, o);
-    return v;
-}
+// chunk record (4 x uint4): [0] candidates (8 x 16 bit: assumed states at the chunk start, 0xffff: chain incomplete),
+//                           [1] end states (8 x 16 bit), [2], [3] code length of the chunk on each chain (8 x 32 bit)
+// lane record  (3 x uint4): [0] the lane's 8 candidates (16 bit each), [1] code lengths of its block (8 x 16 bit),
+//                           [2].x nibble c = the lane's candidate on the chain of chunk candidate c
+// chunk offset (u64)      : bit offset of the chunk in its stream << 3 | chosen chunk candidate
+// sync index   (uint2)    : x = bit offset (low 32), y = offset bits 32..38 | k_P << 7 | k_RP << 14 | first << 22
+constexpr int REC_WORDS = 4, LANEREC_WORDS = 3;
 
-constexpr uint32_t REC_IDENTITY = 0x80000000u;     // in rec.z: no lane of the chunk codes anything
-
-__device__ __forceinline__ uint4 finish_chunk(const State in[NCAND], const State out[NCAND], const uint32_t bits[NCAND],
-                                              bool identity, uint2 *lanerec)
+template <int NC> __device__ __forceinline__ void finish_chunk(const ChunkSol<NC> &S, uint4 *rec, uint4 *lanerec)
 {
     const int lane = threadIdx.x & 31;
-    lanerec[lane] = make_uint2(pack_state(in[0]) | (pack_state(in[1]) << 16), bits[0] | (bits[1] << 16));
-    uint4 rec;
-    rec.x = __shfl_sync(~0u, pack_state(in[0]) | (pack_state(in[1]) << 16), 1);
-    rec.y = __shfl_sync(~0u, pack_state(out[0]) | (pack_state(out[1]) << 16), 31);
-    rec.z = warp_sum(bits[0]) | (identity ? REC_IDENTITY : 0u);
-    rec.w = warp_sum(bits[1]);
-    return rec;
+    uint32_t in16[4] = {0, 0, 0, 0}, b16[4] = {0, 0, 0, 0};
+    uint32_t cand16[4] = {~0u, ~0u, ~0u, ~0u}, end16[4] = {0, 0, 0, 0}, tot[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+    for (int c = 0; c < NC; ++c) {
+        in16[c >> 1] |= (S.in[c] & 0xffffu) << (16 * (c & 1));
+        b16[c >> 1] |= (S.bits[c] & 0xffffu) << (16 * (c & 1));
+        const uint32_t l1 = __shfl_sync(~0u, S.in[c], 1);
+        const uint32_t cand = (S.complete >> c & 1) ? l1 : STATE_INVALID;
+        cand16[c >> 1] = (cand16[c >> 1] & ~(0xffffu << (16 * (c & 1)))) | (cand << (16 * (c & 1)));
+        end16[c >> 1] |= (S.end[c] & 0xffffu) << (16 * (c & 1));
+        tot[c] = S.total[c];
+    }
+    uint4 *lr = lanerec + (size_t)lane * LANEREC_WORDS;
+    lr[0] = make_uint4(in16[0], in16[1], in16[2], in16[3]);
+    lr[1] = make_uint4(b16[0], b16[1], b16[2], b16[3]);
+    lr[2] = make_uint4(S.sel, 0u, 0u, 0u);
+    if (lane == 0) {
+        rec[0] = make_uint4(cand16[0], cand16[1], cand16[2], cand16[3]);
+        rec[1] = make_uint4(end16[0], end16[1], end16[2], end16[3]);
+        rec[2] = make_uint4(tot[0], tot[1], tot[2], tot[3]);
+        rec[3] = make_uint4(tot[4], tot[5], tot[6], tot[7]);
+    }
 }
 
-// the two canonical start states of a warm-up block: the coder's initial state and a run-mode state of
-// the other k_P parity (sparse channels never leave run mode, where differences in k_P keep their parity)
-__device__ __forceinline__ void canonical_states(State c[NCAND])
-{
-    c[0] = initial_state();
-    c[1].kP = 9;
-    c[1].kRP = RL_KRP_INIT;
-}
+// channels that are mostly non-zero run with one candidate (they re-synchronise through k_P = 0 within a block)
+__device__ __forceinline__ bool channel_is_dense(const ChanInfo &I, const Geometry &G) { return (int64_t)I.events * 2 >= G.n; }
 
 // ---- A: speculate ----------------------------------------------------------------------------------------
-// sweep 0: warm-up from canonical states.  sweep > 0: start from the end states chunk w-1 reported in the
-// previous sweep (prev records); a chunk whose assumption did not change just copies its record.
-__global__ void __launch_bounds__(32) rlgr_speculate_kernel(const int32_t *__restrict__ q, Geometry G,
-                                                            const int32_t *__restrict__ lastnz, int sweep,
-                                                            const uint4 *__restrict__ rec_prev, uint4 *__restrict__ rec_cur,
-                                                            uint2 *__restrict__ lanerec, unsigned long long *stats)
+constexpr int SPEC_WARPS = 4;
+constexpr int SPEC_ROUNDS = 4;       // speculation: a chain that is not complete by then is left invalid
+constexpr int PIN_ROUNDS = 34;       // chunk 0 and repairs: the pinned chain always completes
+
+template <int NC>
+__global__ void __launch_bounds__(32 * SPEC_WARPS) rlgr_speculate_kernel(Geometry G, const ChanInfo *__restrict__ info,
+                                                                        const uint2 *__restrict__ ev, uint4 *__restrict__ rec,
+                                                                        uint4 *__restrict__ lanerec, unsigned long long *stats)
 {
-    extern __shared__ uint32_t rl_smem[];
     const int ch = blockIdx.y;
-    const int64_t w = blockIdx.x;
-    const size_t ci = (size_t)ch * G.nchunks + w;
-    State first[NCAND];
-    bool pin;
-    if (w == 0) {
-        first[0] = first[1] = initial_state();
-        pin = true;
-        if (sweep > 0) { if (threadIdx.x == 0) rec_cur[ci] = rec_prev[ci]; return; }
-    } else if (sweep == 0) {
-        canonical_states(first);
-        pin = false;
-    } else {
-        const uint4 mine = rec_prev[ci];
-        const uint32_t guess = rec_prev[ci - 1].y;
-        if (guess == mine.x || (mine.z & REC_IDENTITY)) { if (threadIdx.x == 0) rec_cur[ci] = mine; return; }
-        first[0] = unpack_state(guess & 0xffff);
-        first[1] = unpack_state(guess >> 16);
-        pin = true;
-    }
-    const LaneBlock B = load_chunk(q, G, ch, w, lastnz + (size_t)ch * G.nblk, rl_smem);
-    // mostly non-zero chunks re-synchronise through k_P = 0 whatever the parity: one canonical state is enough
-    if (sweep == 0 && B.single) first[1] = first[0];
-    State in[NCAND], out[NCAND];
-    uint32_t bits[NCAND];
-    int rounds;
-    const bool identity = solve_chunk(B, pin, first, in, out, bits, &rounds);
-    const uint4 rec = finish_chunk(in, out, bits, identity, lanerec + ci * 32);
-    if (threadIdx.x == 0) {
-        rec_cur[ci] = rec;
-        if (stats) { atomicAdd(stats + 0, 1ull); atomicAdd(stats + 1, (unsigned long long)rounds); }
+    const int64_t w = (int64_t)blockIdx.x * SPEC_WARPS + (threadIdx.x >> 5);
+    const ChanInfo I = info[ch];
+    if (w >= (int64_t)I.nchunks || channel_is_dense(I, G) != (NC == 1)) return;
+    const size_t ci = (size_t)ch * G.W + w;
+    const LaneBlock B = lane_block(ev, G, ch, w, I);
+    ChunkSol<NC> S;
+    const long long t0 = clock64();
+    solve_chunk<NC>(B, w == 0, initial_state(), w == 0 ? PIN_ROUNDS : SPEC_ROUNDS, S);
+    finish_chunk<NC>(S, rec + ci * REC_WORDS, lanerec + ci * 32 * LANEREC_WORDS);
+    if ((threadIdx.x & 31) == 0 && stats) {
+        atomicAdd(stats + 0, 1ull);
+        atomicAdd(stats + 1, (unsigned long long)S.rounds);
+        // slowest chunk of the pass: cycles << 24 | channel << 8 | rounds
+        atomicMax(stats + 3, ((unsigned long long)(clock64() - t0) << 24) | ((unsigned long long)(ch & 0xffff) << 8) | (unsigned)S.rounds);
     }
 }
 
 // ---- B: resolve ------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(32) rlgr_resolve_kernel(const int32_t *__restrict__ q, Geometry G,
-                                                          const int32_t *__restrict__ lastnz, uint4 *__restrict__ rec,
-                                                          uint2 *__restrict__ lanerec, unsigned long long *__restrict__ chunkoff,
+__device__ __forceinline__ uint32_t half_of(const uint4 &v, int c)       // 16-bit entry c of 8
+{
+    const uint32_t w = (c >> 1) == 0 ? v.x : (c >> 1) == 1 ? v.y : (c >> 1) == 2 ? v.z : v.w;
+    return (w >> (16 * (c & 1))) & 0xffffu;
+}
+__device__ __forceinline__ uint32_t word_of(const uint4 &a, const uint4 &b, int c)   // 32-bit entry c of 8
+{
+    const uint4 &v = c < 4 ? a : b;
+    return (c & 3) == 0 ? v.x : (c & 3) == 1 ? v.y : (c & 3) == 2 ? v.z : v.w;
+}
+
+__global__ void __launch_bounds__(32) rlgr_resolve_kernel(Geometry G, const ChanInfo *__restrict__ info,
+                                                          const uint2 *__restrict__ ev, uint4 *__restrict__ rec,
+                                                          uint4 *__restrict__ lanerec, unsigned long long *__restrict__ chunkoff,
                                                           int64_t slot_bytes, int64_t *__restrict__ nbytes,
                                                           unsigned long long *__restrict__ totals, int32_t *status,
                                                           unsigned long long *stats)
 {
-    extern __shared__ uint32_t rl_smem[];
     const int ch = blockIdx.x;
     const int lane = threadIdx.x & 31;
-    const int32_t *lastnz_ch = lastnz + (size_t)ch * G.nblk;
+    const ChanInfo I = info[ch];
+    const int64_t nchunks = I.nchunks;
+    const bool dense = channel_is_dense(I, G);
     State s = initial_state();
     unsigned long long off = 0;
-    unsigned long long repairs = 0;
-    for (int64_t base = 0; base < G.nchunks; base += 32) {
-        const int64_t w = base + lane;
-        const size_t ci = (size_t)ch * G.nchunks + w;
-        uint4 r = make_uint4(0, 0, 0, 0);
-        if (w < G.nchunks) r = rec[ci];
-        unsigned long long my_off = 0;
-        const int cnt = (int)min((int64_t)32, G.nchunks - base);
-        for (int i = 0; i < cnt; ++i) {
-            const uint32_t cand = __shfl_sync(~0u, r.x, i);
-            uint32_t ends = __shfl_sync(~0u, r.y, i);
-            uint32_t b0 = __shfl_sync(~0u, r.z, i), b1 = __shfl_sync(~0u, r.w, i);
-            const uint32_t ps = pack_state(s);
-            if (b0 & REC_IDENTITY) {                             // nothing coded in this chunk: state and offset pass through
-                if (lane == i) my_off = off << 1;
-                continue;
+    unsigned long long repairs = 0, repair_rounds = 0;
+    for (int64_t base = 0; base < nchunks; base += 32) {
+      // lane l holds the record of chunk base + l; the chunks are then walked in order with shuffles
+      const int64_t mine = base + lane < nchunks ? base + lane : nchunks - 1;
+      const uint4 *mr = rec + ((size_t)ch * G.W + mine) * REC_WORDS;
+      uint4 m0 = mr[0], m1 = mr[1], m2 = mr[2], m3 = mr[3];
+      const int cnt = (int)min((int64_t)32, nchunks - base);
+      for (int i = 0; i < cnt; ++i) {
+        const int64_t w = base + i;
+        const size_t ci = (size_t)ch * G.W + w;
+        uint4 r0;                                                 // the 8 candidates of chunk w (every lane)
+        r0.x = __shfl_sync(~0u, m0.x, i); r0.y = __shfl_sync(~0u, m0.y, i);
+        r0.z = __shfl_sync(~0u, m0.z, i); r0.w = __shfl_sync(~0u, m0.w, i);
+        const uint32_t ps = pack_state(s);
+        unsigned hit = __ballot_sync(~0u, lane < 8 && half_of(r0, lane & 7) == ps);
+        if (!hit) {                                               // no candidate was the true state: solve this chunk from it
+            const LaneBlock B = lane_block(ev, G, ch, w, I);
+            uint4 *lr = lanerec + ci * 32 * LANEREC_WORDS;
+            int rounds;
+            if (dense) {
+                ChunkSol<1> S;
+                solve_chunk<1>(B, true, s, PIN_ROUNDS, S);
+                finish_chunk<1>(S, rec + ci * REC_WORDS, lr);
+                rounds = S.rounds;
+            } else {
+                ChunkSol<8> S;
+                solve_chunk<8>(B, true, s, PIN_ROUNDS, S);
+                finish_chunk<8>(S, rec + ci * REC_WORDS, lr);
+                rounds = S.rounds;
             }
-            int b = (ps == (cand & 0xffff)) ? 0 : (ps == (cand >> 16)) ? 1 : -1;
-            if (b < 0) {                                          // assumption failed: solve this chunk exactly
-                const LaneBlock B = load_chunk(q, G, ch, base + i, lastnz_ch, rl_smem);
-                State first[NCAND] = {s, s}, in[NCAND], out[NCAND];
-                uint32_t bits[NCAND];
-                solve_chunk(B, true, first, in, out, bits, nullptr);
-                const uint4 fixed = finish_chunk(in, out, bits, false, lanerec + ((size_t)ch * G.nchunks + base + i) * 32);
-                if (lane == i) r = fixed;
-                ends = fixed.y; b0 = fixed.z; b1 = fixed.w;
-                b = 0;
-                ++repairs;
-            }
-            if (lane == i) my_off = (off << 1) | (unsigned)b;
-            off += b ? b1 : b0;
-            s = unpack_state(b ? (ends >> 16) : (ends & 0xffff));
+            __syncwarp();
+            if (lane == i) { m0 = mr[0]; m1 = mr[1]; m2 = mr[2]; m3 = mr[3]; }      // (written by lane 0 just above)
+            hit = 1u;                                             // the pinned chain is candidate 0
+            ++repairs;
+            repair_rounds += (unsigned long long)rounds;
         }
-        if (w < G.nchunks) chunkoff[ci] = my_off;
+        const int b = __ffs((int)hit) - 1;
+        if (lane == 0) chunkoff[ci] = (off << 3) | (unsigned)b;
+        off += __shfl_sync(~0u, word_of(m2, m3, b), i);
+        s = unpack_state(__shfl_sync(~0u, half_of(m1, b), i));
+      }
     }
     if (lane == 0) {
         const int64_t nb = (int64_t)((off + 7) >> 3);
         nbytes[ch] = nb;
         totals[ch] = off;
         if (nb > slot_bytes && status) atomicOr(status, RAHT_ST_STREAM_OVERFLOW);
-        if (stats) atomicAdd(stats + 2, repairs);
+        if (stats) { atomicAdd(stats + 2, repairs); atomicAdd(stats + 4, repair_rounds); }
     }
 }
 
@@ -403,6 +595,7 @@ struct BitSink {
         shared_word = nb != 0;
         overflow = false;
     }
+    __device__ __forceinline__ unsigned long long bit_pos() const { return ((unsigned long long)wi << 5) + nb; }
     __device__ __forceinline__ void flush_word(uint32_t w, bool shared)
     {
         if (wi < cap_words) {
@@ -428,52 +621,62 @@ struct BitSink {
     }
 };
 
-__global__ void __launch_bounds__(32) rlgr_emit_kernel(const int32_t *__restrict__ q, Geometry G,
-                                                       const int32_t *__restrict__ lastnz, const uint2 *__restrict__ lanerec,
-                                                       const unsigned long long *__restrict__ chunkoff,
-                                                       uint8_t *__restrict__ streams, int64_t slot_bytes,
-                                                       uint2 *__restrict__ sync_index, int32_t *status)
+__global__ void __launch_bounds__(32 * SPEC_WARPS) rlgr_emit_kernel(Geometry G, const ChanInfo *__restrict__ info,
+                                                                   const uint2 *__restrict__ ev,
+                                                                   const uint32_t *__restrict__ blockpos,
+                                                                   const uint4 *__restrict__ lanerec,
+                                                                   const unsigned long long *__restrict__ chunkoff,
+                                                                   uint8_t *__restrict__ streams, int64_t slot_bytes,
+                                                                   uint2 *__restrict__ sync_index, int64_t sync_entries,
+                                                                   int32_t *status)
 {
-    extern __shared__ uint32_t rl_smem[];
     const int ch = blockIdx.y;
-    const int64_t w = blockIdx.x;
+    const int64_t w = (int64_t)blockIdx.x * SPEC_WARPS + (threadIdx.x >> 5);
     const int lane = threadIdx.x & 31;
-    const size_t ci = (size_t)ch * G.nchunks + w;
-    const LaneBlock B = load_chunk(q, G, ch, w, lastnz + (size_t)ch * G.nblk, rl_smem);
+    const ChanInfo I = info[ch];
+    if (w >= (int64_t)I.nchunks) return;
+    const size_t ci = (size_t)ch * G.W + w;
+    const LaneBlock B = lane_block(ev, G, ch, w, I);
     const unsigned long long co = chunkoff[ci];
-    const int b = (int)(co & 1);
-    const uint2 lr = lanerec[ci * 32 + lane];
-    State s = unpack_state(b ? (lr.x >> 16) : (lr.x & 0xffff));
-    const uint32_t mybits = lane == 0 ? 0u : (b ? (lr.y >> 16) : (lr.y & 0xffff));
-    uint32_t x = mybits;                                   // exclusive prefix over the lanes
+    const int cb = (int)(co & 7);
+    const uint4 *lr = lanerec + (ci * 32 + lane) * LANEREC_WORDS;
+    const int sel = (int)((lr[2].x >> (4 * cb)) & 7);      // this lane's candidate on the chosen chain
+    State s = unpack_state(half_of(lr[0], sel));
+    const uint32_t mybits = lane == 0 ? 0u : half_of(lr[1], sel);
+    uint32_t x = mybits;                                   // inclusive prefix over the lanes
     for (int o = 1; o < 32; o <<= 1) {
         uint32_t y = __shfl_up_sync(~0u, x, o);
         if (lane >= o) x += y;
     }
-    const unsigned long long begin = (co >> 1) + (x - mybits);
-    if (sync_index) {
-        // sync entry of lanes 1+4k..4+4k: where (bit offset, state) the coder stands before the range's first
-        // event and where that event's non-zero symbol sits.  Lanes without events have no bits and pass the
-        // state through, so the leader lane's (begin, s) are those of the first lane with an event.
-        uint32_t fn = SYNC_NONE;
-        for (int wd = MASK_WORDS - 1; wd >= 0; --wd)
-            if (B.mask[wd]) fn = (uint32_t)(32 * wd + __ffs((int)B.mask[wd]) - 1);
-        uint32_t first = fn;
-        for (int o = 1; o < SYNC_STRIDE; ++o) {                   // nearest lane with an event wins
-            const uint32_t f = __shfl_down_sync(~0u, fn, o);
-            if (first == SYNC_NONE && lane + o < 32 && f != SYNC_NONE) first = (uint32_t)(o * BLOCK_SYMS) + f;
-        }
-        if (lane >= 1 && ((lane - 1) % SYNC_STRIDE) == 0) {
-            const int k = (lane - 1) / SYNC_STRIDE;
-            const uint32_t hi = (uint32_t)((begin >> 32) & 0x7f) | ((uint32_t)(s.kP & 0x7f) << 7) | ((uint32_t)(s.kRP & 0xff) << 14) |
-                                (first << 22);
-            sync_index[ci * SYNC_PER_CHUNK + k] = make_uint2((uint32_t)begin, hi);
-        }
-    }
+    const unsigned long long begin = (co >> 3) + (x - mybits);
     if (lane == 0 || mybits == 0) return;
     BitSink sink;
     sink.init(streams + (size_t)ch * slot_bytes, slot_bytes, begin);
-    code_block(B.row, B.len, B.mask, B.zeros_before, B.is_tail, s, sink);
+    uint2 *sync = sync_index ? sync_index + (size_t)ch * sync_entries : nullptr;
+    int64_t pos = -1;                                      // symbol index of the previous event
+    bool quirk = false;
+    const int units = (B.cnt + EV_GROUP - 1) / EV_GROUP;
+    for (int j = 0; j < units; ++j) {
+        const uint4 a = __ldg(B.base + (j * 32 + lane) * 2);
+        const uint4 b = __ldg(B.base + (j * 32 + lane) * 2 + 1);
+        const uint32_t g[4] = {a.x, a.z, b.x, b.z}, u[4] = {a.y, a.w, b.y, b.w};
+        if (j == 0) pos = (int64_t)blockpos[(size_t)ch * G.nsb + w * CHUNK_LANES - 1 + lane] - (int64_t)g[0] - 1;
+#pragma unroll
+        for (int t = 0; t < 4; ++t)
+            if (j * EV_GROUP + t < B.cnt) {
+                const int64_t np = pos + (int64_t)g[t] + 1;
+                if (sync && (np >> SYNC_SHIFT) != (pos >> SYNC_SHIFT)) {
+                    // first event of its 512-symbol range: where (bit offset, state) the coder stands before it
+                    const unsigned long long at = sink.bit_pos();
+                    const uint32_t hi = (uint32_t)((at >> 32) & 0x7f) | ((uint32_t)(s.kP & 0x7f) << 7) |
+                                        ((uint32_t)(s.kRP & 0xff) << 14) | ((uint32_t)(np & (SYNC_RANGE - 1)) << 22);
+                    sync[np >> SYNC_SHIFT] = make_uint2((uint32_t)at, hi);
+                }
+                pos = np;
+                quirk = emit_event(s, g[t], u[t], sink);
+            }
+    }
+    if (B.is_tail) code_tail(s, B.tail_zeros, quirk, sink);
     sink.finish();
     if (sink.overflow && status) atomicOr(status, RAHT_ST_STREAM_OVERFLOW);
 }
@@ -493,23 +696,18 @@ __global__ void __launch_bounds__(32) rlgr_decode_serial_kernel(const uint8_t *_
     decode_range(br, initial_state(), -1, G.n, G.flag_signed, q + (size_t)ch * G.ld);
 }
 
-// with the encoder's sync index: one thread per entry (SYNC_STRIDE lane blocks)
+// with the encoder's sync index: one thread per entry (512 symbols)
 constexpr int DEC_THREADS = 128;
 __global__ void __launch_bounds__(DEC_THREADS) rlgr_decode_indexed_kernel(const uint8_t *__restrict__ streams, int64_t slot_bytes,
                                                                          const int64_t *__restrict__ nbytes,
-                                                                         const uint2 *__restrict__ sync_index, Geometry G,
-                                                                         int32_t *__restrict__ q)
+                                                                         const uint2 *__restrict__ sync_index, int64_t entries,
+                                                                         Geometry G, int32_t *__restrict__ q)
 {
     const int ch = blockIdx.y;
     const int64_t e = (int64_t)blockIdx.x * DEC_THREADS + threadIdx.x;
-    const int64_t entries = G.nchunks * SYNC_PER_CHUNK;
     if (e >= entries) return;
-    const int64_t w = e / SYNC_PER_CHUNK;
-    const int k = (int)(e - w * SYNC_PER_CHUNK);
-    const int64_t start = (w * CHUNK_LANES + (int64_t)k * SYNC_STRIDE) * BLOCK_SYMS;
-    if (start >= G.n) return;
-    const int nblocks = min(SYNC_STRIDE, CHUNK_LANES - k * SYNC_STRIDE);
-    int64_t end = start + (int64_t)nblocks * BLOCK_SYMS;
+    const int64_t start = e << SYNC_SHIFT;
+    int64_t end = start + SYNC_RANGE;
     if (end > G.n) end = G.n;
     const uint2 ent = sync_index[(size_t)ch * entries + e];
     const uint32_t first = ent.y >> 22;
@@ -525,27 +723,30 @@ __global__ void __launch_bounds__(DEC_THREADS) rlgr_decode_indexed_kernel(const 
 }
 
 struct EncLayout {
-    size_t off_lastnz, off_recA, off_recB, off_lanerec, off_chunkoff, off_totals, off_stats, total;
+    size_t off_lastnz, off_cnt, off_info, off_blockpos, off_rec, off_lanerec, off_chunkoff, off_totals, off_stats, off_ev, total;
 };
 EncLayout enc_layout(int64_t n, int nch)
 {
     EncLayout L;
-    const size_t nblk = (size_t)blocks_of(n), nchunks = (size_t)chunks_of(n), c = (size_t)(nch > 0 ? nch : 0);
+    const size_t nsb = (size_t)sym_blocks_of(n), W = (size_t)chunk_slots_of(n), c = (size_t)(nch > 0 ? nch : 0);
     size_t o = 0;
-    L.off_lastnz = o; o += align_up(c * nblk * 4, 256);
-    L.off_recA = o; o += align_up(c * nchunks * 16, 256);
-    L.off_recB = o; o += align_up(c * nchunks * 16, 256);
-    L.off_lanerec = o; o += align_up(c * nchunks * 32 * 8, 256);
-    L.off_chunkoff = o; o += align_up(c * nchunks * 8, 256);
+    L.off_lastnz = o; o += align_up(c * nsb * 4, 256);
+    L.off_cnt = o; o += align_up(c * nsb * 4, 256);
+    L.off_info = o; o += align_up(c * sizeof(ChanInfo), 256);
+    L.off_blockpos = o; o += align_up(c * nsb * 4, 256);
+    L.off_rec = o; o += align_up(c * W * REC_WORDS * 16, 256);
+    L.off_lanerec = o; o += align_up(c * W * 32 * LANEREC_WORDS * 16, 256);
+    L.off_chunkoff = o; o += align_up(c * W * 8, 256);
     L.off_totals = o; o += align_up(c * 8, 256);
     L.off_stats = o; o += 256;
+    L.off_ev = o; o += align_up(c * W * CHUNK_SLOTS * 8, 256);
     L.total = o + 256;
     return L;
 }
 
 }  // namespace
 
-RAHT_API int64_t raht_rlgr_sync_entries(int64_t n) { return n <= 0 ? 0 : chunks_of(n) * SYNC_PER_CHUNK; }
+RAHT_API int64_t raht_rlgr_sync_entries(int64_t n) { return n <= 0 ? 0 : (n + SYNC_RANGE - 1) >> SYNC_SHIFT; }
 
 RAHT_API size_t raht_rlgr_encode_workspace_bytes(int64_t n, int nch) { return enc_layout(n < 0 ? 0 : n, nch).total; }
 
@@ -565,57 +766,54 @@ RAHT_API int raht_rlgr_encode(const int32_t *q, int64_t n, int64_t ld, int nch, 
         return RAHT_OK;
     }
     const EncLayout L = enc_layout(n, nch);
-    if (!workspace || workspace_bytes < L.total) {
-        raht_set_error("raht_rlgr_encode: workspace too small (%zu < %zu)", workspace_bytes, L.total);
+    if (!workspace || workspace_bytes < L.total || ((uintptr_t)workspace & 15) != 0) {
+        raht_set_error("raht_rlgr_encode: workspace too small or not 16-byte aligned (%zu < %zu)", workspace_bytes, L.total);
         return RAHT_E_WORKSPACE;
     }
     Geometry G;
-    G.n = n; G.ld = ld; G.nblk = blocks_of(n); G.nchunks = chunks_of(n); G.nch = nch; G.flag_signed = flag_signed;
-    RAHT_REQUIRE(G.nchunks < ((int64_t)1 << 31), "raht_rlgr_encode: too many chunks");
+    G.n = n; G.ld = ld; G.nsb = sym_blocks_of(n); G.W = chunk_slots_of(n); G.nch = nch; G.flag_signed = flag_signed;
     char *ws = (char *)workspace;
     int32_t *lastnz = (int32_t *)(ws + L.off_lastnz);
-    uint4 *recA = (uint4 *)(ws + L.off_recA), *recB = (uint4 *)(ws + L.off_recB);
-    uint2 *lanerec = (uint2 *)(ws + L.off_lanerec);
+    uint32_t *cnt = (uint32_t *)(ws + L.off_cnt);
+    ChanInfo *info = (ChanInfo *)(ws + L.off_info);
+    uint32_t *blockpos = (uint32_t *)(ws + L.off_blockpos);
+    uint4 *rec = (uint4 *)(ws + L.off_rec);
+    uint4 *lanerec = (uint4 *)(ws + L.off_lanerec);
     unsigned long long *chunkoff = (unsigned long long *)(ws + L.off_chunkoff);
     unsigned long long *totals = (unsigned long long *)(ws + L.off_totals);
     unsigned long long *stats = (unsigned long long *)(ws + L.off_stats);
-    const size_t smem = (size_t)CHUNK_SMEM_WORDS * 4;
+    uint2 *ev = (uint2 *)(ws + L.off_ev);
     RAHT_CUDA(cudaMemsetAsync(stats, 0, 256, st));
+    const int64_t entries = raht_rlgr_sync_entries(n);
+    if (sync_index) RAHT_CUDA(cudaMemsetAsync(sync_index, 0xff, (size_t)nch * entries * 8, st));   // "no event in this range"
 
-    const unsigned groups = (unsigned)((G.nblk + 32 * K0_WARPS - 1) / (32 * K0_WARPS));
-    (raht_count_launches(1), rlgr_lastnz_kernel)<<<dim3(groups, nch), 32 * K0_WARPS, 0, st>>>(q, G, lastnz);
-    (raht_count_launches(1), rlgr_lastnz_scan_kernel)<<<nch, 1024, 0, st>>>(G, lastnz);
-    const dim3 cgrid((unsigned)G.nchunks, nch);
-    // speculation sweeps: the first from canonical states, later ones from the previous chunk's end states
-    static int sweeps = -1;
-    if (sweeps < 0) {
-        const char *e = getenv("RAHT_RLGR_SWEEPS");
-        sweeps = e ? atoi(e) : 2;
-        if (sweeps < 1) sweeps = 1;
-        if (sweeps > 8) sweeps = 8;
-    }
-    uint4 *rec_cur = recA, *rec_prev = recB;
-    for (int sw = 0; sw < sweeps; ++sw) {
-        (raht_count_launches(1), rlgr_speculate_kernel)<<<cgrid, 32, smem, st>>>(q, G, lastnz, sw, rec_prev, rec_cur, lanerec, stats);
-        uint4 *t = rec_cur; rec_cur = rec_prev; rec_prev = t;
-    }
-    recB = rec_prev;                                          // records of the last sweep
-    (raht_count_launches(1), rlgr_resolve_kernel)<<<nch, 32, smem, st>>>(q, G, lastnz, recB, lanerec, chunkoff, slot_bytes, nbytes,
-                                                                       totals, status, stats);
+    const unsigned groups = (unsigned)((G.nsb + 32 * K1_WARPS - 1) / (32 * K1_WARPS));
+    (raht_count_launches(1), rlgr_count_kernel)<<<dim3(groups, nch), 32 * K1_WARPS, 0, st>>>(q, G, cnt, lastnz);
+    (raht_count_launches(1), rlgr_scan_kernel)<<<nch, 1024, 0, st>>>(G, cnt, lastnz, info);
+    (raht_count_launches(1), rlgr_scatter_kernel)<<<dim3(groups, nch), 32 * K1_WARPS, 0, st>>>(q, G, cnt, lastnz, ev, blockpos);
+    const dim3 cgrid((unsigned)((G.W + SPEC_WARPS - 1) / SPEC_WARPS), nch);
+    // channels that are mostly non-zero with one candidate per block, the others with the 8 state classes
+    raht_count_launches(2);
+    rlgr_speculate_kernel<1><<<cgrid, 32 * SPEC_WARPS, 0, st>>>(G, info, ev, rec, lanerec, stats);
+    rlgr_speculate_kernel<8><<<cgrid, 32 * SPEC_WARPS, 0, st>>>(G, info, ev, rec, lanerec, stats);
+    (raht_count_launches(1), rlgr_resolve_kernel)<<<nch, 32, 0, st>>>(G, info, ev, rec, lanerec, chunkoff, slot_bytes, nbytes,
+                                                                    totals, status, stats);
     (raht_count_launches(1), rlgr_zero_kernel)<<<dim3(64, nch), 256, 0, st>>>(streams, slot_bytes, totals);
-    (raht_count_launches(1), rlgr_emit_kernel)<<<cgrid, 32, smem, st>>>(q, G, lastnz, lanerec, chunkoff, streams, slot_bytes,
-                                                                      (uint2 *)sync_index, status);
+    (raht_count_launches(1), rlgr_emit_kernel)<<<cgrid, 32 * SPEC_WARPS, 0, st>>>(G, info, ev, blockpos, lanerec, chunkoff, streams,
+                                                                                 slot_bytes, (uint2 *)sync_index, entries, status);
     RAHT_LAUNCH_CHECK();
     return RAHT_OK;
 }
 
 // diagnostics of the last raht_rlgr_encode on this workspace: out[0] = chunk solves in the speculation
-// sweeps, out[1] = their fixed-point rounds, out[2] = chunks re-solved by the resolve pass.  Synchronises.
-RAHT_API int raht_rlgr_encode_stats(const void *workspace, int64_t n, int nch, unsigned long long *out3_host, void *stream)
+// pass, out[1] = their fixed-point rounds, out[2] = chunks re-solved by the resolve pass, out[3] = slowest
+// chunk of the speculation pass (SM cycles << 24 | channel << 8 | rounds), out[4] = rounds spent in those re-solves.
+// Synchronises.
+RAHT_API int raht_rlgr_encode_stats(const void *workspace, int64_t n, int nch, unsigned long long *out5_host, void *stream)
 {
-    RAHT_REQUIRE(workspace && out3_host && n > 0, "raht_rlgr_encode_stats: bad arguments");
+    RAHT_REQUIRE(workspace && out5_host && n > 0, "raht_rlgr_encode_stats: bad arguments");
     const EncLayout L = enc_layout(n, nch);
-    RAHT_CUDA(cudaMemcpyAsync(out3_host, (const char *)workspace + L.off_stats, 24, cudaMemcpyDeviceToHost, (cudaStream_t)stream));
+    RAHT_CUDA(cudaMemcpyAsync(out5_host, (const char *)workspace + L.off_stats, 40, cudaMemcpyDeviceToHost, (cudaStream_t)stream));
     RAHT_CUDA(cudaStreamSynchronize((cudaStream_t)stream));
     return RAHT_OK;
 }
@@ -631,12 +829,13 @@ RAHT_API int raht_rlgr_decode(const uint8_t *streams, int64_t slot_bytes, const 
     RAHT_REQUIRE(((uintptr_t)streams & 7) == 0, "raht_rlgr_decode: streams must be 8-byte aligned");
     cudaStream_t st = (cudaStream_t)stream;
     Geometry G;
-    G.n = n; G.ld = ld; G.nblk = blocks_of(n); G.nchunks = chunks_of(n); G.nch = nch; G.flag_signed = flag_signed;
+    G.n = n; G.ld = ld; G.nsb = sym_blocks_of(n); G.W = chunk_slots_of(n); G.nch = nch; G.flag_signed = flag_signed;
     RAHT_CUDA(cudaMemsetAsync(q, 0, ((size_t)(nch - 1) * ld + n) * 4, st));      // the decoders store non-zeros only
     if (sync_index) {
-        const dim3 grid((unsigned)((G.nchunks * SYNC_PER_CHUNK + DEC_THREADS - 1) / DEC_THREADS), nch);
+        const int64_t entries = raht_rlgr_sync_entries(n);
+        const dim3 grid((unsigned)((entries + DEC_THREADS - 1) / DEC_THREADS), nch);
         (raht_count_launches(1), rlgr_decode_indexed_kernel)<<<grid, DEC_THREADS, 0, st>>>(streams, slot_bytes, nbytes,
-                                                                                          (const uint2 *)sync_index, G, q);
+                                                                                          (const uint2 *)sync_index, entries, G, q);
     } else {
         (raht_count_launches(1), rlgr_decode_serial_kernel)<<<nch, 32, 0, st>>>(streams, slot_bytes, nbytes, G, q);
     }

@@ -24,11 +24,20 @@ constexpr int RL_L = 4, RL_U0 = 3, RL_D0 = 1, RL_U1 = 2, RL_D1 = 1;     // membu
 constexpr int RL_KRP_MAX = 32 * RL_L;
 constexpr int RL_KP_INIT = 0, RL_KRP_INIT = 2 * RL_L;                   // membuf.cpp:343-345
 
-constexpr int BLOCK_SYMS = 128;                    // symbols per lane block
-constexpr int MASK_WORDS = BLOCK_SYMS / 32;
+constexpr int EV_BLOCK = 128;                      // events per lane block
+constexpr int EV_GROUP = 4;                        // events per 32-byte unit of the lane-interleaved event store
 constexpr int CHUNK_LANES = 31;                    // lane blocks per warp chunk (lane 0 = warm-up block)
-constexpr int CHUNK_SYMS = BLOCK_SYMS * CHUNK_LANES;
-constexpr int NCAND = 2;                           // speculated start states carried side by side
+constexpr int CHUNK_EVENTS = EV_BLOCK * CHUNK_LANES;
+constexpr int CHUNK_SLOTS = 32 * EV_BLOCK;         // event slots of a chunk in the store (32 lanes)
+constexpr int NCAND = 8;                           // speculated start states of a block carried side by side
+constexpr int SYM_BLOCK = 128;                     // symbols per block of the compaction passes
+constexpr int SYNC_SHIFT = 9;                      // one sync entry per 2^9 = 512 symbols
+constexpr int SYNC_RANGE = 1 << SYNC_SHIFT;
+constexpr uint32_t SYNC_NONE = 1023;               // no non-zero symbol in the entry's range
+
+// slot of event i (0..127) of lane l in a chunk of the store: units of 4 events, lane-interleaved, so that a warp
+// reading unit j of all its lanes touches 1 KB of consecutive memory
+RL_HD uint32_t ev_slot(int lane, int i) { return (uint32_t)((((i >> 2) * 32 + lane) << 2) | (i & 3)); }
 
 struct State {
     int kP, kRP;
@@ -173,94 +182,82 @@ template <class Sink> RL_HD void code_tail(State &s, uint32_t g, bool last_quirk
     }
 }
 
-// One lane block: the events whose non-zero symbol lies in row[0..len), in order.  row holds the
-// mapped symbols u; mask bit i of word w is set iff row[32 w + i] != 0.  zeros_before = number of
-// zero symbols between the previous non-zero of the channel (or its start) and row[0].
-// is_tail: this block holds the channel's last symbol, so the trailing zeros and the tail rule are
-// coded here too.
-template <class Sink>
-RL_HD void code_block(const uint32_t *row, int len, const uint32_t *mask, uint32_t zeros_before, bool is_tail, State &s,
-                      Sink &sink)
+// The state classes that do not re-synchronise: while a channel stays in run mode with k_R = 0 (sparse, small
+// values), two trajectories keep the parity of their k_P difference (every event takes 1 from both, every completed
+// run adds 2) and, unless a value of -1 (p = 0) comes by, their k_RP difference (k_RP moves in steps of 2 there
+// except for p = 2).  Inside a class the trajectories contract (the lower k_P completes more runs) and merge within
+// a few events.  The 8 candidates carried per block are therefore k_P in a-1 .. a+2 x k_RP in {a, a ^ 2} around a
+// state a when it is in that regime, else a and b four times each.
+RL_HD void expand_classes(State a, State b, uint32_t out[8])
 {
-    int prev = -1;
-    bool quirk = false;
-    for (int w = 0; w < MASK_WORDS; ++w) {
-        uint32_t mm = mask[w];
-        while (mm) {
-            const int idx = 32 * w + rl_ctz(mm);
-            mm &= mm - 1;
-            uint32_t g = (uint32_t)(idx - prev - 1) + (prev < 0 ? zeros_before : 0u);
-            uint32_t m = 0;
-            if (g) m = code_zeros(s, g, sink, (bool *)nullptr);
-            quirk = code_nonzero(s, m, (uint64_t)row[idx], sink);
-            prev = idx;
-        }
-    }
-    if (is_tail) {
-        const uint32_t g = prev < 0 ? zeros_before + (uint32_t)len : (uint32_t)(len - 1 - prev);
-        code_tail(s, g, quirk, sink);
+    for (int c = 0; c < 8; ++c) {
+        State s;
+        if (a.kRP < 4) {
+            s.kP = a.kP - 1 + (c & 3);
+            if (s.kP < 0) s.kP = 0;
+            s.kRP = (c >> 2) ? (a.kRP ^ 2) : a.kRP;
+        } else s = c < 4 ? a : b;
+        out[c] = pack_state(s);
     }
 }
 
-// ---- dense blocks: one branch-free step per SYMBOL (lengths only) -----------------------------------------------
-// Same automaton as the event form, advanced one symbol at a time with selects instead of branches, for NC
-// candidate states side by side (independent chains: instruction-level parallelism instead of divergence).
-// Zeros cost as much as non-zeros here, so callers use it for blocks that are mostly non-zero.
-struct SymState {
-    int kP, kRP;
-    uint32_t m;         // open partial run
-    uint32_t bits;
+// ---- event space ------------------------------------------------------------------------------------------
+// The encoder works on the compacted EVENT list of a channel (rlgr.cu): event e = (gap, u) = the number of zero
+// symbols since the previous non-zero symbol (or the channel start) and the mapped non-zero symbol.  A lane
+// block is EV_BLOCK consecutive events; work, warm-up length and chunk count are proportional to the number of
+// events, whatever the zero runs between them.
+struct Event {
+    uint32_t gap, u;
 };
 
-// one symbol x (already mapped; 0 = zero symbol).  Returns true when the tail rule would fire if this were the
-// channel's last symbol (membuf.cpp:416: k at the top of the iteration != 0 and u, post-decrement, == 0).
-RL_HD bool sym_step(SymState &t, uint32_t x)
+// Code length of one event from state s (lengths only, lean form of code_zeros + code_nonzero).
+// Returns the tail quirk of code_nonzero.
+RL_HD bool count_event(State &s, uint32_t g, uint32_t u, uint32_t &bits)
 {
-    const int k = t.kP >> 2;
-    const unsigned kR = (unsigned)(t.kRP >> 2);
-    const bool run = k != 0, z = x == 0;
-    const bool coded = !(run && z);                               // a Golomb-Rice code is written for this symbol
-    const uint32_t v = x - ((run && !z) ? 1u : 0u);               // run mode codes u - 1
-    const uint32_t p = kR > 31 ? 0u : v >> kR;
-    const uint32_t grlen = p < 32 ? p + 1 + kR : 64u;
-    const uint32_t m1 = t.m + 1;
-    const bool complete = !coded && m1 == (1u << k);
-    t.bits += coded ? grlen + (run ? (uint32_t)(1 + k) : 0u) : (complete ? 1u : 0u);
-    const int krp_up = t.kRP + (int)(p > 256u ? 256u : p) - 1;
-    const int krp_new = p ? (krp_up > RL_KRP_MAX ? RL_KRP_MAX : krp_up) : (t.kRP < 2 ? 0 : t.kRP - 2);
-    t.kRP = coded ? krp_new : t.kRP;
-    const int kp_coded = z ? t.kP + RL_U0 : (t.kP < 1 ? 0 : t.kP - 1);   // D0 == D1 == 1
-    t.kP = coded ? kp_coded : (complete ? t.kP + RL_U1 : t.kP);
-    t.m = (coded || complete) ? 0u : m1;
-    return run && v == 0;
+    if (g) {
+        CountSink z{0};
+        code_zeros(s, g, z, (bool *)nullptr);
+        bits += z.bits;
+    }
+    const int k = s.kP >> 2;
+    const unsigned kR = (unsigned)(s.kRP >> 2);
+    const uint32_t v = u - (k ? 1u : 0u);                               // run mode codes u - 1 (membuf.cpp:355)
+    const uint32_t p = kR > 31 ? 0u : (v >> kR);
+    bits += (p < 32 ? p + 1 + kR : 64u) + (k ? 1u + (uint32_t)k : 0u);  // grWrite (:242-256) + `0`, m in k bits (:357-358)
+    const int up = s.kRP + (int)(p > 256u ? 256u : p) - 1;
+    s.kRP = p ? (up > RL_KRP_MAX ? RL_KRP_MAX : up) : (s.kRP < 2 ? 0 : s.kRP - 2);
+    s.kP = s.kP < 1 ? 0 : s.kP - 1;                                     // D0 == D1 == 1
+    return k != 0 && v == 0;
 }
 
-// The block of code_block(), lengths only, for NC candidate states.  last_nz = index of the block's last non-zero
-// symbol (-1: none).  s[] in/out, bits[] out.
-template <int NC>
-RL_HD void count_block_dense(const uint32_t *row, int len, int last_nz, uint32_t zeros_before, bool is_tail, State *s,
-                             uint32_t *bits)
+// The same event with its bits written to sink (put(value, len <= 32)).
+template <class Sink> RL_HD bool emit_event(State &s, uint32_t g, uint32_t u, Sink &sink)
 {
-    SymState t[NC];
-    for (int c = 0; c < NC; ++c) {
-        CountSink k{0};
-        State st = s[c];
-        uint32_t m = 0;
-        if (zeros_before && (last_nz >= 0 || is_tail)) m = code_zeros(st, zeros_before, k, (bool *)nullptr);
-        t[c].kP = st.kP; t[c].kRP = st.kRP; t[c].m = m; t[c].bits = k.bits;
+    uint32_t m = 0;
+    if (g) m = code_zeros(s, g, sink, (bool *)nullptr);
+    const int k = s.kP >> 2;
+    const unsigned kR = (unsigned)(s.kRP >> 2);
+    uint32_t v = u;
+    if (k) {
+        v = u - 1;
+        sink.put(m, 1u + (unsigned)k);                                  // `0` then m in k bits
     }
-    const int end = is_tail ? len : last_nz + 1;
-    bool fire[NC];
-    for (int c = 0; c < NC; ++c) fire[c] = false;
-    for (int i = 0; i < end; ++i) {
-        const uint32_t x = row[i];
-        for (int c = 0; c < NC; ++c) fire[c] = sym_step(t[c], x);
+    const uint32_t p = kR > 31 ? 0u : (v >> kR);
+    if (p + 1 + kR <= 32) {                                             // p ones, a zero, kR low bits: one put
+        const uint32_t ones = ((1u << p) - 1u) << 1;                    // p <= 31 here
+        const uint32_t low = kR ? (v & (0xffffffffu >> (32 - kR))) : 0u;
+        sink.put(((uint64_t)ones << kR) | low, p + 1 + kR);
+    } else if (p < 32) {
+        sink.put((((uint64_t)1) << (p + 1)) - 2, p + 1);
+        sink.put(kR > 31 ? (uint64_t)v : (uint64_t)(v & ((1u << kR) - 1u)), kR);
+    } else {
+        sink.put(0xffffffffull, 32);                                    // escape: 32 ones, then v in 32 bits
+        sink.put((uint64_t)v, 32);
     }
-    for (int c = 0; c < NC; ++c) {
-        if (is_tail && end > 0 && fire[c]) t[c].bits += 1 + (uint32_t)(t[c].kP >> 2);     // write(0); write(m, k_P / L)
-        s[c].kP = t[c].kP; s[c].kRP = t[c].kRP;
-        bits[c] = t[c].bits;
-    }
+    const int up = s.kRP + (int)(p > 256u ? 256u : p) - 1;
+    s.kRP = p ? (up > RL_KRP_MAX ? RL_KRP_MAX : up) : (s.kRP < 2 ? 0 : s.kRP - 2);
+    s.kP = s.kP < 1 ? 0 : s.kP - 1;
+    return k != 0 && v == 0;
 }
 
 // ---- decoder ---------------------------------------------------------------------------------------------

@@ -21,6 +21,9 @@ tree = ops.tree_from_keys(keys)
 order = tree.order()
 T = ops.forward(tree, packed, torch.float64)
 q = ops.quant_reorder(T, order, step)
+if os.environ.get("RLGR_PROBE_SEL"):                     # e.g. "0:1": only these channels
+    a, b = os.environ["RLGR_PROBE_SEL"].split(":")
+    q = q[int(a):int(b)].contiguous()
 
 
 def timed(fn, reps=5):
@@ -42,3 +45,9 @@ zeros = (q == 0).float().mean(dim=1)
 print(f"n={q.shape[1]} step={step} sweeps={os.environ.get('RAHT_RLGR_SWEEPS', '2')} encode {ms_enc:.3f} ms (incl. host sync) "
       f"decode indexed {ms_dec:.3f} ms serial {ms_ser:.1f} ms payload {st.total_bytes()} index {st.index_bytes()} stats {st.stats} "
       f"zero fraction min/median/max {zeros.min():.3f}/{zeros.median():.3f}/{zeros.max():.3f}")
+if os.environ.get("RLGR_PROBE_SPLIT"):
+    for name, sel in (("ch0-2", slice(0, 3)), ("ch3-6", slice(3, 7)), ("ch7-9", slice(7, 10)), ("ch14-58", slice(14, 59)), ("ch0", slice(0, 1)),
+                      ("ch3", slice(3, 4))):
+        qs = q[sel].contiguous()
+        ms, st = timed(lambda: ops.rlgr_encode(qs, 1, want_stats=True))
+        print(f"  {name}: encode {ms:.3f} ms stats {st.stats}")

@@ -1,10 +1,11 @@
 // rlgr_emu.cpp -- host emulation of the chunk-parallel RLGR encoder / indexed decoder of
 // raht-3dgs-codec_b200/csrc/rlgr.cu.  TEST INFRASTRUCTURE: it runs the same arithmetic
-// (csrc/rlgr_core.cuh, compiled for the host) through the same passes -- last-nonzero scan,
-// speculation sweeps with the in-warp fixed point, resolve, emit -- with the 32 lanes of a warp
-// executed one after the other, so that the CPU test-suite can check the ALGORITHM (event alignment,
-// tail rule, speculation + repair exactness, sync index) against the oracle without a GPU.
-// The CUDA kernels themselves are checked on the GPU by tests/test_gpu_parity.py.
+// (csrc/rlgr_core.cuh, compiled for the host) through the same passes -- event compaction into the
+// lane-interleaved store, speculation with the in-warp fixed point, resolve, emit with the sync index
+// written on the way -- with the 32 lanes of a warp executed one after the other, so that the CPU
+// test-suite can check the ALGORITHM (event form, tail rule, speculation + repair exactness, sync
+// index) against the oracle without a GPU.  The CUDA kernels themselves are checked on the GPU by
+// tests/test_gpu_parity.py.
 #include "../../raht-3dgs-codec_b200/csrc/rlgr_core.cuh"
 #include <algorithm>
 #include <cstring>
@@ -14,144 +15,236 @@ using namespace rlgr;
 
 namespace {
 
-constexpr int SYNC_STRIDE = 4;                                                // as in rlgr.cu
-constexpr int SYNC_PER_CHUNK = (CHUNK_LANES + SYNC_STRIDE - 1) / SYNC_STRIDE;
-constexpr uint32_t SYNC_NONE = 1023;
+struct Chan {
+    int64_t n;
+    int64_t W;                    // chunk slots in the store
+    uint32_t events, nblocks, nchunks, tail_zeros;
+    std::vector<Event> store;     // W * CHUNK_SLOTS, lane-interleaved (ev_slot)
+    std::vector<uint32_t> blockpos;
+};
+
+int64_t ev_blocks_of(int64_t e) { return e > 0 ? (e + EV_BLOCK - 1) / EV_BLOCK : 1; }
+int64_t chunks_of_blocks(int64_t nb) { return (nb + CHUNK_LANES - 1) / CHUNK_LANES; }
+
+// K1: compaction (count / scan / scatter of rlgr.cu, done serially)
+void compact(const int32_t *q, int64_t n, int flag_signed, Chan &C)
+{
+    C.n = n;
+    C.W = chunks_of_blocks(ev_blocks_of(n));
+    C.store.assign((size_t)C.W * CHUNK_SLOTS, Event{0xdeadbeefu, 0xdeadbeefu});
+    C.blockpos.assign((size_t)ev_blocks_of(n), 0);
+    uint32_t e = 0;
+    int64_t last = -1;
+    for (int64_t i = 0; i < n; ++i) {
+        if (q[i] == 0) continue;
+        const uint32_t u = flag_signed ? s2u(q[i]) : (uint32_t)q[i];
+        const Event E{(uint32_t)(i - last - 1), u};
+        const uint32_t b = e / EV_BLOCK;
+        const int k = (int)(e % EV_BLOCK);
+        const uint32_t w = b / CHUNK_LANES;
+        const int l = (int)(b - w * CHUNK_LANES) + 1;
+        C.store[(size_t)w * CHUNK_SLOTS + ev_slot(l, k)] = E;
+        if (l == CHUNK_LANES && (int64_t)w + 1 < C.W) C.store[(size_t)(w + 1) * CHUNK_SLOTS + ev_slot(0, k)] = E;
+        if (k == 0) C.blockpos[b] = (uint32_t)i;
+        ++e;
+        last = i;
+    }
+    C.events = e;
+    C.nblocks = (uint32_t)ev_blocks_of(e);
+    C.nchunks = (uint32_t)chunks_of_blocks(C.nblocks);
+    C.tail_zeros = (uint32_t)(n - 1 - last);
+}
 
 struct Lane {
-    std::vector<uint32_t> row;
-    uint32_t mask[MASK_WORDS];
-    int len;
-    uint32_t zeros_before;
+    const Event *base;       // chunk in the store
+    int lane, cnt;
     bool is_tail;
-    int last_nz;
-    bool dense, single;
+    uint32_t tail_zeros;
+    Event at(int i) const { return base[ev_slot(lane, i)]; }
 };
 
-struct Chan {
-    const int32_t *q;
-    int64_t n;
-    int flag_signed;
-    int64_t nblk, nchunks;
-    std::vector<int32_t> lastnz;
-};
-
-void load_chunk(const Chan &C, int64_t w, Lane L[32])
+void lane_block(const Chan &C, int64_t w, int l, Lane &B)
 {
-    for (int l = 0; l < 32; ++l) {
-        const int64_t blk = w * CHUNK_LANES - 1 + l, start = blk * BLOCK_SYMS;
-        Lane &B = L[l];
-        B.row.assign(BLOCK_SYMS, 0);
-        std::memset(B.mask, 0, sizeof(B.mask));
-        for (int i = 0; i < BLOCK_SYMS; ++i) {
-            const int64_t s = start + i;
-            const int32_t v = (s >= 0 && s < C.n) ? C.q[s] : 0;
-            const uint32_t u = C.flag_signed ? s2u(v) : (uint32_t)v;
-            B.row[i] = u;
-            if (u) B.mask[i / 32] |= 1u << (i % 32);
-        }
-        int64_t len = blk < 0 ? 0 : C.n - start;
-        len = std::max<int64_t>(0, std::min<int64_t>(len, BLOCK_SYMS));
-        B.len = (int)len;
-        B.zeros_before = (blk <= 0 || len == 0) ? 0u : (uint32_t)(start - 1 - (int64_t)C.lastnz[blk - 1]);
-        B.is_tail = len > 0 && start + len == C.n;
+    B.base = C.store.data() + (size_t)w * CHUNK_SLOTS;
+    B.lane = l;
+    const int64_t b = w * CHUNK_LANES - 1 + l;
+    int64_t cnt = (b < 0 || b >= (int64_t)C.nblocks) ? 0 : (int64_t)C.events - b * EV_BLOCK;
+    cnt = std::max<int64_t>(0, std::min<int64_t>(cnt, EV_BLOCK));
+    B.cnt = (int)cnt;
+    B.is_tail = b == (int64_t)C.nblocks - 1;
+    B.tail_zeros = C.tail_zeros;
+}
+
+void count_lane(const Lane &B, State &s, uint32_t &bits)
+{
+    bits = 0;
+    bool quirk = false;
+    for (int i = 0; i < B.cnt; ++i) {
+        const Event e = B.at(i);
+        quirk = count_event(s, e.gap, e.u, bits);
     }
-    uint32_t nz = 0;
-    for (int l = 0; l < 32; ++l) {
-        L[l].last_nz = -1;
-        for (int i = 0; i < BLOCK_SYMS; ++i)
-            if (L[l].row[i]) { ++nz; L[l].last_nz = i; }
-    }
-    for (int l = 0; l < 32; ++l) {
-        L[l].dense = nz * 4 >= (uint32_t)(CHUNK_LANES * BLOCK_SYMS);
-        L[l].single = nz * 2 >= (uint32_t)(CHUNK_LANES * BLOCK_SYMS);
+    if (B.is_tail) {
+        CountSink k{0};
+        code_tail(s, B.tail_zeros, quirk, k);
+        bits += k.bits;
     }
 }
 
+constexpr uint32_t STATE_INVALID = 0xffffu;
+constexpr int SPEC_ROUNDS = 4, REPAIR_ROUNDS = 34;      // as in rlgr.cu
+
 struct LaneRes {
-    State in[NCAND], out[NCAND];
+    uint32_t in[NCAND], out[NCAND];      // packed states
     uint32_t bits[NCAND];
+    int sel[NCAND];
+};
+struct ChunkSol {
+    LaneRes R[32];
+    bool complete[NCAND];
+    uint32_t end[NCAND], total[NCAND];
+    int rounds;
 };
 
-int solve_chunk(const Lane L[32], bool pin, const State first[NCAND], LaneRes R[32], bool *identity)
+// the chains that start at lane 1's candidates: sel[c] of every lane, completeness, code length, end state
+void walk_chains(ChunkSol &S, const bool has[32], const int src[32])
 {
-    bool need[32], has[32];
+    LaneRes *R = S.R;
+    int from[32][NCAND];
+    for (int l = 0; l < 32; ++l)
+        for (int c = 0; c < NCAND; ++c) {
+            from[l][c] = 15;
+            for (int k = NCAND - 1; k >= 0; --k) if (R[src[l]].out[c] == R[l].in[k]) from[l][c] = k;
+            if (!has[l]) from[l][c] = c;
+        }
+    for (int l = 0; l < 32; ++l) for (int c = 0; c < NCAND; ++c) R[l].sel[c] = (l == 1) ? c : 15;
+    for (int l = 2; l < 32; ++l)
+        for (int c = 0; c < NCAND; ++c) {
+            const int p = R[src[l]].sel[c];
+            R[l].sel[c] = p == 15 ? 15 : from[l][p];
+        }
+    for (int c = 0; c < NCAND; ++c) {
+        S.complete[c] = true;
+        S.total[c] = 0;
+        for (int l = 1; l < 32; ++l) {
+            if (R[l].sel[c] == 15) S.complete[c] = false;
+            else if (l > 0) S.total[c] += R[l].bits[R[l].sel[c]];
+        }
+        S.end[c] = R[31].out[R[31].sel[c] & (NCAND - 1)];
+    }
+}
+
+// solve_chunk of rlgr.cu with the lanes executed one after the other (every round: all lanes recode, then all
+// lanes look at their predecessor's end states of THIS round)
+// pin: lane 0 forwards `pinned` (the known state at the chunk start); else lane 0 codes the block before the chunk
+// as warm-up.  Every other lane starts from the canonical states canon[0], canon[1].
+void solve_chunk(const Lane L[32], bool pin, State pinned, const State canon[2], int max_rounds, bool expand, ChunkSol &S)
+{
+    bool has[32], d[32][NCAND];
     int src[32];
-    bool any_has = false;
+    LaneRes *R = S.R;
+    uint32_t guess[NCAND], start[NCAND];
+    for (int c = 0; c < NCAND; ++c) {
+        guess[c] = pack_state(canon[c < NCAND / 2 ? 0 : 1]);
+        start[c] = pin ? pack_state(pinned) : guess[c];
+    }
     for (int l = 0; l < 32; ++l) {
-        has[l] = L[l].is_tail;
-        for (int w = 0; w < MASK_WORDS; ++w) has[l] |= L[l].mask[w] != 0;
+        has[l] = L[l].cnt > 0 || L[l].is_tail;
         if (l == 0) has[l] = !pin && has[l];
         src[l] = 0;
         for (int k = 0; k < l; ++k) if (has[k]) src[l] = k;
-        if (l > 0) any_has |= has[l];
-        for (int c = 0; c < NCAND; ++c) { R[l].in[c] = first[c]; R[l].out[c] = first[c]; R[l].bits[c] = 0; }
-        need[l] = has[l];
+        for (int c = 0; c < NCAND; ++c) {
+            R[l].in[c] = l >= 2 ? guess[c] : start[c];
+            R[l].out[c] = R[l].in[c];
+            R[l].bits[c] = 0;
+            d[l][c] = has[l];
+        }
     }
     int r = 0;
-    for (; r < 34; ++r) {
+    for (;;) {
+        for (int l = 0; l < 32; ++l)
+            for (int c = 0; c < NCAND; ++c)
+                if (d[l][c]) {
+                    State s = unpack_state(R[l].in[c]);
+                    count_lane(L[l], s, R[l].bits[c]);
+                    R[l].out[c] = pack_state(s);
+                }
+        ++r;
+        if (r >= 2) {                                             // enough: the pinned chain (repair) / any chain (speculation) is complete
+            for (int l = 1; l < 32; ++l)
+                if (!has[l]) for (int c = 0; c < NCAND; ++c) R[l].in[c] = R[l].out[c] = R[src[l]].out[c];
+            walk_chains(S, has, src);
+            bool done = pin ? S.complete[0] : false;
+            if (!pin) for (int c = 0; c < NCAND; ++c) done |= S.complete[c];
+            if (done) break;
+        }
+        uint32_t o[32][NCAND];
+        for (int l = 0; l < 32; ++l) for (int c = 0; c < NCAND; ++c) o[l][c] = R[src[l]].out[c];
+        bool any = false;
         for (int l = 0; l < 32; ++l) {
-            if (!need[l]) continue;
-            if (L[l].dense) {
-                for (int c = 0; c < NCAND; ++c) R[l].out[c] = R[l].in[c];
-                count_block_dense<NCAND>(L[l].row.data(), L[l].len, L[l].last_nz, L[l].zeros_before, L[l].is_tail, R[l].out,
-                                         R[l].bits);
+            for (int c = 0; c < NCAND; ++c) d[l][c] = false;
+            if (l == 0) continue;
+            if (!has[l]) {
+                for (int c = 0; c < NCAND; ++c) R[l].in[c] = R[l].out[c] = o[l][c];
                 continue;
             }
-            for (int c = 0; c < NCAND; ++c) {
-                State s = R[l].in[c];
-                CountSink k{0};
-                code_block(L[l].row.data(), L[l].len, L[l].mask, L[l].zeros_before, L[l].is_tail, s, k);
-                R[l].out[c] = s;
-                R[l].bits[c] = k.bits;
-            }
-        }
-        bool any = false;
-        State prev_out[32][NCAND];
-        for (int l = 0; l < 32; ++l) for (int c = 0; c < NCAND; ++c) prev_out[l][c] = R[l].out[c];
-        for (int l = 0; l < 32; ++l) {
-            need[l] = false;
-            for (int c = 0; c < NCAND; ++c)
-                if (l > 0 && prev_out[src[l]][c] != R[l].in[c]) {
-                    R[l].in[c] = prev_out[src[l]][c];
-                    if (has[l]) need[l] = true;
-                    else R[l].out[c] = R[l].in[c];
+            if (r >= max_rounds) continue;
+            uint32_t nw[NCAND];
+            bool replace;
+            if (pin && l == 1) continue;                          // lane 1 holds the pinned state
+            if (expand && r == 1) {                               // after the warm-up round: the classes around the predecessor's end states
+                expand_classes(unpack_state(o[l][0]), unpack_state(o[l][NCAND / 2]), nw);
+                replace = true;
+            } else {
+                if (expand && l == 1) continue;                   // lane 1's candidates are the chunk's: fixed after the expansion
+                replace = false;
+                for (int c = 0; c < NCAND; ++c) {
+                    bool cov = false;
+                    for (int k = 0; k < NCAND; ++k) cov |= o[l][c] == R[l].in[k];
+                    replace |= !cov;
+                    nw[c] = o[l][c];
                 }
-            any |= need[l];
+            }
+            if (!replace) continue;
+            const LaneRes old = R[l];
+            for (int c = 0; c < NCAND; ++c) {
+                int m = -1;
+                for (int k = 0; k < NCAND; ++k) if (nw[c] == old.in[k]) { m = k; break; }
+                R[l].in[c] = nw[c];
+                if (m >= 0) { R[l].out[c] = old.out[m]; R[l].bits[c] = old.bits[m]; }
+                else { d[l][c] = true; any = true; }
+            }
         }
         if (!any) break;
     }
-    {
-        State prev_out[32][NCAND];
-        for (int l = 0; l < 32; ++l) for (int c = 0; c < NCAND; ++c) prev_out[l][c] = R[l].out[c];
-        for (int l = 1; l < 32; ++l)
-            if (!has[l]) for (int c = 0; c < NCAND; ++c) { R[l].in[c] = prev_out[src[l]][c]; R[l].out[c] = R[l].in[c]; }
-    }
-    R[0].bits[0] = R[0].bits[1] = 0;
-    if (identity) *identity = !any_has;
-    return r + 1;
+    S.rounds = r;
+    for (int c = 0; c < NCAND; ++c) R[0].bits[c] = 0;
+    walk_chains(S, has, src);
 }
 
-constexpr uint32_t REC_IDENTITY = 0x80000000u;
 struct ChunkRec {
-    uint32_t cand, ends, bits0, bits1;
+    uint32_t cand[NCAND], ends[NCAND], bits[NCAND];
 };
 struct LaneRec {
-    uint32_t starts, bits;
+    uint32_t starts[NCAND], bits[NCAND];
+    uint32_t sel;            // a nibble per chunk candidate
 };
 
-ChunkRec finish_chunk(const LaneRes R[32], bool identity, LaneRec *lr)
+ChunkRec finish_chunk(const ChunkSol &S, LaneRec *lr)
 {
-    ChunkRec rec{0, 0, 0, 0};
+    ChunkRec rec;
     for (int l = 0; l < 32; ++l) {
-        lr[l].starts = pack_state(R[l].in[0]) | (pack_state(R[l].in[1]) << 16);
-        lr[l].bits = R[l].bits[0] | (R[l].bits[1] << 16);
-        rec.bits0 += R[l].bits[0];
-        rec.bits1 += R[l].bits[1];
+        lr[l].sel = 0;
+        for (int c = 0; c < NCAND; ++c) {
+            lr[l].starts[c] = S.R[l].in[c];
+            lr[l].bits[c] = S.R[l].bits[c];
+            lr[l].sel |= (uint32_t)(S.R[l].sel[c] & 15) << (4 * c);
+        }
     }
-    rec.cand = lr[1].starts;
-    if (identity) rec.bits0 |= REC_IDENTITY;
-    rec.ends = pack_state(R[31].out[0]) | (pack_state(R[31].out[1]) << 16);
+    for (int c = 0; c < NCAND; ++c) {
+        rec.cand[c] = S.complete[c] ? lr[1].starts[c] : STATE_INVALID;
+        rec.ends[c] = S.end[c];
+        rec.bits[c] = S.total[c];
+    }
     return rec;
 }
 
@@ -174,98 +267,83 @@ struct HostSink {
 
 extern "C" {
 
-// One channel.  out must be zero-filled by the caller (cap bytes).  stats[0] chunk solves in the sweeps,
-// [1] fixed-point rounds, [2] repairs in the resolve pass, [3] chunks.  sync (optional): 4 x uint32 per chunk.
-// c1_kP: k_P of the second canonical start state.  sweeps: number of speculation sweeps (>= 1).
+// One channel.  out must be zero-filled by the caller (cap bytes).  stats[0] chunk solves in the speculation
+// pass, [1] fixed-point rounds, [2] repairs in the resolve pass, [3] chunks, [4] events, [5] rounds spent in
+// repairs, [6] repairs that needed the exact single-chain fallback.
+// sync (optional): 2 x uint32 per 512 symbols, pre-filled with 0xff by the caller.
+// mode: 0 = the kernel's rule (one canonical state when >= 50 % non-zero), 1 = always two, 2 = always one.
+// c1_kP: k_P of the second canonical start state.  max_spec_rounds: round cap of the speculation pass (0: the kernel's).
 __attribute__((visibility("default"))) int64_t emu_rlgr_encode(const int32_t *q, int64_t n, int flag_signed, uint8_t *out,
-                                                               int64_t cap, uint64_t *stats, uint32_t *sync, int sweeps, int c1_kP)
+                                                               int64_t cap, uint64_t *stats, uint32_t *sync, int mode, int c1_kP,
+                                                               int max_spec_rounds)
 {
     if (n <= 0) return 0;
     Chan C;
-    C.q = q; C.n = n; C.flag_signed = flag_signed;
-    C.nblk = (n + BLOCK_SYMS - 1) / BLOCK_SYMS;
-    C.nchunks = (C.nblk + CHUNK_LANES - 1) / CHUNK_LANES;
-    C.lastnz.assign(C.nblk, -1);
-    for (int64_t b = 0; b < C.nblk; ++b) {                       // K0 + max-scan
-        int32_t last = b ? C.lastnz[b - 1] : -1;
-        for (int64_t i = b * BLOCK_SYMS; i < std::min<int64_t>(n, (b + 1) * BLOCK_SYMS); ++i)
-            if (q[i] != 0) last = (int32_t)i;
-        C.lastnz[b] = last;
-    }
-    std::vector<ChunkRec> prev(C.nchunks), cur(C.nchunks);
-    std::vector<LaneRec> lanerec(C.nchunks * 32);
+    compact(q, n, flag_signed, C);
+    std::vector<ChunkRec> rec(C.nchunks);
+    std::vector<LaneRec> lanerec((size_t)C.nchunks * 32);
     Lane L[32];
-    LaneRes R[32];
-    for (int sweep = 0; sweep < sweeps; ++sweep) {                // A
-        for (int64_t w = 0; w < C.nchunks; ++w) {
-            State first[NCAND];
-            bool pin;
-            if (w == 0) {
-                first[0] = first[1] = initial_state();
-                pin = true;
-                if (sweep > 0) { cur[w] = prev[w]; continue; }
-            } else if (sweep == 0) {
-                first[0] = initial_state();
-                first[1].kP = c1_kP; first[1].kRP = RL_KRP_INIT;
-                pin = false;
-            } else {
-                const uint32_t guess = prev[w - 1].ends;
-                if (guess == prev[w].cand || (prev[w].bits0 & REC_IDENTITY)) { cur[w] = prev[w]; continue; }
-                first[0] = unpack_state(guess & 0xffff);
-                first[1] = unpack_state(guess >> 16);
-                pin = true;
-            }
-            load_chunk(C, w, L);
-            if (sweep == 0 && L[0].single) first[1] = first[0];
-            bool identity = false;
-            const int rounds = solve_chunk(L, pin, first, R, &identity);
-            cur[w] = finish_chunk(R, identity, &lanerec[w * 32]);
-            if (stats) { stats[0]++; stats[1] += rounds; }
-        }
-        std::swap(prev, cur);
+    ChunkSol S;
+    const bool single = mode == 2 || (mode == 0 && (int64_t)C.events * 2 >= n);
+    State canon[2];
+    canon[0] = initial_state();
+    canon[1].kP = c1_kP; canon[1].kRP = RL_KRP_INIT;
+    if (single) canon[1] = canon[0];
+    for (int64_t w = 0; w < C.nchunks; ++w) {                     // A
+        for (int l = 0; l < 32; ++l) lane_block(C, w, l, L[l]);
+        solve_chunk(L, w == 0, initial_state(), canon, max_spec_rounds > 0 ? max_spec_rounds : (w == 0 ? REPAIR_ROUNDS : SPEC_ROUNDS), !single, S);
+        rec[w] = finish_chunk(S, &lanerec[w * 32]);
+        if (stats) { stats[0]++; stats[1] += S.rounds; }
     }
-    std::vector<ChunkRec> &rec = prev;
     std::vector<uint64_t> chunkoff(C.nchunks);
     State s = initial_state();                                    // B
     uint64_t off = 0;
     for (int64_t w = 0; w < C.nchunks; ++w) {
         const uint32_t ps = pack_state(s);
-        int b = ps == (rec[w].cand & 0xffff) ? 0 : ps == (rec[w].cand >> 16) ? 1 : -1;
-        if (rec[w].bits0 & REC_IDENTITY) { b = 0; rec[w].bits0 = 0; rec[w].ends = ps | (ps << 16); }
+        int b = -1;
+        for (int c = NCAND - 1; c >= 0; --c) if (rec[w].cand[c] == ps) b = c;
         if (b < 0) {
-            load_chunk(C, w, L);
-            State first[NCAND] = {s, s};
-            solve_chunk(L, true, first, R, nullptr);
-            rec[w] = finish_chunk(R, false, &lanerec[w * 32]);
+            for (int l = 0; l < 32; ++l) lane_block(C, w, l, L[l]);
+            solve_chunk(L, true, s, canon, REPAIR_ROUNDS, !single, S);
+            if (stats) stats[5] += S.rounds;
+            if (!S.complete[0]) return -2000;                     // the exact chain must always complete
+            rec[w] = finish_chunk(S, &lanerec[w * 32]);
             b = 0;
             if (stats) stats[2]++;
         }
-        chunkoff[w] = (off << 1) | (unsigned)b;
-        off += b ? rec[w].bits1 : rec[w].bits0;
-        s = unpack_state(b ? (rec[w].ends >> 16) : (rec[w].ends & 0xffff));
+        chunkoff[w] = (off << 3) | (unsigned)b;
+        off += rec[w].bits[b];
+        s = unpack_state(rec[w].ends[b]);
     }
-    if (stats) stats[3] = (uint64_t)C.nchunks;
+    if (stats) { stats[3] = C.nchunks; stats[4] = C.events; }
     HostSink sink{out, cap, 0, false};                            // C
     for (int64_t w = 0; w < C.nchunks; ++w) {
-        load_chunk(C, w, L);
-        const int b = (int)(chunkoff[w] & 1);
-        uint64_t begin = chunkoff[w] >> 1;
+        const int b = (int)(chunkoff[w] & 7);
+        uint64_t begin = chunkoff[w] >> 3;
         for (int l = 1; l < 32; ++l) {
+            lane_block(C, w, l, L[l]);
             const LaneRec &lr = lanerec[w * 32 + l];
-            State st = unpack_state(b ? (lr.starts >> 16) : (lr.starts & 0xffff));
-            const uint32_t mybits = b ? (lr.bits >> 16) : (lr.bits & 0xffff);
-            if (sync && (l - 1) % SYNC_STRIDE == 0) {              // sync entry of lanes l .. l+3 (rlgr.cu, emit kernel)
-                uint32_t first = SYNC_NONE;
-                for (int o = 0; o < SYNC_STRIDE && l + o < 32 && first == SYNC_NONE; ++o)
-                    for (int i = 0; i < L[l + o].len; ++i)
-                        if (L[l + o].row[i]) { first = (uint32_t)(o * BLOCK_SYMS + i); break; }
-                const int k = (l - 1) / SYNC_STRIDE;
-                sync[2 * (w * SYNC_PER_CHUNK + k) + 0] = (uint32_t)begin;
-                sync[2 * (w * SYNC_PER_CHUNK + k) + 1] = (uint32_t)((begin >> 32) & 0x7f) | ((uint32_t)(st.kP & 0x7f) << 7) |
-                                                         ((uint32_t)(st.kRP & 0xff) << 14) | (first << 22);
-            }
+            const int sel = (int)((lr.sel >> (4 * b)) & (NCAND - 1));
+            State st = unpack_state(lr.starts[sel]);
+            const uint32_t mybits = lr.bits[sel];
+            if (mybits == 0) continue;
             sink.pos = begin;
-            if (mybits) code_block(L[l].row.data(), L[l].len, L[l].mask, L[l].zeros_before, L[l].is_tail, st, sink);
+            int64_t pos = -1;
+            bool quirk = false;
+            for (int i = 0; i < L[l].cnt; ++i) {
+                const Event e = L[l].at(i);
+                if (i == 0) pos = (int64_t)C.blockpos[w * CHUNK_LANES - 1 + l] - (int64_t)e.gap - 1;
+                const int64_t np = pos + (int64_t)e.gap + 1;
+                if (sync && (np >> SYNC_SHIFT) != (pos >> SYNC_SHIFT)) {     // first event of its 512-symbol range
+                    const uint64_t at = sink.pos;
+                    sync[2 * (np >> SYNC_SHIFT) + 0] = (uint32_t)at;
+                    sync[2 * (np >> SYNC_SHIFT) + 1] = (uint32_t)((at >> 32) & 0x7f) | ((uint32_t)(st.kP & 0x7f) << 7) |
+                                                       ((uint32_t)(st.kRP & 0xff) << 14) | ((uint32_t)(np & (SYNC_RANGE - 1)) << 22);
+                }
+                pos = np;
+                quirk = emit_event(st, e.gap, e.u, sink);
+            }
+            if (L[l].is_tail) code_tail(st, L[l].tail_zeros, quirk, sink);
             if (sink.pos != begin + mybits) return -1000 - l;     // length bookkeeping broken
             begin += mybits;
         }
@@ -288,14 +366,10 @@ __attribute__((visibility("default"))) void emu_rlgr_decode(const uint8_t *buf, 
         decode_range(br, initial_state(), -1, n, flag_signed, out);
         return;
     }
-    const int64_t nblk = (n + BLOCK_SYMS - 1) / BLOCK_SYMS, nchunks = (nblk + CHUNK_LANES - 1) / CHUNK_LANES;
-    for (int64_t e = 0; e < nchunks * SYNC_PER_CHUNK; ++e) {
-        const int64_t w = e / SYNC_PER_CHUNK;
-        const int k = (int)(e - w * SYNC_PER_CHUNK);
-        const int64_t start = (w * CHUNK_LANES + (int64_t)k * SYNC_STRIDE) * BLOCK_SYMS;
-        if (start >= n) continue;
-        const int nblocks = std::min(SYNC_STRIDE, CHUNK_LANES - k * SYNC_STRIDE);
-        const int64_t end = std::min<int64_t>(start + (int64_t)nblocks * BLOCK_SYMS, n);
+    const int64_t entries = (n + SYNC_RANGE - 1) >> SYNC_SHIFT;
+    for (int64_t e = 0; e < entries; ++e) {
+        const int64_t start = e << SYNC_SHIFT;
+        const int64_t end = std::min<int64_t>(start + SYNC_RANGE, n);
         const uint32_t x = sync[2 * e], y = sync[2 * e + 1];
         const uint32_t first = y >> 22;
         if (first == SYNC_NONE || start + first >= end) continue;

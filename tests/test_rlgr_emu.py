@@ -1,4 +1,4 @@
-"""CPU tests of the chunk-parallel RLGR ALGORITHM (event blocks, speculation sweeps, resolve, emit)
+"""CPU tests of the chunk-parallel RLGR ALGORITHM (event compaction, speculation, resolve, emit)
 through the host warp emulation tests/emu/rlgr_emu.cpp, which compiles the same arithmetic header as
 the CUDA kernels (csrc/rlgr_core.cuh).  Checked against the oracle restatement of membuf.cpp, against
 the reference's own coder (oracle/_ref) when built, and against the golden KATs."""
@@ -20,19 +20,20 @@ def emu():
     subprocess.run(["make", "-C", EMU_DIR], check=True, capture_output=True)
     lib = C.CDLL(os.path.join(EMU_DIR, "_build", "librlgr_emu.so"))
     lib.emu_rlgr_encode.restype = C.c_int64
-    lib.emu_rlgr_encode.argtypes = [C.c_void_p, C.c_int64, C.c_int, C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p, C.c_int, C.c_int]
+    lib.emu_rlgr_encode.argtypes = [C.c_void_p, C.c_int64, C.c_int, C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p, C.c_int, C.c_int,
+                                    C.c_int]
 
-    def encode(q, flag_signed=1, sweeps=2, c1_kp=9):
+    def encode(q, flag_signed=1, mode=0, c1_kp=9, spec_rounds=0):
         q = np.ascontiguousarray(q, dtype=np.int32)
         cap = q.size * 12 + 64
         out = np.zeros(cap, dtype=np.uint8)
-        stats = np.zeros(4, dtype=np.uint64)
-        nchunks = ((q.size + 127) // 128 + 30) // 31
-        sync = np.zeros((max(nchunks, 1) * 8, 2), dtype=np.uint32)
+        stats = np.zeros(8, dtype=np.uint64)
+        entries = (q.size + 511) // 512
+        sync = np.full((max(entries, 1), 2), 0xffffffff, dtype=np.uint32)       # "no event in this range"
         nb = lib.emu_rlgr_encode(q.ctypes.data, q.size, flag_signed, out.ctypes.data, cap, stats.ctypes.data, sync.ctypes.data,
-                                 sweeps, c1_kp)
+                                 mode, c1_kp, spec_rounds)
         assert nb >= 0, nb
-        return out[:nb].tobytes(), stats, sync[:nchunks * 8]
+        return out[:nb].tobytes(), stats, sync[:entries]
 
     lib.emu_rlgr_decode.restype = None
     lib.emu_rlgr_decode.argtypes = [C.c_void_p, C.c_int64, C.c_int64, C.c_int, C.c_void_p, C.c_void_p]
@@ -58,9 +59,10 @@ def test_emu_matches_oracle_over_densities(emu, sigma):
     rng = np.random.default_rng(int(sigma * 100) + 1)
     q = np.rint(rng.laplace(0, sigma, 150000)) if sigma > 0 else np.zeros(150000)
     q = np.clip(q, -2**31 + 1, 2**31 - 1).astype(np.int64)
-    for sweeps in (1, 2, 3):
-        got, stats, _ = emu(q, 1, sweeps=sweeps)
-        assert got == orc.rlgr_encode(q, 1), (sigma, sweeps)
+    for mode in (0, 1, 2):                     # kernel rule / always two canonical states / always one
+        for spec_rounds in (0, 1, 2, 40):      # 1: every chain is left incomplete -> everything is repaired
+            got, stats, _ = emu(q, 1, mode=mode, spec_rounds=spec_rounds)
+            assert got == orc.rlgr_encode(q, 1), (sigma, mode, spec_rounds)
     if orc.ref_rlgr_available():
         assert got == orc.ref_rlgr_encode(q, 1)[0]
 
@@ -71,10 +73,12 @@ def test_emu_regime_changes_edges_and_unsigned(emu):
     q = np.concatenate(parts).astype(np.int64)
     got, stats, sync = emu(q, 1)
     assert got == orc.rlgr_encode(q, 1)
-    assert stats[3] * 8 == len(sync)
+    assert stats[4] == np.count_nonzero(q) and stats[3] == max(1, -(-max(1, -(-int(stats[4]) // 128)) // 31))
     for n in (1, 2, 127, 128, 129, 3967, 3968, 3969, 7936, 7937, 12001):
         for last in (None, 0, -1, 7):
             y = np.rint(rng.laplace(0, 0.7, n)).astype(np.int64)
+            if n > 200:
+                y[y == 0] = 1                       # all non-zero: the event count hits the block / chunk edges exactly
             if last is not None:
                 y[-1] = last
             for fs in (1, 0):
