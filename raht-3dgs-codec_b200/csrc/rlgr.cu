@@ -220,32 +220,79 @@ __device__ __forceinline__ LaneBlock lane_block(const uint2 *__restrict__ ev, co
     return B;
 }
 
-// Code lengths of the lane's block for NC candidate start states side by side (independent chains).  s[] in/out.
-template <int NC> __device__ __forceinline__ void count_lane(const LaneBlock &B, State *s, uint32_t *bits)
+// Code lengths of the lane's block for NC candidate start states side by side.  s[] in/out.  The candidates are
+// independent dependency chains kept in registers; for NC > 1 their zero runs advance together in one loop of
+// predicated steps (separate data-dependent loops would serialise the chains and multiply the trip count the warp
+// pays by NC).
+template <int NC> __device__ __forceinline__ void count_lane(const LaneBlock &B, State *s_io, uint32_t *bits_out)
 {
     const int lane = threadIdx.x & 31;
+    int kP[NC], kRP[NC];
+    uint32_t bits[NC];
     bool quirk[NC];
 #pragma unroll
-    for (int c = 0; c < NC; ++c) { bits[c] = 0; quirk[c] = false; }
+    for (int c = 0; c < NC; ++c) { kP[c] = s_io[c].kP; kRP[c] = s_io[c].kRP; bits[c] = 0; quirk[c] = false; }
     const int units = (B.cnt + EV_GROUP - 1) / EV_GROUP;
     for (int j = 0; j < units; ++j) {
         const uint4 a = __ldg(B.base + (j * 32 + lane) * 2);
         const uint4 b = __ldg(B.base + (j * 32 + lane) * 2 + 1);
         const uint32_t g[4] = {a.x, a.z, b.x, b.z}, u[4] = {a.y, a.w, b.y, b.w};
 #pragma unroll
-        for (int t = 0; t < 4; ++t)
-            if (j * EV_GROUP + t < B.cnt) {
-#pragma unroll
-                for (int c = 0; c < NC; ++c) quirk[c] = count_event(s[c], g[t], u[t], bits[c]);
+        for (int t = 0; t < 4; ++t) {
+            if (j * EV_GROUP + t >= B.cnt) break;
+            if (NC == 1) {
+                State st;
+                st.kP = kP[0]; st.kRP = kRP[0];
+                quirk[0] = count_event(st, g[t], u[t], bits[0]);
+                kP[0] = st.kP; kRP[0] = st.kRP;
+                continue;
             }
-    }
-    if (B.is_tail) {
+            if (g[t]) {                                     // the zero run, all candidates together (code_zeros, lengths only)
+                uint32_t gc[NC];
 #pragma unroll
-        for (int c = 0; c < NC; ++c) {
+                for (int c = 0; c < NC; ++c) gc[c] = g[t];
+                bool more = true;
+                while (more) {
+                    more = false;
+#pragma unroll
+                    for (int c = 0; c < NC; ++c) {
+                        const int k = kP[c] >> 2;
+                        const uint32_t run = 1u << (k & 31);
+                        const bool z0 = k == 0 && gc[c] != 0;               // one zero in no-run mode (membuf.cpp:391-413, u == 0)
+                        const bool zr = k != 0 && gc[c] >= run;             // a complete run (:382-390)
+                        bits[c] += z0 ? 1u + (uint32_t)(kRP[c] >> 2) : (zr ? 1u : 0u);
+                        kRP[c] = z0 ? (kRP[c] < 2 ? 0 : kRP[c] - 2) : kRP[c];
+                        kP[c] += z0 ? RL_U0 : (zr ? RL_U1 : 0);
+                        gc[c] -= z0 ? 1u : (zr ? run : 0u);
+                        more |= z0 || zr;
+                    }
+                }
+            }
+#pragma unroll
+            for (int c = 0; c < NC; ++c) {                  // the non-zero symbol (count_event without its zero run)
+                const int k = kP[c] >> 2;
+                const unsigned kR = (unsigned)(kRP[c] >> 2);
+                const uint32_t v = u[t] - (k ? 1u : 0u);
+                const uint32_t p = kR > 31 ? 0u : (v >> kR);
+                bits[c] += (p < 32 ? p + 1 + kR : 64u) + (k ? 1u + (uint32_t)k : 0u);
+                const int up = kRP[c] + (int)(p > 256u ? 256u : p) - 1;
+                kRP[c] = p ? (up > RL_KRP_MAX ? RL_KRP_MAX : up) : (kRP[c] < 2 ? 0 : kRP[c] - 2);
+                kP[c] = kP[c] < 1 ? 0 : kP[c] - 1;
+                quirk[c] = k != 0 && v == 0;
+            }
+        }
+    }
+#pragma unroll
+    for (int c = 0; c < NC; ++c) {
+        State st;
+        st.kP = kP[c]; st.kRP = kRP[c];
+        if (B.is_tail) {
             CountSink k{0};
-            code_tail(s[c], B.tail_zeros, quirk[c], k);
+            code_tail(st, B.tail_zeros, quirk[c], k);
             bits[c] += k.bits;
         }
+        s_io[c] = st;
+        bits_out[c] = bits[c];
     }
 }
 
