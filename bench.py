@@ -35,6 +35,8 @@ WORKLOADS = {
     "c2": (1_000_000, 12, "3DGS scene 1M Gaussians, 59 channels, depth 12 (BASELINE configs[1])"),
     "c3": (6_000_000, 16, "3DGS scene 6M Gaussians, 59 channels, depth 16 (BASELINE configs[2])"),
     "tiny": (50_000, 10, "smoke-sized scene"),
+    # one scene sharded over the ranks by Morton prefix (raht_b200/sharded.py); --n overrides the 50 M
+    "c4": (50_000_000, 18, "50M-Gaussian synthetic scene, depth 18, Morton-prefix sharding (BASELINE configs[3])"),
 }
 STEP = 1.0 / 64          # uniform quantisation step applied to all 59 channels
 D = 59
@@ -311,6 +313,108 @@ def run_gpu(args):
         dist.destroy_process_group()
 
 
+def run_sharded(args):
+    """BASELINE config 4: ONE scene over all ranks (strong scaling).  Every rank starts with a random 1/P sample of
+    the scene; the timed step = bounding box all_reduce, all_to_all of the raw Gaussians to the owner of their Morton
+    prefix, local voxelise / merge / RAHT, all_gather + join of the P low-pass rows, all_to_all of the quantised
+    coefficients to channel shards, RLGR of whole-scene channels -- and the mirror-image decode."""
+    import torch
+    import torch.distributed as dist
+    import helpers
+    from raht_b200 import ops, sharded
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    n, J, desc = WORKLOADS["c4"]
+    if args.n:
+        n = args.n
+    n_local = n // world
+    scene = helpers.synthetic_gaussians(n_local, 4001 + rank)
+    host = [torch.from_numpy(a).pin_memory() for a in scene]
+    devt = [h.to(dev) for h in host]
+    codec = sharded.ShardedCodec(sharded.DeviceBackend(args.tile_rows))
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def step(inputs):
+        enc = codec.encode(*inputs, J=J, step=STEP)
+        rec = codec.decode(enc)
+        return enc, rec
+
+    for _ in range(args.warmup):
+        enc, rec = step(devt)
+    barrier()
+    clocks = ClockSampler(local)
+    clocks.start()
+    launches0 = ops.lib.raht_launch_count()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    barrier()
+    e0.record()
+    for _ in range(args.steps):
+        enc, rec = step(devt)
+    e1.record()
+    barrier()
+    launches = (ops.lib.raht_launch_count() - launches0) // max(args.steps, 1)
+    clk = clocks.stop()
+    t = torch.tensor([e0.elapsed_time(e1)], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms_step = float(t.item()) / args.steps
+    payload = torch.tensor([float(enc.streams.total_bytes())], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(payload)
+
+    pin_rec = torch.empty(rec.numel(), dtype=rec.dtype).pin_memory()
+    pin_streams = torch.empty(int(enc.streams.buf.numel()), dtype=torch.uint8).pin_memory()
+
+    def step_e2e():
+        dv = [h.to(dev, non_blocking=True) for h in host]
+        enc, rec = step(dv)
+        pin_streams.copy_(enc.streams.buf, non_blocking=True)
+        pin_rec[:rec.numel()].copy_(rec.reshape(-1), non_blocking=True)
+        torch.cuda.synchronize()
+        return enc.streams.total_bytes() + rec.numel() * rec.element_size()
+
+    d2h = step_e2e()
+    barrier()
+    e0.record()
+    for _ in range(args.steps):
+        d2h = step_e2e()
+    e1.record()
+    barrier()
+    t = torch.tensor([e0.elapsed_time(e1)], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms_e2e = float(t.item()) / args.steps
+    if rank == 0:
+        nvox = enc.n_total
+        line = {
+            "metric": "Gaussians/s full RAHT encode+decode (59 ch)", "value": round(n_local * world / (ms_step / 1e3), 1),
+            "unit": "Gaussians/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": round(ms_step, 4),
+            "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+            "config": {"workload": desc, "n_gaussians_total": n_local * world, "nvox": nvox, "depth": J, "channels": D,
+                       "quant_step": STEP, "payload_bytes": int(payload.item()), "bits_per_voxel": round(payload.item() * 8 / nvox, 3),
+                       "parallelism": f"Morton-prefix shards x{world}: NCCL all_reduce (bbox), all_to_all (raw Gaussians), all_gather "
+                                      "(low-pass rows), all_to_all (coefficients -> channel shards); bitstream identical to one GPU",
+                       "l2": "per-rank inputs and intermediates exceed the 126 MB L2; no explicit flush"},
+            "clocks": clk,
+            "e2e": {"value": round(n_local * world / (ms_e2e / 1e3), 1), "unit": "Gaussians/s",
+                    "h2d_bytes_per_step": sum(h.numel() * h.element_size() for h in host), "d2h_bytes_per_step": int(d2h)},
+            "gpu_launches": int(launches), "roofline": None, "cpu_baseline": None,
+        }
+        print(json.dumps(line))
+    if world > 1:
+        dist.destroy_process_group()
+
+
 def run_reference(args):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
@@ -353,7 +457,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--workload", default="c2", choices=sorted(WORKLOADS))
-    ap.add_argument("--n", type=int, default=0, help="override the number of Gaussians")
+    ap.add_argument("--num-gaussians", dest="n", type=int, default=0, help="override the number of Gaussians")
     ap.add_argument("--dtype", default="f64", choices=["f64", "f32"], help="transform arithmetic (f64 = bit-exact mode)")
     ap.add_argument("--tile-rows", type=int, default=0)
     ap.add_argument("--cpu-sample", type=int, default=250_000)
@@ -364,6 +468,8 @@ def main():
     args.tile_rows = args.tile_rows or None
     if args.impl == "reference":
         run_reference(args)
+    elif args.workload == "c4":
+        run_sharded(args)
     else:
         run_gpu(args)
 

@@ -29,7 +29,7 @@
 extern "C" {
 #endif
 
-#define RAHT_B200_ABI_VERSION 6
+#define RAHT_B200_ABI_VERSION 7
 
 enum {
     RAHT_OK = 0,
@@ -158,7 +158,7 @@ int raht_tree_level(const uint8_t *level, int64_t n, int l, int64_t *list, uint8
 /* max over rows>=1 of level[] (-1 when n<=1) -> *max_level (device int32): len(List) = max+1.     */
 int raht_tree_max_level(const uint8_t *level, int64_t n, int32_t *max_level, void *stream);
 
-/* order_RAGFT (RAHT_param.py:219-274): row 0, then rows by descending octree level (level/3),
+/* order_RAGFT (RAHT_param.py:219-274): the root (the row of level 255: row 0), then rows by descending octree level (level/3),
  * ascending row index inside a group.  order (n x int64, optional); position (n x int32, optional)
  * is the inverse permutation (the argsort of encode_3dgs.py:267).                                  */
 size_t raht_order_ragft_workspace_bytes(int64_t n);
@@ -192,6 +192,21 @@ int raht_forward(const raht_plan *plan, const void *C, int c_dtype, int D, void 
                  int flags, void *stream);
 int raht_inverse(const raht_plan *plan, const void *T, int t_dtype, int D, void *C, int flags,
                  void *stream);
+
+/* Top of the tree across Morton-prefix shards (no counterpart in the reference, which is
+ * single-GPU: this is the part of RAHT.py:253-336 / iRAHT.py:40-114 that joins the shards).  The
+ * Morton-sorted voxels of a scene are cut into P contiguous ranges; each range is transformed on its
+ * own (raht_forward on its rows), which leaves its low-pass in its first row.  rows (P, D) holds those
+ * first rows; first_keys[i] = first Morton code of range i, prev_last_keys[i] = last code before range
+ * i (i >= 1), offsets[P+1] = global row index of each range's first row (offsets[P] = rows of the
+ * scene).  Runs the P-1 butterflies that join the ranges in place (inverse != 0: their inverses, in
+ * reverse order) with the arithmetic of raht_forward / raht_inverse: together with the per-range
+ * transforms the coefficients are bit-identical to the transform of the whole scene.
+ * level_out (P bytes, optional): level of each range's first row in the whole scene (255 for range
+ * 0) -- what raht_order_ragft needs for those rows.  One CTA; P <= 1024.                          */
+int raht_shard_top(const int64_t *first_keys, const int64_t *prev_last_keys, const int64_t *offsets,
+                   int P, void *rows, int dtype, int D, int inverse, uint8_t *level_out,
+                   int32_t *status, void *stream);
 
 /* ------------------------------------------------------------------------------------------------
  * (a9,a10,a11) Quantise + reorder + channel marshalling.  Replaces encode_3dgs.py:204 (floor(T/step

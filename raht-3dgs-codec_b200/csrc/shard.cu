@@ -1,0 +1,104 @@
+// shard.cu -- the top of the RAHT tree across Morton-prefix shards (the reference has no
+// multi-GPU path, this is the part of python/RAHT.py:253-336 / python/iRAHT.py:40-114 that joins the
+// shards).  A scene is cut into P contiguous ranges of its Morton-sorted voxels (one per GPU); every
+// range is transformed on its own as if it were a whole cloud, which runs every butterfly whose rows
+// lie inside the range and leaves the range's low-pass row (its first row, weight = rows of the
+// range).  The butterflies that remain join those P rows: row i is merged, at the highest bit in
+// which the first Morton code of range i differs from the last code before it, with the nearest
+// earlier range of a higher level -- the same max-Cartesian tree as plan.cuh, with the weights taken
+// from the ranges' global row offsets instead of 1 per row.  Same arithmetic as transform.cu
+// (separately rounded products and sums), so the coefficients are bit-identical to the single-GPU
+// transform of the whole scene.
+#include "common.cuh"
+
+namespace {
+
+constexpr int TOP_MAX = 1024;
+
+template <typename Tel> struct TopArith;
+template <> struct TopArith<double> {
+    static __device__ __forceinline__ double mul(double a, double b) { return __dmul_rn(a, b); }
+    static __device__ __forceinline__ double add(double a, double b) { return __dadd_rn(a, b); }
+    static __device__ __forceinline__ double sub(double a, double b) { return __dsub_rn(a, b); }
+};
+template <> struct TopArith<float> {
+    static __device__ __forceinline__ float mul(float a, float b) { return __fmul_rn(a, b); }
+    static __device__ __forceinline__ float add(float a, float b) { return __fadd_rn(a, b); }
+    static __device__ __forceinline__ float sub(float a, float b) { return __fsub_rn(a, b); }
+};
+
+// level[i] (i >= 1) = highest bit in which prev_last[i] (the last Morton code before range i) and first[i]
+// differ; offsets[P + 1] = global index of each range's first row, offsets[P] = rows of the scene.
+template <typename Tel>
+__global__ void __launch_bounds__(256) shard_top_kernel(const int64_t *__restrict__ first, const int64_t *__restrict__ prev_last,
+                                                        const int64_t *__restrict__ offsets, int P, Tel *__restrict__ rows, int D,
+                                                        int inverse, uint8_t *__restrict__ level_out, int32_t *status)
+{
+    __shared__ uint8_t lev[TOP_MAX];
+    __shared__ int16_t left[TOP_MAX], right[TOP_MAX];
+    __shared__ double ca[TOP_MAX], cb[TOP_MAX];
+    const int tid = threadIdx.x;
+    for (int i = tid; i < P; i += blockDim.x) {
+        if (i == 0) { lev[0] = 255; continue; }
+        const int64_t a = prev_last[i], b = first[i];
+        if (!(a < b) && status) atomicOr(status, RAHT_ST_NOT_SORTED_UNIQUE);
+        const uint64_t x = (uint64_t)a ^ (uint64_t)b;
+        lev[i] = x ? (uint8_t)(63 - __clzll((long long)x)) : (uint8_t)0;
+    }
+    __syncthreads();
+    for (int i = tid; i < P; i += blockDim.x) {
+        if (level_out) level_out[i] = lev[i];
+        if (i == 0) continue;
+        int s = 0, t = P;
+        for (int j = i - 1; j >= 0; --j) if (lev[j] > lev[i]) { s = j; break; }
+        for (int j = i + 1; j < P; ++j) if (lev[j] > lev[i]) { t = j; break; }
+        left[i] = (int16_t)s;
+        right[i] = (int16_t)t;
+        const double w0 = (double)(offsets[i] - offsets[s]), w1 = (double)(offsets[t] - offsets[i]);
+        const double den = __dadd_rn(w0, w1);                                   // RAHT.py:317
+        ca[i] = __dsqrt_rn(__ddiv_rn(w0, den));                                 // :321
+        cb[i] = __dsqrt_rn(__ddiv_rn(w1, den));                                 // :322
+    }
+    __syncthreads();
+    using AR = TopArith<Tel>;
+    // every thread owns channels tid, tid + 256, ...: the butterflies of a channel run in level order without barriers
+    for (int c = tid; c < D; c += blockDim.x) {
+        for (int ll = 0; ll < 63; ++ll) {
+            const int l = inverse ? 62 - ll : ll;
+            for (int i = 1; i < P; ++i) {
+                if (lev[i] != l) continue;
+                Tel *p0 = rows + (size_t)left[i] * D + c, *p1 = rows + (size_t)i * D + c;
+                const Tel a = (Tel)ca[i], b = (Tel)cb[i], x0 = *p0, x1 = *p1;
+                if (!inverse) {
+                    *p0 = AR::add(AR::mul(a, x0), AR::mul(b, x1));             // RAHT.py:331
+                    *p1 = AR::add(AR::mul(-b, x0), AR::mul(a, x1));            // RAHT.py:332
+                } else {
+                    *p0 = AR::sub(AR::mul(a, x0), AR::mul(b, x1));             // iRAHT.py:108
+                    *p1 = AR::add(AR::mul(b, x0), AR::mul(a, x1));             // iRAHT.py:109
+                }
+            }
+        }
+    }
+}
+
+}  // namespace
+
+RAHT_API int raht_shard_top(const int64_t *first_keys, const int64_t *prev_last_keys, const int64_t *offsets, int P,
+                            void *rows, int dtype, int D, int inverse, uint8_t *level_out, int32_t *status, void *stream)
+{
+    RAHT_REQUIRE(P >= 0 && P <= TOP_MAX && D >= 1, "raht_shard_top: P must be in [0, 1024]");
+    if (P == 0) return RAHT_OK;
+    RAHT_REQUIRE(first_keys && prev_last_keys && offsets && rows, "raht_shard_top: null pointer");
+    cudaStream_t st = (cudaStream_t)stream;
+    raht_count_launches(1);
+    if (dtype == RAHT_F64)
+        shard_top_kernel<double><<<1, 256, 0, st>>>(first_keys, prev_last_keys, offsets, P, (double *)rows, D, inverse, level_out, status);
+    else if (dtype == RAHT_F32)
+        shard_top_kernel<float><<<1, 256, 0, st>>>(first_keys, prev_last_keys, offsets, P, (float *)rows, D, inverse, level_out, status);
+    else {
+        raht_set_error("raht_shard_top: bad dtype");
+        return RAHT_E_INVALID;
+    }
+    RAHT_LAUNCH_CHECK();
+    return RAHT_OK;
+}

@@ -64,7 +64,9 @@ constexpr int OR_IPT = 8;
 constexpr int OR_TILE = OR_THREADS * OR_IPT;
 constexpr int OR_WARPS = OR_THREADS / 32;
 
-__device__ __forceinline__ int or_bucket(int64_t i, uint8_t lev) { return i == 0 ? 0 : 1 + (20 - min((int)lev, 62) / 3); }
+// the root is the row with level 255 (row 0 of a whole cloud; the first row of a Morton-prefix shard other than the
+// first carries its level in the whole scene instead, shard.cu)
+__device__ __forceinline__ int or_bucket(int64_t, uint8_t lev) { return lev == 255 ? 0 : 1 + (20 - min((int)lev, 62) / 3); }
 
 __global__ void __launch_bounds__(OR_THREADS) order_count_kernel(const uint8_t *__restrict__ lev, int64_t n, int64_t nblocks,
                                                                 unsigned long long *counts /* [bucket][block] */)

@@ -62,6 +62,7 @@ SIGNATURES = {
     "raht_quantize_f64": (_i, [_p, _i64, _d, _p, _p]),
     "raht_dequantize_f64": (_i, [_p, _i64, _d, _p, _p]),
     "raht_rlgr_encode_workspace_bytes": (_sz, [_i64, _i]),
+    "raht_shard_top": (_i, [_p, _p, _p, _i, _p, _i, _i, _i, _p, _p, _p]),
     "raht_rlgr_sync_entries": (_i64, [_i64]),
     "raht_rlgr_encode": (_i, [_p, _i64, _i64, _i, _i, _p, _i64, _p, _p, _p, _p, _sz, _p]),
     "raht_rlgr_encode_stats": (_i, [_p, _i64, _i, C.POINTER(C.c_ulonglong), _p]),

@@ -62,21 +62,49 @@ class StageTimer:
         return out
 
 
+def _voxel_params(means, J, given=None):
+    """params4 = (vmin xyz, voxel_size) fp32 and params_d2 = (width, voxel_size) fp64 on the device, from the data
+    (voxelize_pc.py:87-97) or from a given (vmin (3,) tensor, width float) -- the `vmin`, `width` arguments of
+    voxelize_pc_batched, used by the sharded encoder for the bounding box of the whole scene."""
+    import ctypes as C
+    dev = means.device
+    st = stream()
+    bounds = torch.empty(6, dtype=torch.float32, device=dev)
+    params4 = torch.empty(4, dtype=torch.float32, device=dev)
+    params_d2 = torch.empty(2, dtype=torch.float64, device=dev)
+    if given is None:
+        check(lib.raht_bounds3_f32(ptr(means), means.shape[0], 3, ptr(bounds), st), "raht_bounds3_f32")
+        check(lib.raht_voxel_params(ptr(bounds), J, 0, None, 0, 0.0, ptr(params4), ptr(params_d2), st), "raht_voxel_params")
+    else:
+        vmin, width = given
+        vm = (C.c_float * 3)(*[float(x) for x in vmin.detach().cpu().tolist()])
+        bounds.zero_()
+        check(lib.raht_voxel_params(ptr(bounds), J, 1, vm, 1, float(width), ptr(params4), ptr(params_d2), st), "raht_voxel_params")
+    return params4, params_d2
+
+
 @torch.no_grad()
-def voxelize_merge(means, quats, scales, opacities, colors, J, packed_dtype=torch.float32, timer=None, status=None):
+def morton_keys_given(means, J, vmin, width):
+    """Morton codes of the Gaussian centres for a given bounding box (no sort)."""
+    means = means.contiguous().float()
+    params4, _ = _voxel_params(means, J, (vmin, width))
+    keys = torch.empty(means.shape[0], dtype=torch.int64, device=means.device)
+    check(lib.raht_morton_keys_f32(ptr(means), means.shape[0], 3, ptr(params4), J, ptr(keys), None, stream()), "raht_morton_keys_f32")
+    return keys
+
+
+@torch.no_grad()
+def voxelize_merge(means, quats, scales, opacities, colors, J, packed_dtype=torch.float32, timer=None, status=None, given=None):
     """Voxelise the Gaussian centres and merge the Gaussians of each voxel.
     Returns (packed (nvox, D), unique_keys int64 (nvox), info dict).  One synchronisation (the voxel
-    count must reach the host); with a shared `status` word the sort status is left to the caller."""
+    count must reach the host); with a shared `status` word the sort status is left to the caller.
+    given = (vmin, width): quantise against this bounding box instead of the data's."""
     timer = timer or StageTimer(False)
     dev = means.device
     N = means.shape[0]
     st = stream()
     means = means.contiguous().float()
-    bounds = torch.empty(6, dtype=torch.float32, device=dev)
-    params4 = torch.empty(4, dtype=torch.float32, device=dev)
-    params_d2 = torch.empty(2, dtype=torch.float64, device=dev)
-    check(lib.raht_bounds3_f32(ptr(means), N, 3, ptr(bounds), st), "raht_bounds3_f32")
-    check(lib.raht_voxel_params(ptr(bounds), J, 0, None, 0, 0.0, ptr(params4), ptr(params_d2), st), "raht_voxel_params")
+    params4, params_d2 = _voxel_params(means, J, given)
     keys = torch.empty(N, dtype=torch.int64, device=dev)
     check(lib.raht_morton_keys_f32(ptr(means), N, 3, ptr(params4), J, ptr(keys), None, st), "raht_morton_keys_f32")
     timer.mark("morton")

@@ -318,6 +318,19 @@ def inverse(tree: RahtTree, T: torch.Tensor, tile_rows=None, flags=0) -> torch.T
     return Cmat
 
 
+def shard_top(first_keys, prev_last_keys, offsets, rows, inverse=False):
+    """The butterflies that join P Morton-prefix ranges (raht_shard_top): rows (P, D) = the ranges' low-pass rows,
+    transformed in place.  Returns (rows, level (P,) uint8 = level of each range's first row in the whole scene)."""
+    L.require_cuda(rows, "rows")
+    P, D = rows.shape
+    rows = rows.contiguous()
+    level = torch.empty(P, dtype=torch.uint8, device=rows.device)
+    status = _status_word(rows.device)
+    check(lib.raht_shard_top(ptr(first_keys.contiguous()), ptr(prev_last_keys.contiguous()), ptr(offsets.contiguous()), P, ptr(rows),
+                             L.dtype_tag(rows.dtype), D, 1 if inverse else 0, ptr(level), ptr(status), stream()), "raht_shard_top")
+    return rows, level
+
+
 def _steps_tensor(step, D, device):
     if isinstance(step, torch.Tensor):
         s = step.to(device=device, dtype=torch.float64).reshape(-1)
