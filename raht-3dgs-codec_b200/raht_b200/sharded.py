@@ -16,7 +16,8 @@ list of the scene.  One process per GPU, `torch.distributed` (NCCL over NVLink) 
 
 Result: coefficients, order and RLGR bytes are bit-identical to the single-GPU encode of the whole scene
 (tests/test_sharded.py).  The compute goes through a small backend object: `DeviceBackend` (the CUDA
-library) in production; the CPU test-suite plugs the oracle in to exercise the host logic with gloo.
+library) is the only one shipped; the CPU test-suite plugs its own checker backend in to exercise the host
+logic (partition, boundary levels, exchanges) over gloo.
 """
 from dataclasses import dataclass, field
 from typing import List, Optional
