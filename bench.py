@@ -344,9 +344,11 @@ def run_sharded(args):
             dist.barrier()
         torch.cuda.synchronize()
 
-    def step(inputs):
-        enc = codec.encode(*inputs, J=J, step=STEP)
-        rec = codec.decode(enc)
+    from raht_b200.codec import StageTimer
+
+    def step(inputs, timer=None):
+        enc = codec.encode(*inputs, J=J, step=STEP, timer=timer)
+        rec = codec.decode(enc, timer=timer)
         return enc, rec
 
     for _ in range(args.warmup):
@@ -358,12 +360,19 @@ def run_sharded(args):
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     barrier()
     e0.record()
+    timers = []
     for _ in range(args.steps):
-        enc, rec = step(devt)
+        tm = StageTimer(True)
+        enc, rec = step(devt, tm)
+        timers.append(tm)
     e1.record()
     barrier()
     launches = (ops.lib.raht_launch_count() - launches0) // max(args.steps, 1)
     clk = clocks.stop()
+    stages = {}
+    for tm in timers:
+        for k, v in tm.result().items():
+            stages[k] = round(stages.get(k, 0.0) + v / len(timers), 3)
     t = torch.tensor([e0.elapsed_time(e1)], dtype=torch.float64, device=dev)
     if world > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
@@ -408,7 +417,7 @@ def run_sharded(args):
             "clocks": clk,
             "e2e": {"value": round(n_local * world / (ms_e2e / 1e3), 1), "unit": "Gaussians/s",
                     "h2d_bytes_per_step": sum(h.numel() * h.element_size() for h in host), "d2h_bytes_per_step": int(d2h)},
-            "gpu_launches": int(launches), "roofline": None, "cpu_baseline": None,
+            "gpu_launches": int(launches), "roofline": None, "cpu_baseline": None, "stages_rank0_ms": stages,
         }
         print(json.dumps(line))
     if world > 1:

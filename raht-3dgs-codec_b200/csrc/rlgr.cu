@@ -394,8 +394,11 @@ template <int NC> __device__ __forceinline__ void walk_chains(ChunkSol<NC> &S, b
     }
 }
 
+// pin_states[NC]: the candidates of lane 1 when pin (the known state at the chunk start NC times, or the states the
+// previous chunk can end in); pin_need: mask of the pinned candidates whose chains must be complete before stopping.
 template <int NC>
-__device__ __forceinline__ void solve_chunk(const LaneBlock &B, bool pin, State pinned, int max_rounds, ChunkSol<NC> &S)
+__device__ __forceinline__ void solve_chunk(const LaneBlock &B, bool pin, const uint32_t *pin_states, unsigned pin_need,
+                                            int max_rounds, ChunkSol<NC> &S)
 {
     const int lane = threadIdx.x & 31;
     bool has = B.cnt > 0 || B.is_tail;
@@ -408,7 +411,7 @@ __device__ __forceinline__ void solve_chunk(const LaneBlock &B, bool pin, State 
     canon[1].kP = 9;                                        // run mode, the other k_P parity
     canon[1].kRP = RL_KRP_INIT;
     for (int c = 0; c < NC; ++c) {
-        S.in[c] = (pin && lane < 2) ? pack_state(pinned) : pack_state(canon[c < NC / 2 ? 0 : 1]);
+        S.in[c] = (pin && lane < 2) ? pin_states[c] : pack_state(canon[c < NC / 2 ? 0 : 1]);
         S.out[c] = S.in[c];
         S.bits[c] = 0;
     }
@@ -424,7 +427,7 @@ __device__ __forceinline__ void solve_chunk(const LaneBlock &B, bool pin, State 
             for (int c = 0; c < NC; ++c) S.in[c] = S.out[c] = o[c];             // no block: pass the states through
         if (r >= 2) {
             walk_chains<NC>(S, has, src);
-            if (pin ? (S.complete & 1u) : (S.complete != 0)) break;
+            if (pin ? ((S.complete & pin_need) == pin_need) : (S.complete != 0)) break;
         }
         if (lane > 0 && has && r < max_rounds && !(pin && lane == 1)) {
             uint32_t nw[NC];
@@ -499,38 +502,6 @@ template <int NC> __device__ __forceinline__ void finish_chunk(const ChunkSol<NC
     }
 }
 
-// channels that are mostly non-zero run with one candidate (they re-synchronise through k_P = 0 within a block)
-__device__ __forceinline__ bool channel_is_dense(const ChanInfo &I, const Geometry &G) { return (int64_t)I.events * 2 >= G.n; }
-
-// ---- A: speculate ----------------------------------------------------------------------------------------
-constexpr int SPEC_WARPS = 4;
-constexpr int SPEC_ROUNDS = 4;       // speculation: a chain that is not complete by then is left invalid
-constexpr int PIN_ROUNDS = 34;       // chunk 0 and repairs: the pinned chain always completes
-
-template <int NC>
-__global__ void __launch_bounds__(32 * SPEC_WARPS) rlgr_speculate_kernel(Geometry G, const ChanInfo *__restrict__ info,
-                                                                        const uint2 *__restrict__ ev, uint4 *__restrict__ rec,
-                                                                        uint4 *__restrict__ lanerec, unsigned long long *stats)
-{
-    const int ch = blockIdx.y;
-    const int64_t w = (int64_t)blockIdx.x * SPEC_WARPS + (threadIdx.x >> 5);
-    const ChanInfo I = info[ch];
-    if (w >= (int64_t)I.nchunks || channel_is_dense(I, G) != (NC == 1)) return;
-    const size_t ci = (size_t)ch * G.W + w;
-    const LaneBlock B = lane_block(ev, G, ch, w, I);
-    ChunkSol<NC> S;
-    const long long t0 = clock64();
-    solve_chunk<NC>(B, w == 0, initial_state(), w == 0 ? PIN_ROUNDS : SPEC_ROUNDS, S);
-    finish_chunk<NC>(S, rec + ci * REC_WORDS, lanerec + ci * 32 * LANEREC_WORDS);
-    if ((threadIdx.x & 31) == 0 && stats) {
-        atomicAdd(stats + 0, 1ull);
-        atomicAdd(stats + 1, (unsigned long long)S.rounds);
-        // slowest chunk of the pass: cycles << 24 | channel << 8 | rounds
-        atomicMax(stats + 3, ((unsigned long long)(clock64() - t0) << 24) | ((unsigned long long)(ch & 0xffff) << 8) | (unsigned)S.rounds);
-    }
-}
-
-// ---- B: resolve ------------------------------------------------------------------------------------------
 __device__ __forceinline__ uint32_t half_of(const uint4 &v, int c)       // 16-bit entry c of 8
 {
     const uint32_t w = (c >> 1) == 0 ? v.x : (c >> 1) == 1 ? v.y : (c >> 1) == 2 ? v.z : v.w;
@@ -542,6 +513,81 @@ __device__ __forceinline__ uint32_t word_of(const uint4 &a, const uint4 &b, int 
     return (c & 3) == 0 ? v.x : (c & 3) == 1 ? v.y : (c & 3) == 2 ? v.z : v.w;
 }
 
+// channels that are mostly non-zero run with one candidate (they re-synchronise through k_P = 0 within a block)
+__device__ __forceinline__ bool channel_is_dense(const ChanInfo &I, const Geometry &G) { return (int64_t)I.events * 2 >= G.n; }
+
+// ---- A: speculate ----------------------------------------------------------------------------------------
+constexpr int SPEC_WARPS = 4;
+constexpr int SPEC_ROUNDS = 4;       // speculation: a chain that is not complete by then is left invalid
+constexpr int RESPEC_ROUNDS = 6;     // second sweep (candidates = the predecessor's end states)
+constexpr int PIN_ROUNDS = 34;       // chunk 0 and repairs: the pinned chain always completes
+
+// sweep 0: every chunk from the canonical warm-up.  sweep 1: a chunk whose predecessor can end (on one of its
+// complete chains) in a state that is not among the chunk's own valid candidates is solved again with exactly
+// those end states as its candidates -- after the predecessor's 31 blocks they are far better guesses than one
+// warm-up block, and the chains of a run of such chunks are repaired together instead of one after the other in
+// the resolve pass.  Records are double-buffered (rec_prev -> rec) so that the sweep reads a consistent state.
+template <int NC>
+__global__ void __launch_bounds__(32 * SPEC_WARPS) rlgr_speculate_kernel(Geometry G, const ChanInfo *__restrict__ info,
+                                                                        const uint2 *__restrict__ ev, int sweep,
+                                                                        const uint4 *__restrict__ rec_prev, uint4 *__restrict__ rec,
+                                                                        uint4 *__restrict__ lanerec, unsigned long long *stats)
+{
+    const int ch = blockIdx.y;
+    const int64_t w = (int64_t)blockIdx.x * SPEC_WARPS + (threadIdx.x >> 5);
+    const int lane = threadIdx.x & 31;
+    const ChanInfo I = info[ch];
+    if (w >= (int64_t)I.nchunks || channel_is_dense(I, G) != (NC == 1)) return;
+    const size_t ci = (size_t)ch * G.W + w;
+    uint32_t pins[NC];
+    unsigned need = 1u;
+    bool pin = w == 0;
+    for (int c = 0; c < NC; ++c) pins[c] = pack_state(initial_state());
+    if (sweep > 0) {
+        const uint4 *mine = rec_prev + ci * REC_WORDS;
+        bool again = false;
+        if (w > 0) {
+            const uint4 pc = rec_prev[(ci - 1) * REC_WORDS], pe = rec_prev[(ci - 1) * REC_WORDS + 1], mc = mine[0];
+            uint32_t fill = STATE_INVALID;
+            for (int c = 0; c < NC; ++c)
+                if (half_of(pc, c) != STATE_INVALID) {            // a complete chain of the predecessor: its end state
+                    const uint32_t e = half_of(pe, c);
+                    if (fill == STATE_INVALID) fill = e;
+                    bool have = false;
+                    for (int k = 0; k < NC; ++k) have |= half_of(mc, k) == e;
+                    again |= !have;
+                }
+            if (again) {
+                need = 0;
+                for (int c = 0; c < NC; ++c) {
+                    const bool ok = half_of(pc, c) != STATE_INVALID;
+                    pins[c] = ok ? half_of(pe, c) : fill;
+                    bool dup = false;
+                    for (int k = 0; k < c; ++k) dup |= pins[k] == pins[c];
+                    if (ok && !dup) need |= 1u << c;
+                }
+                pin = true;
+            }
+        }
+        if (!again) {                                             // keep the record of the first sweep
+            if (lane < REC_WORDS) rec[ci * REC_WORDS + lane] = mine[lane];
+            return;
+        }
+    }
+    const LaneBlock B = lane_block(ev, G, ch, w, I);
+    ChunkSol<NC> S;
+    const long long t0 = clock64();
+    solve_chunk<NC>(B, pin, pins, need, w == 0 ? PIN_ROUNDS : (sweep ? RESPEC_ROUNDS : SPEC_ROUNDS), S);
+    finish_chunk<NC>(S, rec + ci * REC_WORDS, lanerec + ci * 32 * LANEREC_WORDS);
+    if ((threadIdx.x & 31) == 0 && stats) {
+        atomicAdd(stats + 0, 1ull);
+        atomicAdd(stats + 1, (unsigned long long)S.rounds);
+        // slowest chunk of the pass: cycles << 24 | channel << 8 | rounds
+        atomicMax(stats + 3, ((unsigned long long)(clock64() - t0) << 24) | ((unsigned long long)(ch & 0xffff) << 8) | (unsigned)S.rounds);
+    }
+}
+
+// ---- B: resolve ------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(32) rlgr_resolve_kernel(Geometry G, const ChanInfo *__restrict__ info,
                                                           const uint2 *__restrict__ ev, uint4 *__restrict__ rec,
                                                           uint4 *__restrict__ lanerec, unsigned long long *__restrict__ chunkoff,
@@ -575,14 +621,16 @@ __global__ void __launch_bounds__(32) rlgr_resolve_kernel(Geometry G, const Chan
             const LaneBlock B = lane_block(ev, G, ch, w, I);
             uint4 *lr = lanerec + ci * 32 * LANEREC_WORDS;
             int rounds;
+            uint32_t pins[8];
+            for (int c = 0; c < 8; ++c) pins[c] = ps;
             if (dense) {
                 ChunkSol<1> S;
-                solve_chunk<1>(B, true, s, PIN_ROUNDS, S);
+                solve_chunk<1>(B, true, pins, 1u, PIN_ROUNDS, S);
                 finish_chunk<1>(S, rec + ci * REC_WORDS, lr);
                 rounds = S.rounds;
             } else {
                 ChunkSol<8> S;
-                solve_chunk<8>(B, true, s, PIN_ROUNDS, S);
+                solve_chunk<8>(B, true, pins, 1u, PIN_ROUNDS, S);
                 finish_chunk<8>(S, rec + ci * REC_WORDS, lr);
                 rounds = S.rounds;
             }
@@ -770,7 +818,7 @@ __global__ void __launch_bounds__(DEC_THREADS) rlgr_decode_indexed_kernel(const 
 }
 
 struct EncLayout {
-    size_t off_lastnz, off_cnt, off_info, off_blockpos, off_rec, off_lanerec, off_chunkoff, off_totals, off_stats, off_ev, total;
+    size_t off_lastnz, off_cnt, off_info, off_blockpos, off_rec, off_rec2, off_lanerec, off_chunkoff, off_totals, off_stats, off_ev, total;
 };
 EncLayout enc_layout(int64_t n, int nch)
 {
@@ -782,6 +830,7 @@ EncLayout enc_layout(int64_t n, int nch)
     L.off_info = o; o += align_up(c * sizeof(ChanInfo), 256);
     L.off_blockpos = o; o += align_up(c * nsb * 4, 256);
     L.off_rec = o; o += align_up(c * W * REC_WORDS * 16, 256);
+    L.off_rec2 = o; o += align_up(c * W * REC_WORDS * 16, 256);
     L.off_lanerec = o; o += align_up(c * W * 32 * LANEREC_WORDS * 16, 256);
     L.off_chunkoff = o; o += align_up(c * W * 8, 256);
     L.off_totals = o; o += align_up(c * 8, 256);
@@ -824,7 +873,7 @@ RAHT_API int raht_rlgr_encode(const int32_t *q, int64_t n, int64_t ld, int nch, 
     uint32_t *cnt = (uint32_t *)(ws + L.off_cnt);
     ChanInfo *info = (ChanInfo *)(ws + L.off_info);
     uint32_t *blockpos = (uint32_t *)(ws + L.off_blockpos);
-    uint4 *rec = (uint4 *)(ws + L.off_rec);
+    uint4 *rec0 = (uint4 *)(ws + L.off_rec), *rec = (uint4 *)(ws + L.off_rec2);
     uint4 *lanerec = (uint4 *)(ws + L.off_lanerec);
     unsigned long long *chunkoff = (unsigned long long *)(ws + L.off_chunkoff);
     unsigned long long *totals = (unsigned long long *)(ws + L.off_totals);
@@ -840,9 +889,11 @@ RAHT_API int raht_rlgr_encode(const int32_t *q, int64_t n, int64_t ld, int nch, 
     (raht_count_launches(1), rlgr_scatter_kernel)<<<dim3(groups, nch), 32 * K1_WARPS, 0, st>>>(q, G, cnt, lastnz, ev, blockpos);
     const dim3 cgrid((unsigned)((G.W + SPEC_WARPS - 1) / SPEC_WARPS), nch);
     // channels that are mostly non-zero with one candidate per block, the others with the 8 state classes
-    raht_count_launches(2);
-    rlgr_speculate_kernel<1><<<cgrid, 32 * SPEC_WARPS, 0, st>>>(G, info, ev, rec, lanerec, stats);
-    rlgr_speculate_kernel<8><<<cgrid, 32 * SPEC_WARPS, 0, st>>>(G, info, ev, rec, lanerec, stats);
+    raht_count_launches(4);
+    rlgr_speculate_kernel<1><<<cgrid, 32 * SPEC_WARPS, 0, st>>>(G, info, ev, 0, nullptr, rec0, lanerec, stats);
+    rlgr_speculate_kernel<8><<<cgrid, 32 * SPEC_WARPS, 0, st>>>(G, info, ev, 0, nullptr, rec0, lanerec, stats);
+    rlgr_speculate_kernel<1><<<cgrid, 32 * SPEC_WARPS, 0, st>>>(G, info, ev, 1, rec0, rec, lanerec, stats);
+    rlgr_speculate_kernel<8><<<cgrid, 32 * SPEC_WARPS, 0, st>>>(G, info, ev, 1, rec0, rec, lanerec, stats);
     (raht_count_launches(1), rlgr_resolve_kernel)<<<nch, 32, 0, st>>>(G, info, ev, rec, lanerec, chunkoff, slot_bytes, nbytes,
                                                                     totals, status, stats);
     (raht_count_launches(1), rlgr_zero_kernel)<<<dim3(64, nch), 256, 0, st>>>(streams, slot_bytes, totals);

@@ -211,13 +211,18 @@ class ShardedCodec:
 
     # ---- encode ------------------------------------------------------------------------------------
     @torch.no_grad()
-    def encode(self, means, quats, scales, opacities, colors, J, step, transform_dtype=torch.float64, repartition=True):
+    def encode(self, means, quats, scales, opacities, colors, J, step, transform_dtype=torch.float64, repartition=True, timer=None):
         be, P, r = self.be, self.world, self.rank
+        mark = timer.mark if timer is not None else (lambda name: None)
+        mark("start")
         scene = (means, quats, scales, opacities, colors)
         vmin, width = self.scene_bounds(means)
+        mark("bounds_allreduce")
         if repartition:
             scene = self.repartition(scene, J, vmin, width)
+        mark("repartition_alltoall")
         packed, keys = be.voxelize_merge(scene, J, vmin, width)
+        mark("voxelize_merge")
         n, D = packed.shape
         dev = packed.device
         if n and P > 1:
@@ -240,9 +245,11 @@ class ShardedCodec:
         # local transform: every butterfly inside this range; the range's low-pass is left in its first row
         level = be.levels(keys) if n else torch.empty(0, dtype=torch.uint8, device=dev)
         T = be.forward_local(keys, level, packed, transform_dtype) if n else torch.empty(0, D, dtype=transform_dtype, device=dev)
+        mark("raht_local")
         root = T[0].clone() if n else torch.zeros(D, dtype=transform_dtype, device=dev)
         roots = self._all_gather(root)[nonempty].contiguous()     # (P', D)
         roots, top_level = be.shard_top(first, prev_last, offs, roots, False)       # the butterflies that join the ranges
+        mark("top_allgather_join")
         level_g = level.clone()
         if n:
             me = nonempty.index(r)
@@ -254,29 +261,38 @@ class ShardedCodec:
         bucket_counts = self._all_gather(counts)                  # (P, 22)
         q = be.quant_reorder(T, order, step) if n else torch.empty(D, 0, dtype=torch.int32, device=dev)
         q = q[:, :n].contiguous()                                 # (D, n) channel-major, local bucket order
+        mark("order_quant")
         # row-sharded -> channel-sharded: rank k gets channels k, k + P, ... of every rank
         chans = [list(range(k, D, P)) for k in range(P)]
         parts = [q[chans[k]] for k in range(P)]
         got = self._all_to_all(parts, [len(chans[r]) * n_rows[k] for k in range(P)])
         blocks = [got[k].reshape(len(chans[r]), n_rows[k]) for k in range(P)]
+        mark("coeff_alltoall")
         qg = interleave_buckets(blocks, bucket_counts)            # (|C_r|, N) in order_RAGFT order of the whole scene
+        mark("interleave")
         streams = be.rlgr_encode(qg)
+        mark("rlgr_encode")
         return ShardedEncoded(J=J, D=D, step=step, world=P, rank=r, n_rows=n_rows, keys=keys, first_keys=first,
                               prev_last_keys=prev_last, bucket_counts=bucket_counts, channels=chans[r], streams=streams,
                               vmin=vmin, width=width, transform_dtype=transform_dtype)
 
     # ---- decode ------------------------------------------------------------------------------------
     @torch.no_grad()
-    def decode(self, enc: ShardedEncoded):
+    def decode(self, enc: ShardedEncoded, timer=None):
         """Returns the reconstructed attributes (n_local, D) of this rank's voxels (enc.keys)."""
         be, P, r = self.be, self.world, self.rank
+        mark = timer.mark if timer is not None else (lambda name: None)
+        mark("start_dec")
         D, n_rows = enc.D, enc.n_rows
         n = n_rows[r]
         dev = enc.keys.device
         chans = [list(range(k, D, P)) for k in range(P)]
         qg = be.rlgr_decode(enc.streams)                          # (|C_r|, N)
+        mark("rlgr_decode")
         blocks = deinterleave_buckets(qg, enc.bucket_counts, n_rows)
+        mark("deinterleave")
         got = self._all_to_all([b.contiguous() for b in blocks], [len(chans[k]) * n for k in range(P)])
+        mark("coeff_alltoall_dec")
         q = torch.empty(D, n, dtype=torch.int32, device=dev)
         for k in range(P):
             q[chans[k]] = got[k].reshape(len(chans[k]), n)
@@ -296,9 +312,11 @@ class ShardedCodec:
         root = T[0].clone() if n else torch.zeros(D, dtype=enc.transform_dtype, device=dev)
         roots = self._all_gather(root)[nonempty].contiguous()
         roots, _ = be.shard_top(enc.first_keys, enc.prev_last_keys, offs, roots, True)
+        mark("dequant_top_dec")
         if n:
             T[0] = roots[me]
-            return be.inverse_local(enc.keys, level, T)
+            T = be.inverse_local(enc.keys, level, T)
+        mark("iraht_local")
         return T
 
 

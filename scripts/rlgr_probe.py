@@ -13,7 +13,7 @@ from raht_b200 import codec, ops  # noqa: E402
 
 n = int(sys.argv[1]) if len(sys.argv) > 1 else 1_000_000
 step = float(sys.argv[2]) if len(sys.argv) > 2 else 1.0 / 64
-J = 12
+J = int(os.environ.get("RLGR_PROBE_J", "12"))
 dev = "cuda:0"
 scene = [torch.from_numpy(a).to(dev) for a in helpers.synthetic_gaussians(n, 2001)]
 packed, keys, info = codec.voxelize_merge(*scene, J=J)

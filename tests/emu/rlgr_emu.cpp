@@ -8,6 +8,8 @@
 // tests/test_gpu_parity.py.
 #include "../../raht-3dgs-codec_b200/csrc/rlgr_core.cuh"
 #include <algorithm>
+#include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <vector>
 
@@ -91,7 +93,7 @@ void count_lane(const Lane &B, State &s, uint32_t &bits)
 }
 
 constexpr uint32_t STATE_INVALID = 0xffffu;
-constexpr int SPEC_ROUNDS = 4, REPAIR_ROUNDS = 34;      // as in rlgr.cu
+constexpr int SPEC_ROUNDS = 4, RESPEC_ROUNDS = 6, REPAIR_ROUNDS = 34;      // as in rlgr.cu
 
 struct LaneRes {
     uint32_t in[NCAND], out[NCAND];      // packed states
@@ -137,7 +139,8 @@ void walk_chains(ChunkSol &S, const bool has[32], const int src[32])
 // lanes look at their predecessor's end states of THIS round)
 // pin: lane 0 forwards `pinned` (the known state at the chunk start); else lane 0 codes the block before the chunk
 // as warm-up.  Every other lane starts from the canonical states canon[0], canon[1].
-void solve_chunk(const Lane L[32], bool pin, State pinned, const State canon[2], int max_rounds, bool expand, ChunkSol &S)
+void solve_chunk(const Lane L[32], bool pin, const uint32_t pins[NCAND], unsigned pin_need, const State canon[2], int max_rounds,
+                 bool expand, ChunkSol &S)
 {
     bool has[32], d[32][NCAND];
     int src[32];
@@ -145,7 +148,7 @@ void solve_chunk(const Lane L[32], bool pin, State pinned, const State canon[2],
     uint32_t guess[NCAND], start[NCAND];
     for (int c = 0; c < NCAND; ++c) {
         guess[c] = pack_state(canon[c < NCAND / 2 ? 0 : 1]);
-        start[c] = pin ? pack_state(pinned) : guess[c];
+        start[c] = pin ? pins[c] : guess[c];
     }
     for (int l = 0; l < 32; ++l) {
         has[l] = L[l].cnt > 0 || L[l].is_tail;
@@ -173,8 +176,9 @@ void solve_chunk(const Lane L[32], bool pin, State pinned, const State canon[2],
             for (int l = 1; l < 32; ++l)
                 if (!has[l]) for (int c = 0; c < NCAND; ++c) R[l].in[c] = R[l].out[c] = R[src[l]].out[c];
             walk_chains(S, has, src);
-            bool done = pin ? S.complete[0] : false;
-            if (!pin) for (int c = 0; c < NCAND; ++c) done |= S.complete[c];
+            bool done = pin;
+            if (pin) { for (int c = 0; c < NCAND; ++c) if ((pin_need >> c & 1) && !S.complete[c]) done = false; }
+            else for (int c = 0; c < NCAND; ++c) done |= S.complete[c];
             if (done) break;
         }
         uint32_t o[32][NCAND];
@@ -269,7 +273,7 @@ extern "C" {
 
 // One channel.  out must be zero-filled by the caller (cap bytes).  stats[0] chunk solves in the speculation
 // pass, [1] fixed-point rounds, [2] repairs in the resolve pass, [3] chunks, [4] events, [5] rounds spent in
-// repairs, [6] repairs that needed the exact single-chain fallback.
+// repairs, [6] chunks solved again in the second sweep, [7] repairs where the true state was a candidate whose chain was incomplete.
 // sync (optional): 2 x uint32 per 512 symbols, pre-filled with 0xff by the caller.
 // mode: 0 = the kernel's rule (one canonical state when >= 50 % non-zero), 1 = always two, 2 = always one.
 // c1_kP: k_P of the second canonical start state.  max_spec_rounds: round cap of the speculation pass (0: the kernel's).
@@ -291,9 +295,41 @@ __attribute__((visibility("default"))) int64_t emu_rlgr_encode(const int32_t *q,
     if (single) canon[1] = canon[0];
     for (int64_t w = 0; w < C.nchunks; ++w) {                     // A
         for (int l = 0; l < 32; ++l) lane_block(C, w, l, L[l]);
-        solve_chunk(L, w == 0, initial_state(), canon, max_spec_rounds > 0 ? max_spec_rounds : (w == 0 ? REPAIR_ROUNDS : SPEC_ROUNDS), !single, S);
+        uint32_t pins[NCAND];
+        for (int c = 0; c < NCAND; ++c) pins[c] = pack_state(initial_state());
+        solve_chunk(L, w == 0, pins, 1u, canon, max_spec_rounds > 0 ? max_spec_rounds : (w == 0 ? REPAIR_ROUNDS : SPEC_ROUNDS), !single, S);
         rec[w] = finish_chunk(S, &lanerec[w * 32]);
         if (stats) { stats[0]++; stats[1] += S.rounds; }
+    }
+    {                                                             // A, sweep 1: candidates = the predecessor's end states
+        const std::vector<ChunkRec> prev = rec;
+        const int nce = single ? 1 : NCAND;                       // the dense kernel carries one candidate
+        for (int64_t w = 1; w < C.nchunks; ++w) {
+            bool again = false;
+            uint32_t fill = STATE_INVALID;
+            for (int c = 0; c < nce; ++c)
+                if (prev[w - 1].cand[c] != STATE_INVALID) {
+                    const uint32_t e = prev[w - 1].ends[c];
+                    if (fill == STATE_INVALID) fill = e;
+                    bool have = false;
+                    for (int k = 0; k < nce; ++k) have |= prev[w].cand[k] == e;
+                    again |= !have;
+                }
+            if (!again) continue;
+            uint32_t pins[NCAND];
+            unsigned need = 0;
+            for (int c = 0; c < NCAND; ++c) {
+                const bool ok = c < nce && prev[w - 1].cand[c] != STATE_INVALID;
+                pins[c] = ok ? prev[w - 1].ends[c] : fill;
+                bool dup = false;
+                for (int k = 0; k < c; ++k) dup |= pins[k] == pins[c];
+                if (ok && !dup) need |= 1u << c;
+            }
+            for (int l = 0; l < 32; ++l) lane_block(C, w, l, L[l]);
+            solve_chunk(L, true, pins, need, canon, max_spec_rounds > 0 ? max_spec_rounds : RESPEC_ROUNDS, !single, S);
+            rec[w] = finish_chunk(S, &lanerec[w * 32]);
+            if (stats) { stats[0]++; stats[1] += S.rounds; stats[6]++; }
+        }
     }
     std::vector<uint64_t> chunkoff(C.nchunks);
     State s = initial_state();                                    // B
@@ -303,8 +339,19 @@ __attribute__((visibility("default"))) int64_t emu_rlgr_encode(const int32_t *q,
         int b = -1;
         for (int c = NCAND - 1; c >= 0; --c) if (rec[w].cand[c] == ps) b = c;
         if (b < 0) {
+            if (stats) for (int c = 0; c < NCAND; ++c) if (lanerec[w * 32 + 1].starts[c] == ps) { stats[7]++; break; }   // present, chain incomplete
+            if (getenv("RLGR_EMU_DEBUG")) {
+                fprintf(stderr, "miss chunk %ld true (%d,%d) cands:", (long)w, s.kP, s.kRP);
+                for (int c = 0; c < NCAND; ++c) {
+                    const State t = unpack_state(lanerec[w * 32 + 1].starts[c]);
+                    fprintf(stderr, " (%d,%d)%s", t.kP, t.kRP, rec[w].cand[c] == STATE_INVALID ? "x" : "");
+                }
+                fprintf(stderr, "\n");
+            }
             for (int l = 0; l < 32; ++l) lane_block(C, w, l, L[l]);
-            solve_chunk(L, true, s, canon, REPAIR_ROUNDS, !single, S);
+            uint32_t pins[NCAND];
+            for (int c = 0; c < NCAND; ++c) pins[c] = ps;
+            solve_chunk(L, true, pins, 1u, canon, REPAIR_ROUNDS, !single, S);
             if (stats) stats[5] += S.rounds;
             if (!S.complete[0]) return -2000;                     // the exact chain must always complete
             rec[w] = finish_chunk(S, &lanerec[w * 32]);
