@@ -157,6 +157,35 @@ def stage_bytes(nvox, n_in, payload, J):
     }
 
 
+# kernels of each pipeline stage with their launches per step: DRAM traffic of a stage = sum over its kernels of the
+# per-launch dram__bytes_read.sum + dram__bytes_write.sum of the latest `ncu --set full` capture kept under profiles/
+STAGE_KERNELS = {
+    "rlgr_encode": [("rlgr_count_kernel", 1), ("rlgr_scan_kernel", 1), ("rlgr_scatter_kernel", 1), ("rlgr_speculate_kernel", 2),
+                    ("rlgr_resolve_kernel", 1), ("rlgr_zero_kernel", 1), ("rlgr_emit_kernel", 1)],
+    "rlgr_decode": [("rlgr_decode_indexed_kernel", 1)],
+    "merge": [("merge_kernel<float, 2>", 1)],
+    "raht": [("transform_stage0_kernel<float, double, 59, 1>", 1), ("transform_upper_kernel<double, 1>", 5)],
+    "iraht": [("transform_stage0_kernel<double, double, 59, 0>", 1), ("transform_upper_kernel<double, 0>", 5)],
+    "quant_reorder": [("quant_reorder_kernel<double>", 1)],
+    "dequant_unreorder": [("dequant_unreorder_kernel<double>", 1)],
+}
+
+
+def stage_traffic(stage):
+    """(bytes per step or None, source file) from the newest profiles/*ncu_full*.json (scripts/ncu_full_summary.py)."""
+    import glob
+    files = sorted(glob.glob(os.path.join(ROOT, "profiles", "*ncu_full*.json")))
+    if not files or stage not in STAGE_KERNELS:
+        return None, None
+    prof = json.load(open(files[-1]))
+    total = 0
+    for name, launches in STAGE_KERNELS[stage]:
+        if name not in prof:
+            return None, os.path.basename(files[-1])
+        total += launches * (prof[name]["dram_read_bytes"] + prof[name]["dram_write_bytes"])
+    return int(total), os.path.basename(files[-1])
+
+
 def run_gpu(args):
     import torch
     import torch.distributed as dist
@@ -274,9 +303,12 @@ def run_gpu(args):
     roofline = None
     if dom:
         achieved = sb.get(dom, 0) / (stages[dom] / 1e3) / 1e9
+        traffic, traffic_src = stage_traffic(dom) if args.workload == "c2" and not args.n else (None, None)
         roofline = {"bound": "hbm", "kernel": dom, "achieved": round(achieved, 2), "peak": peak, "unit": "GB/s",
-                    "frac": round(achieved / peak, 4), "traffic": None, "peak_source": peak_src,
-                    "algorithmic_bytes_per_launch": sb.get(dom, 0), "ms_per_launch": round(stages[dom], 4)}
+                    "frac": round(achieved / peak, 4), "traffic": traffic, "traffic_source": traffic_src, "peak_source": peak_src,
+                    "algorithmic_bytes_per_launch": sb.get(dom, 0), "ms_per_launch": round(stages[dom], 4),
+                    "note": "kernel = the pipeline stage with the largest CUDA-event time in this run (a group of kernels, STAGE_KERNELS); "
+                            "per-stage GB/s and fractions are under `stages`"}
     per_stage = {k: {"ms": round(v, 4), "GBps": round(sb.get(k, 0) / (v / 1e3) / 1e9, 1) if v > 0 else None,
                      "frac_of_peak": round(sb.get(k, 0) / (v / 1e3) / 1e9 / peak, 4) if v > 0 else None}
                  for k, v in stages.items()}

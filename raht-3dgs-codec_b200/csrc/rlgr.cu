@@ -528,10 +528,9 @@ constexpr int PIN_ROUNDS = 34;       // chunk 0 and repairs: the pinned chain al
 // warm-up block, and the chains of a run of such chunks are repaired together instead of one after the other in
 // the resolve pass.  Records are double-buffered (rec_prev -> rec) so that the sweep reads a consistent state.
 template <int NC>
-__global__ void __launch_bounds__(32 * SPEC_WARPS) rlgr_speculate_kernel(Geometry G, const ChanInfo *__restrict__ info,
-                                                                        const uint2 *__restrict__ ev, int sweep,
-                                                                        const uint4 *__restrict__ rec_prev, uint4 *__restrict__ rec,
-                                                                        uint4 *__restrict__ lanerec, unsigned long long *stats)
+__device__ __forceinline__ void speculate_chunk(const Geometry &G, const ChanInfo *__restrict__ info, const uint2 *__restrict__ ev,
+                                                int sweep, const uint4 *__restrict__ rec_prev, uint4 *__restrict__ rec,
+                                                uint4 *__restrict__ lanerec, unsigned long long *stats)
 {
     const int ch = blockIdx.y;
     const int64_t w = (int64_t)blockIdx.x * SPEC_WARPS + (threadIdx.x >> 5);
@@ -585,6 +584,17 @@ __global__ void __launch_bounds__(32 * SPEC_WARPS) rlgr_speculate_kernel(Geometr
         // slowest chunk of the pass: cycles << 24 | channel << 8 | rounds
         atomicMax(stats + 3, ((unsigned long long)(clock64() - t0) << 24) | ((unsigned long long)(ch & 0xffff) << 8) | (unsigned)S.rounds);
     }
+}
+
+// one launch for both kinds of channel (blockIdx.z): the few chunks of the sparse channels, bound by the latency
+// of their 8-candidate chains, run under the many chunks of the dense channels, which are bound by issue slots
+__global__ void __launch_bounds__(32 * SPEC_WARPS) rlgr_speculate_kernel(Geometry G, const ChanInfo *__restrict__ info,
+                                                                        const uint2 *__restrict__ ev, int sweep,
+                                                                        const uint4 *__restrict__ rec_prev, uint4 *__restrict__ rec,
+                                                                        uint4 *__restrict__ lanerec, unsigned long long *stats)
+{
+    if (blockIdx.z == 0) speculate_chunk<8>(G, info, ev, sweep, rec_prev, rec, lanerec, stats);
+    else speculate_chunk<1>(G, info, ev, sweep, rec_prev, rec, lanerec, stats);
 }
 
 // ---- B: resolve ------------------------------------------------------------------------------------------
@@ -888,12 +898,9 @@ RAHT_API int raht_rlgr_encode(const int32_t *q, int64_t n, int64_t ld, int nch, 
     (raht_count_launches(1), rlgr_scan_kernel)<<<nch, 1024, 0, st>>>(G, cnt, lastnz, info);
     (raht_count_launches(1), rlgr_scatter_kernel)<<<dim3(groups, nch), 32 * K1_WARPS, 0, st>>>(q, G, cnt, lastnz, ev, blockpos);
     const dim3 cgrid((unsigned)((G.W + SPEC_WARPS - 1) / SPEC_WARPS), nch);
-    // channels that are mostly non-zero with one candidate per block, the others with the 8 state classes
-    raht_count_launches(4);
-    rlgr_speculate_kernel<1><<<cgrid, 32 * SPEC_WARPS, 0, st>>>(G, info, ev, 0, nullptr, rec0, lanerec, stats);
-    rlgr_speculate_kernel<8><<<cgrid, 32 * SPEC_WARPS, 0, st>>>(G, info, ev, 0, nullptr, rec0, lanerec, stats);
-    rlgr_speculate_kernel<1><<<cgrid, 32 * SPEC_WARPS, 0, st>>>(G, info, ev, 1, rec0, rec, lanerec, stats);
-    rlgr_speculate_kernel<8><<<cgrid, 32 * SPEC_WARPS, 0, st>>>(G, info, ev, 1, rec0, rec, lanerec, stats);
+    const dim3 sgrid(cgrid.x, nch, 2);
+    (raht_count_launches(1), rlgr_speculate_kernel)<<<sgrid, 32 * SPEC_WARPS, 0, st>>>(G, info, ev, 0, nullptr, rec0, lanerec, stats);
+    (raht_count_launches(1), rlgr_speculate_kernel)<<<sgrid, 32 * SPEC_WARPS, 0, st>>>(G, info, ev, 1, rec0, rec, lanerec, stats);
     (raht_count_launches(1), rlgr_resolve_kernel)<<<nch, 32, 0, st>>>(G, info, ev, rec, lanerec, chunkoff, slot_bytes, nbytes,
                                                                     totals, status, stats);
     (raht_count_launches(1), rlgr_zero_kernel)<<<dim3(64, nch), 256, 0, st>>>(streams, slot_bytes, totals);
