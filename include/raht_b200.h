@@ -245,10 +245,11 @@ size_t raht_rlgr_encode_workspace_bytes(int64_t n, int nch);
 int raht_rlgr_encode(const int32_t *q, int64_t n, int64_t ld, int nch, int flag_signed,
                      uint8_t *streams, int64_t slot_bytes, int64_t *nbytes, void *sync_index,
                      int32_t *status, void *workspace, size_t workspace_bytes, void *stream);
-/* diagnostics of the last encode on `workspace`: out5_host = {chunk solves in the speculation pass,
+/* diagnostics of the last encode on `workspace`: out6_host = {chunk solves in the speculation pass,
  * their fixed-point rounds, chunks re-solved by the resolve pass, slowest chunk of the speculation
- * pass as SM cycles << 24 | channel << 8 | rounds, rounds spent in the re-solves}.  Synchronises.    */
-int raht_rlgr_encode_stats(const void *workspace, int64_t n, int nch, unsigned long long *out5_host,
+ * pass as SM cycles << 24 | channel << 8 | rounds, rounds spent in the re-solves, chunks settled
+ * through the transition tables}.  Synchronises.                                                     */
+int raht_rlgr_encode_stats(const void *workspace, int64_t n, int nch, unsigned long long *out6_host,
                            void *stream);
 int raht_rlgr_decode(const uint8_t *streams, int64_t slot_bytes, const int64_t *nbytes,
                      const void *sync_index, int64_t n, int64_t ld, int nch, int flag_signed,

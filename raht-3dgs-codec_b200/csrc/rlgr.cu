@@ -198,7 +198,8 @@ __global__ void __launch_bounds__(32 * K1_WARPS) rlgr_scatter_kernel(const int32
 
 // ---- one lane block of the event store ---------------------------------------------------------------------
 struct LaneBlock {
-    const uint4 *base;         // the chunk in the store, as 16-byte units: unit j of this lane at base[(j * 32 + lane) * 2 + {0,1}]
+    const uint4 *base;         // the chunk in the store, as 16-byte units: unit j of store lane `slot` at base[(j * 32 + slot) * 2 + {0,1}]
+    int slot;                  // store lane of the block (= the thread's lane, except in the table pass where a warp shares one block)
     int cnt;                   // events of this lane's block (0: none)
     bool is_tail;              // the block holds the channel's last event (or the channel has none): it also codes the tail
     uint32_t tail_zeros;
@@ -211,6 +212,7 @@ __device__ __forceinline__ LaneBlock lane_block(const uint2 *__restrict__ ev, co
     const int lane = threadIdx.x & 31;
     LaneBlock B;
     B.base = (const uint4 *)(ev + ((size_t)ch * G.W + w) * CHUNK_SLOTS);
+    B.slot = lane;
     const int64_t b = w * CHUNK_LANES - 1 + lane;
     int64_t cnt = (b < 0 || b >= (int64_t)I.nblocks) ? 0 : (int64_t)I.events - b * EV_BLOCK;
     cnt = cnt < 0 ? 0 : (cnt > EV_BLOCK ? EV_BLOCK : cnt);
@@ -226,7 +228,7 @@ __device__ __forceinline__ LaneBlock lane_block(const uint2 *__restrict__ ev, co
 // pays by NC).
 template <int NC> __device__ __forceinline__ void count_lane(const LaneBlock &B, State *s_io, uint32_t *bits_out)
 {
-    const int lane = threadIdx.x & 31;
+    const int lane = B.slot;
     int kP[NC], kRP[NC];
     uint32_t bits[NC];
     bool quirk[NC];
@@ -545,7 +547,7 @@ __device__ __forceinline__ void speculate_chunk(const Geometry &G, const ChanInf
     if (sweep > 0) {
         const uint4 *mine = rec_prev + ci * REC_WORDS;
         bool again = false;
-        if (w > 0) {
+        if (w > 0 && NC == 1) {                                   // (the sparse channels go through the tables instead)
             const uint4 pc = rec_prev[(ci - 1) * REC_WORDS], pe = rec_prev[(ci - 1) * REC_WORDS + 1], mc = mine[0];
             uint32_t fill = STATE_INVALID;
             for (int c = 0; c < NC; ++c)
@@ -576,7 +578,8 @@ __device__ __forceinline__ void speculate_chunk(const Geometry &G, const ChanInf
     const LaneBlock B = lane_block(ev, G, ch, w, I);
     ChunkSol<NC> S;
     const long long t0 = clock64();
-    solve_chunk<NC>(B, pin, pins, need, w == 0 ? PIN_ROUNDS : (sweep ? RESPEC_ROUNDS : SPEC_ROUNDS), S);
+    // (chunk 0 of a dense channel runs until its pinned chain is complete; a sparse one falls back on its table)
+    solve_chunk<NC>(B, pin, pins, need, (w == 0 && NC == 1) ? PIN_ROUNDS : (sweep ? RESPEC_ROUNDS : SPEC_ROUNDS), S);
     finish_chunk<NC>(S, rec + ci * REC_WORDS, lanerec + ci * 32 * LANEREC_WORDS);
     if ((threadIdx.x & 31) == 0 && stats) {
         atomicAdd(stats + 0, 1ull);
@@ -597,19 +600,192 @@ __global__ void __launch_bounds__(32 * SPEC_WARPS) rlgr_speculate_kernel(Geometr
     else speculate_chunk<1>(G, info, ev, sweep, rec_prev, rec, lanerec, stats);
 }
 
+// ---- table mode for the sparse channels ---------------------------------------------------------------------------
+// A sparse channel in run mode with k_R = 0 does not re-synchronise: its block map is one-to-one on the states it
+// visits, and when the values are one-signed (position channels: no p = 0 event ever clamps k_RP) the classes are
+// more than a handful of candidates can cover.  There the block's transition is tabulated instead of guessed:
+//   T1  warp per block: the block coded from all 128 states of a window (16 k_P x 8 k_RP values around the state the
+//       first sweep estimated at the block's start), 4 states per lane as independent chains, events broadcast;
+//   T2  warp per chunk: the 128 states of its first block's window followed through the 31 tables;
+//   resolve looks the true state up in the chunk's table (falls back to the candidate records / a pinned repair when
+//       it lies outside the window or its chain leaves a later window);
+//   T3  the chunks resolved that way get their lane records from one more walk through the tables.
+// Exact by construction: a table entry is the coder's own arithmetic from that state.
+constexpr int TAB_KP = 16, TAB_KRP = 8, TAB_STATES = TAB_KP * TAB_KRP;       // 128 = 32 lanes x 4
+constexpr uint32_t TAB_DEAD = 0xffffu;
+
+__device__ __forceinline__ uint32_t tab_window(uint32_t centre)      // packed (k_P0, k_RP0) of the window around a state
+{
+    const State c = unpack_state(centre);
+    State w;
+    w.kP = c.kP > 6 ? c.kP - 6 : 0;
+    w.kRP = c.kRP > 3 ? c.kRP - 3 : 0;
+    return pack_state(w);
+}
+__device__ __forceinline__ int tab_index(uint32_t window, uint32_t state)    // -1: outside
+{
+    if (window == 0xffffffffu) return -1;
+    const State w = unpack_state(window), s = unpack_state(state);
+    const int a = s.kP - w.kP, b = s.kRP - w.kRP;
+    return (a >= 0 && a < TAB_KP && b >= 0 && b < TAB_KRP) ? a * TAB_KRP + b : -1;
+}
+__device__ __forceinline__ uint32_t tab_state(uint32_t window, int idx)
+{
+    State s = unpack_state(window);
+    s.kP += idx / TAB_KRP;
+    s.kRP += idx % TAB_KRP;
+    return pack_state(s);
+}
+
+// Only the chunks the candidate records may fail on are tabulated: no complete chain of their own, or a complete
+// chain of the predecessor ending in a state they do not have (in a stretch of such chunks every one qualifies).
+constexpr uint32_t TAB_NO_WINDOW = 0xffffffffu;
+__device__ __forceinline__ bool chunk_suspect1(const uint4 *__restrict__ rec, size_t ci, int64_t w)
+{
+    const uint4 mc = rec[ci * REC_WORDS];
+    bool any = false;
+    for (int c = 0; c < 8; ++c) any |= half_of(mc, c) != STATE_INVALID;
+    if (!any) return true;
+    if (w == 0) return false;
+    const uint4 pc = rec[(ci - 1) * REC_WORDS], pe = rec[(ci - 1) * REC_WORDS + 1];
+    for (int c = 0; c < 8; ++c)
+        if (half_of(pc, c) != STATE_INVALID) {
+            const uint32_t e = half_of(pe, c);
+            bool have = false;
+            for (int k = 0; k < 8; ++k) have |= half_of(mc, k) == e;
+            if (!have) return true;
+        }
+    return false;
+}
+
+// ... and the two chunks behind such a chunk: the state a table hands on need not be one the next chunks guessed
+__device__ __forceinline__ bool chunk_suspect(const uint4 *__restrict__ rec, size_t ci, int64_t w)
+{
+    return chunk_suspect1(rec, ci, w) || (w >= 1 && chunk_suspect1(rec, ci - 1, w - 1)) || (w >= 2 && chunk_suspect1(rec, ci - 2, w - 2));
+}
+
+// tables: uint32 [channel][block][128] = end state | bits << 16; headers: uint32 [channel][block] = window
+__global__ void __launch_bounds__(32 * SPEC_WARPS) rlgr_table_kernel(Geometry G, const ChanInfo *__restrict__ info,
+                                                                    const uint2 *__restrict__ ev, const uint4 *__restrict__ rec,
+                                                                    const uint4 *__restrict__ lanerec,
+                                                                    uint32_t *__restrict__ tables, uint32_t *__restrict__ headers)
+{
+    const int ch = blockIdx.y;
+    const int64_t b = (int64_t)blockIdx.x * SPEC_WARPS + (threadIdx.x >> 5);
+    const int lane = threadIdx.x & 31;
+    const ChanInfo I = info[ch];
+    if (b >= (int64_t)I.nblocks || channel_is_dense(I, G)) return;
+    const int64_t w = b / CHUNK_LANES;
+    const int l = (int)(b - w * CHUNK_LANES) + 1;
+    if (!chunk_suspect(rec, (size_t)ch * G.W + w, w)) {
+        if (lane == 0) headers[(size_t)ch * G.nsb + b] = TAB_NO_WINDOW;
+        return;
+    }
+    LaneBlock B;
+    B.base = (const uint4 *)(ev + ((size_t)ch * G.W + w) * CHUNK_SLOTS);
+    B.slot = l;
+    int64_t cnt = (int64_t)I.events - b * EV_BLOCK;
+    B.cnt = (int)(cnt < 0 ? 0 : (cnt > EV_BLOCK ? EV_BLOCK : cnt));
+    B.is_tail = b == (int64_t)I.nblocks - 1;
+    B.tail_zeros = I.tail_zeros;
+    // window around the first sweep's estimate of the state at the block's start (slot 1 of the lane's candidates)
+    const uint4 lr0 = lanerec[(((size_t)ch * G.W + w) * 32 + l) * LANEREC_WORDS];
+    const uint32_t window = tab_window(half_of(lr0, 1));
+    State st[4];
+    uint32_t bits[4];
+#pragma unroll
+    for (int k = 0; k < 4; ++k) st[k] = unpack_state(tab_state(window, lane * 4 + k));
+    count_lane<4>(B, st, bits);
+    uint32_t *T = tables + ((size_t)ch * G.nsb + b) * TAB_STATES;
+    uint4 out;
+    out.x = pack_state(st[0]) | (bits[0] << 16); out.y = pack_state(st[1]) | (bits[1] << 16);
+    out.z = pack_state(st[2]) | (bits[2] << 16); out.w = pack_state(st[3]) | (bits[3] << 16);
+    ((uint4 *)T)[lane] = out;
+    if (lane == 0) headers[(size_t)ch * G.nsb + b] = window;
+}
+
+// chunk tables: uint2 [channel][chunk][128] = (end state or TAB_DEAD, code length of the chunk)
+__global__ void __launch_bounds__(32 * SPEC_WARPS) rlgr_chunk_table_kernel(Geometry G, const ChanInfo *__restrict__ info,
+                                                                          const uint32_t *__restrict__ tables,
+                                                                          const uint32_t *__restrict__ headers,
+                                                                          uint2 *__restrict__ ctab)
+{
+    const int ch = blockIdx.y;
+    const int64_t w = (int64_t)blockIdx.x * SPEC_WARPS + (threadIdx.x >> 5);
+    const int lane = threadIdx.x & 31;
+    const ChanInfo I = info[ch];
+    if (w >= (int64_t)I.nchunks || channel_is_dense(I, G)) return;
+    const int64_t b0 = w * CHUNK_LANES;
+    const int nb = (int)min((int64_t)CHUNK_LANES, (int64_t)I.nblocks - b0);
+    const uint32_t *H = headers + (size_t)ch * G.nsb + b0;
+    const uint32_t *T = tables + ((size_t)ch * G.nsb + b0) * TAB_STATES;
+    uint32_t s[4], bits[4] = {0, 0, 0, 0};
+    const uint32_t w0 = H[0];
+    if (w0 == TAB_NO_WINDOW) return;                      // not tabulated: the resolve pass sees no window
+#pragma unroll
+    for (int k = 0; k < 4; ++k) s[k] = tab_state(w0, lane * 4 + k);
+    for (int j = 0; j < nb; ++j) {
+        const uint32_t win = H[j];
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+            const int idx = s[k] == TAB_DEAD ? -1 : tab_index(win, s[k]);
+            if (idx < 0) { s[k] = TAB_DEAD; continue; }
+            const uint32_t e = T[(size_t)j * TAB_STATES + idx];
+            s[k] = e & 0xffffu;
+            bits[k] += e >> 16;
+        }
+    }
+    uint2 *C = ctab + ((size_t)ch * G.W + w) * TAB_STATES + lane * 4;
+#pragma unroll
+    for (int k = 0; k < 4; ++k) C[k] = make_uint2(s[k], bits[k]);
+}
+
+// lane records of the chunks the resolve pass settled through the tables (cstart = true state | 1 << 16)
+__global__ void __launch_bounds__(32 * SPEC_WARPS) rlgr_table_lanes_kernel(Geometry G, const ChanInfo *__restrict__ info,
+                                                                          const uint32_t *__restrict__ tables,
+                                                                          const uint32_t *__restrict__ headers,
+                                                                          const uint32_t *__restrict__ cstart, uint4 *__restrict__ lanerec)
+{
+    const int ch = blockIdx.y;
+    const int64_t w = (int64_t)blockIdx.x * SPEC_WARPS + (threadIdx.x >> 5);
+    const int lane = threadIdx.x & 31;
+    const ChanInfo I = info[ch];
+    if (w >= (int64_t)I.nchunks || channel_is_dense(I, G)) return;
+    const size_t ci = (size_t)ch * G.W + w;
+    const uint32_t cs = cstart[ci];
+    if (!(cs >> 16)) return;
+    const int64_t b0 = w * CHUNK_LANES;
+    const int nb = (int)min((int64_t)CHUNK_LANES, (int64_t)I.nblocks - b0);
+    const uint32_t *H = headers + (size_t)ch * G.nsb + b0;
+    const uint32_t *T = tables + ((size_t)ch * G.nsb + b0) * TAB_STATES;
+    uint32_t s = cs & 0xffffu, mine_s = s, mine_b = 0;
+    for (int j = 0; j < nb; ++j) {                        // every lane walks; lane j + 1 keeps block j
+        const uint32_t e = T[(size_t)j * TAB_STATES + tab_index(H[j], s)];
+        if (lane == j + 1) { mine_s = s; mine_b = e >> 16; }
+        s = e & 0xffffu;
+    }
+    if (lane > nb) mine_s = s;                            // lanes without a block: the state passes through
+    uint4 *lr = lanerec + (ci * 32 + lane) * LANEREC_WORDS;
+    lr[0] = make_uint4(mine_s, 0u, 0u, 0u);
+    lr[1] = make_uint4(lane == 0 ? 0u : mine_b, 0u, 0u, 0u);
+    lr[2] = make_uint4(0u, 0u, 0u, 0u);
+}
+
 // ---- B: resolve ------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(32) rlgr_resolve_kernel(Geometry G, const ChanInfo *__restrict__ info,
                                                           const uint2 *__restrict__ ev, uint4 *__restrict__ rec,
                                                           uint4 *__restrict__ lanerec, unsigned long long *__restrict__ chunkoff,
                                                           int64_t slot_bytes, int64_t *__restrict__ nbytes,
                                                           unsigned long long *__restrict__ totals, int32_t *status,
-                                                          unsigned long long *stats)
+                                                          unsigned long long *stats, const uint32_t *__restrict__ headers,
+                                                          const uint2 *__restrict__ ctab, uint32_t *__restrict__ cstart)
 {
     const int ch = blockIdx.x;
     const int lane = threadIdx.x & 31;
     const ChanInfo I = info[ch];
     const int64_t nchunks = I.nchunks;
     const bool dense = channel_is_dense(I, G);
+    unsigned long long table_hits = 0;
     State s = initial_state();
     unsigned long long off = 0;
     unsigned long long repairs = 0, repair_rounds = 0;
@@ -627,6 +803,21 @@ __global__ void __launch_bounds__(32) rlgr_resolve_kernel(Geometry G, const Chan
         r0.z = __shfl_sync(~0u, m0.z, i); r0.w = __shfl_sync(~0u, m0.w, i);
         const uint32_t ps = pack_state(s);
         unsigned hit = __ballot_sync(~0u, lane < 8 && half_of(r0, lane & 7) == ps);
+        if (!dense) {
+            if (lane == 0) cstart[ci] = 0u;
+            if (!hit) {                                           // sparse channel: the chunk's transition table
+                const int idx = tab_index(headers[(size_t)ch * G.nsb + w * CHUNK_LANES], ps);
+                uint2 e = make_uint2(TAB_DEAD, 0u);
+                if (idx >= 0) e = ctab[ci * TAB_STATES + idx];
+                if (e.x != TAB_DEAD) {
+                    if (lane == 0) { chunkoff[ci] = off << 3; cstart[ci] = ps | (1u << 16); }
+                    off += e.y;
+                    s = unpack_state(e.x);
+                    ++table_hits;
+                    continue;
+                }
+            }
+        }
         if (!hit) {                                               // no candidate was the true state: solve this chunk from it
             const LaneBlock B = lane_block(ev, G, ch, w, I);
             uint4 *lr = lanerec + ci * 32 * LANEREC_WORDS;
@@ -661,7 +852,7 @@ __global__ void __launch_bounds__(32) rlgr_resolve_kernel(Geometry G, const Chan
         nbytes[ch] = nb;
         totals[ch] = off;
         if (nb > slot_bytes && status) atomicOr(status, RAHT_ST_STREAM_OVERFLOW);
-        if (stats) { atomicAdd(stats + 2, repairs); atomicAdd(stats + 4, repair_rounds); }
+        if (stats) { atomicAdd(stats + 2, repairs); atomicAdd(stats + 4, repair_rounds); atomicAdd(stats + 5, table_hits); }
     }
 }
 
@@ -828,7 +1019,7 @@ __global__ void __launch_bounds__(DEC_THREADS) rlgr_decode_indexed_kernel(const 
 }
 
 struct EncLayout {
-    size_t off_lastnz, off_cnt, off_info, off_blockpos, off_rec, off_rec2, off_lanerec, off_chunkoff, off_totals, off_stats, off_ev, total;
+    size_t off_lastnz, off_cnt, off_info, off_blockpos, off_rec, off_rec2, off_lanerec, off_chunkoff, off_totals, off_stats, off_ev, off_tables, off_headers, off_ctab, off_cstart, total;
 };
 EncLayout enc_layout(int64_t n, int nch)
 {
@@ -846,6 +1037,10 @@ EncLayout enc_layout(int64_t n, int nch)
     L.off_totals = o; o += align_up(c * 8, 256);
     L.off_stats = o; o += 256;
     L.off_ev = o; o += align_up(c * W * CHUNK_SLOTS * 8, 256);
+    L.off_tables = o; o += align_up(c * nsb * TAB_STATES * 4, 256);
+    L.off_headers = o; o += align_up(c * nsb * 4, 256);
+    L.off_ctab = o; o += align_up(c * W * TAB_STATES * 8, 256);
+    L.off_cstart = o; o += align_up(c * W * 4, 256);
     L.total = o + 256;
     return L;
 }
@@ -889,6 +1084,9 @@ RAHT_API int raht_rlgr_encode(const int32_t *q, int64_t n, int64_t ld, int nch, 
     unsigned long long *totals = (unsigned long long *)(ws + L.off_totals);
     unsigned long long *stats = (unsigned long long *)(ws + L.off_stats);
     uint2 *ev = (uint2 *)(ws + L.off_ev);
+    uint32_t *tables = (uint32_t *)(ws + L.off_tables), *headers = (uint32_t *)(ws + L.off_headers);
+    uint2 *ctab = (uint2 *)(ws + L.off_ctab);
+    uint32_t *cstart = (uint32_t *)(ws + L.off_cstart);
     RAHT_CUDA(cudaMemsetAsync(stats, 0, 256, st));
     const int64_t entries = raht_rlgr_sync_entries(n);
     if (sync_index) RAHT_CUDA(cudaMemsetAsync(sync_index, 0xff, (size_t)nch * entries * 8, st));   // "no event in this range"
@@ -901,8 +1099,12 @@ RAHT_API int raht_rlgr_encode(const int32_t *q, int64_t n, int64_t ld, int nch, 
     const dim3 sgrid(cgrid.x, nch, 2);
     (raht_count_launches(1), rlgr_speculate_kernel)<<<sgrid, 32 * SPEC_WARPS, 0, st>>>(G, info, ev, 0, nullptr, rec0, lanerec, stats);
     (raht_count_launches(1), rlgr_speculate_kernel)<<<sgrid, 32 * SPEC_WARPS, 0, st>>>(G, info, ev, 1, rec0, rec, lanerec, stats);
+    const dim3 bgrid((unsigned)((G.nsb + SPEC_WARPS - 1) / SPEC_WARPS), nch);
+    (raht_count_launches(1), rlgr_table_kernel)<<<bgrid, 32 * SPEC_WARPS, 0, st>>>(G, info, ev, rec, lanerec, tables, headers);
+    (raht_count_launches(1), rlgr_chunk_table_kernel)<<<cgrid, 32 * SPEC_WARPS, 0, st>>>(G, info, tables, headers, ctab);
     (raht_count_launches(1), rlgr_resolve_kernel)<<<nch, 32, 0, st>>>(G, info, ev, rec, lanerec, chunkoff, slot_bytes, nbytes,
-                                                                    totals, status, stats);
+                                                                    totals, status, stats, headers, ctab, cstart);
+    (raht_count_launches(1), rlgr_table_lanes_kernel)<<<cgrid, 32 * SPEC_WARPS, 0, st>>>(G, info, tables, headers, cstart, lanerec);
     (raht_count_launches(1), rlgr_zero_kernel)<<<dim3(64, nch), 256, 0, st>>>(streams, slot_bytes, totals);
     (raht_count_launches(1), rlgr_emit_kernel)<<<cgrid, 32 * SPEC_WARPS, 0, st>>>(G, info, ev, blockpos, lanerec, chunkoff, streams,
                                                                                  slot_bytes, (uint2 *)sync_index, entries, status);
@@ -912,13 +1114,13 @@ RAHT_API int raht_rlgr_encode(const int32_t *q, int64_t n, int64_t ld, int nch, 
 
 // diagnostics of the last raht_rlgr_encode on this workspace: out[0] = chunk solves in the speculation
 // pass, out[1] = their fixed-point rounds, out[2] = chunks re-solved by the resolve pass, out[3] = slowest
-// chunk of the speculation pass (SM cycles << 24 | channel << 8 | rounds), out[4] = rounds spent in those re-solves.
-// Synchronises.
+// chunk of the speculation pass (SM cycles << 24 | channel << 8 | rounds), out[4] = rounds spent in those re-solves,
+// out[5] = chunks settled through the transition tables.  Synchronises.
 RAHT_API int raht_rlgr_encode_stats(const void *workspace, int64_t n, int nch, unsigned long long *out5_host, void *stream)
 {
     RAHT_REQUIRE(workspace && out5_host && n > 0, "raht_rlgr_encode_stats: bad arguments");
     const EncLayout L = enc_layout(n, nch);
-    RAHT_CUDA(cudaMemcpyAsync(out5_host, (const char *)workspace + L.off_stats, 40, cudaMemcpyDeviceToHost, (cudaStream_t)stream));
+    RAHT_CUDA(cudaMemcpyAsync(out5_host, (const char *)workspace + L.off_stats, 48, cudaMemcpyDeviceToHost, (cudaStream_t)stream));
     RAHT_CUDA(cudaStreamSynchronize((cudaStream_t)stream));
     return RAHT_OK;
 }

@@ -431,9 +431,9 @@ def rlgr_encode(q: torch.Tensor, flag_signed=1, slot_bytes=None, with_index=True
             continue
         out = RlgrStreams(buf, slot, nbytes, n, nch, index)
         if want_stats and n > 0 and nch > 0:
-            st = (C.c_ulonglong * 5)()
+            st = (C.c_ulonglong * 6)()
             check(lib.raht_rlgr_encode_stats(ptr(ws), n, nch, st, stream()), "raht_rlgr_encode_stats")
-            out.stats = {"solves": int(st[0]), "rounds": int(st[1]), "repairs": int(st[2]), "repair_rounds": int(st[4]),
+            out.stats = {"solves": int(st[0]), "rounds": int(st[1]), "repairs": int(st[2]), "repair_rounds": int(st[4]), "table_hits": int(st[5]),
                          "chunks": nch * entries,
                          "slowest_chunk": {"cycles": int(st[3]) >> 24, "channel": (int(st[3]) >> 8) & 0xffff, "rounds": int(st[3]) & 0xff}}
         return out

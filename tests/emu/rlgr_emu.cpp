@@ -5,7 +5,9 @@
 // written on the way -- with the 32 lanes of a warp executed one after the other, so that the CPU
 // test-suite can check the ALGORITHM (event form, tail rule, speculation + repair exactness, sync
 // index) against the oracle without a GPU.  The CUDA kernels themselves are checked on the GPU by
-// tests/test_gpu_parity.py.
+// tests/test_gpu_parity.py.  Not mirrored here: the transition tables of rlgr.cu (an extra way for the resolve pass
+// to settle a chunk before it falls back on the pinned repair, which IS mirrored) and the one-candidate kernel
+// instantiation for dense channels (here: 8 equal candidates).
 #include "../../raht-3dgs-codec_b200/csrc/rlgr_core.cuh"
 #include <algorithm>
 #include <cstdio>
