@@ -29,6 +29,7 @@ class EncodedScene:
     streams: ops.RlgrStreams          # D closed RLGR streams
     transform_dtype: torch.dtype = torch.float64
     tree: Optional[ops.RahtTree] = field(default=None, repr=False)   # encoder-side cache (decoder rebuilds from keys)
+    packed: Optional[torch.Tensor] = field(default=None, repr=False)  # merged attributes (nvox, D) fp32 when keep_packed
 
     def payload_bytes(self) -> int:
         """Bytes of the D reference-format RLGR streams."""
@@ -167,7 +168,7 @@ def decode_attributes(keys, streams, D, step, transform_dtype=torch.float64, tre
 
 @torch.no_grad()
 def encode_scene(means, quats, scales, opacities, colors, J, step, transform_dtype=torch.float64, tile_rows=None,
-                 timer=None, flags=0) -> EncodedScene:
+                 timer=None, flags=0, keep_packed=False) -> EncodedScene:
     timer = timer or StageTimer(False)
     timer.mark("start")
     status = ops._status_word(means.device)
@@ -176,7 +177,7 @@ def encode_scene(means, quats, scales, opacities, colors, J, step, transform_dty
     width, voxel_size = info["params_d2"].cpu().tolist()          # after the coder's synchronisation: no extra wait
     return EncodedScene(J=J, n_in=info["N"], nvox=info["Nvox"], D=packed.shape[1], step=step, vmin=info["vmin"],
                         voxel_size=voxel_size, width=width, keys=keys, streams=streams,
-                        transform_dtype=transform_dtype, tree=tree)
+                        transform_dtype=transform_dtype, tree=tree, packed=packed if keep_packed else None)
 
 
 @torch.no_grad()
@@ -198,3 +199,95 @@ def psnr(Cref: torch.Tensor, Crec: torch.Tensor, c0=0, c1=None) -> float:
     c1 = Cref.shape[1] if c1 is None else c1
     s = float(ops.sse(Cref.to(torch.float64), Crec.to(torch.float64), c0, c1).item())
     return -10.0 * math.log10(s / (Cref.shape[0] * (c1 - c0)) + 1e-10)
+
+
+class ScenePipeline:
+    """Streams scenes from pinned HOST buffers through encode + decode with the copies off the compute stream
+    ("overlap H2D of scene k+1 with compute of scene k on a second stream"): the H2D of the next
+    scene runs under the current scene's kernels and the D2H of the current results under the next scene's, so a
+    stream of scenes moves at max(H2D, compute, D2H) per scene instead of their sum (PCIe is full duplex).
+
+        pipe = ScenePipeline(J, step)
+        pipe.submit(host_scene)            # pinned (means, quats, scales, opacities, colors); starts its H2D
+        for next_scene in scenes:
+            pipe.submit(next_scene)        # prefetch
+            out = pipe.run()               # encode + decode of the oldest submitted scene; D2H queued on the copy-out stream
+        out = pipe.run(); pipe.finish()    # drain
+
+    `run()` returns a dict of pinned host tensors (streams, sizes, sync index, keys, and -- result="attributes" -- the
+    decoded attributes, or -- result="psnr", what the reference's rate-distortion loop reads back,
+    encode_3dgs.py:298-310 -- the sum of squared errors of the reconstruction) that are valid after `finish()` (or
+    `out["done"].synchronize()`)."""
+
+    def __init__(self, J, step, transform_dtype=torch.float64, tile_rows=None, device=None, result="attributes"):
+        self.J, self.step, self.dtype, self.tile_rows = J, step, transform_dtype, tile_rows
+        assert result in ("attributes", "psnr")
+        self.result = result
+        self.dev = torch.device("cuda", torch.cuda.current_device()) if device is None else torch.device(device)
+        self.s_in = torch.cuda.Stream(self.dev)
+        self.s_out = torch.cuda.Stream(self.dev)
+        self.queue = []                  # (device tensors, H2D-done event)
+        self.pending = []                # outputs whose D2H may still be running (keeps the device tensors alive)
+        self.pinned = {}                 # reusable pinned output buffers, two sets (ping-pong)
+        self.flip = 0
+
+    def submit(self, host_scene):
+        with torch.cuda.stream(self.s_in):
+            dv = [h.to(self.dev, non_blocking=True) for h in host_scene]
+            ev = torch.cuda.Event()
+            ev.record(self.s_in)
+        self.queue.append((dv, ev))
+        return sum(h.numel() * h.element_size() for h in host_scene)
+
+    def _pin(self, name, numel, dtype):
+        key = (name, self.flip)
+        buf = self.pinned.get(key)
+        if buf is None or buf.numel() < numel or buf.dtype != dtype:
+            buf = torch.empty(max(numel, 1), dtype=dtype).pin_memory()
+            self.pinned[key] = buf
+        return buf[:numel]
+
+    @torch.no_grad()
+    def run(self):
+        dv, ev = self.queue.pop(0)
+        main = torch.cuda.current_stream(self.dev)
+        main.wait_event(ev)
+        for t in dv:
+            t.record_stream(main)
+        enc = encode_scene(*dv, J=self.J, step=self.step, transform_dtype=self.dtype, tile_rows=self.tile_rows,
+                           keep_packed=self.result == "psnr")
+        sizes = enc.streams.sizes()                      # (the encoder has synchronised: no extra wait)
+        slot = enc.streams.slot_bytes
+        compact = torch.cat([enc.streams.buf[c * slot: c * slot + sizes[c]] for c in range(enc.D)])
+        coords, Crec = decode_scene(enc, reuse_tree=False, tile_rows=self.tile_rows)
+        if self.result == "psnr":                        # -10 log10(sse / (nvox D) + 1e-10) on the host from one double
+            final = ("sse", ops.sse(enc.packed.to(torch.float64), Crec.to(torch.float64)))
+        else:
+            final = ("attributes", Crec.reshape(-1))
+        done_compute = torch.cuda.Event()
+        done_compute.record(main)
+        idx = enc.streams.sync_index.view(torch.uint8).reshape(-1) if enc.streams.sync_index is not None else None
+        outs = {"sizes": sizes, "nvox": enc.nvox}
+        with torch.cuda.stream(self.s_out):
+            self.s_out.wait_event(done_compute)
+            for name, t in (("streams", compact), ("index", idx), ("keys", enc.keys), final):
+                if t is None:
+                    continue
+                t.record_stream(self.s_out)
+                dst = self._pin(name, t.numel(), t.dtype)
+                dst.copy_(t, non_blocking=True)
+                outs[name] = dst
+            done = torch.cuda.Event()
+            done.record(self.s_out)
+        outs["done"] = done
+        outs["d2h_bytes"] = sum(outs[k].numel() * outs[k].element_size() for k in ("streams", "index", "keys", "attributes", "sse") if k in outs)
+        self.pending.append(outs)
+        if len(self.pending) > 2:                        # the ping-pong buffers of two steps ago are about to be reused
+            self.pending.pop(0)["done"].synchronize()
+        self.flip ^= 1
+        return outs
+
+    def finish(self):
+        for o in self.pending:
+            o["done"].synchronize()
+        self.pending.clear()

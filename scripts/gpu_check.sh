@@ -18,7 +18,8 @@ run golden_raht "golden_raht_pipeline"
 run oracle_raht "oracle_raht_pipeline"
 run rlgr "rlgr"
 run misc "plain_lists or raht_param_errors or fp32_mode"
-run scene "scene_roundtrip"
+run scene "scene_roundtrip or scene_pipeline"
+run sharded "sharded"
 echo "=== smoke" | tee -a gpurun_out/summary.txt
 timeout 600 python -c "import __graft_entry__ as g; g.smoke()" > gpurun_out/smoke.log 2>&1; echo "exit $?" | tee -a gpurun_out/summary.txt
 tail -n 2 gpurun_out/smoke.log | tee -a gpurun_out/summary.txt
@@ -26,3 +27,6 @@ echo "=== bench" | tee -a gpurun_out/summary.txt
 timeout 900 python bench.py --steps 3 --warmup 3 > gpurun_out/bench.json 2> gpurun_out/bench.err; echo "exit $?" | tee -a gpurun_out/summary.txt
 tail -c 3000 gpurun_out/bench.json | tee -a gpurun_out/summary.txt
 tail -n 5 gpurun_out/bench.err | tee -a gpurun_out/summary.txt
+echo "=== all gpu tests in one process (as the driver runs them)" | tee -a gpurun_out/summary.txt
+timeout 1500 python -m pytest tests -m gpu -q -x --timeout 900 > gpurun_out/test_all.log 2>&1; echo "exit $?" | tee -a gpurun_out/summary.txt
+tail -n 3 gpurun_out/test_all.log | tee -a gpurun_out/summary.txt

@@ -346,6 +346,29 @@ def test_rlgr_regime_changes_and_unsigned():
                 assert np.array_equal(ops.rlgr_decode(st, fs, use_index=False).cpu().numpy(), z), (n, last, fs)
 
 
+def test_rlgr_one_signed_sparse_channels_use_the_tables():
+    """Sparse channels whose non-zeros are all positive never meet the p = 0 event that re-synchronises k_RP, and in
+    run mode k_P keeps the parity of its differences: the candidate records fail and the transition tables of
+    rlgr.cu (128-state window per block) must settle the chunks -- with the reference's bytes."""
+    from raht_b200 import ops
+    rng = np.random.default_rng(2024)
+    n, nch = 600000, 6
+    x = np.zeros((nch, n), dtype=np.int32)
+    for c in range(nch):
+        dens = (0.04, 0.08, 0.12, 0.2, 0.3, 0.15)[c]
+        mag = (1.2, 2.0, 3.0, 1.5, 6.0, 40.0)[c]
+        nz = rng.random(n) < dens * (0.4 + 1.2 * np.linspace(0, 1, n) ** (c % 3))          # density drifts along the channel
+        v = 1 + np.floor(rng.exponential(mag, n)).astype(np.int32)
+        x[c, nz] = v[nz]
+    x[5, n // 2:] *= -1                                                                    # one channel changes sign half-way
+    streams = ops.rlgr_encode(cu(x), 1, want_stats=True)
+    exp, _, _, _ = orc.rlgr_encode_channels(x, 1)
+    assert streams.to_bytes() == exp
+    assert streams.stats["table_hits"] > 0, streams.stats
+    assert np.array_equal(ops.rlgr_decode(streams, 1).cpu().numpy(), x)
+    assert np.array_equal(ops.rlgr_decode(streams, 1, use_index=False).cpu().numpy(), x)
+
+
 # ---------------------------------------------------------------------------------------------------
 # whole scene, size-independent properties at a BASELINE-sized input
 # ---------------------------------------------------------------------------------------------------
@@ -375,3 +398,40 @@ def test_scene_roundtrip_properties_1m():
     # decode without the encoder-side tree gives the same result
     _, Crec2 = codec.decode_scene(enc, reuse_tree=False)
     assert torch.equal(Crec, Crec2)
+
+
+def test_scene_pipeline_matches_direct_calls():
+    """codec.ScenePipeline (copies on side streams, prefetch) must hand back exactly what encode_scene / decode_scene
+    produce, for every scene of a stream of different scenes."""
+    import torch
+    from raht_b200 import codec
+    J, step = 10, 0.02
+    scenes = [helpers.synthetic_gaussians(60000 + 7000 * k, 300 + k) for k in range(4)]
+    hosts = [[torch.from_numpy(a).pin_memory() for a in sc] for sc in scenes]
+    pipe = codec.ScenePipeline(J, step)
+    outs = []
+    pipe.submit(hosts[0])
+    for k in range(len(hosts)):
+        if k + 1 < len(hosts):
+            pipe.submit(hosts[k + 1])
+        o = pipe.run()
+        o["done"].synchronize()
+        outs.append({n: (o[n].clone() if hasattr(o[n], "clone") else o[n]) for n in ("streams", "keys", "attributes", "sizes", "nvox")})
+    pipe.finish()
+    for sc, o in zip(scenes, outs):
+        enc = codec.encode_scene(*[cu(a) for a in sc], J=J, step=step)
+        _, Crec = codec.decode_scene(enc)
+        assert o["nvox"] == enc.nvox and o["sizes"] == enc.streams.sizes()
+        assert bytes(o["streams"].numpy()) == b"".join(enc.streams.to_bytes())
+        assert np.array_equal(o["keys"].numpy(), enc.keys.cpu().numpy())
+        assert np.array_equal(o["attributes"].numpy().reshape(enc.nvox, -1), Crec.cpu().numpy())
+    # result="psnr": the squared error instead of the attributes
+    pipe = codec.ScenePipeline(J, step, result="psnr")
+    pipe.submit(hosts[0])
+    o = pipe.run()
+    pipe.finish()
+    packed, _, _ = codec.voxelize_merge(*[cu(a) for a in scenes[0]], J=J)
+    enc = codec.encode_scene(*[cu(a) for a in scenes[0]], J=J, step=step)
+    _, Crec = codec.decode_scene(enc)
+    sse = float(((packed.double() - Crec) ** 2).sum().item())
+    assert abs(float(o["sse"][0]) - sse) <= 1e-9 * sse and "attributes" not in o
