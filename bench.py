@@ -301,6 +301,27 @@ def run_gpu(args):
 
     e2e_value, d2h, wall_e2e = time_e2e("psnr")
     e2e_attr_value, d2h_attr, _ = time_e2e("attributes")
+    # container, outside the metric: bytes and device time of pack / unpack of the last scene
+    from raht_b200 import container as cont
+    enc, _ = step_resident()
+    box = cont.pack(enc)
+    cont.unpack(box)
+    torch.cuda.synchronize()
+    c0, c1, c2 = (torch.cuda.Event(enable_timing=True) for _ in range(3))
+    c0.record()
+    for _ in range(3):
+        box = cont.pack(enc)
+    c1.record()
+    for _ in range(3):
+        back = cont.unpack(box)
+    c2.record()
+    torch.cuda.synchronize()
+    hb = cont.parse_header(box[:76].cpu().numpy().tobytes())["header_bytes"]
+    hdr = cont.parse_header(box[:hb].cpu().numpy().tobytes())
+    container_info = {"bytes": int(box.numel()), "geometry_bytes": int(sum(hdr["geo_bytes"])),
+                      "raw_keys_bytes": int(enc.nvox * 8), "pack_ms": round(c0.elapsed_time(c1) / 3, 4),
+                      "unpack_ms": round(c1.elapsed_time(c2) / 3, 4), "keys_roundtrip": bool(torch.equal(back.keys, enc.keys)),
+                      "what": "raht_b200.container: header + RLGR-coded Morton deltas + the attribute streams + sync indices in one device buffer"}
     clocks.mark_end()
     clk = clocks.stop()
     clk["window"] = "samples (nvidia-smi -lms 50) between the start of the device-timed region and the end of the e2e regions"
@@ -357,6 +378,7 @@ def run_gpu(args):
         "roofline": roofline,
         "stages": per_stage,
         "cpu_baseline": cpu,
+        "container": container_info,
     }
     print(json.dumps(line))
     if world > 1:

@@ -29,7 +29,7 @@
 extern "C" {
 #endif
 
-#define RAHT_B200_ABI_VERSION 7
+#define RAHT_B200_ABI_VERSION 8
 
 enum {
     RAHT_OK = 0,
@@ -260,6 +260,34 @@ int raht_rlgr_decode(const uint8_t *streams, int64_t slot_bytes, const int64_t *
 int raht_sse_f64(const double *A, const double *B, int64_t n, int D, int c0, int c1, double *sse,
                  void *workspace, size_t workspace_bytes, void *stream);
 size_t raht_sse_workspace_bytes(int64_t n, int D);
+
+/* ------------------------------------------------------------------------------------------------
+ * (f1, f2) Container support: geometry symbols and stream packing.  The reference never serialises
+ * its bitstreams (python/encode_3dgs.py:247 takes len(buf) and drops the bytes) and ships the voxel
+ * positions uncompressed in a PLY (python/test_voxelize_3dgs.py:284-288); the container format is
+ * defined by this build (raht_b200/container.py; checker: oracle/container_oracle.py).
+ *
+ * raht_geometry_symbols: keys[n] sorted unique Morton codes (>= 0) -> symbols[3][ld] int32:
+ *   d[0] = key[0], d[i] = key[i] - key[i-1] - 1; symbols[j][i] = (d[i] >> 21 j) & 0x1fffff.
+ *   They are coded with raht_rlgr_encode(..., nch = 3, flag_signed = 0, ...).
+ *   status |= RAHT_ST_NOT_SORTED_UNIQUE / RAHT_ST_OUT_OF_BOUNDS (negative key).
+ * raht_geometry_keys: the inverse (64-bit inclusive scan).
+ * raht_streams_pack: the nch streams of an encoder call (slot c at streams + c * slot_bytes,
+ *   nbytes[c] bytes) laid end to end in `out`, each padded with zero bytes to a multiple of 8;
+ *   offsets[nch + 1] (device) receives the start of every stream and the total.  A total above
+ *   out_capacity sets RAHT_ST_STREAM_OVERFLOW and writes nothing past the capacity.
+ * raht_streams_unpack: the inverse, offsets[nch + 1] as written by the packer (device memory).
+ * ------------------------------------------------------------------------------------------------ */
+int raht_geometry_symbols(const int64_t *keys, int64_t n, int64_t ld, int32_t *symbols,
+                          int32_t *status, void *stream);
+size_t raht_geometry_keys_workspace_bytes(int64_t n);
+int raht_geometry_keys(const int32_t *symbols, int64_t n, int64_t ld, int64_t *keys,
+                       void *workspace, size_t workspace_bytes, void *stream);
+int raht_streams_pack(const uint8_t *streams, int64_t slot_bytes, const int64_t *nbytes, int nch,
+                      uint8_t *out, int64_t out_capacity, int64_t *offsets, int32_t *status,
+                      void *stream);
+int raht_streams_unpack(const uint8_t *packed, const int64_t *offsets, int nch, uint8_t *streams,
+                        int64_t slot_bytes, void *stream);
 
 #ifdef __cplusplus
 }

@@ -69,6 +69,11 @@ SIGNATURES = {
     "raht_rlgr_decode": (_i, [_p, _i64, _p, _p, _i64, _i64, _i, _i, _p, _p]),
     "raht_sse_workspace_bytes": (_sz, [_i64, _i]),
     "raht_sse_f64": (_i, [_p, _p, _i64, _i, _i, _i, _p, _p, _sz, _p]),
+    "raht_geometry_symbols": (_i, [_p, _i64, _i64, _p, _p, _p]),
+    "raht_geometry_keys_workspace_bytes": (_sz, [_i64]),
+    "raht_geometry_keys": (_i, [_p, _i64, _i64, _p, _p, _sz, _p]),
+    "raht_streams_pack": (_i, [_p, _i64, _p, _i, _p, _i64, _p, _p, _p]),
+    "raht_streams_unpack": (_i, [_p, _p, _i, _p, _i64, _p]),
 }
 
 for _name, (_res, _args) in SIGNATURES.items():

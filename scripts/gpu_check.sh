@@ -20,6 +20,7 @@ run rlgr "rlgr"
 run misc "plain_lists or raht_param_errors or fp32_mode"
 run scene "scene_roundtrip or scene_pipeline"
 run sharded "sharded"
+run container "container or geometry_symbols or sync_index_matches"
 echo "=== smoke" | tee -a gpurun_out/summary.txt
 timeout 600 python -c "import __graft_entry__ as g; g.smoke()" > gpurun_out/smoke.log 2>&1; echo "exit $?" | tee -a gpurun_out/summary.txt
 tail -n 2 gpurun_out/smoke.log | tee -a gpurun_out/summary.txt
