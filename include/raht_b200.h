@@ -58,6 +58,10 @@ long long raht_launch_count(void);
 const char *raht_last_error(void);
 /* number of SMs / compute capability of the current device (major*10+minor); <0 on error */
 int raht_device_info(int *sm_count, int *cc);
+/* `bytes` (<= 1 MiB) of device memory stored into PINNED host memory by a kernel on `stream` (no copy engine:
+ * a small result does not queue behind another stream's bulk device-to-host copy); valid on the host after
+ * the stream (or an event recorded behind the call) has been synchronised.                                */
+int raht_publish_host(const void *src, void *pinned_host, size_t bytes, void *stream);
 
 /* ------------------------------------------------------------------------------------------------
  * (a1,a2) Voxelisation front end.   Replaces python/voxelize_pc.py:25-59 (get_morton_code) and
@@ -260,6 +264,10 @@ int raht_rlgr_decode(const uint8_t *streams, int64_t slot_bytes, const int64_t *
 int raht_sse_f64(const double *A, const double *B, int64_t n, int D, int c0, int c1, double *sse,
                  void *workspace, size_t workspace_bytes, void *stream);
 size_t raht_sse_workspace_bytes(int64_t n, int D);
+/* the same with either matrix in fp32 or fp64 (RAHT_F32 / RAHT_F64): the merged attributes are fp32, the
+ * reconstruction fp64 (the reference up-casts before subtracting, encode_3dgs.py:298).                */
+int raht_sse(const void *A, int a_dtype, const void *B, int b_dtype, int64_t n, int D, int c0, int c1,
+             double *sse, void *workspace, size_t workspace_bytes, void *stream);
 
 /* ------------------------------------------------------------------------------------------------
  * (f1, f2) Container support: geometry symbols and stream packing.  The reference never serialises

@@ -92,17 +92,25 @@ __global__ void __launch_bounds__(256) dequantize_kernel(const double *__restric
 // ---- sum of squared differences -----------------------------------------------------------------
 constexpr int SSE_BLOCKS_MAX = 1184;      // 148 SMs x 8
 
-__global__ void __launch_bounds__(256) sse_partial_kernel(const double *__restrict__ A, const double *__restrict__ B,
+template <typename TA, typename TB>
+__global__ void __launch_bounds__(256) sse_partial_kernel(const TA *__restrict__ A, const TB *__restrict__ B,
                                                           int64_t n, int D, int c0, int c1, double *partial)
 {
     const int wc = c1 - c0;
     const int64_t total = n * wc;
     double acc = 0.0;
-    for (int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; e < total; e += (int64_t)gridDim.x * blockDim.x) {
-        int64_t r = e / wc;
-        int c = c0 + (int)(e - r * wc);
-        double d = A[r * D + c] - B[r * D + c];
-        acc += d * d;
+    if (wc == D) {                                   // all columns: the matrices are two flat arrays
+        for (int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; e < total; e += (int64_t)gridDim.x * blockDim.x) {
+            const double d = (double)A[e] - (double)B[e];
+            acc += d * d;
+        }
+    } else {
+        for (int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; e < total; e += (int64_t)gridDim.x * blockDim.x) {
+            int64_t r = e / wc;
+            int c = c0 + (int)(e - r * wc);
+            const double d = (double)A[r * D + c] - (double)B[r * D + c];
+            acc += d * d;
+        }
     }
     __shared__ double s[8];
     for (int o = 16; o; o >>= 1) acc += __shfl_xor_sync(~0u, acc, o);
@@ -207,20 +215,36 @@ RAHT_API size_t raht_sse_workspace_bytes(int64_t n, int D)
     return (size_t)SSE_BLOCKS_MAX * 8 + 256;
 }
 
-RAHT_API int raht_sse_f64(const double *A, const double *B, int64_t n, int D, int c0, int c1, double *sse, void *workspace,
-                          size_t workspace_bytes, void *stream)
+RAHT_API int raht_sse(const void *A, int a_dtype, const void *B, int b_dtype, int64_t n, int D, int c0, int c1, double *sse,
+                      void *workspace, size_t workspace_bytes, void *stream)
 {
-    RAHT_REQUIRE(n >= 0 && D >= 1 && c0 >= 0 && c1 <= D && c0 < c1 && sse && workspace, "raht_sse_f64: bad arguments");
+    RAHT_REQUIRE(n >= 0 && D >= 1 && c0 >= 0 && c1 <= D && c0 < c1 && sse && workspace, "raht_sse: bad arguments");
+    RAHT_REQUIRE((a_dtype == RAHT_F32 || a_dtype == RAHT_F64) && (b_dtype == RAHT_F32 || b_dtype == RAHT_F64), "raht_sse: bad dtype");
     if (workspace_bytes < raht_sse_workspace_bytes(n, D)) {
-        raht_set_error("raht_sse_f64: workspace too small");
+        raht_set_error("raht_sse: workspace too small");
         return RAHT_E_WORKSPACE;
     }
     cudaStream_t st = (cudaStream_t)stream;
     int nb = grid_for(n * (c1 - c0), 256, 8);
     if (nb > SSE_BLOCKS_MAX) nb = SSE_BLOCKS_MAX;
     if (n == 0) nb = 1;
-    (raht_count_launches(1), sse_partial_kernel)<<<nb, 256, 0, st>>>(A, B, n, D, c0, c1, (double *)workspace);
-    (raht_count_launches(1), sse_final_kernel)<<<1, 256, 0, st>>>((const double *)workspace, nb, sse);
+    double *part = (double *)workspace;
+    raht_count_launches(2);
+    if (a_dtype == RAHT_F64 && b_dtype == RAHT_F64)
+        sse_partial_kernel<double, double><<<nb, 256, 0, st>>>((const double *)A, (const double *)B, n, D, c0, c1, part);
+    else if (a_dtype == RAHT_F32 && b_dtype == RAHT_F64)
+        sse_partial_kernel<float, double><<<nb, 256, 0, st>>>((const float *)A, (const double *)B, n, D, c0, c1, part);
+    else if (a_dtype == RAHT_F64 && b_dtype == RAHT_F32)
+        sse_partial_kernel<double, float><<<nb, 256, 0, st>>>((const double *)A, (const float *)B, n, D, c0, c1, part);
+    else
+        sse_partial_kernel<float, float><<<nb, 256, 0, st>>>((const float *)A, (const float *)B, n, D, c0, c1, part);
+    sse_final_kernel<<<1, 256, 0, st>>>((const double *)workspace, nb, sse);
     RAHT_LAUNCH_CHECK();
     return RAHT_OK;
+}
+
+RAHT_API int raht_sse_f64(const double *A, const double *B, int64_t n, int D, int c0, int c1, double *sse, void *workspace,
+                          size_t workspace_bytes, void *stream)
+{
+    return raht_sse(A, RAHT_F64, B, RAHT_F64, n, D, c0, c1, sse, workspace, workspace_bytes, stream);
 }

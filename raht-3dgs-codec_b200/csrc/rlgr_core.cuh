@@ -263,106 +263,127 @@ template <class Sink> RL_HD bool emit_event(State &s, uint32_t g, uint32_t u, Si
 // ---- decoder ---------------------------------------------------------------------------------------------
 // MSB-first reader over big-endian 32-bit words; acc holds the next nbits bits left-aligned.
 struct BitReader {
+    // 64-bit window over a big-endian bit stream, refilled 32 bits at a time.  The word after the window (`ahead`) is
+    // loaded one refill early, so a refill never waits for memory: it consumes the word fetched by the previous one and
+    // starts the next fetch (on the GPU a warp refills on almost every symbol -- some lane always runs dry -- and used
+    // to stall on that load every time).
     const uint32_t *in;
-    int64_t n_words, pos;
+    uint32_t n_words, pos;             // pos: index of `ahead`
+    uint32_t ahead;                    // raw (still byte-swapped) so that nothing touches the loaded value before the next refill
     uint64_t acc;
     int nbits;
+    RL_HD uint32_t word(uint32_t i) const { return i < n_words ? in[i] : 0u; }
     RL_HD void init(const uint8_t *stream, int64_t readable_bytes, unsigned long long begin_bit)
     {
         in = (const uint32_t *)stream;
-        n_words = (readable_bytes + 3) >> 2;
-        pos = (int64_t)(begin_bit >> 5);
+        n_words = (uint32_t)((readable_bytes + 3) >> 2);
+        pos = (uint32_t)(begin_bit >> 5);
+        ahead = word(pos);
         acc = 0;
         nbits = 0;
-        const unsigned skip = (unsigned)(begin_bit & 31);
-        if (skip) { fill(); acc <<= skip; nbits -= (int)skip; }
+        const unsigned skip_bits = (unsigned)(begin_bit & 31);
+        if (skip_bits) { fill(); acc <<= skip_bits; nbits -= (int)skip_bits; }
     }
     RL_HD void fill()                  // afterwards nbits >= 33
     {
         if (nbits <= 32) {
-            const uint32_t w = pos < n_words ? rl_bswap32(in[pos]) : 0u;
-            ++pos;
-            acc |= (uint64_t)w << (32 - nbits);
+            acc |= (uint64_t)rl_bswap32(ahead) << (32 - nbits);
             nbits += 32;
+            ++pos;
+            ahead = word(pos);
         }
+    }
+    RL_HD void skip(unsigned len)      // len <= nbits
+    {
+        acc <<= len;
+        nbits -= (int)len;
     }
     RL_HD unsigned get1()
     {
         fill();
         const unsigned b = (unsigned)(acc >> 63);
-        acc <<= 1;
-        --nbits;
+        skip(1);
         return b;
     }
-    RL_HD uint64_t get(unsigned len)   // len <= 32
+    RL_HD uint32_t get(unsigned len)   // len <= 32
     {
         if (len == 0) return 0;
         fill();
-        const uint64_t v = acc >> (64 - len);
-        acc <<= len;
-        nbits -= (int)len;
+        const uint32_t v = (uint32_t)(acc >> (64 - len));
+        skip(len);
         return v;
     }
-    RL_HD uint64_t gr(unsigned kr)     // membuf.cpp:228-240 (grRead)
+    RL_HD int ones()                   // leading ones of the window after a refill, capped at 32
     {
         fill();
-        const int p = rl_clz64(~acc);             // leading ones (bits past nbits read as zero)
+        const int p = rl_clz64(~acc);  // bits past nbits read as zero
+        return p > 32 ? 32 : p;
+    }
+    RL_HD uint32_t gr(unsigned kr)     // membuf.cpp:228-240 (grRead); values are < 2^32 (written unmasked as 32 bits)
+    {
+        const int p = ones();
         if (p >= 32) {
-            acc <<= 32;
-            nbits -= 32;
+            skip(32);
             return get(32);
         }
-        acc <<= (p + 1);
-        nbits -= p + 1;
-        return (((uint64_t)p) << kr) + get(kr);
+        skip((unsigned)p + 1);
+        return (uint32_t)(((uint64_t)p << kr) + get(kr));        // kr can be 32 (k_RP = 128)
     }
 };
 
 // Events from reader br in state s.  dst is pre-zeroed: only non-zero symbols are stored, so zero runs cost
-// nothing and the tail of the stream is never read.
+// nothing and the tail of the stream is never read.  Positions are 32-bit (the coder takes n < 2^31 symbols).
 //   first_pos < 0: plain sequential decode of symbols [0, end) (reader at the stream start);
 //   first_pos >= 0: the reader stands before an event whose non-zero symbol is dst[first_pos] (a sync entry);
 //   the zeros in front of it are decoded and dropped, then decoding continues up to `end`.
-RL_HD void decode_range(BitReader &br, State s, int64_t first_pos, int64_t end, int flag_signed,
+// One loop body for both modes of the coder: the run prefix (k > 0 only) is the divergent part, the Golomb-Rice
+// symbol, the adaptation and the store are shared (lanes of a warp sit in different modes all the time).
+RL_HD void decode_range(BitReader &br, State s, int64_t first_pos, int64_t end64, int flag_signed,
                                              int32_t *__restrict__ dst)
 {
     bool synced = first_pos < 0;
-    int64_t pos = 0;
+    const uint32_t first = synced ? 0u : (uint32_t)first_pos, end = (uint32_t)end64;
+    uint32_t pos = 0;
     while (pos < end) {                                                    // membuf.cpp:266-334
         int k = s.kP / RL_L;
         const unsigned kR = (unsigned)(s.kRP / RL_L);
-        if (k) {
-            uint64_t m = 0;
-            while (br.get1()) {                                            // complete runs
-                m += ((uint64_t)1) << k;
-                s.kP += RL_U1;
-                k = s.kP / RL_L;
-                if (m > (uint64_t)1 << 40) break;                          // corrupt stream guard
+        const bool run = k != 0;
+        if (run) {
+            uint32_t m = 0;
+            bool bad = false;
+            for (;;) {                                                     // complete runs: one 1 bit each
+                const int p = br.ones();
+                for (int j = 0; j < p; ++j) {
+                    m += 1u << k;
+                    s.kP += RL_U1;
+                    k = s.kP / RL_L;
+                    if (m >= (1u << 31) || k > 30) { bad = true; break; }  // corrupt stream guard
+                }
+                if (bad) break;
+                if (p < 32) { br.skip((unsigned)p + 1); break; }
+                br.skip(32);
             }
+            if (bad) return;
             m += br.get((unsigned)k);
             if (synced) {
-                if (m >= (uint64_t)(end - pos)) break;                     // the next non-zero lies past this range
-                pos += (int64_t)m;
+                if (m >= end - pos) break;                                 // the next non-zero lies past this range
+                pos += m;
             } else {
-                pos = first_pos;
+                pos = first;
                 synced = true;
             }
-            const uint64_t u = br.gr(kR);
-            const uint64_t val = u + 1;
-            dst[pos++] = flag_signed ? u2s(val) : (int32_t)val;
-            adapt_krp(s, u >> kR);
-            s.kP = s.kP < RL_D1 ? 0 : s.kP - RL_D1;
-        } else {
-            const uint64_t u = br.gr(kR);
-            if (u) {
-                if (!synced) { pos = first_pos; synced = true; }
-                dst[pos] = flag_signed ? u2s(u) : (int32_t)u;
-            }
-            if (synced) ++pos;
-            adapt_krp(s, u >> kR);
-            if (u) s.kP = s.kP < RL_D0 ? 0 : s.kP - RL_D0;
-            else s.kP += RL_U0;
         }
+        const uint32_t u = br.gr(kR);
+        adapt_krp(s, (uint64_t)u >> kR);
+        if (run || u) {                                                    // a non-zero symbol: u + 1 after a run
+            if (!synced) { pos = first; synced = true; }
+            const uint64_t val = (uint64_t)u + (run ? 1u : 0u);
+            dst[pos] = flag_signed ? u2s(val) : (int32_t)val;
+            s.kP = s.kP < RL_D1 ? 0 : s.kP - RL_D1;                        // D0 == D1
+        } else {
+            s.kP += RL_U0;
+        }
+        if (synced) ++pos;
     }
 }
 

@@ -32,6 +32,7 @@ SIGNATURES = {
     "raht_last_error": (C.c_char_p, []),
     "raht_launch_count": (C.c_longlong, []),
     "raht_device_info": (_i, [C.POINTER(_i), C.POINTER(_i)]),
+    "raht_publish_host": (_i, [_p, _p, _sz, _p]),
     "raht_bounds3_f32": (_i, [_p, _i64, _i64, _p, _p]),
     "raht_voxel_params": (_i, [_p, _i, _i, C.POINTER(C.c_float), _i, _d, _p, _p, _p]),
     "raht_morton_keys_f32": (_i, [_p, _i64, _i64, _p, _i, _p, _p, _p]),
@@ -69,6 +70,7 @@ SIGNATURES = {
     "raht_rlgr_decode": (_i, [_p, _i64, _p, _p, _i64, _i64, _i, _i, _p, _p]),
     "raht_sse_workspace_bytes": (_sz, [_i64, _i]),
     "raht_sse_f64": (_i, [_p, _p, _i64, _i, _i, _i, _p, _p, _sz, _p]),
+    "raht_sse": (_i, [_p, _i, _p, _i, _i64, _i, _i, _i, _p, _p, _sz, _p]),
     "raht_geometry_symbols": (_i, [_p, _i64, _i64, _p, _p, _p]),
     "raht_geometry_keys_workspace_bytes": (_sz, [_i64]),
     "raht_geometry_keys": (_i, [_p, _i64, _i64, _p, _p, _sz, _p]),
@@ -116,3 +118,30 @@ def dtype_tag(dt: torch.dtype) -> int:
     if dt == torch.float32:
         return RAHT_F32
     raise TypeError(f"unsupported dtype {dt}")
+
+
+_SCRATCH = {}
+
+
+def read_host(*tensors):
+    """Small device tensors -> numpy copies on the host with ONE synchronisation of the current stream and no copy
+    engine (raht_publish_host): the sizes and status words the host has to wait for."""
+    import numpy as np
+    dev = tensors[0].device
+    need = sum((t.numel() * t.element_size() + 15) // 16 * 16 for t in tensors)
+    buf = _SCRATCH.get(dev)
+    if buf is None or buf.numel() < need:
+        buf = torch.empty(max(need, 1 << 16), dtype=torch.uint8).pin_memory()
+        _SCRATCH[dev] = buf
+    st, o, views = stream(), 0, []
+    for t in tensors:
+        t = t.contiguous()
+        nb = t.numel() * t.element_size()
+        check(lib.raht_publish_host(ptr(t), C.c_void_p(buf.data_ptr() + o), nb, st), "raht_publish_host")
+        views.append((o, nb, t.dtype, tuple(t.shape)))
+        o += (nb + 15) // 16 * 16
+    torch.cuda.current_stream(dev).synchronize()
+    out = []
+    for o, nb, dt, shape in views:
+        out.append(buf[o:o + nb].view(dt).reshape(shape).numpy().copy())
+    return out

@@ -115,7 +115,7 @@ def voxelize_merge(means, quats, scales, opacities, colors, J, packed_dtype=torc
     _, offsets, unique_keys, nvox = ops.voxel_segments(keys_sorted)
     timer.mark("segments")
     if not deferred:
-        ops.raise_for_status(int(status.item()))
+        ops.raise_for_status(int(L.read_host(status)[0][0]))
     _, packed = ops.merge_segments(idx32, offsets, means, quats.contiguous().float(), scales.contiguous().float(),
                                    opacities.contiguous().float(), colors.contiguous().float(), True, separate=False,
                                    packed_dtype=packed_dtype)
@@ -162,7 +162,7 @@ def decode_attributes(keys, streams, D, step, transform_dtype=torch.float64, tre
     Crec = ops.inverse(tree, T, tile_rows, flags)
     timer.mark("iraht")
     if status is not None:
-        ops.raise_for_status(int(status.item()))      # the decoder's one synchronisation: were the keys a valid voxel list?
+        ops.raise_for_status(int(L.read_host(status)[0][0]))      # the decoder's one synchronisation: were the keys a valid voxel list?
     return Crec
 
 
@@ -174,7 +174,7 @@ def encode_scene(means, quats, scales, opacities, colors, J, step, transform_dty
     status = ops._status_word(means.device)
     packed, keys, info = voxelize_merge(means, quats, scales, opacities, colors, J, torch.float32, timer, status)
     tree, streams = encode_attributes(keys, packed, step, transform_dtype, tile_rows, timer, flags, status)
-    width, voxel_size = info["params_d2"].cpu().tolist()          # after the coder's synchronisation: no extra wait
+    width, voxel_size = L.read_host(info["params_d2"])[0].tolist()          # after the coder's synchronisation: no extra wait
     return EncodedScene(J=J, n_in=info["N"], nvox=info["Nvox"], D=packed.shape[1], step=step, vmin=info["vmin"],
                         voxel_size=voxel_size, width=width, keys=keys, streams=streams,
                         transform_dtype=transform_dtype, tree=tree, packed=packed if keep_packed else None)
@@ -197,7 +197,7 @@ def psnr(Cref: torch.Tensor, Crec: torch.Tensor, c0=0, c1=None) -> float:
     """-10 log10(mean((C - C_rec)^2) + 1e-10)   (encode_3dgs.py:298-299)."""
     import math
     c1 = Cref.shape[1] if c1 is None else c1
-    s = float(ops.sse(Cref.to(torch.float64), Crec.to(torch.float64), c0, c1).item())
+    s = float(L.read_host(ops.sse(Cref, Crec, c0, c1))[0][0])
     return -10.0 * math.log10(s / (Cref.shape[0] * (c1 - c0)) + 1e-10)
 
 
@@ -214,7 +214,7 @@ class ScenePipeline:
             out = pipe.run()               # encode + decode of the oldest submitted scene; D2H queued on the copy-out stream
         out = pipe.run(); pipe.finish()    # drain
 
-    `run()` returns a dict of pinned host tensors (streams, sizes, sync index, keys, and -- result="attributes" -- the
+    `run()` returns a dict of pinned host tensors (streams end to end, each padded to 8 bytes, their sizes, sync index, keys, and -- result="attributes" -- the
     decoded attributes, or -- result="psnr", what the reference's rate-distortion loop reads back,
     encode_3dgs.py:298-310 -- the sum of squared errors of the reconstruction) that are valid after `finish()` (or
     `out["done"].synchronize()`)."""
@@ -257,11 +257,10 @@ class ScenePipeline:
         enc = encode_scene(*dv, J=self.J, step=self.step, transform_dtype=self.dtype, tile_rows=self.tile_rows,
                            keep_packed=self.result == "psnr")
         sizes = enc.streams.sizes()                      # (the encoder has synchronised: no extra wait)
-        slot = enc.streams.slot_bytes
-        compact = torch.cat([enc.streams.buf[c * slot: c * slot + sizes[c]] for c in range(enc.D)])
+        compact, _ = enc.streams.packed()                # end to end, each padded to 8 bytes
         coords, Crec = decode_scene(enc, reuse_tree=False, tile_rows=self.tile_rows)
         if self.result == "psnr":                        # -10 log10(sse / (nvox D) + 1e-10) on the host from one double
-            final = ("sse", ops.sse(enc.packed.to(torch.float64), Crec.to(torch.float64)))
+            final = ("sse", ops.sse(enc.packed, Crec))
         else:
             final = ("attributes", Crec.reshape(-1))
         done_compute = torch.cuda.Event()

@@ -48,7 +48,7 @@ def geometry_symbols(keys: torch.Tensor, status=None) -> torch.Tensor:
     status = ops._status_word(keys.device) if own else status
     check(lib.raht_geometry_symbols(ptr(keys.contiguous()), n, ld, ptr(sym), ptr(status), stream()), "raht_geometry_symbols")
     if own:
-        ops.raise_for_status(int(status.item()))
+        ops.raise_for_status(int(L.read_host(status)[0][0]))
     return sym[:, :n]
 
 
@@ -86,14 +86,6 @@ def _header(J, D, n_in, nvox, vmin, voxel_size, width, steps, geo_sizes, attr_si
     return (fixed + var).ljust(hb, b"\0")
 
 
-def _pack_streams(streams: ops.RlgrStreams, out: torch.Tensor, status):
-    """-> device offsets (nch + 1).  `out` is an 8-aligned slice of the container."""
-    offsets = torch.empty(streams.nch + 1, dtype=torch.int64, device=out.device)
-    check(lib.raht_streams_pack(ptr(streams.buf), streams.slot_bytes, ptr(streams.nbytes), streams.nch, ptr(out), out.numel(),
-                                ptr(offsets), ptr(status), stream()), "raht_streams_pack")
-    return offsets
-
-
 @torch.no_grad()
 def pack(enc: EncodedScene, with_index=True) -> torch.Tensor:
     """EncodedScene -> one uint8 CUDA tensor (the container).  Two synchronisations: the sizes of the attribute streams
@@ -115,9 +107,9 @@ def pack(enc: EncodedScene, with_index=True) -> torch.Tensor:
     out = torch.empty(len(head) + geo_body + attr_body + index_bytes, dtype=torch.uint8, device=dev)
     out[:len(head)].copy_(torch.frombuffer(bytearray(head), dtype=torch.uint8), non_blocking=True)
     o = len(head)
-    _pack_streams(geo, out[o:o + geo_body], status)
+    geo.packed(out[o:o + geo_body], status)
     o += geo_body
-    _pack_streams(enc.streams, out[o:o + attr_body], status)
+    enc.streams.packed(out[o:o + attr_body], status)
     o += attr_body
     if with_index:
         for s in (geo, enc.streams):

@@ -86,7 +86,7 @@ def voxel_segments(sorted_keys: torch.Tensor, want_unique=True):
     ws = workspace(ws_bytes, dev)
     check(lib.raht_voxel_segments(ptr(sorted_keys), n, ptr(vi), ptr(off), ptr(uk), ptr(nvox), ptr(ws), ws_bytes,
                                   stream()), "raht_voxel_segments")
-    nv = int(nvox.item())
+    nv = int(L.read_host(nvox)[0][0])
     return vi[:nv], off[:nv + 1], (uk[:nv] if want_unique else None), nv
 
 
@@ -151,7 +151,7 @@ class RahtTree:
         if self._max_level is None:
             out = torch.empty(1, dtype=torch.int32, device=self.device)
             check(lib.raht_tree_max_level(ptr(self.level), self.n, ptr(out), stream()), "raht_tree_max_level")
-            self._max_level = int(out.item())
+            self._max_level = int(L.read_host(out)[0].reshape(-1)[0])
         return self._max_level
 
     @property
@@ -198,7 +198,7 @@ class RahtTree:
         ws = workspace(ws_bytes, dev)
         check(lib.raht_tree_level(ptr(self.level), n, l, ptr(lst), ptr(flg), ptr(wts), ptr(cnt), ptr(ws), ws_bytes,
                                   stream()), "raht_tree_level")
-        c = int(cnt.item())
+        c = int(L.read_host(cnt)[0].reshape(-1)[0])
         return lst[:c].clone(), flg[:c].to(torch.bool), wts[:c].clone()
 
     # -- order_RAGFT ------------------------------------------------------------------------------
@@ -224,7 +224,7 @@ def tree_from_keys(MC: torch.Tensor, validate=True, status=None) -> RahtTree:
     status = _status_word(MC.device) if status is None else status
     check(lib.raht_tree_levels(ptr(MC), n, ptr(level), ptr(status), stream()), "raht_tree_levels")
     if validate and not deferred:
-        s = int(status.item())
+        s = int(L.read_host(status)[0][0])
         if s & L.ST_NOT_SORTED_UNIQUE:
             raise ValueError("RAHT_param: rows must be Morton-sorted and unique (duplicate or unsorted voxels)")
     return RahtTree(level, n)
@@ -355,7 +355,7 @@ def quant_reorder(T: torch.Tensor, order, step, check_overflow=True, status=None
     status = _status_word(dev) if status is None else status
     check(lib.raht_quant_reorder(ptr(T), L.dtype_tag(T.dtype), n, D, ptr(order), ptr(steps), ptr(q), ld, ptr(status),
                                  stream()), "raht_quant_reorder")
-    if check_overflow and not deferred and int(status.item()) & L.ST_INT32_OVERFLOW:
+    if check_overflow and not deferred and int(L.read_host(status)[0][0]) & L.ST_INT32_OVERFLOW:
         raise OverflowError("quantised coefficient does not fit int32 (encode_3dgs.py:215 would truncate)")
     return q[:, :n]
 
@@ -385,12 +385,27 @@ class RlgrStreams:
         self.buf, self.slot_bytes, self.nbytes, self.n, self.nch = buf, slot_bytes, nbytes, n, nch
         self.sync_index = sync_index
         self.stats = None
+        self._sizes = None
 
     def sizes(self):
-        return self.nbytes.cpu().tolist()
+        """Stream lengths in bytes on the host (one D2H, cached)."""
+        if self._sizes is None:
+            self._sizes = [int(x) for x in L.read_host(self.nbytes)[0]]
+        return self._sizes
 
     def total_bytes(self):
-        return int(self.nbytes.sum().item())
+        return int(sum(self.sizes()))
+
+    def packed(self, out=None, status=None):
+        """The nch streams end to end, each padded with zero bytes to a multiple of 8 (raht_streams_pack) ->
+        (uint8 tensor, device offsets (nch + 1) int64).  `out`: an 8-byte-aligned uint8 slice to fill, else allocated."""
+        total = sum((int(b) + 7) // 8 * 8 for b in self.sizes())
+        if out is None:
+            out = torch.empty(total, dtype=torch.uint8, device=self.buf.device)
+        offsets = torch.empty(self.nch + 1, dtype=torch.int64, device=self.buf.device)
+        check(lib.raht_streams_pack(ptr(self.buf), self.slot_bytes, ptr(self.nbytes), self.nch, ptr(out), out.numel(),
+                                    ptr(offsets), ptr(status), stream()), "raht_streams_pack")
+        return out, offsets
 
     def index_bytes(self):
         return 0 if self.sync_index is None else self.sync_index.numel() * self.sync_index.element_size()
@@ -423,13 +438,15 @@ def rlgr_encode(q: torch.Tensor, flag_signed=1, slot_bytes=None, with_index=True
         status = _status_word(dev) if status is None else status
         check(lib.raht_rlgr_encode(ptr(q), n, ld, nch, flag_signed, ptr(buf), slot, ptr(nbytes), ptr(index), ptr(status),
                                    ptr(ws), ws_bytes, stream()), "raht_rlgr_encode")
-        bits = int(status.item())
+        st_host, nb_host = L.read_host(status, nbytes)                # the encoder's one synchronisation
+        bits = int(st_host[0])
         raise_for_status(bits)
         if bits & L.ST_STREAM_OVERFLOW:
-            slot = (int(nbytes.max().item()) + 64 + 7) // 8 * 8       # exact size is known even on overflow
+            slot = (int(nb_host.max()) + 64 + 7) // 8 * 8             # exact size is known even on overflow
             status.zero_()
             continue
         out = RlgrStreams(buf, slot, nbytes, n, nch, index)
+        out._sizes = [int(x) for x in nb_host]
         if want_stats and n > 0 and nch > 0:
             st = (C.c_ulonglong * 6)()
             check(lib.raht_rlgr_encode_stats(ptr(ws), n, nch, st, stream()), "raht_rlgr_encode_stats")
@@ -452,11 +469,13 @@ def rlgr_decode(streams: RlgrStreams, flag_signed=1, use_index=True) -> torch.Te
 
 
 def sse(A: torch.Tensor, B: torch.Tensor, c0=0, c1=None) -> torch.Tensor:
+    """Sum of squared differences of two (n, D) matrices (fp32 or fp64 each), accumulated in fp64 -> device double."""
     n, D = A.shape
     c1 = D if c1 is None else c1
     out = torch.empty(1, dtype=torch.float64, device=A.device)
     ws_bytes = lib.raht_sse_workspace_bytes(n, D)
     ws = workspace(ws_bytes, A.device)
-    check(lib.raht_sse_f64(ptr(A.contiguous()), ptr(B.contiguous()), n, D, c0, c1, ptr(out), ptr(ws), ws_bytes, stream()),
-          "raht_sse_f64")
+    A, B = A.contiguous(), B.contiguous()
+    check(lib.raht_sse(ptr(A), L.dtype_tag(A.dtype), ptr(B), L.dtype_tag(B.dtype), n, D, c0, c1, ptr(out), ptr(ws), ws_bytes, stream()),
+          "raht_sse")
     return out

@@ -422,7 +422,11 @@ def test_scene_pipeline_matches_direct_calls():
         enc = codec.encode_scene(*[cu(a) for a in sc], J=J, step=step)
         _, Crec = codec.decode_scene(enc)
         assert o["nvox"] == enc.nvox and o["sizes"] == enc.streams.sizes()
-        assert bytes(o["streams"].numpy()) == b"".join(enc.streams.to_bytes())
+        raw, off, parts = o["streams"].numpy(), 0, []
+        for sz in o["sizes"]:                                            # streams end to end, each padded to 8 bytes
+            parts.append(bytes(raw[off:off + sz]))
+            off += (sz + 7) // 8 * 8
+        assert parts == enc.streams.to_bytes() and off == raw.size
         assert np.array_equal(o["keys"].numpy(), enc.keys.cpu().numpy())
         assert np.array_equal(o["attributes"].numpy().reshape(enc.nvox, -1), Crec.cpu().numpy())
     # result="psnr": the squared error instead of the attributes
