@@ -324,10 +324,45 @@ template <int NC> struct ChunkSol {
     int rounds;
 };
 
-template <int NC> __device__ __forceinline__ void recode(const LaneBlock &B, ChunkSol<NC> &S, unsigned dirty)
+// The 8-candidate solves of the sparse channels are bound by the latency of a lone warp (a few chunks per channel,
+// every lane coding its block from up to 8 states one after the other: measured 200 k cycles per round against 30 k
+// for a dense chunk).  Their CTA therefore carries 7 more warps that each code the blocks from ONE of the distinct
+// states: the solving warp posts the states in shared memory, all 8 warps run the single-state coder side by side.
+struct Helpers {
+    uint32_t state[8][32], out[8][32], bits[8][32];      // [distinct state k][lane]
+    int m[32];                                           // distinct states posted by the lane
+    long long w;                                         // chunk being solved
+    int cmd;                                             // 1: states posted, 0: finished
+};
+
+__device__ __forceinline__ void helper_loop(Helpers *H, const uint2 *__restrict__ ev, const Geometry &G, int ch, const ChanInfo &I)
 {
-    if (!dirty) return;
+    const int lane = threadIdx.x & 31, k = threadIdx.x >> 5;
+    for (;;) {
+        __syncthreads();                                                        // (A) a command is posted
+        if (H->cmd == 0) break;
+        if (H->m[lane] > k) {
+            const LaneBlock B = lane_block(ev, G, ch, (int64_t)H->w, I);
+            State t[1] = {unpack_state(H->state[k][lane])};
+            uint32_t b[1];
+            count_lane<1>(B, t, b);
+            H->out[k][lane] = pack_state(t[0]);
+            H->bits[k][lane] = b[0];
+        }
+        __syncthreads();                                                        // (B) results are in
+    }
+}
+__device__ __forceinline__ void helpers_release(Helpers *H)                      // by the solving warp, all lanes
+{
+    __syncwarp();
+    if ((threadIdx.x & 31) == 0) H->cmd = 0;
+    __syncthreads();                                                            // (A)
+}
+
+template <int NC> __device__ __forceinline__ void recode(const LaneBlock &B, ChunkSol<NC> &S, unsigned dirty, Helpers *H)
+{
     if (NC == 1) {
+        if (!dirty) return;
         State t[1] = {unpack_state(S.in[0])};
         uint32_t b[1];
         count_lane<1>(B, t, b);
@@ -335,6 +370,7 @@ template <int NC> __device__ __forceinline__ void recode(const LaneBlock &B, Chu
         S.bits[0] = b[0];
         return;
     }
+    if (!H && !dirty) return;
     // the distinct states among the dirty candidates, coded side by side
     uint32_t ds[NC];
     int rep[NC], m = 0;
@@ -348,8 +384,21 @@ template <int NC> __device__ __forceinline__ void recode(const LaneBlock &B, Chu
     }
     State t[NC];
     uint32_t b[NC];
-    for (int k = 0; k < NC; ++k) t[k] = unpack_state(ds[k < m ? k : 0]);
-    if (m == 1) count_lane<1>(B, t, b);
+    for (int k = 0; k < NC; ++k) { t[k] = unpack_state(ds[k < m ? k : 0]); b[k] = 0; }
+    if (H) {                                             // (the whole warp is here: the barriers are CTA-wide)
+        const int lane = threadIdx.x & 31;
+        if (!__any_sync(~0u, m > 1)) {                   // one state per lane: nothing to share out
+            if (m) count_lane<1>(B, t, b);
+        } else {
+            H->m[lane] = m;
+            for (int k = 1; k < NC; ++k) if (k < m) H->state[k][lane] = ds[k];
+            if (lane == 0) H->cmd = 1;
+            __syncthreads();                                                    // (A)
+            if (m) count_lane<1>(B, t, b);
+            __syncthreads();                                                    // (B)
+            for (int k = 1; k < NC; ++k) if (k < m) { t[k] = unpack_state(H->out[k][lane]); b[k] = H->bits[k][lane]; }
+        }
+    } else if (m == 1) count_lane<1>(B, t, b);
     else if (m == 2) count_lane<(NC >= 2 ? 2 : 1)>(B, t, b);
     else if (m <= 4) count_lane<(NC >= 4 ? 4 : 1)>(B, t, b);
     else count_lane<NC>(B, t, b);
@@ -400,7 +449,7 @@ template <int NC> __device__ __forceinline__ void walk_chains(ChunkSol<NC> &S, b
 // previous chunk can end in); pin_need: mask of the pinned candidates whose chains must be complete before stopping.
 template <int NC>
 __device__ __forceinline__ void solve_chunk(const LaneBlock &B, bool pin, const uint32_t *pin_states, unsigned pin_need,
-                                            int max_rounds, ChunkSol<NC> &S)
+                                            int max_rounds, ChunkSol<NC> &S, Helpers *H = nullptr)
 {
     const int lane = threadIdx.x & 31;
     bool has = B.cnt > 0 || B.is_tail;
@@ -420,7 +469,7 @@ __device__ __forceinline__ void solve_chunk(const LaneBlock &B, bool pin, const 
     unsigned dirty = has ? (1u << NC) - 1 : 0u;
     int r = 0;
     for (;;) {
-        recode<NC>(B, S, dirty);
+        recode<NC>(B, S, dirty, H);
         ++r;
         dirty = 0;
         uint32_t o[NC];
@@ -519,7 +568,8 @@ __device__ __forceinline__ uint32_t word_of(const uint4 &a, const uint4 &b, int 
 __device__ __forceinline__ bool channel_is_dense(const ChanInfo &I, const Geometry &G) { return (int64_t)I.events * 2 >= G.n; }
 
 // ---- A: speculate ----------------------------------------------------------------------------------------
-constexpr int SPEC_WARPS = 4;
+constexpr int SPEC_WARPS = 4;        // table / emit passes: chunks per CTA
+constexpr int SOLVE_WARPS = 8;       // speculation and resolve: 8 dense chunks per CTA, or one sparse chunk and its 7 helper warps
 constexpr int SPEC_ROUNDS = 4;       // speculation: a chain that is not complete by then is left invalid
 constexpr int RESPEC_ROUNDS = 6;     // second sweep (candidates = the predecessor's end states)
 constexpr int PIN_ROUNDS = 34;       // chunk 0 and repairs: the pinned chain always completes
@@ -532,10 +582,12 @@ constexpr int PIN_ROUNDS = 34;       // chunk 0 and repairs: the pinned chain al
 template <int NC>
 __device__ __forceinline__ void speculate_chunk(const Geometry &G, const ChanInfo *__restrict__ info, const uint2 *__restrict__ ev,
                                                 int sweep, const uint4 *__restrict__ rec_prev, uint4 *__restrict__ rec,
-                                                uint4 *__restrict__ lanerec, unsigned long long *stats)
+                                                uint4 *__restrict__ lanerec, unsigned long long *stats, Helpers *H)
 {
     const int ch = blockIdx.y;
-    const int64_t w = (int64_t)blockIdx.x * SPEC_WARPS + (threadIdx.x >> 5);
+    const int warp = threadIdx.x >> 5;
+    // dense: a chunk per warp; sparse: a chunk per CTA, warp 0 solves and the others code single states for it
+    const int64_t w = NC == 1 ? (int64_t)blockIdx.x * SOLVE_WARPS + warp : (int64_t)blockIdx.x;
     const int lane = threadIdx.x & 31;
     const ChanInfo I = info[ch];
     if (w >= (int64_t)I.nchunks || channel_is_dense(I, G) != (NC == 1)) return;
@@ -571,15 +623,22 @@ __device__ __forceinline__ void speculate_chunk(const Geometry &G, const ChanInf
             }
         }
         if (!again) {                                             // keep the record of the first sweep
-            if (lane < REC_WORDS) rec[ci * REC_WORDS + lane] = mine[lane];
+            if (warp == 0 || NC == 1)
+                if (lane < REC_WORDS) rec[ci * REC_WORDS + lane] = mine[lane];
             return;
         }
     }
+    if (NC > 1 && warp > 0) {                                     // helper warps of a sparse chunk
+        helper_loop(H, ev, G, ch, I);
+        return;
+    }
+    if (NC > 1 && lane == 0) H->w = (long long)w;                 // (read by the helpers after the first barrier)
     const LaneBlock B = lane_block(ev, G, ch, w, I);
     ChunkSol<NC> S;
     const long long t0 = clock64();
     // (chunk 0 of a dense channel runs until its pinned chain is complete; a sparse one falls back on its table)
-    solve_chunk<NC>(B, pin, pins, need, (w == 0 && NC == 1) ? PIN_ROUNDS : (sweep ? RESPEC_ROUNDS : SPEC_ROUNDS), S);
+    solve_chunk<NC>(B, pin, pins, need, (w == 0 && NC == 1) ? PIN_ROUNDS : (sweep ? RESPEC_ROUNDS : SPEC_ROUNDS), S, NC > 1 ? H : nullptr);
+    if (NC > 1) helpers_release(H);
     finish_chunk<NC>(S, rec + ci * REC_WORDS, lanerec + ci * 32 * LANEREC_WORDS);
     if ((threadIdx.x & 31) == 0 && stats) {
         atomicAdd(stats + 0, 1ull);
@@ -589,15 +648,17 @@ __device__ __forceinline__ void speculate_chunk(const Geometry &G, const ChanInf
     }
 }
 
-// one launch for both kinds of channel (blockIdx.z): the few chunks of the sparse channels, bound by the latency
-// of their 8-candidate chains, run under the many chunks of the dense channels, which are bound by issue slots
-__global__ void __launch_bounds__(32 * SPEC_WARPS) rlgr_speculate_kernel(Geometry G, const ChanInfo *__restrict__ info,
-                                                                        const uint2 *__restrict__ ev, int sweep,
-                                                                        const uint4 *__restrict__ rec_prev, uint4 *__restrict__ rec,
-                                                                        uint4 *__restrict__ lanerec, unsigned long long *stats)
+// one launch for both kinds of channel (blockIdx.z): the few chunks of the sparse channels (z = 0, scheduled first:
+// one chunk per CTA, bound by the latency of their chains) run under the many chunks of the dense channels
+// (z = 1: 8 chunks per CTA, bound by issue slots)
+__global__ void __launch_bounds__(32 * SOLVE_WARPS) rlgr_speculate_kernel(Geometry G, const ChanInfo *__restrict__ info,
+                                                                         const uint2 *__restrict__ ev, int sweep,
+                                                                         const uint4 *__restrict__ rec_prev, uint4 *__restrict__ rec,
+                                                                         uint4 *__restrict__ lanerec, unsigned long long *stats)
 {
-    if (blockIdx.z == 0) speculate_chunk<8>(G, info, ev, sweep, rec_prev, rec, lanerec, stats);
-    else speculate_chunk<1>(G, info, ev, sweep, rec_prev, rec, lanerec, stats);
+    __shared__ Helpers helpers;
+    if (blockIdx.z == 0) speculate_chunk<8>(G, info, ev, sweep, rec_prev, rec, lanerec, stats, &helpers);
+    else speculate_chunk<1>(G, info, ev, sweep, rec_prev, rec, lanerec, stats, nullptr);
 }
 
 // ---- table mode for the sparse channels ---------------------------------------------------------------------------
@@ -772,7 +833,7 @@ __global__ void __launch_bounds__(32 * SPEC_WARPS) rlgr_table_lanes_kernel(Geome
 }
 
 // ---- B: resolve ------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(32) rlgr_resolve_kernel(Geometry G, const ChanInfo *__restrict__ info,
+__global__ void __launch_bounds__(32 * SOLVE_WARPS) rlgr_resolve_kernel(Geometry G, const ChanInfo *__restrict__ info,
                                                           const uint2 *__restrict__ ev, uint4 *__restrict__ rec,
                                                           uint4 *__restrict__ lanerec, unsigned long long *__restrict__ chunkoff,
                                                           int64_t slot_bytes, int64_t *__restrict__ nbytes,
@@ -785,6 +846,11 @@ __global__ void __launch_bounds__(32) rlgr_resolve_kernel(Geometry G, const Chan
     const ChanInfo I = info[ch];
     const int64_t nchunks = I.nchunks;
     const bool dense = channel_is_dense(I, G);
+    __shared__ Helpers helpers;                          // warps 1..7: single-state coders for the re-solves of a sparse channel
+    if (threadIdx.x >= 32) {
+        if (!dense) helper_loop(&helpers, ev, G, ch, I);
+        return;
+    }
     unsigned long long table_hits = 0;
     State s = initial_state();
     unsigned long long off = 0;
@@ -831,7 +897,8 @@ __global__ void __launch_bounds__(32) rlgr_resolve_kernel(Geometry G, const Chan
                 rounds = S.rounds;
             } else {
                 ChunkSol<8> S;
-                solve_chunk<8>(B, true, pins, 1u, PIN_ROUNDS, S);
+                if (lane == 0) helpers.w = (long long)w;
+                solve_chunk<8>(B, true, pins, 1u, PIN_ROUNDS, S, &helpers);
                 finish_chunk<8>(S, rec + ci * REC_WORDS, lr);
                 rounds = S.rounds;
             }
@@ -847,6 +914,7 @@ __global__ void __launch_bounds__(32) rlgr_resolve_kernel(Geometry G, const Chan
         s = unpack_state(__shfl_sync(~0u, half_of(m1, b), i));
       }
     }
+    if (!dense) helpers_release(&helpers);
     if (lane == 0) {
         const int64_t nb = (int64_t)((off + 7) >> 3);
         nbytes[ch] = nb;
@@ -1096,13 +1164,13 @@ RAHT_API int raht_rlgr_encode(const int32_t *q, int64_t n, int64_t ld, int nch, 
     (raht_count_launches(1), rlgr_scan_kernel)<<<nch, 1024, 0, st>>>(G, cnt, lastnz, info);
     (raht_count_launches(1), rlgr_scatter_kernel)<<<dim3(groups, nch), 32 * K1_WARPS, 0, st>>>(q, G, cnt, lastnz, ev, blockpos);
     const dim3 cgrid((unsigned)((G.W + SPEC_WARPS - 1) / SPEC_WARPS), nch);
-    const dim3 sgrid(cgrid.x, nch, 2);
-    (raht_count_launches(1), rlgr_speculate_kernel)<<<sgrid, 32 * SPEC_WARPS, 0, st>>>(G, info, ev, 0, nullptr, rec0, lanerec, stats);
-    (raht_count_launches(1), rlgr_speculate_kernel)<<<sgrid, 32 * SPEC_WARPS, 0, st>>>(G, info, ev, 1, rec0, rec, lanerec, stats);
+    const dim3 sgrid((unsigned)G.W, nch, 2);                 // z = 0: a sparse chunk per CTA; z = 1: 8 dense chunks per CTA (the rest exit)
+    (raht_count_launches(1), rlgr_speculate_kernel)<<<sgrid, 32 * SOLVE_WARPS, 0, st>>>(G, info, ev, 0, nullptr, rec0, lanerec, stats);
+    (raht_count_launches(1), rlgr_speculate_kernel)<<<sgrid, 32 * SOLVE_WARPS, 0, st>>>(G, info, ev, 1, rec0, rec, lanerec, stats);
     const dim3 bgrid((unsigned)((G.nsb + SPEC_WARPS - 1) / SPEC_WARPS), nch);
     (raht_count_launches(1), rlgr_table_kernel)<<<bgrid, 32 * SPEC_WARPS, 0, st>>>(G, info, ev, rec, lanerec, tables, headers);
     (raht_count_launches(1), rlgr_chunk_table_kernel)<<<cgrid, 32 * SPEC_WARPS, 0, st>>>(G, info, tables, headers, ctab);
-    (raht_count_launches(1), rlgr_resolve_kernel)<<<nch, 32, 0, st>>>(G, info, ev, rec, lanerec, chunkoff, slot_bytes, nbytes,
+    (raht_count_launches(1), rlgr_resolve_kernel)<<<nch, 32 * SOLVE_WARPS, 0, st>>>(G, info, ev, rec, lanerec, chunkoff, slot_bytes, nbytes,
                                                                     totals, status, stats, headers, ctab, cstart);
     (raht_count_launches(1), rlgr_table_lanes_kernel)<<<cgrid, 32 * SPEC_WARPS, 0, st>>>(G, info, tables, headers, cstart, lanerec);
     (raht_count_launches(1), rlgr_zero_kernel)<<<dim3(64, nch), 256, 0, st>>>(streams, slot_bytes, totals);
