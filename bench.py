@@ -52,9 +52,17 @@ def load_peaks():
 # ---------------------------------------------------------------------------------------------------
 # CPU path (oracle): used for cpu_baseline and for --impl reference
 # ---------------------------------------------------------------------------------------------------
+def host_cores():
+    try:
+        return max(1, len(os.sched_getaffinity(0)))
+    except AttributeError:
+        return max(1, os.cpu_count() or 1)
+
+
 def cpu_pipeline(scene, J, step, use_ref_rlgr):
     """Full encode + decode on the host with the CPU restatement of the reference (oracle/)."""
     from oracle import oracle_ctypes as orc
+    orc.set_num_threads(host_cores())                     # (torchrun exports OMP_NUM_THREADS=1: the CPU arm gets every core anyway)
     means, quats, scales, opac, colors = scene
     n = means.shape[0]
     r = orc.voxelize(means, J, want_delta=False)
@@ -68,8 +76,12 @@ def cpu_pipeline(scene, J, step, use_ref_rlgr):
     q = np.ascontiguousarray(orc.quantize(T, step)[order].T.astype(np.int32))
     nvox = q.shape[1]
     if use_ref_rlgr:
-        streams = [orc.ref_rlgr_encode(q[c].astype(np.int64), 1)[0] for c in range(q.shape[0])]
-        qd = np.stack([orc.ref_rlgr_decode(streams[c], nvox, 1)[0] for c in range(q.shape[0])]).astype(np.int32)
+        # the reference codes its channels one after the other on one core (encode_3dgs.py:225-247); here every channel
+        # gets its own host thread (ctypes releases the GIL), so the CPU arm uses all the cores it can
+        from concurrent.futures import ThreadPoolExecutor
+        with ThreadPoolExecutor(max_workers=host_cores()) as pool:
+            streams = list(pool.map(lambda c: orc.ref_rlgr_encode(q[c].astype(np.int64), 1)[0], range(q.shape[0])))
+            qd = np.stack(list(pool.map(lambda c: orc.ref_rlgr_decode(streams[c], nvox, 1)[0], range(q.shape[0])))).astype(np.int32)
     else:
         _, out, cap, nb = orc.rlgr_encode_channels(q, 1)
         qd = orc.rlgr_decode_channels(out, cap, nb, nvox, q.shape[0], 1)
@@ -522,7 +534,7 @@ def run_reference(args):
     kind = "port"   # the transform/voxeliser are the C restatement; only the entropy coder is the reference's own object code
     cpu = {"value": round(v, 1), "unit": "Gaussians/s", "cores": orc.num_threads(), "kind": kind,
            "sample": f"first {sample} Gaussians of the scene per step; oracle/raht_oracle.c (OpenMP) + "
-                     + ("reference RLGR coder oracle/_ref/librlgr_ref.so (1 thread, as the reference)" if use_ref else "oracle RLGR (1 thread per channel)")}
+                     + ("reference RLGR coder oracle/_ref/librlgr_ref.so, one channel per host thread" if use_ref else "oracle RLGR (1 thread per channel)")}
     line = {
         "impl": "reference", "metric": "Gaussians/s full RAHT encode+decode (59 ch)", "value": round(v, 1), "unit": "Gaussians/s",
         "n_gpus": int(os.environ.get("WORLD_SIZE", "1")), "steps": args.steps, "warmup": args.warmup, "ms_per_step": round(secs * 1e3, 2),
