@@ -182,7 +182,11 @@ transform_stage0_kernel(PlanDev P, const Tin *__restrict__ A, const Tel *B, Tel 
 // processed in passes of DS = min(D, UP_ELEMS / n_rows) so that any tile fits the same shared-memory
 // budget; a typical tile (100-300 rows) takes one pass.  A: source of a row unless this tile deferred
 // it and B is given (inverse: then B, which the upper stage already wrote).  O: destination.
+// The butterflies of different channels are independent, so a stage with few tiles (the top of the hierarchy: 16, 2,
+// 1 tiles, each a serial chain of up to 64 rounds) is spread over gridDim.y groups of channels: a lone CTA per tile
+// took 40 us there whatever the tile held.
 constexpr int UP_ELEMS = 8192;     // row elements staged per pass
+constexpr int UP_GROUPS_MAX = 16;
 
 template <typename Tel, bool FWD>
 __global__ void __launch_bounds__(TR_THREADS)
@@ -237,10 +241,13 @@ transform_upper_kernel(PlanDev P, int stage, const Tel *A, const Tel *B, Tel *O,
     __syncthreads();
 
     using AR = Arith<Tel>;
+    const int per = (D + (int)gridDim.y - 1) / (int)gridDim.y;            // channels of this CTA's group
+    const int cb = (int)blockIdx.y * per, ce = min(D, cb + per);
+    if (cb >= ce) return;
     int DS = UP_ELEMS / n_rows;
-    if (DS > D) DS = D;
-    for (int d0 = 0; d0 < D; d0 += DS) {
-        const int dn = min(DS, D - d0);
+    if (DS > ce - cb) DS = ce - cb;
+    for (int d0 = cb; d0 < ce; d0 += DS) {
+        const int dn = min(DS, ce - d0);
         const int n_el = n_rows * dn;
         for (int i = tid; i < n_el; i += TR_THREADS) {
             const int j = i / dn, c = i - j * dn;
@@ -312,7 +319,11 @@ int launch_upper(const raht_plan *P, int k, const Tel *A, const Tel *B, Tel *O, 
     const size_t smem = (size_t)(UP_ELEMS + 2 * PLAN_UP_CAP) * sizeof(Tel) + (size_t)PLAN_UP_CAP * 9 + 16;
     auto kern = transform_upper_kernel<Tel, FWD>;
     RAHT_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    (raht_count_launches(1), kern)<<<(unsigned)P->d.tiles[k], TR_THREADS, smem, st>>>(P->d, k, A, B, O, D);
+    const int64_t tiles = P->d.tiles[k];
+    int groups = tiles >= 2 * sm_count_cached() ? 1 : (int)((4 * (int64_t)sm_count_cached() + tiles - 1) / tiles);
+    if (groups > UP_GROUPS_MAX) groups = UP_GROUPS_MAX;
+    if (groups > D) groups = D;
+    (raht_count_launches(1), kern)<<<dim3((unsigned)tiles, (unsigned)groups), TR_THREADS, smem, st>>>(P->d, k, A, B, O, D);
     RAHT_LAUNCH_CHECK();
     return RAHT_OK;
 }

@@ -148,7 +148,8 @@ plan_tile_kernel(PlanDev P, int stage, const uint8_t *__restrict__ level, double
     __shared__ int hist[PLAN_MAX_ROUNDS], offs[PLAN_MAX_ROUNDS], cur[PLAN_MAX_ROUNDS];
     __shared__ int s_off[PLAN_FANIN + 1];
     __shared__ int wsum[PB_WARPS];
-    __shared__ int s_nbf, s_nr, s_bfoff, s_run;
+    __shared__ int s_nbf, s_nr, s_bfoff, s_run, s_npend;
+    __shared__ uint16_t s_pend[PLAN_UP_CAP];       // entries whose partners lie far away
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int64_t tile = blockIdx.x;
@@ -158,6 +159,7 @@ plan_tile_kernel(PlanDev P, int stage, const uint8_t *__restrict__ level, double
     const int64_t n_total = P.n;
 
     if (tid < PLAN_MAX_ROUNDS) { hist[tid] = 0; cur[tid] = 0; }
+    if (tid == 0) s_npend = 0;
     int n_rows;
     if (stage == 0) {
         const int64_t base = tile * P.tile_rows;
@@ -191,8 +193,11 @@ plan_tile_kernel(PlanDev P, int stage, const uint8_t *__restrict__ level, double
     if (tid == 0 && last) { s_lev[n_rows] = 255; s_orig[n_rows] = (uint32_t)n_total; }   // virtual end of the cloud
     __syncthreads();
 
-    // partner search: s = nearest earlier entry with a higher level, t = nearest later one
+    // partner search: s = nearest earlier entry with a higher level, t = nearest later one.  Nearly every entry finds
+    // both within a few positions; the few that have to look far (the high levels of an upper tile: up to 1000 steps,
+    // which used to set the duration of the whole stage) are handed to a warp each, 32 positions per step.
     const int lim = last ? n_rows + 1 : n_rows;
+    constexpr int NEAR = 16;
     for (int j = tid; j < n_rows; j += PB_THREADS) {
         const int l = s_lev[j];
         if (l == 255) {                                   // the root: never a right sibling
@@ -202,15 +207,48 @@ plan_tile_kernel(PlanDev P, int stage, const uint8_t *__restrict__ level, double
             continue;
         }
         int s = -1, t = -1;
-        for (int i = j - 1; i >= 0; --i)
+        bool far = false;
+        const int lo = max(0, j - NEAR);
+        for (int i = j - 1; i >= lo; --i)
             if (s_lev[i] > l) { s = i; break; }
-        if (s >= 0)
-            for (int i = j + 1; i < lim; ++i)
+        if (s < 0 && lo > 0) far = true;
+        if (!far && s >= 0) {
+            const int hi = min(lim, j + 1 + NEAR);
+            for (int i = j + 1; i < hi; ++i)
                 if (s_lev[i] > l) { t = i; break; }
+            if (t < 0 && hi < lim) far = true;
+        }
+        if (far) {
+            s_pend[atomicAdd(&s_npend, 1)] = (uint16_t)j;
+            continue;
+        }
         const bool in_tile = (s >= 0) && (t >= 0);
         s_s[j] = in_tile ? (uint16_t)s : (uint16_t)0xffff;
         s_t[j] = in_tile ? (uint16_t)t : (uint16_t)1;
         if (in_tile) atomicAdd(&hist[min(l, PLAN_MAX_ROUNDS - 1)], 1);
+    }
+    __syncthreads();
+    for (int p = warp; p < s_npend; p += PB_WARPS) {
+        const int j = s_pend[p];
+        const int l = s_lev[j];
+        int s = -1, t = -1;
+        for (int base = j - 1; base >= 0 && s < 0; base -= 32) {
+            const int i = base - lane;
+            const unsigned b = __ballot_sync(~0u, i >= 0 && s_lev[i] > l);
+            if (b) s = base - (__ffs((int)b) - 1);
+        }
+        if (s >= 0)
+            for (int base = j + 1; base < lim && t < 0; base += 32) {
+                const int i = base + lane;
+                const unsigned b = __ballot_sync(~0u, i < lim && s_lev[i] > l);
+                if (b) t = base + (__ffs((int)b) - 1);
+            }
+        if (lane == 0) {
+            const bool in_tile = (s >= 0) && (t >= 0);
+            s_s[j] = in_tile ? (uint16_t)s : (uint16_t)0xffff;
+            s_t[j] = in_tile ? (uint16_t)t : (uint16_t)1;
+            if (in_tile) atomicAdd(&hist[min(l, PLAN_MAX_ROUNDS - 1)], 1);
+        }
     }
     if (tid == 0) s_run = 0;
     __syncthreads();
