@@ -174,6 +174,8 @@ def stage_bytes(nvox, n_in, payload, J):
         "raht_param": nvox * 21, "raht_param_dec": nvox * 21,
         "raht": nvox * (D * 4 + D * 8 + 13),            # fp32 packed rows in, fp64 coefficients out
         "quant_reorder": nvox * (D * 8 + 8 + D * 4),
+        "raht_quant": nvox * (D * 4 + 13 + 4 + D * 4),  # fused: fp32 rows in, int32 symbols out (the fp64 coefficients stay on chip)
+        "dequant_iraht": nvox * (D * 4 + 13 + 4 + D * 8),
         "rlgr_encode": nvox * D * 4 + payload,
         "rlgr_decode": payload + nvox * D * 4,
         "dequant_unreorder": nvox * (D * 4 + 8 + D * 8),
@@ -237,8 +239,8 @@ def run_gpu(args):
     h2d_bytes = sum(h.numel() * h.element_size() for h in host)
 
     def step_resident(timer=None):
-        enc = codec.encode_scene(*devt, J=J, step=STEP, transform_dtype=tdtype, tile_rows=args.tile_rows, timer=timer)
-        coords, Crec = codec.decode_scene(enc, reuse_tree=False, tile_rows=args.tile_rows, timer=timer)
+        enc = codec.encode_scene(*devt, J=J, step=STEP, transform_dtype=tdtype, tile_rows=args.tile_rows, timer=timer, fused=args.fused)
+        coords, Crec = codec.decode_scene(enc, reuse_tree=False, tile_rows=args.tile_rows, timer=timer, fused=args.fused)
         return enc, Crec
 
     def barrier():
@@ -557,6 +559,7 @@ def main():
     ap.add_argument("--dtype", default="f64", choices=["f64", "f32"], help="transform arithmetic (f64 = bit-exact mode)")
     ap.add_argument("--tile-rows", type=int, default=0)
     ap.add_argument("--cpu-sample", type=int, default=250_000)
+    ap.add_argument("--fused", action="store_true", help="transform and quantisation in one pass (raht_forward_quant / raht_dequant_inverse) instead of the reference's two")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--port-rlgr", action="store_true", help="reference arm: use the oracle RLGR port instead of oracle/_ref")
     args = ap.parse_args()

@@ -212,6 +212,18 @@ int raht_shard_top(const int64_t *first_keys, const int64_t *prev_last_keys, con
                    int P, void *rows, int dtype, int D, int inverse, uint8_t *level_out,
                    int32_t *status, void *stream);
 
+/* Fused forms of raht_forward + raht_quant_reorder and of raht_dequant_unreorder + raht_inverse (same results, bit for
+ * bit): the rows a stage-0 tile of the plan finishes -- all but the ones it defers to the upper stages -- are quantised
+ * straight out of shared memory (or dequantised straight into it), so the fp64 coefficient matrix never makes its round
+ * trip through HBM.  pos[n] (device int32): position of row r in the coded order (inverse permutation of order_RAGFT,
+ * raht_order_ragft's second output); steps[D] (device); q: channel-major int32 (D, ld).  T: scratch (n, D) of t_dtype;
+ * afterwards only the rows deferred by stage 0 hold coefficients.                                                      */
+int raht_forward_quant(const raht_plan *plan, const void *C, int c_dtype, int D, void *T, int t_dtype,
+                       const int32_t *pos, const double *steps, int32_t *q, int64_t ld, int32_t *status,
+                       int flags, void *stream);
+int raht_dequant_inverse(const raht_plan *plan, const int32_t *q, int64_t ld, const int32_t *pos,
+                         const double *steps, int D, void *T, int t_dtype, void *C, int flags, void *stream);
+
 /* ------------------------------------------------------------------------------------------------
  * (a9,a10,a11) Quantise + reorder + channel marshalling.  Replaces encode_3dgs.py:204 (floor(T/step
  * +0.5)), :210 (index_select(order_RAGFT)), :215-222 (int32 cast, per-channel sequences) and the

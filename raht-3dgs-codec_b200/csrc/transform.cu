@@ -29,8 +29,30 @@ template <> struct Arith<float> {
     static __device__ __forceinline__ float sub(float a, float b) { return __fsub_rn(a, b); }
 };
 
+// Quantisation fused into stage 0 (raht_forward_quant / raht_dequant_inverse): the rows a stage-0 tile finishes -- all
+// but the ~15 % it defers to the upper stages -- never exist as fp64 coefficients in HBM.
+//   QM_FWD: instead of the write-back, finished rows are quantised and stored at their order_RAGFT position in the
+//           channel-major int32 matrix; deferred rows go to T as before (the upper stages work on T, and
+//           quant_deferred_kernel quantises them afterwards);
+//   QM_INV: instead of the load from T, finished rows are gathered from the int32 matrix and dequantised; deferred
+//           rows come from C, where the upper stages left them (dequant_deferred_kernel fills T for those stages).
+enum { QM_NONE = 0, QM_FWD = 1, QM_INV = 2 };
+struct QuantArgs {
+    const int32_t *pos;        // [n] position of row r in the coded order (inverse permutation of order_RAGFT)
+    const double *steps;       // [D]
+    int32_t *q;                // (D, ld) channel-major
+    int64_t ld;
+    int32_t *status;
+};
+__device__ __forceinline__ int32_t quantise_one(double v, double step, bool &ovf)
+{
+    const double qq = floor(__dadd_rn(__ddiv_rn(v, step), 0.5));            // encode_3dgs.py:204
+    ovf |= !(qq >= -2147483648.0 && qq <= 2147483647.0);
+    return (int32_t)qq;                                                     // :215 .to(torch.int32)
+}
+
 template <typename Tel> struct SmemLayout {
-    size_t off_ab, off_sched, off_hdr, off_flag, off_bar, total;
+    size_t off_ab, off_sched, off_hdr, off_flag, off_bar, off_pos, off_step, total;
     __host__ __device__ SmemLayout(int R, int D)
     {
         size_t o = (size_t)R * D * sizeof(Tel);
@@ -40,6 +62,9 @@ template <typename Tel> struct SmemLayout {
         off_hdr = o; o += sizeof(TileHdr);
         off_bar = o; o += 8;
         off_flag = o; o += (size_t)R;
+        o = (o + 7) & ~(size_t)7;
+        off_step = o; o += (size_t)D * 8;
+        off_pos = o; o += (size_t)R * 4;
         total = (o + 15) & ~(size_t)15;
     }
 };
@@ -48,9 +73,9 @@ template <typename Tel> struct SmemLayout {
 // A: source rows (row-major, Tin).  B: second source for the rows this tile deferred (inverse only: the
 // upper stages have already rewritten them in the output), may be nullptr.  O: destination.
 // FWD: forward butterflies in schedule order, else inverse butterflies in reverse order.
-template <typename Tin, typename Tel, int DT, bool FWD>
+template <typename Tin, typename Tel, int DT, bool FWD, int QM = QM_NONE>
 __global__ void __launch_bounds__(TR_THREADS)
-transform_stage0_kernel(PlanDev P, const Tin *__restrict__ A, const Tel *B, Tel *O, int D_rt, int use_tma)
+transform_stage0_kernel(PlanDev P, const Tin *__restrict__ A, const Tel *B, Tel *O, int D_rt, int use_tma, QuantArgs Q)
 {
     extern __shared__ __align__(128) unsigned char tr_smem[];
     const int D = DT ? DT : D_rt;
@@ -62,6 +87,8 @@ transform_stage0_kernel(PlanDev P, const Tin *__restrict__ A, const Tel *B, Tel 
     TileHdr *s_hdr = (TileHdr *)(tr_smem + L.off_hdr);
     uint64_t *s_bar = (uint64_t *)(tr_smem + L.off_bar);
     uint8_t *s_flag = tr_smem + L.off_flag;
+    double *s_step = (double *)(tr_smem + L.off_step);
+    int32_t *s_pos = (int32_t *)(tr_smem + L.off_pos);
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int64_t tile = blockIdx.x;
@@ -79,9 +106,13 @@ transform_stage0_kernel(PlanDev P, const Tin *__restrict__ A, const Tel *B, Tel 
     bool tma_in = false, tma_out = false;
     if constexpr (sizeof(Tin) == sizeof(Tel)) {
         if (use_tma && (tile_bytes % 16) == 0) {
-            tma_in = (((uintptr_t)(A + base * D)) % 16) == 0;
-            tma_out = (((uintptr_t)(O + base * D)) % 16) == 0;
+            tma_in = QM != QM_INV && (((uintptr_t)(A + base * D)) % 16) == 0;
+            tma_out = QM != QM_FWD && (((uintptr_t)(O + base * D)) % 16) == 0;
         }
+    }
+    if constexpr (QM != QM_NONE) {
+        for (int c = tid; c < D; c += TR_THREADS) s_step[c] = Q.steps[c];
+        for (int j = tid; j < n_rows; j += TR_THREADS) s_pos[j] = Q.pos[base + j];
     }
     if (tma_in) {
         if (tid == 0) {
@@ -104,7 +135,7 @@ transform_stage0_kernel(PlanDev P, const Tin *__restrict__ A, const Tel *B, Tel 
         s_ab[2 * j] = (Tel)c.x;
         s_ab[2 * j + 1] = (Tel)c.y;
     }
-    const bool patch = (B != nullptr);
+    const bool patch = (B != nullptr) || QM == QM_FWD;       // (QM_FWD: the flags pick the rows that go to T)
     if (patch) {
         for (int j = tid; j < n_rows; j += TR_THREADS) s_flag[j] = 0;
         __syncthreads();
@@ -115,13 +146,22 @@ transform_stage0_kernel(PlanDev P, const Tin *__restrict__ A, const Tel *B, Tel 
 
     if (tma_in) {
         mbar_wait(s_bar, 0);
+    } else if constexpr (QM == QM_INV) {
+        // a warp per channel: the positions of consecutive rows of one level bucket are consecutive
+        for (int c = warp; c < D; c += TR_WARPS) {
+            const int32_t *qc = Q.q + (size_t)c * Q.ld;
+            const double st = s_step[c];
+            for (int j = lane; j < n_rows; j += 32)
+                if (!(B != nullptr && s_flag[j])) s_rows[j * D + c] = (Tel)__dmul_rn((double)qc[s_pos[j]], st);   // encode_3dgs.py:261
+        }
+        __syncthreads();
     } else {
         const Tin *src = A + base * D;
         const int n_el = n_rows * D;
         for (int i = tid; i < n_el; i += TR_THREADS) s_rows[i] = (Tel)src[i];
         __syncthreads();
     }
-    if (patch) {
+    if (patch && B != nullptr) {
         for (int j = warp; j < n_rows; j += TR_WARPS)
             if (s_flag[j]) {
                 const Tel *src = B + (size_t)(base + j) * D;
@@ -157,7 +197,21 @@ transform_stage0_kernel(PlanDev P, const Tin *__restrict__ A, const Tel *B, Tel 
     }
 
     // write back
-    if (tma_out) {
+    if constexpr (QM == QM_FWD) {
+        bool ovf = false;
+        for (int c = warp; c < D; c += TR_WARPS) {
+            int32_t *qc = Q.q + (size_t)c * Q.ld;
+            const double st = s_step[c];
+            for (int j = lane; j < n_rows; j += 32)
+                if (!s_flag[j]) qc[s_pos[j]] = quantise_one((double)s_rows[j * D + c], st, ovf);
+        }
+        if (__any_sync(~0u, ovf) && lane == 0 && Q.status) atomicOr(Q.status, RAHT_ST_INT32_OVERFLOW);
+        for (int j = warp; j < n_rows; j += TR_WARPS)
+            if (s_flag[j]) {
+                Tel *dst = O + (size_t)(base + j) * D;
+                for (int c = lane; c < D; c += 32) dst[c] = s_rows[j * D + c];
+            }
+    } else if (tma_out) {
         fence_proxy_async();
         __syncthreads();
         if (tid == 0) {
@@ -286,6 +340,51 @@ transform_upper_kernel(PlanDev P, int stage, const Tel *A, const Tel *B, Tel *O,
     }
 }
 
+// rows the stage-0 tiles deferred, a warp per row: after the upper stages of the forward transform (T -> q), or before
+// those of the inverse (q -> T)
+template <typename Tel, bool TO_Q>
+__global__ void __launch_bounds__(TR_THREADS) deferred_rows_kernel(PlanDev P, Tel *T, int D, QuantArgs Q)
+{
+    const int64_t tile = blockIdx.x;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int n_def = min((int)P.hdr[tile].n_def, PLAN_DEFER_MAX);
+    bool ovf = false;
+    for (int j = warp; j < n_def; j += TR_WARPS) {
+        const size_t row = P.def_rows[(size_t)tile * PLAN_DEFER_MAX + j];
+        const size_t at = (size_t)Q.pos[row];
+        Tel *t = T + row * D;
+        for (int c = lane; c < D; c += 32) {
+            if (TO_Q) Q.q[(size_t)c * Q.ld + at] = quantise_one((double)t[c], Q.steps[c], ovf);
+            else t[c] = (Tel)__dmul_rn((double)Q.q[(size_t)c * Q.ld + at], Q.steps[c]);
+        }
+    }
+    if (TO_Q && __any_sync(~0u, ovf) && lane == 0 && Q.status) atomicOr(Q.status, RAHT_ST_INT32_OVERFLOW);
+}
+
+template <typename Tin, typename Tel, int DT, bool FWD, int QM>
+int launch_stage0_q(const raht_plan *P, const Tin *A, const Tel *B, Tel *O, int D, int use_tma, const QuantArgs &Q, cudaStream_t st)
+{
+    const int R = P->d.tile_rows;
+    SmemLayout<Tel> L(R, D);
+    auto kern = transform_stage0_kernel<Tin, Tel, DT, FWD, QM>;
+    if (L.total > 227 * 1024) {
+        raht_set_error("transform: tile of %d rows x %d channels needs %zu bytes of shared memory (> 227 KB)", R, D, L.total);
+        return RAHT_E_INVALID;
+    }
+    RAHT_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)L.total));
+    (raht_count_launches(1), kern)<<<(unsigned)P->d.tiles[0], TR_THREADS, L.total, st>>>(P->d, A, B, O, D, use_tma, Q);
+    RAHT_LAUNCH_CHECK();
+    return RAHT_OK;
+}
+template <typename Tin, typename Tel, bool FWD, int QM>
+int launch_stage0_qd(const raht_plan *P, const Tin *A, const Tel *B, Tel *O, int D, int use_tma, const QuantArgs &Q, cudaStream_t st)
+{
+    switch (D) {
+    case 59: return launch_stage0_q<Tin, Tel, 59, FWD, QM>(P, A, B, O, D, use_tma, Q, st);
+    default: return launch_stage0_q<Tin, Tel, 0, FWD, QM>(P, A, B, O, D, use_tma, Q, st);
+    }
+}
+
 template <typename Tin, typename Tel, int DT, bool FWD>
 int launch_stage0(const raht_plan *P, const Tin *A, const Tel *B, Tel *O, int D, int use_tma, cudaStream_t st)
 {
@@ -297,7 +396,7 @@ int launch_stage0(const raht_plan *P, const Tin *A, const Tel *B, Tel *O, int D,
         return RAHT_E_INVALID;
     }
     RAHT_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)L.total));
-    (raht_count_launches(1), kern)<<<(unsigned)P->d.tiles[0], TR_THREADS, L.total, st>>>(P->d, A, B, O, D, use_tma);
+    (raht_count_launches(1), kern)<<<(unsigned)P->d.tiles[0], TR_THREADS, L.total, st>>>(P->d, A, B, O, D, use_tma, QuantArgs());
     RAHT_LAUNCH_CHECK();
     return RAHT_OK;
 }
@@ -351,7 +450,71 @@ int inverse_impl(const raht_plan *P, const Tel *T, Tel *C, int D, int use_tma, c
     return rc;
 }
 
+template <typename Tin, typename Tel>
+int forward_quant_impl(const raht_plan *P, const Tin *C, Tel *T, int D, int use_tma, const QuantArgs &Q, cudaStream_t st)
+{
+    int rc = launch_stage0_qd<Tin, Tel, true, QM_FWD>(P, C, (const Tel *)nullptr, T, D, use_tma, Q, st);
+    for (int k = 1; k < P->d.n_stages && rc == RAHT_OK; ++k)
+        rc = launch_upper<Tel, true>(P, k, (const Tel *)T, (const Tel *)nullptr, T, D, st);
+    if (rc == RAHT_OK && P->d.n_stages > 1) {
+        raht_count_launches(1);
+        deferred_rows_kernel<Tel, true><<<(unsigned)P->d.tiles[0], TR_THREADS, 0, st>>>(P->d, T, D, Q);
+        RAHT_LAUNCH_CHECK();
+    }
+    return rc;
+}
+
+template <typename Tel>
+int dequant_inverse_impl(const raht_plan *P, Tel *T, Tel *C, int D, int use_tma, const QuantArgs &Q, cudaStream_t st)
+{
+    int rc = RAHT_OK;
+    const int S = P->d.n_stages;
+    if (S > 1) {
+        raht_count_launches(1);
+        deferred_rows_kernel<Tel, false><<<(unsigned)P->d.tiles[0], TR_THREADS, 0, st>>>(P->d, T, D, Q);
+        RAHT_LAUNCH_CHECK();
+    }
+    for (int k = S - 1; k >= 1 && rc == RAHT_OK; --k)
+        rc = launch_upper<Tel, false>(P, k, (const Tel *)T, k == S - 1 ? (const Tel *)nullptr : (const Tel *)C, C, D, st);
+    if (rc == RAHT_OK)
+        rc = launch_stage0_qd<Tel, Tel, false, QM_INV>(P, (const Tel *)T, S > 1 ? (const Tel *)C : (const Tel *)nullptr, C, D, use_tma, Q, st);
+    return rc;
+}
+
 }  // namespace
+
+RAHT_API int raht_forward_quant(const raht_plan *plan, const void *C, int c_dtype, int D, void *T, int t_dtype, const int32_t *pos,
+                                const double *steps, int32_t *q, int64_t ld, int32_t *status, int flags, void *stream)
+{
+    RAHT_REQUIRE(plan && D >= 1 && ld >= plan->d.n, "raht_forward_quant: bad arguments");
+    if (plan->d.n == 0) return RAHT_OK;
+    RAHT_REQUIRE(C && T && C != T && pos && steps && q, "raht_forward_quant: null or aliased pointer");
+    cudaStream_t st = (cudaStream_t)stream;
+    const int use_tma = (flags & 1) ? 0 : 1;
+    QuantArgs Q;
+    Q.pos = pos; Q.steps = steps; Q.q = q; Q.ld = ld; Q.status = status;
+    if (c_dtype == RAHT_F32 && t_dtype == RAHT_F64) return forward_quant_impl<float, double>(plan, (const float *)C, (double *)T, D, use_tma, Q, st);
+    if (c_dtype == RAHT_F64 && t_dtype == RAHT_F64) return forward_quant_impl<double, double>(plan, (const double *)C, (double *)T, D, use_tma, Q, st);
+    if (c_dtype == RAHT_F32 && t_dtype == RAHT_F32) return forward_quant_impl<float, float>(plan, (const float *)C, (float *)T, D, use_tma, Q, st);
+    raht_set_error("raht_forward_quant: unsupported dtype pair");
+    return RAHT_E_INVALID;
+}
+
+RAHT_API int raht_dequant_inverse(const raht_plan *plan, const int32_t *q, int64_t ld, const int32_t *pos, const double *steps, int D,
+                                  void *T, int t_dtype, void *C, int flags, void *stream)
+{
+    RAHT_REQUIRE(plan && D >= 1 && ld >= plan->d.n, "raht_dequant_inverse: bad arguments");
+    if (plan->d.n == 0) return RAHT_OK;
+    RAHT_REQUIRE(C && T && C != T && pos && steps && q, "raht_dequant_inverse: null or aliased pointer");
+    cudaStream_t st = (cudaStream_t)stream;
+    const int use_tma = (flags & 1) ? 0 : 1;
+    QuantArgs Q;
+    Q.pos = pos; Q.steps = steps; Q.q = const_cast<int32_t *>(q); Q.ld = ld; Q.status = nullptr;
+    if (t_dtype == RAHT_F64) return dequant_inverse_impl<double>(plan, (double *)T, (double *)C, D, use_tma, Q, st);
+    if (t_dtype == RAHT_F32) return dequant_inverse_impl<float>(plan, (float *)T, (float *)C, D, use_tma, Q, st);
+    raht_set_error("raht_dequant_inverse: bad dtype");
+    return RAHT_E_INVALID;
+}
 
 RAHT_API int raht_forward(const raht_plan *plan, const void *C, int c_dtype, int D, void *T, int t_dtype, int flags,
                           void *stream)

@@ -58,6 +58,8 @@ SIGNATURES = {
     "raht_plan_info": (_i, [_p, C.POINTER(_i64), _i]),
     "raht_forward": (_i, [_p, _p, _i, _i, _p, _i, _i, _p]),
     "raht_inverse": (_i, [_p, _p, _i, _i, _p, _i, _p]),
+    "raht_forward_quant": (_i, [_p, _p, _i, _i, _p, _i, _p, _p, _p, _i64, _p, _i, _p]),
+    "raht_dequant_inverse": (_i, [_p, _p, _i64, _p, _p, _i, _p, _i, _p, _i, _p]),
     "raht_quant_reorder": (_i, [_p, _i, _i64, _i, _p, _p, _p, _i64, _p, _p]),
     "raht_dequant_unreorder": (_i, [_p, _i64, _i64, _i, _p, _p, _p, _i, _p]),
     "raht_quantize_f64": (_i, [_p, _i64, _d, _p, _p]),

@@ -125,8 +125,13 @@ def voxelize_merge(means, quats, scales, opacities, colors, J, packed_dtype=torc
 
 
 @torch.no_grad()
-def encode_attributes(keys, Cmat, step, transform_dtype=torch.float64, tile_rows=None, timer=None, flags=0, status=None):
+def encode_attributes(keys, Cmat, step, transform_dtype=torch.float64, tile_rows=None, timer=None, flags=0, status=None, fused=False):
     """RAHT_param -> RAHT -> quantise -> reorder -> RLGR for rows that are Morton-sorted unique voxels.
+    fused: transform and quantisation in one pass (ops.forward_quant; same symbols, bit for bit), else the two
+    reference steps one after the other.  Off by default: on sparse scenes (the 1 M bench scene: consecutive voxels fall
+    into different level buckets of order_RAGFT) the fused pass scatters 4-byte symbols from the transform tiles and
+    is no faster than the two passes, whose reorder kernel moves whole rows (measured: forward -0.04 ms, inverse
+    +0.05 ms per step); it pays on dense clouds, where a tile's rows stay together in the coded order.
     Device-side validation (sorted/unique keys, int32 overflow, sort stall) accumulates in one status
     word that is read once, after the entropy coder."""
     timer = timer or StageTimer(False)
@@ -135,18 +140,22 @@ def encode_attributes(keys, Cmat, step, transform_dtype=torch.float64, tile_rows
     order, _ = tree.order(want_position=True)
     tree.plan(tile_rows)
     timer.mark("raht_param")
-    T = ops.forward(tree, Cmat, transform_dtype, tile_rows, flags)
-    timer.mark("raht")
-    q = ops.quant_reorder(T, order, step, status=status)
-    timer.mark("quant_reorder")
+    if fused:
+        q = ops.forward_quant(tree, Cmat, step, transform_dtype, tile_rows, flags, status)
+        timer.mark("raht_quant")
+    else:
+        T = ops.forward(tree, Cmat, transform_dtype, tile_rows, flags)
+        timer.mark("raht")
+        q = ops.quant_reorder(T, order, step, status=status)
+        timer.mark("quant_reorder")
     streams = ops.rlgr_encode(q, 1, status=status)
     timer.mark("rlgr_encode")
     return tree, streams
 
 
 @torch.no_grad()
-def decode_attributes(keys, streams, D, step, transform_dtype=torch.float64, tree=None, tile_rows=None, timer=None, flags=0):
-    """RLGR^-1 -> dequantise -> inverse reorder -> iRAHT."""
+def decode_attributes(keys, streams, D, step, transform_dtype=torch.float64, tree=None, tile_rows=None, timer=None, flags=0, fused=False):
+    """RLGR^-1 -> dequantise -> inverse reorder -> iRAHT (fused: the last three in one pass, ops.dequant_inverse)."""
     timer = timer or StageTimer(False)
     status = None
     if tree is None:
@@ -157,10 +166,14 @@ def decode_attributes(keys, streams, D, step, transform_dtype=torch.float64, tre
     order = tree.order()
     q = ops.rlgr_decode(streams, 1)
     timer.mark("rlgr_decode")
-    T = ops.dequant_unreorder(q, order, step, transform_dtype)
-    timer.mark("dequant_unreorder")
-    Crec = ops.inverse(tree, T, tile_rows, flags)
-    timer.mark("iraht")
+    if fused:
+        Crec = ops.dequant_inverse(tree, q, step, transform_dtype, tile_rows, flags)
+        timer.mark("dequant_iraht")
+    else:
+        T = ops.dequant_unreorder(q, order, step, transform_dtype)
+        timer.mark("dequant_unreorder")
+        Crec = ops.inverse(tree, T, tile_rows, flags)
+        timer.mark("iraht")
     if status is not None:
         ops.raise_for_status(int(L.read_host(status)[0][0]))      # the decoder's one synchronisation: were the keys a valid voxel list?
     return Crec
@@ -168,12 +181,12 @@ def decode_attributes(keys, streams, D, step, transform_dtype=torch.float64, tre
 
 @torch.no_grad()
 def encode_scene(means, quats, scales, opacities, colors, J, step, transform_dtype=torch.float64, tile_rows=None,
-                 timer=None, flags=0, keep_packed=False) -> EncodedScene:
+                 timer=None, flags=0, keep_packed=False, fused=False) -> EncodedScene:
     timer = timer or StageTimer(False)
     timer.mark("start")
     status = ops._status_word(means.device)
     packed, keys, info = voxelize_merge(means, quats, scales, opacities, colors, J, torch.float32, timer, status)
-    tree, streams = encode_attributes(keys, packed, step, transform_dtype, tile_rows, timer, flags, status)
+    tree, streams = encode_attributes(keys, packed, step, transform_dtype, tile_rows, timer, flags, status, fused)
     width, voxel_size = L.read_host(info["params_d2"])[0].tolist()          # after the coder's synchronisation: no extra wait
     return EncodedScene(J=J, n_in=info["N"], nvox=info["Nvox"], D=packed.shape[1], step=step, vmin=info["vmin"],
                         voxel_size=voxel_size, width=width, keys=keys, streams=streams,
@@ -181,12 +194,12 @@ def encode_scene(means, quats, scales, opacities, colors, J, step, transform_dty
 
 
 @torch.no_grad()
-def decode_scene(enc: EncodedScene, reuse_tree=False, tile_rows=None, timer=None, flags=0):
+def decode_scene(enc: EncodedScene, reuse_tree=False, tile_rows=None, timer=None, flags=0, fused=False):
     """Returns (voxel coordinates (nvox,3) fp32 integer-valued, attributes (nvox, D))."""
     timer = timer or StageTimer(False)
     timer.mark("start_dec")
     Crec = decode_attributes(enc.keys, enc.streams, enc.D, enc.step, enc.transform_dtype,
-                             enc.tree if reuse_tree else None, tile_rows, timer, flags)
+                             enc.tree if reuse_tree else None, tile_rows, timer, flags, fused)
     coords = torch.empty(enc.nvox, 3, dtype=torch.float32, device=enc.keys.device)
     check(lib.raht_morton_decode_f32(ptr(enc.keys), enc.nvox, enc.J, ptr(coords), stream()), "raht_morton_decode_f32")
     timer.mark("geometry")

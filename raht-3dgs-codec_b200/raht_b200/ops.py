@@ -374,6 +374,52 @@ def dequant_unreorder(q: torch.Tensor, order, step, out_dtype=torch.float64) -> 
     return T
 
 
+def forward_quant(tree: RahtTree, Cmat: torch.Tensor, step, out_dtype=torch.float64, tile_rows=None, flags=0, status=None) -> torch.Tensor:
+    """quant_reorder(forward(tree, C), order_RAGFT, step) in one pass (raht_forward_quant): the coefficients of the rows a
+    stage-0 tile finishes are quantised out of shared memory and never written as fp64.  Same q, bit for bit."""
+    L.require_cuda(Cmat, "C")
+    if Cmat.dtype not in (torch.float32, torch.float64):
+        Cmat = Cmat.to(torch.float64)
+    if Cmat.dtype == torch.float64 and out_dtype == torch.float32:
+        Cmat = Cmat.to(torch.float32)
+    Cmat = Cmat.contiguous()
+    n, D = Cmat.shape
+    if n != tree.n:
+        raise ValueError(f"C has {n} rows, tree has {tree.n}")
+    dev = Cmat.device
+    _, pos = tree.order(want_position=True)
+    steps = _steps_tensor(step, D, dev)
+    ld = max((n + 3) // 4 * 4, 1)
+    q = torch.empty(D, ld, dtype=torch.int32, device=dev)
+    T = torch.empty(n, D, dtype=out_dtype, device=dev)                  # scratch: only the deferred rows are written
+    deferred = status is not None
+    status = _status_word(dev) if status is None else status
+    check(lib.raht_forward_quant(tree.plan(tile_rows), ptr(Cmat), L.dtype_tag(Cmat.dtype), D, ptr(T), L.dtype_tag(out_dtype), ptr(pos),
+                                 ptr(steps), ptr(q), ld, ptr(status), flags, stream()), "raht_forward_quant")
+    if not deferred and int(L.read_host(status)[0][0]) & L.ST_INT32_OVERFLOW:
+        raise OverflowError("quantised coefficient does not fit int32 (encode_3dgs.py:215 would truncate)")
+    return q[:, :n]
+
+
+def dequant_inverse(tree: RahtTree, q: torch.Tensor, step, out_dtype=torch.float64, tile_rows=None, flags=0) -> torch.Tensor:
+    """inverse(tree, dequant_unreorder(q, order_RAGFT, step)) in one pass (raht_dequant_inverse)."""
+    L.require_cuda(q, "q")
+    D, n = q.shape
+    if n != tree.n:
+        raise ValueError(f"q has {n} columns, tree has {tree.n}")
+    dev = q.device
+    if q.dtype != torch.int32 or q.stride(1) != 1:
+        q = q.to(torch.int32).contiguous()
+    ld = q.stride(0) if D > 1 else max(n, 1)
+    _, pos = tree.order(want_position=True)
+    steps = _steps_tensor(step, D, dev)
+    T = torch.empty(n, D, dtype=out_dtype, device=dev)                  # scratch (deferred rows)
+    Cmat = torch.empty(n, D, dtype=out_dtype, device=dev)
+    check(lib.raht_dequant_inverse(tree.plan(tile_rows), ptr(q), ld, ptr(pos), ptr(steps), D, ptr(T), L.dtype_tag(out_dtype), ptr(Cmat),
+                                   flags, stream()), "raht_dequant_inverse")
+    return Cmat
+
+
 class RlgrStreams:
     """nch closed RLGR streams in one device buffer (slot per channel).
 

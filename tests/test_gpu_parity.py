@@ -439,3 +439,34 @@ def test_scene_pipeline_matches_direct_calls():
     _, Crec = codec.decode_scene(enc)
     sse = float(((packed.double() - Crec) ** 2).sum().item())
     assert abs(float(o["sse"][0]) - sse) <= 1e-9 * sse and "attributes" not in o
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("n,J,D,tile_rows,dtype", [(1, 3, 3, None, "f64"), (7, 2, 2, None, "f64"), (300, 5, 5, 32, "f64"),
+                                                   (20000, 8, 59, None, "f64"), (20000, 8, 59, 64, "f32"), (70000, 10, 11, 128, "f64")])
+def test_fused_quantisation_matches_the_two_reference_steps(n, J, D, tile_rows, dtype):
+    """raht_forward_quant == raht_forward + raht_quant_reorder and raht_dequant_inverse == raht_dequant_unreorder +
+    raht_inverse, bit for bit (encode_3dgs.py:198-210 and :255-276), whatever the number of plan stages."""
+    import torch
+    from raht_b200 import ops
+    rng = np.random.default_rng(n + D)
+    keys = np.sort(rng.choice(1 << (3 * J), size=min(n, 1 << (3 * J)), replace=False)).astype(np.int64)
+    C = rng.normal(0, 3, size=(keys.size, D)).astype(np.float32)
+    C[:, 0] *= 1000.0
+    tdt = torch.float64 if dtype == "f64" else torch.float32
+    steps = [0.03125 * (1 + (c % 3)) for c in range(D)]
+    for step in (0.25, steps):
+        tree = ops.tree_from_keys(torch.from_numpy(keys).cuda())
+        order = tree.order()
+        Cd = torch.from_numpy(C).cuda()
+        T = ops.forward(tree, Cd, tdt, tile_rows)
+        q_ref = ops.quant_reorder(T, order, step)
+        q = ops.forward_quant(tree, Cd, step, tdt, tile_rows)
+        assert torch.equal(q, q_ref)
+        rec_ref = ops.inverse(tree, ops.dequant_unreorder(q_ref, order, step, tdt), tile_rows)
+        rec = ops.dequant_inverse(tree, q_ref, step, tdt, tile_rows)
+        assert torch.equal(rec, rec_ref)
+    # int32 overflow is still reported
+    big = torch.full((keys.size, D), 3.0e9, dtype=torch.float32).cuda()
+    with pytest.raises(OverflowError):
+        ops.forward_quant(ops.tree_from_keys(torch.from_numpy(keys).cuda()), big, 0.5, tdt, tile_rows)
