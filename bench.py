@@ -106,18 +106,25 @@ def time_cpu(scene, J, step, sample_n, reps, use_ref_rlgr):
 
 # ---------------------------------------------------------------------------------------------------
 class ClockSampler:
+    """SM clock and clock-event reasons sampled DURING the timed regions.
+
+    NVML in this process (pynvml: two light queries, SM clock and event-reason mask, every 10 ms from a side thread that
+    holds no GIL inside the calls); `nvidia-smi -lms` in a side process only when pynvml is missing.  Both are started
+    BEFORE the warm-up.  History: nvidia-smi started together with the timed region stalled kernel launches for ~10 ms
+    while it initialised NVML; once running, each of its polls (it reads power and a dozen more fields) still put a
+    1-2 ms bubble into whichever stage was executing -- one step in five at 50 ms polling."""
+
     Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
          "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
 
-    """nvidia-smi polling in a side process.  It is started BEFORE the warm-up (its start-up initialises NVML and
-    enumerates the GPUs, which can stall kernel launches for milliseconds: measured as a 10 ms bubble in one stage when it
-    used to start together with the timed region) and keeps polling; only the samples taken between mark_begin() and
-    mark_end() -- the timed regions -- are reported."""
-
     def __init__(self, gpu_index):
         self.idx = gpu_index
-        self.rows = []
+        self.rows = []          # nvidia-smi: (time, csv line); nvml: (time, sm MHz, reason mask)
         self.proc = None
+        self.nvml = None
+        self.handle = None
+        self.max_mhz = None
+        self.stop_flag = False
         self.t0 = self.t1 = None
 
     def mark_begin(self):
@@ -126,7 +133,28 @@ class ClockSampler:
     def mark_end(self):
         self.t1 = time.time()
 
+    def _nvml_handle(self, nv):
+        try:
+            import torch
+            p = torch.cuda.get_device_properties(self.idx)
+            bus = f"{p.pci_domain_id:08x}:{p.pci_bus_id:02x}:{p.pci_device_id:02x}.0"
+            return nv.nvmlDeviceGetHandleByPciBusId(bus.encode())
+        except Exception:
+            return nv.nvmlDeviceGetHandleByIndex(self.idx)
+
     def start(self):
+        try:
+            import pynvml as nv
+            nv.nvmlInit()
+            self.handle = self._nvml_handle(nv)
+            self.max_mhz = float(nv.nvmlDeviceGetMaxClockInfo(self.handle, nv.NVML_CLOCK_SM))
+            nv.nvmlDeviceGetClockInfo(self.handle, nv.NVML_CLOCK_SM)
+            self.nvml = nv
+            self.thread = threading.Thread(target=self._poll_nvml, daemon=True)
+            self.thread.start()
+            return
+        except Exception:
+            self.nvml = None
         try:
             self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "50",
                                           "-i", str(self.idx)], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
@@ -135,11 +163,36 @@ class ClockSampler:
         except Exception:
             self.proc = None
 
+    def _poll_nvml(self):
+        nv = self.nvml
+        while not self.stop_flag:
+            try:
+                t = time.time()
+                mhz = float(nv.nvmlDeviceGetClockInfo(self.handle, nv.NVML_CLOCK_SM))
+                mask = int(nv.nvmlDeviceGetCurrentClocksEventReasons(self.handle))
+                self.rows.append((t, mhz, mask))
+            except Exception:
+                pass
+            time.sleep(0.01)
+
     def _read(self):
         for line in self.proc.stdout:
             self.rows.append((time.time(), line.strip()))
 
     def stop(self):
+        t0, t1 = self.t0 or 0.0, self.t1 or time.time()
+        if self.nvml is not None:
+            self.stop_flag = True
+            self.thread.join(timeout=1.0)
+            nv = self.nvml
+            inside = [r for r in self.rows if t0 <= r[0] <= t1 + 0.02]
+            names = [("hw_slowdown", nv.nvmlClocksEventReasonHwSlowdown), ("hw_thermal_slowdown", nv.nvmlClocksEventReasonHwThermalSlowdown),
+                     ("sw_thermal_slowdown", nv.nvmlClocksEventReasonSwThermalSlowdown), ("sw_power_cap", nv.nvmlClocksEventReasonSwPowerCap),
+                     ("hw_power_brake_slowdown", nv.nvmlClocksEventReasonHwPowerBrakeSlowdown)]
+            reasons = sorted({nm for _, _, m in inside for nm, bit in names if m & bit})
+            sm = [r[1] for r in inside]
+            return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": self.max_mhz, "reasons": reasons, "samples": len(sm),
+                    "source": "nvml"}
         if not self.proc:
             return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
         self.proc.terminate()
@@ -149,7 +202,6 @@ class ClockSampler:
             self.proc.kill()
         sm, mx, reasons = [], None, set()
         names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
-        t0, t1 = self.t0 or 0.0, self.t1 or time.time()
         inside = [r for t, r in self.rows if t0 <= t <= t1 + 0.05]
         for r in inside:
             f = [x.strip() for x in r.split(",")]
@@ -162,7 +214,8 @@ class ClockSampler:
             for nm, v in zip(names, f[4:8]):
                 if v.lower().startswith("active"):
                     reasons.add(nm)
-        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": mx, "reasons": sorted(reasons), "samples": len(sm)}
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": mx, "reasons": sorted(reasons), "samples": len(sm),
+                "source": "nvidia-smi"}
 
 
 def stage_bytes(nvox, n_in, payload, J):
@@ -338,7 +391,7 @@ def run_gpu(args):
                       "what": "raht_b200.container: header + RLGR-coded Morton deltas + the attribute streams + sync indices in one device buffer"}
     clocks.mark_end()
     clk = clocks.stop()
-    clk["window"] = "samples (nvidia-smi -lms 50) between the start of the device-timed region and the end of the e2e regions"
+    clk["window"] = "samples between the start of the device-timed region and the end of the e2e regions"
 
     if rank != 0:
         if world > 1:

@@ -1062,6 +1062,10 @@ __global__ void __launch_bounds__(32) rlgr_decode_serial_kernel(const uint8_t *_
 
 // with the encoder's sync index: one thread per entry (512 symbols)
 constexpr int DEC_THREADS = 128;
+// (Tried and dropped: feeding the window from a per-thread cp.async ring in shared memory instead of a register loaded
+// one refill ahead.  It removes the long-scoreboard stalls -- a register loaded from global memory is a warp-wide
+// scoreboard entry, so every refill waits for the load some OTHER lane issued an iteration earlier -- but the ring
+// bookkeeping costs 34 % more instructions and the kernel got slower, 692 against 606 us.)
 __global__ void __launch_bounds__(DEC_THREADS) rlgr_decode_indexed_kernel(const uint8_t *__restrict__ streams, int64_t slot_bytes,
                                                                          const int64_t *__restrict__ nbytes,
                                                                          const uint2 *__restrict__ sync_index, int64_t entries,
@@ -1081,9 +1085,12 @@ __global__ void __launch_bounds__(DEC_THREADS) rlgr_decode_indexed_kernel(const 
     s.kRP = (int)((ent.y >> 14) & 0xff);
     int64_t nb = nbytes ? nbytes[ch] : slot_bytes;
     if (nb > slot_bytes) nb = slot_bytes;
+    const unsigned long long begin = (unsigned long long)ent.x | ((unsigned long long)(ent.y & 0x7f) << 32);
+    // positions relative to the range: the reader starts before the event whose non-zero is symbol `first` of it
+    int32_t *dst = q + (size_t)ch * G.ld + start;
     BitReader br;
-    br.init(streams + (size_t)ch * slot_bytes, nb, (unsigned long long)ent.x | ((unsigned long long)(ent.y & 0x7f) << 32));
-    decode_range(br, s, start + first, end, G.flag_signed, q + (size_t)ch * G.ld);
+    br.init(streams + (size_t)ch * slot_bytes, nb, begin);
+    decode_range(br, s, (int64_t)first, end - start, G.flag_signed, dst);
 }
 
 struct EncLayout {
@@ -1209,8 +1216,8 @@ RAHT_API int raht_rlgr_decode(const uint8_t *streams, int64_t slot_bytes, const 
     if (sync_index) {
         const int64_t entries = raht_rlgr_sync_entries(n);
         const dim3 grid((unsigned)((entries + DEC_THREADS - 1) / DEC_THREADS), nch);
-        (raht_count_launches(1), rlgr_decode_indexed_kernel)<<<grid, DEC_THREADS, 0, st>>>(streams, slot_bytes, nbytes,
-                                                                                          (const uint2 *)sync_index, entries, G, q);
+        raht_count_launches(1);
+        rlgr_decode_indexed_kernel<<<grid, DEC_THREADS, 0, st>>>(streams, slot_bytes, nbytes, (const uint2 *)sync_index, entries, G, q);
     } else {
         (raht_count_launches(1), rlgr_decode_serial_kernel)<<<nch, 32, 0, st>>>(streams, slot_bytes, nbytes, G, q);
     }

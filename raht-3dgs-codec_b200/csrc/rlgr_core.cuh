@@ -262,23 +262,39 @@ template <class Sink> RL_HD bool emit_event(State &s, uint32_t g, uint32_t u, Si
 
 // ---- decoder ---------------------------------------------------------------------------------------------
 // MSB-first reader over big-endian 32-bit words; acc holds the next nbits bits left-aligned.
-struct BitReader {
-    // 64-bit window over a big-endian bit stream, refilled 32 bits at a time.  The word after the window (`ahead`) is
-    // loaded one refill early, so a refill never waits for memory: it consumes the word fetched by the previous one and
-    // starts the next fetch (on the GPU a warp refills on almost every symbol -- some lane always runs dry -- and used
-    // to stall on that load every time).
+// Word sources: next() returns the following 32 bits of the stream (big-endian order restored).
+// GlobalWords reads the stream in place, one word ahead of its use.
+struct GlobalWords {
     const uint32_t *in;
     uint32_t n_words, pos;             // pos: index of `ahead`
     uint32_t ahead;                    // raw (still byte-swapped) so that nothing touches the loaded value before the next refill
-    uint64_t acc;
-    int nbits;
     RL_HD uint32_t word(uint32_t i) const { return i < n_words ? in[i] : 0u; }
-    RL_HD void init(const uint8_t *stream, int64_t readable_bytes, unsigned long long begin_bit)
+    RL_HD void start(const uint8_t *stream, int64_t readable_bytes, uint32_t first_word)
     {
         in = (const uint32_t *)stream;
         n_words = (uint32_t)((readable_bytes + 3) >> 2);
-        pos = (uint32_t)(begin_bit >> 5);
+        pos = first_word;
         ahead = word(pos);
+    }
+    RL_HD uint32_t next()
+    {
+        const uint32_t w = rl_bswap32(ahead);
+        ++pos;
+        ahead = word(pos);
+        return w;
+    }
+};
+
+template <class Words> struct BitReaderT {
+    // 64-bit window over a big-endian bit stream, refilled 32 bits at a time from a word source that runs ahead of
+    // the window, so that a refill never waits for memory (on the GPU a warp refills on almost every symbol -- some
+    // lane always runs dry).
+    Words src;
+    uint64_t acc;
+    int nbits;
+    RL_HD void init(const uint8_t *stream, int64_t readable_bytes, unsigned long long begin_bit)
+    {
+        src.start(stream, readable_bytes, (uint32_t)(begin_bit >> 5));
         acc = 0;
         nbits = 0;
         const unsigned skip_bits = (unsigned)(begin_bit & 31);
@@ -287,10 +303,8 @@ struct BitReader {
     RL_HD void fill()                  // afterwards nbits >= 33
     {
         if (nbits <= 32) {
-            acc |= (uint64_t)rl_bswap32(ahead) << (32 - nbits);
+            acc |= (uint64_t)src.next() << (32 - nbits);
             nbits += 32;
-            ++pos;
-            ahead = word(pos);
         }
     }
     RL_HD void skip(unsigned len)      // len <= nbits
@@ -330,6 +344,7 @@ struct BitReader {
         return (uint32_t)(((uint64_t)p << kr) + get(kr));        // kr can be 32 (k_RP = 128)
     }
 };
+using BitReader = BitReaderT<GlobalWords>;
 
 // Events from reader br in state s.  dst is pre-zeroed: only non-zero symbols are stored, so zero runs cost
 // nothing and the tail of the stream is never read.  Positions are 32-bit (the coder takes n < 2^31 symbols).
@@ -338,7 +353,8 @@ struct BitReader {
 //   the zeros in front of it are decoded and dropped, then decoding continues up to `end`.
 // One loop body for both modes of the coder: the run prefix (k > 0 only) is the divergent part, the Golomb-Rice
 // symbol, the adaptation and the store are shared (lanes of a warp sit in different modes all the time).
-RL_HD void decode_range(BitReader &br, State s, int64_t first_pos, int64_t end64, int flag_signed,
+template <class Reader>
+RL_HD void decode_range(Reader &br, State s, int64_t first_pos, int64_t end64, int flag_signed,
                                              int32_t *__restrict__ dst)
 {
     bool synced = first_pos < 0;
