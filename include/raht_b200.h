@@ -271,6 +271,13 @@ int raht_rlgr_decode(const uint8_t *streams, int64_t slot_bytes, const int64_t *
                      const void *sync_index, int64_t n, int64_t ld, int nch, int flag_signed,
                      int32_t *q, void *stream);
 
+/* (f3) per-channel range of an (n, D) matrix: minmax[0..D) = column minima, minmax[D..2D) = column maxima (device
+ * doubles).  Feeds the per-attribute quantisation steps of encode_3dgs_debug.py:326-381 (range of the coefficients of
+ * an attribute group / levels allotted to it); the rule itself is host arithmetic (raht_b200/codec.py).             */
+size_t raht_channel_minmax_workspace_bytes(int64_t n, int D);
+int raht_channel_minmax(const void *T, int t_dtype, int64_t n, int D, double *minmax, void *workspace,
+                        size_t workspace_bytes, void *stream);
+
 /* (a13) sum over rows of (A-B)^2 in fp64 for columns [c0,c1) of two (n, D) matrices -> *sse
  * (device double, overwritten), encode_3dgs.py:298-310.                                            */
 int raht_sse_f64(const double *A, const double *B, int64_t n, int D, int c0, int c1, double *sse,

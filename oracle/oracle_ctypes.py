@@ -267,3 +267,24 @@ def ref_rlgr_decode(buf, N, flag_signed=1):
     ns = C.c_longlong()
     _ref_lib().ref_rlgr_decode(b, len(buf), N, flag_signed, seq, C.byref(ns))
     return seq, ns.value
+
+
+# ---- per-attribute quantisation steps (python/encode_3dgs_debug.py:326-381), numpy restatement ---------------------------
+IMPORTANCE_56 = {"quats": 1.0 / 21.93, "scales": 1.0 / 26.36, "opacity": 1.0 / 42.22, "colors": 1.0 / 38.67}   # :336-341
+
+
+def per_attribute_steps(Coeff, attr_ranges, importance_weights, total_levels_budget=1024):
+    """Coeff (N, D) float64 -> ({name: (step, levels, range)}, Coeff_enc) exactly as the reference loop :348-381."""
+    n_channels = Coeff.shape[1]
+    total_importance = sum(importance_weights.values())
+    per, enc = {}, np.zeros_like(Coeff)
+    for name, (a, b) in attr_ranges.items():
+        if a >= n_channels:
+            continue
+        coeff_attr = Coeff[:, a:b]
+        range_attr = coeff_attr.max() - coeff_attr.min()
+        levels = max(int(total_levels_budget * importance_weights[name] / total_importance), 2)
+        step = max(range_attr / max(levels - 1, 1), 1e-6)
+        per[name] = (float(step), levels, float(range_attr))
+        enc[:, a:b] = np.floor(Coeff[:, a:b] / step + 0.5)
+    return per, enc

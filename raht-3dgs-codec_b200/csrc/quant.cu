@@ -137,6 +137,44 @@ __global__ void __launch_bounds__(256) sse_final_kernel(const double *partial, i
     }
 }
 
+// ---- per-channel minimum and maximum (coefficient range for the per-attribute steps, encode_3dgs_debug.py:353-355) ----
+constexpr int MM_BLOCKS_MAX = 592;        // 148 SMs x 4
+constexpr int MM_ROWS = 4;                // rows in flight per CTA pass (blockDim.y)
+
+template <typename Tel>
+__global__ void __launch_bounds__(256) minmax_partial_kernel(const Tel *__restrict__ T, int64_t n, int D, double *__restrict__ partial)
+{
+    extern __shared__ double mm_s[];                             // [MM_ROWS][2][D]
+    const int cx = threadIdx.x, ry = threadIdx.y, cw = blockDim.x;
+    for (int c0 = 0; c0 < D; c0 += cw) {
+        const int c = c0 + cx;
+        double lo = INFINITY, hi = -INFINITY;
+        if (c < D)
+            for (int64_t r = (int64_t)blockIdx.x * MM_ROWS + ry; r < n; r += (int64_t)gridDim.x * MM_ROWS) {
+                const double v = (double)T[(size_t)r * D + c];
+                lo = fmin(lo, v);
+                hi = fmax(hi, v);
+            }
+        if (c < D) { mm_s[(ry * 2 + 0) * D + c] = lo; mm_s[(ry * 2 + 1) * D + c] = hi; }
+    }
+    __syncthreads();
+    for (int c = threadIdx.y * blockDim.x + threadIdx.x; c < D; c += blockDim.x * blockDim.y) {
+        double lo = INFINITY, hi = -INFINITY;
+        for (int y = 0; y < MM_ROWS; ++y) { lo = fmin(lo, mm_s[(y * 2 + 0) * D + c]); hi = fmax(hi, mm_s[(y * 2 + 1) * D + c]); }
+        partial[((size_t)blockIdx.x * 2 + 0) * D + c] = lo;
+        partial[((size_t)blockIdx.x * 2 + 1) * D + c] = hi;
+    }
+}
+__global__ void __launch_bounds__(256) minmax_final_kernel(const double *__restrict__ partial, int nb, int D, double *__restrict__ out)
+{
+    for (int c = blockIdx.x * blockDim.x + threadIdx.x; c < D; c += gridDim.x * blockDim.x) {
+        double lo = INFINITY, hi = -INFINITY;
+        for (int b = 0; b < nb; ++b) { lo = fmin(lo, partial[((size_t)b * 2 + 0) * D + c]); hi = fmax(hi, partial[((size_t)b * 2 + 1) * D + c]); }
+        out[c] = lo;
+        out[D + c] = hi;
+    }
+}
+
 size_t qr_smem_bytes(int D) { return ((size_t)D * QR_PITCH + 1) * 4 + (size_t)D * 8 + 16; }
 
 }  // namespace
@@ -247,4 +285,36 @@ RAHT_API int raht_sse_f64(const double *A, const double *B, int64_t n, int D, in
                           size_t workspace_bytes, void *stream)
 {
     return raht_sse(A, RAHT_F64, B, RAHT_F64, n, D, c0, c1, sse, workspace, workspace_bytes, stream);
+}
+
+RAHT_API size_t raht_channel_minmax_workspace_bytes(int64_t n, int D)
+{
+    (void)n;
+    return (size_t)MM_BLOCKS_MAX * 2 * (size_t)(D > 0 ? D : 1) * 8 + 256;
+}
+
+RAHT_API int raht_channel_minmax(const void *T, int t_dtype, int64_t n, int D, double *minmax, void *workspace, size_t workspace_bytes,
+                                 void *stream)
+{
+    RAHT_REQUIRE(n >= 1 && D >= 1 && T && minmax && workspace, "raht_channel_minmax: bad arguments (n must be >= 1)");
+    if (workspace_bytes < raht_channel_minmax_workspace_bytes(n, D)) {
+        raht_set_error("raht_channel_minmax: workspace too small");
+        return RAHT_E_WORKSPACE;
+    }
+    const size_t smem = (size_t)MM_ROWS * 2 * D * 8;
+    RAHT_REQUIRE(smem <= 48 * 1024, "raht_channel_minmax: D too large");
+    cudaStream_t st = (cudaStream_t)stream;
+    int nb = (int)((n + MM_ROWS - 1) / MM_ROWS);
+    if (nb > MM_BLOCKS_MAX) nb = MM_BLOCKS_MAX;
+    const dim3 block(64, MM_ROWS);
+    raht_count_launches(2);
+    if (t_dtype == RAHT_F64) minmax_partial_kernel<double><<<nb, block, smem, st>>>((const double *)T, n, D, (double *)workspace);
+    else if (t_dtype == RAHT_F32) minmax_partial_kernel<float><<<nb, block, smem, st>>>((const float *)T, n, D, (double *)workspace);
+    else {
+        raht_set_error("raht_channel_minmax: bad dtype");
+        return RAHT_E_INVALID;
+    }
+    minmax_final_kernel<<<(D + 255) / 256, 256, 0, st>>>((const double *)workspace, nb, D, minmax);
+    RAHT_LAUNCH_CHECK();
+    return RAHT_OK;
 }

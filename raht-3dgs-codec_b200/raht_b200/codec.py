@@ -124,6 +124,50 @@ def voxelize_merge(means, quats, scales, opacities, colors, J, packed_dtype=torc
     return packed, unique_keys, info
 
 
+# Visual-importance weights of the attribute groups (encode_3dgs_debug.py:336-341: 1 / rendering PSNR of the ablation of
+# each group) and the levels budget (:346).  The reference codes 56 channels (no positions); with the merged means in
+# front (D = 59) they get the weight of the quaternions (a choice of this build: the reference does not code them).
+IMPORTANCE = {"means": 1.0 / 21.93, "quats": 1.0 / 21.93, "scales": 1.0 / 26.36, "opacity": 1.0 / 42.22, "colors": 1.0 / 38.67}
+LEVELS_BUDGET = 1024
+
+
+def attribute_ranges(D):
+    """Channel ranges of the attribute groups (encode_3dgs_debug.py:327-332) for the 56-channel reference layout, or the
+    59-channel layout of this build (merged means in front)."""
+    o = 3 if D >= 59 else 0
+    r = {"means": (0, 3)} if o else {}
+    r.update({"quats": (o, o + 4), "scales": (o + 4, o + 7), "opacity": (o + 7, o + 8), "colors": (o + 8, D)})
+    return r
+
+
+@torch.no_grad()
+def per_attribute_steps(T, ranges=None, weights=None, budget=LEVELS_BUDGET):
+    """Quantisation step per channel from the coefficient range of its attribute group and the group's share of a levels
+    budget (encode_3dgs_debug.py:343-366): levels = max(int(budget * w / sum(w)), 2), step = max(range / max(levels - 1, 1),
+    1e-6), range = max - min over the group's channels.  Returns (list of D steps, {group: {step, levels, range, channels}}).
+    The range is reduced on the device (raht_channel_minmax); the rule is host arithmetic, as in the reference."""
+    n, D = T.shape
+    ranges = attribute_ranges(D) if ranges is None else ranges
+    weights = {g: IMPORTANCE[g] for g in ranges} if weights is None else weights
+    lo, hi = ops.channel_minmax(T)
+    lo, hi = L.read_host(lo, hi)
+    total = sum(weights[g] for g in weights)              # (the reference sums every weight it lists, :344)
+    steps, info = [0.0] * D, {}
+    for g, (a, b) in ranges.items():
+        if a >= D:
+            continue
+        b = min(b, D)
+        rng = float(hi[a:b].max() - lo[a:b].min())
+        levels = max(int(budget * weights[g] / total), 2)
+        step = max(rng / max(levels - 1, 1), 1e-6)
+        info[g] = {"step": step, "levels": levels, "range": rng, "channels": (a, b)}
+        for c in range(a, b):
+            steps[c] = step
+    if any(s == 0.0 for s in steps):
+        raise ValueError("per_attribute_steps: the attribute ranges do not cover every channel")
+    return steps, info
+
+
 @torch.no_grad()
 def encode_attributes(keys, Cmat, step, transform_dtype=torch.float64, tile_rows=None, timer=None, flags=0, status=None, fused=False):
     """RAHT_param -> RAHT -> quantise -> reorder -> RLGR for rows that are Morton-sorted unique voxels.
@@ -136,6 +180,10 @@ def encode_attributes(keys, Cmat, step, transform_dtype=torch.float64, tile_rows
     word that is read once, after the entropy coder."""
     timer = timer or StageTimer(False)
     status = ops._status_word(keys.device) if status is None else status
+    if isinstance(step, str):
+        if step != "per_attribute":
+            raise ValueError(f"unknown step rule {step!r}")
+        fused = False                                              # the rule needs the coefficients before they are quantised
     tree = ops.tree_from_keys(keys, validate=True, status=status)
     order, _ = tree.order(want_position=True)
     tree.plan(tile_rows)
@@ -146,6 +194,9 @@ def encode_attributes(keys, Cmat, step, transform_dtype=torch.float64, tile_rows
     else:
         T = ops.forward(tree, Cmat, transform_dtype, tile_rows, flags)
         timer.mark("raht")
+        if isinstance(step, str):                                  # "per_attribute": steps from the coefficient ranges
+            step, _ = per_attribute_steps(T)
+            tree.steps = step
         q = ops.quant_reorder(T, order, step, status=status)
         timer.mark("quant_reorder")
     streams = ops.rlgr_encode(q, 1, status=status)
@@ -188,6 +239,7 @@ def encode_scene(means, quats, scales, opacities, colors, J, step, transform_dty
     packed, keys, info = voxelize_merge(means, quats, scales, opacities, colors, J, torch.float32, timer, status)
     tree, streams = encode_attributes(keys, packed, step, transform_dtype, tile_rows, timer, flags, status, fused)
     width, voxel_size = L.read_host(info["params_d2"])[0].tolist()          # after the coder's synchronisation: no extra wait
+    step = getattr(tree, "steps", step)                            # "per_attribute": the steps the rule picked
     return EncodedScene(J=J, n_in=info["N"], nvox=info["Nvox"], D=packed.shape[1], step=step, vmin=info["vmin"],
                         voxel_size=voxel_size, width=width, keys=keys, streams=streams,
                         transform_dtype=transform_dtype, tree=tree, packed=packed if keep_packed else None)

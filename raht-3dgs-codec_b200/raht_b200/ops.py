@@ -514,6 +514,20 @@ def rlgr_decode(streams: RlgrStreams, flag_signed=1, use_index=True) -> torch.Te
     return q[:, :n]
 
 
+def channel_minmax(T: torch.Tensor):
+    """(min (D,), max (D,)) fp64 device tensors of the columns of an (n, D) fp32 / fp64 matrix (raht_channel_minmax)."""
+    L.require_cuda(T, "T")
+    T = T.contiguous()
+    n, D = T.shape
+    if n < 1:
+        raise ValueError("channel_minmax of an empty matrix")
+    out = torch.empty(2, D, dtype=torch.float64, device=T.device)
+    ws_bytes = lib.raht_channel_minmax_workspace_bytes(n, D)
+    ws = workspace(ws_bytes, T.device)
+    check(lib.raht_channel_minmax(ptr(T), L.dtype_tag(T.dtype), n, D, ptr(out), ptr(ws), ws_bytes, stream()), "raht_channel_minmax")
+    return out[0], out[1]
+
+
 def sse(A: torch.Tensor, B: torch.Tensor, c0=0, c1=None) -> torch.Tensor:
     """Sum of squared differences of two (n, D) matrices (fp32 or fp64 each), accumulated in fp64 -> device double."""
     n, D = A.shape

@@ -470,3 +470,51 @@ def test_fused_quantisation_matches_the_two_reference_steps(n, J, D, tile_rows, 
     big = torch.full((keys.size, D), 3.0e9, dtype=torch.float32).cuda()
     with pytest.raises(OverflowError):
         ops.forward_quant(ops.tree_from_keys(torch.from_numpy(keys).cuda()), big, 0.5, tdt, tile_rows)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("D", [56, 59])
+def test_per_attribute_steps_match_the_reference_rule(D):
+    """encode_3dgs_debug.py:326-381: range of the coefficients per attribute group -> levels -> step -> quantise."""
+    import torch
+    from raht_b200 import codec, ops
+    rng = np.random.default_rng(D)
+    J, n = 8, 15000
+    keys = np.sort(rng.choice(1 << (3 * J), size=n, replace=False)).astype(np.int64)
+    C = rng.normal(0, 1, size=(n, D)) * np.linspace(0.2, 5.0, D)
+    tree_o = orc.Tree(keys, J)
+    T_o, _ = tree_o.forward(C)
+    tree = ops.tree_from_keys(torch.from_numpy(keys).cuda())
+    T = ops.forward(tree, torch.from_numpy(C).cuda(), torch.float64)
+    assert np.array_equal(T.cpu().numpy(), T_o)
+    lo, hi = ops.channel_minmax(T)
+    assert np.array_equal(lo.cpu().numpy(), T_o.min(0)) and np.array_equal(hi.cpu().numpy(), T_o.max(0))
+    lo32, hi32 = ops.channel_minmax(T.float())
+    assert np.array_equal(lo32.cpu().numpy(), T_o.astype(np.float32).min(0).astype(np.float64))
+    ranges = codec.attribute_ranges(D)
+    steps, info = codec.per_attribute_steps(T)
+    want, enc_o = orc.per_attribute_steps(T_o, ranges, {g: codec.IMPORTANCE[g] for g in ranges})
+    steps_o, info_o = codec.per_attribute_steps(T, ranges, {g: codec.IMPORTANCE[g] for g in ranges})
+    for g, (a, b) in ranges.items():
+        assert (info_o[g]["step"], info_o[g]["levels"], info_o[g]["range"]) == want[g]
+    q = ops.quant_reorder(T, None, steps_o)
+    assert np.array_equal(q.cpu().numpy().T.astype(np.float64), enc_o)
+    assert steps == steps_o
+    if D == 56:
+        assert [info[g]["levels"] for g in ("quats", "scales", "opacity", "colors")] == [350, 291, 182, 198]
+
+
+@pytest.mark.gpu
+def test_scene_with_per_attribute_steps_roundtrips_through_the_container():
+    import torch
+    from raht_b200 import codec, container
+    scene = [torch.from_numpy(a).cuda() for a in helpers.synthetic_gaussians(20000, 8)]
+    enc = codec.encode_scene(*scene, J=8, step="per_attribute")
+    assert isinstance(enc.step, list) and len(enc.step) == 59 and len(set(enc.step)) == 5
+    _, ref = codec.decode_scene(enc)
+    dec = container.unpack(container.pack(enc))
+    assert dec.step == enc.step
+    _, rec = codec.decode_scene(dec)
+    assert torch.equal(rec, ref)
+    packed, _, _ = codec.voxelize_merge(*scene, J=8)
+    assert codec.psnr(packed, rec) > 20.0
