@@ -29,7 +29,7 @@
 extern "C" {
 #endif
 
-#define RAHT_B200_ABI_VERSION 8
+#define RAHT_B200_ABI_VERSION 9
 
 enum {
     RAHT_OK = 0,
