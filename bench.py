@@ -310,6 +310,7 @@ def run_gpu(args):
     timers = []
     launches0 = ops.lib.raht_launch_count()
     barrier()
+    mem0 = torch.cuda.memory_stats(dev)
     clocks.mark_begin()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e0.record()
@@ -321,6 +322,8 @@ def run_gpu(args):
     barrier()
     ms_total = e0.elapsed_time(e1)
     launches = (ops.lib.raht_launch_count() - launches0) // max(args.steps, 1)
+    mem1 = torch.cuda.memory_stats(dev)
+    cuda_mallocs = int(mem1.get("segment.all.allocated", 0) - mem0.get("segment.all.allocated", 0))
     t = torch.tensor([ms_total], dtype=torch.float64, device=dev)
     if world > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
@@ -442,6 +445,7 @@ def run_gpu(args):
                 "with_attributes": {"value": round(e2e_attr_value, 1), "unit": "Gaussians/s", "d2h_bytes_per_step": int(d2h_attr),
                                     "how": "the same plus the decoded attributes (nvox x 59 fp64) copied to pinned host memory"}},
         "gpu_launches": int(launches),
+        "cuda_mallocs_in_timed_region": cuda_mallocs,
         "roofline": roofline,
         "stages": per_stage,
         "cpu_baseline": cpu,

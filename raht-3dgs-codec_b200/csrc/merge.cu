@@ -15,23 +15,33 @@ namespace {
 constexpr int MG_UNROLL = 4;      // voxels per warp iteration: their dependent loads are issued level by level
 constexpr int MG_WARPS = 8;
 
-// address of channel c of Gaussian g in the reference's five arrays (select chain, no branches)
-__device__ __forceinline__ const float *channel_ptr(int c, int64_t g, const float *means, const float *quats,
-                                                    const float *scales, const float *opac, const float *colors, int color_dim)
+// What a lane needs to know about its output channel c = 32 k + lane, fixed for the whole kernel: where the channel
+// lives in the reference's five arrays (base pointer + row stride) and how its sum is finished.
+enum { CH_MEAN = 0, CH_QUAT = 1, CH_OPAC = 2, CH_COLOR = 3, CH_NONE = 4 };   // CH_MEAN also covers the scales (same rule)
+struct LaneChannel {
+    const float *base;
+    int stride;
+    int kind;
+};
+__device__ __forceinline__ LaneChannel lane_channel(int c, int OC, const float *means, const float *quats, const float *scales,
+                                                    const float *opac, const float *colors, int color_dim)
 {
-    const float *p = colors + g * color_dim + (c - 11);
-    p = c == 10 ? opac + g : p;
-    p = c < 10 ? scales + g * 3 + (c - 7) : p;
-    p = c < 7 ? quats + g * 4 + (c - 3) : p;
-    p = c < 3 ? means + g * 3 + c : p;
-    return p;
+    LaneChannel L;
+    L.base = colors + (c - 11); L.stride = color_dim; L.kind = CH_COLOR;
+    if (c == 10) { L.base = opac; L.stride = 1; L.kind = CH_OPAC; }
+    if (c < 10) { L.base = scales + (c - 7); L.stride = 3; L.kind = CH_MEAN; }
+    if (c < 7) { L.base = quats + (c - 3); L.stride = 4; L.kind = CH_QUAT; }
+    if (c < 3) { L.base = means + c; L.stride = 3; L.kind = CH_MEAN; }
+    if (c >= OC) { L.base = means; L.stride = 0; L.kind = CH_NONE; }
+    return L;
 }
 
 // One warp per voxel, lane = output channel (slot k holds channel 32 k + lane), NS slots.  The offsets, the member
 // index and the member's opacity are warp-uniform; the colour row and the packed output row are contiguous across
 // the lanes.  Every channel sums its members in segment order with separately rounded multiply and add, starting
 // from 0 as the reference does (merge_cluster.cu:36-72,97-106), so the result is a deterministic function of the inputs.
-template <typename OutT, int NS>
+// SEP: also write the five separate output arrays of the reference interface (the codec only takes the packed rows).
+template <typename OutT, int NS, bool SEP>
 __global__ void __launch_bounds__(32 * MG_WARPS)
 merge_kernel(const int32_t *__restrict__ cidx, const int32_t *__restrict__ coff, int64_t nclu,
              const float *__restrict__ means, const float *__restrict__ quats, const float *__restrict__ scales,
@@ -41,6 +51,9 @@ merge_kernel(const int32_t *__restrict__ cidx, const int32_t *__restrict__ coff,
 {
     const int OC = 11 + color_dim;
     const int lane = threadIdx.x & 31;
+    LaneChannel ch[NS];
+#pragma unroll
+    for (int k = 0; k < NS; ++k) ch[k] = lane_channel(32 * k + lane, OC, means, quats, scales, opac, colors, color_dim);
     const int64_t nwarps = (int64_t)gridDim.x * MG_WARPS;
     for (int64_t v0 = (int64_t)blockIdx.x * MG_WARPS + (threadIdx.x >> 5); v0 < nclu; v0 += MG_UNROLL * nwarps) {
         int s[MG_UNROLL], t[MG_UNROLL], g[MG_UNROLL];
@@ -57,10 +70,8 @@ merge_kernel(const int32_t *__restrict__ cidx, const int32_t *__restrict__ coff,
 #pragma unroll
         for (int u = 0; u < MG_UNROLL; ++u)
 #pragma unroll
-            for (int k = 0; k < NS; ++k) {
-                const int c = 32 * k + lane;
-                x[u][k] = (g[u] >= 0 && c < OC) ? *channel_ptr(c, g[u], means, quats, scales, opac, colors, color_dim) : 0.f;
-            }
+            for (int k = 0; k < NS; ++k)
+                x[u][k] = (g[u] >= 0 && ch[k].kind != CH_NONE) ? ch[k].base[(int64_t)g[u] * ch[k].stride] : 0.f;
 #pragma unroll
         for (int u = 0; u < MG_UNROLL; ++u) {
             const int64_t v = v0 + u * nwarps;
@@ -75,17 +86,14 @@ merge_kernel(const int32_t *__restrict__ cidx, const int32_t *__restrict__ coff,
                 if (i > s[u]) {
                     const int64_t gi = cidx[i];
 #pragma unroll
-                    for (int k = 0; k < NS; ++k) {
-                        const int c = 32 * k + lane;
-                        xm[k] = c < OC ? *channel_ptr(c, gi, means, quats, scales, opac, colors, color_dim) : 0.f;
-                    }
+                    for (int k = 0; k < NS; ++k) xm[k] = ch[k].kind != CH_NONE ? ch[k].base[gi * ch[k].stride] : 0.f;
                 }
                 const float o = __shfl_sync(~0u, xm[0], 10);                 // the member's opacity
                 const float w = by_opacity ? o : 1.0f;                       // :42
                 wsum = __fadd_rn(wsum, w);
 #pragma unroll
                 for (int k = 0; k < NS; ++k) {
-                    const float wk = (k == 0 && lane == 10) ? 1.0f : w;      // the opacity channel sums the raw opacities (:60)
+                    const float wk = ch[k].kind == CH_OPAC ? 1.0f : w;       // the opacity channel sums the raw opacities (:60)
                     acc[k] = __fadd_rn(acc[k], __fmul_rn(xm[k], wk));
                 }
             }
@@ -97,23 +105,40 @@ merge_kernel(const int32_t *__restrict__ cidx, const int32_t *__restrict__ coff,
             const bool empty = t[u] <= s[u];                                 // :27-29
 #pragma unroll
             for (int k = 0; k < NS; ++k) {
+                const int kind = ch[k].kind;
+                if (kind == CH_NONE) continue;
                 const int c = 32 * k + lane;
-                if (c >= OC) continue;
-                float out;
-                if (c >= 3 && c < 7) out = qn > 0.0f ? __fdiv_rn(acc[k], qn) : (c == 6 ? 1.0f : 0.0f);   // :77-87
-                else if (c == 10) out = fminf(acc[k], 1.0f);                                            // :94
-                else if (c < 10) out = __fdiv_rn(acc[k], wsum == 0.0f ? 1.0f : wsum);                   // :65-72
-                else out = wsum > 0.0f ? __fdiv_rn(acc[k], wsum) : 0.0f;                                 // :108-109
+                // one division per channel: by the quaternion norm (:77-87), or by the weight sum -- means and scales take
+                // 1 for an all-zero weight (:65-72), colours give 0 then (:108-109)
+                const float den = kind == CH_QUAT ? qn : ((kind == CH_MEAN && wsum == 0.0f) ? 1.0f : wsum);
+                float out = __fdiv_rn(acc[k], den);
+                if (kind == CH_QUAT && !(qn > 0.0f)) out = c == 6 ? 1.0f : 0.0f;
+                if (kind == CH_COLOR && !(wsum > 0.0f)) out = 0.0f;
+                if (kind == CH_OPAC) out = fminf(acc[k], 1.0f);                                          // :94
                 if (empty) out = 0.0f;
-                if (c < 3) { if (m_means) m_means[v * 3 + c] = out; }
-                else if (c < 7) { if (m_quats) m_quats[v * 4 + (c - 3)] = out; }
-                else if (c < 10) { if (m_scales) m_scales[v * 3 + (c - 7)] = out; }
-                else if (c == 10) { if (m_opac) m_opac[v] = out; }
-                else { if (m_colors) m_colors[v * (int64_t)color_dim + (c - 11)] = out; }
+                if constexpr (SEP) {
+                    if (c < 3) { if (m_means) m_means[v * 3 + c] = out; }
+                    else if (c < 7) { if (m_quats) m_quats[v * 4 + (c - 3)] = out; }
+                    else if (c < 10) { if (m_scales) m_scales[v * 3 + (c - 7)] = out; }
+                    else if (c == 10) { if (m_opac) m_opac[v] = out; }
+                    else { if (m_colors) m_colors[v * (int64_t)color_dim + (c - 11)] = out; }
+                }
                 if (packed) packed[v * OC + c] = (OutT)out;
             }
         }
     }
+}
+
+template <typename OutT, bool SEP>
+void launch_merge_s(int slots, int grid, cudaStream_t st, const int32_t *ci, const int32_t *co, int64_t n, const float *me,
+                    const float *qu, const float *sc, const float *op, const float *cl, int cd, int byo, float *m1, float *m2,
+                    float *m3, float *m4, float *m5, OutT *pk)
+{
+    const int T = 32 * MG_WARPS;
+    if (slots <= 1) merge_kernel<OutT, 1, SEP><<<grid, T, 0, st>>>(ci, co, n, me, qu, sc, op, cl, cd, byo, m1, m2, m3, m4, m5, pk);
+    else if (slots <= 2) merge_kernel<OutT, 2, SEP><<<grid, T, 0, st>>>(ci, co, n, me, qu, sc, op, cl, cd, byo, m1, m2, m3, m4, m5, pk);
+    else if (slots <= 4) merge_kernel<OutT, 4, SEP><<<grid, T, 0, st>>>(ci, co, n, me, qu, sc, op, cl, cd, byo, m1, m2, m3, m4, m5, pk);
+    else merge_kernel<OutT, 8, SEP><<<grid, T, 0, st>>>(ci, co, n, me, qu, sc, op, cl, cd, byo, m1, m2, m3, m4, m5, pk);
 }
 
 template <typename OutT>
@@ -121,11 +146,8 @@ void launch_merge(int slots, int grid, cudaStream_t st, const int32_t *ci, const
                   const float *qu, const float *sc, const float *op, const float *cl, int cd, int byo, float *m1, float *m2,
                   float *m3, float *m4, float *m5, OutT *pk)
 {
-    const int T = 32 * MG_WARPS;
-    if (slots <= 1) merge_kernel<OutT, 1><<<grid, T, 0, st>>>(ci, co, n, me, qu, sc, op, cl, cd, byo, m1, m2, m3, m4, m5, pk);
-    else if (slots <= 2) merge_kernel<OutT, 2><<<grid, T, 0, st>>>(ci, co, n, me, qu, sc, op, cl, cd, byo, m1, m2, m3, m4, m5, pk);
-    else if (slots <= 4) merge_kernel<OutT, 4><<<grid, T, 0, st>>>(ci, co, n, me, qu, sc, op, cl, cd, byo, m1, m2, m3, m4, m5, pk);
-    else merge_kernel<OutT, 8><<<grid, T, 0, st>>>(ci, co, n, me, qu, sc, op, cl, cd, byo, m1, m2, m3, m4, m5, pk);
+    if (m1 || m2 || m3 || m4 || m5) launch_merge_s<OutT, true>(slots, grid, st, ci, co, n, me, qu, sc, op, cl, cd, byo, m1, m2, m3, m4, m5, pk);
+    else launch_merge_s<OutT, false>(slots, grid, st, ci, co, n, me, qu, sc, op, cl, cd, byo, m1, m2, m3, m4, m5, pk);
 }
 
 }  // namespace

@@ -116,6 +116,30 @@ def workspace(nbytes: int, device) -> torch.Tensor:
     return torch.empty(max(int(nbytes), 256), dtype=torch.uint8, device=device)
 
 
+_WS_CACHE = {}
+
+
+def workspace_cached(tag: str, nbytes: int, device) -> torch.Tensor:
+    """Scratch memory that lives across calls, one buffer per (purpose, device, stream): the big workspaces (the RLGR
+    encoder's is 1.3 GB for a 1 M x 59 scene) are not handed back to the caching allocator between calls, where another
+    request may split them and the next encode pays a cudaMalloc in the middle of its stage.  Stream-ordered use only:
+    the buffer belongs to the stream that is current when it is requested."""
+    dev = torch.device(device)
+    key = (tag, dev.index if dev.index is not None else torch.cuda.current_device(), torch.cuda.current_stream(dev).cuda_stream)
+    buf = _WS_CACHE.get(key)
+    need = max(int(nbytes), 256)
+    if buf is None or buf.numel() < need:
+        _WS_CACHE.pop(key, None)
+        buf = torch.empty(need, dtype=torch.uint8, device=dev)
+        _WS_CACHE[key] = buf
+    return buf
+
+
+def release_workspaces():
+    """Drop the cached workspaces (they are otherwise kept for the life of the process)."""
+    _WS_CACHE.clear()
+
+
 def dtype_tag(dt: torch.dtype) -> int:
     if dt == torch.float64:
         return RAHT_F64

@@ -291,17 +291,31 @@ class ScenePipeline:
         self.dev = torch.device("cuda", torch.cuda.current_device()) if device is None else torch.device(device)
         self.s_in = torch.cuda.Stream(self.dev)
         self.s_out = torch.cuda.Stream(self.dev)
-        self.queue = []                  # (device tensors, H2D-done event)
+        self.queue = []                  # (device tensors, H2D-done event, input set)
+        self.inputs = [None, None]       # two sets of device input tensors, reused (no allocation per scene)
+        self.input_free = [None, None]   # event: the encode that read the set has finished
+        self.n_submitted = 0
         self.pending = []                # outputs whose D2H may still be running (keeps the device tensors alive)
         self.pinned = {}                 # reusable pinned output buffers, two sets (ping-pong)
         self.flip = 0
 
     def submit(self, host_scene):
+        """Start the H2D copy of a pinned host scene into one of the pipeline's two device input sets (the set is free
+        once the encode that read it two submissions ago has finished: awaited on the copy-in stream, not on the host)."""
+        slot = self.n_submitted & 1
+        self.n_submitted += 1
+        bufs = self.inputs[slot]
+        if bufs is None or any(b.shape != h.shape or b.dtype != h.dtype for b, h in zip(bufs, host_scene)):
+            bufs = [torch.empty(h.shape, dtype=h.dtype, device=self.dev) for h in host_scene]
+            self.inputs[slot] = bufs
         with torch.cuda.stream(self.s_in):
-            dv = [h.to(self.dev, non_blocking=True) for h in host_scene]
+            if self.input_free[slot] is not None:
+                self.s_in.wait_event(self.input_free[slot])
+            for b, h in zip(bufs, host_scene):
+                b.copy_(h, non_blocking=True)
             ev = torch.cuda.Event()
             ev.record(self.s_in)
-        self.queue.append((dv, ev))
+        self.queue.append((bufs, ev, slot))
         return sum(h.numel() * h.element_size() for h in host_scene)
 
     def _pin(self, name, numel, dtype):
@@ -314,13 +328,16 @@ class ScenePipeline:
 
     @torch.no_grad()
     def run(self):
-        dv, ev = self.queue.pop(0)
+        if len(self.queue) > 2:
+            raise RuntimeError("ScenePipeline: at most two scenes may be in flight (submit, then run)")
+        dv, ev, slot = self.queue.pop(0)
         main = torch.cuda.current_stream(self.dev)
         main.wait_event(ev)
-        for t in dv:
-            t.record_stream(main)
         enc = encode_scene(*dv, J=self.J, step=self.step, transform_dtype=self.dtype, tile_rows=self.tile_rows,
                            keep_packed=self.result == "psnr")
+        free = torch.cuda.Event()                        # the inputs have been read (merge is long done; the encoder has synchronised)
+        free.record(main)
+        self.input_free[slot] = free
         sizes = enc.streams.sizes()                      # (the encoder has synchronised: no extra wait)
         compact, _ = enc.streams.packed()                # end to end, each padded to 8 bytes
         coords, Crec = decode_scene(enc, reuse_tree=False, tile_rows=self.tile_rows)

@@ -67,7 +67,7 @@ def radix_sort_pairs(keys: torch.Tensor, end_bit: int, vals: torch.Tensor = None
     if n == 0:
         return keys_out, vals_out, status
     ws_bytes = lib.raht_radix_sort_workspace_bytes(n, begin_bit, end_bit)
-    ws = workspace(ws_bytes, dev)
+    ws = L.workspace_cached("radix_sort", ws_bytes, dev)
     check(lib.raht_radix_sort_pairs(ptr(keys), ptr(keys_out), ptr(vals), ptr(vals_out), n, begin_bit, end_bit,
                                     ptr(status), ptr(ws), ws_bytes, stream()), "raht_radix_sort_pairs")
     return keys_out, vals_out, status
@@ -476,7 +476,7 @@ def rlgr_encode(q: torch.Tensor, flag_signed=1, slot_bytes=None, with_index=True
     slot = slot_bytes or ((n * 4 + 64 + 7) // 8 * 8)
     entries = int(lib.raht_rlgr_sync_entries(n))
     ws_bytes = lib.raht_rlgr_encode_workspace_bytes(n, nch)
-    ws = workspace(ws_bytes, dev)
+    ws = L.workspace_cached("rlgr_encode", ws_bytes, dev)
     while True:
         buf = torch.empty(nch * slot, dtype=torch.uint8, device=dev)
         nbytes = torch.zeros(nch, dtype=torch.int64, device=dev)
