@@ -241,11 +241,12 @@ def stage_bytes(nvox, n_in, payload, J):
 # per-launch dram__bytes_read.sum + dram__bytes_write.sum of the latest `ncu --set full` capture kept under profiles/
 STAGE_KERNELS = {
     "rlgr_encode": [("rlgr_count_kernel", 1), ("rlgr_scan_kernel", 1), ("rlgr_scatter_kernel", 1), ("rlgr_speculate_kernel", 2),
-                    ("rlgr_resolve_kernel", 1), ("rlgr_zero_kernel", 1), ("rlgr_emit_kernel", 1)],
+                    ("rlgr_table_kernel", 1), ("rlgr_chunk_table_kernel", 1), ("rlgr_resolve_kernel", 1), ("rlgr_table_lanes_kernel", 1),
+                    ("rlgr_zero_kernel", 1), ("rlgr_emit_kernel", 1)],
     "rlgr_decode": [("rlgr_decode_indexed_kernel", 1)],
-    "merge": [("merge_kernel<float, 2>", 1)],
-    "raht": [("transform_stage0_kernel<float, double, 59, 1>", 1), ("transform_upper_kernel<double, 1>", 5)],
-    "iraht": [("transform_stage0_kernel<double, double, 59, 0>", 1), ("transform_upper_kernel<double, 0>", 5)],
+    "merge": [("merge_kernel<float, 2, 0>", 1)],
+    "raht": [("transform_stage0_kernel<float, double, 59, 1, 0>", 1), ("transform_upper_kernel<double, 1>", 5)],
+    "iraht": [("transform_stage0_kernel<double, double, 59, 0, 0>", 1), ("transform_upper_kernel<double, 0>", 5)],
     "quant_reorder": [("quant_reorder_kernel<double>", 1)],
     "dequant_unreorder": [("dequant_unreorder_kernel<double>", 1)],
 }
@@ -254,7 +255,9 @@ STAGE_KERNELS = {
 def stage_traffic(stage):
     """(bytes per step or None, source file) from the newest profiles/*ncu_full*.json (scripts/ncu_full_summary.py)."""
     import glob
-    files = sorted(glob.glob(os.path.join(ROOT, "profiles", "*ncu_full*.json")))
+    import re
+    files = sorted(glob.glob(os.path.join(ROOT, "profiles", "*ncu_full*.json")),
+                   key=lambda f: [int(x) for x in re.findall(r"\d+", os.path.basename(f))])      # r01 ... v8 < v11
     if not files or stage not in STAGE_KERNELS:
         return None, None
     prof = json.load(open(files[-1]))
