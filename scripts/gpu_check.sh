@@ -18,7 +18,7 @@ run golden_raht "golden_raht_pipeline"
 run oracle_raht "oracle_raht_pipeline"
 run rlgr "rlgr"
 run misc "plain_lists or raht_param_errors or fp32_mode"
-run scene "scene_roundtrip or scene_pipeline"
+run scene "scene_roundtrip or scene_pipeline or fused or per_attribute or scene_with"
 run sharded "sharded"
 run container "container or geometry_symbols or sync_index_matches"
 echo "=== smoke" | tee -a gpurun_out/summary.txt

@@ -398,6 +398,19 @@ def test_scene_roundtrip_properties_1m():
     # decode without the encoder-side tree gives the same result
     _, Crec2 = codec.decode_scene(enc, reuse_tree=False)
     assert torch.equal(Crec, Crec2)
+    # the chunk-parallel decoder (sync index) and the sequential one (the reference's way) agree on every symbol
+    q = ops.rlgr_decode(enc.streams, 1)
+    assert torch.equal(q, ops.rlgr_decode(enc.streams, 1, use_index=False))
+    # fused transform + quantisation: the same bitstreams and the same reconstruction
+    enc_f = codec.encode_scene(*args, J=J, step=1.0 / 256, fused=True)
+    assert torch.equal(enc_f.streams.nbytes, enc.streams.nbytes) and enc_f.streams.to_bytes() == enc.streams.to_bytes()
+    assert torch.equal(codec.decode_scene(enc_f, fused=True)[1], Crec)
+    # through the container
+    from raht_b200 import container
+    box = container.pack(enc)
+    dec = container.unpack(box)
+    assert torch.equal(dec.keys, enc.keys) and torch.equal(codec.decode_scene(dec)[1], Crec)
+    assert box.numel() < enc.payload_bytes() + enc.index_bytes() + enc.nvox * 3 + 4096     # geometry under 3 bytes per voxel
 
 
 def test_scene_pipeline_matches_direct_calls():
