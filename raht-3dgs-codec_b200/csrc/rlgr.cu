@@ -1065,7 +1065,9 @@ constexpr int DEC_THREADS = 128;
 // (Tried and dropped: feeding the window from a per-thread cp.async ring in shared memory instead of a register loaded
 // one refill ahead.  It removes the long-scoreboard stalls -- a register loaded from global memory is a warp-wide
 // scoreboard entry, so every refill waits for the load some OTHER lane issued an iteration earlier -- but the ring
-// bookkeeping costs 34 % more instructions and the kernel got slower, 692 against 606 us.)
+// bookkeeping costs 34 % more instructions and the kernel got slower, 692 against 606 us.  Loading on a fixed beat --
+// every second event all lanes merge the words they requested two events earlier into a 64-bit reserve and request
+// the next two -- did not help either, 657 us: the compiler makes the loop's branch wait for the loads in flight.)
 __global__ void __launch_bounds__(DEC_THREADS) rlgr_decode_indexed_kernel(const uint8_t *__restrict__ streams, int64_t slot_bytes,
                                                                          const int64_t *__restrict__ nbytes,
                                                                          const uint2 *__restrict__ sync_index, int64_t entries,
