@@ -1068,31 +1068,109 @@ constexpr int DEC_THREADS = 128;
 // bookkeeping costs 34 % more instructions and the kernel got slower, 692 against 606 us.  Loading on a fixed beat --
 // every second event all lanes merge the words they requested two events earlier into a 64-bit reserve and request
 // the next two -- did not help either, 657 us: the compiler makes the loop's branch wait for the loads in flight.)
+// One step of rlgr::decode_range (membuf.cpp:266-334): a zero run and its non-zero symbol in run mode, one symbol
+// otherwise.  have = true: a non-zero symbol `val` at position `at` (relative to the range) came out of it.
+__device__ __forceinline__ void decode_step(BitReader &br, State &s, bool &synced, uint32_t first, uint32_t &pos, uint32_t end,
+                                            int flag_signed, bool &have, uint32_t &at, int32_t &val)
+{
+    int k = s.kP / RL_L;
+    const unsigned kR = (unsigned)(s.kRP / RL_L);
+    const bool run = k != 0;
+    if (run) {
+        uint32_t m = 0;
+        bool bad = false;
+        for (;;) {                                                         // complete runs: one 1 bit each
+            const int p = br.ones();
+            for (int j = 0; j < p; ++j) {
+                m += 1u << k;
+                s.kP += RL_U1;
+                k = s.kP / RL_L;
+                if (m >= (1u << 31) || k > 30) { bad = true; break; }      // corrupt stream guard
+            }
+            if (bad) break;
+            if (p < 32) { br.skip((unsigned)p + 1); break; }
+            br.skip(32);
+        }
+        if (!bad) m += br.get((unsigned)k);
+        if (bad || (synced && m >= end - pos)) { pos = end; return; }      // the next non-zero lies past this range
+        if (synced) pos += m;
+        else { pos = first; synced = true; }
+    }
+    const uint32_t u = br.gr(kR);
+    adapt_krp(s, (uint64_t)u >> kR);
+    if (run || u) {
+        if (!synced) { pos = first; synced = true; }
+        const uint64_t v = (uint64_t)u + (run ? 1u : 0u);
+        have = true;
+        at = pos++;
+        val = flag_signed ? u2s(v) : (int32_t)v;
+        s.kP = s.kP < RL_D1 ? 0 : s.kP - RL_D1;
+    } else {
+        s.kP += RL_U0;
+        if (synced) ++pos;
+    }
+}
+
+// One thread per sync entry (512 symbols), but the symbols do not leave the thread one by one: 59 M four-byte stores,
+// every lane of a warp to a different cache line, were what bound the kernel (53 M sectors through the L1 tag stage for
+// 236 MB of output; doubling the threads did not make it faster).  The range is decoded in windows of 32 symbols into
+// a row of shared memory per lane; after each window the warp writes its 32 rows out as 32 full lines -- zeros
+// included, so the output needs no memset.
+constexpr int DEC_WIN = 32, DEC_PITCH = DEC_WIN + 1;
 __global__ void __launch_bounds__(DEC_THREADS) rlgr_decode_indexed_kernel(const uint8_t *__restrict__ streams, int64_t slot_bytes,
                                                                          const int64_t *__restrict__ nbytes,
                                                                          const uint2 *__restrict__ sync_index, int64_t entries,
                                                                          Geometry G, int32_t *__restrict__ q)
 {
+    __shared__ int32_t stage[DEC_THREADS / 32][32][DEC_PITCH];
     const int ch = blockIdx.y;
-    const int64_t e = (int64_t)blockIdx.x * DEC_THREADS + threadIdx.x;
-    if (e >= entries) return;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int64_t e0 = (int64_t)blockIdx.x * DEC_THREADS + warp * 32;      // first entry of this warp
+    const int64_t e = e0 + lane;
     const int64_t start = e << SYNC_SHIFT;
-    int64_t end = start + SYNC_RANGE;
-    if (end > G.n) end = G.n;
-    const uint2 ent = sync_index[(size_t)ch * entries + e];
-    const uint32_t first = ent.y >> 22;
-    if (first == SYNC_NONE || start + first >= end) return;                // nothing but zeros in this range
+    const uint32_t end = e < entries ? (uint32_t)min((int64_t)SYNC_RANGE, G.n - start) : 0u;
+    uint32_t first = SYNC_NONE;
+    uint2 ent = make_uint2(0u, 0u);
+    if (e < entries) {
+        ent = sync_index[(size_t)ch * entries + e];
+        first = ent.y >> 22;
+    }
+    BitReader br;
     State s;
     s.kP = (int)((ent.y >> 7) & 0x7f);
     s.kRP = (int)((ent.y >> 14) & 0xff);
-    int64_t nb = nbytes ? nbytes[ch] : slot_bytes;
-    if (nb > slot_bytes) nb = slot_bytes;
-    const unsigned long long begin = (unsigned long long)ent.x | ((unsigned long long)(ent.y & 0x7f) << 32);
-    // positions relative to the range: the reader starts before the event whose non-zero is symbol `first` of it
-    int32_t *dst = q + (size_t)ch * G.ld + start;
-    BitReader br;
-    br.init(streams + (size_t)ch * slot_bytes, nb, begin);
-    decode_range(br, s, (int64_t)first, end - start, G.flag_signed, dst);
+    bool synced = false, have = false;
+    uint32_t pos = 0, at = 0;
+    int32_t val = 0;
+    if (first != SYNC_NONE && first < end) {                               // else: nothing but zeros in this range
+        int64_t nb = nbytes ? nbytes[ch] : slot_bytes;
+        if (nb > slot_bytes) nb = slot_bytes;
+        br.init(streams + (size_t)ch * slot_bytes, nb, (unsigned long long)ent.x | ((unsigned long long)(ent.y & 0x7f) << 32));
+    } else {
+        pos = end;
+    }
+    int32_t *row = stage[warp][lane];
+    for (int i = 0; i < DEC_WIN; ++i) row[i] = 0;
+    __syncwarp();
+    int32_t *qch = q + (size_t)ch * G.ld;
+    const int rows = (int)min((int64_t)32, entries - e0);                  // ranges of this warp that exist
+    for (uint32_t w0 = 0; w0 < (uint32_t)SYNC_RANGE; w0 += DEC_WIN) {
+        if (!__any_sync(~0u, w0 < end)) break;                             // past the end of the channel
+        for (;;) {                                                         // one loop, one decode step per turn: the lanes stay together
+            if (have && at < w0 + DEC_WIN) { row[at - w0] = val; have = false; }
+            const bool more = !have && pos < end;
+            if (!__any_sync(~0u, more)) break;
+            if (more) decode_step(br, s, synced, first, pos, end, G.flag_signed, have, at, val);
+        }
+        __syncwarp();
+        for (int r = 0; r < rows; ++r) {
+            const int64_t g = ((e0 + r) << SYNC_SHIFT) + w0 + lane;
+            const int32_t v = stage[warp][r][lane];
+            stage[warp][r][lane] = 0;
+            if (g < G.n) qch[g] = v;
+        }
+        __syncwarp();
+    }
 }
 
 struct EncLayout {
@@ -1214,13 +1292,13 @@ RAHT_API int raht_rlgr_decode(const uint8_t *streams, int64_t slot_bytes, const 
     cudaStream_t st = (cudaStream_t)stream;
     Geometry G;
     G.n = n; G.ld = ld; G.nsb = sym_blocks_of(n); G.W = chunk_slots_of(n); G.nch = nch; G.flag_signed = flag_signed;
-    RAHT_CUDA(cudaMemsetAsync(q, 0, ((size_t)(nch - 1) * ld + n) * 4, st));      // the decoders store non-zeros only
-    if (sync_index) {
+    if (sync_index) {                                        // (writes every symbol: no memset)
         const int64_t entries = raht_rlgr_sync_entries(n);
         const dim3 grid((unsigned)((entries + DEC_THREADS - 1) / DEC_THREADS), nch);
         raht_count_launches(1);
         rlgr_decode_indexed_kernel<<<grid, DEC_THREADS, 0, st>>>(streams, slot_bytes, nbytes, (const uint2 *)sync_index, entries, G, q);
     } else {
+        RAHT_CUDA(cudaMemsetAsync(q, 0, ((size_t)(nch - 1) * ld + n) * 4, st));  // the serial decoder stores non-zeros only
         (raht_count_launches(1), rlgr_decode_serial_kernel)<<<nch, 32, 0, st>>>(streams, slot_bytes, nbytes, G, q);
     }
     RAHT_LAUNCH_CHECK();
