@@ -636,8 +636,9 @@ __device__ __forceinline__ void speculate_chunk(const Geometry &G, const ChanInf
     const LaneBlock B = lane_block(ev, G, ch, w, I);
     ChunkSol<NC> S;
     const long long t0 = clock64();
-    // (chunk 0 of a dense channel runs until its pinned chain is complete; a sparse one falls back on its table)
-    solve_chunk<NC>(B, pin, pins, need, (w == 0 && NC == 1) ? PIN_ROUNDS : (sweep ? RESPEC_ROUNDS : SPEC_ROUNDS), S, NC > 1 ? H : nullptr);
+    // (chunk 0 runs until its pinned chain is complete: with the helper warps a sparse chunk's rounds are cheap, and
+    // the re-solve it would otherwise need sits on the critical path of the resolve pass)
+    solve_chunk<NC>(B, pin, pins, need, w == 0 ? PIN_ROUNDS : (sweep ? RESPEC_ROUNDS : SPEC_ROUNDS), S, NC > 1 ? H : nullptr);
     if (NC > 1) helpers_release(H);
     finish_chunk<NC>(S, rec + ci * REC_WORDS, lanerec + ci * 32 * LANEREC_WORDS);
     if ((threadIdx.x & 31) == 0 && stats) {
@@ -852,67 +853,85 @@ __global__ void __launch_bounds__(32 * SOLVE_WARPS) rlgr_resolve_kernel(Geometry
         return;
     }
     unsigned long long table_hits = 0;
-    State s = initial_state();
+    uint32_t ps = pack_state(initial_state());
     unsigned long long off = 0;
     unsigned long long repairs = 0, repair_rounds = 0;
     for (int64_t base = 0; base < nchunks; base += 32) {
-      // lane l holds the record of chunk base + l; the chunks are then walked in order with shuffles
-      const int64_t mine = base + lane < nchunks ? base + lane : nchunks - 1;
-      const uint4 *mr = rec + ((size_t)ch * G.W + mine) * REC_WORDS;
-      uint4 m0 = mr[0], m1 = mr[1], m2 = mr[2], m3 = mr[3];
-      const int cnt = (int)min((int64_t)32, nchunks - base);
-      for (int i = 0; i < cnt; ++i) {
-        const int64_t w = base + i;
-        const size_t ci = (size_t)ch * G.W + w;
-        uint4 r0;                                                 // the 8 candidates of chunk w (every lane)
-        r0.x = __shfl_sync(~0u, m0.x, i); r0.y = __shfl_sync(~0u, m0.y, i);
-        r0.z = __shfl_sync(~0u, m0.z, i); r0.w = __shfl_sync(~0u, m0.w, i);
-        const uint32_t ps = pack_state(s);
-        unsigned hit = __ballot_sync(~0u, lane < 8 && half_of(r0, lane & 7) == ps);
-        if (!dense) {
-            if (lane == 0) cstart[ci] = 0u;
-            if (!hit) {                                           // sparse channel: the chunk's transition table
-                const int idx = tab_index(headers[(size_t)ch * G.nsb + w * CHUNK_LANES], ps);
-                uint2 e = make_uint2(TAB_DEAD, 0u);
-                if (idx >= 0) e = ctab[ci * TAB_STATES + idx];
-                if (e.x != TAB_DEAD) {
-                    if (lane == 0) { chunkoff[ci] = off << 3; cstart[ci] = ps | (1u << 16); }
-                    off += e.y;
-                    s = unpack_state(e.x);
-                    ++table_hits;
-                    continue;
+        // lane l holds the record of chunk base + l.  The only serial part is the chain of states: at step i every lane
+        // looks the state up in its own record and lane i's answer is broadcast (one shuffle per chunk); which
+        // candidate a chunk took, its code length and its start state stay in its lane, and the bit offsets of the
+        // batch come from one prefix sum afterwards.
+        const int64_t mine = base + lane < nchunks ? base + lane : nchunks - 1;
+        const size_t cm = (size_t)ch * G.W + mine;
+        const uint4 *mr = rec + cm * REC_WORDS;
+        uint4 m0 = mr[0], m1 = mr[1], m2 = mr[2], m3 = mr[3];
+        const int cnt = (int)min((int64_t)32, nchunks - base);
+        uint32_t my_sel = 0, my_bits = 0, my_start = 0;              // my_start: 0 = settled by a record, else state | 1 << 16 (table)
+        for (int i = 0; i < cnt; ++i) {
+            int b = -1;
+#pragma unroll
+            for (int c = 7; c >= 0; --c) b = half_of(m0, c) == ps ? c : b;
+            uint32_t e = b >= 0 ? half_of(m1, b) : STATE_INVALID;
+            uint32_t bits = b >= 0 ? word_of(m2, m3, b) : 0u;
+            uint32_t e_i = __shfl_sync(~0u, e, i);
+            uint32_t start_flag = 0;
+            if (e_i == STATE_INVALID) {                              // (warp-uniform) no candidate of chunk i starts in the true state
+                const int64_t w = base + i;
+                const size_t ci = (size_t)ch * G.W + w;
+                bool settled = false;
+                if (!dense) {                                        // sparse channel: the chunk's transition table
+                    const int idx = tab_index(headers[(size_t)ch * G.nsb + w * CHUNK_LANES], ps);
+                    uint2 te = make_uint2(TAB_DEAD, 0u);
+                    if (idx >= 0) te = ctab[ci * TAB_STATES + idx];
+                    if (te.x != TAB_DEAD) {
+                        e_i = te.x;
+                        if (lane == i) { b = 0; bits = te.y; start_flag = ps | (1u << 16); }
+                        ++table_hits;
+                        settled = true;
+                    }
+                }
+                if (!settled) {                                      // solve this chunk again from the true state
+                    const LaneBlock B = lane_block(ev, G, ch, w, I);
+                    uint4 *lr = lanerec + ci * 32 * LANEREC_WORDS;
+                    int rounds;
+                    uint32_t pins[8];
+                    for (int c = 0; c < 8; ++c) pins[c] = ps;
+                    if (dense) {
+                        ChunkSol<1> S;
+                        solve_chunk<1>(B, true, pins, 1u, PIN_ROUNDS, S);
+                        finish_chunk<1>(S, rec + ci * REC_WORDS, lr);
+                        rounds = S.rounds;
+                    } else {
+                        ChunkSol<8> S;
+                        if (lane == 0) helpers.w = (long long)w;
+                        solve_chunk<8>(B, true, pins, 1u, PIN_ROUNDS, S, &helpers);
+                        finish_chunk<8>(S, rec + ci * REC_WORDS, lr);
+                        rounds = S.rounds;
+                    }
+                    __syncwarp();
+                    const uint4 *rr = rec + ci * REC_WORDS;          // (written by lane 0 just above): the pinned chain is candidate 0
+                    const uint4 n1 = rr[1], n2 = rr[2];
+                    e_i = half_of(n1, 0);
+                    if (lane == i) { m0 = rr[0]; m1 = n1; m2 = n2; m3 = rr[3]; b = 0; bits = n2.x; }
+                    ++repairs;
+                    repair_rounds += (unsigned long long)rounds;
                 }
             }
+            if (lane == i) { my_sel = (uint32_t)b; my_bits = bits; my_start = start_flag; }
+            ps = e_i;
         }
-        if (!hit) {                                               // no candidate was the true state: solve this chunk from it
-            const LaneBlock B = lane_block(ev, G, ch, w, I);
-            uint4 *lr = lanerec + ci * 32 * LANEREC_WORDS;
-            int rounds;
-            uint32_t pins[8];
-            for (int c = 0; c < 8; ++c) pins[c] = ps;
-            if (dense) {
-                ChunkSol<1> S;
-                solve_chunk<1>(B, true, pins, 1u, PIN_ROUNDS, S);
-                finish_chunk<1>(S, rec + ci * REC_WORDS, lr);
-                rounds = S.rounds;
-            } else {
-                ChunkSol<8> S;
-                if (lane == 0) helpers.w = (long long)w;
-                solve_chunk<8>(B, true, pins, 1u, PIN_ROUNDS, S, &helpers);
-                finish_chunk<8>(S, rec + ci * REC_WORDS, lr);
-                rounds = S.rounds;
-            }
-            __syncwarp();
-            if (lane == i) { m0 = mr[0]; m1 = mr[1]; m2 = mr[2]; m3 = mr[3]; }      // (written by lane 0 just above)
-            hit = 1u;                                             // the pinned chain is candidate 0
-            ++repairs;
-            repair_rounds += (unsigned long long)rounds;
+        // bit offsets of the batch
+        uint32_t incl = lane < cnt ? my_bits : 0u;
+        unsigned long long run = incl;
+        for (int o = 1; o < 32; o <<= 1) {
+            const unsigned long long y = __shfl_up_sync(~0u, run, o);
+            if (lane >= o) run += y;
         }
-        const int b = __ffs((int)hit) - 1;
-        if (lane == 0) chunkoff[ci] = (off << 3) | (unsigned)b;
-        off += __shfl_sync(~0u, word_of(m2, m3, b), i);
-        s = unpack_state(__shfl_sync(~0u, half_of(m1, b), i));
-      }
+        if (lane < cnt) {
+            chunkoff[cm] = ((off + run - incl) << 3) | (my_sel & 7u);
+            if (!dense) cstart[cm] = my_start;
+        }
+        off += __shfl_sync(~0u, run, 31);
     }
     if (!dense) helpers_release(&helpers);
     if (lane == 0) {
