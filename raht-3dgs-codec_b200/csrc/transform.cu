@@ -10,6 +10,7 @@
 // Arithmetic (fp64 mode): a*x0 + b*x1 and (-b)*x0 + a*x1 with separately rounded products and sum
 // (__dmul_rn / __dadd_rn never contract to FMA) -- bit-exact with torch on CPU (RAHT.py:331-332).
 #include "plan.cuh"
+#include <cstdlib>
 
 namespace {
 
@@ -52,7 +53,7 @@ __device__ __forceinline__ int32_t quantise_one(double v, double step, bool &ovf
 }
 
 template <typename Tel> struct SmemLayout {
-    size_t off_ab, off_sched, off_hdr, off_flag, off_bar, off_pos, off_step, total;
+    size_t off_ab, off_sched, off_hdr, off_flag, off_bar, off_pos, off_step, off_def, total;
     __host__ __device__ SmemLayout(int R, int D)
     {
         size_t o = (size_t)R * D * sizeof(Tel);
@@ -65,6 +66,7 @@ template <typename Tel> struct SmemLayout {
         o = (o + 7) & ~(size_t)7;
         off_step = o; o += (size_t)D * 8;
         off_pos = o; o += (size_t)R * 4;
+        off_def = o; o += (size_t)PLAN_DEFER_MAX * 2 + 2;
         total = (o + 15) & ~(size_t)15;
     }
 };
@@ -89,6 +91,7 @@ transform_stage0_kernel(PlanDev P, const Tin *__restrict__ A, const Tel *B, Tel 
     uint8_t *s_flag = tr_smem + L.off_flag;
     double *s_step = (double *)(tr_smem + L.off_step);
     int32_t *s_pos = (int32_t *)(tr_smem + L.off_pos);
+    uint16_t *s_def = (uint16_t *)(tr_smem + L.off_def);
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int64_t tile = blockIdx.x;
@@ -104,11 +107,9 @@ transform_stage0_kernel(PlanDev P, const Tin *__restrict__ A, const Tel *B, Tel 
 
     // bulk copies need 16-byte granularity; tiles that do not qualify (ragged last tile) use plain loads
     bool tma_in = false, tma_out = false;
-    if constexpr (sizeof(Tin) == sizeof(Tel)) {
-        if (use_tma && (tile_bytes % 16) == 0) {
-            tma_in = QM != QM_INV && (((uintptr_t)(A + base * D)) % 16) == 0;
-            tma_out = QM != QM_FWD && (((uintptr_t)(O + base * D)) % 16) == 0;
-        }
+    if (use_tma && (tile_bytes % 16) == 0) {
+        if constexpr (sizeof(Tin) == sizeof(Tel)) tma_in = QM != QM_INV && (((uintptr_t)(A + base * D)) % 16) == 0;
+        tma_out = QM != QM_FWD && (((uintptr_t)(O + base * D)) % 16) == 0;
     }
     if constexpr (QM != QM_NONE) {
         for (int c = tid; c < D; c += TR_THREADS) s_step[c] = Q.steps[c];
@@ -140,9 +141,30 @@ transform_stage0_kernel(PlanDev P, const Tin *__restrict__ A, const Tel *B, Tel 
         for (int j = tid; j < n_rows; j += TR_THREADS) s_flag[j] = 0;
         __syncthreads();
         const int n_def = s_hdr->n_def;
-        for (int j = tid; j < n_def; j += TR_THREADS) s_flag[P.def_local[(size_t)tile * PLAN_DEFER_MAX + j]] = 1;
+        for (int j = tid; j < n_def; j += TR_THREADS) {
+            const uint16_t dl = P.def_local[(size_t)tile * PLAN_DEFER_MAX + j];
+            s_flag[dl] = 1;
+            s_def[j] = dl;
+        }
     }
     __syncthreads();
+
+    // rows this tile deferred come from B: the first PF_ITEMS elements per thread are requested BEFORE the wait for the
+    // bulk copy (a dependent second round of loads after it cost ~1 us per tile), the rest (tiles that defer more than
+    // ~34 rows) afterwards
+    constexpr int PF_ITEMS = 8;
+    Tel pf[PF_ITEMS];
+    const int n_patch = (B != nullptr) ? (int)s_hdr->n_def * D : 0;
+    if (n_patch) {
+#pragma unroll
+        for (int u = 0; u < PF_ITEMS; ++u) {
+            const int idx = tid + u * TR_THREADS;
+            if (idx < n_patch) {
+                const int j = idx / D, c = idx - j * D;
+                pf[u] = B[(size_t)(base + s_def[j]) * D + c];
+            }
+        }
+    }
 
     if (tma_in) {
         mbar_wait(s_bar, 0);
@@ -158,15 +180,47 @@ transform_stage0_kernel(PlanDev P, const Tin *__restrict__ A, const Tel *B, Tel 
     } else {
         const Tin *src = A + base * D;
         const int n_el = n_rows * D;
-        for (int i = tid; i < n_el; i += TR_THREADS) s_rows[i] = (Tel)src[i];
+        bool done = false;
+        if constexpr (sizeof(Tin) == 4 && sizeof(Tel) == 8) {
+            // fp32 rows widened on the way in: 16-byte requests, LD_BATCH of them in flight per thread before the first
+            // use (a scalar loop kept ~4 KB per CTA in flight and was bound by the round trip, not by the bandwidth)
+            if ((n_el & 3) == 0 && (((uintptr_t)src) & 15) == 0) {
+                constexpr int LD_BATCH = 8;
+                const float4 *src4 = (const float4 *)src;
+                const int n4 = n_el >> 2;
+                for (int i0 = tid; i0 < n4; i0 += LD_BATCH * TR_THREADS) {
+                    float4 v[LD_BATCH];
+#pragma unroll
+                    for (int u = 0; u < LD_BATCH; ++u)
+                        if (i0 + u * TR_THREADS < n4) v[u] = __ldg(src4 + i0 + u * TR_THREADS);
+#pragma unroll
+                    for (int u = 0; u < LD_BATCH; ++u)
+                        if (i0 + u * TR_THREADS < n4) {
+                            double2 *dst = (double2 *)(s_rows + 4 * (size_t)(i0 + u * TR_THREADS));
+                            dst[0] = make_double2((double)v[u].x, (double)v[u].y);
+                            dst[1] = make_double2((double)v[u].z, (double)v[u].w);
+                        }
+                }
+                done = true;
+            }
+        }
+        if (!done)
+            for (int i = tid; i < n_el; i += TR_THREADS) s_rows[i] = (Tel)src[i];
         __syncthreads();
     }
-    if (patch && B != nullptr) {
-        for (int j = warp; j < n_rows; j += TR_WARPS)
-            if (s_flag[j]) {
-                const Tel *src = B + (size_t)(base + j) * D;
-                for (int c = lane; c < D; c += 32) s_rows[j * D + c] = src[c];
+    if (n_patch) {
+#pragma unroll
+        for (int u = 0; u < PF_ITEMS; ++u) {
+            const int idx = tid + u * TR_THREADS;
+            if (idx < n_patch) {
+                const int j = idx / D, c = idx - j * D;
+                s_rows[(int)s_def[j] * D + c] = pf[u];
             }
+        }
+        for (int idx = tid + PF_ITEMS * TR_THREADS; idx < n_patch; idx += TR_THREADS) {
+            const int j = idx / D, c = idx - j * D;
+            s_rows[(int)s_def[j] * D + c] = B[(size_t)(base + s_def[j]) * D + c];
+        }
     }
     __syncthreads();
 
@@ -241,14 +295,15 @@ transform_stage0_kernel(PlanDev P, const Tin *__restrict__ A, const Tel *B, Tel 
 // took 40 us there whatever the tile held.
 constexpr int UP_ELEMS = 8192;     // row elements staged per pass
 constexpr int UP_GROUPS_MAX = 16;
+constexpr int UP_GROUPS_MANY = 2, UP_ELEMS_MANY = 2560;      // stages with >= 2 tiles per SM (sweep: scripts/gpu_upper_sweep.sh)
 
 template <typename Tel, bool FWD>
 __global__ void __launch_bounds__(TR_THREADS)
-transform_upper_kernel(PlanDev P, int stage, const Tel *A, const Tel *B, Tel *O, int D)
+transform_upper_kernel(PlanDev P, int stage, const Tel *A, const Tel *B, Tel *O, int D, int up_elems)
 {
     extern __shared__ __align__(128) unsigned char tr_smem[];
-    Tel *s_rows = (Tel *)tr_smem;                                          // UP_ELEMS
-    Tel *s_ab = s_rows + UP_ELEMS;                                         // 2 * PLAN_UP_CAP
+    Tel *s_rows = (Tel *)tr_smem;                                          // up_elems
+    Tel *s_ab = s_rows + up_elems;                                         // 2 * PLAN_UP_CAP
     uint32_t *s_sched = (uint32_t *)(s_ab + 2 * PLAN_UP_CAP);              // PLAN_UP_CAP
     uint32_t *s_rowid = s_sched + PLAN_UP_CAP;                             // PLAN_UP_CAP
     uint8_t *s_flag = (uint8_t *)(s_rowid + PLAN_UP_CAP);                  // PLAN_UP_CAP
@@ -261,13 +316,17 @@ transform_upper_kernel(PlanDev P, int stage, const Tel *A, const Tel *B, Tel *O,
     if (tid < (int)(sizeof(TileHdr) / 4)) ((uint32_t *)&s_hdr)[tid] = ((const uint32_t *)(P.hdr + gt))[tid];
     const int64_t c0 = tile * PLAN_FANIN;
     const int64_t cbase = P.tile_base[stage - 1];
-    if (tid == 0) {
-        int run = 0;
-        for (int c = 0; c < PLAN_FANIN; ++c) {
-            s_off[c] = run;
-            if (c0 + c < P.tiles[stage - 1]) run += min((int)P.hdr[cbase + c0 + c].n_def, PLAN_DEFER_MAX);
+    if (tid < 32) {                                          // entries per child tile: eight independent loads, one scan
+        int cnt = 0;
+        if (tid < PLAN_FANIN && c0 + tid < P.tiles[stage - 1]) cnt = min((int)P.hdr[cbase + c0 + tid].n_def, PLAN_DEFER_MAX);
+        int incl = cnt;
+#pragma unroll
+        for (int o = 1; o < PLAN_FANIN; o <<= 1) {
+            const int v = __shfl_up_sync(~0u, incl, o);
+            if (tid >= o) incl += v;
         }
-        s_off[PLAN_FANIN] = run;
+        if (tid < PLAN_FANIN) s_off[tid] = incl - cnt;
+        if (tid == PLAN_FANIN - 1) s_off[PLAN_FANIN] = incl;
     }
     __syncthreads();
     const int n_rows = s_hdr.n_rows;
@@ -298,15 +357,27 @@ transform_upper_kernel(PlanDev P, int stage, const Tel *A, const Tel *B, Tel *O,
     const int per = (D + (int)gridDim.y - 1) / (int)gridDim.y;            // channels of this CTA's group
     const int cb = (int)blockIdx.y * per, ce = min(D, cb + per);
     if (cb >= ce) return;
-    int DS = UP_ELEMS / n_rows;
+    int DS = up_elems / n_rows;
     if (DS > ce - cb) DS = ce - cb;
     for (int d0 = cb; d0 < ce; d0 += DS) {
         const int dn = min(DS, ce - d0);
         const int n_el = n_rows * dn;
-        for (int i = tid; i < n_el; i += TR_THREADS) {
-            const int j = i / dn, c = i - j * dn;
-            const Tel *src = (B && s_flag[j]) ? B : A;
-            s_rows[j * dn + c] = src[(size_t)s_rowid[j] * D + d0 + c];
+        // gather, UP_BATCH requests in flight per thread (one at a time, the stage was bound by the round trip of each)
+        constexpr int UP_BATCH = 8;
+        for (int i0 = tid; i0 < n_el; i0 += UP_BATCH * TR_THREADS) {
+            Tel v[UP_BATCH];
+#pragma unroll
+            for (int u = 0; u < UP_BATCH; ++u) {
+                const int i = i0 + u * TR_THREADS;
+                if (i < n_el) {
+                    const int j = i / dn, c = i - j * dn;
+                    const Tel *src = (B && s_flag[j]) ? B : A;
+                    v[u] = src[(size_t)s_rowid[j] * D + d0 + c];
+                }
+            }
+#pragma unroll
+            for (int u = 0; u < UP_BATCH; ++u)
+                if (i0 + u * TR_THREADS < n_el) s_rows[i0 + u * TR_THREADS] = v[u];      // = s_rows[j * dn + c]
         }
         __syncthreads();
         for (int kk = 0; kk < n_rounds; ++kk) {
@@ -415,14 +486,28 @@ int launch_stage0_d(const raht_plan *P, const Tin *A, const Tel *B, Tel *O, int 
 template <typename Tel, bool FWD>
 int launch_upper(const raht_plan *P, int k, const Tel *A, const Tel *B, Tel *O, int D, cudaStream_t st)
 {
-    const size_t smem = (size_t)(UP_ELEMS + 2 * PLAN_UP_CAP) * sizeof(Tel) + (size_t)PLAN_UP_CAP * 9 + 16;
     auto kern = transform_upper_kernel<Tel, FWD>;
-    RAHT_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     const int64_t tiles = P->d.tiles[k];
-    int groups = tiles >= 2 * sm_count_cached() ? 1 : (int)((4 * (int64_t)sm_count_cached() + tiles - 1) / tiles);
-    if (groups > UP_GROUPS_MAX) groups = UP_GROUPS_MAX;
+    // Stages with many tiles (typically ~70 entries each, up to 64 dependent rounds) are bound by how many of those
+    // chains an SM holds, i.e. by shared memory per CTA: channel groups over gridDim.y shrink the staging area a tile
+    // needs.  Stages with few tiles are spread over up to 16 channel groups to fill the GPU.
+    static const int env_groups = getenv("RAHT_UP_GROUPS") ? atoi(getenv("RAHT_UP_GROUPS")) : UP_GROUPS_MANY;
+    static const int env_elems = getenv("RAHT_UP_ELEMS") ? atoi(getenv("RAHT_UP_ELEMS")) : UP_ELEMS_MANY;
+    int groups, up_elems;
+    if (tiles >= 2 * sm_count_cached()) {
+        groups = env_groups;
+        up_elems = env_elems;
+    } else {
+        groups = (int)((4 * (int64_t)sm_count_cached() + tiles - 1) / tiles);
+        if (groups > UP_GROUPS_MAX) groups = UP_GROUPS_MAX;
+        up_elems = UP_ELEMS;
+    }
     if (groups > D) groups = D;
-    (raht_count_launches(1), kern)<<<dim3((unsigned)tiles, (unsigned)groups), TR_THREADS, smem, st>>>(P->d, k, A, B, O, D);
+    if (up_elems > UP_ELEMS) up_elems = UP_ELEMS;
+    if (up_elems < PLAN_UP_CAP) up_elems = PLAN_UP_CAP;                // one channel of the largest tile must fit
+    const size_t smem = (size_t)(up_elems + 2 * PLAN_UP_CAP) * sizeof(Tel) + (size_t)PLAN_UP_CAP * 9 + 16;
+    RAHT_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(UP_ELEMS + 2 * PLAN_UP_CAP) * (int)sizeof(Tel) + PLAN_UP_CAP * 9 + 16));
+    (raht_count_launches(1), kern)<<<dim3((unsigned)tiles, (unsigned)groups), TR_THREADS, smem, st>>>(P->d, k, A, B, O, D, up_elems);
     RAHT_LAUNCH_CHECK();
     return RAHT_OK;
 }

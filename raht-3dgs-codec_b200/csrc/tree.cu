@@ -171,13 +171,17 @@ plan_tile_kernel(PlanDev P, int stage, const uint8_t *__restrict__ level, double
     } else {
         const int64_t c0 = tile * PLAN_FANIN;
         const int64_t cbase = P.tile_base[stage - 1];
-        if (tid == 0) {
-            int run = 0;
-            for (int c = 0; c < PLAN_FANIN; ++c) {
-                s_off[c] = run;
-                if (c0 + c < P.tiles[stage - 1]) run += min((int)P.hdr[cbase + c0 + c].n_def, PLAN_DEFER_MAX);
+        if (tid < 32) {                                      // entries per child tile: eight independent loads, one scan
+            int cnt = 0;
+            if (tid < PLAN_FANIN && c0 + tid < P.tiles[stage - 1]) cnt = min((int)P.hdr[cbase + c0 + tid].n_def, PLAN_DEFER_MAX);
+            int incl = cnt;
+#pragma unroll
+            for (int o = 1; o < PLAN_FANIN; o <<= 1) {
+                const int v = __shfl_up_sync(~0u, incl, o);
+                if (tid >= o) incl += v;
             }
-            s_off[PLAN_FANIN] = run;
+            if (tid < PLAN_FANIN) s_off[tid] = incl - cnt;
+            if (tid == PLAN_FANIN - 1) s_off[PLAN_FANIN] = incl;
         }
         __syncthreads();
         n_rows = s_off[PLAN_FANIN];

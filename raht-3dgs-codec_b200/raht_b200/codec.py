@@ -5,6 +5,7 @@ RAHT_param -> RAHT -> quantise -> reorder -> RLGR and back) with every step on t
 Channel layout of the coded matrix (D = 11 + color_dim, 59 for 3DGS with 48 SH coefficients):
 [merged_means 3 | quats 4 | scales 3 | opacity 1 | colors].
 """
+import os
 from dataclasses import dataclass, field
 from typing import Optional
 
@@ -38,6 +39,42 @@ class EncodedScene:
     def index_bytes(self) -> int:
         """Bytes of the optional sync index (side information for chunk-parallel decoding)."""
         return self.streams.index_bytes()
+
+
+# The tree / plan kernels (RAHT_param) are chains of small, latency-bound launches that need nothing but the voxel keys:
+# they run on a side stream next to the stage that is independent of them -- the segment merge in the encoder, the RLGR
+# decoder in the decoder -- and the main stream waits for them before the first butterfly.  RAHT_NO_OVERLAP=1 keeps
+# everything on one stream (per-kernel profiling, A/B measurements).
+OVERLAP = os.environ.get("RAHT_NO_OVERLAP") is None
+_SIDE = {}
+
+
+def _side_stream(device) -> "torch.cuda.Stream":
+    dev = torch.device(device)
+    key = dev.index if dev.index is not None else torch.cuda.current_device()
+    s = _SIDE.get(key)
+    if s is None:
+        s = _SIDE[key] = torch.cuda.Stream(device=dev)
+    return s
+
+
+def _build_tree(keys, status, tile_rows, want_position):
+    tree = ops.tree_from_keys(keys, validate=True, status=status)
+    tree.order(want_position=want_position)
+    tree.plan(tile_rows)
+    return tree
+
+
+def start_tree(keys, status, tile_rows=None, want_position=True):
+    """Queue tree_from_keys + order_RAGFT + the transform plan on the side stream (after everything queued on the current
+    stream so far).  Returns (tree, side stream): `torch.cuda.current_stream().wait_stream(side)` before the tree is used.
+    Memory: what the side stream allocates is consumed on the main stream and freed after it; the next side-stream job
+    starts with a wait for the main stream, so the caching allocator's per-stream reuse stays ordered."""
+    side = _side_stream(keys.device)
+    side.wait_stream(torch.cuda.current_stream(keys.device))
+    with torch.cuda.stream(side):
+        tree = _build_tree(keys, status, tile_rows, want_position)
+    return tree, side
 
 
 class StageTimer:
@@ -95,7 +132,8 @@ def morton_keys_given(means, J, vmin, width):
 
 
 @torch.no_grad()
-def voxelize_merge(means, quats, scales, opacities, colors, J, packed_dtype=torch.float32, timer=None, status=None, given=None):
+def voxelize_merge(means, quats, scales, opacities, colors, J, packed_dtype=torch.float32, timer=None, status=None, given=None,
+                   on_keys=None):
     """Voxelise the Gaussian centres and merge the Gaussians of each voxel.
     Returns (packed (nvox, D), unique_keys int64 (nvox), info dict).  One synchronisation (the voxel
     count must reach the host); with a shared `status` word the sort status is left to the caller.
@@ -116,6 +154,8 @@ def voxelize_merge(means, quats, scales, opacities, colors, J, packed_dtype=torc
     timer.mark("segments")
     if not deferred:
         ops.raise_for_status(int(L.read_host(status)[0][0]))
+    if on_keys is not None:                                        # the caller's work that needs the voxel keys only (side stream)
+        on_keys(unique_keys)
     _, packed = ops.merge_segments(idx32, offsets, means, quats.contiguous().float(), scales.contiguous().float(),
                                    opacities.contiguous().float(), colors.contiguous().float(), True, separate=False,
                                    packed_dtype=packed_dtype)
@@ -169,7 +209,8 @@ def per_attribute_steps(T, ranges=None, weights=None, budget=LEVELS_BUDGET):
 
 
 @torch.no_grad()
-def encode_attributes(keys, Cmat, step, transform_dtype=torch.float64, tile_rows=None, timer=None, flags=0, status=None, fused=False):
+def encode_attributes(keys, Cmat, step, transform_dtype=torch.float64, tile_rows=None, timer=None, flags=0, status=None, fused=False,
+                      tree_job=None):
     """RAHT_param -> RAHT -> quantise -> reorder -> RLGR for rows that are Morton-sorted unique voxels.
     fused: transform and quantisation in one pass (ops.forward_quant; same symbols, bit for bit), else the two
     reference steps one after the other.  Off by default: on sparse scenes (the 1 M bench scene: consecutive voxels fall
@@ -184,9 +225,12 @@ def encode_attributes(keys, Cmat, step, transform_dtype=torch.float64, tile_rows
         if step != "per_attribute":
             raise ValueError(f"unknown step rule {step!r}")
         fused = False                                              # the rule needs the coefficients before they are quantised
-    tree = ops.tree_from_keys(keys, validate=True, status=status)
+    if tree_job is not None:                                       # (tree, side stream) from start_tree(): already queued
+        tree, side = tree_job
+        torch.cuda.current_stream(keys.device).wait_stream(side)
+    else:
+        tree = _build_tree(keys, status, tile_rows, True)
     order, _ = tree.order(want_position=True)
-    tree.plan(tile_rows)
     timer.mark("raht_param")
     if fused:
         q = ops.forward_quant(tree, Cmat, step, transform_dtype, tile_rows, flags, status)
@@ -209,14 +253,20 @@ def decode_attributes(keys, streams, D, step, transform_dtype=torch.float64, tre
     """RLGR^-1 -> dequantise -> inverse reorder -> iRAHT (fused: the last three in one pass, ops.dequant_inverse)."""
     timer = timer or StageTimer(False)
     status = None
+    side = None
     if tree is None:
         status = ops._status_word(keys.device)
-        tree = ops.tree_from_keys(keys, validate=True, status=status)
-        tree.plan(tile_rows)
-        timer.mark("raht_param_dec")
-    order = tree.order()
+        if OVERLAP:
+            tree, side = start_tree(keys, status, tile_rows, want_position=fused)
+        else:
+            tree = _build_tree(keys, status, tile_rows, fused)
+            timer.mark("raht_param_dec")
     q = ops.rlgr_decode(streams, 1)
     timer.mark("rlgr_decode")
+    if side is not None:
+        torch.cuda.current_stream(keys.device).wait_stream(side)
+        timer.mark("raht_param_dec")                               # what is left of the tree / plan after the overlap
+    order = tree.order()
     if fused:
         Crec = ops.dequant_inverse(tree, q, step, transform_dtype, tile_rows, flags)
         timer.mark("dequant_iraht")
@@ -236,8 +286,11 @@ def encode_scene(means, quats, scales, opacities, colors, J, step, transform_dty
     timer = timer or StageTimer(False)
     timer.mark("start")
     status = ops._status_word(means.device)
-    packed, keys, info = voxelize_merge(means, quats, scales, opacities, colors, J, torch.float32, timer, status)
-    tree, streams = encode_attributes(keys, packed, step, transform_dtype, tile_rows, timer, flags, status, fused)
+    job = []
+    on_keys = (lambda k: job.append(start_tree(k, status, tile_rows))) if OVERLAP else None
+    packed, keys, info = voxelize_merge(means, quats, scales, opacities, colors, J, torch.float32, timer, status, on_keys=on_keys)
+    tree, streams = encode_attributes(keys, packed, step, transform_dtype, tile_rows, timer, flags, status, fused,
+                                      tree_job=job[0] if job else None)
     width, voxel_size = L.read_host(info["params_d2"])[0].tolist()          # after the coder's synchronisation: no extra wait
     step = getattr(tree, "steps", step)                            # "per_attribute": the steps the rule picked
     return EncodedScene(J=J, n_in=info["N"], nvox=info["Nvox"], D=packed.shape[1], step=step, vmin=info["vmin"],

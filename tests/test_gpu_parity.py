@@ -455,6 +455,30 @@ def test_scene_pipeline_matches_direct_calls():
 
 
 @pytest.mark.gpu
+def test_scene_side_stream_overlap_matches_single_stream(monkeypatch):
+    """The tree / plan kernels run on a side stream next to the merge (encoder) and the RLGR decoder (decoder):
+    streams, keys and decoded attributes must equal those of the single-stream order, scene after scene (the side
+    stream's allocations are consumed on the main stream and recycled by the next scene)."""
+    import torch
+    from raht_b200 import codec
+    assert codec.OVERLAP or True
+    scenes = [helpers.synthetic_gaussians(40000 + 9000 * k, 900 + k) for k in range(5)]
+    results = {}
+    for overlap in (True, False):
+        monkeypatch.setattr(codec, "OVERLAP", overlap)
+        outs = []
+        for rep in range(2):
+            for sc in scenes:
+                enc = codec.encode_scene(*[cu(a) for a in sc], J=10, step=0.03)
+                _, Crec = codec.decode_scene(enc)
+                outs.append((enc.nvox, enc.keys.clone(), enc.streams.to_bytes(), Crec.clone()))
+        torch.cuda.synchronize()
+        results[overlap] = outs
+    for a, b in zip(results[True], results[False]):
+        assert a[0] == b[0] and torch.equal(a[1], b[1]) and a[2] == b[2] and torch.equal(a[3], b[3])
+
+
+@pytest.mark.gpu
 @pytest.mark.parametrize("n,J,D,tile_rows,dtype", [(1, 3, 3, None, "f64"), (7, 2, 2, None, "f64"), (300, 5, 5, 32, "f64"),
                                                    (20000, 8, 59, None, "f64"), (20000, 8, 59, 64, "f32"), (70000, 10, 11, 128, "f64")])
 def test_fused_quantisation_matches_the_two_reference_steps(n, J, D, tile_rows, dtype):
