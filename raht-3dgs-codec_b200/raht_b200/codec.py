@@ -43,9 +43,11 @@ class EncodedScene:
 
 # The tree / plan kernels (RAHT_param) are chains of small, latency-bound launches that need nothing but the voxel keys:
 # they run on a side stream next to the stage that is independent of them -- the segment merge in the encoder, the RLGR
-# decoder in the decoder -- and the main stream waits for them before the first butterfly.  RAHT_NO_OVERLAP=1 keeps
-# everything on one stream (per-kernel profiling, A/B measurements).
-OVERLAP = os.environ.get("RAHT_NO_OVERLAP") is None
+# decoder in the decoder -- and the main stream waits for them before the first butterfly.  OFF by default (RAHT_OVERLAP=1
+# turns it on): measured on the 1 M bench scene it LOSES -- the plan's small launches, interleaved with the co-running
+# kernel's CTAs, stretch it by more than they take alone (merge 0.31 -> 0.43 ms, RLGR decode 0.57 -> 1.00 ms; step
+# 4.09 -> 4.34 ms).  Kept, with its parity test, for scenes where the co-running stage is longer.
+OVERLAP = os.environ.get("RAHT_OVERLAP") is not None
 _SIDE = {}
 
 
