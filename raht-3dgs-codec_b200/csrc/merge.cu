@@ -12,7 +12,7 @@
 
 namespace {
 
-constexpr int MG_UNROLL = 4;      // voxels per warp iteration: their dependent loads are issued level by level
+constexpr int MG_UNROLL = 4;      // voxels per group: their row gathers are in flight together (two groups buffered)
 constexpr int MG_WARPS = 8;
 
 // What a lane needs to know about its output channel c = 32 k + lane, fixed for the whole kernel: where the channel
@@ -36,11 +36,92 @@ __device__ __forceinline__ LaneChannel lane_channel(int c, int OC, const float *
     return L;
 }
 
-// One warp per voxel, lane = output channel (slot k holds channel 32 k + lane), NS slots.  The offsets, the member
-// index and the member's opacity are warp-uniform; the colour row and the packed output row are contiguous across
-// the lanes.  Every channel sums its members in segment order with separately rounded multiply and add, starting
-// from 0 as the reference does (merge_cluster.cu:36-72,97-106), so the result is a deterministic function of the inputs.
+// A warp takes blocks of 32 consecutive voxels.  Lane l reads the segment bounds and the first member index of voxel l
+// of the block (two coalesced round trips per 32 voxels; they used to be two dependent, warp-uniform round trips per
+// group of four), then the voxels are processed MG_UNROLL at a time, lane = output channel (slot k holds channel
+// 32 k + lane, NS slots): the member's colour row and the packed output row are contiguous across the lanes.  The row
+// gathers of the next group are issued before the current group is finished (two register buffers), so the only
+// dependent round trips left per block are the two index loads.  Every channel sums its members in segment order with
+// separately rounded multiply and add, starting from 0 as the reference does (merge_cluster.cu:36-72,97-106), so the
+// result is a deterministic function of the inputs.
 // SEP: also write the five separate output arrays of the reference interface (the codec only takes the packed rows).
+template <int NS>
+__device__ __forceinline__ void merge_load_group(const LaneChannel (&ch)[NS], int gl, int j0, float (&x)[MG_UNROLL][NS])
+{
+#pragma unroll
+    for (int u = 0; u < MG_UNROLL; ++u) {
+        const int g = __shfl_sync(~0u, gl, j0 + u);
+#pragma unroll
+        for (int k = 0; k < NS; ++k)
+            x[u][k] = (g >= 0 && ch[k].kind != CH_NONE) ? ch[k].base[(int64_t)g * ch[k].stride] : 0.f;
+    }
+}
+
+template <typename OutT, int NS, bool SEP>
+__device__ __forceinline__ void merge_finish_group(const LaneChannel (&ch)[NS], const int32_t *__restrict__ cidx, int sl, int tl, int j0,
+                                                   int64_t vb, int64_t nclu, const float (&x)[MG_UNROLL][NS], int OC, int color_dim,
+                                                   int by_opacity, float *__restrict__ m_means, float *__restrict__ m_quats,
+                                                   float *__restrict__ m_scales, float *__restrict__ m_opac,
+                                                   float *__restrict__ m_colors, OutT *__restrict__ packed)
+{
+    const int lane = threadIdx.x & 31;
+#pragma unroll
+    for (int u = 0; u < MG_UNROLL; ++u) {
+        const int64_t v = vb + j0 + u;
+        const int su = __shfl_sync(~0u, sl, j0 + u), tu = __shfl_sync(~0u, tl, j0 + u);
+        if (v >= nclu) continue;                                         // warp-uniform
+        float acc[NS], wsum = 0.f;
+#pragma unroll
+        for (int k = 0; k < NS; ++k) acc[k] = 0.f;
+        float xm[NS];
+#pragma unroll
+        for (int k = 0; k < NS; ++k) xm[k] = x[u][k];
+        for (int i = su; i < tu; ++i) {                                  // warp-uniform trip count (1 for most voxels)
+            if (i > su) {
+                const int64_t gi = cidx[i];
+#pragma unroll
+                for (int k = 0; k < NS; ++k) xm[k] = ch[k].kind != CH_NONE ? ch[k].base[gi * ch[k].stride] : 0.f;
+            }
+            const float o = __shfl_sync(~0u, xm[0], 10);                 // the member's opacity
+            const float w = by_opacity ? o : 1.0f;                       // :42
+            wsum = __fadd_rn(wsum, w);
+#pragma unroll
+            for (int k = 0; k < NS; ++k) {
+                const float wk = ch[k].kind == CH_OPAC ? 1.0f : w;       // the opacity channel sums the raw opacities (:60)
+                acc[k] = __fadd_rn(acc[k], __fmul_rn(xm[k], wk));
+            }
+        }
+        // quaternion norm from lanes 3..6 (:74-76)
+        const float q0 = __shfl_sync(~0u, acc[0], 3), q1 = __shfl_sync(~0u, acc[0], 4);
+        const float q2 = __shfl_sync(~0u, acc[0], 5), q3 = __shfl_sync(~0u, acc[0], 6);
+        const float qn = __fsqrt_rn(__fadd_rn(__fadd_rn(__fadd_rn(__fmul_rn(q0, q0), __fmul_rn(q1, q1)), __fmul_rn(q2, q2)),
+                                              __fmul_rn(q3, q3)));
+        const bool empty = tu <= su;                                     // :27-29
+#pragma unroll
+        for (int k = 0; k < NS; ++k) {
+            const int kind = ch[k].kind;
+            if (kind == CH_NONE) continue;
+            const int c = 32 * k + lane;
+            // one division per channel: by the quaternion norm (:77-87), or by the weight sum -- means and scales take
+            // 1 for an all-zero weight (:65-72), colours give 0 then (:108-109)
+            const float den = kind == CH_QUAT ? qn : ((kind == CH_MEAN && wsum == 0.0f) ? 1.0f : wsum);
+            float out = __fdiv_rn(acc[k], den);
+            if (kind == CH_QUAT && !(qn > 0.0f)) out = c == 6 ? 1.0f : 0.0f;
+            if (kind == CH_COLOR && !(wsum > 0.0f)) out = 0.0f;
+            if (kind == CH_OPAC) out = fminf(acc[k], 1.0f);                                          // :94
+            if (empty) out = 0.0f;
+            if constexpr (SEP) {
+                if (c < 3) { if (m_means) m_means[v * 3 + c] = out; }
+                else if (c < 7) { if (m_quats) m_quats[v * 4 + (c - 3)] = out; }
+                else if (c < 10) { if (m_scales) m_scales[v * 3 + (c - 7)] = out; }
+                else if (c == 10) { if (m_opac) m_opac[v] = out; }
+                else { if (m_colors) m_colors[v * (int64_t)color_dim + (c - 11)] = out; }
+            }
+            if (packed) packed[v * OC + c] = (OutT)out;
+        }
+    }
+}
+
 template <typename OutT, int NS, bool SEP>
 __global__ void __launch_bounds__(32 * MG_WARPS)
 merge_kernel(const int32_t *__restrict__ cidx, const int32_t *__restrict__ coff, int64_t nclu,
@@ -49,83 +130,37 @@ merge_kernel(const int32_t *__restrict__ cidx, const int32_t *__restrict__ coff,
              float *__restrict__ m_means, float *__restrict__ m_quats, float *__restrict__ m_scales,
              float *__restrict__ m_opac, float *__restrict__ m_colors, OutT *__restrict__ packed)
 {
+    static_assert(32 % (2 * MG_UNROLL) == 0, "a block of 32 voxels is a whole number of group pairs");
     const int OC = 11 + color_dim;
     const int lane = threadIdx.x & 31;
     LaneChannel ch[NS];
 #pragma unroll
     for (int k = 0; k < NS; ++k) ch[k] = lane_channel(32 * k + lane, OC, means, quats, scales, opac, colors, color_dim);
     const int64_t nwarps = (int64_t)gridDim.x * MG_WARPS;
-    for (int64_t v0 = (int64_t)blockIdx.x * MG_WARPS + (threadIdx.x >> 5); v0 < nclu; v0 += MG_UNROLL * nwarps) {
-        int s[MG_UNROLL], t[MG_UNROLL], g[MG_UNROLL];
-        float x[MG_UNROLL][NS];
-#pragma unroll
-        for (int u = 0; u < MG_UNROLL; ++u) {
-            const int64_t v = v0 + u * nwarps;
-            const bool ok = v < nclu;
-            s[u] = ok ? coff[v] : 0;
-            t[u] = ok ? coff[v + 1] : 0;
+    const int64_t nblk = (nclu + 31) >> 5;
+    for (int64_t b = (int64_t)blockIdx.x * MG_WARPS + (threadIdx.x >> 5); b < nblk; b += nwarps) {
+        const int64_t vb = b << 5;
+        int sl = 0, tl = 0;
+        if (vb + lane < nclu) {
+            sl = coff[vb + lane];
+            tl = coff[vb + lane + 1];
         }
-#pragma unroll
-        for (int u = 0; u < MG_UNROLL; ++u) g[u] = t[u] > s[u] ? cidx[s[u]] : -1;
-#pragma unroll
-        for (int u = 0; u < MG_UNROLL; ++u)
-#pragma unroll
-            for (int k = 0; k < NS; ++k)
-                x[u][k] = (g[u] >= 0 && ch[k].kind != CH_NONE) ? ch[k].base[(int64_t)g[u] * ch[k].stride] : 0.f;
-#pragma unroll
-        for (int u = 0; u < MG_UNROLL; ++u) {
-            const int64_t v = v0 + u * nwarps;
-            if (v >= nclu) continue;                                         // warp-uniform
-            float acc[NS], wsum = 0.f;
-#pragma unroll
-            for (int k = 0; k < NS; ++k) acc[k] = 0.f;
-            float xm[NS];
-#pragma unroll
-            for (int k = 0; k < NS; ++k) xm[k] = x[u][k];
-            for (int i = s[u]; i < t[u]; ++i) {                              // warp-uniform trip count (1 for most voxels)
-                if (i > s[u]) {
-                    const int64_t gi = cidx[i];
-#pragma unroll
-                    for (int k = 0; k < NS; ++k) xm[k] = ch[k].kind != CH_NONE ? ch[k].base[gi * ch[k].stride] : 0.f;
-                }
-                const float o = __shfl_sync(~0u, xm[0], 10);                 // the member's opacity
-                const float w = by_opacity ? o : 1.0f;                       // :42
-                wsum = __fadd_rn(wsum, w);
-#pragma unroll
-                for (int k = 0; k < NS; ++k) {
-                    const float wk = ch[k].kind == CH_OPAC ? 1.0f : w;       // the opacity channel sums the raw opacities (:60)
-                    acc[k] = __fadd_rn(acc[k], __fmul_rn(xm[k], wk));
-                }
-            }
-            // quaternion norm from lanes 3..6 (:74-76)
-            const float q0 = __shfl_sync(~0u, acc[0], 3), q1 = __shfl_sync(~0u, acc[0], 4);
-            const float q2 = __shfl_sync(~0u, acc[0], 5), q3 = __shfl_sync(~0u, acc[0], 6);
-            const float qn = __fsqrt_rn(__fadd_rn(__fadd_rn(__fadd_rn(__fmul_rn(q0, q0), __fmul_rn(q1, q1)), __fmul_rn(q2, q2)),
-                                                  __fmul_rn(q3, q3)));
-            const bool empty = t[u] <= s[u];                                 // :27-29
-#pragma unroll
-            for (int k = 0; k < NS; ++k) {
-                const int kind = ch[k].kind;
-                if (kind == CH_NONE) continue;
-                const int c = 32 * k + lane;
-                // one division per channel: by the quaternion norm (:77-87), or by the weight sum -- means and scales take
-                // 1 for an all-zero weight (:65-72), colours give 0 then (:108-109)
-                const float den = kind == CH_QUAT ? qn : ((kind == CH_MEAN && wsum == 0.0f) ? 1.0f : wsum);
-                float out = __fdiv_rn(acc[k], den);
-                if (kind == CH_QUAT && !(qn > 0.0f)) out = c == 6 ? 1.0f : 0.0f;
-                if (kind == CH_COLOR && !(wsum > 0.0f)) out = 0.0f;
-                if (kind == CH_OPAC) out = fminf(acc[k], 1.0f);                                          // :94
-                if (empty) out = 0.0f;
-                if constexpr (SEP) {
-                    if (c < 3) { if (m_means) m_means[v * 3 + c] = out; }
-                    else if (c < 7) { if (m_quats) m_quats[v * 4 + (c - 3)] = out; }
-                    else if (c < 10) { if (m_scales) m_scales[v * 3 + (c - 7)] = out; }
-                    else if (c == 10) { if (m_opac) m_opac[v] = out; }
-                    else { if (m_colors) m_colors[v * (int64_t)color_dim + (c - 11)] = out; }
-                }
-                if (packed) packed[v * OC + c] = (OutT)out;
+        const int gl = tl > sl ? cidx[sl] : -1;
+        const int nv = (int)min((int64_t)32, nclu - vb);
+        float xa[MG_UNROLL][NS], xb[MG_UNROLL][NS];
+        merge_load_group<NS>(ch, gl, 0, xa);
+        for (int j0 = 0; j0 < nv; j0 += 2 * MG_UNROLL) {                 // warp-uniform
+            const bool second = j0 + MG_UNROLL < nv;
+            if (second) merge_load_group<NS>(ch, gl, j0 + MG_UNROLL, xb);
+            merge_finish_group<OutT, NS, SEP>(ch, cidx, sl, tl, j0, vb, nclu, xa, OC, color_dim, by_opacity, m_means, m_quats,
+                                              m_scales, m_opac, m_colors, packed);
+            if (second) {
+                if (j0 + 2 * MG_UNROLL < nv) merge_load_group<NS>(ch, gl, j0 + 2 * MG_UNROLL, xa);
+                merge_finish_group<OutT, NS, SEP>(ch, cidx, sl, tl, j0 + MG_UNROLL, vb, nclu, xb, OC, color_dim, by_opacity, m_means,
+                                                  m_quats, m_scales, m_opac, m_colors, packed);
             }
         }
+        // (requesting the next block's bounds and member indices a block ahead was measured: 73 registers, no gain)
     }
 }
 
@@ -167,7 +202,7 @@ RAHT_API int raht_merge_segments(const int32_t *cluster_indices, const int32_t *
     RAHT_REQUIRE(color_dim <= 245, "raht_merge_segments: color_dim must be <= 245");
     cudaStream_t st = (cudaStream_t)stream;
     const int slots = (11 + color_dim + 31) / 32;
-    const int grid = grid_for((num_clusters + MG_UNROLL - 1) / MG_UNROLL, MG_WARPS, 6);
+    const int grid = grid_for((num_clusters + 31) / 32, MG_WARPS, 4);                  // a warp per block of 32 voxels; 4 CTAs of 64 registers per SM
     raht_count_launches(1);
     if (packed && packed_dtype == RAHT_F64)
         launch_merge<double>(slots, grid, st, cluster_indices, cluster_offsets, num_clusters, means, quats, scales, opacities,
