@@ -17,7 +17,15 @@ constexpr int QR_WARPS = QR_THREADS / 32;
 constexpr int QR_P = 128;              // positions per CTA
 constexpr int QR_PITCH = QR_P + 1;     // odd pitch: conflict-free transposition
 
-template <typename Tel>
+// A warp takes the positions j = warp, warp + 8, ... of the CTA's 128 (QR_ROWS = 16 of them).  Their rows are known up
+// front: lane i reads order[] for the i-th of them (one round trip instead of one per row), and -- NS > 0: D <= 32 NS,
+// the row held in NS registers per lane -- the rows are gathered QR_BATCH at a time before the first is quantised, so
+// a warp keeps QR_BATCH x D x 8 bytes in flight (one row at a time, the kernel moved 2.3 TB/s and was bound by the
+// order -> row round trips, not by the bandwidth).  NS = 0: any D, a row at a time.
+constexpr int QR_ROWS = QR_P / QR_WARPS;
+constexpr int QR_BATCH = 4;
+
+template <typename Tel, int NS>
 __global__ void __launch_bounds__(QR_THREADS)
 quant_reorder_kernel(const Tel *__restrict__ T, int64_t n, int D, const int64_t *__restrict__ order,
                      const double *__restrict__ steps, int32_t *__restrict__ q, int64_t ld, int32_t *status)
@@ -28,17 +36,55 @@ quant_reorder_kernel(const Tel *__restrict__ T, int64_t n, int D, const int64_t 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int64_t p0 = (int64_t)blockIdx.x * QR_P;
     const int np = (int)min((int64_t)QR_P, n - p0);
+    int64_t my_row = -1;                                     // row of the warp's lane-th position
+    if (lane < QR_ROWS && warp + QR_WARPS * lane < np) {
+        const int64_t p = p0 + warp + QR_WARPS * lane;
+        my_row = order ? order[p] : p;
+    }
     for (int c = tid; c < D; c += QR_THREADS) s_step[c] = steps[c];
     __syncthreads();
     bool ovf = false;
-    for (int j = warp; j < np; j += QR_WARPS) {
-        const int64_t row = order ? order[p0 + j] : (p0 + j);
-        const Tel *src = T + (size_t)row * D;
-        for (int c = lane; c < D; c += 32) {
-            double v = (double)src[c];
-            double qq = floor(__dadd_rn(__ddiv_rn(v, s_step[c]), 0.5));       // encode_3dgs.py:204
-            ovf |= !(qq >= -2147483648.0 && qq <= 2147483647.0);
-            s_q[c * QR_PITCH + j] = (int32_t)qq;                              // :215 .to(torch.int32)
+    if constexpr (NS > 0) {
+        double st[NS];
+#pragma unroll
+        for (int k = 0; k < NS; ++k) st[k] = lane + 32 * k < D ? s_step[lane + 32 * k] : 1.0;
+#pragma unroll
+        for (int i0 = 0; i0 < QR_ROWS; i0 += QR_BATCH) {
+            Tel v[QR_BATCH][NS];
+#pragma unroll
+            for (int r = 0; r < QR_BATCH; ++r) {
+                const int64_t row = __shfl_sync(~0u, my_row, i0 + r);
+#pragma unroll
+                for (int k = 0; k < NS; ++k)
+                    if (row >= 0 && lane + 32 * k < D) v[r][k] = T[(size_t)row * D + lane + 32 * k];
+            }
+#pragma unroll
+            for (int r = 0; r < QR_BATCH; ++r) {
+                const int j = warp + QR_WARPS * (i0 + r);
+                if (j >= np) continue;                                                    // warp-uniform
+#pragma unroll
+                for (int k = 0; k < NS; ++k) {
+                    const int c = lane + 32 * k;
+                    if (c < D) {
+                        double qq = floor(__dadd_rn(__ddiv_rn((double)v[r][k], st[k]), 0.5));     // encode_3dgs.py:204
+                        ovf |= !(qq >= -2147483648.0 && qq <= 2147483647.0);
+                        s_q[c * QR_PITCH + j] = (int32_t)qq;                              // :215 .to(torch.int32)
+                    }
+                }
+            }
+        }
+    } else {
+        for (int i = 0; i < QR_ROWS; ++i) {
+            const int j = warp + QR_WARPS * i;
+            const int64_t row = __shfl_sync(~0u, my_row, i);
+            if (j >= np) continue;
+            const Tel *src = T + (size_t)row * D;
+            for (int c = lane; c < D; c += 32) {
+                double v = (double)src[c];
+                double qq = floor(__dadd_rn(__ddiv_rn(v, s_step[c]), 0.5));
+                ovf |= !(qq >= -2147483648.0 && qq <= 2147483647.0);
+                s_q[c * QR_PITCH + j] = (int32_t)qq;
+            }
         }
     }
     if (__any_sync(~0u, ovf) && lane == 0 && status) atomicOr(status, RAHT_ST_INT32_OVERFLOW);
@@ -61,6 +107,11 @@ dequant_unreorder_kernel(const int32_t *__restrict__ q, int64_t ld, int64_t n, i
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int64_t p0 = (int64_t)blockIdx.x * QR_P;
     const int np = (int)min((int64_t)QR_P, n - p0);
+    int64_t my_row = -1;                                     // row of the warp's lane-th position (one round trip for all 16)
+    if (lane < QR_ROWS && warp + QR_WARPS * lane < np) {
+        const int64_t p = p0 + warp + QR_WARPS * lane;
+        my_row = order ? order[p] : p;
+    }
     for (int c = tid; c < D; c += QR_THREADS) s_step[c] = steps[c];
     const int total = D * QR_P;
     for (int i = tid; i < total; i += QR_THREADS) {
@@ -68,8 +119,10 @@ dequant_unreorder_kernel(const int32_t *__restrict__ q, int64_t ld, int64_t n, i
         if (j < np) s_q[c * QR_PITCH + j] = q[(size_t)c * ld + p0 + j];
     }
     __syncthreads();
-    for (int j = warp; j < np; j += QR_WARPS) {
-        const int64_t row = order ? order[p0 + j] : (p0 + j);
+    for (int i = 0; i < QR_ROWS; ++i) {
+        const int j = warp + QR_WARPS * i;
+        const int64_t row = __shfl_sync(~0u, my_row, i);
+        if (j >= np) continue;                                                    // warp-uniform
         Tel *dst = T + (size_t)row * D;
         for (int c = lane; c < D; c += 32)
             dst[c] = (Tel)__dmul_rn((double)s_q[c * QR_PITCH + j], s_step[c]);    // encode_3dgs.py:261
@@ -191,11 +244,13 @@ RAHT_API int raht_quant_reorder(const void *T, int t_dtype, int64_t n, int D, co
     unsigned grid = (unsigned)((n + QR_P - 1) / QR_P);
     raht_count_launches(1);
     if (t_dtype == RAHT_F64) {
-        RAHT_CUDA(cudaFuncSetAttribute(quant_reorder_kernel<double>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        quant_reorder_kernel<double><<<grid, QR_THREADS, smem, st>>>((const double *)T, n, D, order, steps, q, ld, status);
+        auto kern = D <= 32 ? quant_reorder_kernel<double, 1> : D <= 64 ? quant_reorder_kernel<double, 2> : quant_reorder_kernel<double, 0>;
+        RAHT_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        kern<<<grid, QR_THREADS, smem, st>>>((const double *)T, n, D, order, steps, q, ld, status);
     } else if (t_dtype == RAHT_F32) {
-        RAHT_CUDA(cudaFuncSetAttribute(quant_reorder_kernel<float>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        quant_reorder_kernel<float><<<grid, QR_THREADS, smem, st>>>((const float *)T, n, D, order, steps, q, ld, status);
+        auto kern = D <= 32 ? quant_reorder_kernel<float, 1> : D <= 64 ? quant_reorder_kernel<float, 2> : quant_reorder_kernel<float, 0>;
+        RAHT_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        kern<<<grid, QR_THREADS, smem, st>>>((const float *)T, n, D, order, steps, q, ld, status);
     } else {
         raht_set_error("raht_quant_reorder: bad dtype");
         return RAHT_E_INVALID;
