@@ -247,7 +247,7 @@ STAGE_KERNELS = {
     "merge": [("merge_kernel<float, 2, 0>", 1)],
     "raht": [("transform_stage0_kernel<float, double, 59, 1, 0>", 1), ("transform_upper_kernel<double, 1>", 5)],
     "iraht": [("transform_stage0_kernel<double, double, 59, 0, 0>", 1), ("transform_upper_kernel<double, 0>", 5)],
-    "quant_reorder": [("quant_reorder_kernel<double>", 1)],
+    "quant_reorder": [("quant_reorder_kernel<double, 2>", 1)],
     "dequant_unreorder": [("dequant_unreorder_kernel<double>", 1)],
 }
 
