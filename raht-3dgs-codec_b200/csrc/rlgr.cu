@@ -235,9 +235,16 @@ template <int NC> __device__ __forceinline__ void count_lane(const LaneBlock &B,
 #pragma unroll
     for (int c = 0; c < NC; ++c) { kP[c] = s_io[c].kP; kRP[c] = s_io[c].kRP; bits[c] = 0; quirk[c] = false; }
     const int units = (B.cnt + EV_GROUP - 1) / EV_GROUP;
+    // the units of a block are at fixed addresses: two of them are requested ahead of the one being coded (the coder's
+    // state chain is long, but shorter than a round trip to the event store)
+    uint4 a1, b1, a2, b2;
+    a1 = b1 = a2 = b2 = make_uint4(0u, 0u, 0u, 0u);
+    if (units > 0) { a1 = __ldg(B.base + lane * 2); b1 = __ldg(B.base + lane * 2 + 1); }
+    if (units > 1) { a2 = __ldg(B.base + (32 + lane) * 2); b2 = __ldg(B.base + (32 + lane) * 2 + 1); }
     for (int j = 0; j < units; ++j) {
-        const uint4 a = __ldg(B.base + (j * 32 + lane) * 2);
-        const uint4 b = __ldg(B.base + (j * 32 + lane) * 2 + 1);
+        const uint4 a = a1, b = b1;
+        a1 = a2; b1 = b2;
+        if (j + 2 < units) { a2 = __ldg(B.base + ((j + 2) * 32 + lane) * 2); b2 = __ldg(B.base + ((j + 2) * 32 + lane) * 2 + 1); }
         const uint32_t g[4] = {a.x, a.z, b.x, b.z}, u[4] = {a.y, a.w, b.y, b.w};
 #pragma unroll
         for (int t = 0; t < 4; ++t) {
@@ -1039,9 +1046,14 @@ __global__ void __launch_bounds__(32 * SPEC_WARPS) rlgr_emit_kernel(Geometry G, 
     int64_t pos = -1;                                      // symbol index of the previous event
     bool quirk = false;
     const int units = (B.cnt + EV_GROUP - 1) / EV_GROUP;
+    uint4 a1, b1, a2, b2;                                   // two units requested ahead, as in count_lane
+    a1 = b1 = a2 = b2 = make_uint4(0u, 0u, 0u, 0u);
+    if (units > 0) { a1 = __ldg(B.base + lane * 2); b1 = __ldg(B.base + lane * 2 + 1); }
+    if (units > 1) { a2 = __ldg(B.base + (32 + lane) * 2); b2 = __ldg(B.base + (32 + lane) * 2 + 1); }
     for (int j = 0; j < units; ++j) {
-        const uint4 a = __ldg(B.base + (j * 32 + lane) * 2);
-        const uint4 b = __ldg(B.base + (j * 32 + lane) * 2 + 1);
+        const uint4 a = a1, b = b1;
+        a1 = a2; b1 = b2;
+        if (j + 2 < units) { a2 = __ldg(B.base + ((j + 2) * 32 + lane) * 2); b2 = __ldg(B.base + ((j + 2) * 32 + lane) * 2 + 1); }
         const uint32_t g[4] = {a.x, a.z, b.x, b.z}, u[4] = {a.y, a.w, b.y, b.w};
         if (j == 0) pos = (int64_t)blockpos[(size_t)ch * G.nsb + w * CHUNK_LANES - 1 + lane] - (int64_t)g[0] - 1;
 #pragma unroll
