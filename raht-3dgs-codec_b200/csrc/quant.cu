@@ -114,9 +114,21 @@ dequant_unreorder_kernel(const int32_t *__restrict__ q, int64_t ld, int64_t n, i
     }
     for (int c = tid; c < D; c += QR_THREADS) s_step[c] = steps[c];
     const int total = D * QR_P;
-    for (int i = tid; i < total; i += QR_THREADS) {
-        int c = i / QR_P, j = i - c * QR_P;
-        if (j < np) s_q[c * QR_PITCH + j] = q[(size_t)c * ld + p0 + j];
+    constexpr int LD_BATCH = 8;                              // symbol loads in flight per thread
+    for (int i0 = tid; i0 < total; i0 += LD_BATCH * QR_THREADS) {
+        int32_t v[LD_BATCH];
+#pragma unroll
+        for (int u = 0; u < LD_BATCH; ++u) {
+            const int i = i0 + u * QR_THREADS;
+            const int c = i / QR_P, j = i - c * QR_P;
+            if (i < total && j < np) v[u] = q[(size_t)c * ld + p0 + j];
+        }
+#pragma unroll
+        for (int u = 0; u < LD_BATCH; ++u) {
+            const int i = i0 + u * QR_THREADS;
+            const int c = i / QR_P, j = i - c * QR_P;
+            if (i < total && j < np) s_q[c * QR_PITCH + j] = v[u];
+        }
     }
     __syncthreads();
     for (int i = 0; i < QR_ROWS; ++i) {
