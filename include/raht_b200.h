@@ -29,7 +29,7 @@
 extern "C" {
 #endif
 
-#define RAHT_B200_ABI_VERSION 9
+#define RAHT_B200_ABI_VERSION 10
 
 enum {
     RAHT_OK = 0,
@@ -229,9 +229,14 @@ int raht_dequant_inverse(const raht_plan *plan, const int32_t *q, int64_t ld, co
  * +0.5)), :210 (index_select(order_RAGFT)), :215-222 (int32 cast, per-channel sequences) and the
  * mirror :255-268.  steps: D doubles (device) -- one per channel (encode_3dgs_debug.py:376-381);
  * q is channel-major int32: q[c*ld + p] = quantised T[order[p], c].  order == NULL = identity.
+ * flags: 0 = true division, what torch computes on the CPU (the parity convention);
+ * RAHT_QUANT_RECIPROCAL = T * (1/step), what torch computes on CUDA for tensor / python_scalar (the
+ * reference's production device, encode_3dgs.py:22,204); identical for power-of-two steps.
  * ------------------------------------------------------------------------------------------------ */
+#define RAHT_QUANT_RECIPROCAL 1
 int raht_quant_reorder(const void *T, int t_dtype, int64_t n, int D, const int64_t *order,
-                       const double *steps, int32_t *q, int64_t ld, int32_t *status, void *stream);
+                       const double *steps, int32_t *q, int64_t ld, int32_t *status, int flags,
+                       void *stream);
 int raht_dequant_unreorder(const int32_t *q, int64_t ld, int64_t n, int D, const int64_t *order,
                            const double *steps, void *T, int t_dtype, void *stream);
 /* row-major variants without marshalling: Coeff_enc = floor(T/step+0.5) (fp64 out), and q*step */

@@ -288,3 +288,29 @@ def per_attribute_steps(Coeff, attr_ranges, importance_weights, total_levels_bud
         per[name] = (float(step), levels, float(range_attr))
         enc[:, a:b] = np.floor(Coeff[:, a:b] / step + 0.5)
     return per, enc
+
+
+# ---- the reference's own merge kernel (cuda/merge_cluster.cu, compiled in place for sm_100 by oracle/Makefile) ----------
+def ref_merge_path(kind="ieee"):
+    """kind: 'ieee' (--fmad=false), 'default' (nvcc defaults: FMA contraction), 'fast' (--use_fast_math, as shipped)."""
+    return os.path.join(_HERE, "_ref", f"libmerge_ref_{kind}.so")
+
+
+def ref_merge_available(kind="ieee"):
+    return os.path.exists(ref_merge_path(kind))
+
+
+_merge_libs = {}
+
+
+def ref_merge_launch(kind, cidx_ptr, coff_ptr, nclu, means_ptr, quats_ptr, scales_ptr, opac_ptr, colors_ptr, color_dim, by_opacity,
+                     out_ptrs, stream_ptr=0):
+    """Launch merge_weighted_mean_kernel on DEVICE pointers (ints, e.g. tensor.data_ptr()); the five outputs must be
+    zero-filled by the caller (merge_cluster_wrapper.cu:64-69).  Returns the CUDA error code of the launch."""
+    lib_ = _merge_libs.get(kind)
+    if lib_ is None:
+        lib_ = _merge_libs[kind] = C.CDLL(ref_merge_path(kind))
+        lib_.ref_merge_launch.restype = C.c_int
+        lib_.ref_merge_launch.argtypes = [C.c_void_p, C.c_void_p, C.c_int] + [C.c_void_p] * 5 + [C.c_int, C.c_int] + [C.c_void_p] * 6
+    return lib_.ref_merge_launch(cidx_ptr, coff_ptr, int(nclu), means_ptr, quats_ptr, scales_ptr, opac_ptr, colors_ptr, int(color_dim),
+                                 1 if by_opacity else 0, *out_ptrs, stream_ptr)

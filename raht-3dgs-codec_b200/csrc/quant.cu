@@ -25,7 +25,10 @@ constexpr int QR_PITCH = QR_P + 1;     // odd pitch: conflict-free transposition
 constexpr int QR_ROWS = QR_P / QR_WARPS;
 constexpr int QR_BATCH = 4;
 
-template <typename Tel, int NS>
+// RECIP: multiply by the correctly rounded reciprocal of the step instead of dividing -- what torch evaluates on CUDA for
+// `tensor / python_scalar` (ATen div_true_kernel_cuda: a CPU-scalar divisor becomes a multiplication by 1 / b), i.e. the
+// reference's floor(Coeff / step + 0.5) on its production device; identical for power-of-two steps.
+template <typename Tel, int NS, int RECIP>
 __global__ void __launch_bounds__(QR_THREADS)
 quant_reorder_kernel(const Tel *__restrict__ T, int64_t n, int D, const int64_t *__restrict__ order,
                      const double *__restrict__ steps, int32_t *__restrict__ q, int64_t ld, int32_t *status)
@@ -41,7 +44,7 @@ quant_reorder_kernel(const Tel *__restrict__ T, int64_t n, int D, const int64_t 
         const int64_t p = p0 + warp + QR_WARPS * lane;
         my_row = order ? order[p] : p;
     }
-    for (int c = tid; c < D; c += QR_THREADS) s_step[c] = steps[c];
+    for (int c = tid; c < D; c += QR_THREADS) s_step[c] = RECIP ? __ddiv_rn(1.0, steps[c]) : steps[c];
     __syncthreads();
     bool ovf = false;
     if constexpr (NS > 0) {
@@ -66,7 +69,8 @@ quant_reorder_kernel(const Tel *__restrict__ T, int64_t n, int D, const int64_t 
                 for (int k = 0; k < NS; ++k) {
                     const int c = lane + 32 * k;
                     if (c < D) {
-                        double qq = floor(__dadd_rn(__ddiv_rn((double)v[r][k], st[k]), 0.5));     // encode_3dgs.py:204
+                        const double sc = RECIP ? __dmul_rn((double)v[r][k], st[k]) : __ddiv_rn((double)v[r][k], st[k]);
+                        double qq = floor(__dadd_rn(sc, 0.5));                                    // encode_3dgs.py:204
                         ovf |= !(qq >= -2147483648.0 && qq <= 2147483647.0);
                         s_q[c * QR_PITCH + j] = (int32_t)qq;                              // :215 .to(torch.int32)
                     }
@@ -81,7 +85,7 @@ quant_reorder_kernel(const Tel *__restrict__ T, int64_t n, int D, const int64_t 
             const Tel *src = T + (size_t)row * D;
             for (int c = lane; c < D; c += 32) {
                 double v = (double)src[c];
-                double qq = floor(__dadd_rn(__ddiv_rn(v, s_step[c]), 0.5));
+                double qq = floor(__dadd_rn(RECIP ? __dmul_rn(v, s_step[c]) : __ddiv_rn(v, s_step[c]), 0.5));
                 ovf |= !(qq >= -2147483648.0 && qq <= 2147483647.0);
                 s_q[c * QR_PITCH + j] = (int32_t)qq;
             }
@@ -244,29 +248,41 @@ size_t qr_smem_bytes(int D) { return ((size_t)D * QR_PITCH + 1) * 4 + (size_t)D 
 
 }  // namespace
 
+template <typename Tel, int RECIP>
+static int quant_reorder_launch(const Tel *T, int64_t n, int D, const int64_t *order, const double *steps, int32_t *q, int64_t ld,
+                                int32_t *status, size_t smem, cudaStream_t st)
+{
+    unsigned grid = (unsigned)((n + QR_P - 1) / QR_P);
+    auto kern = D <= 32 ? quant_reorder_kernel<Tel, 1, RECIP> : D <= 64 ? quant_reorder_kernel<Tel, 2, RECIP> : quant_reorder_kernel<Tel, 0, RECIP>;
+    RAHT_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    kern<<<grid, QR_THREADS, smem, st>>>(T, n, D, order, steps, q, ld, status);
+    return RAHT_OK;
+}
+
 RAHT_API int raht_quant_reorder(const void *T, int t_dtype, int64_t n, int D, const int64_t *order, const double *steps,
-                                int32_t *q, int64_t ld, int32_t *status, void *stream)
+                                int32_t *q, int64_t ld, int32_t *status, int flags, void *stream)
 {
     RAHT_REQUIRE(n >= 0 && D >= 1 && ld >= n && steps, "raht_quant_reorder: bad arguments");
+    RAHT_REQUIRE((flags & ~RAHT_QUANT_RECIPROCAL) == 0, "raht_quant_reorder: unknown flags");
     if (n == 0) return RAHT_OK;
     RAHT_REQUIRE(T && q, "raht_quant_reorder: null pointer");
     size_t smem = qr_smem_bytes(D);
     RAHT_REQUIRE(smem <= 227 * 1024, "raht_quant_reorder: D too large");
     cudaStream_t st = (cudaStream_t)stream;
-    unsigned grid = (unsigned)((n + QR_P - 1) / QR_P);
+    const bool recip = (flags & RAHT_QUANT_RECIPROCAL) != 0;
     raht_count_launches(1);
+    int rc;
     if (t_dtype == RAHT_F64) {
-        auto kern = D <= 32 ? quant_reorder_kernel<double, 1> : D <= 64 ? quant_reorder_kernel<double, 2> : quant_reorder_kernel<double, 0>;
-        RAHT_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        kern<<<grid, QR_THREADS, smem, st>>>((const double *)T, n, D, order, steps, q, ld, status);
+        rc = recip ? quant_reorder_launch<double, 1>((const double *)T, n, D, order, steps, q, ld, status, smem, st)
+                   : quant_reorder_launch<double, 0>((const double *)T, n, D, order, steps, q, ld, status, smem, st);
     } else if (t_dtype == RAHT_F32) {
-        auto kern = D <= 32 ? quant_reorder_kernel<float, 1> : D <= 64 ? quant_reorder_kernel<float, 2> : quant_reorder_kernel<float, 0>;
-        RAHT_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        kern<<<grid, QR_THREADS, smem, st>>>((const float *)T, n, D, order, steps, q, ld, status);
+        rc = recip ? quant_reorder_launch<float, 1>((const float *)T, n, D, order, steps, q, ld, status, smem, st)
+                   : quant_reorder_launch<float, 0>((const float *)T, n, D, order, steps, q, ld, status, smem, st);
     } else {
         raht_set_error("raht_quant_reorder: bad dtype");
         return RAHT_E_INVALID;
     }
+    if (rc != RAHT_OK) return rc;
     RAHT_LAUNCH_CHECK();
     return RAHT_OK;
 }

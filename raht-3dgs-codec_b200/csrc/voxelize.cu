@@ -33,14 +33,16 @@ __host__ __device__ __forceinline__ uint64_t morton3(uint64_t x, uint64_t y, uin
 }
 
 // ---- bounds -----------------------------------------------------------------------------------
+// (the branch is on the SIGN BIT, not on v >= 0: -0.0f must take the path of the negative values, where its pattern
+// 0x80000000 orders correctly; as a signed int it would be INT_MIN and win every minimum / lose every maximum)
 __device__ __forceinline__ void atomic_min_f32(float *addr, float v)
 {
-    if (v >= 0.0f) atomicMin((int *)addr, __float_as_int(v));
+    if (__float_as_int(v) >= 0) atomicMin((int *)addr, __float_as_int(v));
     else atomicMax((unsigned *)addr, __float_as_uint(v));
 }
 __device__ __forceinline__ void atomic_max_f32(float *addr, float v)
 {
-    if (v >= 0.0f) atomicMax((int *)addr, __float_as_int(v));
+    if (__float_as_int(v) >= 0) atomicMax((int *)addr, __float_as_int(v));
     else atomicMin((unsigned *)addr, __float_as_uint(v));
 }
 

@@ -60,7 +60,7 @@ SIGNATURES = {
     "raht_inverse": (_i, [_p, _p, _i, _i, _p, _i, _p]),
     "raht_forward_quant": (_i, [_p, _p, _i, _i, _p, _i, _p, _p, _p, _i64, _p, _i, _p]),
     "raht_dequant_inverse": (_i, [_p, _p, _i64, _p, _p, _i, _p, _i, _p, _i, _p]),
-    "raht_quant_reorder": (_i, [_p, _i, _i64, _i, _p, _p, _p, _i64, _p, _p]),
+    "raht_quant_reorder": (_i, [_p, _i, _i64, _i, _p, _p, _p, _i64, _p, _i, _p]),
     "raht_dequant_unreorder": (_i, [_p, _i64, _i64, _i, _p, _p, _p, _i, _p]),
     "raht_quantize_f64": (_i, [_p, _i64, _d, _p, _p]),
     "raht_dequantize_f64": (_i, [_p, _i64, _d, _p, _p]),
@@ -99,8 +99,15 @@ def check(rc: int, what: str = ""):
 
 
 def ptr(t):
-    """Device pointer of a tensor (None -> NULL)."""
-    return None if t is None else C.c_void_p(t.data_ptr())
+    """Device pointer of a tensor (None -> NULL).  The library launches on the CURRENT device's current stream (stream()
+    below; it never calls cudaSetDevice), so a tensor of another GPU is refused here instead of faulting in a kernel:
+    multi-GPU processes select the device first (`torch.cuda.set_device` / `with torch.cuda.device(d)`)."""
+    if t is None:
+        return None
+    if t.is_cuda and t.device.index != torch.cuda.current_device():
+        raise RuntimeError(f"tensor on {t.device} but the current CUDA device is cuda:{torch.cuda.current_device()}: "
+                           "select the device (torch.cuda.set_device / torch.cuda.device) before calling raht_b200")
+    return C.c_void_p(t.data_ptr())
 
 
 def stream():

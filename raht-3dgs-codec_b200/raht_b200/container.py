@@ -116,6 +116,10 @@ def pack(enc: EncodedScene, with_index=True) -> torch.Tensor:
             b = s.sync_index.reshape(-1).view(torch.uint8)
             out[o:o + b.numel()].copy_(b)
             o += b.numel()
+    bits = int(L.read_host(status)[0][0])                   # raht_streams_pack reports a destination that is too small here
+    ops.raise_for_status(bits)
+    if bits & L.ST_STREAM_OVERFLOW:
+        raise RuntimeError("container.pack: stream sizes changed between the size read and the pack (internal error)")
     return out
 
 
@@ -175,6 +179,19 @@ def unpack(container, device=None) -> EncodedScene:
         raise ValueError("container: truncated header")
     h = parse_header((head_src if head_src is not None else container)[:hb].cpu().numpy().tobytes())
     D, nvox = h["D"], h["nvox"]
+    # the header is untrusted input: every size the kernels will index with is checked against the buffer first
+    if not (1 <= h["J"] <= 21) or not (1 <= D <= 4096) or nvox < 0 or nvox > (1 << 40):
+        raise ValueError("container: J, D or nvox out of range")
+    if len(h["attr_bytes"]) != D or len(h["geo_bytes"]) != N_GEO:
+        raise ValueError("container: malformed stream table")
+    if any(s < 0 or s > total for s in h["geo_bytes"] + h["attr_bytes"]) or any(not (st > 0.0) for st in h["steps"]):
+        raise ValueError("container: stream size or quantisation step out of range")
+    if h["flags"] & FLAG_INDEX:
+        want = int(lib.raht_rlgr_sync_entries(nvox))
+        if h["geo_entries"] != want or h["attr_entries"] != want:
+            raise ValueError("container: sync index does not match the number of voxels")
+    elif h["geo_entries"] or h["attr_entries"]:
+        raise ValueError("container: index entries without the index flag")
     geo_body, attr_body = sum(_pad8(s) for s in h["geo_bytes"]), sum(_pad8(s) for s in h["attr_bytes"])
     index_bytes = (N_GEO * h["geo_entries"] + D * h["attr_entries"]) * 8
     if hb + geo_body + attr_body + index_bytes > total:

@@ -342,9 +342,14 @@ def _steps_tensor(step, D, device):
     return torch.tensor([float(x) for x in step], dtype=torch.float64, device=device)
 
 
-def quant_reorder(T: torch.Tensor, order, step, check_overflow=True, status=None) -> torch.Tensor:
+def quant_reorder(T: torch.Tensor, order, step, check_overflow=True, status=None, division="exact") -> torch.Tensor:
     """q[c, p] = int32(floor(T[order[p], c] / step_c + 0.5)), channel-major (D, n).
-    status: shared device status word (no synchronisation here; the caller checks it later)."""
+    status: shared device status word (no synchronisation here; the caller checks it later).
+    division: "exact" = true division (torch on the CPU: the parity convention); "reciprocal" = T * (1 / step), what
+    torch evaluates on CUDA for `Coeff / step` with a Python scalar (encode_3dgs.py:204 on the reference's production
+    device) -- the two differ in a handful of symbols when the step is not a power of two."""
+    if division not in ("exact", "reciprocal"):
+        raise ValueError(f"quant_reorder: unknown division mode {division!r}")
     n, D = T.shape
     dev = T.device
     T = T.contiguous()
@@ -354,7 +359,7 @@ def quant_reorder(T: torch.Tensor, order, step, check_overflow=True, status=None
     deferred = status is not None
     status = _status_word(dev) if status is None else status
     check(lib.raht_quant_reorder(ptr(T), L.dtype_tag(T.dtype), n, D, ptr(order), ptr(steps), ptr(q), ld, ptr(status),
-                                 stream()), "raht_quant_reorder")
+                                 1 if division == "reciprocal" else 0, stream()), "raht_quant_reorder")
     if check_overflow and not deferred and int(L.read_host(status)[0][0]) & L.ST_INT32_OVERFLOW:
         raise OverflowError("quantised coefficient does not fit int32 (encode_3dgs.py:215 would truncate)")
     return q[:, :n]

@@ -30,7 +30,9 @@ def test_library_exports_every_declared_symbol():
 def test_ctypes_signatures_cover_header():
     from raht_b200 import _lib
     assert sorted(_lib.SIGNATURES) == declared_symbols()
-    assert _lib.lib.raht_abi_version() == 9
+    import re
+    header = open(os.path.join(ROOT, "include", "raht_b200.h")).read()
+    assert _lib.lib.raht_abi_version() == int(re.search(r"#define RAHT_B200_ABI_VERSION (\d+)", header).group(1)) == 10
 
 
 def test_argument_validation_without_gpu():
