@@ -7,13 +7,16 @@ One "step" = one pass of the hot path over one synthetic scene:
     decode: RAHT_param from the voxel keys -> RLGR decode -> dequantise + inverse reorder -> iRAHT
 `value`  : Gaussians/s with the scene already resident in HBM (CUDA events, max over ranks).
 `e2e`    : the same through the public Python API from pinned HOST buffers, H2D of the scene and D2H
-           of the bitstreams and of the decoded attributes inside the timed region.
+           of the bitstreams (and, `with_attributes`, of the decoded attributes) inside the timed region.
 `roofline`: the dominant kernel family of the step, algorithmic bytes / measured duration vs the
            measured HBM peak of MEASURED_PEAKS.json.
-`cpu_baseline` / --impl reference: the CPU restatement of the reference path (oracle/, plus the
-           reference's own RLGR coder from oracle/_ref when built) on the host cores.
-N > 1 ranks (torchrun): every rank codes its own scene (scene-per-GPU, BASELINE config 5) -- weak scaling,
-no data-path collective.
+`parity` : the GPU bitstreams / keys / decoded attributes of the timed scene compared with the CPU checker
+           (the cpu_baseline leg, which runs the whole scene anyway) -- the bench checks what it times.
+`cpu_baseline` / --impl reference: the reference's CPU path on the host cores (see run_reference).
+Sub-records of the N = 1 line: `c3` (BASELINE configs[2]: 6 M Gaussians, depth 16) and `sparse` (C2 at a coarse step).
+N > 1 ranks (torchrun): every rank codes its own scene (scene-per-GPU replicas, weak scaling, no data-path collective)
+for the headline; the line additionally carries `sharded` (BASELINE configs[3]: ONE 50 M-Gaussian scene over all
+ranks by Morton prefix, strong scaling, NCCL) and `c5` (BASELINE configs[4]: 64 scenes x 2 M, depth 14, streamed).
 """
 import argparse
 import json
@@ -24,22 +27,25 @@ import threading
 import time
 
 ROOT = os.path.dirname(os.path.abspath(__file__))
-for p in (ROOT, os.path.join(ROOT, "raht-3dgs-codec_b200"), os.path.join(ROOT, "tests")):
+for p in (ROOT, os.path.join(ROOT, "raht-3dgs-codec_b200")):
     if p not in sys.path:
         sys.path.insert(0, p)
 
 import numpy as np  # noqa: E402
 
 WORKLOADS = {
-    # name: (n_gaussians, depth, description)          BASELINE.json configs[1] / configs[2]
-    "c2": (1_000_000, 12, "3DGS scene 1M Gaussians, 59 channels, depth 12 (BASELINE configs[1])"),
-    "c3": (6_000_000, 16, "3DGS scene 6M Gaussians, 59 channels, depth 16 (BASELINE configs[2])"),
-    "tiny": (50_000, 10, "smoke-sized scene"),
-    # one scene sharded over the ranks by Morton prefix (raht_b200/sharded.py); --n overrides the 50 M
-    "c4": (50_000_000, 18, "50M-Gaussian synthetic scene, depth 18, Morton-prefix sharding (BASELINE configs[3])"),
+    # name: (n_gaussians, depth, seed, description)          BASELINE.json configs[1] / configs[2]
+    "c2": (1_000_000, 12, 2001, "3DGS scene 1M Gaussians, 59 channels, depth 12 (BASELINE configs[1])"),
+    "c3": (6_000_000, 16, 3001, "3DGS scene 6M Gaussians, 59 channels, depth 16 (BASELINE configs[2])"),
+    "tiny": (50_000, 10, 2001, "smoke-sized scene"),
+    # one scene sharded over the ranks by Morton prefix (raht_b200/sharded.py); --num-gaussians overrides the 50 M
+    "c4": (50_000_000, 18, 4001, "50M-Gaussian synthetic scene, depth 18, Morton-prefix sharding (BASELINE configs[3])"),
+    "c5": (2_000_000, 14, 5001, "64 scenes x 2M Gaussians, depth 14, one scene stream per GPU (BASELINE configs[4])"),
 }
-STEP = 1.0 / 64          # uniform quantisation step applied to all 59 channels
+STEP = 1.0 / 64          # uniform quantisation step applied to all 59 channels (dense regime: ~300 bits per voxel)
+SPARSE_STEP = 0.25       # the coarse step of the `sparse` sub-record (most channels mostly zero: RLGR run mode, tables)
 D = 59
+METRIC = "Gaussians/s full RAHT encode+decode (59 ch)"
 
 
 def load_peaks():
@@ -50,7 +56,7 @@ def load_peaks():
 
 
 # ---------------------------------------------------------------------------------------------------
-# CPU path (oracle): used for cpu_baseline and for --impl reference
+# CPU paths: used for cpu_baseline / parity and for --impl reference.  The only places that load oracle/.
 # ---------------------------------------------------------------------------------------------------
 def host_cores():
     try:
@@ -59,8 +65,8 @@ def host_cores():
         return max(1, os.cpu_count() or 1)
 
 
-def cpu_pipeline(scene, J, step, use_ref_rlgr):
-    """Full encode + decode on the host with the CPU restatement of the reference (oracle/)."""
+def cpu_pipeline(scene, J, step, use_ref_rlgr, want_streams=False):
+    """Full encode + decode on the host with the CPU restatement of the reference (oracle/raht_oracle.c, OpenMP)."""
     from oracle import oracle_ctypes as orc
     orc.set_num_threads(host_cores())                     # (torchrun exports OMP_NUM_THREADS=1: the CPU arm gets every core anyway)
     means, quats, scales, opac, colors = scene
@@ -83,25 +89,77 @@ def cpu_pipeline(scene, J, step, use_ref_rlgr):
             streams = list(pool.map(lambda c: orc.ref_rlgr_encode(q[c].astype(np.int64), 1)[0], range(q.shape[0])))
             qd = np.stack(list(pool.map(lambda c: orc.ref_rlgr_decode(streams[c], nvox, 1)[0], range(q.shape[0])))).astype(np.int32)
     else:
-        _, out, cap, nb = orc.rlgr_encode_channels(q, 1)
+        streams, out, cap, nb = orc.rlgr_encode_channels(q, 1)
         qd = orc.rlgr_decode_channels(out, cap, nb, nvox, q.shape[0], 1)
     # decoder side: tree again from the keys, dequantise, inverse reorder, iRAHT
     t2 = orc.Tree(keys, J)
     inv = np.argsort(t2.order(), kind="stable")
     Tdec = orc.dequantize(qd.T.astype(np.float64), step)[inv]
     Crec = t2.inverse(Tdec)
+    if want_streams:
+        return nvox, Crec, keys, list(streams)
     return nvox, Crec
 
 
-def time_cpu(scene, J, step, sample_n, reps, use_ref_rlgr):
-    sample = tuple(a[:sample_n] for a in scene)
-    best = None
-    for _ in range(reps):
-        t0 = time.perf_counter()
-        cpu_pipeline(sample, J, step, use_ref_rlgr)
-        dt = time.perf_counter() - t0
-        best = dt if best is None else min(best, dt)
-    return sample_n / best, best
+def reference_python_pipeline(scene, J, step, stage_s=None):
+    """The REFERENCE's own CPU path, in the call order of its drivers, on torch-CPU with every host core:
+        test_voxelize_3dgs.py:203-247   voxelize_pc_batched -> cluster arrays -> merge
+        encode_3dgs.py:144-276          RAHT_param_reorder_fast -> RAHT2_optimized -> floor(Coeff/step+0.5) ->
+                                        index_select(order_RAGFT) -> int32 -> rlgr per channel -> decode -> * step ->
+                                        argsort(order) gather -> inverse_RAHT_optimized
+    The Python operators are the reference's files (oracle/refpy.py: /root/reference/python, else the copy staged
+    under oracle/_ref/python); the entropy coder is the reference's object code (oracle/_ref/librlgr_ref.so).  Two
+    deviations, both in the reference's FAVOUR: the merge, which the reference only has as a CUDA kernel, is the C
+    restatement with OpenMP; and the channels are coded one per host thread through a ctypes veneer instead of one
+    after the other through Python lists (encode_3dgs.py:218-247: 9.9 s wall for 4.5 s inside the coder)."""
+    import torch
+    from concurrent.futures import ThreadPoolExecutor
+    from oracle import oracle_ctypes as orc
+    from oracle import refpy
+    ref = refpy.load()
+    cores = host_cores()
+    torch.set_num_threads(cores)
+    orc.set_num_threads(cores)
+    means, quats, scales, opac, colors = scene
+    n = means.shape[0]
+    marks = [("start", time.perf_counter())]
+
+    def mark(name):
+        marks.append((name, time.perf_counter()))
+
+    with torch.no_grad():
+        PCvox, _, voxel_indices, _, info = ref.voxelize_pc.voxelize_pc_batched(torch.from_numpy(means), J=J, device="cpu")
+        mark("voxelize")
+        cidx = info["sort_idx"].int().numpy()
+        coff = torch.cat([voxel_indices, torch.tensor([n], dtype=voxel_indices.dtype)]).int().numpy()
+        mm, mq, ms, mo, mc = orc.merge_clusters(cidx, coff, means, quats, scales, opac, colors, True)
+        C = torch.from_numpy(np.concatenate([mm, mq, ms, mo[:, None], mc], 1)).to(torch.float64)
+        mark("merge")
+        V = PCvox[:, :3].to(torch.float64)
+        origin = torch.zeros(3, dtype=torch.float64)
+        ListC, FlagsC, weightsC, order = ref.RAHT_param.RAHT_param_reorder_fast(V, origin, 2 ** J, J)
+        mark("raht_param")
+        Coeff, _ = ref.RAHT.RAHT2_optimized(C, ListC, FlagsC, weightsC)
+        mark("raht")
+        Coeff_enc = torch.floor(Coeff / step + 0.5)
+        reordered = Coeff_enc.index_select(0, order)
+        cols = np.ascontiguousarray(reordered.to(torch.int32).numpy().T)
+        mark("quant_reorder")
+        nvox = cols.shape[1]
+        with ThreadPoolExecutor(max_workers=cores) as pool:
+            streams = list(pool.map(lambda c: orc.ref_rlgr_encode(cols[c].astype(np.int64), 1)[0], range(cols.shape[0])))
+            mark("rlgr_encode")
+            dec = list(pool.map(lambda c: orc.ref_rlgr_decode(streams[c], nvox, 1)[0], range(cols.shape[0])))
+        mark("rlgr_decode")
+        coeff_dec = torch.from_numpy(np.stack(dec, axis=1).astype(np.int32)).to(torch.float64) * step
+        coeff_dec = coeff_dec[torch.argsort(order), :]
+        mark("dequant_unreorder")
+        C_rec = ref.iRAHT.inverse_RAHT_optimized(coeff_dec, ListC, FlagsC, weightsC)
+        mark("iraht")
+    if stage_s is not None:
+        for (_, t0), (name, t1) in zip(marks[:-1], marks[1:]):
+            stage_s[name] = stage_s.get(name, 0.0) + (t1 - t0)
+    return nvox, C_rec, sum(len(b) for b in streams)
 
 
 # ---------------------------------------------------------------------------------------------------
@@ -218,6 +276,8 @@ class ClockSampler:
                 "source": "nvidia-smi"}
 
 
+
+
 def stage_bytes(nvox, n_in, payload, J):
     """Algorithmic (compulsory) bytes per stage for one step, SURVEY 8(d)."""
     passes = (3 * J + 7) // 8
@@ -247,115 +307,195 @@ STAGE_KERNELS = {
     "merge": [("merge_kernel<float, 2, 0>", 1)],
     "raht": [("transform_stage0_kernel<float, double, 59, 1, 0>", 1), ("transform_upper_kernel<double, 1>", 5)],
     "iraht": [("transform_stage0_kernel<double, double, 59, 0, 0>", 1), ("transform_upper_kernel<double, 0>", 5)],
-    "quant_reorder": [("quant_reorder_kernel<double, 2>", 1)],
+    "quant_reorder": [("quant_reorder_kernel<double, 2, 0>", 1)],
     "dequant_unreorder": [("dequant_unreorder_kernel<double>", 1)],
 }
 
 
 def stage_traffic(stage):
-    """(bytes per step or None, source file) from the newest profiles/*ncu_full*.json (scripts/ncu_full_summary.py)."""
+    """(bytes per step or None, source file) from the newest profiles/*ncu_full*.json (scripts/ncu_full_summary.py);
+    the capture's own STAGE_KERNELS table ("_stage_kernels" in the json) wins over the one above when present."""
     import glob
     import re
     files = sorted(glob.glob(os.path.join(ROOT, "profiles", "*ncu_full*.json")),
-                   key=lambda f: [int(x) for x in re.findall(r"\d+", os.path.basename(f))])      # r01 ... v8 < v11
-    if not files or stage not in STAGE_KERNELS:
+                   key=lambda f: [int(x) for x in re.findall(r"\d+", os.path.basename(f))])      # r01 ... v8 < v11 < r02
+    if not files:
         return None, None
     prof = json.load(open(files[-1]))
+    table = prof.get("_stage_kernels", STAGE_KERNELS)
+    if stage not in table:
+        return None, os.path.basename(files[-1])
     total = 0
-    for name, launches in STAGE_KERNELS[stage]:
+    for name, launches in table[stage]:
         if name not in prof:
             return None, os.path.basename(files[-1])
         total += launches * (prof[name]["dram_read_bytes"] + prof[name]["dram_write_bytes"])
     return int(total), os.path.basename(files[-1])
 
 
+def bind_rank_to_cores(local, world):
+    """Before anything is pinned: bind this rank to its own share of the host cores next to its GPU (NVML's ideal CPU set
+    for the device, intersected with what the process may use, split between the ranks that share it), so that the
+    pinned staging buffers are first-touched on that NUMA node and the ranks' host threads do not migrate over each
+    other.  Returns a short description for the JSON line.  N = 1: untouched (the CPU baseline wants every core)."""
+    if world <= 1:
+        return {"bound": False, "cores": host_cores()}
+    try:
+        allowed = sorted(os.sched_getaffinity(0))
+        pools = []
+        try:
+            import pynvml as nv
+            nv.nvmlInit()
+            words = (max(allowed) + 64) // 64
+            vis = os.environ.get("CUDA_VISIBLE_DEVICES")
+            ids = [int(x) for x in vis.split(",")] if vis and all(x.strip().isdigit() for x in vis.split(",")) else list(range(world))
+            for r in range(world):
+                h = nv.nvmlDeviceGetHandleByIndex(ids[r] if r < len(ids) else r)
+                mask = nv.nvmlDeviceGetCpuAffinity(h, words)
+                ideal = {w * 64 + b for w, word in enumerate(mask) for b in range(64) if (int(word) >> b) & 1}
+                pools.append(tuple(sorted(ideal & set(allowed))) or tuple(allowed))
+        except Exception:
+            pools = [tuple(allowed)] * world
+        mine = pools[local]
+        sharers = [r for r in range(world) if pools[r] == mine]
+        pos = sharers.index(local)
+        per = len(mine) // len(sharers)
+        share = list(mine[pos * per:(pos + 1) * per]) if per >= 2 else list(mine)
+        os.sched_setaffinity(0, share)
+        return {"bound": per >= 2, "cores": len(share), "first_core": share[0], "gpu_ideal_cores": len(mine), "ranks_sharing": len(sharers)}
+    except Exception as e:                                 # binding is an optimisation, never a reason to fail the bench
+        return {"bound": False, "error": str(e)[:80]}
+
+
 def run_gpu(args):
     import torch
     import torch.distributed as dist
-    import helpers
-    from raht_b200 import codec, ops
 
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
     local = int(os.environ.get("LOCAL_RANK", "0"))
+    binding = bind_rank_to_cores(local, world)
+    from raht_b200 import codec, ops, synth
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
     if world > 1:
         dist.init_process_group("nccl", device_id=dev)
-    n, J, desc = WORKLOADS[args.workload]
+    n, J, seed, desc = WORKLOADS[args.workload]
     if args.n:
         n = args.n
     tdtype = torch.float64 if args.dtype == "f64" else torch.float32
-
-    clocks = ClockSampler(local)
-    clocks.start()
-    scene = helpers.synthetic_gaussians(n, 2001 + rank)
-    host = [torch.from_numpy(a).pin_memory() for a in scene]
-    devt = [h.to(dev) for h in host]
-    h2d_bytes = sum(h.numel() * h.element_size() for h in host)
-
-    def step_resident(timer=None):
-        enc = codec.encode_scene(*devt, J=J, step=STEP, transform_dtype=tdtype, tile_rows=args.tile_rows, timer=timer, fused=args.fused)
-        coords, Crec = codec.decode_scene(enc, reuse_tree=False, tile_rows=args.tile_rows, timer=timer, fused=args.fused)
-        return enc, Crec
 
     def barrier():
         if world > 1:
             dist.barrier()
         torch.cuda.synchronize()
 
-    for _ in range(args.warmup):
-        enc, Crec = step_resident()
-    barrier()
+    def max_over_ranks(x):
+        t = torch.tensor([x], dtype=torch.float64, device=dev)
+        if world > 1:
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    def gather_ranks(x):
+        t = torch.tensor([x], dtype=torch.float64, device=dev)
+        if world == 1:
+            return [float(x)]
+        out = [torch.empty_like(t) for _ in range(world)]
+        dist.all_gather(out, t)
+        return [float(o.item()) for o in out]
+
+    clocks = ClockSampler(local)
+    clocks.start()
+    scene = synth.synthetic_gaussians(n, seed + rank)
+    host = [torch.from_numpy(a).pin_memory() for a in scene]
+    devt = [h.to(dev) for h in host]
+    h2d_bytes = sum(h.numel() * h.element_size() for h in host)
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+
+    def measure_resident(inputs, J_, step, steps, warmup):
+        """W warm-up steps, then K timed steps (CUDA events, barrier + synchronize on both sides) with per-stage events."""
+        def one(timer=None):
+            enc = codec.encode_scene(*inputs, J=J_, step=step, transform_dtype=tdtype, tile_rows=args.tile_rows, timer=timer, fused=args.fused)
+            _, Crec = codec.decode_scene(enc, reuse_tree=False, tile_rows=args.tile_rows, timer=timer, fused=args.fused)
+            return enc, Crec
+        for _ in range(warmup):
+            enc, Crec = one()
+        barrier()
+        timers = []
+        launches0 = ops.lib.raht_launch_count()
+        mem0 = torch.cuda.memory_stats(dev)
+        barrier()
+        e0.record()
+        for _ in range(steps):
+            tm = codec.StageTimer(True)
+            enc, Crec = one(tm)
+            timers.append(tm)
+        e1.record()
+        barrier()
+        ms_step = max_over_ranks(e0.elapsed_time(e1)) / steps
+        launches = (ops.lib.raht_launch_count() - launches0) // max(steps, 1)
+        mem1 = torch.cuda.memory_stats(dev)
+        stages, stage_max = {}, {}
+        for tm in timers:
+            for k, v in tm.result().items():
+                stages[k] = stages.get(k, 0.0) + v / len(timers)
+                stage_max[k] = max(stage_max.get(k, 0.0), v)
+        return {"ms_step": ms_step, "launches": int(launches), "stages": stages, "stage_max": stage_max, "enc": enc, "Crec": Crec,
+                "cuda_mallocs": int(mem1.get("segment.all.allocated", 0) - mem0.get("segment.all.allocated", 0))}
+
+    def per_stage_table(res, n_in, J_, peak):
+        enc = res["enc"]
+        sb = stage_bytes(enc.nvox, n_in, enc.payload_bytes(), J_)
+        return sb, {k: {"ms": round(v, 4), "max_ms": round(res["stage_max"][k], 4),
+                        "GBps": round(sb.get(k, 0) / (v / 1e3) / 1e9, 1) if v > 0 else None,
+                        "frac_of_peak": round(sb.get(k, 0) / (v / 1e3) / 1e9 / peak, 4) if v > 0 else None}
+                    for k, v in res["stages"].items()}
+
+    peak, peak_src = load_peaks()
+    clocks.mark_begin()
+    main = measure_resident(devt, J, STEP, args.steps, args.warmup)
+    ms_step = main["ms_step"]
+    value = n * world / (ms_step / 1e3)
+    enc = main["enc"]
     nvox, payload, index_bytes = enc.nvox, enc.payload_bytes(), enc.index_bytes()
 
-    # ---- timed region: device-resident inputs ------------------------------------------------------
-    timers = []
-    launches0 = ops.lib.raht_launch_count()
-    barrier()
-    mem0 = torch.cuda.memory_stats(dev)
-    clocks.mark_begin()
-    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    e0.record()
-    for _ in range(args.steps):
-        tm = codec.StageTimer(True)
-        step_resident(tm)
-        timers.append(tm)
-    e1.record()
-    barrier()
-    ms_total = e0.elapsed_time(e1)
-    launches = (ops.lib.raht_launch_count() - launches0) // max(args.steps, 1)
-    mem1 = torch.cuda.memory_stats(dev)
-    cuda_mallocs = int(mem1.get("segment.all.allocated", 0) - mem0.get("segment.all.allocated", 0))
-    t = torch.tensor([ms_total], dtype=torch.float64, device=dev)
-    if world > 1:
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-    ms_step = float(t.item()) / args.steps
-    value = n * world / (ms_step / 1e3)
-
-    stages, stage_max = {}, {}
-    for tm in timers:
-        for k, v in tm.result().items():
-            stages[k] = stages.get(k, 0.0) + v / len(timers)
-            stage_max[k] = max(stage_max.get(k, 0.0), v)
+    # ---- parity of what was just timed (rank 0, N = 1): GPU results of the timed scene vs the CPU checker ------------
+    cpu = parity = None
+    if world == 1 and not args.no_cpu_baseline:
+        from oracle import oracle_ctypes as orc
+        got_streams = enc.streams.to_bytes()
+        got_keys = enc.keys.cpu().numpy()
+        got_rec = main["Crec"].cpu().numpy()
+        t0 = time.perf_counter()
+        nvox_cpu, Crec_cpu, keys_cpu, streams_cpu = cpu_pipeline(scene, J, STEP, False, want_streams=True)
+        secs = time.perf_counter() - t0
+        cpu = {"value": round(n / secs, 1), "unit": "Gaussians/s", "cores": orc.num_threads(), "kind": "port",
+               "sample": f"the whole timed scene ({n} Gaussians), full encode+decode once ({secs:.1f} s), oracle/raht_oracle.c with OpenMP; "
+                         "the reference's own Python path is timed by --impl reference"}
+        bad = [c for c in range(len(streams_cpu)) if got_streams[c] != streams_cpu[c]]
+        parity = {"checked": True, "against": "oracle/raht_oracle.c (CPU restatement pinned to the reference, DESIGN 2) on the timed scene",
+                  "nvox_equal": bool(nvox_cpu == nvox), "keys_equal": bool(np.array_equal(got_keys, keys_cpu)),
+                  "streams_equal": not bad, "streams_compared": len(streams_cpu), "bytes_compared": int(sum(len(b) for b in streams_cpu)),
+                  "decoded_attributes_equal": bool(np.array_equal(got_rec, Crec_cpu))}
+        if bad:
+            parity["first_differing_channel"] = bad[0]
+        del got_streams, got_rec, Crec_cpu, streams_cpu
+    main["Crec"] = None
 
     # ---- end to end from host buffers ------------------------------------------------------------
     # codec.ScenePipeline: every step copies its scene from pinned host memory (H2D on a copy-in stream, prefetched
     # under the previous step's kernels), encodes + decodes it, and copies the bitstreams, sync index, voxel keys and
-    # the decoded attributes back to pinned host memory (copy-out stream, under the next step's kernels).  All of it,
-    # including the pipeline's fill and drain, lies inside the timed region.
-    # `e2e` reads back what the reference's rate-distortion loop reads back (encode_3dgs.py:247,298-310): the
-    # bitstreams with their sizes and the squared error of the reconstruction (PSNR), plus the sync index and the voxel
-    # keys; `e2e.with_attributes` additionally copies the decoded attributes (fp64, 472 MB) to the host.
-    def time_e2e(result):
-        pipe = codec.ScenePipeline(J, STEP, tdtype, args.tile_rows, dev, result=result)
+    # (with_attributes) the decoded attributes back to pinned host memory (copy-out stream, under the next step's
+    # kernels).  All of it, including the pipeline's fill and drain, lies inside the timed region.
+    def time_e2e(result, hosts, J_, steps):
+        pipe = codec.ScenePipeline(J_, STEP, tdtype, args.tile_rows, dev, result=result)
 
         def run_e2e(k):
             d2h = 0
-            pipe.submit(host)
+            pipe.submit(hosts[0])
             for i in range(k):
                 if i + 1 < k:
-                    pipe.submit(host)                              # H2D of the next step's scene
+                    pipe.submit(hosts[(i + 1) % len(hosts)])       # H2D of the next step's scene
                 d2h = pipe.run()["d2h_bytes"]
             pipe.finish()
             return d2h
@@ -364,19 +504,32 @@ def run_gpu(args):
         barrier()
         t0 = time.perf_counter()
         e0.record()
-        d2h = run_e2e(args.steps)
+        d2h = run_e2e(steps)
         e1.record()
         barrier()
-        t = torch.tensor([e0.elapsed_time(e1)], dtype=torch.float64, device=dev)
-        if world > 1:
-            dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        return n * world / (float(t.item()) / args.steps / 1e3), d2h, time.perf_counter() - t0
+        ms = max_over_ranks(e0.elapsed_time(e1))
+        return ms, d2h, time.perf_counter() - t0
 
-    e2e_value, d2h, wall_e2e = time_e2e("psnr")
-    e2e_attr_value, d2h_attr, _ = time_e2e("attributes")
+    ms_e2e, d2h, wall_e2e = time_e2e("psnr", [host], J, args.steps)
+    e2e_value = n * world / (ms_e2e / args.steps / 1e3)
+    ms_attr, d2h_attr, _ = time_e2e("attributes", [host], J, args.steps)
+    e2e_attr_value = n * world / (ms_attr / args.steps / 1e3)
+
+    # plain pinned -> device copy, all ranks at once: the host-side ceiling of the e2e number
+    probe_src = torch.empty(1 << 29, dtype=torch.uint8).pin_memory()
+    probe_dst = torch.empty(1 << 29, dtype=torch.uint8, device=dev)
+    probe_dst.copy_(probe_src, non_blocking=True)
+    barrier()
+    e0.record()
+    for _ in range(4):
+        probe_dst.copy_(probe_src, non_blocking=True)
+    e1.record()
+    barrier()
+    h2d_probe = gather_ranks(4 * probe_src.numel() / (e0.elapsed_time(e1) / 1e3) / 1e9)
+    del probe_src, probe_dst
+
     # container, outside the metric: bytes and device time of pack / unpack of the last scene
     from raht_b200 import container as cont
-    enc, _ = step_resident()
     box = cont.pack(enc)
     cont.unpack(box)
     torch.cuda.synchronize()
@@ -395,41 +548,74 @@ def run_gpu(args):
                       "raw_keys_bytes": int(enc.nvox * 8), "pack_ms": round(c0.elapsed_time(c1) / 3, 4),
                       "unpack_ms": round(c1.elapsed_time(c2) / 3, 4), "keys_roundtrip": bool(torch.equal(back.keys, enc.keys)),
                       "what": "raht_b200.container: header + RLGR-coded Morton deltas + the attribute streams + sync indices in one device buffer"}
+    del box, back
     clocks.mark_end()
     clk = clocks.stop()
     clk["window"] = "samples between the start of the device-timed region and the end of the e2e regions"
+
+    sb, per_stage = per_stage_table(main, n, J, peak)
+    stages = main["stages"]
+    dom = max(stages, key=stages.get) if stages else None
+    roofline = None
+    if dom:
+        achieved = sb.get(dom, 0) / (stages[dom] / 1e3) / 1e9
+        traffic, traffic_src = stage_traffic(dom) if args.workload == "c2" and not args.n else (None, None)
+        raht_ms = stages.get("raht", 0.0) + stages.get("iraht", 0.0)
+        roofline = {"bound": "hbm", "kernel": dom, "achieved": round(achieved, 2), "peak": peak, "unit": "GB/s",
+                    "frac": round(achieved / peak, 4), "traffic": traffic, "traffic_source": traffic_src, "peak_source": peak_src,
+                    "algorithmic_bytes_per_launch": sb.get(dom, 0), "ms_per_launch": round(stages[dom], 4),
+                    "raht_passes": {"ms": round(raht_ms, 4), "GBps": round((sb["raht"] + sb["iraht"]) / (raht_ms / 1e3) / 1e9, 1),
+                                    "frac": round((sb["raht"] + sb["iraht"]) / (raht_ms / 1e3) / 1e9 / peak, 4)} if raht_ms > 0 else None,
+                    "note": "kernel = the pipeline stage with the largest CUDA-event time in this run (a group of kernels, STAGE_KERNELS); "
+                            "per-stage GB/s and fractions are under `stages`; raht_passes = forward + inverse transform together "
+                            "(the north-star bar is >= 0.60 on these)"}
+
+    # ---- sub-records ------------------------------------------------------------------------------
+    del devt
+    main["enc"] = enc = None
+    torch.cuda.empty_cache()
+    sub = {}
+    if world == 1 and args.workload == "c2" and not args.n and not args.no_subrecords:
+        # the same scene at a coarse step: most channels mostly zero (RLGR run mode, helper warps, transition tables)
+        devt2 = [h.to(dev) for h in host]
+        r = measure_resident(devt2, J, SPARSE_STEP, max(args.steps, 3), 3)
+        _, st_tab = per_stage_table(r, n, J, peak)
+        sub["sparse"] = {"quant_step": SPARSE_STEP, "ms_per_step": round(r["ms_step"], 4), "value": round(n / (r["ms_step"] / 1e3), 1),
+                         "unit": "Gaussians/s", "payload_bytes": r["enc"].payload_bytes(),
+                         "bits_per_voxel": round(r["enc"].payload_bytes() * 8 / r["enc"].nvox, 3),
+                         "rlgr_encode_ms": round(r["stages"].get("rlgr_encode", 0.0), 4), "rlgr_decode_ms": round(r["stages"].get("rlgr_decode", 0.0), 4)}
+        del devt2, r
+        torch.cuda.empty_cache()
+        # BASELINE configs[2]: 6 M Gaussians, depth 16, fp64 bit-exact mode (the scene tests/test_gpu_scale_parity.py checks)
+        n3, J3, seed3, desc3 = WORKLOADS["c3"]
+        scene3 = synth.synthetic_gaussians(n3, seed3)
+        dev3 = [torch.from_numpy(a).to(dev) for a in scene3]
+        del scene3
+        r = measure_resident(dev3, J3, STEP, max(args.steps, 3), 3)
+        sb3, st_tab = per_stage_table(r, n3, J3, peak)
+        enc_stages = ("morton", "sort", "segments", "merge", "raht_param", "raht", "quant_reorder", "rlgr_encode")
+        raht_ms = r["stages"].get("raht", 0.0) + r["stages"].get("iraht", 0.0)
+        sub["c3"] = {"workload": desc3, "n_gaussians": n3, "nvox": r["enc"].nvox, "depth": J3, "quant_step": STEP,
+                     "ms_per_step": round(r["ms_step"], 4), "value": round(n3 / (r["ms_step"] / 1e3), 1), "unit": "Gaussians/s",
+                     "encode_ms": round(sum(r["stages"].get(k, 0.0) for k in enc_stages), 4),
+                     "gpu_launches": r["launches"], "payload_bytes": r["enc"].payload_bytes(),
+                     "raht_passes": {"ms": round(raht_ms, 4), "frac": round((sb3["raht"] + sb3["iraht"]) / (raht_ms / 1e3) / 1e9 / peak, 4)},
+                     "stages": st_tab}
+        del dev3, r
+        torch.cuda.empty_cache()
+    if not args.no_subrecords and args.workload == "c2" and not args.n:
+        sub["c5"] = c5_record(args, dev, rank, world, barrier, max_over_ranks, tdtype)
+        torch.cuda.empty_cache()
+        if world > 1:
+            sub["sharded"] = sharded_record(args, dev, rank, world, barrier, max_over_ranks)
 
     if rank != 0:
         if world > 1:
             dist.destroy_process_group()
         return
 
-    peak, peak_src = load_peaks()
-    sb = stage_bytes(nvox, n, payload, J)
-    dom = max(stages, key=stages.get) if stages else None
-    roofline = None
-    if dom:
-        achieved = sb.get(dom, 0) / (stages[dom] / 1e3) / 1e9
-        traffic, traffic_src = stage_traffic(dom) if args.workload == "c2" and not args.n else (None, None)
-        roofline = {"bound": "hbm", "kernel": dom, "achieved": round(achieved, 2), "peak": peak, "unit": "GB/s",
-                    "frac": round(achieved / peak, 4), "traffic": traffic, "traffic_source": traffic_src, "peak_source": peak_src,
-                    "algorithmic_bytes_per_launch": sb.get(dom, 0), "ms_per_launch": round(stages[dom], 4),
-                    "note": "kernel = the pipeline stage with the largest CUDA-event time in this run (a group of kernels, STAGE_KERNELS); "
-                            "per-stage GB/s and fractions are under `stages`"}
-    per_stage = {k: {"ms": round(v, 4), "max_ms": round(stage_max[k], 4), "GBps": round(sb.get(k, 0) / (v / 1e3) / 1e9, 1) if v > 0 else None,
-                     "frac_of_peak": round(sb.get(k, 0) / (v / 1e3) / 1e9 / peak, 4) if v > 0 else None}
-                 for k, v in stages.items()}
-
-    cpu = None
-    if world == 1 and not args.no_cpu_baseline:
-        from oracle import oracle_ctypes as orc
-        sample = min(n, args.cpu_sample)
-        v, secs = time_cpu(scene, J, STEP, sample, 1, False)
-        cpu = {"value": round(v, 1), "unit": "Gaussians/s", "cores": orc.num_threads(), "kind": "port",
-               "sample": f"first {sample} Gaussians of the same scene, full encode+decode once ({secs:.1f} s), oracle/raht_oracle.c with OpenMP"}
-
     line = {
-        "metric": "Gaussians/s full RAHT encode+decode (59 ch)", "value": round(value, 1), "unit": "Gaussians/s",
+        "metric": METRIC, "value": round(value, 1), "unit": "Gaussians/s",
         "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": round(ms_step, 4),
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": args.dtype, "data": "synthetic",
         "config": {"workload": desc, "n_gaussians_per_gpu": n, "nvox": nvox, "depth": J, "channels": D, "quant_step": STEP,
@@ -445,163 +631,225 @@ def run_gpu(args):
                 "how": "codec.ScenePipeline(result='psnr'): H2D of step k+1 and D2H of step k-1 overlap the kernels of step k (3 streams); "
                        "read back per step: bitstreams + sizes, sync index, voxel keys, squared error of the reconstruction "
                        "(what the reference driver reads back, encode_3dgs.py:247,298-310)",
+                "h2d_GBps_per_rank_achieved": round(h2d_bytes / (ms_e2e / args.steps / 1e3) / 1e9, 2),
+                "h2d_probe_GBps_per_rank": [round(x, 1) for x in h2d_probe],
+                "h2d_probe": "plain pinned->device copy of 512 MiB x 4 on every rank at the same time: the host-side ceiling of this number",
+                "host_binding": binding,
                 "with_attributes": {"value": round(e2e_attr_value, 1), "unit": "Gaussians/s", "d2h_bytes_per_step": int(d2h_attr),
                                     "how": "the same plus the decoded attributes (nvox x 59 fp64) copied to pinned host memory"}},
-        "gpu_launches": int(launches),
-        "cuda_mallocs_in_timed_region": cuda_mallocs,
+        "gpu_launches": main["launches"],
+        "cuda_mallocs_in_timed_region": main["cuda_mallocs"],
         "roofline": roofline,
         "stages": per_stage,
         "cpu_baseline": cpu,
+        "parity": parity,
         "container": container_info,
     }
+    line.update(sub)
     print(json.dumps(line))
     if world > 1:
         dist.destroy_process_group()
 
 
-def run_sharded(args):
-    """BASELINE config 4: ONE scene over all ranks (strong scaling).  Every rank starts with a random 1/P sample of
-    the scene; the timed step = bounding box all_reduce, all_to_all of the raw Gaussians to the owner of their Morton
-    prefix, local voxelise / merge / RAHT, all_gather + join of the P low-pass rows, all_to_all of the quantised
-    coefficients to channel shards, RLGR of whole-scene channels -- and the mirror-image decode."""
+def c5_record(args, dev, rank, world, barrier, max_over_ranks, tdtype):
+    """BASELINE configs[4] (encode_dataset.py:29,104 walks frames one after the other): 64 scenes x 2 M Gaussians, depth 14,
+    one scene stream per GPU -- 64 / N scenes per rank through codec.ScenePipeline from pinned host memory (H2D, encode,
+    decode, D2H of streams + index + keys + squared error inside the timed region).  Each rank cycles through
+    `distinct` different scenes (generated on the device, copied to pinned host memory before the clock starts)."""
+    import torch
+    from raht_b200 import codec, synth
+    n5, J5, seed5, desc5 = WORKLOADS["c5"]
+    total_scenes = 64
+    per_rank = max(total_scenes // world, 1)
+    distinct = min(per_rank, 4)
+    hosts = []
+    for k in range(distinct):
+        sc = synth.synthetic_gaussians_device(n5, seed5 + rank * 64 + k, dev)
+        hosts.append([t.cpu().pin_memory() for t in sc])
+        del sc
+    torch.cuda.empty_cache()
+    pipe = codec.ScenePipeline(J5, STEP, tdtype, args.tile_rows, dev, result="psnr")
+
+    def run(k):
+        pipe.submit(hosts[0])
+        for i in range(k):
+            if i + 1 < k:
+                pipe.submit(hosts[(i + 1) % distinct])
+            pipe.run()
+        pipe.finish()
+
+    run(3)
+    barrier()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    run(per_rank)
+    e1.record()
+    barrier()
+    ms = max_over_ranks(e0.elapsed_time(e1))
+    h2d = sum(h.numel() * h.element_size() for h in hosts[0])
+    return {"workload": desc5, "scenes": per_rank * world, "scenes_per_rank": per_rank, "distinct_scenes_per_rank": distinct,
+            "n_gaussians_per_scene": n5, "depth": J5, "quant_step": STEP, "ms_total": round(ms, 3),
+            "scenes_per_s": round(per_rank * world / (ms / 1e3), 2), "value": round(per_rank * world * n5 / (ms / 1e3), 1),
+            "unit": "Gaussians/s", "h2d_bytes_per_scene": h2d, "h2d_GBps_per_rank": round(per_rank * h2d / (ms / 1e3) / 1e9, 2),
+            "how": "end to end from pinned host memory through codec.ScenePipeline(result='psnr'), copies inside the timed region"}
+
+
+def sharded_record(args, dev, rank, world, barrier, max_over_ranks, n_total=None):
+    """BASELINE configs[3]: ONE scene over all ranks (strong scaling).  Every rank starts with a random 1/P sample of the
+    scene; the timed step = the whole sharded encode + decode of raht_b200/sharded.py (NCCL exchanges included)."""
     import torch
     import torch.distributed as dist
-    import helpers
-    from raht_b200 import ops, sharded
+    from raht_b200 import ops, sharded, synth
+    from raht_b200.codec import StageTimer
+    n, J, seed, desc = WORKLOADS["c4"]
+    n = n_total or args.sharded_n or n
+    n_local = n // world
+    devt = list(synth.synthetic_gaussians_device(n_local, seed + rank, dev))
+    codec_ = sharded.ShardedCodec(sharded.DeviceBackend(args.tile_rows))
 
+    def step(inputs, timer=None):
+        enc = codec_.encode(*inputs, J=J, step=STEP, timer=timer)
+        rec = codec_.decode(enc, timer=timer)
+        return enc, rec
+
+    for _ in range(2):
+        enc, rec = step(devt)
+    barrier()
+    launches0 = ops.lib.raht_launch_count()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    steps = max(min(args.steps, 3), 2)
+    barrier()
+    e0.record()
+    timers = []
+    for _ in range(steps):
+        tm = StageTimer(True)
+        enc, rec = step(devt, tm)
+        timers.append(tm)
+    e1.record()
+    barrier()
+    launches = (ops.lib.raht_launch_count() - launches0) // steps
+    stages = {}
+    for tm in timers:
+        for k, v in tm.result().items():
+            stages[k] = round(stages.get(k, 0.0) + v / len(timers), 3)
+    ms_step = max_over_ranks(e0.elapsed_time(e1)) / steps
+    payload = torch.tensor([float(enc.streams.total_bytes())], dtype=torch.float64, device=dev)
+    rows = torch.tensor([float(enc.n_rows[rank])], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(payload)
+        dist.all_reduce(rows, op=dist.ReduceOp.MAX)
+    nvox = enc.n_total
+    limiting = max(stages, key=stages.get) if stages else None
+    out = {"workload": desc, "scaling": "strong", "n_gaussians_total": n_local * world, "nvox": nvox, "depth": J, "quant_step": STEP,
+           "ms_per_step": round(ms_step, 3), "value": round(n_local * world / (ms_step / 1e3), 1), "unit": "Gaussians/s",
+           "gpu_launches_rank0": int(launches), "payload_bytes": int(payload.item()),
+           "max_rows_on_a_rank": int(rows.item()), "balance": round(nvox / world / max(rows.item(), 1.0), 3),
+           "stages_rank0_ms": stages, "limiting_stage_rank0": limiting,
+           "collective_bytes_per_rank": getattr(enc, "collective_bytes", None),
+           "parallelism": f"Morton-prefix shards x{world} (raht_b200/sharded.py): bitstream identical to one GPU"}
+    del devt, enc, rec
+    torch.cuda.empty_cache()
+    return out
+
+
+def run_sharded(args):
+    """--workload c4 on its own: the sharded scene as the headline line (strong scaling)."""
+    import torch
+    import torch.distributed as dist
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
     local = int(os.environ.get("LOCAL_RANK", "0"))
+    bind_rank_to_cores(local, world)
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
     if world > 1:
         dist.init_process_group("nccl", device_id=dev)
-    n, J, desc = WORKLOADS["c4"]
-    if args.n:
-        n = args.n
-    n_local = n // world
-    scene = helpers.synthetic_gaussians(n_local, 4001 + rank)
-    host = [torch.from_numpy(a).pin_memory() for a in scene]
-    devt = [h.to(dev) for h in host]
-    codec = sharded.ShardedCodec(sharded.DeviceBackend(args.tile_rows))
 
     def barrier():
         if world > 1:
             dist.barrier()
         torch.cuda.synchronize()
 
-    from raht_b200.codec import StageTimer
-
-    def step(inputs, timer=None):
-        enc = codec.encode(*inputs, J=J, step=STEP, timer=timer)
-        rec = codec.decode(enc, timer=timer)
-        return enc, rec
+    def max_over_ranks(x):
+        t = torch.tensor([x], dtype=torch.float64, device=dev)
+        if world > 1:
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
 
     clocks = ClockSampler(local)
     clocks.start()
-    for _ in range(args.warmup):
-        enc, rec = step(devt)
-    barrier()
-    launches0 = ops.lib.raht_launch_count()
-    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    barrier()
     clocks.mark_begin()
-    e0.record()
-    timers = []
-    for _ in range(args.steps):
-        tm = StageTimer(True)
-        enc, rec = step(devt, tm)
-        timers.append(tm)
-    e1.record()
-    barrier()
-    launches = (ops.lib.raht_launch_count() - launches0) // max(args.steps, 1)
+    rec = sharded_record(args, dev, rank, world, barrier, max_over_ranks, n_total=args.n or None)
     clocks.mark_end()
     time.sleep(0.06)
     clk = clocks.stop()
-    stages = {}
-    for tm in timers:
-        for k, v in tm.result().items():
-            stages[k] = round(stages.get(k, 0.0) + v / len(timers), 3)
-    t = torch.tensor([e0.elapsed_time(e1)], dtype=torch.float64, device=dev)
-    if world > 1:
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-    ms_step = float(t.item()) / args.steps
-    payload = torch.tensor([float(enc.streams.total_bytes())], dtype=torch.float64, device=dev)
-    if world > 1:
-        dist.all_reduce(payload)
-
-    pin_rec = torch.empty(rec.numel(), dtype=rec.dtype).pin_memory()
-    pin_streams = torch.empty(int(enc.streams.buf.numel()), dtype=torch.uint8).pin_memory()
-
-    def step_e2e():
-        dv = [h.to(dev, non_blocking=True) for h in host]
-        enc, rec = step(dv)
-        pin_streams.copy_(enc.streams.buf, non_blocking=True)
-        pin_rec[:rec.numel()].copy_(rec.reshape(-1), non_blocking=True)
-        torch.cuda.synchronize()
-        return enc.streams.total_bytes() + rec.numel() * rec.element_size()
-
-    d2h = step_e2e()
-    barrier()
-    e0.record()
-    for _ in range(args.steps):
-        d2h = step_e2e()
-    e1.record()
-    barrier()
-    t = torch.tensor([e0.elapsed_time(e1)], dtype=torch.float64, device=dev)
-    if world > 1:
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-    ms_e2e = float(t.item()) / args.steps
     if rank == 0:
-        nvox = enc.n_total
-        line = {
-            "metric": "Gaussians/s full RAHT encode+decode (59 ch)", "value": round(n_local * world / (ms_step / 1e3), 1),
-            "unit": "Gaussians/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": round(ms_step, 4),
-            "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-            "config": {"workload": desc, "n_gaussians_total": n_local * world, "nvox": nvox, "depth": J, "channels": D,
-                       "quant_step": STEP, "payload_bytes": int(payload.item()), "bits_per_voxel": round(payload.item() * 8 / nvox, 3),
-                       "parallelism": f"Morton-prefix shards x{world}: NCCL all_reduce (bbox), all_to_all (raw Gaussians), all_gather "
-                                      "(low-pass rows), all_to_all (coefficients -> channel shards); bitstream identical to one GPU",
-                       "l2": "per-rank inputs and intermediates exceed the 126 MB L2; no explicit flush"},
-            "clocks": clk,
-            "e2e": {"value": round(n_local * world / (ms_e2e / 1e3), 1), "unit": "Gaussians/s",
-                    "h2d_bytes_per_step": sum(h.numel() * h.element_size() for h in host), "d2h_bytes_per_step": int(d2h)},
-            "gpu_launches": int(launches), "roofline": None, "cpu_baseline": None, "stages_rank0_ms": stages,
-        }
+        line = {"metric": METRIC, "value": rec["value"], "unit": "Gaussians/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+                "ms_per_step": rec["ms_per_step"], "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f64",
+                "data": "synthetic", "config": {"workload": rec["workload"], "n_gaussians_total": rec["n_gaussians_total"], "nvox": rec["nvox"],
+                                                "depth": rec["depth"], "channels": D, "quant_step": STEP, "parallelism": rec["parallelism"]},
+                "clocks": clk, "gpu_launches": rec["gpu_launches_rank0"], "roofline": None, "cpu_baseline": None, "sharded": rec}
         print(json.dumps(line))
     if world > 1:
         dist.destroy_process_group()
 
 
 def run_reference(args):
+    """--impl reference: the reference's own CPU path on the box's host cores, on the WHOLE configured scene
+    (same_config: the scene, depth, channels and step of the b200 arm), every step one full encode + decode."""
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
-    import helpers
     from oracle import oracle_ctypes as orc
-    n, J, desc = WORKLOADS[args.workload]
+    from oracle import refpy
+    from raht_b200 import synth
+    n, J, seed, desc = WORKLOADS[args.workload if args.workload in ("c2", "c3", "tiny") else "c2"]
     if args.n:
         n = args.n
-    sample = min(n, args.cpu_sample)
-    scene = helpers.synthetic_gaussians(n, 2001)
-    use_ref = orc.ref_rlgr_available() and not args.port_rlgr
-    sub = tuple(a[:sample] for a in scene)
+    if args.cpu_sample:
+        n = min(n, args.cpu_sample)
+    scene = synth.synthetic_gaussians(WORKLOADS[args.workload][0] if not args.n else args.n, seed)
+    scene = tuple(a[:n] for a in scene)
+    use_python = refpy.available() and orc.ref_rlgr_available() and not args.port
+    stage_s = {}
+    if use_python:
+        def one():
+            return reference_python_pipeline(scene, J, STEP, stage_s)[0]
+    else:
+        use_ref = orc.ref_rlgr_available() and not args.port_rlgr
+        def one():
+            return cpu_pipeline(scene, J, STEP, use_ref)[0]
     for _ in range(args.warmup):
-        cpu_pipeline(sub, J, STEP, use_ref)
+        one()
+    stage_s.clear()
     t0 = time.perf_counter()
     for _ in range(args.steps):
-        nvox, _ = cpu_pipeline(sub, J, STEP, use_ref)
-    secs = (time.perf_counter() - t0) / args.steps
-    v = sample / secs
-    kind = "port"   # the transform/voxeliser are the C restatement; only the entropy coder is the reference's own object code
-    cpu = {"value": round(v, 1), "unit": "Gaussians/s", "cores": orc.num_threads(), "kind": kind,
-           "sample": f"first {sample} Gaussians of the scene per step; oracle/raht_oracle.c (OpenMP) + "
-                     + ("reference RLGR coder oracle/_ref/librlgr_ref.so, one channel per host thread" if use_ref else "oracle RLGR (1 thread per channel)")}
+        nvox = one()
+    secs = (time.perf_counter() - t0) / max(args.steps, 1)
+    v = n / secs
+    # the OpenMP port as a second, labelled number (one step)
+    t0 = time.perf_counter()
+    cpu_pipeline(scene, J, STEP, orc.ref_rlgr_available())
+    port_secs = time.perf_counter() - t0
+    if use_python:
+        kind = "reference"
+        sample = (f"the whole scene ({n} Gaussians) per step: the reference's Python operators ({os.path.relpath(refpy.directory(), ROOT) if refpy.directory().startswith(ROOT) else refpy.directory()}) "
+                  "on torch-CPU in the order of test_voxelize_3dgs.py:203-247 + encode_3dgs.py:144-276, RLGR by the reference coder's object code "
+                  "(oracle/_ref/librlgr_ref.so), one channel per host thread; merge = C restatement (the reference has only a CUDA kernel)")
+    else:
+        kind = "port"
+        sample = f"the whole scene ({n} Gaussians) per step: oracle/raht_oracle.c (OpenMP)" + (" + reference RLGR coder oracle/_ref/librlgr_ref.so" if orc.ref_rlgr_available() and not args.port_rlgr else "")
+    cpu = {"value": round(v, 1), "unit": "Gaussians/s", "cores": host_cores(), "kind": kind, "sample": sample,
+           "stages_s": {k: round(x / max(args.steps, 1), 3) for k, x in stage_s.items()} or None,
+           "port": {"value": round(n / port_secs, 1), "unit": "Gaussians/s", "kind": "port",
+                    "sample": f"the same scene once through oracle/raht_oracle.c with OpenMP ({port_secs:.1f} s)"}}
+    full = WORKLOADS[args.workload][0] if not args.n else args.n
     line = {
-        "impl": "reference", "metric": "Gaussians/s full RAHT encode+decode (59 ch)", "value": round(v, 1), "unit": "Gaussians/s",
+        "impl": "reference", "metric": METRIC, "value": round(v, 1), "unit": "Gaussians/s",
         "n_gpus": int(os.environ.get("WORLD_SIZE", "1")), "steps": args.steps, "warmup": args.warmup, "ms_per_step": round(secs * 1e3, 2),
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-        "config": {"workload": desc, "n_gaussians_per_gpu": n, "nvox": int(nvox), "depth": J, "channels": D, "quant_step": STEP},
+        "config": {"workload": desc, "n_gaussians_per_gpu": n, "nvox": int(nvox), "depth": J, "channels": D, "quant_step": STEP,
+                   "same_config": bool(n == full)},
         "cpu_baseline": cpu,
         "e2e": {"value": round(v, 1), "unit": "Gaussians/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
     }
@@ -618,10 +866,13 @@ def main():
     ap.add_argument("--num-gaussians", dest="n", type=int, default=0, help="override the number of Gaussians")
     ap.add_argument("--dtype", default="f64", choices=["f64", "f32"], help="transform arithmetic (f64 = bit-exact mode)")
     ap.add_argument("--tile-rows", type=int, default=0)
-    ap.add_argument("--cpu-sample", type=int, default=250_000)
+    ap.add_argument("--cpu-sample", type=int, default=0, help="reference arm: only the first K Gaussians of the scene (0 = the whole scene)")
     ap.add_argument("--fused", action="store_true", help="transform and quantisation in one pass (raht_forward_quant / raht_dequant_inverse) instead of the reference's two")
     ap.add_argument("--no-cpu-baseline", action="store_true")
-    ap.add_argument("--port-rlgr", action="store_true", help="reference arm: use the oracle RLGR port instead of oracle/_ref")
+    ap.add_argument("--no-subrecords", action="store_true", help="only the headline workload (no sparse / c3 / c5 / sharded sub-records)")
+    ap.add_argument("--sharded-n", type=int, default=0, help="Gaussians of the sharded sub-record's scene (default: 50 M)")
+    ap.add_argument("--port", action="store_true", help="reference arm: the OpenMP port instead of the reference's Python operators")
+    ap.add_argument("--port-rlgr", action="store_true", help="reference arm (port): the oracle RLGR instead of oracle/_ref")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "b200" else args.warmup
     args.tile_rows = args.tile_rows or None

@@ -45,40 +45,13 @@ def rlgr_kats():
     return list(zip(seqs, outs, [int(f) for f in g["flag_signed"]]))
 
 
-def spread3(x):
-    x = x.astype(np.uint64) & np.uint64(0x1fffff)
-    x = (x | (x << np.uint64(32))) & np.uint64(0x1f00000000ffff)
-    x = (x | (x << np.uint64(16))) & np.uint64(0x1f0000ff0000ff)
-    x = (x | (x << np.uint64(8))) & np.uint64(0x100f00f00f00f00f)
-    x = (x | (x << np.uint64(4))) & np.uint64(0x10c30c30c30c30c3)
-    x = (x | (x << np.uint64(2))) & np.uint64(0x1249249249249249)
-    return x
-
-
-def morton_np(P):
-    return (spread3(P[:, 2]) | (spread3(P[:, 1]) << np.uint64(1)) | (spread3(P[:, 0]) << np.uint64(2))).astype(np.int64)
-
-
-def synthetic_gaussians(n, seed, color_dim=48):
-    """3DGS-like scene of SURVEY 8(d): 70 % on ellipsoid shells, 30 % uniform; fp32."""
-    rng = np.random.default_rng(seed)
-    n_shell = int(0.7 * n)
-    k = 64
-    centres = rng.uniform(-0.7, 0.7, size=(k, 3))
-    radii = rng.uniform(0.05, 0.3, size=(k, 3))
-    which = rng.integers(0, k, size=n_shell)
-    d = rng.normal(size=(n_shell, 3))
-    d /= np.linalg.norm(d, axis=1, keepdims=True)
-    shell = centres[which] + radii[which] * d + rng.normal(0, 0.002, size=(n_shell, 3))
-    uni = rng.uniform(-1, 1, size=(n - n_shell, 3))
-    means = np.concatenate([shell, uni]).astype(np.float32)
-    rng.shuffle(means)
-    quats = rng.normal(size=(n, 4)).astype(np.float32)
-    quats /= np.linalg.norm(quats, axis=1, keepdims=True)
-    scales = np.exp(rng.normal(-4, 1, size=(n, 3))).astype(np.float32)
-    opac = (1.0 / (1.0 + np.exp(-rng.normal(0, 2, size=n)))).astype(np.float32)
-    colors = np.concatenate([0.5 * rng.normal(size=(n, 3)), 0.1 * rng.normal(size=(n, color_dim - 3))], 1).astype(np.float32)
-    return means, quats, scales, opac, colors
+import sys as _sys
+_PKG = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "raht-3dgs-codec_b200")
+if _PKG not in _sys.path:
+    _sys.path.insert(0, _PKG)
+# the scene generators live in the package (bench.py times exactly the scenes the tests check); they are numpy-only,
+# but importing the package loads libraht_b200.so -- which every test module needs anyway
+from raht_b200.synth import synthetic_gaussians, morton_np, sphere_point_cloud, _spread3 as spread3  # noqa: E402,F401
 
 
 def unique_sorted_voxels(n, J, seed, clustered=True):
