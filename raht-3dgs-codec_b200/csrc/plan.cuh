@@ -54,6 +54,7 @@ struct PlanDev {
     uint32_t *sched;                        // [slots0 + n]
     double2 *ab;                            // [slots0 + n]
     unsigned int *bump;                     // next free upper-stage schedule slot (starts at slots0)
+    unsigned int *arrive;                   // [tiles_total] child tiles planned so far (the hierarchy is built in one launch)
 };
 
 struct raht_plan {

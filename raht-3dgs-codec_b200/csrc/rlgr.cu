@@ -37,6 +37,9 @@ struct Geometry {
     int64_t nsb;         // 128-symbol blocks per channel (compaction passes)
     int64_t W;           // chunk slots per channel in the event store (enough for n events)
     int nch, flag_signed;
+    const int32_t *q;    // the symbols (dense channels are coded straight from them)
+    const int32_t *lastnz;   // after the scan pass: last non-zero symbol at or before the end of every 128-symbol block
+    int vec;             // q rows are 16-byte aligned: whole units of 8 symbols are read as two 16-byte loads
 };
 
 __host__ __device__ inline int64_t sym_blocks_of(int64_t n) { return (n + SYM_BLOCK - 1) / SYM_BLOCK; }
@@ -47,9 +50,12 @@ __host__ __device__ inline int64_t chunk_slots_of(int64_t n) { return chunks_of_
 // per-channel header written by the scan pass
 struct ChanInfo {
     uint32_t events;     // non-zero symbols of the channel
-    uint32_t nblocks;    // event blocks (>= 1: the block of an empty channel codes the tail)
+    uint32_t nblocks;    // lane blocks: blocks of 128 events, or (dense) of 128 symbols (>= 1: the block of an empty channel codes the tail)
     uint32_t nchunks;
     uint32_t tail_zeros; // zero symbols after the last event
+    uint32_t dense;      // at least half of the symbols are non-zero: coded in SYMBOL space, straight from q (no event store)
+    uint32_t tail_block; // dense: the symbol block that holds the last non-zero symbol
+    uint32_t pad0, pad1;
 };
 
 // ---- K1a: non-zero count and last non-zero symbol of every 128-symbol block -----------------------------
@@ -130,9 +136,12 @@ __global__ void __launch_bounds__(1024) rlgr_scan_kernel(Geometry G, uint32_t *_
     if (threadIdx.x == 0) {
         ChanInfo I;
         I.events = carry_sum;
-        I.nblocks = (uint32_t)ev_blocks_of(carry_sum);
+        I.dense = (int64_t)carry_sum * 2 >= G.n ? 1u : 0u;
+        I.nblocks = I.dense ? (uint32_t)G.nsb : (uint32_t)ev_blocks_of(carry_sum);
         I.nchunks = (uint32_t)chunks_of_blocks(I.nblocks);
         I.tail_zeros = (uint32_t)(G.n - 1 - (int64_t)carry_max);
+        I.tail_block = carry_max < 0 ? 0u : (uint32_t)(carry_max / SYM_BLOCK);
+        I.pad0 = I.pad1 = 0u;
         info[blockIdx.x] = I;
     }
 }
@@ -156,13 +165,13 @@ __device__ __forceinline__ void store_event(uint2 *__restrict__ evc, uint32_t *_
 __global__ void __launch_bounds__(32 * K1_WARPS) rlgr_scatter_kernel(const int32_t *__restrict__ q, Geometry G,
                                                                     const uint32_t *__restrict__ evbase,
                                                                     const int32_t *__restrict__ lastnz, uint2 *__restrict__ ev,
-                                                                    uint32_t *__restrict__ blockpos)
+                                                                    uint32_t *__restrict__ blockpos, const ChanInfo *__restrict__ info)
 {
     const int lane = threadIdx.x & 31;
     const int64_t group = (int64_t)blockIdx.x * K1_WARPS + (threadIdx.x >> 5);
     const int ch = blockIdx.y;
     const int64_t blk0 = group * 32;
-    if (blk0 >= G.nsb) return;
+    if (blk0 >= G.nsb || info[ch].dense) return;            // dense channels are coded from q itself
     const int32_t *src = q + (size_t)ch * G.ld;
     uint2 *evc = ev + (size_t)ch * G.W * CHUNK_SLOTS;
     uint32_t *bpos = blockpos + (size_t)ch * G.nsb;
@@ -200,9 +209,15 @@ __global__ void __launch_bounds__(32 * K1_WARPS) rlgr_scatter_kernel(const int32
 struct LaneBlock {
     const uint4 *base;         // the chunk in the store, as 16-byte units: unit j of store lane `slot` at base[(j * 32 + slot) * 2 + {0,1}]
     int slot;                  // store lane of the block (= the thread's lane, except in the table pass where a warp shares one block)
-    int cnt;                   // events of this lane's block (0: none)
+    int cnt;                   // events of this lane's block (0: none); dense channels: its SYMBOLS
     bool is_tail;              // the block holds the channel's last event (or the channel has none): it also codes the tail
     uint32_t tail_zeros;
+    // dense channels (symbol space): the block is 128 consecutive symbols of q, its events are found on the fly
+    const int32_t *sym;        // nullptr: event space
+    uint32_t gap0;             // zero symbols pending in front of the block (since the last non-zero symbol before it)
+    int64_t pos0;              // index of the block's first symbol
+    int vec, flag_signed;
+    int avail;                 // symbols of the channel from the block's start (<= 128): what may be read
 };
 
 // Lane l of chunk w holds block 31 w - 1 + l (lane 0: the block before the chunk).
@@ -214,12 +229,105 @@ __device__ __forceinline__ LaneBlock lane_block(const uint2 *__restrict__ ev, co
     B.base = (const uint4 *)(ev + ((size_t)ch * G.W + w) * CHUNK_SLOTS);
     B.slot = lane;
     const int64_t b = w * CHUNK_LANES - 1 + lane;
+    B.tail_zeros = I.tail_zeros;
+    B.sym = nullptr;
+    B.gap0 = 0;
+    B.pos0 = 0;
+    B.vec = G.vec; B.flag_signed = G.flag_signed; B.avail = 0;
+    if (I.dense) {                                          // symbol space: blocks up to the one with the last non-zero symbol
+        const bool live = b >= 0 && b <= (int64_t)I.tail_block;
+        B.pos0 = b * SYM_BLOCK;
+        B.is_tail = b == (int64_t)I.tail_block;
+        B.sym = G.q + (size_t)ch * G.ld + (live ? B.pos0 : 0);
+        B.cnt = 0;
+        B.avail = 0;
+        if (live) {                                         // the block ends with its last non-zero symbol (an event boundary)
+            const int32_t *ln = G.lastnz + (size_t)ch * G.nsb + b;
+            const int64_t last = ln[0];
+            const int64_t prev = b > 0 ? (int64_t)ln[-1] : -1;
+            B.cnt = last >= B.pos0 ? (int)(last - B.pos0 + 1) : 0;
+            B.gap0 = (uint32_t)(B.pos0 - 1 - prev);
+            const int64_t av = G.n - B.pos0;
+            B.avail = (int)(av > SYM_BLOCK ? SYM_BLOCK : av);
+        }
+        return B;
+    }
     int64_t cnt = (b < 0 || b >= (int64_t)I.nblocks) ? 0 : (int64_t)I.events - b * EV_BLOCK;
     cnt = cnt < 0 ? 0 : (cnt > EV_BLOCK ? EV_BLOCK : cnt);
     B.cnt = (int)cnt;
     B.is_tail = b == (int64_t)I.nblocks - 1;
-    B.tail_zeros = I.tail_zeros;
     return B;
+}
+
+// ---- dense channels: a lane block in symbol space -------------------------------------------------------------
+// Every lane walks its own block of q -- the symbols from the block's start to its last non-zero symbol -- in units of
+// 8 symbols (two 16-byte loads = one 32-byte sector, so DRAM traffic is exactly the symbols), two units requested
+// ahead of the one being coded, and feeds every symbol to the per-symbol machine of rlgr_core.cuh: all lanes of the
+// warp do the same work per symbol.  f(index in block, mapped symbol); whole units run unguarded.
+template <class F> __device__ __forceinline__ void walk_symbols(const LaneBlock &B, F &&f)
+{
+    const int n = B.cnt;
+    const int32_t *p = B.sym;
+    const int units = (n + 7) >> 3;
+    const int vunits = B.vec ? (B.avail >> 3) : 0;           // units that may be read as two 16-byte loads
+    const uint4 *v = (const uint4 *)p;
+    // _s2u (membuf.cpp:4-14) as the zig-zag (x << 1) ^ (x >> 31); unsigned symbols pass through
+    const int sh = B.flag_signed ? 1 : 0;
+    const uint32_t sm = B.flag_signed ? 0xffffffffu : 0u;
+    uint4 a1, b1, a2, b2;
+    a1 = b1 = a2 = b2 = make_uint4(0u, 0u, 0u, 0u);
+    if (0 < units && 0 < vunits) { a1 = __ldg(v); b1 = __ldg(v + 1); }
+    if (1 < units && 1 < vunits) { a2 = __ldg(v + 2); b2 = __ldg(v + 3); }
+    for (int j = 0; j < units; ++j) {
+        uint4 a = a1, b = b1;
+        a1 = a2; b1 = b2;
+        if (j + 2 < units && j + 2 < vunits) { a2 = __ldg(v + 2 * (j + 2)); b2 = __ldg(v + 2 * (j + 2) + 1); }
+        if (j >= vunits) {                                   // the channel's last, partial unit, or rows that are not 16-byte aligned
+            int32_t y[8];
+#pragma unroll
+            for (int t = 0; t < 8; ++t) y[t] = j * 8 + t < B.avail ? __ldg(p + j * 8 + t) : 0;
+            a = make_uint4((uint32_t)y[0], (uint32_t)y[1], (uint32_t)y[2], (uint32_t)y[3]);
+            b = make_uint4((uint32_t)y[4], (uint32_t)y[5], (uint32_t)y[6], (uint32_t)y[7]);
+        }
+        const int32_t x[8] = {(int32_t)a.x, (int32_t)a.y, (int32_t)a.z, (int32_t)a.w, (int32_t)b.x, (int32_t)b.y, (int32_t)b.z, (int32_t)b.w};
+        if (j * 8 + 8 <= n) {
+#pragma unroll
+            for (int t = 0; t < 8; ++t) f(j * 8 + t, ((uint32_t)x[t] << sh) ^ ((uint32_t)(x[t] >> 31) & sm));
+        } else {
+#pragma unroll
+            for (int t = 0; t < 8; ++t)
+                if (j * 8 + t < n) f(j * 8 + t, ((uint32_t)x[t] << sh) ^ ((uint32_t)(x[t] >> 31) & sm));
+        }
+    }
+}
+
+__device__ __forceinline__ uint32_t last_mapped(const LaneBlock &B)      // the block's last (non-zero) symbol, mapped
+{
+    const int32_t x = B.cnt > 0 ? __ldg(B.sym + B.cnt - 1) : 0;
+    return B.flag_signed ? s2u(x) : (uint32_t)x;
+}
+
+// code length of the block from state st (in/out)
+__device__ __forceinline__ void count_lane_sym(const LaneBlock &B, State &st, uint32_t &bits_out)
+{
+    SymState t;
+    t.kP = st.kP; t.kRP = st.kRP; t.m = 0;
+    uint32_t bits = 0;
+    if (B.gap0 && B.cnt > 0) {
+        CountSink z{0};
+        sym_begin(t, B.gap0, z);
+        bits = z.bits;
+    }
+    walk_symbols(B, [&](int, uint32_t u) { sym_count(t, u, bits); });
+    State s;
+    s.kP = t.kP; s.kRP = t.kRP;
+    if (B.is_tail) {
+        CountSink k{0};
+        code_tail(s, B.tail_zeros, B.cnt > 0 && sym_tail_quirk(t, last_mapped(B)), k);
+        bits += k.bits;
+    }
+    st = s;
+    bits_out = bits;
 }
 
 // Code lengths of the lane's block for NC candidate start states side by side.  s[] in/out.  The candidates are
@@ -228,6 +336,10 @@ __device__ __forceinline__ LaneBlock lane_block(const uint2 *__restrict__ ev, co
 // pays by NC).
 template <int NC> __device__ __forceinline__ void count_lane(const LaneBlock &B, State *s_io, uint32_t *bits_out)
 {
+    if (NC == 1 && B.sym) {                                  // (warp-uniform: a chunk belongs to one channel)
+        count_lane_sym(B, s_io[0], bits_out[0]);
+        return;
+    }
     const int lane = B.slot;
     int kP[NC], kRP[NC];
     uint32_t bits[NC];
@@ -572,7 +684,7 @@ __device__ __forceinline__ uint32_t word_of(const uint4 &a, const uint4 &b, int 
 }
 
 // channels that are mostly non-zero run with one candidate (they re-synchronise through k_P = 0 within a block)
-__device__ __forceinline__ bool channel_is_dense(const ChanInfo &I, const Geometry &G) { return (int64_t)I.events * 2 >= G.n; }
+__device__ __forceinline__ bool channel_is_dense(const ChanInfo &I, const Geometry &) { return I.dense != 0; }
 
 // ---- A: speculate ----------------------------------------------------------------------------------------
 constexpr int SPEC_WARPS = 4;        // table / emit passes: chunks per CTA
@@ -659,7 +771,7 @@ __device__ __forceinline__ void speculate_chunk(const Geometry &G, const ChanInf
 // one launch for both kinds of channel (blockIdx.z): the few chunks of the sparse channels (z = 0, scheduled first:
 // one chunk per CTA, bound by the latency of their chains) run under the many chunks of the dense channels
 // (z = 1: 8 chunks per CTA, bound by issue slots)
-__global__ void __launch_bounds__(32 * SOLVE_WARPS) rlgr_speculate_kernel(Geometry G, const ChanInfo *__restrict__ info,
+__global__ void __launch_bounds__(32 * SOLVE_WARPS, 4) rlgr_speculate_kernel(Geometry G, const ChanInfo *__restrict__ info,
                                                                          const uint2 *__restrict__ ev, int sweep,
                                                                          const uint4 *__restrict__ rec_prev, uint4 *__restrict__ rec,
                                                                          uint4 *__restrict__ lanerec, unsigned long long *stats)
@@ -740,19 +852,22 @@ __global__ void __launch_bounds__(32 * SPEC_WARPS) rlgr_table_kernel(Geometry G,
                                                                     uint32_t *__restrict__ tables, uint32_t *__restrict__ headers)
 {
     const int ch = blockIdx.y;
-    const int64_t b = (int64_t)blockIdx.x * SPEC_WARPS + (threadIdx.x >> 5);
     const int lane = threadIdx.x & 31;
     const ChanInfo I = info[ch];
-    if (b >= (int64_t)I.nblocks || channel_is_dense(I, G)) return;
+    if (channel_is_dense(I, G)) return;
+    // (a grid-stride loop over the channel's blocks: the launch of one CTA per 4 blocks cost 66 us on the 1 M scene,
+    // where every channel is dense and every CTA returned at once)
+    for (int64_t b = (int64_t)blockIdx.x * SPEC_WARPS + (threadIdx.x >> 5); b < (int64_t)I.nblocks; b += (int64_t)gridDim.x * SPEC_WARPS) {
     const int64_t w = b / CHUNK_LANES;
     const int l = (int)(b - w * CHUNK_LANES) + 1;
     if (!chunk_suspect(rec, (size_t)ch * G.W + w, w)) {
         if (lane == 0) headers[(size_t)ch * G.nsb + b] = TAB_NO_WINDOW;
-        return;
+        continue;
     }
     LaneBlock B;
     B.base = (const uint4 *)(ev + ((size_t)ch * G.W + w) * CHUNK_SLOTS);
     B.slot = l;
+    B.sym = nullptr; B.gap0 = 0; B.pos0 = 0; B.vec = 0; B.flag_signed = G.flag_signed; B.avail = 0;
     int64_t cnt = (int64_t)I.events - b * EV_BLOCK;
     B.cnt = (int)(cnt < 0 ? 0 : (cnt > EV_BLOCK ? EV_BLOCK : cnt));
     B.is_tail = b == (int64_t)I.nblocks - 1;
@@ -771,6 +886,7 @@ __global__ void __launch_bounds__(32 * SPEC_WARPS) rlgr_table_kernel(Geometry G,
     out.z = pack_state(st[2]) | (bits[2] << 16); out.w = pack_state(st[3]) | (bits[3] << 16);
     ((uint4 *)T)[lane] = out;
     if (lane == 0) headers[(size_t)ch * G.nsb + b] = window;
+    }
 }
 
 // chunk tables: uint2 [channel][chunk][128] = (end state or TAB_DEAD, code length of the chunk)
@@ -969,8 +1085,8 @@ __global__ void __launch_bounds__(256) rlgr_zero_kernel(uint8_t *__restrict__ st
 // stream; words it shares with its neighbours are OR-ed atomically, the others stored.
 struct BitSink {
     uint32_t *words;
-    int64_t cap_words;
-    int64_t wi;           // index of the word being assembled
+    uint32_t cap_words;   // (a slot holds < 2^31 words: n < 2^31 symbols, 4 n + 64 bytes at most)
+    uint32_t wi;          // index of the word being assembled
     uint64_t acc;
     unsigned nb;          // bits in acc (the first word starts with begin % 32 zero bits that are not ours)
     bool shared_word;     // the word being assembled has bits of the previous lane
@@ -978,8 +1094,8 @@ struct BitSink {
     __device__ __forceinline__ void init(uint8_t *stream, int64_t slot_bytes, unsigned long long begin_bit)
     {
         words = (uint32_t *)stream;
-        cap_words = slot_bytes >> 2;
-        wi = (int64_t)(begin_bit >> 5);
+        cap_words = (uint32_t)(slot_bytes >> 2);
+        wi = (uint32_t)(begin_bit >> 5);
         nb = (unsigned)(begin_bit & 31);
         acc = 0;
         shared_word = nb != 0;
@@ -1043,8 +1159,38 @@ __global__ void __launch_bounds__(32 * SPEC_WARPS) rlgr_emit_kernel(Geometry G, 
     BitSink sink;
     sink.init(streams + (size_t)ch * slot_bytes, slot_bytes, begin);
     uint2 *sync = sync_index ? sync_index + (size_t)ch * sync_entries : nullptr;
-    int64_t pos = -1;                                      // symbol index of the previous event
     bool quirk = false;
+    // first event of its 512-symbol range: where (bit offset, state) the coder stands before it
+    auto sync_entry = [&](int64_t np) {
+        const unsigned long long at = sink.bit_pos();
+        const uint32_t hi = (uint32_t)((at >> 32) & 0x7f) | ((uint32_t)(s.kP & 0x7f) << 7) |
+                            ((uint32_t)(s.kRP & 0xff) << 14) | ((uint32_t)(np & (SYNC_RANGE - 1)) << 22);
+        sync[np >> SYNC_SHIFT] = make_uint2((uint32_t)at, hi);
+    };
+    if (B.sym) {                                           // dense channel: symbol by symbol, straight from q
+        // sync index: the block's first event is the first of its 512-symbol range iff the zeros pending in front of the
+        // block reach back to the start of the range (ranges start at block boundaries); the coder stands before that
+        // event in the block's start state at the block's first bit
+        bool want_sync = sync && B.cnt > 0 && B.gap0 >= (uint32_t)(B.pos0 & (SYNC_RANGE - 1));
+        const unsigned long long at0 = begin;
+        const State s0 = s;
+        SymState t;
+        t.kP = s.kP; t.kRP = s.kRP; t.m = 0;
+        if (B.gap0 && B.cnt > 0) sym_begin(t, B.gap0, sink);
+        walk_symbols(B, [&](int i, uint32_t u) {
+            if (want_sync && u != 0) {
+                const int64_t np = B.pos0 + i;
+                const uint32_t hi = (uint32_t)((at0 >> 32) & 0x7f) | ((uint32_t)(s0.kP & 0x7f) << 7) |
+                                    ((uint32_t)(s0.kRP & 0xff) << 14) | ((uint32_t)(np & (SYNC_RANGE - 1)) << 22);
+                sync[np >> SYNC_SHIFT] = make_uint2((uint32_t)at0, hi);
+                want_sync = false;
+            }
+            sym_emit(t, u, sink);
+        });
+        quirk = B.cnt > 0 && sym_tail_quirk(t, last_mapped(B));
+        s.kP = t.kP; s.kRP = t.kRP;
+    } else {
+    int64_t pos = -1;                                      // symbol index of the previous event
     const int units = (B.cnt + EV_GROUP - 1) / EV_GROUP;
     uint4 a1, b1, a2, b2;                                   // two units requested ahead, as in count_lane
     a1 = b1 = a2 = b2 = make_uint4(0u, 0u, 0u, 0u);
@@ -1060,16 +1206,11 @@ __global__ void __launch_bounds__(32 * SPEC_WARPS) rlgr_emit_kernel(Geometry G, 
         for (int t = 0; t < 4; ++t)
             if (j * EV_GROUP + t < B.cnt) {
                 const int64_t np = pos + (int64_t)g[t] + 1;
-                if (sync && (np >> SYNC_SHIFT) != (pos >> SYNC_SHIFT)) {
-                    // first event of its 512-symbol range: where (bit offset, state) the coder stands before it
-                    const unsigned long long at = sink.bit_pos();
-                    const uint32_t hi = (uint32_t)((at >> 32) & 0x7f) | ((uint32_t)(s.kP & 0x7f) << 7) |
-                                        ((uint32_t)(s.kRP & 0xff) << 14) | ((uint32_t)(np & (SYNC_RANGE - 1)) << 22);
-                    sync[np >> SYNC_SHIFT] = make_uint2((uint32_t)at, hi);
-                }
+                if (sync && (np >> SYNC_SHIFT) != (pos >> SYNC_SHIFT)) sync_entry(np);
                 pos = np;
                 quirk = emit_event(s, g[t], u[t], sink);
             }
+    }
     }
     if (B.is_tail) code_tail(s, B.tail_zeros, quirk, sink);
     sink.finish();
@@ -1259,8 +1400,11 @@ RAHT_API int raht_rlgr_encode(const int32_t *q, int64_t n, int64_t ld, int nch, 
     }
     Geometry G;
     G.n = n; G.ld = ld; G.nsb = sym_blocks_of(n); G.W = chunk_slots_of(n); G.nch = nch; G.flag_signed = flag_signed;
+    G.q = q;
+    G.vec = (((uintptr_t)q & 15) == 0 && (ld % 4) == 0) ? 1 : 0;
     char *ws = (char *)workspace;
     int32_t *lastnz = (int32_t *)(ws + L.off_lastnz);
+    G.lastnz = lastnz;
     uint32_t *cnt = (uint32_t *)(ws + L.off_cnt);
     ChanInfo *info = (ChanInfo *)(ws + L.off_info);
     uint32_t *blockpos = (uint32_t *)(ws + L.off_blockpos);
@@ -1280,12 +1424,12 @@ RAHT_API int raht_rlgr_encode(const int32_t *q, int64_t n, int64_t ld, int nch, 
     const unsigned groups = (unsigned)((G.nsb + 32 * K1_WARPS - 1) / (32 * K1_WARPS));
     (raht_count_launches(1), rlgr_count_kernel)<<<dim3(groups, nch), 32 * K1_WARPS, 0, st>>>(q, G, cnt, lastnz);
     (raht_count_launches(1), rlgr_scan_kernel)<<<nch, 1024, 0, st>>>(G, cnt, lastnz, info);
-    (raht_count_launches(1), rlgr_scatter_kernel)<<<dim3(groups, nch), 32 * K1_WARPS, 0, st>>>(q, G, cnt, lastnz, ev, blockpos);
+    (raht_count_launches(1), rlgr_scatter_kernel)<<<dim3(groups, nch), 32 * K1_WARPS, 0, st>>>(q, G, cnt, lastnz, ev, blockpos, info);
     const dim3 cgrid((unsigned)((G.W + SPEC_WARPS - 1) / SPEC_WARPS), nch);
     const dim3 sgrid((unsigned)G.W, nch, 2);                 // z = 0: a sparse chunk per CTA; z = 1: 8 dense chunks per CTA (the rest exit)
     (raht_count_launches(1), rlgr_speculate_kernel)<<<sgrid, 32 * SOLVE_WARPS, 0, st>>>(G, info, ev, 0, nullptr, rec0, lanerec, stats);
     (raht_count_launches(1), rlgr_speculate_kernel)<<<sgrid, 32 * SOLVE_WARPS, 0, st>>>(G, info, ev, 1, rec0, rec, lanerec, stats);
-    const dim3 bgrid((unsigned)((G.nsb + SPEC_WARPS - 1) / SPEC_WARPS), nch);
+    const dim3 bgrid((unsigned)min((int64_t)192, (G.nsb + SPEC_WARPS - 1) / SPEC_WARPS), nch);    // grid-stride over the blocks
     (raht_count_launches(1), rlgr_table_kernel)<<<bgrid, 32 * SPEC_WARPS, 0, st>>>(G, info, ev, rec, lanerec, tables, headers);
     (raht_count_launches(1), rlgr_chunk_table_kernel)<<<cgrid, 32 * SPEC_WARPS, 0, st>>>(G, info, tables, headers, ctab);
     (raht_count_launches(1), rlgr_resolve_kernel)<<<nch, 32 * SOLVE_WARPS, 0, st>>>(G, info, ev, rec, lanerec, chunkoff, slot_bytes, nbytes,
@@ -1323,6 +1467,7 @@ RAHT_API int raht_rlgr_decode(const uint8_t *streams, int64_t slot_bytes, const 
     cudaStream_t st = (cudaStream_t)stream;
     Geometry G;
     G.n = n; G.ld = ld; G.nsb = sym_blocks_of(n); G.W = chunk_slots_of(n); G.nch = nch; G.flag_signed = flag_signed;
+    G.q = nullptr; G.lastnz = nullptr; G.vec = 0;
     if (sync_index) {                                        // (writes every symbol: no memset)
         const int64_t entries = raht_rlgr_sync_entries(n);
         const dim3 grid((unsigned)((entries + DEC_THREADS - 1) / DEC_THREADS), nch);

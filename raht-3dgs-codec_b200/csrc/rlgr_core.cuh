@@ -260,6 +260,105 @@ template <class Sink> RL_HD bool emit_event(State &s, uint32_t g, uint32_t u, Si
     return k != 0 && v == 0;
 }
 
+// ---- dense channels: the coder as a per-SYMBOL machine -----------------------------------------------------
+// membuf.cpp:340-423 symbol by symbol, branch-free where the lanes of a warp would diverge: the state is
+// (k_P, k_RP, m) with m = zeros of the open partial run.  A lane block of a dense channel is a range of SYMBOLS that
+// ends with a non-zero symbol (an event boundary: m = 0 there, so blocks still hand on (k_P, k_RP) only); the zeros
+// pending in front of the block are coded first (sym_begin), which leaves the run counter the block starts with.
+// Every lane of a warp does the same work per symbol, whatever the symbol is -- the event form above serialises the
+// lanes that sit in a zero run, in run mode or in an escape against those that do not.
+struct SymState {
+    int kP, kRP;
+    uint32_t m;
+};
+
+template <class Sink> RL_HD void sym_begin(SymState &t, uint32_t gap0, Sink &sink)
+{
+    State s;
+    s.kP = t.kP; s.kRP = t.kRP;
+    t.m = gap0 ? code_zeros(s, gap0, sink, (bool *)nullptr) : 0u;
+    t.kP = s.kP; t.kRP = s.kRP;
+}
+
+RL_HD uint32_t rl_shr_clamp(uint32_t v, uint32_t sh)                // v >> sh with sh in 0 .. 32 (32 -> 0)
+{
+#if defined(__CUDA_ARCH__)
+    return __funnelshift_rc(v, 0u, sh);
+#else
+    return sh > 31 ? 0u : (v >> sh);
+#endif
+}
+RL_HD int rl_max0(int x) { return x < 0 ? 0 : x; }
+
+// One symbol, code length only.  u = the mapped symbol (_s2u; 0 for a zero).  Written as straight-line selects: every
+// lane of a warp executes the same ~35 instructions whatever its symbol and mode are.
+RL_HD void sym_count(SymState &t, uint32_t u, uint32_t &bits)
+{
+    const uint32_t k = (uint32_t)t.kP >> 2;
+    const uint32_t kR = (uint32_t)t.kRP >> 2;                          // 0 .. 32
+    const bool nz = u != 0, run = t.kP >= RL_L;
+    const bool coded = nz || !run;                                      // a Golomb-Rice code is written (:359, :393)
+    const uint32_t v = u - (run ? 1u : 0u);                             // run mode codes u - 1 (:355)
+    const uint32_t p = rl_shr_clamp(v, kR);
+    const uint32_t gr = p < 32 ? p + 1 + kR : 64u;                      // grWrite (:242-256)
+    const uint32_t m1 = t.m + 1;
+    const bool full = run && !nz && m1 == (1u << (k & 31));             // a complete run: one 1 bit (:383-389)
+    bits += (coded ? gr + (run ? 1u + k : 0u) : 0u) + (full ? 1u : 0u);
+    const int pc = (int)(p > 256u ? 256u : p);
+    const int up = t.kRP + pc - 1;
+    const int adapted = p ? (up > RL_KRP_MAX ? RL_KRP_MAX : up) : rl_max0(t.kRP - 2);
+    t.kRP = coded ? adapted : t.kRP;
+    const int grow = run ? (full ? t.kP + RL_U1 : t.kP) : t.kP + RL_U0;
+    t.kP = nz ? rl_max0(t.kP - 1) : grow;                               // D0 == D1 == 1
+    t.m = (run && !nz && !full) ? m1 : 0u;
+}
+
+// The tail quirk (membuf.cpp:416-419 looks at the k and the decremented u of the LAST symbol) for a block that ends
+// with the channel's last non-zero symbol u_last, from the state AFTER it: the symbol was coded in run mode
+// (k_P >= 4 before it, i.e. k_P >= 3 after its decrement) with u - 1 == 0.
+RL_HD bool sym_tail_quirk(const SymState &after, uint32_t u_last) { return u_last == 1u && after.kP >= RL_L - 1; }
+
+// The same symbol with its bits written to sink (put(value, len <= 32)).  The common case -- run prefix, unary part
+// and remainder together fit 32 bits -- is one put.
+template <class Sink> RL_HD void sym_emit(SymState &t, uint32_t u, Sink &sink)
+{
+    const uint32_t k = (uint32_t)t.kP >> 2;
+    const uint32_t kR = (uint32_t)t.kRP >> 2;
+    const bool run = t.kP >= RL_L;
+    if (run && u == 0) {                                                // a zero in run mode (:382-390)
+        const uint32_t m1 = t.m + 1;
+        if (m1 == (1u << (k & 31))) {
+            sink.put(1, 1);
+            t.kP += RL_U1;
+            t.m = 0;
+        } else t.m = m1;
+        return;
+    }
+    const uint32_t v = u - (run ? 1u : 0u);
+    const uint32_t p = rl_shr_clamp(v, kR);
+    const uint32_t plen = run ? 1u + k : 0u;                            // `0` then m in k bits (:357-358)
+    const uint32_t glen = p + 1 + kR;                                   // p ones, a zero, kR low bits (:242-256)
+    if (p < 32 && glen + plen <= 32) {                                  // (kR <= 31 here)
+        const uint32_t ones = ((1u << p) - 1u) << 1;
+        const uint32_t low = v & ~(0xffffffffu << kR);
+        sink.put((uint64_t)((((run ? t.m : 0u) << (p + 1)) | ones) << kR | low), glen + plen);
+    } else {
+        if (run) sink.put(t.m, plen);
+        if (p < 32) {
+            sink.put((((uint64_t)1) << (p + 1)) - 2, p + 1);
+            sink.put(kR > 31 ? (uint64_t)v : (uint64_t)(v & ((1u << kR) - 1u)), kR);
+        } else {
+            sink.put(0xffffffffull, 32);                                // escape: 32 ones, then v in 32 bits
+            sink.put((uint64_t)v, 32);
+        }
+    }
+    const int pc = (int)(p > 256u ? 256u : p);
+    const int up = t.kRP + pc - 1;
+    t.kRP = p ? (up > RL_KRP_MAX ? RL_KRP_MAX : up) : rl_max0(t.kRP - 2);
+    t.kP = u ? rl_max0(t.kP - 1) : t.kP + RL_U0;                        // (u == 0 only in no-run mode here)
+    t.m = 0;
+}
+
 // ---- decoder ---------------------------------------------------------------------------------------------
 // MSB-first reader over big-endian 32-bit words; acc holds the next nbits bits left-aligned.
 // Word sources: next() returns the following 32 bits of the stream (big-endian order restored).

@@ -136,10 +136,18 @@ __global__ void __launch_bounds__(OR_THREADS) order_scatter_kernel(const uint8_t
 constexpr int PB_THREADS = 256;
 constexpr int PB_WARPS = PB_THREADS / 32;
 
-__global__ void plan_init_kernel(PlanDev P) { *P.bump = (unsigned int)P.slots0; }
+// arrive[]: one counter per upper tile = how many of its child tiles have been planned
+__global__ void __launch_bounds__(256) plan_init_kernel(PlanDev P)
+{
+    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i == 0) *P.bump = (unsigned int)P.slots0;
+    if (i < P.tiles_total) P.arrive[i] = 0u;
+}
 
-__global__ void __launch_bounds__(PB_THREADS)
-plan_tile_kernel(PlanDev P, int stage, const uint8_t *__restrict__ level, double *__restrict__ w)
+// One tile of one stage.  Upper tiles read what OTHER CTAs of the same launch wrote (the deferred lists of their child
+// tiles): those loads go to L2 (__ldcg), behind the fence / counter hand-over of plan_kernel.
+__device__ __forceinline__ void plan_tile(const PlanDev &P, int stage, int64_t tile, const uint8_t *__restrict__ level,
+                                          double *__restrict__ w)
 {
     __shared__ uint32_t s_orig[PLAN_UP_CAP + 1];   // original row of each entry (+ virtual end of the cloud)
     __shared__ uint16_t s_s[PLAN_UP_CAP];          // local index of the left row, 0xffff = not schedulable here
@@ -152,7 +160,6 @@ plan_tile_kernel(PlanDev P, int stage, const uint8_t *__restrict__ level, double
     __shared__ uint16_t s_pend[PLAN_UP_CAP];       // entries whose partners lie far away
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const int64_t tile = blockIdx.x;
     const int64_t gt = P.tile_base[stage] + tile;
     const bool last = tile == P.tiles[stage] - 1;
     const bool multi = P.tiles[stage] > 1;
@@ -173,7 +180,7 @@ plan_tile_kernel(PlanDev P, int stage, const uint8_t *__restrict__ level, double
         const int64_t cbase = P.tile_base[stage - 1];
         if (tid < 32) {                                      // entries per child tile: eight independent loads, one scan
             int cnt = 0;
-            if (tid < PLAN_FANIN && c0 + tid < P.tiles[stage - 1]) cnt = min((int)P.hdr[cbase + c0 + tid].n_def, PLAN_DEFER_MAX);
+            if (tid < PLAN_FANIN && c0 + tid < P.tiles[stage - 1]) cnt = min((int)__ldcg(&P.hdr[cbase + c0 + tid].n_def), PLAN_DEFER_MAX);
             int incl = cnt;
 #pragma unroll
             for (int o = 1; o < PLAN_FANIN; o <<= 1) {
@@ -189,8 +196,8 @@ plan_tile_kernel(PlanDev P, int stage, const uint8_t *__restrict__ level, double
             const int cnt = s_off[c + 1] - s_off[c];
             const size_t src = (size_t)(cbase + c0 + c) * PLAN_DEFER_MAX;
             for (int j = tid; j < cnt; j += PB_THREADS) {
-                s_orig[s_off[c] + j] = P.def_rows[src + j];
-                s_lev[s_off[c] + j] = P.def_lev[src + j];
+                s_orig[s_off[c] + j] = __ldcg(P.def_rows + src + j);
+                s_lev[s_off[c] + j] = __ldcg(P.def_lev + src + j);
             }
         }
     }
@@ -325,9 +332,38 @@ plan_tile_kernel(PlanDev P, int stage, const uint8_t *__restrict__ level, double
     }
 }
 
+// The whole hierarchy in ONE launch of tiles[0] CTAs: a CTA plans its stage-0 tile, then signs in at the parent tile's
+// counter; the CTA that signs in last (all PLAN_FANIN children are done, their deferred lists fenced to L2) goes on to
+// plan the parent, and so on up to the single top tile.  Nobody waits, so no co-residency is needed.  (Round 1 launched
+// one kernel per stage: 6-7 dependent launches of ~20 us for a hierarchy whose upper stages have 977 / 123 / 16 / 2 / 1
+// tiles at 1 M rows.)
+__global__ void __launch_bounds__(PB_THREADS) plan_kernel(PlanDev P, const uint8_t *__restrict__ level, double *__restrict__ w)
+{
+    __shared__ int s_last;
+    int stage = 0;
+    int64_t tile = blockIdx.x;
+    for (;;) {
+        plan_tile(P, stage, tile, level, w);
+        if (stage + 1 >= P.n_stages) break;
+        const int64_t parent = tile / PLAN_FANIN;
+        const int64_t children = min((int64_t)PLAN_FANIN, P.tiles[stage] - parent * PLAN_FANIN);
+        __threadfence();                                   // this tile's header and deferred list, before the sign-in
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            const unsigned prev = atomicAdd(P.arrive + P.tile_base[stage + 1] + parent, 1u);
+            s_last = prev + 1 == (unsigned)children;
+            __threadfence();
+        }
+        __syncthreads();
+        if (!s_last) break;
+        ++stage;
+        tile = parent;
+    }
+}
+
 struct PlanLayout {
     PlanDev d;          // sizes and stage table filled in; pointers as byte offsets from the workspace start
-    size_t off_hdr, off_def_rows, off_def_local, off_def_lev, off_sched, off_ab, off_bump, total;
+    size_t off_hdr, off_def_rows, off_def_local, off_def_lev, off_sched, off_ab, off_bump, off_arrive, total;
 };
 
 PlanLayout plan_layout(int64_t n, int tile_rows)
@@ -358,6 +394,7 @@ PlanLayout plan_layout(int64_t n, int tile_rows)
     L.off_sched = o; o += align_up((size_t)(d.slots0 + n) * 4, 256);
     L.off_ab = o; o += align_up((size_t)(d.slots0 + n) * 16, 256);
     L.off_bump = o; o += 256;
+    L.off_arrive = o; o += align_up((size_t)base * 4, 256);
     L.total = o;
     return L;
 }
@@ -465,11 +502,11 @@ RAHT_API int raht_plan_create(const uint8_t *level, int64_t n, int tile_rows, do
     P->d.sched = (uint32_t *)(ws + L.off_sched);
     P->d.ab = (double2 *)(ws + L.off_ab);
     P->d.bump = (unsigned int *)(ws + L.off_bump);
+    P->d.arrive = (unsigned int *)(ws + L.off_arrive);
     if (n > 0) {
         cudaStream_t st = (cudaStream_t)stream;
-        (raht_count_launches(1), plan_init_kernel)<<<1, 1, 0, st>>>(P->d);
-        for (int k = 0; k < P->d.n_stages; ++k)
-            (raht_count_launches(1), plan_tile_kernel)<<<(unsigned)P->d.tiles[k], PB_THREADS, 0, st>>>(P->d, k, level, w);
+        (raht_count_launches(1), plan_init_kernel)<<<(unsigned)((P->d.tiles_total + 255) / 256), 256, 0, st>>>(P->d);
+        (raht_count_launches(1), plan_kernel)<<<(unsigned)P->d.tiles[0], PB_THREADS, 0, st>>>(P->d, level, w);
         cudaError_t e = cudaGetLastError();
         if (e != cudaSuccess) {
             raht_set_error("raht_plan_create: launch: %s", cudaGetErrorString(e));

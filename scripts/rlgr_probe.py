@@ -5,10 +5,10 @@ import os
 import sys
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
-for p in (ROOT, os.path.join(ROOT, "raht-3dgs-codec_b200"), os.path.join(ROOT, "tests")):
+for p in (ROOT, os.path.join(ROOT, "raht-3dgs-codec_b200")):
     sys.path.insert(0, p)
 import torch  # noqa: E402
-import helpers  # noqa: E402
+from raht_b200 import synth as helpers  # noqa: E402
 from raht_b200 import codec, ops  # noqa: E402
 
 n = int(sys.argv[1]) if len(sys.argv) > 1 else 1_000_000

@@ -6,10 +6,10 @@ import os
 import sys
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
-for p in (ROOT, os.path.join(ROOT, "raht-3dgs-codec_b200"), os.path.join(ROOT, "tests")):
+for p in (ROOT, os.path.join(ROOT, "raht-3dgs-codec_b200")):
     sys.path.insert(0, p)
 import torch  # noqa: E402
-import helpers  # noqa: E402
+from raht_b200 import synth as helpers  # noqa: E402
 from raht_b200 import codec  # noqa: E402
 
 args = [a for a in sys.argv[1:] if not a.startswith("--")]

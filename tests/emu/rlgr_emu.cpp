@@ -401,6 +401,98 @@ __attribute__((visibility("default"))) int64_t emu_rlgr_encode(const int32_t *q,
     return sink.overflow ? -nb : nb;
 }
 
+// Dense channels (rlgr.cu: channels with at least half of their symbols non-zero) are coded in SYMBOL space: lane
+// blocks of 128 symbols walked by the per-symbol machine of rlgr_core.cuh (sym_begin / sym_count / sym_emit), a block's
+// start state first guessed from a warm-up over the last `warm` symbols of the block before it.  This entry point runs
+// that path block by block with the state carried exactly (the fixed-point rounds that repair wrong guesses are the
+// same as in emu_rlgr_encode and are not repeated here): it checks the machine, the block-boundary convention
+// (pending zeros are coded by the block that holds the non-zero symbol that ends them; a block stops at its last
+// non-zero symbol), the tail rule, the length bookkeeping (sym_count == bits written by sym_emit) and the sync index.
+// stats[0] = blocks, stats[1] = blocks whose warm-up guess equals the true start state.
+__attribute__((visibility("default"))) int64_t emu_rlgr_encode_dense(const int32_t *q, int64_t n, int flag_signed, uint8_t *out,
+                                                                     int64_t cap, uint32_t *sync, int warm, uint64_t *stats)
+{
+    if (n <= 0) return 0;
+    const int64_t nsb = (n + SYM_BLOCK - 1) / SYM_BLOCK;
+    int64_t lastnz = -1;
+    for (int64_t i = n - 1; i >= 0; --i) if (q[i] != 0) { lastnz = i; break; }
+    const int64_t tail_block = lastnz < 0 ? 0 : lastnz / SYM_BLOCK;
+    const uint32_t tail_zeros = (uint32_t)(n - 1 - lastnz);
+    HostSink sink{out, cap, 0, false};
+    State s = initial_state();
+    int64_t prev_nz = -1;                                         // last non-zero symbol before the block
+    auto mapped = [&](int64_t i) { return q[i] == 0 ? 0u : (flag_signed ? s2u(q[i]) : (uint32_t)q[i]); };
+    for (int64_t b = 0; b <= tail_block && b < nsb; ++b) {
+        const int64_t pos0 = b * SYM_BLOCK;
+        int64_t last = -1;                                        // last non-zero symbol of the block
+        for (int64_t i = std::min<int64_t>(pos0 + SYM_BLOCK, n) - 1; i >= pos0; --i) if (q[i] != 0) { last = i; break; }
+        const int cnt = last < 0 ? 0 : (int)(last - pos0 + 1);
+        const uint32_t gap0 = (uint32_t)(pos0 - 1 - prev_nz);
+        const bool is_tail = b == tail_block;
+        if (stats) {                                              // would the warm-up over the previous block have guessed s?
+            stats[0]++;
+            if (b > 0) {
+                int64_t plast = -1;
+                for (int64_t i = pos0 - 1; i >= pos0 - SYM_BLOCK; --i) if (q[i] != 0) { plast = i; break; }
+                const int pcnt = plast < 0 ? 0 : (int)(plast - (pos0 - SYM_BLOCK) + 1);
+                int from = (pcnt - warm) & ~7;
+                if (from < 0) from = 0;
+                SymState g{RL_KP_INIT, RL_KRP_INIT, 0};
+                uint32_t dummy = 0;
+                for (int i = from; i < pcnt; ++i) sym_count(g, mapped(pos0 - SYM_BLOCK + i), dummy);
+                if (pcnt > 0 ? (g.kP == s.kP && g.kRP == s.kRP) : false) stats[1]++;
+            } else stats[1]++;
+        }
+        // lengths
+        SymState t{s.kP, s.kRP, 0};
+        uint32_t bits = 0;
+        bool quirk = false;
+        if (cnt > 0 || is_tail) {
+            CountSink cs{0};
+            if (cnt > 0) sym_begin(t, gap0, cs);
+            bits = cs.bits;
+            for (int i = 0; i < cnt; ++i) sym_count(t, mapped(pos0 + i), bits);
+            if (cnt > 0 && t.m != 0) return -3000;                // a block ends at an event boundary
+            quirk = cnt > 0 && sym_tail_quirk(t, mapped(pos0 + cnt - 1));
+            if (is_tail) {
+                State st{t.kP, t.kRP};
+                CountSink k{0};
+                code_tail(st, tail_zeros, quirk, k);
+                bits += k.bits;
+            }
+        }
+        // bits
+        const uint64_t begin = sink.pos;
+        SymState e{s.kP, s.kRP, 0};
+        bool q2 = false;
+        // sync index: a block's first event is the first of its 512-symbol range iff the zeros pending in front of the
+        // block reach back to the start of the range (ranges start at block boundaries); the coder stands before that
+        // event in the block's start state at the block's first bit
+        bool want_sync = sync && cnt > 0 && gap0 >= (uint32_t)(pos0 & (SYNC_RANGE - 1));
+        if (cnt > 0) sym_begin(e, gap0, sink);
+        for (int i = 0; i < cnt; ++i) {
+            const int64_t np = pos0 + i;
+            if (want_sync && q[np] != 0) {
+                sync[2 * (np >> SYNC_SHIFT) + 0] = (uint32_t)begin;
+                sync[2 * (np >> SYNC_SHIFT) + 1] = (uint32_t)((begin >> 32) & 0x7f) | ((uint32_t)(s.kP & 0x7f) << 7) |
+                                                   ((uint32_t)(s.kRP & 0xff) << 14) | ((uint32_t)(np & (SYNC_RANGE - 1)) << 22);
+                want_sync = false;
+            }
+            sym_emit(e, mapped(np), sink);
+        }
+        q2 = cnt > 0 && sym_tail_quirk(e, mapped(pos0 + cnt - 1));
+        if (cnt > 0 && (e.kP != t.kP || e.kRP != t.kRP || e.m != 0 || q2 != quirk)) return -3100;
+        if (is_tail) {
+            State st{e.kP, e.kRP};
+            code_tail(st, tail_zeros, q2, sink);
+        }
+        if (sink.pos != begin + bits) return -3200;               // sym_count and sym_emit disagree on the length
+        if (cnt > 0) { s.kP = t.kP; s.kRP = t.kRP; prev_nz = last; }
+    }
+    const int64_t nb = (int64_t)((sink.pos + 7) >> 3);
+    return sink.overflow ? -nb : nb;
+}
+
 // Decoder: out must be zero-filled (n int32).  sync == nullptr: sequential decode from the stream start;
 // else every sync entry is decoded on its own, as the threads of rlgr_decode_indexed_kernel do.
 __attribute__((visibility("default"))) void emu_rlgr_decode(const uint8_t *buf, int64_t nbytes, int64_t n, int flag_signed,
