@@ -29,7 +29,7 @@
 extern "C" {
 #endif
 
-#define RAHT_B200_ABI_VERSION 10
+#define RAHT_B200_ABI_VERSION 11
 
 enum {
     RAHT_OK = 0,
@@ -320,6 +320,64 @@ int raht_streams_pack(const uint8_t *streams, int64_t slot_bytes, const int64_t 
                       void *stream);
 int raht_streams_unpack(const uint8_t *packed, const int64_t *offsets, int nch, uint8_t *streams,
                         int64_t slot_bytes, void *stream);
+
+/* ------------------------------------------------------------------------------------------------
+ * Scene-level calls: one leg of the pipeline per host call.  Same kernels, same order and same
+ * results as the per-operator entry points above (python/test_voxelize_3dgs.py:198-265 for the
+ * front, python/encode_3dgs.py:144-276 for encode / decode); what changes is the host side -- the
+ * launches of a leg are issued back to back from C out of ONE caller-owned workspace (256-byte
+ * aligned device memory), instead of one allocator round trip and one FFI transition per kernel.
+ * The only synchronisation an encode needs is the caller's, between raht_scene_front and
+ * raht_scene_encode: the voxel count sizes the second leg.  Nothing here synchronises.
+ *
+ * events (optional): cudaEvent_t handles, recorded behind the stages of the call in the order
+ *   front:  morton, sort, segments            encode: merge, raht_param, raht, quant_reorder, rlgr_encode
+ *   decode: raht_param_dec, rlgr_decode, dequant_unreorder, iraht, geometry
+ * (NULL entries are skipped), so that the stages can still be timed.
+ * *_pinned_host (optional): PINNED host memory that receives the small results without a copy
+ *   engine (raht_publish_host); valid once the stream has been synchronised.
+ * Two workspaces per encode / decode: the TREE workspace (raht_scene_tree_workspace_bytes) holds what a
+ *   caller may keep next to the coded scene -- level, order_RAGFT, its inverse, w and the plan that
+ *   *plan points into (raht_plan_destroy frees the host handle only); the scratch workspace holds the
+ *   coefficients, the symbols and the coder's workspace and is dead when the call's work is done.
+ * layout_host (optional, 11 x int64): byte offsets of level (nvox x u8), order (nvox x i64), position
+ *   (nvox x i32), w (nvox x f64), the plan workspace and its size IN THE TREE WORKSPACE; of packed
+ *   (nvox x D f32; -1 when the caller supplied packed_out), T (nvox x D of t_dtype), q (D x ld int32),
+ *   ld itself and steps (D x f64) IN THE SCRATCH -- every intermediate can be looked at without a copy.
+ * ------------------------------------------------------------------------------------------------ */
+size_t raht_scene_front_workspace_bytes(int64_t n, int J);
+/* means (n,3) fp32 -> params4 / params_d2 (raht_voxel_params; use_given != 0: quantise against the
+ * caller's vmin_host[3] / width_host), unique_keys (n x u64, first *nvox valid), sort_idx (n x u32:
+ * the stable sort permutation = cluster_indices), cluster_offsets ((n + 1) x i32, first *nvox + 1
+ * valid), *nvox (device int64) and, when given, front_pinned_host[0..8) = nvox, [8..24) = params_d2. */
+int raht_scene_front(const float *means, int64_t n, int J, int use_given, const float *vmin_host,
+                     double width_host, float *params4, double *params_d2, uint64_t *unique_keys,
+                     uint32_t *sort_idx, int32_t *cluster_offsets, int64_t *nvox,
+                     void *front_pinned_host, int32_t *status, void *workspace, size_t workspace_bytes,
+                     void **events, void *stream);
+size_t raht_scene_tree_workspace_bytes(int64_t nvox, int tile_rows);
+size_t raht_scene_encode_workspace_bytes(int64_t nvox, int D, int t_dtype, int own_packed);
+/* D = 11 + color_dim channels [means3 quats4 scales3 opacity1 colors]; steps_host: D doubles (host).
+ * packed_out (nvox x D fp32, optional): the merged attributes (else kept in the workspace).
+ * streams / slot_bytes / nbytes / sync_index / status as raht_rlgr_encode.  results_pinned_host
+ * (8 D + 4 bytes): the D stream lengths, then the status word.                                     */
+int raht_scene_encode(const uint32_t *sort_idx, const int32_t *cluster_offsets, int64_t nvox,
+                      const float *means, const float *quats, const float *scales,
+                      const float *opacities, const float *colors, int color_dim,
+                      const uint64_t *keys, const double *steps_host, int t_dtype, int tile_rows,
+                      void *packed_out, uint8_t *streams, int64_t slot_bytes, int64_t *nbytes,
+                      void *sync_index, int32_t *status, void *results_pinned_host, raht_plan **plan,
+                      int64_t *layout_host, void *tree_workspace, size_t tree_workspace_bytes,
+                      void *workspace, size_t workspace_bytes, void **events, void *stream);
+size_t raht_scene_decode_workspace_bytes(int64_t nvox, int D, int t_dtype);
+/* keys (nvox sorted unique Morton codes) + the D streams -> attributes (nvox x D of t_dtype) and,
+ * when coords != NULL, the voxel coordinates (nvox x 3 fp32).  The tree is rebuilt from the keys.  */
+int raht_scene_decode(const uint64_t *keys, int64_t nvox, int J, const uint8_t *streams,
+                      int64_t slot_bytes, const int64_t *nbytes, const void *sync_index, int D,
+                      const double *steps_host, int t_dtype, int tile_rows, void *attributes,
+                      float *coords, int32_t *status, void *status_pinned_host, raht_plan **plan,
+                      int64_t *layout_host, void *tree_workspace, size_t tree_workspace_bytes,
+                      void *workspace, size_t workspace_bytes, void **events, void *stream);
 
 #ifdef __cplusplus
 }

@@ -54,7 +54,9 @@ struct PlanDev {
     uint32_t *sched;                        // [slots0 + n]
     double2 *ab;                            // [slots0 + n]
     unsigned int *bump;                     // next free upper-stage schedule slot (starts at slots0)
-    unsigned int *arrive;                   // [tiles_total] child tiles planned so far (the hierarchy is built in one launch)
+    unsigned int *arrive;                   // [tiles_total] child tiles that have signed in (plan build, forward transform); zero between launches
+    unsigned int *done;                     // [tiles_total] epoch of the inverse transform that finished the tile
+    unsigned int *ticket;                   // next work item of the inverse transform; zero between launches
 };
 
 struct raht_plan {

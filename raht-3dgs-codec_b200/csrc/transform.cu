@@ -71,15 +71,34 @@ template <typename Tel> struct SmemLayout {
     }
 };
 
+// ---- hand-over between the tiles of one launch (chained kernels below) ------------------------------------------------
+__device__ __forceinline__ unsigned ld_acquire_u32(const unsigned *p)
+{
+    unsigned v;
+    asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    return v;
+}
+__device__ __forceinline__ void st_release_u32(unsigned *p, unsigned v)
+{
+    asm volatile("st.release.gpu.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+__device__ __forceinline__ void bulk_wait0() { asm volatile("cp.async.bulk.wait_group 0;" ::: "memory"); }
+__device__ __forceinline__ void fence_proxy_async_all() { asm volatile("fence.proxy.async;" ::: "memory"); }
+template <typename T> __device__ __forceinline__ T ld_cg(const T *p) { return __ldcg(p); }
+
+// CHAIN (stage0_tile / upper_tile): 0 = a launch per stage (the tile's inputs were written by earlier launches);
+// 1 = forward chain, 2 = inverse chain: rows another CTA of the SAME launch wrote are read from L2 (ld.cg) behind an
+// acquire of that CTA's hand-over, and this tile's own output is fenced before its hand-over.
+enum { CHAIN_NONE = 0, CHAIN_FWD = 1, CHAIN_INV = 2 };
+
 // ---- stage 0: tiles of consecutive rows ------------------------------------------------------------------
 // A: source rows (row-major, Tin).  B: second source for the rows this tile deferred (inverse only: the
 // upper stages have already rewritten them in the output), may be nullptr.  O: destination.
 // FWD: forward butterflies in schedule order, else inverse butterflies in reverse order.
-template <typename Tin, typename Tel, int DT, bool FWD, int QM = QM_NONE>
-__global__ void __launch_bounds__(TR_THREADS)
-transform_stage0_kernel(PlanDev P, const Tin *__restrict__ A, const Tel *B, Tel *O, int D_rt, int use_tma, QuantArgs Q)
+template <typename Tin, typename Tel, int DT, bool FWD, int QM, int CHAIN>
+__device__ __forceinline__ void stage0_tile(const PlanDev &P, int64_t tile, const Tin *__restrict__ A, const Tel *B, Tel *O, int D_rt,
+                                            int use_tma, const QuantArgs &Q, unsigned char *tr_smem, unsigned epoch)
 {
-    extern __shared__ __align__(128) unsigned char tr_smem[];
     const int D = DT ? DT : D_rt;
     const int R = P.tile_rows;
     const SmemLayout<Tel> L(R, D);
@@ -94,7 +113,6 @@ transform_stage0_kernel(PlanDev P, const Tin *__restrict__ A, const Tel *B, Tel 
     uint16_t *s_def = (uint16_t *)(tr_smem + L.off_def);
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const int64_t tile = blockIdx.x;
     const int64_t base = tile * R;
 
     if (tid < (int)(sizeof(TileHdr) / 4)) ((uint32_t *)s_hdr)[tid] = ((const uint32_t *)(P.hdr + tile))[tid];
@@ -155,13 +173,25 @@ transform_stage0_kernel(PlanDev P, const Tin *__restrict__ A, const Tel *B, Tel 
     constexpr int PF_ITEMS = 8;
     Tel pf[PF_ITEMS];
     const int n_patch = (B != nullptr) ? (int)s_hdr->n_def * D : 0;
+    if constexpr (CHAIN == CHAIN_INV) {
+        // the rows this tile deferred are written by its parent tile in THIS launch: wait for its hand-over (the bulk
+        // load of the tile and the schedule loads above are already in flight)
+        if (B != nullptr && P.n_stages > 1) {
+            if (tid == 0) {
+                const unsigned *flag = P.done + P.tile_base[1] + tile / PLAN_FANIN;
+                while (ld_acquire_u32(flag) != epoch) __nanosleep(64);
+            }
+            __syncthreads();
+        }
+    }
     if (n_patch) {
 #pragma unroll
         for (int u = 0; u < PF_ITEMS; ++u) {
             const int idx = tid + u * TR_THREADS;
             if (idx < n_patch) {
                 const int j = idx / D, c = idx - j * D;
-                pf[u] = B[(size_t)(base + s_def[j]) * D + c];
+                const Tel *src = B + (size_t)(base + s_def[j]) * D + c;
+                pf[u] = CHAIN == CHAIN_INV ? ld_cg(src) : *src;
             }
         }
     }
@@ -219,7 +249,8 @@ transform_stage0_kernel(PlanDev P, const Tin *__restrict__ A, const Tel *B, Tel 
         }
         for (int idx = tid + PF_ITEMS * TR_THREADS; idx < n_patch; idx += TR_THREADS) {
             const int j = idx / D, c = idx - j * D;
-            s_rows[(int)s_def[j] * D + c] = B[(size_t)(base + s_def[j]) * D + c];
+            const Tel *src = B + (size_t)(base + s_def[j]) * D + c;
+            s_rows[(int)s_def[j] * D + c] = CHAIN == CHAIN_INV ? ld_cg(src) : *src;
         }
     }
     __syncthreads();
@@ -276,13 +307,22 @@ transform_stage0_kernel(PlanDev P, const Tin *__restrict__ A, const Tel *B, Tel 
                 bulk_s2g(dst + off, src + off, sz);
             }
             bulk_commit();
-            bulk_wait_read0();
+            if constexpr (CHAIN == CHAIN_NONE) bulk_wait_read0();
+            else { bulk_wait0(); fence_proxy_async_all(); }   // the stores must have landed before the hand-over
         }
     } else {
         Tel *dst = O + base * D;
         const int n_el = n_rows * D;
         for (int i = tid; i < n_el; i += TR_THREADS) dst[i] = s_rows[i];
     }
+}
+
+template <typename Tin, typename Tel, int DT, bool FWD, int QM = QM_NONE>
+__global__ void __launch_bounds__(TR_THREADS)
+transform_stage0_kernel(PlanDev P, const Tin *__restrict__ A, const Tel *B, Tel *O, int D_rt, int use_tma, QuantArgs Q)
+{
+    extern __shared__ __align__(128) unsigned char tr_smem[];
+    stage0_tile<Tin, Tel, DT, FWD, QM, CHAIN_NONE>(P, (int64_t)blockIdx.x, A, B, O, D_rt, use_tma, Q, tr_smem, 0u);
 }
 
 // ---- stages >= 1: tiles of gathered rows -------------------------------------------------------------------
@@ -297,11 +337,10 @@ constexpr int UP_ELEMS = 8192;     // row elements staged per pass
 constexpr int UP_GROUPS_MAX = 16;
 constexpr int UP_GROUPS_MANY = 2, UP_ELEMS_MANY = 2560;      // stages with >= 2 tiles per SM (sweep: scripts/gpu_upper_sweep.sh)
 
-template <typename Tel, bool FWD>
-__global__ void __launch_bounds__(TR_THREADS)
-transform_upper_kernel(PlanDev P, int stage, const Tel *A, const Tel *B, Tel *O, int D, int up_elems)
+template <typename Tel, bool FWD, int CHAIN>
+__device__ __forceinline__ void upper_tile(const PlanDev &P, int stage, int64_t tile, const Tel *A, const Tel *B, Tel *O, int D,
+                                           int up_elems, int cb, int ce, unsigned char *tr_smem)
 {
-    extern __shared__ __align__(128) unsigned char tr_smem[];
     Tel *s_rows = (Tel *)tr_smem;                                          // up_elems
     Tel *s_ab = s_rows + up_elems;                                         // 2 * PLAN_UP_CAP
     uint32_t *s_sched = (uint32_t *)(s_ab + 2 * PLAN_UP_CAP);              // PLAN_UP_CAP
@@ -311,7 +350,6 @@ transform_upper_kernel(PlanDev P, int stage, const Tel *A, const Tel *B, Tel *O,
     __shared__ int s_off[PLAN_FANIN + 1];
 
     const int tid = threadIdx.x;
-    const int64_t tile = blockIdx.x;
     const int64_t gt = P.tile_base[stage] + tile;
     if (tid < (int)(sizeof(TileHdr) / 4)) ((uint32_t *)&s_hdr)[tid] = ((const uint32_t *)(P.hdr + gt))[tid];
     const int64_t c0 = tile * PLAN_FANIN;
@@ -354,8 +392,6 @@ transform_upper_kernel(PlanDev P, int stage, const Tel *A, const Tel *B, Tel *O,
     __syncthreads();
 
     using AR = Arith<Tel>;
-    const int per = (D + (int)gridDim.y - 1) / (int)gridDim.y;            // channels of this CTA's group
-    const int cb = (int)blockIdx.y * per, ce = min(D, cb + per);
     if (cb >= ce) return;
     int DS = up_elems / n_rows;
     if (DS > ce - cb) DS = ce - cb;
@@ -371,8 +407,9 @@ transform_upper_kernel(PlanDev P, int stage, const Tel *A, const Tel *B, Tel *O,
                 const int i = i0 + u * TR_THREADS;
                 if (i < n_el) {
                     const int j = i / dn, c = i - j * dn;
-                    const Tel *src = (B && s_flag[j]) ? B : A;
-                    v[u] = src[(size_t)s_rowid[j] * D + d0 + c];
+                    const Tel *src = ((B && s_flag[j]) ? B : A) + (size_t)s_rowid[j] * D + d0 + c;
+                    // forward chain: every gathered row was written in this launch; inverse chain: those from B (the parent's)
+                    v[u] = (CHAIN == CHAIN_FWD || (CHAIN == CHAIN_INV && B && s_flag[j])) ? ld_cg(src) : *src;
                 }
             }
 #pragma unroll
@@ -390,15 +427,15 @@ transform_upper_kernel(PlanDev P, int stage, const Tel *A, const Tel *B, Tel *O,
                 const int c = idx - (idx / dn) * dn;
                 const uint32_t ent = s_sched[e];
                 const int r = ent & 4095, s = (ent >> 12) & 4095;
-                const Tel ca = s_ab[2 * e], cb = s_ab[2 * e + 1];
+                const Tel ca = s_ab[2 * e], cbv = s_ab[2 * e + 1];
                 Tel *p0 = s_rows + s * dn + c, *p1 = s_rows + r * dn + c;
                 const Tel x0 = *p0, x1 = *p1;
                 if (FWD) {
-                    *p0 = AR::add(AR::mul(ca, x0), AR::mul(cb, x1));
-                    *p1 = AR::add(AR::mul(-cb, x0), AR::mul(ca, x1));
+                    *p0 = AR::add(AR::mul(ca, x0), AR::mul(cbv, x1));
+                    *p1 = AR::add(AR::mul(-cbv, x0), AR::mul(ca, x1));
                 } else {
-                    *p0 = AR::sub(AR::mul(ca, x0), AR::mul(cb, x1));
-                    *p1 = AR::add(AR::mul(cb, x0), AR::mul(ca, x1));
+                    *p0 = AR::sub(AR::mul(ca, x0), AR::mul(cbv, x1));
+                    *p1 = AR::add(AR::mul(cbv, x0), AR::mul(ca, x1));
                 }
             }
             __syncthreads();
@@ -409,6 +446,96 @@ transform_upper_kernel(PlanDev P, int stage, const Tel *A, const Tel *B, Tel *O,
         }
         __syncthreads();
     }
+}
+
+template <typename Tel, bool FWD>
+__global__ void __launch_bounds__(TR_THREADS)
+transform_upper_kernel(PlanDev P, int stage, const Tel *A, const Tel *B, Tel *O, int D, int up_elems)
+{
+    extern __shared__ __align__(128) unsigned char tr_smem[];
+    const int per = (D + (int)gridDim.y - 1) / (int)gridDim.y;            // channels of this CTA's group
+    const int cb = (int)blockIdx.y * per, ce = min(D, cb + per);
+    upper_tile<Tel, FWD, CHAIN_NONE>(P, stage, (int64_t)blockIdx.x, A, B, O, D, up_elems, cb, ce, tr_smem);
+}
+
+// ---- the whole transform in ONE launch -------------------------------------------------------------------------------
+// Round 1 ran a launch per stage: at 1 M rows the five upper stages (977 / 123 / 16 / 2 / 1 tiles, 7 % of the rows) cost
+// 5 x 27 us of dependent launches next to 0.2 ms of stage 0.
+// Forward (bottom-up): a CTA runs its stage-0 tile, then signs in at the parent tile's counter; the CTA that signs in
+// last runs the parent (its children's rows are fenced to L2), and so on to the top -- nobody waits, the upper stages
+// run in the shadow of the stage-0 stream, and only the last few tiles of the chain are exposed.
+// Inverse (top-down): the tiles are handed out by TICKET in topological order (top tile, ..., stage-1 tiles, stage-0
+// tiles); a tile spins on its parent's done-flag, which a smaller ticket -- a CTA that is already running -- sets:
+// forward progress needs no co-residency.  A stage-0 tile has its bulk load in flight while it waits.
+// arrive[] / ticket are left at zero for the next launch; done[] is compared with a per-launch epoch.
+constexpr int UP_FIXED_BYTES = PLAN_UP_CAP * 9 + 16;                       // s_sched, s_rowid, s_flag
+template <typename Tel> __host__ __device__ inline size_t upper_fixed_bytes() { return (size_t)2 * PLAN_UP_CAP * sizeof(Tel) + UP_FIXED_BYTES; }
+
+template <typename Tin, typename Tel, int DT>
+__global__ void __launch_bounds__(TR_THREADS)
+transform_forward_chain_kernel(PlanDev P, const Tin *__restrict__ A, Tel *O, int D_rt, int use_tma, int up_elems)
+{
+    extern __shared__ __align__(128) unsigned char tr_smem[];
+    __shared__ int s_last;
+    const int D = DT ? DT : D_rt;
+    stage0_tile<Tin, Tel, DT, true, QM_NONE, CHAIN_FWD>(P, (int64_t)blockIdx.x, A, (const Tel *)nullptr, O, D_rt, use_tma, QuantArgs(), tr_smem, 0u);
+    int stage = 0;
+    int64_t tile = blockIdx.x;
+    while (stage + 1 < P.n_stages) {
+        const int64_t parent = tile / PLAN_FANIN;
+        const int64_t children = min((int64_t)PLAN_FANIN, P.tiles[stage] - parent * PLAN_FANIN);
+        __threadfence();                                   // this tile's rows, before the sign-in
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            unsigned *ctr = P.arrive + P.tile_base[stage + 1] + parent;
+            const unsigned prev = atomicAdd(ctr, 1u);
+            s_last = prev + 1 == (unsigned)children;
+            if (s_last) *ctr = 0u;                         // ready for the next launch
+            __threadfence();
+        }
+        __syncthreads();
+        if (!s_last) break;
+        ++stage;
+        tile = parent;
+        upper_tile<Tel, true, CHAIN_FWD>(P, stage, tile, (const Tel *)O, (const Tel *)nullptr, O, D, up_elems, 0, D, tr_smem);
+    }
+}
+
+template <typename Tel, int DT>
+__global__ void __launch_bounds__(TR_THREADS)
+transform_inverse_chain_kernel(PlanDev P, const Tel *__restrict__ T, Tel *C, int D_rt, int use_tma, int up_elems, unsigned epoch)
+{
+    extern __shared__ __align__(128) unsigned char tr_smem[];
+    __shared__ unsigned s_ticket;
+    const int D = DT ? DT : D_rt;
+    if (threadIdx.x == 0) {
+        const unsigned t = atomicAdd(P.ticket, 1u);
+        if (t + 1 == (unsigned)P.tiles_total) *P.ticket = 0u;             // every ticket is out: ready for the next launch
+        s_ticket = t;
+    }
+    __syncthreads();
+    // ticket -> (stage, tile): the top stage first
+    int64_t rest = s_ticket;
+    int stage = P.n_stages - 1;
+    while (stage > 0 && rest >= P.tiles[stage]) { rest -= P.tiles[stage]; --stage; }
+    const int64_t tile = rest;
+    if (stage == 0) {
+        stage0_tile<Tel, Tel, DT, false, QM_NONE, CHAIN_INV>(P, tile, T, P.n_stages > 1 ? (const Tel *)C : (const Tel *)nullptr, C, D_rt, use_tma,
+                                                             QuantArgs(), tr_smem, epoch);
+        return;
+    }
+    const bool top = stage == P.n_stages - 1;
+    if (!top) {
+        if (threadIdx.x == 0) {
+            const unsigned *flag = P.done + P.tile_base[stage + 1] + tile / PLAN_FANIN;
+            while (ld_acquire_u32(flag) != epoch) __nanosleep(64);
+        }
+        __syncthreads();
+    }
+    upper_tile<Tel, false, CHAIN_INV>(P, stage, tile, T, top ? (const Tel *)nullptr : (const Tel *)C, C, D, up_elems, 0, D, tr_smem);
+    __threadfence();                                       // this tile's rows, before the hand-over to its children
+    __syncthreads();
+    if (threadIdx.x == 0) st_release_u32(P.done + P.tile_base[stage] + tile, epoch);
 }
 
 // rows the stage-0 tiles deferred, a warp per row: after the upper stages of the forward transform (T -> q), or before
@@ -512,9 +639,81 @@ int launch_upper(const raht_plan *P, int k, const Tel *A, const Tel *B, Tel *O, 
     return RAHT_OK;
 }
 
+// RAHT_CHAIN=0: a launch per stage (round 1), for A/B timing and as the cross-check of the chained kernels in the tests
+inline bool use_chain()
+{
+    static const int on = getenv("RAHT_CHAIN") ? atoi(getenv("RAHT_CHAIN")) : 1;
+    return on != 0;
+}
+unsigned next_epoch()
+{
+    static unsigned epoch = 0;
+    unsigned e = __atomic_add_fetch(&epoch, 1u, __ATOMIC_RELAXED);
+    if (e == 0) e = __atomic_add_fetch(&epoch, 1u, __ATOMIC_RELAXED);     // 0 = "never done" (plan_init)
+    return e;
+}
+
+// shared memory of a chained kernel: the stage-0 layout, or what the largest upper tile needs for one channel
+template <typename Tel> size_t chain_smem_bytes(int R, int D, int *up_elems)
+{
+    SmemLayout<Tel> L(R, D);
+    size_t smem = L.total;
+    const size_t fixed = upper_fixed_bytes<Tel>();
+    const size_t min_upper = fixed + (size_t)2048 * sizeof(Tel);
+    if (smem < min_upper) smem = min_upper;
+    int ue = (int)((smem - fixed) / sizeof(Tel));
+    if (ue > UP_ELEMS) ue = UP_ELEMS;
+    if (ue < PLAN_UP_CAP) {                                              // one channel of the largest tile must fit
+        ue = PLAN_UP_CAP;
+        smem = fixed + (size_t)ue * sizeof(Tel);
+    }
+    *up_elems = ue;
+    return smem;
+}
+
+template <typename Tin, typename Tel, int DT>
+int launch_forward_chain(const raht_plan *P, const Tin *C, Tel *T, int D, int use_tma, cudaStream_t st)
+{
+    int up_elems = 0;
+    const size_t smem = chain_smem_bytes<Tel>(P->d.tile_rows, D, &up_elems);
+    if (smem > 227 * 1024) {
+        raht_set_error("transform: tile of %d rows x %d channels needs %zu bytes of shared memory (> 227 KB)", P->d.tile_rows, D, smem);
+        return RAHT_E_INVALID;
+    }
+    auto kern = transform_forward_chain_kernel<Tin, Tel, DT>;
+    RAHT_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    (raht_count_launches(1), kern)<<<(unsigned)P->d.tiles[0], TR_THREADS, smem, st>>>(P->d, C, T, D, use_tma, up_elems);
+    RAHT_LAUNCH_CHECK();
+    return RAHT_OK;
+}
+
+template <typename Tel, int DT>
+int launch_inverse_chain(const raht_plan *P, const Tel *T, Tel *C, int D, int use_tma, cudaStream_t st)
+{
+    int up_elems = 0;
+    const size_t smem = chain_smem_bytes<Tel>(P->d.tile_rows, D, &up_elems);
+    if (smem > 227 * 1024) {
+        raht_set_error("transform: tile of %d rows x %d channels needs %zu bytes of shared memory (> 227 KB)", P->d.tile_rows, D, smem);
+        return RAHT_E_INVALID;
+    }
+    auto kern = transform_inverse_chain_kernel<Tel, DT>;
+    RAHT_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    (raht_count_launches(1), kern)<<<(unsigned)P->d.tiles_total, TR_THREADS, smem, st>>>(P->d, T, C, D, use_tma, up_elems, next_epoch());
+    RAHT_LAUNCH_CHECK();
+    return RAHT_OK;
+}
+
 template <typename Tin, typename Tel>
 int forward_impl(const raht_plan *P, const Tin *C, Tel *T, int D, int use_tma, cudaStream_t st)
 {
+    if (use_chain()) {
+        switch (D) {
+        case 3: return launch_forward_chain<Tin, Tel, 3>(P, C, T, D, use_tma, st);
+        case 56: return launch_forward_chain<Tin, Tel, 56>(P, C, T, D, use_tma, st);
+        case 59: return launch_forward_chain<Tin, Tel, 59>(P, C, T, D, use_tma, st);
+        default: return launch_forward_chain<Tin, Tel, 0>(P, C, T, D, use_tma, st);
+        }
+    }
     // stage 0: C -> T (every row); stages >= 1: in place on T
     int rc = launch_stage0_d<Tin, Tel, true>(P, C, (const Tel *)nullptr, T, D, use_tma, st);
     for (int k = 1; k < P->d.n_stages && rc == RAHT_OK; ++k)
@@ -525,6 +724,14 @@ int forward_impl(const raht_plan *P, const Tin *C, Tel *T, int D, int use_tma, c
 template <typename Tel>
 int inverse_impl(const raht_plan *P, const Tel *T, Tel *C, int D, int use_tma, cudaStream_t st)
 {
+    if (use_chain()) {
+        switch (D) {
+        case 3: return launch_inverse_chain<Tel, 3>(P, T, C, D, use_tma, st);
+        case 56: return launch_inverse_chain<Tel, 56>(P, T, C, D, use_tma, st);
+        case 59: return launch_inverse_chain<Tel, 59>(P, T, C, D, use_tma, st);
+        default: return launch_inverse_chain<Tel, 0>(P, T, C, D, use_tma, st);
+        }
+    }
     // top stage first.  A row is read from C when an upper stage has already rewritten it (the rows a
     // tile defers to the next stage), else from T; every row of a tile that ran is written to C.
     int rc = RAHT_OK;

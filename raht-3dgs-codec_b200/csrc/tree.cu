@@ -140,8 +140,8 @@ constexpr int PB_WARPS = PB_THREADS / 32;
 __global__ void __launch_bounds__(256) plan_init_kernel(PlanDev P)
 {
     const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (i == 0) *P.bump = (unsigned int)P.slots0;
-    if (i < P.tiles_total) P.arrive[i] = 0u;
+    if (i == 0) { *P.bump = (unsigned int)P.slots0; *P.ticket = 0u; }
+    if (i < P.tiles_total) { P.arrive[i] = 0u; P.done[i] = 0u; }
 }
 
 // One tile of one stage.  Upper tiles read what OTHER CTAs of the same launch wrote (the deferred lists of their child
@@ -352,6 +352,7 @@ __global__ void __launch_bounds__(PB_THREADS) plan_kernel(PlanDev P, const uint8
         if (threadIdx.x == 0) {
             const unsigned prev = atomicAdd(P.arrive + P.tile_base[stage + 1] + parent, 1u);
             s_last = prev + 1 == (unsigned)children;
+            if (s_last) P.arrive[P.tile_base[stage + 1] + parent] = 0u;       // zero again for the transforms that reuse it
             __threadfence();
         }
         __syncthreads();
@@ -363,7 +364,7 @@ __global__ void __launch_bounds__(PB_THREADS) plan_kernel(PlanDev P, const uint8
 
 struct PlanLayout {
     PlanDev d;          // sizes and stage table filled in; pointers as byte offsets from the workspace start
-    size_t off_hdr, off_def_rows, off_def_local, off_def_lev, off_sched, off_ab, off_bump, off_arrive, total;
+    size_t off_hdr, off_def_rows, off_def_local, off_def_lev, off_sched, off_ab, off_bump, off_arrive, off_done, total;
 };
 
 PlanLayout plan_layout(int64_t n, int tile_rows)
@@ -395,6 +396,7 @@ PlanLayout plan_layout(int64_t n, int tile_rows)
     L.off_ab = o; o += align_up((size_t)(d.slots0 + n) * 16, 256);
     L.off_bump = o; o += 256;
     L.off_arrive = o; o += align_up((size_t)base * 4, 256);
+    L.off_done = o; o += align_up((size_t)base * 4, 256);
     L.total = o;
     return L;
 }
@@ -503,6 +505,8 @@ RAHT_API int raht_plan_create(const uint8_t *level, int64_t n, int tile_rows, do
     P->d.ab = (double2 *)(ws + L.off_ab);
     P->d.bump = (unsigned int *)(ws + L.off_bump);
     P->d.arrive = (unsigned int *)(ws + L.off_arrive);
+    P->d.done = (unsigned int *)(ws + L.off_done);
+    P->d.ticket = (unsigned int *)(ws + L.off_bump) + 16;
     if (n > 0) {
         cudaStream_t st = (cudaStream_t)stream;
         (raht_count_launches(1), plan_init_kernel)<<<(unsigned)((P->d.tiles_total + 255) / 256), 256, 0, st>>>(P->d);

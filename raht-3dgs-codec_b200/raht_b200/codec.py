@@ -92,6 +92,20 @@ class StageTimer:
             e.record()
             self.marks.append((name, e))
 
+    def handles(self, names):
+        """Event handles for the stages of a scene-level C call (raht_scene_*: `events`), or None when timing is off.
+        Returns (ctypes array of cudaEvent_t, commit): commit() appends the events to the marks once the call is queued."""
+        if not self.enabled:
+            return None, (lambda: None)
+        import ctypes as C
+        evs = []
+        for _ in names:
+            e = torch.cuda.Event(enable_timing=True)
+            e.record()                                    # (a torch event gets its handle on its first record)
+            evs.append(e)
+        arr = (C.c_void_p * len(names))(*[C.c_void_p(e.cuda_event) for e in evs])
+        return arr, (lambda: self.marks.extend(zip(names, evs)))
+
     def result(self):
         if not self.enabled or len(self.marks) < 2:
             return {}
@@ -282,11 +296,169 @@ def decode_attributes(keys, streams, D, step, transform_dtype=torch.float64, tre
     return Crec
 
 
+# ---- scene-level calls (csrc/scene.cu): one leg of the pipeline per host call -------------------------------------------
+_PINNED = {}
+
+
+def _pinned_results(device, nbytes):
+    key = (device.index if device.index is not None else torch.cuda.current_device(), torch.cuda.current_stream(device).cuda_stream)
+    buf = _PINNED.get(key)
+    if buf is None or buf.numel() < nbytes:
+        buf = _PINNED[key] = torch.empty(max(nbytes, 4096), dtype=torch.uint8).pin_memory()
+    return buf
+
+
+def _steps_host(step, D):
+    import ctypes as C
+    if isinstance(step, torch.Tensor):
+        step = step.detach().cpu().reshape(-1).tolist()
+    if isinstance(step, (int, float)):
+        vals = [float(step)] * D
+    else:
+        vals = [float(x) for x in step]
+        if len(vals) == 1:
+            vals = vals * D
+    if len(vals) != D or any(not (v > 0.0) for v in vals):
+        raise ValueError(f"need one positive quantisation step, or {D}")
+    return (C.c_double * D)(*vals)
+
+
+def _tree_from_workspace(tree_ws, layout, nvox, tile_rows, plan_handle):
+    """ops.RahtTree over the tree workspace a scene-level call filled (no copies)."""
+    lv = tree_ws[layout[0]:layout[0] + nvox]
+    tree = ops.RahtTree(lv, nvox)
+    tree._order = tree_ws[layout[1]:layout[1] + 8 * nvox].view(torch.int64)
+    tree._position = tree_ws[layout[2]:layout[2] + 4 * nvox].view(torch.int32)
+    tree._w = tree_ws[layout[3]:layout[3] + 8 * nvox].view(torch.float64)
+    tree._plans[tile_rows] = ops._PlanHandle(plan_handle, tree_ws)
+    return tree
+
+
+@torch.no_grad()
+def _encode_scene_calls(means, quats, scales, opacities, colors, J, step, transform_dtype, tile_rows, timer, keep_packed, given=None):
+    """encode_scene through raht_scene_front + raht_scene_encode: two host calls and one synchronisation between them (the
+    voxel count sizes the second leg), one more at the end (stream lengths and status word)."""
+    import ctypes as C
+    dev = means.device
+    N = means.shape[0]
+    st = stream()
+    tile_rows = tile_rows or ops.DEFAULT_TILE_ROWS
+    means, quats, scales = means.contiguous().float(), quats.contiguous().float(), scales.contiguous().float()
+    opacities, colors = opacities.contiguous().float(), colors.contiguous().float()
+    cd = colors.shape[1]
+    D = 11 + cd
+    steps = _steps_host(step, D)
+    tag = L.dtype_tag(transform_dtype)
+    # outputs of the front that outlive the call, carved out of one allocation
+    o_keys, o_idx = 256, 256 + (N * 8 + 255) // 256 * 256
+    o_off = o_idx + (N * 4 + 255) // 256 * 256
+    front = torch.empty(o_off + (N + 1) * 4 + 256, dtype=torch.uint8, device=dev)
+    params4 = front[0:16].view(torch.float32)
+    params_d2 = front[16:32].view(torch.float64)
+    nvox_dev = front[32:40].view(torch.int64)
+    status = front[40:44].view(torch.int32)
+    front[32:48].zero_()
+    keys_all = front[o_keys:o_keys + N * 8].view(torch.int64)
+    idx32 = front[o_idx:o_idx + N * 4].view(torch.int32)
+    offsets = front[o_off:o_off + (N + 1) * 4].view(torch.int32)
+    ws_bytes = lib.raht_scene_front_workspace_bytes(N, J)
+    ws = L.workspace_cached("scene_front", ws_bytes, dev)
+    pin = _pinned_results(dev, 64 + 8 * D + 64)
+    ev, commit = timer.handles(("morton", "sort", "segments"))
+    if given is None:
+        use_given, vm, width = 0, None, 0.0
+    else:
+        use_given, vm, width = 1, (C.c_float * 3)(*[float(x) for x in given[0].detach().cpu().tolist()]), float(given[1])
+    check(lib.raht_scene_front(ptr(means), N, J, use_given, vm, width, ptr(params4), ptr(params_d2), ptr(keys_all), ptr(idx32),
+                               ptr(offsets), ptr(nvox_dev), C.c_void_p(pin.data_ptr()), ptr(status), ptr(ws), ws.numel(), ev, st),
+          "raht_scene_front")
+    commit()
+    torch.cuda.current_stream(dev).synchronize()                      # the voxel count sizes everything that follows
+    head = pin[:24].numpy()
+    nvox = int(head[:8].view("int64")[0])
+    width_h, voxel_size_h = (float(x) for x in head[8:24].view("float64"))
+    keys = keys_all[:nvox]
+    # second leg
+    slot = (nvox * 4 + 64 + 7) // 8 * 8
+    entries = int(lib.raht_rlgr_sync_entries(nvox))
+    buf = torch.empty(D * slot, dtype=torch.uint8, device=dev)
+    nbytes = torch.empty(D, dtype=torch.int64, device=dev)
+    index = torch.empty(D * entries, 2, dtype=torch.int32, device=dev)
+    packed = torch.empty(nvox, D, dtype=torch.float32, device=dev) if keep_packed else None
+    tree_bytes = lib.raht_scene_tree_workspace_bytes(nvox, tile_rows)
+    tree_ws = torch.empty(tree_bytes, dtype=torch.uint8, device=dev)
+    enc_bytes = lib.raht_scene_encode_workspace_bytes(nvox, D, tag, 0 if keep_packed else 1)
+    enc_ws = L.workspace_cached("scene_encode", enc_bytes, dev)
+    layout = (C.c_int64 * 11)()
+    plan = C.c_void_p()
+    ev, commit = timer.handles(("merge", "raht_param", "raht", "quant_reorder", "rlgr_encode"))
+    check(lib.raht_scene_encode(ptr(idx32), ptr(offsets), nvox, ptr(means), ptr(quats), ptr(scales), ptr(opacities), ptr(colors), cd,
+                                ptr(keys), steps, tag, tile_rows, ptr(packed), ptr(buf), slot, ptr(nbytes), ptr(index), ptr(status),
+                                C.c_void_p(pin.data_ptr() + 64), C.byref(plan), layout, ptr(tree_ws), tree_ws.numel(), ptr(enc_ws),
+                                enc_ws.numel(), ev, st), "raht_scene_encode")
+    commit()
+    tree = _tree_from_workspace(tree_ws, list(layout), nvox, tile_rows, plan)
+    torch.cuda.current_stream(dev).synchronize()                      # stream lengths and the status word
+    res = pin[64:64 + 8 * D + 4].numpy()
+    sizes = [int(x) for x in res[:8 * D].view("int64")]
+    bits = int(res[8 * D:8 * D + 4].view("int32")[0])
+    ops.raise_for_status(bits)
+    if bits & L.ST_STREAM_OVERFLOW:                                   # (more than 4 bytes per symbol: code the symbols again into wider slots)
+        lay = list(layout)
+        q = enc_ws[lay[8]:lay[8] + D * lay[9] * 4].view(torch.int32).reshape(D, lay[9])[:, :nvox]
+        streams = ops.rlgr_encode(q, 1, slot_bytes=(max(sizes) + 64 + 7) // 8 * 8)
+    else:
+        streams = ops.RlgrStreams(buf, slot, nbytes, nvox, D, index)
+        streams._sizes = sizes
+    return EncodedScene(J=J, n_in=N, nvox=nvox, D=D, step=step, vmin=params4[:3], voxel_size=voxel_size_h, width=width_h, keys=keys,
+                        streams=streams, transform_dtype=transform_dtype, tree=tree, packed=packed)
+
+
+@torch.no_grad()
+def _decode_scene_calls(enc, tile_rows, timer):
+    """decode_scene through raht_scene_decode: one host call; the tree is rebuilt from the voxel keys."""
+    import ctypes as C
+    dev = enc.keys.device
+    nvox, D = enc.nvox, enc.D
+    tile_rows = tile_rows or ops.DEFAULT_TILE_ROWS
+    tag = L.dtype_tag(enc.transform_dtype)
+    steps = _steps_host(enc.step, D)
+    S = enc.streams
+    Crec = torch.empty(nvox, D, dtype=enc.transform_dtype, device=dev)
+    coords = torch.empty(nvox, 3, dtype=torch.float32, device=dev)
+    status = torch.zeros(1, dtype=torch.int32, device=dev)
+    tree_ws = L.workspace_cached("scene_decode_tree", lib.raht_scene_tree_workspace_bytes(nvox, tile_rows), dev)
+    ws = L.workspace_cached("scene_decode", lib.raht_scene_decode_workspace_bytes(nvox, D, tag), dev)
+    pin = _pinned_results(dev, 64 + 8 * D + 64)
+    plan = C.c_void_p()
+    ev, commit = timer.handles(("raht_param_dec", "rlgr_decode", "dequant_unreorder", "iraht", "geometry"))
+    check(lib.raht_scene_decode(ptr(enc.keys), nvox, enc.J, ptr(S.buf), S.slot_bytes, ptr(S.nbytes), ptr(S.sync_index), D, steps, tag,
+                                tile_rows, ptr(Crec), ptr(coords), ptr(status), C.c_void_p(pin.data_ptr() + 64 + 8 * D + 8), C.byref(plan),
+                                None, ptr(tree_ws), tree_ws.numel(), ptr(ws), ws.numel(), ev, stream()), "raht_scene_decode")
+    commit()
+    lib.raht_plan_destroy(plan)                                       # (host handle only; the kernels are queued with copies of it)
+    torch.cuda.current_stream(dev).synchronize()                      # the decoder's one synchronisation: were the keys a valid voxel list?
+    ops.raise_for_status(int(pin[64 + 8 * D + 8:64 + 8 * D + 12].numpy().view("int32")[0]))
+    return coords, Crec
+
+
+# RAHT_SCENE_CALLS=0 (or codec.SCENE_CALLS = False): encode_scene / decode_scene go through the per-operator entry points,
+# one host call per kernel, as in round 1 -- kept as the reference point of tests/test_gpu_parity.py
+# (test_scene_level_calls_match_the_operator_path) and for timing comparisons.
+SCENE_CALLS = os.environ.get("RAHT_SCENE_CALLS", "1") != "0"
+
+
+def _plain_step(step):
+    return SCENE_CALLS and not isinstance(step, str)
+
+
 @torch.no_grad()
 def encode_scene(means, quats, scales, opacities, colors, J, step, transform_dtype=torch.float64, tile_rows=None,
                  timer=None, flags=0, keep_packed=False, fused=False) -> EncodedScene:
     timer = timer or StageTimer(False)
     timer.mark("start")
+    if not fused and not OVERLAP and flags == 0 and _plain_step(step) and means.shape[0] > 0:
+        return _encode_scene_calls(means, quats, scales, opacities, colors, J, step, transform_dtype, tile_rows, timer, keep_packed)
     status = ops._status_word(means.device)
     job = []
     on_keys = (lambda k: job.append(start_tree(k, status, tile_rows))) if OVERLAP else None
@@ -305,6 +477,9 @@ def decode_scene(enc: EncodedScene, reuse_tree=False, tile_rows=None, timer=None
     """Returns (voxel coordinates (nvox,3) fp32 integer-valued, attributes (nvox, D))."""
     timer = timer or StageTimer(False)
     timer.mark("start_dec")
+    if (SCENE_CALLS and not fused and not OVERLAP and flags == 0 and not reuse_tree and enc.nvox > 0 and enc.streams.nch == enc.D
+            and enc.streams.n == enc.nvox):
+        return _decode_scene_calls(enc, tile_rows, timer)
     Crec = decode_attributes(enc.keys, enc.streams, enc.D, enc.step, enc.transform_dtype,
                              enc.tree if reuse_tree else None, tile_rows, timer, flags, fused)
     coords = torch.empty(enc.nvox, 3, dtype=torch.float32, device=enc.keys.device)

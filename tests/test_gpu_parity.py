@@ -555,3 +555,32 @@ def test_scene_with_per_attribute_steps_roundtrips_through_the_container():
     assert torch.equal(rec, ref)
     packed, _, _ = codec.voxelize_merge(*scene, J=8)
     assert codec.psnr(packed, rec) > 20.0
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("n,J,step", [(1, 4, 0.5), (3000, 6, 0.02), (120000, 11, 1.0 / 64), (250000, 16, [0.01 * (1 + c % 4) for c in range(59)])])
+def test_scene_level_calls_match_the_operator_path(n, J, step, monkeypatch):
+    """raht_scene_front / raht_scene_encode / raht_scene_decode (one host call per leg, csrc/scene.cu) against the same
+    pipeline driven operator by operator: keys, merged attributes, order, streams, sync index and decoded attributes are
+    the same bytes; the tree a scene-level encode returns is usable by the operators."""
+    from raht_b200 import codec, ops
+    scene = [cu(a) for a in helpers.synthetic_gaussians(n, 4242 + n)]
+    monkeypatch.setattr(codec, "SCENE_CALLS", True)
+    a = codec.encode_scene(*scene, J=J, step=step, keep_packed=True)
+    ca, ra = codec.decode_scene(a)
+    monkeypatch.setattr(codec, "SCENE_CALLS", False)
+    b = codec.encode_scene(*scene, J=J, step=step, keep_packed=True)
+    cb, rb = codec.decode_scene(b)
+    assert a.nvox == b.nvox and a.D == b.D and a.voxel_size == b.voxel_size and a.width == b.width
+    assert torch.equal(a.vmin, b.vmin) and torch.equal(a.keys, b.keys) and torch.equal(a.packed, b.packed)
+    assert a.streams.sizes() == b.streams.sizes() and a.streams.to_bytes() == b.streams.to_bytes()
+    assert torch.equal(a.streams.sync_index, b.streams.sync_index)
+    assert torch.equal(ca, cb) and torch.equal(ra, rb)
+    if a.nvox > 1:
+        assert torch.equal(a.tree.order(), b.tree.order()) and torch.equal(a.tree.level, b.tree.level) and torch.equal(a.tree.w, b.tree.w)
+        T = ops.forward(a.tree, a.packed, torch.float64)                       # the plan inside the tree workspace
+        assert torch.equal(T, ops.forward(b.tree, b.packed, torch.float64))
+    monkeypatch.setattr(codec, "SCENE_CALLS", True)
+    _, rc = codec.decode_scene(b)                                              # streams of one path, decoder of the other
+    assert torch.equal(rc, ra)
+    assert torch.equal(codec.decode_scene(a, reuse_tree=True)[1], ra)
