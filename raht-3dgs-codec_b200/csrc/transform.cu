@@ -538,6 +538,67 @@ transform_inverse_chain_kernel(PlanDev P, const Tel *__restrict__ T, Tel *C, int
     if (threadIdx.x == 0) st_release_u32(P.done + P.tile_base[stage] + tile, epoch);
 }
 
+// The upper stages alone as one launch (stage 0 keeps its own launch and exits without waiting for its bulk store to land):
+// forward: a CTA per stage-1 tile, last-arriver chaining from there up; inverse: tickets over the upper tiles, top first.
+template <typename Tel>
+__global__ void __launch_bounds__(TR_THREADS) transform_upper_forward_chain_kernel(PlanDev P, Tel *O, int D, int up_elems)
+{
+    extern __shared__ __align__(128) unsigned char tr_smem[];
+    __shared__ int s_last;
+    int stage = 1;
+    int64_t tile = blockIdx.x;
+    upper_tile<Tel, true, CHAIN_NONE>(P, stage, tile, (const Tel *)O, (const Tel *)nullptr, O, D, up_elems, 0, D, tr_smem);
+    while (stage + 1 < P.n_stages) {
+        const int64_t parent = tile / PLAN_FANIN;
+        const int64_t children = min((int64_t)PLAN_FANIN, P.tiles[stage] - parent * PLAN_FANIN);
+        __threadfence();
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            unsigned *ctr = P.arrive + P.tile_base[stage + 1] + parent;
+            const unsigned prev = atomicAdd(ctr, 1u);
+            s_last = prev + 1 == (unsigned)children;
+            if (s_last) *ctr = 0u;
+            __threadfence();
+        }
+        __syncthreads();
+        if (!s_last) break;
+        ++stage;
+        tile = parent;
+        upper_tile<Tel, true, CHAIN_FWD>(P, stage, tile, (const Tel *)O, (const Tel *)nullptr, O, D, up_elems, 0, D, tr_smem);
+    }
+}
+
+template <typename Tel>
+__global__ void __launch_bounds__(TR_THREADS) transform_upper_inverse_chain_kernel(PlanDev P, const Tel *__restrict__ T, Tel *C, int D,
+                                                                                   int up_elems, unsigned epoch)
+{
+    extern __shared__ __align__(128) unsigned char tr_smem[];
+    __shared__ unsigned s_ticket;
+    const unsigned total = (unsigned)(P.tiles_total - P.tiles[0]);
+    if (threadIdx.x == 0) {
+        const unsigned t = atomicAdd(P.ticket, 1u);
+        if (t + 1 == total) *P.ticket = 0u;
+        s_ticket = t;
+    }
+    __syncthreads();
+    int64_t rest = s_ticket;
+    int stage = P.n_stages - 1;
+    while (stage > 1 && rest >= P.tiles[stage]) { rest -= P.tiles[stage]; --stage; }
+    const int64_t tile = rest;
+    const bool top = stage == P.n_stages - 1;
+    if (!top) {
+        if (threadIdx.x == 0) {
+            const unsigned *flag = P.done + P.tile_base[stage + 1] + tile / PLAN_FANIN;
+            while (ld_acquire_u32(flag) != epoch) __nanosleep(64);
+        }
+        __syncthreads();
+    }
+    upper_tile<Tel, false, CHAIN_INV>(P, stage, tile, T, top ? (const Tel *)nullptr : (const Tel *)C, C, D, up_elems, 0, D, tr_smem);
+    __threadfence();
+    __syncthreads();
+    if (threadIdx.x == 0) st_release_u32(P.done + P.tile_base[stage] + tile, epoch);
+}
+
 // rows the stage-0 tiles deferred, a warp per row: after the upper stages of the forward transform (T -> q), or before
 // those of the inverse (q -> T)
 template <typename Tel, bool TO_Q>
@@ -640,17 +701,57 @@ int launch_upper(const raht_plan *P, int k, const Tel *A, const Tel *B, Tel *O, 
 }
 
 // RAHT_CHAIN=0: a launch per stage (round 1), for A/B timing and as the cross-check of the chained kernels in the tests
-inline bool use_chain()
-{
-    static const int on = getenv("RAHT_CHAIN") ? atoi(getenv("RAHT_CHAIN")) : 1;
-    return on != 0;
-}
 unsigned next_epoch()
 {
     static unsigned epoch = 0;
     unsigned e = __atomic_add_fetch(&epoch, 1u, __ATOMIC_RELAXED);
     if (e == 0) e = __atomic_add_fetch(&epoch, 1u, __ATOMIC_RELAXED);     // 0 = "never done" (plan_init)
     return e;
+}
+
+// RAHT_CHAIN: 0 = a launch per stage (default); 1 = stage 0 + ONE launch for all upper stages; 2 = everything in one launch.
+// The chained forms are bit-identical (tests) and were built to remove the 5 dependent upper-stage launches of a 1 M-row
+// transform; measured on B200 (scripts/gpu_chain_ab.sh, 1 M / 6 M rows) they LOSE: mode 1 raht 0.337 -> 0.367 ms, iraht
+// 0.372 -> 0.420 ms; mode 2 raht 0.370, iraht 0.375 ms.  The upper stages are not launch-bound but bound by the latency of a
+// tile's dependent rounds, and a chained tile is run by ONE CTA over all channels where the per-stage launches spread a stage
+// over channel groups (up to 16 CTAs per tile); in mode 2 every stage-0 CTA additionally has to wait for its bulk store to
+// LAND before it may sign in at its parent, which holds its 63 KB of shared memory ~1-2 us longer.  Kept as options.
+inline int chain_mode()
+{
+    static const int m = getenv("RAHT_CHAIN") ? atoi(getenv("RAHT_CHAIN")) : 0;
+    return m;
+}
+
+template <typename Tel> int upper_chain_smem(int *up_elems, size_t *smem)
+{
+    const size_t fixed = upper_fixed_bytes<Tel>();
+    *up_elems = 4096;                                                     // 32 KB of rows: 3-4 CTAs per SM
+    *smem = fixed + (size_t)*up_elems * sizeof(Tel);
+    return RAHT_OK;
+}
+
+template <typename Tel> int launch_upper_forward_chain(const raht_plan *P, Tel *T, int D, cudaStream_t st)
+{
+    int up_elems;
+    size_t smem;
+    upper_chain_smem<Tel>(&up_elems, &smem);
+    auto kern = transform_upper_forward_chain_kernel<Tel>;
+    RAHT_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    (raht_count_launches(1), kern)<<<(unsigned)P->d.tiles[1], TR_THREADS, smem, st>>>(P->d, T, D, up_elems);
+    RAHT_LAUNCH_CHECK();
+    return RAHT_OK;
+}
+
+template <typename Tel> int launch_upper_inverse_chain(const raht_plan *P, const Tel *T, Tel *C, int D, cudaStream_t st)
+{
+    int up_elems;
+    size_t smem;
+    upper_chain_smem<Tel>(&up_elems, &smem);
+    auto kern = transform_upper_inverse_chain_kernel<Tel>;
+    RAHT_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    (raht_count_launches(1), kern)<<<(unsigned)(P->d.tiles_total - P->d.tiles[0]), TR_THREADS, smem, st>>>(P->d, T, C, D, up_elems, next_epoch());
+    RAHT_LAUNCH_CHECK();
+    return RAHT_OK;
 }
 
 // shared memory of a chained kernel: the stage-0 layout, or what the largest upper tile needs for one channel
@@ -706,7 +807,12 @@ int launch_inverse_chain(const raht_plan *P, const Tel *T, Tel *C, int D, int us
 template <typename Tin, typename Tel>
 int forward_impl(const raht_plan *P, const Tin *C, Tel *T, int D, int use_tma, cudaStream_t st)
 {
-    if (use_chain()) {
+    if (chain_mode() == 1) {
+        int rc = launch_stage0_d<Tin, Tel, true>(P, C, (const Tel *)nullptr, T, D, use_tma, st);
+        if (rc == RAHT_OK && P->d.n_stages > 1) rc = launch_upper_forward_chain<Tel>(P, T, D, st);
+        return rc;
+    }
+    if (chain_mode() == 2) {
         switch (D) {
         case 3: return launch_forward_chain<Tin, Tel, 3>(P, C, T, D, use_tma, st);
         case 56: return launch_forward_chain<Tin, Tel, 56>(P, C, T, D, use_tma, st);
@@ -724,7 +830,13 @@ int forward_impl(const raht_plan *P, const Tin *C, Tel *T, int D, int use_tma, c
 template <typename Tel>
 int inverse_impl(const raht_plan *P, const Tel *T, Tel *C, int D, int use_tma, cudaStream_t st)
 {
-    if (use_chain()) {
+    if (chain_mode() == 1) {
+        int rc = RAHT_OK;
+        if (P->d.n_stages > 1) rc = launch_upper_inverse_chain<Tel>(P, T, C, D, st);
+        if (rc == RAHT_OK) rc = launch_stage0_d<Tel, Tel, false>(P, T, P->d.n_stages > 1 ? (const Tel *)C : (const Tel *)nullptr, C, D, use_tma, st);
+        return rc;
+    }
+    if (chain_mode() == 2) {
         switch (D) {
         case 3: return launch_inverse_chain<Tel, 3>(P, T, C, D, use_tma, st);
         case 56: return launch_inverse_chain<Tel, 56>(P, T, C, D, use_tma, st);
