@@ -29,7 +29,7 @@
 extern "C" {
 #endif
 
-#define RAHT_B200_ABI_VERSION 11
+#define RAHT_B200_ABI_VERSION 12
 
 enum {
     RAHT_OK = 0,
@@ -211,6 +211,23 @@ int raht_inverse(const raht_plan *plan, const void *T, int t_dtype, int D, void 
 int raht_shard_top(const int64_t *first_keys, const int64_t *prev_last_keys, const int64_t *offsets,
                    int P, void *rows, int dtype, int D, int inverse, uint8_t *level_out,
                    int32_t *status, void *stream);
+
+/* The same join over up to 1024 CELLS (aligned Morton-prefix subtrees, any of which may be empty): range i holds
+ * counts[i] rows, first_keys[i] / last_keys[i] are its first and last Morton code (ignored when counts[i] == 0).
+ * A rank that owns several cells transforms them as a FOREST (level 255 on the first row of every cell, see
+ * raht_plan_create) and contributes one row per cell.  level_out[C] as above (0 for empty cells).            */
+int raht_shard_top_cells(const int64_t *first_keys, const int64_t *last_keys, const int64_t *counts,
+                         int C, void *rows, int dtype, int D, int inverse, uint8_t *level_out,
+                         int32_t *status, void *stream);
+
+/* Gaussians as packed fp32 rows [means3 | quats4 | scales3 | opacity | colors] for the repartition exchange of
+ * the sharded encoder (one collective instead of one per attribute array): out[i] = the row of Gaussian perm[i]
+ * (perm == NULL: identity), and the inverse.                                                                */
+int raht_pack_rows(const uint32_t *perm, int64_t n, const float *means, const float *quats,
+                   const float *scales, const float *opacities, const float *colors, int color_dim,
+                   float *out, void *stream);
+int raht_unpack_rows(const float *rows, int64_t n, int color_dim, float *means, float *quats,
+                     float *scales, float *opacities, float *colors, void *stream);
 
 /* Fused forms of raht_forward + raht_quant_reorder and of raht_dequant_unreorder + raht_inverse (same results, bit for
  * bit): the rows a stage-0 tile of the plan finishes -- all but the ones it defers to the upper stages -- are quantised

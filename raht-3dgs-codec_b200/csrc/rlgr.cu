@@ -956,6 +956,48 @@ __global__ void __launch_bounds__(32 * SPEC_WARPS) rlgr_table_lanes_kernel(Geome
     lr[2] = make_uint4(0u, 0u, 0u, 0u);
 }
 
+// Exact walk of one chunk from its TRUE start state, block after block: lane l codes block l once the state has come
+// down the lanes to it.  This is the repair of the sparse channels: their trajectories do not re-synchronise (that is why
+// the chunk ended up here), so a pinned fixed point would advance the true state by one lane per ROUND anyway -- 29
+// rounds of 8-candidate recodes with helper hand-overs, 0.8 ms per chunk on the 50 M-symbol position channel (97 such
+// chunks: 78 of the 105 ms of that encode) -- where the walk pays 31 single-state block codings and nothing else.
+__device__ __forceinline__ void walk_chunk_exact(const LaneBlock &B, uint32_t start, uint4 *rec, uint4 *lanerec, uint32_t &end_state,
+                                                 uint32_t &total_bits)
+{
+    const int lane = threadIdx.x & 31;
+    const bool has = lane > 0 && (B.cnt > 0 || B.is_tail);
+    uint32_t s = start, my_in = start, my_bits = 0, total = 0;
+    for (int l = 1; l < 32; ++l) {
+        uint32_t out = s, b = 0;
+        if (lane == l) {
+            my_in = s;
+            if (has) {
+                State t[1] = {unpack_state(s)};
+                uint32_t bb[1];
+                count_lane<1>(B, t, bb);
+                out = pack_state(t[0]);
+                b = bb[0];
+                my_bits = b;
+            }
+        }
+        s = __shfl_sync(~0u, out, l);
+        total += __shfl_sync(~0u, b, l);
+    }
+    if (lane == 0) my_in = start;
+    uint4 *lr = lanerec + (size_t)lane * LANEREC_WORDS;
+    lr[0] = make_uint4(my_in & 0xffffu, 0u, 0u, 0u);
+    lr[1] = make_uint4(lane == 0 ? 0u : (my_bits & 0xffffu), 0u, 0u, 0u);
+    lr[2] = make_uint4(0u, 0u, 0u, 0u);
+    if (lane == 0) {
+        rec[0] = make_uint4((start & 0xffffu) | (STATE_INVALID << 16), ~0u, ~0u, ~0u);
+        rec[1] = make_uint4(s & 0xffffu, 0u, 0u, 0u);
+        rec[2] = make_uint4(total, 0u, 0u, 0u);
+        rec[3] = make_uint4(0u, 0u, 0u, 0u);
+    }
+    end_state = s;
+    total_bits = total;
+}
+
 // ---- B: resolve ------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(32 * SOLVE_WARPS) rlgr_resolve_kernel(Geometry G, const ChanInfo *__restrict__ info,
                                                           const uint2 *__restrict__ ev, uint4 *__restrict__ rec,
@@ -1025,11 +1067,9 @@ __global__ void __launch_bounds__(32 * SOLVE_WARPS) rlgr_resolve_kernel(Geometry
                         finish_chunk<1>(S, rec + ci * REC_WORDS, lr);
                         rounds = S.rounds;
                     } else {
-                        ChunkSol<8> S;
-                        if (lane == 0) helpers.w = (long long)w;
-                        solve_chunk<8>(B, true, pins, 1u, PIN_ROUNDS, S, &helpers);
-                        finish_chunk<8>(S, rec + ci * REC_WORDS, lr);
-                        rounds = S.rounds;
+                        uint32_t e_x, t_x;
+                        walk_chunk_exact(B, ps, rec + ci * REC_WORDS, lr, e_x, t_x);
+                        rounds = 31;
                     }
                     __syncwarp();
                     const uint4 *rr = rec + ci * REC_WORDS;          // (written by lane 0 just above): the pinned chain is candidate 0

@@ -81,6 +81,122 @@ __global__ void __launch_bounds__(256) shard_top_kernel(const int64_t *__restric
     }
 }
 
+// The same join over CELLS (aligned Morton-prefix subtrees), some of which may be empty: range i holds counts[i] rows,
+// first[i] / last[i] are its first and last Morton code.  Empty cells take no part.  level_out[i]: level of the cell's
+// first row in the whole scene (255 for the first non-empty cell, 0 for empty cells).
+template <typename Tel>
+__global__ void __launch_bounds__(256) shard_top_cells_kernel(const int64_t *__restrict__ first, const int64_t *__restrict__ last,
+                                                              const int64_t *__restrict__ counts, int C, Tel *__restrict__ rows, int D,
+                                                              int inverse, uint8_t *__restrict__ level_out, int32_t *status)
+{
+    __shared__ uint8_t lev[TOP_MAX], live[TOP_MAX];
+    __shared__ int16_t left[TOP_MAX], prevne[TOP_MAX];
+    __shared__ double ca[TOP_MAX], cb[TOP_MAX];
+    __shared__ long long off[TOP_MAX + 1];
+    const int tid = threadIdx.x;
+    if (tid == 0) {                                        // C <= 1024: offsets and the previous non-empty cell, serially
+        long long run = 0;
+        int p = -1;
+        for (int i = 0; i < C; ++i) {
+            off[i] = run;
+            prevne[i] = (int16_t)p;
+            const long long c = counts[i];
+            live[i] = c > 0;
+            if (c > 0) { run += c; p = i; }
+        }
+        off[C] = run;
+    }
+    __syncthreads();
+    for (int i = tid; i < C; i += blockDim.x) {
+        uint8_t l = 0;
+        if (live[i]) {
+            if (prevne[i] < 0) l = 255;
+            else {
+                const int64_t a = last[prevne[i]], b = first[i];
+                if (!(a < b) && status) atomicOr(status, RAHT_ST_NOT_SORTED_UNIQUE);
+                const uint64_t x = (uint64_t)a ^ (uint64_t)b;
+                l = x ? (uint8_t)(63 - __clzll((long long)x)) : (uint8_t)0;
+            }
+        }
+        lev[i] = l;
+    }
+    __syncthreads();
+    for (int i = tid; i < C; i += blockDim.x) {
+        if (level_out) level_out[i] = lev[i];
+        left[i] = -1;
+        if (!live[i] || lev[i] == 255) continue;
+        int s = -1, t = C;
+        for (int j = i - 1; j >= 0; --j) if (live[j] && lev[j] > lev[i]) { s = j; break; }
+        for (int j = i + 1; j < C; ++j) if (live[j] && lev[j] > lev[i]) { t = j; break; }
+        left[i] = (int16_t)s;                              // (s >= 0: the first non-empty cell has level 255)
+        const double w0 = (double)(off[i] - off[s]), w1 = (double)(off[t] - off[i]);
+        const double den = __dadd_rn(w0, w1);                                   // RAHT.py:317
+        ca[i] = __dsqrt_rn(__ddiv_rn(w0, den));                                 // :321
+        cb[i] = __dsqrt_rn(__ddiv_rn(w1, den));                                 // :322
+    }
+    __syncthreads();
+    using AR = TopArith<Tel>;
+    for (int c = tid; c < D; c += blockDim.x) {
+        for (int ll = 0; ll < 63; ++ll) {
+            const int l = inverse ? 62 - ll : ll;
+            for (int i = 1; i < C; ++i) {
+                if (left[i] < 0 || lev[i] != l) continue;
+                Tel *p0 = rows + (size_t)left[i] * D + c, *p1 = rows + (size_t)i * D + c;
+                const Tel a = (Tel)ca[i], b = (Tel)cb[i], x0 = *p0, x1 = *p1;
+                if (!inverse) {
+                    *p0 = AR::add(AR::mul(a, x0), AR::mul(b, x1));             // RAHT.py:331
+                    *p1 = AR::add(AR::mul(-b, x0), AR::mul(a, x1));            // RAHT.py:332
+                } else {
+                    *p0 = AR::sub(AR::mul(a, x0), AR::mul(b, x1));             // iRAHT.py:108
+                    *p1 = AR::add(AR::mul(b, x0), AR::mul(a, x1));             // iRAHT.py:109
+                }
+            }
+        }
+    }
+}
+
+// Gaussians as packed rows [means3 quats4 scales3 opacity1 colors] for the repartition exchange: out[i] = row perm[i]
+// (perm == NULL: identity); and back.  A warp per row.
+__global__ void __launch_bounds__(256) pack_rows_kernel(const uint32_t *__restrict__ perm, int64_t n, const float *__restrict__ means,
+                                                        const float *__restrict__ quats, const float *__restrict__ scales,
+                                                        const float *__restrict__ opac, const float *__restrict__ colors, int cd,
+                                                        float *__restrict__ out)
+{
+    const int lane = threadIdx.x & 31;
+    const int D = 11 + cd;
+    for (int64_t i = (int64_t)blockIdx.x * 8 + (threadIdx.x >> 5); i < n; i += (int64_t)gridDim.x * 8) {
+        const size_t r = perm ? (size_t)perm[i] : (size_t)i;
+        float *dst = out + (size_t)i * D;
+        for (int c = lane; c < D; c += 32) {
+            float v;
+            if (c < 3) v = means[r * 3 + c];
+            else if (c < 7) v = quats[r * 4 + c - 3];
+            else if (c < 10) v = scales[r * 3 + c - 7];
+            else if (c == 10) v = opac[r];
+            else v = colors[r * cd + c - 11];
+            dst[c] = v;
+        }
+    }
+}
+__global__ void __launch_bounds__(256) unpack_rows_kernel(const float *__restrict__ in, int64_t n, int cd, float *__restrict__ means,
+                                                          float *__restrict__ quats, float *__restrict__ scales, float *__restrict__ opac,
+                                                          float *__restrict__ colors)
+{
+    const int lane = threadIdx.x & 31;
+    const int D = 11 + cd;
+    for (int64_t i = (int64_t)blockIdx.x * 8 + (threadIdx.x >> 5); i < n; i += (int64_t)gridDim.x * 8) {
+        const float *src = in + (size_t)i * D;
+        for (int c = lane; c < D; c += 32) {
+            const float v = src[c];
+            if (c < 3) means[(size_t)i * 3 + c] = v;
+            else if (c < 7) quats[(size_t)i * 4 + c - 3] = v;
+            else if (c < 10) scales[(size_t)i * 3 + c - 7] = v;
+            else if (c == 10) opac[i] = v;
+            else colors[(size_t)i * cd + c - 11] = v;
+        }
+    }
+}
+
 }  // namespace
 
 RAHT_API int raht_shard_top(const int64_t *first_keys, const int64_t *prev_last_keys, const int64_t *offsets, int P,
@@ -99,6 +215,50 @@ RAHT_API int raht_shard_top(const int64_t *first_keys, const int64_t *prev_last_
         raht_set_error("raht_shard_top: bad dtype");
         return RAHT_E_INVALID;
     }
+    RAHT_LAUNCH_CHECK();
+    return RAHT_OK;
+}
+
+RAHT_API int raht_shard_top_cells(const int64_t *first_keys, const int64_t *last_keys, const int64_t *counts, int C, void *rows,
+                                  int dtype, int D, int inverse, uint8_t *level_out, int32_t *status, void *stream)
+{
+    RAHT_REQUIRE(C >= 0 && C <= TOP_MAX && D >= 1, "raht_shard_top_cells: C must be in [0, 1024]");
+    if (C == 0) return RAHT_OK;
+    RAHT_REQUIRE(first_keys && last_keys && counts && rows, "raht_shard_top_cells: null pointer");
+    cudaStream_t st = (cudaStream_t)stream;
+    raht_count_launches(1);
+    if (dtype == RAHT_F64)
+        shard_top_cells_kernel<double><<<1, 256, 0, st>>>(first_keys, last_keys, counts, C, (double *)rows, D, inverse, level_out, status);
+    else if (dtype == RAHT_F32)
+        shard_top_cells_kernel<float><<<1, 256, 0, st>>>(first_keys, last_keys, counts, C, (float *)rows, D, inverse, level_out, status);
+    else {
+        raht_set_error("raht_shard_top_cells: bad dtype");
+        return RAHT_E_INVALID;
+    }
+    RAHT_LAUNCH_CHECK();
+    return RAHT_OK;
+}
+
+RAHT_API int raht_pack_rows(const uint32_t *perm, int64_t n, const float *means, const float *quats, const float *scales,
+                            const float *opacities, const float *colors, int color_dim, float *out, void *stream)
+{
+    RAHT_REQUIRE(n >= 0 && color_dim >= 0, "raht_pack_rows: bad arguments");
+    if (n == 0) return RAHT_OK;
+    RAHT_REQUIRE(means && quats && scales && opacities && (colors || color_dim == 0) && out, "raht_pack_rows: null pointer");
+    raht_count_launches(1);
+    pack_rows_kernel<<<grid_for(n, 8, 8), 256, 0, (cudaStream_t)stream>>>(perm, n, means, quats, scales, opacities, colors, color_dim, out);
+    RAHT_LAUNCH_CHECK();
+    return RAHT_OK;
+}
+
+RAHT_API int raht_unpack_rows(const float *rows, int64_t n, int color_dim, float *means, float *quats, float *scales, float *opacities,
+                              float *colors, void *stream)
+{
+    RAHT_REQUIRE(n >= 0 && color_dim >= 0, "raht_unpack_rows: bad arguments");
+    if (n == 0) return RAHT_OK;
+    RAHT_REQUIRE(rows && means && quats && scales && opacities && (colors || color_dim == 0), "raht_unpack_rows: null pointer");
+    raht_count_launches(1);
+    unpack_rows_kernel<<<grid_for(n, 8, 8), 256, 0, (cudaStream_t)stream>>>(rows, n, color_dim, means, quats, scales, opacities, colors);
     RAHT_LAUNCH_CHECK();
     return RAHT_OK;
 }

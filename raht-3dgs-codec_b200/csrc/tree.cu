@@ -162,7 +162,6 @@ __device__ __forceinline__ void plan_tile(const PlanDev &P, int stage, int64_t t
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int64_t gt = P.tile_base[stage] + tile;
     const bool last = tile == P.tiles[stage] - 1;
-    const bool multi = P.tiles[stage] > 1;
     const int64_t n_total = P.n;
 
     if (tid < PLAN_MAX_ROUNDS) { hist[tid] = 0; cur[tid] = 0; }
@@ -211,10 +210,13 @@ __device__ __forceinline__ void plan_tile(const PlanDev &P, int stage, int64_t t
     constexpr int NEAR = 16;
     for (int j = tid; j < n_rows; j += PB_THREADS) {
         const int l = s_lev[j];
-        if (l == 255) {                                   // the root: never a right sibling
+        if (l == 255) {                                   // a root: never a right sibling, and nobody merges it -> final here
+            // (level 255 marks row 0 of a cloud, or the first row of every cell of a FOREST -- the sharded encoder
+            // transforms the aligned Morton-prefix cells of a rank side by side, shard.cu.  Roots are not handed up the
+            // hierarchy: with hundreds of them the 129-entry bound of a tile's deferred list would not hold.)
             s_s[j] = 0xffff;
-            s_t[j] = multi ? 1 : 0;                       // s_t doubles as the "deferred" flag for unschedulable entries
-            if (!multi && w) w[s_orig[j]] = (double)n_total;
+            s_t[j] = 0;                                   // s_t doubles as the "deferred" flag for unschedulable entries
+            if (w && s_orig[j] == 0) w[0] = (double)n_total;      // RAHT.py:325-328: the root of a whole cloud carries every row
             continue;
         }
         int s = -1, t = -1;

@@ -1,23 +1,28 @@
 """Morton-prefix sharding of ONE scene over the GPUs of a box (BASELINE config 4).
 
-The reference is single-GPU; this module keeps its arithmetic and its bitstream.  Rank r of P owns the
-Gaussians whose voxel falls into the r-th range of Morton prefixes (a spatial box: octant halves for
-P = 2, 4, 8), so that the concatenation of the ranks' Morton-sorted voxels in rank order IS the sorted voxel
-list of the scene.  One process per GPU, `torch.distributed` (NCCL over NVLink) for the exchanges:
+The reference is single-GPU; this module keeps its arithmetic and its bitstream.  The bounding cube is cut into
+2^B CELLS by the top B bits of the Morton code (aligned subtrees of the RAHT tree); rank r of P owns a CONTIGUOUS run of
+cells, chosen from the all-reduced cell histogram so that every rank gets about N / P Gaussians whatever the scene looks
+like -- and whatever P is (a rank's range is a union of aligned subtrees by construction; the first version cut the prefix
+space evenly, which is not aligned for P = 5, 7, ...).  The concatenation of the ranks' Morton-sorted voxels in rank order
+IS the sorted voxel list of the scene.  One process per GPU, `torch.distributed` (NCCL over NVLink) for the exchanges:
 
   encode   1 all_reduce   scene bounding box (6 floats)                                  [voxelize_pc.py:87-95]
-           (optional)     all_to_all of the raw Gaussians to the rank that owns their prefix
-           2 all_gather   per rank: rows, first / last Morton code, 22 order-bucket counts
-           --             voxelise + merge + RAHT of the local range (every butterfly inside the range)
-           3 all_gather   the P low-pass rows (D values each); every rank joins them (raht_shard_top)
-           4 all_to_all   quantised coefficients, row-sharded -> channel-sharded in order_RAGFT order
+           2 all_reduce   cell histogram (2^B counts) -> the same owner table on every rank
+           3 all_to_all   the raw Gaussians to their owner, as ONE exchange of packed 236-byte rows (raht_pack_rows)
+           --             voxelise + merge, then the RAHT of the rank's cells as a FOREST: every butterfly below the cell
+                          roots; each cell's low-pass is left in its first row
+           4 all_reduce   one row per cell (2^B x D, the owner contributes, the others add zero bits) + per cell
+                          (rows, first code, last code); every rank joins the cells (raht_shard_top_cells)
+           5 all_gather   rows and the 22 order-bucket counts per rank
+           6 all_to_all   quantised coefficients, row-sharded -> channel-sharded in order_RAGFT order
            --             rank k entropy-codes channels k, k + P, ... of the WHOLE scene
   decode   the mirror image.
 
 Result: coefficients, order and RLGR bytes are bit-identical to the single-GPU encode of the whole scene
-(tests/test_sharded.py).  The compute goes through a small backend object: `DeviceBackend` (the CUDA
-library) is the only one shipped; the CPU test-suite plugs its own checker backend in to exercise the host
-logic (partition, boundary levels, exchanges) over gloo.
+(tests/test_sharded.py, world sizes 2, 3, 5 and 8).  The compute goes through a small backend object: `DeviceBackend`
+(the CUDA library) is the only one shipped; the CPU test-suite plugs its own checker backend in to exercise the host
+logic (partition, cell levels, exchanges) over gloo.
 """
 from dataclasses import dataclass, field
 from typing import List, Optional
@@ -34,13 +39,22 @@ def order_bucket(level: torch.Tensor) -> torch.Tensor:
     return torch.where(lv == 255, torch.zeros_like(lv), 1 + (20 - torch.clamp(lv, max=62) // 3))
 
 
-def owner_of_key(keys: torch.Tensor, J: int, world: int) -> torch.Tensor:
-    """Rank that owns a Morton code: equal ranges of the top ceil(log2 P) prefix bits."""
-    bits = max((world - 1).bit_length(), 0)
-    if bits == 0:
-        return torch.zeros_like(keys)
-    prefix = keys >> (3 * J - bits)
-    return (prefix * world) >> bits
+CELL_BITS_PER_RANK = 5   # ~32 cells per rank on average: the balance error of a rank is one cell
+CELL_BITS_MAX = 10       # raht_shard_top_cells joins up to 1024 cells
+
+
+def cell_bits(world: int, J: int) -> int:
+    """B: the top B bits of the 3J-bit Morton code number the cells."""
+    return max(0, min(3 * J, CELL_BITS_MAX, (max(world, 1) - 1).bit_length() + CELL_BITS_PER_RANK)) if world > 1 else 0
+
+
+def owner_table(hist: torch.Tensor, world: int) -> torch.Tensor:
+    """Owner rank of every cell from the global histogram (device tensor, no synchronisation): a cell goes to the rank in
+    whose share [r N / P, (r + 1) N / P) its first Gaussian falls -- contiguous runs of cells, balanced to within one cell."""
+    h = hist.to(torch.int64)
+    start = torch.cumsum(h, 0) - h
+    total = torch.clamp(h.sum(), min=1)
+    return torch.clamp((start * world) // total, max=world - 1)
 
 
 class DeviceBackend:
@@ -59,12 +73,40 @@ class DeviceBackend:
     def keys(self, means, J, vmin, width):
         return self.codec.morton_keys_given(means, J, vmin, width)
 
+    def pack_by_owner(self, scene, owner, world):
+        """Gaussians as packed (n, D) fp32 rows grouped by owner rank (stable): one hand-written radix pass over the owner
+        ids gives the permutation, raht_pack_rows gathers the five attribute arrays through it."""
+        from ._lib import lib, check, ptr, stream
+        means, quats, scales, opac, colors = [t.contiguous().float() for t in scene]
+        n, cd = means.shape[0], colors.shape[1]
+        out = torch.empty(n, 11 + cd, dtype=torch.float32, device=means.device)
+        if n == 0:
+            return out
+        _, perm, _ = self.ops.radix_sort_pairs(owner.to(torch.int64).contiguous(), max((world - 1).bit_length(), 1))
+        check(lib.raht_pack_rows(ptr(perm), n, ptr(means), ptr(quats), ptr(scales), ptr(opac), ptr(colors), cd, ptr(out), stream()),
+              "raht_pack_rows")
+        return out
+
+    def unpack_rows(self, rows, color_dim):
+        from ._lib import lib, check, ptr, stream
+        n, dev = rows.shape[0], rows.device
+        outs = [torch.empty(n, 3, dtype=torch.float32, device=dev), torch.empty(n, 4, dtype=torch.float32, device=dev),
+                torch.empty(n, 3, dtype=torch.float32, device=dev), torch.empty(n, dtype=torch.float32, device=dev),
+                torch.empty(n, color_dim, dtype=torch.float32, device=dev)]
+        check(lib.raht_unpack_rows(ptr(rows.contiguous()), n, color_dim, *[ptr(o) for o in outs], stream()), "raht_unpack_rows")
+        return tuple(outs)
+
     def voxelize_merge(self, scene, J, vmin, width):
         packed, keys, _ = self.codec.voxelize_merge(*scene, J=J, given=(vmin, width))
         return packed, keys
 
-    def levels(self, keys):
-        return self.ops.tree_from_keys(keys).level
+    def levels(self, keys, cut):
+        """level[] of the rank's rows with every cell a tree of its own: rows that start a cell (their level in the whole
+        scene is >= cut, the lowest prefix bit) become roots (255)."""
+        level = self.ops.tree_from_keys(keys).level
+        if keys.shape[0]:
+            level[level >= cut] = 255
+        return level
 
     def forward_local(self, keys, level, packed, dtype):
         tree = self.ops.RahtTree(level, level.shape[0])
@@ -74,8 +116,17 @@ class DeviceBackend:
         tree = self.ops.RahtTree(level, level.shape[0])
         return self.ops.inverse(tree, T, self.tile_rows)
 
-    def shard_top(self, first, prev_last, offsets, rows, inverse):
-        return self.ops.shard_top(first, prev_last, offsets, rows, inverse)
+    def shard_top_cells(self, first, last, counts, rows, inverse):
+        """raht_shard_top_cells: rows (C, D) in place -> (rows, level of every cell's first row in the whole scene)."""
+        import ctypes as C
+        from ._lib import lib, check, ptr, stream, dtype_tag
+        ncell, D = rows.shape
+        level = torch.empty(ncell, dtype=torch.uint8, device=rows.device)
+        status = torch.zeros(1, dtype=torch.int32, device=rows.device)
+        check(lib.raht_shard_top_cells(ptr(first.contiguous()), ptr(last.contiguous()), ptr(counts.contiguous()), ncell, ptr(rows),
+                                       dtype_tag(rows.dtype), D, 1 if inverse else 0, ptr(level), ptr(status), stream()),
+              "raht_shard_top_cells")
+        return rows, level
 
     def order(self, level_global):
         return self.ops.RahtTree(level_global, level_global.shape[0]).order()
@@ -105,15 +156,16 @@ class ShardedEncoded:
     rank: int
     n_rows: List[int]                    # voxels per rank
     keys: torch.Tensor                   # this rank's voxels (Morton codes, sorted)
-    first_keys: torch.Tensor             # (P,) first code of every non-empty rank, prev_last_keys likewise
-    prev_last_keys: torch.Tensor
+    cell_bits: int                       # B: the scene is cut into 2^B cells
+    cell_meta: torch.Tensor              # (2^B, 3) int64: voxels, first and last Morton code of every cell of the SCENE
+    cell_level: torch.Tensor             # (2^B,) uint8: level of every cell's first row in the whole scene
     bucket_counts: torch.Tensor          # (P, 22)
     channels: List[int]                  # channels whose whole-scene stream this rank holds
     streams: object                      # the backend's stream object for those channels
     vmin: torch.Tensor = None
     width: float = 0.0
     transform_dtype: torch.dtype = torch.float64
-    timings: dict = field(default_factory=dict)
+    collective_bytes: dict = field(default_factory=dict)      # bytes this rank put into each exchange of the encode
 
     @property
     def n_total(self):
@@ -188,26 +240,74 @@ class ShardedCodec:
         width = float((hi - lo).max().item())                    # fp32 subtraction, as V0 = V - vmin; width = V0.max()
         return lo, width
 
-    def repartition(self, scene, J, vmin, width):
-        """Send every Gaussian to the rank that owns its Morton prefix (all_to_all of the raw rows)."""
+    def cell_owner(self, means, J, vmin, width, B):
+        """(owner rank of every local Gaussian, owner table of the cells): cells by the top B bits of the Morton code, owners
+        from the all-reduced histogram -- device arithmetic only, the same table on every rank."""
+        ncell = 1 << B
+        keys = self.be.keys(means, J, vmin, width)
+        cell = keys >> (3 * J - B) if B else torch.zeros_like(keys)
+        hist = torch.zeros(ncell, dtype=torch.int64, device=keys.device)
+        hist.scatter_add_(0, cell, torch.ones_like(cell))
+        if self.world > 1:
+            self._all_reduce(hist, dist.ReduceOp.SUM)
+        table = owner_table(hist, self.world)
+        return table[cell], table
+
+    def repartition(self, scene, owner):
+        """Every Gaussian to the rank that owns its cell: ONE all_to_all of packed rows.  Returns (scene, bytes sent)."""
         if self.world == 1:
-            return scene
-        means = scene[0]
-        owner = owner_of_key(self.be.keys(means, J, vmin, width), J, self.world)
-        perm = torch.argsort(owner, stable=True)
-        counts = torch.bincount(owner, minlength=self.world)
-        all_counts = self._all_gather(counts)                     # (P, P): [sender][receiver]
-        send_sizes = counts.tolist()
+            return scene, 0
+        cd = scene[4].shape[1]
+        D = 11 + cd
+        counts = torch.zeros(self.world, dtype=torch.int64, device=owner.device)
+        counts.scatter_add_(0, owner, torch.ones_like(owner))
+        all_counts = self._all_gather(counts).cpu()               # (P, P): [sender][receiver] -- the split sizes must reach the host
+        send_sizes = all_counts[self.rank].tolist()
         recv_sizes = all_counts[:, self.rank].tolist()
-        out = []
-        for a in scene:
-            cols = 1 if a.dim() == 1 else a.shape[1]
-            rows = a[perm].reshape(-1, cols)
-            parts = list(torch.split(rows, send_sizes))
-            got = self._all_to_all(parts, [r * cols for r in recv_sizes])
-            cat = torch.cat(got).reshape(-1, cols)
-            out.append(cat.reshape(-1) if a.dim() == 1 else cat)
-        return tuple(out)
+        rows = self.be.pack_by_owner(scene, owner, self.world)    # grouped by owner, stable
+        parts = list(torch.split(rows, send_sizes))
+        got = self._all_to_all(parts, [r * D for r in recv_sizes])
+        rows_in = torch.cat(got).reshape(-1, D)
+        return self.be.unpack_rows(rows_in, cd), int(rows.numel() * 4)
+
+    def _cell_meta(self, keys, J, B):
+        """Per cell of the scene, from this rank's sorted voxel keys: (count, first key, last key) and the row at which
+        the cell starts here (meaningful where count > 0).  Device arithmetic only."""
+        ncell = 1 << B
+        dev = keys.device
+        n = keys.shape[0]
+        cnt = torch.zeros(ncell, dtype=torch.int64, device=dev)
+        if n:
+            cell = keys >> (3 * J - B) if B else torch.zeros_like(keys)
+            cnt.scatter_add_(0, cell, torch.ones_like(cell))
+        start = torch.cumsum(cnt, 0) - cnt
+        live = cnt > 0
+        zero = torch.zeros_like(cnt)
+        if n:
+            first = torch.where(live, keys[torch.clamp(start, max=n - 1)], zero)
+            last = torch.where(live, keys[torch.clamp(start + cnt - 1, min=0, max=n - 1)], zero)
+        else:
+            first, last = zero, zero.clone()
+        return torch.stack([cnt, first, last], 1), start, live
+
+    def _join_cells(self, T, start, live, meta, inverse):
+        """The butterflies above the cells: every rank contributes the low-pass rows of its cells (first row of each),
+        an all_reduce over the bit patterns (the owner's row plus zeros: exact, signed zeros included) hands every rank all
+        of them, raht_shard_top_cells joins them, and the rank's own rows go back.  Returns the cells' levels."""
+        ncell, D = live.shape[0], T.shape[1]
+        dev = T.device
+        n = T.shape[0]
+        rows = torch.zeros(ncell, D, dtype=T.dtype, device=dev)
+        if n:
+            mine = torch.nonzero(live).reshape(-1)                # (a few hundred cells at most)
+            rows[mine] = T[start[mine]]
+        if self.world > 1:
+            as_int = rows.view(torch.int64 if T.dtype == torch.float64 else torch.int32)
+            self._all_reduce(as_int, dist.ReduceOp.SUM)
+        rows, cell_level = self.be.shard_top_cells(meta[:, 1].contiguous(), meta[:, 2].contiguous(), meta[:, 0].contiguous(), rows, inverse)
+        if n:
+            T[start[mine]] = rows[mine]
+        return cell_level
 
     # ---- encode ------------------------------------------------------------------------------------
     @torch.no_grad()
@@ -215,66 +315,62 @@ class ShardedCodec:
         be, P, r = self.be, self.world, self.rank
         mark = timer.mark if timer is not None else (lambda name: None)
         mark("start")
+        sent = {}
         scene = (means, quats, scales, opacities, colors)
         vmin, width = self.scene_bounds(means)
         mark("bounds_allreduce")
-        if repartition:
-            scene = self.repartition(scene, J, vmin, width)
+        B = cell_bits(P, J)
+        if repartition and P > 1:
+            owner, _ = self.cell_owner(means, J, vmin, width, B)
+            mark("cell_histogram")
+            scene, sent["repartition_alltoall"] = self.repartition(scene, owner)
         mark("repartition_alltoall")
         packed, keys = be.voxelize_merge(scene, J, vmin, width)
         mark("voxelize_merge")
         n, D = packed.shape
         dev = packed.device
-        if n and P > 1:
-            own = owner_of_key(keys[[0, -1]], J, P)
-            if int(own[0]) != r or int(own[1]) != r:
-                raise ValueError("sharded encode: this rank holds Gaussians outside its Morton-prefix range (use repartition=True)")
-        # per rank: rows, first and last code
-        meta = torch.zeros(3, dtype=torch.int64, device=dev)
-        meta[0] = n
-        if n:
-            meta[1], meta[2] = keys[0], keys[-1]
-        allmeta = self._all_gather(meta)                          # (P, 3)
-        n_rows = allmeta[:, 0].tolist()
-        nonempty = [k for k in range(P) if n_rows[k] > 0]
-        first = allmeta[nonempty, 1].contiguous()
-        last = allmeta[nonempty, 2]
-        prev_last = torch.cat([first[:1], last[:-1]]).contiguous() if nonempty else first
-        offs = torch.zeros(len(nonempty) + 1, dtype=torch.int64, device=dev)
-        offs[1:] = torch.cumsum(allmeta[nonempty, 0], 0)
-        # local transform: every butterfly inside this range; the range's low-pass is left in its first row
-        level = be.levels(keys) if n else torch.empty(0, dtype=torch.uint8, device=dev)
+        # the rank's cells as a forest: every butterfly below the cell roots; each cell's low-pass is left in its first row
+        level = be.levels(keys, 3 * J - B) if n else torch.empty(0, dtype=torch.uint8, device=dev)
         T = be.forward_local(keys, level, packed, transform_dtype) if n else torch.empty(0, D, dtype=transform_dtype, device=dev)
         mark("raht_local")
-        root = T[0].clone() if n else torch.zeros(D, dtype=transform_dtype, device=dev)
-        roots = self._all_gather(root)[nonempty].contiguous()     # (P', D)
-        roots, top_level = be.shard_top(first, prev_last, offs, roots, False)       # the butterflies that join the ranges
-        mark("top_allgather_join")
+        meta_local, start, live = self._cell_meta(keys, J, B)
+        meta = meta_local.clone()
+        if P > 1:
+            self._all_reduce(meta, dist.ReduceOp.SUM)             # (every cell has one owner: the others add zeros)
+        cell_level = self._join_cells(T, start, live, meta, False)
+        sent["cells_allreduce"] = int(meta.numel() * 8 + (1 << B) * D * T.element_size())
+        mark("top_allreduce_join")
         level_g = level.clone()
         if n:
-            me = nonempty.index(r)
-            T[0] = roots[me]
-            level_g[0] = top_level[me]                            # 255 on the first range: the root of the scene
-        # order_RAGFT of the scene restricted to this range, and where each of its groups sits in the whole sequence
+            mine = torch.nonzero(live).reshape(-1)
+            level_g[start[mine]] = cell_level[mine]               # 255 on the first cell of the scene: its root
+        # order_RAGFT of the scene restricted to this rank, and where each of its groups sits in the whole sequence
         order = be.order(level_g) if n else torch.empty(0, dtype=torch.int64, device=dev)
-        counts = torch.bincount(order_bucket(level_g), minlength=N_BUCKETS) if n else torch.zeros(N_BUCKETS, dtype=torch.int64, device=dev)
-        bucket_counts = self._all_gather(counts)                  # (P, 22)
+        counts = torch.zeros(N_BUCKETS + 1, dtype=torch.int64, device=dev)
+        if n:
+            bk = order_bucket(level_g)
+            counts[:N_BUCKETS].scatter_add_(0, bk, torch.ones_like(bk))
+        counts[N_BUCKETS] = n
+        gathered = self._all_gather(counts).cpu()                 # (P, 23): one small host read for the exchange sizes
+        bucket_counts = gathered[:, :N_BUCKETS].contiguous()
+        n_rows = gathered[:, N_BUCKETS].tolist()
         q = be.quant_reorder(T, order, step) if n else torch.empty(D, 0, dtype=torch.int32, device=dev)
-        q = q[:, :n].contiguous()                                 # (D, n) channel-major, local bucket order
+        q = q[:, :n]
         mark("order_quant")
         # row-sharded -> channel-sharded: rank k gets channels k, k + P, ... of every rank
         chans = [list(range(k, D, P)) for k in range(P)]
-        parts = [q[chans[k]] for k in range(P)]
+        parts = [q[chans[k]].contiguous() for k in range(P)] if P > 1 else [q.contiguous()]
         got = self._all_to_all(parts, [len(chans[r]) * n_rows[k] for k in range(P)])
         blocks = [got[k].reshape(len(chans[r]), n_rows[k]) for k in range(P)]
+        sent["coeff_alltoall"] = int(q.numel() * 4)
         mark("coeff_alltoall")
         qg = interleave_buckets(blocks, bucket_counts)            # (|C_r|, N) in order_RAGFT order of the whole scene
         mark("interleave")
         streams = be.rlgr_encode(qg)
         mark("rlgr_encode")
-        return ShardedEncoded(J=J, D=D, step=step, world=P, rank=r, n_rows=n_rows, keys=keys, first_keys=first,
-                              prev_last_keys=prev_last, bucket_counts=bucket_counts, channels=chans[r], streams=streams,
-                              vmin=vmin, width=width, transform_dtype=transform_dtype)
+        return ShardedEncoded(J=J, D=D, step=step, world=P, rank=r, n_rows=n_rows, keys=keys, cell_bits=B, cell_meta=meta,
+                              cell_level=cell_level, bucket_counts=bucket_counts, channels=chans[r], streams=streams,
+                              vmin=vmin, width=width, transform_dtype=transform_dtype, collective_bytes=sent)
 
     # ---- decode ------------------------------------------------------------------------------------
     @torch.no_grad()
@@ -283,7 +379,7 @@ class ShardedCodec:
         be, P, r = self.be, self.world, self.rank
         mark = timer.mark if timer is not None else (lambda name: None)
         mark("start_dec")
-        D, n_rows = enc.D, enc.n_rows
+        D, n_rows, J, B = enc.D, enc.n_rows, enc.J, enc.cell_bits
         n = n_rows[r]
         dev = enc.keys.device
         chans = [list(range(k, D, P)) for k in range(P)]
@@ -296,25 +392,17 @@ class ShardedCodec:
         q = torch.empty(D, n, dtype=torch.int32, device=dev)
         for k in range(P):
             q[chans[k]] = got[k].reshape(len(chans[k]), n)
-        nonempty = [k for k in range(P) if n_rows[k] > 0]
-        offs = torch.zeros(len(nonempty) + 1, dtype=torch.int64, device=dev)
-        offs[1:] = torch.cumsum(torch.tensor([n_rows[k] for k in nonempty], dtype=torch.int64, device=dev), 0)
-        level = be.levels(enc.keys) if n else torch.empty(0, dtype=torch.uint8, device=dev)
-        # the levels of the ranges' first rows in the whole scene (no data needed: P codes)
-        _, top_level = be.shard_top(enc.first_keys, enc.prev_last_keys, offs,
-                                    torch.zeros(len(nonempty), D, dtype=enc.transform_dtype, device=dev), True)
+        level = be.levels(enc.keys, 3 * J - B) if n else torch.empty(0, dtype=torch.uint8, device=dev)
+        _, start, live = self._cell_meta(enc.keys, J, B)
         level_g = level.clone()
         if n:
-            me = nonempty.index(r)
-            level_g[0] = top_level[me]
+            mine = torch.nonzero(live).reshape(-1)
+            level_g[start[mine]] = enc.cell_level[mine]
         order = be.order(level_g) if n else torch.empty(0, dtype=torch.int64, device=dev)
         T = be.dequant_unreorder(q, order, enc.step, enc.transform_dtype) if n else torch.empty(0, D, dtype=enc.transform_dtype, device=dev)
-        root = T[0].clone() if n else torch.zeros(D, dtype=enc.transform_dtype, device=dev)
-        roots = self._all_gather(root)[nonempty].contiguous()
-        roots, _ = be.shard_top(enc.first_keys, enc.prev_last_keys, offs, roots, True)
+        self._join_cells(T, start, live, enc.cell_meta, True)
         mark("dequant_top_dec")
         if n:
-            T[0] = roots[me]
             T = be.inverse_local(enc.keys, level, T)
         mark("iraht_local")
         return T
