@@ -156,7 +156,7 @@ __device__ __forceinline__ void plan_tile(const PlanDev &P, int stage, int64_t t
     __shared__ int hist[PLAN_MAX_ROUNDS], offs[PLAN_MAX_ROUNDS], cur[PLAN_MAX_ROUNDS];
     __shared__ int s_off[PLAN_FANIN + 1];
     __shared__ int wsum[PB_WARPS];
-    __shared__ int s_nbf, s_nr, s_bfoff, s_run, s_npend;
+    __shared__ int s_nbf, s_nr, s_bfoff, s_run, s_npend, s_lastroot;
     __shared__ uint16_t s_pend[PLAN_UP_CAP];       // entries whose partners lie far away
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -165,7 +165,7 @@ __device__ __forceinline__ void plan_tile(const PlanDev &P, int stage, int64_t t
     const int64_t n_total = P.n;
 
     if (tid < PLAN_MAX_ROUNDS) { hist[tid] = 0; cur[tid] = 0; }
-    if (tid == 0) s_npend = 0;
+    if (tid == 0) { s_npend = 0; s_lastroot = -1; }
     int n_rows;
     if (stage == 0) {
         const int64_t base = tile * P.tile_rows;
@@ -202,6 +202,9 @@ __device__ __forceinline__ void plan_tile(const PlanDev &P, int stage, int64_t t
     }
     if (tid == 0 && last) { s_lev[n_rows] = 255; s_orig[n_rows] = (uint32_t)n_total; }   // virtual end of the cloud
     __syncthreads();
+    for (int j = tid; j < n_rows; j += PB_THREADS)
+        if (s_lev[j] == 255) atomicMax(&s_lastroot, j);
+    __syncthreads();
 
     // partner search: s = nearest earlier entry with a higher level, t = nearest later one.  Nearly every entry finds
     // both within a few positions; the few that have to look far (the high levels of an upper tile: up to 1000 steps,
@@ -210,13 +213,17 @@ __device__ __forceinline__ void plan_tile(const PlanDev &P, int stage, int64_t t
     constexpr int NEAR = 16;
     for (int j = tid; j < n_rows; j += PB_THREADS) {
         const int l = s_lev[j];
-        if (l == 255) {                                   // a root: never a right sibling, and nobody merges it -> final here
-            // (level 255 marks row 0 of a cloud, or the first row of every cell of a FOREST -- the sharded encoder
-            // transforms the aligned Morton-prefix cells of a rank side by side, shard.cu.  Roots are not handed up the
-            // hierarchy: with hundreds of them the 129-entry bound of a tile's deferred list would not hold.)
+        if (l == 255) {                                   // a root: never a right sibling
+            // Level 255 marks row 0 of a cloud, or the first row of every cell of a FOREST (the sharded encoder transforms
+            // the aligned Morton-prefix cells of a rank side by side, shard.cu).  A root is the left partner of the
+            // high-level entries of its cell, so it travels up the hierarchy with them -- but only while its cell
+            // reaches past the end of this tile: a root that is followed by another root in the same tile (or by the end
+            // of the cloud) has its whole cell here and is final.  At most ONE root per tile is handed up, which keeps
+            // the 129-entry bound of the deferred list whatever the number of cells.
+            const bool up = j == s_lastroot && !last;
             s_s[j] = 0xffff;
-            s_t[j] = 0;                                   // s_t doubles as the "deferred" flag for unschedulable entries
-            if (w && s_orig[j] == 0) w[0] = (double)n_total;      // RAHT.py:325-328: the root of a whole cloud carries every row
+            s_t[j] = up ? 1 : 0;                          // s_t doubles as the "deferred" flag for unschedulable entries
+            if (!up && w && s_orig[j] == 0) w[0] = (double)n_total;   // RAHT.py:325-328: the root of a whole cloud carries every row
             continue;
         }
         int s = -1, t = -1;

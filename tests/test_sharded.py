@@ -1,10 +1,10 @@
 """Morton-prefix sharding of one scene (raht_b200/sharded.py): P ranks must produce the
 coefficients and the RLGR bytes of the single-process encode of the whole scene, bit for bit.
 
-CPU (not gpu): world_size 2 and 3 over gloo with the ORACLE plugged in as the compute backend -- checks the
+CPU (not gpu): world_size 2, 3 and 5 over gloo with the ORACLE plugged in as the compute backend -- checks the
 host logic (partition by prefix, boundary levels, the butterflies that join the ranges, order_RAGFT across
 ranks, the row-sharded -> channel-sharded exchange and its mirror).
-GPU: the same with the CUDA library as backend, two processes sharing cuda:0 (gloo, staged through the host;
+GPU: the same with the CUDA library as backend, 2 / 3 / 8 processes sharing cuda:0 (gloo, staged through the host;
 on a multi-GPU box the production path is NCCL, see bench.py --workload c4)."""
 import os
 import sys
@@ -190,7 +190,7 @@ def _run(world, use_cuda, n_scene=N_SCENE, J=J):
     assert np.array_equal(np.concatenate([o["rec"] for o in outs]), rec)                # decoded attributes, bit for bit
 
 
-@pytest.mark.parametrize("world", [2, 3, 5, 8])
+@pytest.mark.parametrize("world", [2, 3, 5])
 def test_sharded_encode_matches_single_process_gloo_cpu(world):
     """World sizes that are not powers of two included (5: the first version gave rank 3 the prefixes 101 and 110, which are
     not siblings -- every rank's range is now a union of whole cells, each transformed as its own tree)."""
@@ -213,7 +213,7 @@ def test_interleave_roundtrip():
 
 
 @pytest.mark.gpu
-@pytest.mark.parametrize("world,n_scene,J", [(2, N_SCENE, J), (3, 60000, 10), (2, 2_000_000, 16)])
+@pytest.mark.parametrize("world,n_scene,J", [(2, N_SCENE, J), (3, 60000, 10), (8, 50000, 9), (2, 2_000_000, 16)])
 def test_sharded_encode_matches_single_process_cuda(world, n_scene, J):
     """The CUDA library behind the sharded codec, `world` processes sharing cuda:0 (gloo, staged through the host), up to a
     2 M-Gaussian scene at depth 16: keys, every RLGR stream and the decoded attributes equal the single-process oracle's."""
