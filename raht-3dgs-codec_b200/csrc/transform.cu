@@ -371,7 +371,9 @@ __device__ __forceinline__ void upper_tile(const PlanDev &P, int stage, int64_t 
     const int n_bf = s_hdr.n_bf;
     const int n_rounds = s_hdr.n_rounds;
     const size_t bf_off = s_hdr.bf_off;
-    if (n_bf == 0) return;                                   // nothing scheduled: every row stays as it is
+    // nothing scheduled: forward, every row stays as it is; the inverse still has to carry the tile's rows from T (or from
+    // the parent's output) to C -- a forest root that became final in this tile is read from C by the child that deferred it
+    if (n_bf == 0 && FWD) return;
     for (int c = 0; c < PLAN_FANIN; ++c) {
         const int cnt = s_off[c + 1] - s_off[c];
         const size_t src = (size_t)(cbase + c0 + c) * PLAN_DEFER_MAX;

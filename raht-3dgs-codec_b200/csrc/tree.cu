@@ -156,7 +156,7 @@ __device__ __forceinline__ void plan_tile(const PlanDev &P, int stage, int64_t t
     __shared__ int hist[PLAN_MAX_ROUNDS], offs[PLAN_MAX_ROUNDS], cur[PLAN_MAX_ROUNDS];
     __shared__ int s_off[PLAN_FANIN + 1];
     __shared__ int wsum[PB_WARPS];
-    __shared__ int s_nbf, s_nr, s_bfoff, s_run, s_npend, s_lastroot;
+    __shared__ int s_nbf, s_nr, s_bfoff, s_run, s_npend, s_lastroot, s_firstroot;
     __shared__ uint16_t s_pend[PLAN_UP_CAP];       // entries whose partners lie far away
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -165,7 +165,7 @@ __device__ __forceinline__ void plan_tile(const PlanDev &P, int stage, int64_t t
     const int64_t n_total = P.n;
 
     if (tid < PLAN_MAX_ROUNDS) { hist[tid] = 0; cur[tid] = 0; }
-    if (tid == 0) { s_npend = 0; s_lastroot = -1; }
+    if (tid == 0) { s_npend = 0; s_lastroot = -1; s_firstroot = 0x7fffffff; }
     int n_rows;
     if (stage == 0) {
         const int64_t base = tile * P.tile_rows;
@@ -203,7 +203,7 @@ __device__ __forceinline__ void plan_tile(const PlanDev &P, int stage, int64_t t
     if (tid == 0 && last) { s_lev[n_rows] = 255; s_orig[n_rows] = (uint32_t)n_total; }   // virtual end of the cloud
     __syncthreads();
     for (int j = tid; j < n_rows; j += PB_THREADS)
-        if (s_lev[j] == 255) atomicMax(&s_lastroot, j);
+        if (s_lev[j] == 255) { atomicMax(&s_lastroot, j); atomicMin(&s_firstroot, j); }
     __syncthreads();
 
     // partner search: s = nearest earlier entry with a higher level, t = nearest later one.  Nearly every entry finds
@@ -216,11 +216,12 @@ __device__ __forceinline__ void plan_tile(const PlanDev &P, int stage, int64_t t
         if (l == 255) {                                   // a root: never a right sibling
             // Level 255 marks row 0 of a cloud, or the first row of every cell of a FOREST (the sharded encoder transforms
             // the aligned Morton-prefix cells of a rank side by side, shard.cu).  A root is the left partner of the
-            // high-level entries of its cell, so it travels up the hierarchy with them -- but only while its cell
-            // reaches past the end of this tile: a root that is followed by another root in the same tile (or by the end
-            // of the cloud) has its whole cell here and is final.  At most ONE root per tile is handed up, which keeps
-            // the 129-entry bound of the deferred list whatever the number of cells.
-            const bool up = j == s_lastroot && !last;
+            // high-level entries of its own cell AND the right boundary of those of the cell before it, so it travels up
+            // the hierarchy as long as either cell reaches out of this tile: the LAST root of a tile goes up unless the
+            // cloud ends here, the FIRST one unless the cloud starts with it; a root between two others has both cells
+            // entirely inside the tile and is final.  At most two roots per tile are handed up: with at most 63 + 63
+            // ordinary entries (levels 0 .. 62) the 129-entry bound of the deferred list holds for any number of cells.
+            const bool up = !((j != s_firstroot || s_orig[j] == 0) && (j != s_lastroot || last));
             s_s[j] = 0xffff;
             s_t[j] = up ? 1 : 0;                          // s_t doubles as the "deferred" flag for unschedulable entries
             if (!up && w && s_orig[j] == 0) w[0] = (double)n_total;   // RAHT.py:325-328: the root of a whole cloud carries every row
