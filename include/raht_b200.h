@@ -29,7 +29,7 @@
 extern "C" {
 #endif
 
-#define RAHT_B200_ABI_VERSION 12
+#define RAHT_B200_ABI_VERSION 13
 
 enum {
     RAHT_OK = 0,
@@ -228,6 +228,11 @@ int raht_pack_rows(const uint32_t *perm, int64_t n, const float *means, const fl
                    float *out, void *stream);
 int raht_unpack_rows(const float *rows, int64_t n, int color_dim, float *means, float *quats,
                      float *scales, float *opacities, float *colors, void *stream);
+
+/* counts[b] (nbins <= 4096 int64, overwritten) = how many values[i] >> shift equal b (larger ones count in the last
+ * bin): the cell histogram and the per-owner counts of the sharded partition.                               */
+int raht_histogram_i64(const int64_t *values, int64_t n, int shift, int nbins, int64_t *counts,
+                       void *stream);
 
 /* Fused forms of raht_forward + raht_quant_reorder and of raht_dequant_unreorder + raht_inverse (same results, bit for
  * bit): the rows a stage-0 tile of the plan finishes -- all but the ones it defers to the upper stages -- are quantised

@@ -197,6 +197,30 @@ __global__ void __launch_bounds__(256) unpack_rows_kernel(const float *__restric
     }
 }
 
+// Histogram of (v[i] >> shift) over a few bins (cells of the sharded partition, owner ranks): per-CTA counters in
+// shared memory, a warp adds one count per distinct bin (match_any) -- a global scatter_add over 2 .. 1024 bins serialises
+// 25 M atomics on a handful of addresses (measured 5-10 ms per histogram in the first sharded version).
+constexpr int HIST_MAX_BINS = 4096;
+__global__ void __launch_bounds__(256) histogram_kernel(const int64_t *__restrict__ v, int64_t n, int shift, int nbins,
+                                                        unsigned long long *__restrict__ out)
+{
+    extern __shared__ unsigned int h[];
+    for (int b = threadIdx.x; b < nbins; b += blockDim.x) h[b] = 0u;
+    __syncthreads();
+    const int lane = threadIdx.x & 31;
+    for (int64_t i0 = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x - lane); i0 < n; i0 += (int64_t)gridDim.x * blockDim.x) {
+        const int64_t i = i0 + lane;
+        const bool ok = i < n;
+        int b = ok ? (int)((uint64_t)v[i] >> shift) : -1;
+        if (b >= nbins) b = nbins - 1;
+        const unsigned peers = __match_any_sync(~0u, b);
+        if (ok && lane == __ffs((int)peers) - 1) atomicAdd(&h[b], (unsigned)__popc(peers));
+    }
+    __syncthreads();
+    for (int b = threadIdx.x; b < nbins; b += blockDim.x)
+        if (h[b]) atomicAdd(out + b, (unsigned long long)h[b]);
+}
+
 }  // namespace
 
 RAHT_API int raht_shard_top(const int64_t *first_keys, const int64_t *prev_last_keys, const int64_t *offsets, int P,
@@ -259,6 +283,19 @@ RAHT_API int raht_unpack_rows(const float *rows, int64_t n, int color_dim, float
     RAHT_REQUIRE(rows && means && quats && scales && opacities && (colors || color_dim == 0), "raht_unpack_rows: null pointer");
     raht_count_launches(1);
     unpack_rows_kernel<<<grid_for(n, 8, 8), 256, 0, (cudaStream_t)stream>>>(rows, n, color_dim, means, quats, scales, opacities, colors);
+    RAHT_LAUNCH_CHECK();
+    return RAHT_OK;
+}
+
+RAHT_API int raht_histogram_i64(const int64_t *values, int64_t n, int shift, int nbins, int64_t *counts, void *stream)
+{
+    RAHT_REQUIRE(n >= 0 && shift >= 0 && shift < 64 && nbins >= 1 && nbins <= HIST_MAX_BINS && counts, "raht_histogram_i64: bad arguments");
+    cudaStream_t st = (cudaStream_t)stream;
+    RAHT_CUDA(cudaMemsetAsync(counts, 0, (size_t)nbins * 8, st));
+    if (n == 0) return RAHT_OK;
+    RAHT_REQUIRE(values, "raht_histogram_i64: null pointer");
+    raht_count_launches(1);
+    histogram_kernel<<<grid_for(n, 256, 4), 256, (size_t)nbins * 4, st>>>(values, n, shift, nbins, (unsigned long long *)counts);
     RAHT_LAUNCH_CHECK();
     return RAHT_OK;
 }

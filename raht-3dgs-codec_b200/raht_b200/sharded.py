@@ -73,6 +73,13 @@ class DeviceBackend:
     def keys(self, means, J, vmin, width):
         return self.codec.morton_keys_given(means, J, vmin, width)
 
+    def histogram(self, values, shift, nbins):
+        """counts (nbins,) int64 of values >> shift (raht_histogram_i64: shared-memory counters, no contended global atomics)."""
+        from ._lib import lib, check, ptr, stream
+        out = torch.empty(nbins, dtype=torch.int64, device=values.device)
+        check(lib.raht_histogram_i64(ptr(values.contiguous()), values.shape[0], shift, nbins, ptr(out), stream()), "raht_histogram_i64")
+        return out
+
     def pack_by_owner(self, scene, owner, world):
         """Gaussians as packed (n, D) fp32 rows grouped by owner rank (stable): one hand-written radix pass over the owner
         ids gives the permutation, raht_pack_rows gathers the five attribute arrays through it."""
@@ -204,29 +211,35 @@ class ShardedCodec:
         else:
             dist.all_reduce(t, op=op, group=self.group)
 
-    def _all_to_all(self, chunks: List[torch.Tensor], recv_sizes: List[int]) -> List[torch.Tensor]:
-        """chunks[k] goes to rank k; returns what every rank sent here (1-D tensors)."""
+    def _exchange(self, send: torch.Tensor, send_sizes: List[int], recv_sizes: List[int]) -> torch.Tensor:
+        """all_to_all of flat buffers: elements [sum(send_sizes[:k]), +send_sizes[k]) of `send` go to rank k; returns what
+        every rank sent here, in rank order, as ONE flat tensor (no concatenation on either side)."""
+        send = send.reshape(-1)
         if self.world == 1:
-            return [chunks[0].reshape(-1).clone()]
-        send = torch.cat([c.reshape(-1) for c in chunks])
+            return send
         recv = torch.empty(sum(recv_sizes), dtype=send.dtype, device=send.device)
         if dist.get_backend(self.group) == "gloo":              # host path of the tests: pairwise send / recv
-            dev = chunks[0].device
-            outs = [None] * self.world
+            so = [0]
+            for x in send_sizes:
+                so.append(so[-1] + x)
+            ro = [0]
+            for x in recv_sizes:
+                ro.append(ro[-1] + x)
+            host_send = send.cpu()
+            host_recv = torch.empty(sum(recv_sizes), dtype=send.dtype)
             reqs = []
             for k in range(self.world):
                 if k == self.rank:
-                    outs[k] = chunks[k].reshape(-1).clone()
+                    host_recv[ro[k]:ro[k + 1]] = host_send[so[k]:so[k + 1]]
                     continue
-                outs[k] = torch.empty(recv_sizes[k], dtype=send.dtype)
-                reqs.append(dist.isend(chunks[k].reshape(-1).cpu().contiguous(), k, group=self.group))
-                reqs.append(dist.irecv(outs[k], k, group=self.group))
+                reqs.append(dist.isend(host_send[so[k]:so[k + 1]].contiguous(), k, group=self.group))
+                reqs.append(dist.irecv(host_recv[ro[k]:ro[k + 1]], k, group=self.group))
             for q in reqs:
                 q.wait()
-            return [o.to(dev) for o in outs]
-        dist.all_to_all_single(recv, send, output_split_sizes=recv_sizes, input_split_sizes=[c.numel() for c in chunks],
-                               group=self.group)
-        return list(torch.split(recv, recv_sizes))
+            recv.copy_(host_recv)
+            return recv
+        dist.all_to_all_single(recv, send, output_split_sizes=recv_sizes, input_split_sizes=send_sizes, group=self.group)
+        return recv
 
     # ---- partition ---------------------------------------------------------------------------------
     def scene_bounds(self, means):
@@ -246,8 +259,7 @@ class ShardedCodec:
         ncell = 1 << B
         keys = self.be.keys(means, J, vmin, width)
         cell = keys >> (3 * J - B) if B else torch.zeros_like(keys)
-        hist = torch.zeros(ncell, dtype=torch.int64, device=keys.device)
-        hist.scatter_add_(0, cell, torch.ones_like(cell))
+        hist = self.be.histogram(keys, 3 * J - B if B else 63, ncell)
         if self.world > 1:
             self._all_reduce(hist, dist.ReduceOp.SUM)
         table = owner_table(hist, self.world)
@@ -259,15 +271,12 @@ class ShardedCodec:
             return scene, 0
         cd = scene[4].shape[1]
         D = 11 + cd
-        counts = torch.zeros(self.world, dtype=torch.int64, device=owner.device)
-        counts.scatter_add_(0, owner, torch.ones_like(owner))
+        counts = self.be.histogram(owner, 0, self.world)
         all_counts = self._all_gather(counts).cpu()               # (P, P): [sender][receiver] -- the split sizes must reach the host
         send_sizes = all_counts[self.rank].tolist()
         recv_sizes = all_counts[:, self.rank].tolist()
         rows = self.be.pack_by_owner(scene, owner, self.world)    # grouped by owner, stable
-        parts = list(torch.split(rows, send_sizes))
-        got = self._all_to_all(parts, [r * D for r in recv_sizes])
-        rows_in = torch.cat(got).reshape(-1, D)
+        rows_in = self._exchange(rows, [c * D for c in send_sizes], [c * D for c in recv_sizes]).reshape(-1, D)
         return self.be.unpack_rows(rows_in, cd), int(rows.numel() * 4)
 
     def _cell_meta(self, keys, J, B):
@@ -276,10 +285,12 @@ class ShardedCodec:
         ncell = 1 << B
         dev = keys.device
         n = keys.shape[0]
-        cnt = torch.zeros(ncell, dtype=torch.int64, device=dev)
-        if n:
-            cell = keys >> (3 * J - B) if B else torch.zeros_like(keys)
-            cnt.scatter_add_(0, cell, torch.ones_like(cell))
+        if n and B:                                                # the keys are sorted: a cell is a contiguous run of rows
+            lower = torch.arange(ncell + 1, dtype=torch.int64, device=dev) << (3 * J - B)
+            edges = torch.searchsorted(keys, lower)
+            cnt = edges[1:] - edges[:-1]
+        else:
+            cnt = torch.full((ncell,), n, dtype=torch.int64, device=dev)
         start = torch.cumsum(cnt, 0) - cnt
         live = cnt > 0
         zero = torch.zeros_like(cnt)
@@ -347,9 +358,10 @@ class ShardedCodec:
         # order_RAGFT of the scene restricted to this rank, and where each of its groups sits in the whole sequence
         order = be.order(level_g) if n else torch.empty(0, dtype=torch.int64, device=dev)
         counts = torch.zeros(N_BUCKETS + 1, dtype=torch.int64, device=dev)
-        if n:
-            bk = order_bucket(level_g)
-            counts[:N_BUCKETS].scatter_add_(0, bk, torch.ones_like(bk))
+        if n:                                                      # (order lists the rows bucket by bucket: the counts are its run lengths)
+            bk = order_bucket(level_g[order])
+            edges = torch.searchsorted(bk, torch.arange(N_BUCKETS + 1, dtype=torch.int64, device=dev))
+            counts[:N_BUCKETS] = edges[1:] - edges[:-1]
         counts[N_BUCKETS] = n
         gathered = self._all_gather(counts).cpu()                 # (P, 23): one small host read for the exchange sizes
         bucket_counts = gathered[:, :N_BUCKETS].contiguous()
@@ -359,9 +371,14 @@ class ShardedCodec:
         mark("order_quant")
         # row-sharded -> channel-sharded: rank k gets channels k, k + P, ... of every rank
         chans = [list(range(k, D, P)) for k in range(P)]
-        parts = [q[chans[k]].contiguous() for k in range(P)] if P > 1 else [q.contiguous()]
-        got = self._all_to_all(parts, [len(chans[r]) * n_rows[k] for k in range(P)])
-        blocks = [got[k].reshape(len(chans[r]), n_rows[k]) for k in range(P)]
+        by_dest = torch.tensor([c for k in range(P) for c in chans[k]], dtype=torch.int64, device=dev)
+        send = q[by_dest] if P > 1 else q.contiguous()           # (D, n): the channels grouped by destination, one gather
+        recv = self._exchange(send, [len(chans[k]) * n for k in range(P)], [len(chans[r]) * n_rows[k] for k in range(P)])
+        blocks, o = [], 0
+        for k in range(P):
+            m = len(chans[r]) * n_rows[k]
+            blocks.append(recv[o:o + m].reshape(len(chans[r]), n_rows[k]))
+            o += m
         sent["coeff_alltoall"] = int(q.numel() * 4)
         mark("coeff_alltoall")
         qg = interleave_buckets(blocks, bucket_counts)            # (|C_r|, N) in order_RAGFT order of the whole scene
@@ -385,13 +402,19 @@ class ShardedCodec:
         chans = [list(range(k, D, P)) for k in range(P)]
         qg = be.rlgr_decode(enc.streams)                          # (|C_r|, N)
         mark("rlgr_decode")
-        blocks = deinterleave_buckets(qg, enc.bucket_counts, n_rows)
+        Cr = len(chans[r])
+        flat = torch.empty(Cr * sum(n_rows), dtype=torch.int32, device=dev)
+        blocks, o = [], 0
+        for k in range(P):                                        # one send buffer, a view per destination
+            blocks.append(flat[o:o + Cr * n_rows[k]].reshape(Cr, n_rows[k]))
+            o += Cr * n_rows[k]
+        deinterleave_buckets(qg, enc.bucket_counts, n_rows, out=blocks)
         mark("deinterleave")
-        got = self._all_to_all([b.contiguous() for b in blocks], [len(chans[k]) * n for k in range(P)])
+        recv = self._exchange(flat, [Cr * n_rows[k] for k in range(P)], [len(chans[k]) * n for k in range(P)])
         mark("coeff_alltoall_dec")
+        by_src = torch.tensor([c for k in range(P) for c in chans[k]], dtype=torch.int64, device=dev)
         q = torch.empty(D, n, dtype=torch.int32, device=dev)
-        for k in range(P):
-            q[chans[k]] = got[k].reshape(len(chans[k]), n)
+        q[by_src] = recv.reshape(D, n)                            # (grouped by source rank k = channels k, k + P, ...)
         level = be.levels(enc.keys, 3 * J - B) if n else torch.empty(0, dtype=torch.uint8, device=dev)
         _, start, live = self._cell_meta(enc.keys, J, B)
         level_g = level.clone()
@@ -436,10 +459,10 @@ def interleave_buckets(blocks: List[torch.Tensor], bucket_counts: torch.Tensor) 
     return out
 
 
-def deinterleave_buckets(qg: torch.Tensor, bucket_counts: torch.Tensor, n_rows: List[int]) -> List[torch.Tensor]:
+def deinterleave_buckets(qg: torch.Tensor, bucket_counts: torch.Tensor, n_rows: List[int], out=None) -> List[torch.Tensor]:
     segs, _ = _segments(bucket_counts)
     C = qg.shape[0]
-    blocks = [torch.empty(C, n_rows[k], dtype=qg.dtype, device=qg.device) for k in range(len(n_rows))]
+    blocks = out if out is not None else [torch.empty(C, n_rows[k], dtype=qg.dtype, device=qg.device) for k in range(len(n_rows))]
     for k, ls, gs, c in segs:
         blocks[k][:, ls:ls + c] = qg[:, gs:gs + c]
     return blocks

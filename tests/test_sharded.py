@@ -21,7 +21,7 @@ from oracle import oracle_ctypes as orc
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 PKG = os.path.join(ROOT, "raht-3dgs-codec_b200")
-J, STEP, N_SCENE = 8, 0.05, 24000          # defaults of the CPU runs; the GPU run also takes a BASELINE-sized scene
+J, STEP, N_SCENE = 8, 0.05, 16000          # defaults of the CPU runs; the GPU run also takes a BASELINE-sized scene
 
 
 def _msb(x):
@@ -52,6 +52,9 @@ class OracleBackend:
         packed = np.concatenate([mm, mq, ms, mo[:, None], mc], 1).astype(np.float32)
         keys = r["MC_sorted"][r["voxel_indices"]].astype(np.int64)
         return torch.from_numpy(packed), torch.from_numpy(keys)
+
+    def histogram(self, values, shift, nbins):
+        return torch.from_numpy(np.bincount(np.minimum(values.numpy() >> shift, nbins - 1), minlength=nbins).astype(np.int64))
 
     def pack_by_owner(self, scene, owner, world):
         means, quats, scales, opac, colors = [a.numpy() for a in scene]
