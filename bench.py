@@ -41,6 +41,8 @@ WORKLOADS = {
     # one scene sharded over the ranks by Morton prefix (raht_b200/sharded.py); --num-gaussians overrides the 50 M
     "c4": (50_000_000, 18, 4001, "50M-Gaussian synthetic scene, depth 18, Morton-prefix sharding (BASELINE configs[3])"),
     "c5": (2_000_000, 14, 5001, "64 scenes x 2M Gaussians, depth 14, one scene stream per GPU (BASELINE configs[4])"),
+    # the encode_ply.py workload: a voxelised RGB point cloud, 11 quantisation steps per frame (run_c1)
+    "c1": (750_000, 10, 1001, "python/encode_ply.py RAHT+RLGR on a synthetic 10-bit voxelised point cloud (~750K voxels, RGB; BASELINE configs[0])"),
 }
 STEP = 1.0 / 64          # uniform quantisation step applied to all 59 channels (dense regime: ~300 bits per voxel)
 SPARSE_STEP = 0.25       # the coarse step of the `sparse` sub-record (most channels mostly zero: RLGR run mode, tables)
@@ -794,6 +796,107 @@ def run_sharded(args):
         dist.destroy_process_group()
 
 
+def reference_ply_frame(V, rgb, J, steps):
+    """The reference's point-cloud frame (python/encode_ply.py:104-214) on torch-CPU with its own Python operators and its
+    own coder object code (three channels, one host thread each)."""
+    import torch
+    from concurrent.futures import ThreadPoolExecutor
+    from oracle import oracle_ctypes as orc
+    from oracle import refpy
+    ref = refpy.load()
+    torch.set_num_threads(host_cores())
+    with torch.no_grad():
+        C = ref.utils.rgb_to_yuv(torch.from_numpy(rgb).to(torch.float64)).contiguous()
+        Vt = torch.from_numpy(V.astype(np.float64))
+        ListC, FlagsC, weightsC, order = ref.RAHT_param.RAHT_param_reorder_fast(Vt, torch.zeros(3, dtype=torch.float64), 2 ** J, J)
+        Coeff, _ = ref.RAHT.RAHT2_optimized(C, ListC, FlagsC, weightsC)
+        inv = torch.argsort(order)
+        total = 0
+        with ThreadPoolExecutor(max_workers=3) as pool:
+            for step in steps:
+                enc = torch.floor(Coeff / step + 0.5)
+                cols = np.ascontiguousarray(enc.index_select(0, order).to(torch.int32).numpy().T)
+                streams = list(pool.map(lambda c: orc.ref_rlgr_encode(cols[c].astype(np.int64), 1)[0], range(3)))
+                dec = list(pool.map(lambda c: orc.ref_rlgr_decode(streams[c], cols.shape[1], 1)[0], range(3)))
+                total += sum(len(b) for b in streams)
+                Cd = (torch.from_numpy(np.stack(dec, axis=1).astype(np.int32)).to(torch.float64) * step)[inv, :]
+                ref.iRAHT.inverse_RAHT_optimized(Cd, ListC, FlagsC, weightsC)
+    return total
+
+
+def run_c1(args):
+    """BASELINE configs[0]: one frame of python/encode_ply.py per step -- RGB -> YUV, RAHT_param + RAHT, then the reference's
+    11 quantisation steps, each with quantise / reorder / RLGR encode / RLGR decode / dequantise / iRAHT."""
+    import torch
+    from raht_b200 import codec, ops, synth
+    n_target, J, seed, desc = WORKLOADS["c1"]
+    dev = torch.device("cuda", int(os.environ.get("LOCAL_RANK", "0")))
+    torch.cuda.set_device(dev)
+    if int(os.environ.get("RANK", "0")) != 0:
+        return
+    V, rgb = synth.sphere_point_cloud(seed=seed)
+    Vd, rgbd = torch.from_numpy(V.astype(np.float64)).to(dev), torch.from_numpy(rgb).to(dev)
+    nvox = V.shape[0]
+    steps = codec.PLY_COLOR_STEPS
+    clocks = ClockSampler(dev.index)
+    clocks.start()
+
+    def measure(fused):
+        for _ in range(args.warmup):
+            res, _ = codec.encode_ply_frame(Vd, rgbd, J, fused=fused)
+        torch.cuda.synchronize()
+        launches0 = ops.lib.raht_launch_count()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        timers = []
+        e0.record()
+        for _ in range(args.steps):
+            tm = codec.StageTimer(True)
+            res, _ = codec.encode_ply_frame(Vd, rgbd, J, fused=fused, timer=tm)
+            timers.append(tm)
+        e1.record()
+        torch.cuda.synchronize()
+        stages = {}
+        for tm in timers:
+            for k, v in tm.result().items():
+                stages[k] = stages.get(k, 0.0) + v / len(timers)
+        return e0.elapsed_time(e1) / args.steps, stages, (ops.lib.raht_launch_count() - launches0) // args.steps, res
+
+    clocks.mark_begin()
+    ms, stages, launches, res = measure(False)
+    ms_fused, stages_fused, _, res_fused = measure(True)
+    clocks.mark_end()
+    clk = clocks.stop()
+    cpu = None
+    if not args.no_cpu_baseline:
+        from oracle import refpy
+        if refpy.available():
+            t0 = time.perf_counter()
+            total = reference_ply_frame(V, rgb, J, steps)
+            secs = time.perf_counter() - t0
+            cpu = {"value": round(nvox * len(steps) / secs, 1), "unit": "voxel-steps/s", "cores": host_cores(), "kind": "reference",
+                   "sample": f"the whole frame once ({secs:.1f} s): the reference's Python operators on torch-CPU + its RLGR object code",
+                   "bytes_equal_to_gpu": bool(total == sum(r["bytes"] for r in res))}
+    peak, peak_src = load_peaks()
+    raht_bytes = nvox * (2 * 3 * 8 + 13)
+    line = {
+        "metric": "voxel-steps/s RAHT+RLGR encode+decode of an RGB point cloud (3 ch, 11 quantisation steps per frame)",
+        "value": round(nvox * len(steps) / (ms / 1e3), 1), "unit": "voxel-steps/s", "n_gpus": 1, "steps": args.steps, "warmup": args.warmup,
+        "ms_per_step": round(ms, 4), "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+        "config": {"workload": desc, "nvox": nvox, "depth": J, "channels": 3, "quant_steps": steps,
+                   "rates_bpp": [round(r["bpp"], 4) for r in res], "psnr_y": [round(r["psnr_y"], 3) for r in res]},
+        "clocks": clk, "gpu_launches": int(launches),
+        "stages": {k: round(v, 4) for k, v in stages.items()},
+        "fused_transform_quantisation": {"ms_per_step": round(ms_fused, 4), "stages": {k: round(v, 4) for k, v in stages_fused.items()},
+                                         "bytes_equal": [a["bytes"] for a in res] == [b["bytes"] for b in res_fused],
+                                         "verdict": "fused pays" if ms_fused < ms else "two passes are faster"},
+        "roofline": {"bound": "hbm", "kernel": "raht", "achieved": round(raht_bytes / (stages.get("raht", 1e9) / 1e3) / 1e9, 2), "peak": peak,
+                     "unit": "GB/s", "frac": round(raht_bytes / (stages.get("raht", 1e9) / 1e3) / 1e9 / peak, 4), "traffic": None,
+                     "peak_source": peak_src},
+        "cpu_baseline": cpu,
+    }
+    print(json.dumps(line))
+
+
 def run_reference(args):
     """--impl reference: the reference's own CPU path on the box's host cores, on the WHOLE configured scene
     (same_config: the scene, depth, channels and step of the b200 arm), every step one full encode + decode."""
@@ -803,6 +906,25 @@ def run_reference(args):
     from oracle import oracle_ctypes as orc
     from oracle import refpy
     from raht_b200 import synth
+    if args.workload == "c1":
+        from raht_b200.codec import PLY_COLOR_STEPS
+        _, J, seed, desc = WORKLOADS["c1"]
+        V, rgb = synth.sphere_point_cloud(seed=seed)
+        for _ in range(args.warmup):
+            reference_ply_frame(V, rgb, J, PLY_COLOR_STEPS)
+        t0 = time.perf_counter()
+        for _ in range(args.steps):
+            reference_ply_frame(V, rgb, J, PLY_COLOR_STEPS)
+        secs = (time.perf_counter() - t0) / max(args.steps, 1)
+        v = V.shape[0] * len(PLY_COLOR_STEPS) / secs
+        print(json.dumps({"impl": "reference", "metric": "voxel-steps/s RAHT+RLGR encode+decode of an RGB point cloud (3 ch, 11 quantisation steps per frame)",
+                          "value": round(v, 1), "unit": "voxel-steps/s", "n_gpus": 1, "steps": args.steps, "warmup": args.warmup,
+                          "ms_per_step": round(secs * 1e3, 2), "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64",
+                          "data": "synthetic", "config": {"workload": desc, "nvox": int(V.shape[0]), "depth": J, "channels": 3, "same_config": True},
+                          "cpu_baseline": {"value": round(v, 1), "unit": "voxel-steps/s", "cores": host_cores(), "kind": "reference",
+                                           "sample": "the whole frame per step: the reference's Python operators on torch-CPU + its RLGR object code"},
+                          "e2e": {"value": round(v, 1), "unit": "voxel-steps/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}))
+        return
     n, J, seed, desc = WORKLOADS[args.workload if args.workload in ("c2", "c3", "tiny") else "c2"]
     if args.n:
         n = args.n
@@ -880,6 +1002,8 @@ def main():
         run_reference(args)
     elif args.workload == "c4":
         run_sharded(args)
+    elif args.workload == "c1":
+        run_c1(args)
     else:
         run_gpu(args)
 

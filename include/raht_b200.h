@@ -29,7 +29,7 @@
 extern "C" {
 #endif
 
-#define RAHT_B200_ABI_VERSION 13
+#define RAHT_B200_ABI_VERSION 14
 
 enum {
     RAHT_OK = 0,
@@ -342,6 +342,11 @@ int raht_streams_pack(const uint8_t *streams, int64_t slot_bytes, const int64_t 
                       void *stream);
 int raht_streams_unpack(const uint8_t *packed, const int64_t *offsets, int nch, uint8_t *streams,
                         int64_t slot_bytes, void *stream);
+
+/* (g) Point-cloud path of python/encode_ply.py: utils.rgb_to_yuv (python/utils.py:4-33), BT.709 full range,
+ * rgb (n, 3) fp32 or fp64 in [0, 255] -> yuv (n, 3) fp64 in [0, 255], clipped.  Floating-point row: within 1e-10 of
+ * the reference's matmul (whose summation order is the BLAS's).                                              */
+int raht_rgb_to_yuv(const void *rgb, int dtype, int64_t n, double *yuv, void *stream);
 
 /* ------------------------------------------------------------------------------------------------
  * Scene-level calls: one leg of the pipeline per host call.  Same kernels, same order and same

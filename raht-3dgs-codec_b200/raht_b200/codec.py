@@ -488,6 +488,61 @@ def decode_scene(enc: EncodedScene, reuse_tree=False, tile_rows=None, timer=None
     return coords, Crec
 
 
+PLY_COLOR_STEPS = [1, 2, 4, 6, 8, 12, 16, 20, 24, 32, 64]        # encode_ply.py:29
+
+
+@torch.no_grad()
+def encode_ply_frame(V, Crgb, J, steps=None, fused=False, timer=None, keep_reconstruction=False):
+    """One frame of the reference's point-cloud driver (python/encode_ply.py:104-214; BASELINE configs[0]):
+    colours -> YUV (utils.rgb_to_yuv), RAHT_param + RAHT once, then for every quantisation step of the list
+    (encode_ply.py:29) quantise, PSNR of the luma coefficients (:151-152), reorder, RLGR of the three channels, and the
+    decoder: RLGR^-1, dequantise, inverse reorder, iRAHT.  V: (N, 3) Morton-sorted unique voxel coordinates (what
+    read_ply_file returns for a voxelised cloud), Crgb: (N, 3) in [0, 255].
+    fused: transform + quantisation in one pass per step (ops.forward_quant) instead of one transform and a quantisation
+    per step.  Returns (per-step list of {step, bytes, bpp, psnr_y[, C_rec]}, Cyuv)."""
+    import math
+    import utils as shim_utils
+    timer = timer or StageTimer(False)
+    steps = PLY_COLOR_STEPS if steps is None else steps
+    dev = V.device
+    timer.mark("start")
+    C = shim_utils.rgb_to_yuv(Crgb)                                             # encode_ply.py:108
+    timer.mark("rgb_to_yuv")
+    status = ops._status_word(dev)
+    keys, status = ops.morton_keys_f64(V, (0.0, 0.0, 0.0), float(2 ** J), J)    # :113-115 origin 0, width 2^J
+    tree = _build_tree(keys, status, None, True)
+    order, _ = tree.order(want_position=True)
+    timer.mark("raht_param")
+    N = C.shape[0]
+    T = None if fused else ops.forward(tree, C, torch.float64)                  # :121
+    timer.mark("raht")
+    out = []
+    for step in steps:
+        q = ops.forward_quant(tree, C, step, torch.float64, status=status) if fused else ops.quant_reorder(T, order, step, status=status)
+        timer.mark("quant_reorder")
+        streams = ops.rlgr_encode(q, 1, status=status)                          # :158-176 (reads the status word: the step's one sync)
+        timer.mark("rlgr_encode")
+        qd = ops.rlgr_decode(streams, 1)                                        # :179-189
+        timer.mark("rlgr_decode")
+        Td = ops.dequant_unreorder(qd, order, step, torch.float64)              # :199-206
+        timer.mark("dequant_unreorder")
+        rec = {"step": step, "bytes": streams.total_bytes(), "bpp": streams.total_bytes() * 8.0 / max(N, 1)}
+        # :149-152  MSE of the quantised luma COEFFICIENTS over 255^2 (orthonormal transform: equals the luma MSE)
+        y = Td[:, 0] if fused else None
+        ref_y = T[:, 0] if T is not None else None
+        if ref_y is not None:
+            mse = float(L.read_host(ops.sse(ref_y.reshape(-1, 1).contiguous(), Td[:, :1].contiguous()))[0][0]) / (N * 255.0 ** 2)
+            rec["psnr_y"] = -10.0 * math.log10(mse) if mse > 0 else float("inf")
+        Crec = ops.inverse(tree, Td)                                            # :207
+        timer.mark("iraht")
+        if keep_reconstruction:
+            rec["C_rec"] = Crec
+            rec["streams"] = streams
+        del y
+        out.append(rec)
+    return out, C
+
+
 def psnr(Cref: torch.Tensor, Crec: torch.Tensor, c0=0, c1=None) -> float:
     """-10 log10(mean((C - C_rec)^2) + 1e-10)   (encode_3dgs.py:298-299)."""
     import math

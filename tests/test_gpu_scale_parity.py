@@ -91,3 +91,42 @@ def test_reference_format_streams_without_index_decode_at_scale():
     assert streams.sync_index is None
     assert streams.to_bytes() == cpu_streams(x)
     assert np.array_equal(ops.rlgr_decode(streams, 1, use_index=False).cpu().numpy(), x)
+
+
+def test_c1_point_cloud_frame_is_bit_exact_with_the_oracle():
+    """BASELINE configs[0] -- the encode_ply.py workload at its size: ~750 K voxels on a sphere surface at depth 10, RGB ->
+    YUV, RAHT, the reference's 11 quantisation steps (encode_ply.py:29), RLGR of Y / U / V and back.  The colour transform
+    is a floating-point row (1e-10); from the SAME YUV input on, symbols, bytes and reconstructions are bit-exact, for
+    the two-pass path and for the fused transform + quantisation."""
+    from raht_b200 import codec, synth, ops
+    import utils as shim_utils
+    V, rgb = synth.sphere_point_cloud()
+    assert 600_000 < V.shape[0] < 900_000
+    J = 10
+    Vd, rgbd = torch.from_numpy(V.astype(np.float64)).to(DEV), torch.from_numpy(rgb).to(DEV)
+    yuv = shim_utils.rgb_to_yuv(rgbd)
+    np.testing.assert_allclose(yuv.cpu().numpy(), orc.rgb_to_yuv(rgb), rtol=0, atol=1e-10)
+    res, C = codec.encode_ply_frame(Vd, rgbd, J, keep_reconstruction=True)
+    assert torch.equal(C, yuv)
+    Cn = C.cpu().numpy()
+    keys = orc.morton(V, J)
+    t = orc.Tree(keys, J)
+    T_o, _ = t.forward(Cn)
+    order_o = t.order()
+    inv_o = np.argsort(order_o, kind="stable")
+    assert [r["step"] for r in res] == codec.PLY_COLOR_STEPS
+    for r in res:
+        step = r["step"]
+        q_o = np.ascontiguousarray(orc.quantize(T_o, step)[order_o].T.astype(np.int32))
+        exp = cpu_streams(q_o)
+        assert r["streams"].to_bytes() == exp, f"step {step}: RLGR bytes"
+        assert r["bytes"] == sum(len(b) for b in exp)
+        Tdec = orc.dequantize(q_o.T.astype(np.float64), step)[inv_o]
+        assert np.array_equal(r["C_rec"].cpu().numpy(), t.inverse(Tdec)), f"step {step}: reconstruction"
+        y_hat = np.floor(T_o[:, 0] / step + 0.5) * step                                     # encode_ply.py:149-152
+        psnr = -10 * np.log10(np.linalg.norm(T_o[:, 0] - y_hat) ** 2 / (len(keys) * 255.0 ** 2))
+        assert abs(r["psnr_y"] - psnr) <= 1e-9 * abs(psnr)
+    res_f, _ = codec.encode_ply_frame(Vd, rgbd, J, steps=[1, 12, 64], fused=True, keep_reconstruction=True)
+    for rf in res_f:
+        r = next(x for x in res if x["step"] == rf["step"])
+        assert rf["streams"].to_bytes() == r["streams"].to_bytes() and torch.equal(rf["C_rec"], r["C_rec"])
