@@ -273,8 +273,8 @@ int raht_dequantize_f64(const double *q, int64_t count, double step, double *T, 
  * nbytes[c]: closed stream length (exact even when the stream did not fit: RAHT_ST_STREAM_OVERFLOW).
  *
  * sync_index (optional, device, nch * raht_rlgr_sync_entries(n) entries of 8 bytes): side
- * information the encoder can emit next to the reference bitstream -- for every range of 512
- * symbols [512 r, 512 r + 512), raht_rlgr_sync_entries(n) = ceil(n / 512) per channel, the bit offset
+ * information the encoder can emit next to the reference bitstream -- for every range of 256
+ * symbols [256 r, 256 r + 256), raht_rlgr_sync_entries(n) = ceil(n / 256) per channel, the bit offset
  * and coder state (k_P, k_RP) before the range's first event and the position of that event's
  * non-zero symbol inside the range:
  *   word 0 = bit offset (low 32), word 1 = offset bits 32..38 | k_P << 7 | k_RP << 14 | first << 22

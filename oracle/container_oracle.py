@@ -19,7 +19,8 @@ from . import oracle_ctypes as orc
 MAGIC, VERSION, N_GEO, DIGIT_BITS = b"R3GC", 1, 3, 21
 FLAG_INDEX, FLAG_F32 = 1, 2
 FIXED = "<4sHHIIIIIQQ4fdd"
-SYNC_SHIFT = 9
+SYNC_SHIFT = 8
+SYNC_RANGE = 1 << SYNC_SHIFT
 
 
 def pad8(x):
@@ -52,12 +53,12 @@ def _gr_len(u, kr):                       # membuf.cpp:242-256 (grWrite): p ones
 
 
 def rlgr_sync_index(seq, flag_signed=1):
-    """(ceil(n / 512), 2) uint32: for every range of 512 symbols the position of the coder (bit offset, k_P, k_RP) before
+    """(ceil(n / 256), 2) uint32: for every range of 256 symbols the position of the coder (bit offset, k_P, k_RP) before
     the event -- zeros, then one non-zero -- whose non-zero is the first of the range, and that symbol's place in the range
     (include/raht_b200.h, sync_index).  Ranges without a non-zero keep 0xffffffff in both words.  Walks the coder of
     membuf.cpp:351-414 symbol by symbol, counting bits only."""
     n = len(seq)
-    idx = np.full(((n + 511) >> SYNC_SHIFT, 2), 0xffffffff, dtype=np.uint32)
+    idx = np.full(((n + SYNC_RANGE - 1) >> SYNC_SHIFT, 2), 0xffffffff, dtype=np.uint32)
     kP, kRP, m, bits = 0, 8, 0, 0
     ev = (0, 0, 8)
     last = -1
@@ -90,7 +91,7 @@ def rlgr_sync_index(seq, flag_signed=1):
             if r != last:
                 b, a, c = ev
                 idx[r, 0] = b & 0xffffffff
-                idx[r, 1] = ((b >> 32) & 0x7f) | ((a & 0x7f) << 7) | ((c & 0xff) << 14) | ((i & 511) << 22)
+                idx[r, 1] = ((b >> 32) & 0x7f) | ((a & 0x7f) << 7) | ((c & 0xff) << 14) | ((i & (SYNC_RANGE - 1)) << 22)
                 last = r
             ev = (bits, kP, kRP)
     return idx
@@ -111,7 +112,7 @@ def pack_scene(J, n_in, steps, vmin, voxel_size, width, keys, q, with_index=True
     D, nvox = q.shape
     sym = geometry_symbols(keys)
     geo, attr = _encode_channels(sym, 0), _encode_channels(q, 1)
-    entries = ((nvox + 511) >> SYNC_SHIFT) if with_index else 0
+    entries = ((nvox + SYNC_RANGE - 1) >> SYNC_SHIFT) if with_index else 0
     steps = [float(s) for s in (steps if isinstance(steps, (list, tuple, np.ndarray)) else [steps])]
     var = struct.pack(f"<{len(steps)}d", *steps) + struct.pack(f"<{N_GEO}Q", *[len(s) for s in geo]) + \
         struct.pack(f"<{D}Q", *[len(s) for s in attr]) + struct.pack("<QQ", entries, entries)

@@ -19,7 +19,7 @@
 //                        the matching candidate (or the chunk is re-solved exactly), giving each chunk
 //                        its start state and bit offset and the channel its byte length;
 //   C   emit             every lane re-codes its block from its now-known state at its now-known bit
-//                        offset, and writes the sync index (one entry per 512 symbols) on the way.
+//                        offset, and writes the sync index (one entry per 256 symbols) on the way.
 // All of it is exact: speculation only decides how much is recomputed.  Work, warm-up length and the
 // number of chunks are proportional to the number of EVENTS, so zero runs cost nothing and sparse
 // channels (which never re-synchronise) have few chunks to repair.  The decoder is range-parallel
@@ -1200,7 +1200,7 @@ __global__ void __launch_bounds__(32 * SPEC_WARPS) rlgr_emit_kernel(Geometry G, 
     sink.init(streams + (size_t)ch * slot_bytes, slot_bytes, begin);
     uint2 *sync = sync_index ? sync_index + (size_t)ch * sync_entries : nullptr;
     bool quirk = false;
-    // first event of its 512-symbol range: where (bit offset, state) the coder stands before it
+    // first event of its 256-symbol range: where (bit offset, state) the coder stands before it
     auto sync_entry = [&](int64_t np) {
         const unsigned long long at = sink.bit_pos();
         const uint32_t hi = (uint32_t)((at >> 32) & 0x7f) | ((uint32_t)(s.kP & 0x7f) << 7) |
@@ -1208,7 +1208,7 @@ __global__ void __launch_bounds__(32 * SPEC_WARPS) rlgr_emit_kernel(Geometry G, 
         sync[np >> SYNC_SHIFT] = make_uint2((uint32_t)at, hi);
     };
     if (B.sym) {                                           // dense channel: symbol by symbol, straight from q
-        // sync index: the block's first event is the first of its 512-symbol range iff the zeros pending in front of the
+        // sync index: the block's first event is the first of its 256-symbol range iff the zeros pending in front of the
         // block reach back to the start of the range (ranges start at block boundaries); the coder stands before that
         // event in the block's start state at the block's first bit
         bool want_sync = sync && B.cnt > 0 && B.gap0 >= (uint32_t)(B.pos0 & (SYNC_RANGE - 1));
@@ -1272,7 +1272,7 @@ __global__ void __launch_bounds__(32) rlgr_decode_serial_kernel(const uint8_t *_
     decode_range(br, initial_state(), -1, G.n, G.flag_signed, q + (size_t)ch * G.ld);
 }
 
-// with the encoder's sync index: one thread per entry (512 symbols)
+// with the encoder's sync index: one thread per entry (256 symbols)
 constexpr int DEC_THREADS = 128;
 // (Tried and dropped: feeding the window from a per-thread cp.async ring in shared memory instead of a register loaded
 // one refill ahead.  It removes the long-scoreboard stalls -- a register loaded from global memory is a warp-wide
@@ -1323,7 +1323,7 @@ __device__ __forceinline__ void decode_step(BitReader &br, State &s, bool &synce
     }
 }
 
-// One thread per sync entry (512 symbols), but the symbols do not leave the thread one by one: 59 M four-byte stores,
+// One thread per sync entry (256 symbols), but the symbols do not leave the thread one by one: 59 M four-byte stores,
 // every lane of a warp to a different cache line, were what bound the kernel (53 M sectors through the L1 tag stage for
 // 236 MB of output; doubling the threads did not make it faster).  The range is decoded in windows of 32 symbols into
 // a row of shared memory per lane; after each window the warp writes its 32 rows out as 32 full lines -- zeros

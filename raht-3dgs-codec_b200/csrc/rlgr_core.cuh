@@ -31,7 +31,7 @@ constexpr int CHUNK_EVENTS = EV_BLOCK * CHUNK_LANES;
 constexpr int CHUNK_SLOTS = 32 * EV_BLOCK;         // event slots of a chunk in the store (32 lanes)
 constexpr int NCAND = 8;                           // speculated start states of a block carried side by side
 constexpr int SYM_BLOCK = 128;                     // symbols per block of the compaction passes
-constexpr int SYNC_SHIFT = 9;                      // one sync entry per 2^9 = 512 symbols
+constexpr int SYNC_SHIFT = 8;                      // one sync entry per 2^8 = 256 symbols
 constexpr int SYNC_RANGE = 1 << SYNC_SHIFT;
 constexpr uint32_t SYNC_NONE = 1023;               // no non-zero symbol in the entry's range
 

@@ -429,7 +429,7 @@ class RlgrStreams:
     """nch closed RLGR streams in one device buffer (slot per channel).
 
     sync_index (optional): the encoder's side information for parallel decoding -- 8 bytes per range
-    of 512 symbols (bit offset, coder state, position of the first non-zero); the streams themselves
+    of 256 symbols (bit offset, coder state, position of the first non-zero); the streams themselves
     are the reference bitstreams and do not depend on it."""
 
     def __init__(self, buf, slot_bytes, nbytes, n, nch, sync_index=None):

@@ -276,7 +276,7 @@ extern "C" {
 // One channel.  out must be zero-filled by the caller (cap bytes).  stats[0] chunk solves in the speculation
 // pass, [1] fixed-point rounds, [2] repairs in the resolve pass, [3] chunks, [4] events, [5] rounds spent in
 // repairs, [6] chunks solved again in the second sweep, [7] repairs where the true state was a candidate whose chain was incomplete.
-// sync (optional): 2 x uint32 per 512 symbols, pre-filled with 0xff by the caller.
+// sync (optional): 2 x uint32 per 256 symbols, pre-filled with 0xff by the caller.
 // mode: 0 = the kernel's rule (one canonical state when >= 50 % non-zero), 1 = always two, 2 = always one.
 // c1_kP: k_P of the second canonical start state.  max_spec_rounds: round cap of the speculation pass (0: the kernel's).
 __attribute__((visibility("default"))) int64_t emu_rlgr_encode(const int32_t *q, int64_t n, int flag_signed, uint8_t *out,
@@ -383,7 +383,7 @@ __attribute__((visibility("default"))) int64_t emu_rlgr_encode(const int32_t *q,
                 const Event e = L[l].at(i);
                 if (i == 0) pos = (int64_t)C.blockpos[w * CHUNK_LANES - 1 + l] - (int64_t)e.gap - 1;
                 const int64_t np = pos + (int64_t)e.gap + 1;
-                if (sync && (np >> SYNC_SHIFT) != (pos >> SYNC_SHIFT)) {     // first event of its 512-symbol range
+                if (sync && (np >> SYNC_SHIFT) != (pos >> SYNC_SHIFT)) {     // first event of its 256-symbol range
                     const uint64_t at = sink.pos;
                     sync[2 * (np >> SYNC_SHIFT) + 0] = (uint32_t)at;
                     sync[2 * (np >> SYNC_SHIFT) + 1] = (uint32_t)((at >> 32) & 0x7f) | ((uint32_t)(st.kP & 0x7f) << 7) |
@@ -465,7 +465,7 @@ __attribute__((visibility("default"))) int64_t emu_rlgr_encode_dense(const int32
         const uint64_t begin = sink.pos;
         SymState e{s.kP, s.kRP, 0};
         bool q2 = false;
-        // sync index: a block's first event is the first of its 512-symbol range iff the zeros pending in front of the
+        // sync index: a block's first event is the first of its 256-symbol range iff the zeros pending in front of the
         // block reach back to the start of the range (ranges start at block boundaries); the coder stands before that
         // event in the block's start state at the block's first bit
         bool want_sync = sync && cnt > 0 && gap0 >= (uint32_t)(pos0 & (SYNC_RANGE - 1));

@@ -44,11 +44,12 @@ def test_sync_index_walk_on_known_streams():
     # all zeros: no entry; a lone non-zero: the event starts at the stream start with the initial state (k_P 0, k_RP 8)
     assert np.all(cor.rlgr_sync_index(np.zeros(1000, np.int64)) == 0xffffffff)
     idx = cor.rlgr_sync_index(np.array([0, 0, 0, 5] + [0] * 600 + [1], np.int64))
-    assert idx.shape == (2, 2)
+    assert idx.shape == (3, 2)                                        # ranges of 256 symbols
     assert idx[0, 0] == 0 and idx[0, 1] == (0 << 7 | 8 << 14 | 3 << 22)
-    # second range: its first non-zero is symbol 604 (place 92); the event starts right after the code of the 5
+    assert np.all(idx[1] == 0xffffffff)                               # nothing but zeros in [256, 512)
+    # third range: its first non-zero is symbol 604 (place 92); the event starts right after the code of the 5
     bits_first = len(orc.rlgr_encode(np.array([0, 0, 0, 5], np.int64))) * 8
-    assert idx[1, 1] >> 22 == 604 - 512 and 0 < idx[1, 0] <= bits_first
+    assert idx[2, 1] >> 22 == 604 - 512 and 0 < idx[2, 0] <= bits_first
 
 
 def test_container_restatement_roundtrip():
@@ -60,7 +61,7 @@ def test_container_restatement_roundtrip():
         assert h["J"] == 7 and h["n_in"] == 4321 and h["nvox"] == len(keys) and h["steps"] == [0.25]
         assert h["vmin"] == (-1.0, 0.5, 2.0) and h["voxel_size"] == 0.015625 and h["width"] == 2.0
         assert np.array_equal(h["keys"], keys) and np.array_equal(h["q"], q)
-        n_index = (3 + 4) * ((len(keys) + 511) // 512) * 8 if with_index else 0
+        n_index = (3 + 4) * ((len(keys) + 255) // 256) * 8 if with_index else 0
         assert h["body_end"] + n_index == len(data)
     # per-channel steps
     data = cor.pack_scene(7, 10, [1.0, 2.0, 4.0, 8.0], (0, 0, 0), 1.0, 128.0, keys, q, False)

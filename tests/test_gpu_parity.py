@@ -314,7 +314,7 @@ def test_rlgr_random_vs_oracle(zfrac, scale, n):
     assert streams.to_bytes() == exp
     assert np.array_equal(ops.rlgr_decode(streams, 1).cpu().numpy(), x)                       # chunk-parallel, sync index
     assert np.array_equal(ops.rlgr_decode(streams, 1, use_index=False).cpu().numpy(), x)      # channel-serial
-    assert streams.stats["chunks"] == nch * ((n + 511) // 512)                                 # one sync entry per 512 symbols
+    assert streams.stats["chunks"] == nch * ((n + 255) // 256)                                 # one sync entry per 256 symbols
     no_index = ops.rlgr_encode(cu(x), 1, with_index=False)
     assert no_index.sync_index is None and no_index.to_bytes() == exp
 

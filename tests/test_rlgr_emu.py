@@ -28,7 +28,7 @@ def emu():
         cap = q.size * 12 + 64
         out = np.zeros(cap, dtype=np.uint8)
         stats = np.zeros(8, dtype=np.uint64)
-        entries = (q.size + 511) // 512
+        entries = (q.size + 255) // 256
         sync = np.full((max(entries, 1), 2), 0xffffffff, dtype=np.uint32)       # "no event in this range"
         nb = lib.emu_rlgr_encode(q.ctypes.data, q.size, flag_signed, out.ctypes.data, cap, stats.ctypes.data, sync.ctypes.data,
                                  mode, c1_kp, spec_rounds)
@@ -133,7 +133,7 @@ def emu_dense():
         cap = q.size * 12 + 64
         out = np.zeros(cap, dtype=np.uint8)
         stats = np.zeros(8, dtype=np.uint64)
-        entries = (q.size + 511) // 512
+        entries = (q.size + 255) // 256
         sync = np.full((max(entries, 1), 2), 0xffffffff, dtype=np.uint32)
         nb = lib.emu_rlgr_encode_dense(q.ctypes.data, q.size, flag_signed, out.ctypes.data, cap, sync.ctypes.data, warm, stats.ctypes.data)
         assert nb >= 0, nb
