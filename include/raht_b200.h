@@ -29,7 +29,7 @@
 extern "C" {
 #endif
 
-#define RAHT_B200_ABI_VERSION 14
+#define RAHT_B200_ABI_VERSION 15
 
 enum {
     RAHT_OK = 0,
@@ -347,6 +347,18 @@ int raht_streams_unpack(const uint8_t *packed, const int64_t *offsets, int nch, 
  * rgb (n, 3) fp32 or fp64 in [0, 255] -> yuv (n, 3) fp64 in [0, 255], clipped.  Floating-point row: within 1e-10 of
  * the reference's matmul (whose summation order is the BLAS's).                                              */
 int raht_rgb_to_yuv(const void *rgb, int dtype, int64_t n, double *yuv, void *stream);
+
+/* (f1) Scene I/O: the vertex records of the reference's 3DGS PLY files built / split on the device.
+ * Replaces the per-vertex Python write loop of python/quality_eval.py:18-117 (save_ply) and the numpy
+ * structured-dtype parse of python/data_util.py:272-382 (read_compressed_3dgs_ply).  A record is 14 + color_dim
+ * little-endian fp32: x y z | nx ny nz (zeros) | colours | opacity | scale_0..2 | rot_0..3.
+ * unpack: v_int (n, 3) int64 = positions truncated (optional), means (n, 3) fp32 (optional), attributes
+ * (n, 8 + color_dim) fp32 = [rot 4 | scale 3 | opacity | colours] -- the reader's column order.              */
+int raht_ply_pack_vertices(const float *means, const float *quats, const float *scales,
+                           const float *opacities, const float *colors, int color_dim, int64_t n,
+                           float *records, void *stream);
+int raht_ply_unpack_vertices(const float *records, int color_dim, int64_t n, int64_t *v_int,
+                             float *means, float *attributes, void *stream);
 
 /* ------------------------------------------------------------------------------------------------
  * Scene-level calls: one leg of the pipeline per host call.  Same kernels, same order and same

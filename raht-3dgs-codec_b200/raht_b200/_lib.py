@@ -81,6 +81,8 @@ SIGNATURES = {
     "raht_streams_pack": (_i, [_p, _i64, _p, _i, _p, _i64, _p, _p, _p]),
     "raht_streams_unpack": (_i, [_p, _p, _i, _p, _i64, _p]),
     "raht_shard_top_cells": (_i, [_p, _p, _p, _i, _p, _i, _i, _i, _p, _p, _p]),
+    "raht_ply_pack_vertices": (_i, [_p, _p, _p, _p, _p, _i, _i64, _p, _p]),
+    "raht_ply_unpack_vertices": (_i, [_p, _i, _i64, _p, _p, _p, _p]),
     "raht_rgb_to_yuv": (_i, [_p, _i, _i64, _p, _p]),
     "raht_histogram_i64": (_i, [_p, _i64, _i, _i, _p, _p]),
     "raht_pack_rows": (_i, [_p, _i64, _p, _p, _p, _p, _p, _i, _p, _p]),
