@@ -305,6 +305,8 @@ STAGE_KERNELS = {
     "rlgr_encode": [("rlgr_count_kernel", 1), ("rlgr_scan_kernel", 1), ("rlgr_scatter_kernel", 1), ("rlgr_speculate_kernel", 2),
                     ("rlgr_table_kernel", 1), ("rlgr_chunk_table_kernel", 1), ("rlgr_resolve_kernel", 1), ("rlgr_table_lanes_kernel", 1),
                     ("rlgr_zero_kernel", 1), ("rlgr_emit_kernel", 1)],
+    "raht_param": [("levels_kernel", 1), ("order_count_kernel", 1), ("scan_counts_kernel", 1), ("order_scatter_kernel", 1),
+                   ("plan_init_kernel", 1), ("plan_kernel", 1)],
     "rlgr_decode": [("rlgr_decode_indexed_kernel", 1)],
     "merge": [("merge_kernel<float, 2, 0>", 1)],
     "raht": [("transform_stage0_kernel<float, double, 59, 1, 0>", 1), ("transform_upper_kernel<double, 1>", 5)],
@@ -875,7 +877,10 @@ def run_c1(args):
             secs = time.perf_counter() - t0
             cpu = {"value": round(nvox * len(steps) / secs, 1), "unit": "voxel-steps/s", "cores": host_cores(), "kind": "reference",
                    "sample": f"the whole frame once ({secs:.1f} s): the reference's Python operators on torch-CPU + its RLGR object code",
-                   "bytes_equal_to_gpu": bool(total == sum(r["bytes"] for r in res))}
+                   "payload_bytes_reference_cpu": int(total), "payload_bytes_gpu": int(sum(r["bytes"] for r in res)),
+                   "note": "the unmodified reference on torch-CPU differs from the bit-exact convention in the last bits of T (torch-CPU's "
+                           "vectorised sqrt is not correctly rounded, its matmul order is the BLAS's): the payloads agree to a few bytes, the "
+                           "bit-exact comparison is tests/test_gpu_scale_parity.py::test_c1_point_cloud_frame_is_bit_exact_with_the_oracle"}
     peak, peak_src = load_peaks()
     raht_bytes = nvox * (2 * 3 * 8 + 13)
     line = {

@@ -229,10 +229,12 @@ def encode_attributes(keys, Cmat, step, transform_dtype=torch.float64, tile_rows
                       tree_job=None):
     """RAHT_param -> RAHT -> quantise -> reorder -> RLGR for rows that are Morton-sorted unique voxels.
     fused: transform and quantisation in one pass (ops.forward_quant; same symbols, bit for bit), else the two
-    reference steps one after the other.  Off by default: on sparse scenes (the 1 M bench scene: consecutive voxels fall
-    into different level buckets of order_RAGFT) the fused pass scatters 4-byte symbols from the transform tiles and
-    is no faster than the two passes, whose reorder kernel moves whole rows (measured: forward -0.04 ms, inverse
-    +0.05 ms per step); it pays on dense clouds, where a tile's rows stay together in the coded order.
+    reference steps one after the other.  Off by default -- measured, it does not pay on either kind of scene: on the
+    sparse 3DGS scenes (1 M bench scene: consecutive voxels fall into different level buckets of order_RAGFT) the fused pass
+    scatters 4-byte symbols from the transform tiles where the reorder kernel moves whole rows (forward -0.04 ms, inverse
+    +0.05 ms per step), and on the dense point cloud of encode_ply.py (777 K voxels, 11 quantisation steps per frame,
+    bench.py --workload c1) the two-pass path transforms ONCE and quantises eleven times, while the fused one repeats the
+    transform per step: 10.14 ms against 10.40 ms per frame.
     Device-side validation (sorted/unique keys, int32 overflow, sort stall) accumulates in one status
     word that is read once, after the entropy coder."""
     timer = timer or StageTimer(False)

@@ -5,7 +5,7 @@ cd "$(dirname "$0")/.."
 mkdir -p gpurun_out
 RE="${1:-.*}"
 CNT="${2:-170}"
-timeout 1500 ncu --set full --clock-control none ${NCU_SOURCE:+--import-source on} -k "regex:$RE" -c "$CNT" -f -o gpurun_out/full \
+timeout 2400 ncu --set full --clock-control none ${NCU_SOURCE:+--import-source on} -k "regex:$RE" -c "$CNT" -f -o gpurun_out/full \
     python scripts/step_once.py > gpurun_out/ncu_full.log 2>&1
 echo "ncu exit $?"
 ncu -i gpurun_out/full.ncu-rep --page raw --csv > gpurun_out/full_raw.csv 2> gpurun_out/full_raw.err

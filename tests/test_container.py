@@ -157,3 +157,20 @@ def test_container_rejects_damage_cuda():
         container.unpack(data[:len(data) // 2])
     with pytest.raises(ValueError):
         container.unpack(data[:40])
+    # a header that lies about its sizes (advisor, round 1): every field the kernels index with is checked against the buffer
+    import struct
+    def patched(off, fmt, value):
+        b = bytearray(data)
+        struct.pack_into(fmt, b, off, value)
+        return bytes(b)
+    hb = struct.unpack_from("<I", data, 8)[0]
+    n_steps = struct.unpack_from("<I", data, 24)[0]
+    var = 76 + 8 * n_steps                       # geo_bytes[3], attr_bytes[D], geo_entries, attr_entries follow the steps
+    D = struct.unpack_from("<I", data, 16)[0]
+    for bad in (patched(12, "<I", 40),                                   # J out of range
+                patched(36, "<Q", 1 << 50),                              # nvox absurd
+                patched(var + 8 * (3 + D), "<Q", 1),                     # geo_entries too small for nvox: the decoder would read past the index
+                patched(var + 8 * (3 + D) + 8, "<Q", 10 ** 9),           # attr_entries too large
+                patched(var, "<Q", 1 << 40)):                            # a stream longer than the file
+        with pytest.raises(ValueError):
+            container.unpack(bad)
