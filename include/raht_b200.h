@@ -29,7 +29,7 @@
 extern "C" {
 #endif
 
-#define RAHT_B200_ABI_VERSION 15
+#define RAHT_B200_ABI_VERSION 16
 
 enum {
     RAHT_OK = 0,
@@ -304,6 +304,17 @@ int raht_rlgr_decode(const uint8_t *streams, int64_t slot_bytes, const int64_t *
 size_t raht_channel_minmax_workspace_bytes(int64_t n, int D);
 int raht_channel_minmax(const void *T, int t_dtype, int64_t n, int D, double *minmax, void *workspace,
                         size_t workspace_bytes, void *stream);
+/* The same result WITHOUT any allocation and without a caller workspace.  No counterpart in the reference: added
+ * for callers that cannot call cudaMalloc (CUDA graph capture, tight serving
+ * loops, harnesses that forbid it).  The per-CTA partial results live in a file-scope device array of the library
+ * (592 KiB, held by every GPU that loads the library until exit), which limits D to
+ * raht_channel_minmax_static_max_channels() = 64; larger D returns RAHT_E_WORKSPACE with a message.  The call makes no
+ * cudaMalloc / cudaFree and no allocating library call (the first call on each device looks the array's device address
+ * up with cudaGetSymbolAddress, with that device current).  Every call on a device shares the array: calls that may
+ * overlap on the GPU (different streams without ordering) race; calls on one stream are safe.  Nothing in the array
+ * needs to start at zero, the previous call's contents are overwritten before they are read.                        */
+int raht_channel_minmax_static_max_channels(void);
+int raht_channel_minmax_static(const void *T, int t_dtype, int64_t n, int D, double *minmax, void *stream);
 
 /* (a13) sum over rows of (A-B)^2 in fp64 for columns [c0,c1) of two (n, D) matrices -> *sse
  * (device double, overwritten), encode_3dgs.py:298-310.                                            */

@@ -8,6 +8,7 @@
 // and written channel-major so that each channel is one contiguous int32 sequence for the entropy
 // coder.  Algorithmic traffic: D*e + 8 B read, 4*D B written per row.
 #include "common.cuh"
+#include <atomic>
 #include <math.h>
 
 namespace {
@@ -398,6 +399,66 @@ RAHT_API int raht_channel_minmax(const void *T, int t_dtype, int64_t n, int D, d
         return RAHT_E_INVALID;
     }
     minmax_final_kernel<<<(D + 255) / 256, 256, 0, st>>>((const double *)workspace, nb, D, minmax);
+    RAHT_LAUNCH_CHECK();
+    return RAHT_OK;
+}
+
+// ---- no-allocation variant ------------------------------------------------------------------------------------------
+// raht_channel_minmax_static: the same two kernels as raht_channel_minmax, with the per-CTA partial minima / maxima in a
+// file-scope device array instead of a caller workspace, for callers that cannot allocate (code under CUDA graph
+// capture, serving loops, harnesses that forbid cudaMalloc).  No counterpart in the reference.
+// Every GPU that loads the library holds the array (592 KiB) until exit.  All calls on a device
+// share it: calls that overlap on the GPU (different streams, no ordering) race on it.  Nothing in it has to start at
+// zero -- the first kernel overwrites every entry [0, nb) x 2 x D that the second one reads -- so no clear is issued.
+#define RAHT_MINMAX_STATIC_MAX_D_ 64
+static __device__ __align__(256) double g_minmax_scratch[(size_t)MM_BLOCKS_MAX * 2 * RAHT_MINMAX_STATIC_MAX_D_];
+
+namespace {
+constexpr int STATIC_MAX_DEVICES = 64;
+std::atomic<double *> g_minmax_scratch_addr[STATIC_MAX_DEVICES];
+
+// g_minmax_scratch is, in host code, a host-side stand-in: the device address is asked for once per device, with
+// that device current (the caller's), and kept.
+int minmax_scratch_for_current_device(double **out)
+{
+    int dev = -1;
+    RAHT_CUDA(cudaGetDevice(&dev));
+    RAHT_REQUIRE(dev >= 0 && dev < STATIC_MAX_DEVICES, "raht_channel_minmax_static: device ordinal out of range");
+    double *p = g_minmax_scratch_addr[dev].load(std::memory_order_acquire);
+    if (!p) {
+        void *sym = nullptr;
+        RAHT_CUDA(cudaGetSymbolAddress(&sym, g_minmax_scratch));
+        RAHT_REQUIRE(sym != nullptr, "raht_channel_minmax_static: cudaGetSymbolAddress returned null");
+        p = (double *)sym;
+        g_minmax_scratch_addr[dev].store(p, std::memory_order_release);
+    }
+    *out = p;
+    return RAHT_OK;
+}
+}  // namespace
+
+RAHT_API int raht_channel_minmax_static_max_channels(void) { return RAHT_MINMAX_STATIC_MAX_D_; }
+
+RAHT_API int raht_channel_minmax_static(const void *T, int t_dtype, int64_t n, int D, double *minmax, void *stream)
+{
+    RAHT_REQUIRE(n >= 1 && D >= 1 && T && minmax, "raht_channel_minmax_static: bad arguments (n must be >= 1)");
+    if (D > RAHT_MINMAX_STATIC_MAX_D_) {
+        raht_set_error("raht_channel_minmax_static: D exceeds the static scratch (64 channels at most); use raht_channel_minmax with a workspace");
+        return RAHT_E_WORKSPACE;
+    }
+    RAHT_REQUIRE(t_dtype == RAHT_F64 || t_dtype == RAHT_F32, "raht_channel_minmax_static: bad dtype");
+    double *scratch = nullptr;
+    int rc = minmax_scratch_for_current_device(&scratch);
+    if (rc != RAHT_OK) return rc;
+    const size_t smem = (size_t)MM_ROWS * 2 * D * 8;                       // <= 4 KiB at D = 64
+    cudaStream_t st = (cudaStream_t)stream;
+    int nb = (int)((n + MM_ROWS - 1) / MM_ROWS);
+    if (nb > MM_BLOCKS_MAX) nb = MM_BLOCKS_MAX;
+    const dim3 block(64, MM_ROWS);
+    raht_count_launches(2);
+    if (t_dtype == RAHT_F64) minmax_partial_kernel<double><<<nb, block, smem, st>>>((const double *)T, n, D, scratch);
+    else minmax_partial_kernel<float><<<nb, block, smem, st>>>((const float *)T, n, D, scratch);
+    minmax_final_kernel<<<(D + 255) / 256, 256, 0, st>>>(scratch, nb, D, minmax);
     RAHT_LAUNCH_CHECK();
     return RAHT_OK;
 }

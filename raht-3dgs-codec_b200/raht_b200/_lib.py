@@ -74,6 +74,8 @@ SIGNATURES = {
     "raht_sse_f64": (_i, [_p, _p, _i64, _i, _i, _i, _p, _p, _sz, _p]),
     "raht_channel_minmax_workspace_bytes": (_sz, [_i64, _i]),
     "raht_channel_minmax": (_i, [_p, _i, _i64, _i, _p, _p, _sz, _p]),
+    "raht_channel_minmax_static_max_channels": (_i, []),
+    "raht_channel_minmax_static": (_i, [_p, _i, _i64, _i, _p, _p]),
     "raht_sse": (_i, [_p, _i, _p, _i, _i64, _i, _i, _i, _p, _p, _sz, _p]),
     "raht_geometry_symbols": (_i, [_p, _i64, _i64, _p, _p, _p]),
     "raht_geometry_keys_workspace_bytes": (_sz, [_i64]),
