@@ -29,7 +29,7 @@
 extern "C" {
 #endif
 
-#define RAHT_B200_ABI_VERSION 16
+#define RAHT_B200_ABI_VERSION 17
 
 enum {
     RAHT_OK = 0,
@@ -297,6 +297,14 @@ int raht_rlgr_encode_stats(const void *workspace, int64_t n, int nch, unsigned l
 int raht_rlgr_decode(const uint8_t *streams, int64_t slot_bytes, const int64_t *nbytes,
                      const void *sync_index, int64_t n, int64_t ld, int nch, int flag_signed,
                      int32_t *q, void *stream);
+/* Sync index of streams that came without one (written by the reference coder, membuf.cpp:340-423): one walk of
+ * every stream (a warp per channel: bit positions and coder states only, the stream staged through shared memory
+ * ahead of the parsing lane), writing the entries raht_rlgr_encode would have written -- entry r points before the
+ * event that holds the first non-zero symbol of range r.  raht_rlgr_decode with that index is then parallel over
+ * ranges; the walk is the serial part the format forces (rlgrRead, membuf.cpp:258-338, carries k_P / k_RP from
+ * symbol to symbol).  sync_index: nch * raht_rlgr_sync_entries(n) entries of 8 bytes, fully written.            */
+int raht_rlgr_build_index(const uint8_t *streams, int64_t slot_bytes, const int64_t *nbytes, int64_t n,
+                          int nch, void *sync_index, void *stream);
 
 /* (f3) per-channel range of an (n, D) matrix: minmax[0..D) = column minima, minmax[D..2D) = column maxima (device
  * doubles).  Feeds the per-attribute quantisation steps of encode_3dgs_debug.py:326-381 (range of the coefficients of

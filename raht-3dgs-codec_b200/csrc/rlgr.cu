@@ -1257,6 +1257,31 @@ __global__ void __launch_bounds__(32 * SPEC_WARPS) rlgr_emit_kernel(Geometry G, 
     if (sink.overflow && status) atomicOr(status, RAHT_ST_STREAM_OVERFLOW);
 }
 
+// Golomb-Rice symbol whose whole code (p ones, a zero, kR bits) lies in the top 32 bits of the window: ~12 dependent
+// instructions instead of the general reader's two refills, escape test and 64-bit arithmetic.  false (nothing
+// consumed): an escape (p >= 32) or a code longer than 32 bits -- the caller takes the general path.
+template <class Reader>
+__device__ __forceinline__ bool gr_fast(Reader &br, unsigned kR, uint32_t &u, uint32_t &p_out, unsigned &len_out)
+{
+    br.fill();                                                             // >= 33 valid bits
+    const uint32_t hi = (uint32_t)(br.acc >> 32), lo = (uint32_t)br.acc;
+    const unsigned p = (unsigned)__clz((int)~hi);                          // 32 when the top word is all ones
+    const unsigned len = p + 1u + kR;
+    if (len > 32u) return false;
+    const uint32_t rest = __funnelshift_lc(lo, hi, p + 1u);                // the window behind the prefix
+    u = (p << kR) + __funnelshift_rc(rest, 0u, 32u - kR);                  // kR = 0: shift by 32 -> 0
+    br.acc <<= len;
+    br.nbits -= (int)len;
+    p_out = p;
+    len_out = len;
+    return true;
+}
+__device__ __forceinline__ void adapt_krp_small(State &s, uint32_t p)      // adapt_krp for p < 32
+{
+    const int t = s.kRP + (p ? (int)p - 1 : -2);
+    s.kRP = min(max(t, 0), RL_KRP_MAX);
+}
+
 // ---- decoder (BitReader and decode_range live in rlgr_core.cuh) ---------------------------------------------
 // without a sync index: one thread per channel
 __global__ void __launch_bounds__(32) rlgr_decode_serial_kernel(const uint8_t *__restrict__ streams, int64_t slot_bytes,
@@ -1270,6 +1295,138 @@ __global__ void __launch_bounds__(32) rlgr_decode_serial_kernel(const uint8_t *_
     BitReader br;
     br.init(streams + (size_t)ch * slot_bytes, nb, 0);
     decode_range(br, initial_state(), -1, G.n, G.flag_signed, q + (size_t)ch * G.ld);
+}
+
+// A stream without a sync index (written by the reference coder) in two passes: this kernel WALKS it once -- bit
+// positions and coder states only, no symbol leaves the thread -- and writes the sync index the encoder would have
+// written next to it; rlgr_decode_indexed_kernel then decodes every 256-symbol range in parallel.  The walk is the
+// serial part the format forces (the state is carried from symbol to symbol, membuf.cpp:266-334), so it is made as
+// cheap per symbol as it gets: a warp per channel, the lanes copy the stream into a ring in shared memory ahead of
+// lane 0, which parses out of the ring (no global round trip per refill, no scattered stores).
+constexpr uint32_t IDX_RING = 4096, IDX_MARGIN = 8;                       // words; one decode step reads < 8 words
+struct RingWords {
+    const uint32_t *ring;
+    uint32_t pos, ahead;                                                   // pos: index of `ahead` = words handed out
+    __device__ __forceinline__ void open(const uint32_t *r)
+    {
+        ring = r;
+        pos = 0;
+        ahead = ring[0];
+    }
+    __device__ __forceinline__ uint32_t next()
+    {
+        const uint32_t w = rl_bswap32(ahead);
+        ++pos;
+        ahead = ring[pos & (IDX_RING - 1)];
+        return w;
+    }
+};
+__global__ void __launch_bounds__(32) rlgr_index_kernel(const uint8_t *__restrict__ streams, int64_t slot_bytes,
+                                                       const int64_t *__restrict__ nbytes, Geometry G,
+                                                       uint2 *__restrict__ sync_index, int64_t entries)
+{
+    __shared__ uint32_t ring[IDX_RING];
+    const int ch = blockIdx.x, lane = threadIdx.x;
+    int64_t nb = nbytes ? nbytes[ch] : slot_bytes;
+    if (nb > slot_bytes) nb = slot_bytes;
+    if (nb < 0) nb = 0;
+    const uint32_t n_words = (uint32_t)((nb + 3) >> 2);
+    const uint32_t *in = (const uint32_t *)(streams + (size_t)ch * slot_bytes);
+    uint2 *ent = sync_index + (size_t)ch * entries;
+    for (int64_t e = lane; e < entries; e += 32) ent[e] = make_uint2(0u, SYNC_NONE << 22);
+    BitReaderT<RingWords> br;
+    State s = initial_state();
+    const uint32_t n = (uint32_t)G.n;
+    uint32_t pos = 0, loaded = 0, rd = 0;
+    int64_t marked = -1;                                                   // last range that has its entry
+    bool opened = false;
+    for (;;) {
+        const uint32_t hi = rd + IDX_RING - 32;
+        for (uint32_t i = loaded + lane; i < hi; i += 32) ring[i & (IDX_RING - 1)] = i < n_words ? in[i] : 0u;
+        loaded = hi;
+        __syncwarp();
+        int done = 0;
+        if (lane == 0) {
+            if (!opened) {
+                br.src.open(ring);
+                br.acc = 0;
+                br.nbits = 0;
+                opened = true;
+            }
+            while (pos < n && br.src.pos + IDX_MARGIN < loaded) {
+                if (s.kP < RL_L) {                                         // no-run mode: one symbol, the lean way
+                    uint32_t u, p;
+                    unsigned len;
+                    if (gr_fast(br, (unsigned)s.kRP / RL_L, u, p, len)) {
+                        if (u) {
+                            const int64_t r = (int64_t)(pos >> SYNC_SHIFT);
+                            if (r != marked) {
+                                marked = r;
+                                const unsigned long long at = (unsigned long long)br.src.pos * 32ull - (unsigned long long)(br.nbits + (int)len);
+                                ent[r] = make_uint2((uint32_t)at, (uint32_t)((at >> 32) & 0x7f) | ((uint32_t)s.kP << 7) |
+                                                                      ((uint32_t)s.kRP << 14) | ((pos & (SYNC_RANGE - 1)) << 22));
+                            }
+                            s.kP = max(s.kP - RL_D0, 0);
+                        } else {
+                            s.kP += RL_U0;
+                        }
+                        adapt_krp_small(s, p);
+                        ++pos;
+                        continue;
+                    }
+                }
+                const unsigned long long at_bit = (unsigned long long)br.src.pos * 32ull - (unsigned long long)br.nbits;
+                const State before = s;
+                int k = s.kP / RL_L;
+                const unsigned kR = (unsigned)(s.kRP / RL_L);
+                const bool run = k != 0;
+                if (run) {
+                    uint32_t m = 0;
+                    bool bad = false;
+                    for (;;) {
+                        const int p = br.ones();
+                        for (int j = 0; j < p; ++j) {
+                            m += 1u << k;
+                            s.kP += RL_U1;
+                            k = s.kP / RL_L;
+                            if (m >= (1u << 31) || k > 30) { bad = true; break; }
+                        }
+                        if (bad) break;
+                        if (p < 32) { br.skip((unsigned)p + 1); break; }
+                        br.skip(32);
+                    }
+                    if (!bad) m += br.get((unsigned)k);
+                    if (bad || m >= n - pos) { pos = n; break; }           // zeros to the end (or a corrupt stream)
+                    pos += m;
+                }
+                uint32_t u, pf;
+                unsigned lf;
+                if (gr_fast(br, kR, u, pf, lf)) {
+                    adapt_krp_small(s, pf);
+                } else {
+                    u = br.gr(kR);
+                    adapt_krp(s, (uint64_t)u >> kR);
+                }
+                if (run || u) {
+                    const int64_t r = (int64_t)(pos >> SYNC_SHIFT);
+                    if (r != marked) {
+                        marked = r;
+                        ent[r] = make_uint2((uint32_t)at_bit, (uint32_t)((at_bit >> 32) & 0x7f) | ((uint32_t)before.kP << 7) |
+                                                                  ((uint32_t)before.kRP << 14) | ((pos & (SYNC_RANGE - 1)) << 22));
+                    }
+                    s.kP = s.kP < RL_D1 ? 0 : s.kP - RL_D1;
+                } else {
+                    s.kP += RL_U0;
+                }
+                ++pos;
+            }
+            done = pos >= n;
+            rd = br.src.pos;
+        }
+        done = __shfl_sync(~0u, done, 0);
+        rd = __shfl_sync(~0u, rd, 0);
+        if (done) break;
+    }
 }
 
 // with the encoder's sync index: one thread per entry (256 symbols)
@@ -1308,8 +1465,14 @@ __device__ __forceinline__ void decode_step(BitReader &br, State &s, bool &synce
         if (synced) pos += m;
         else { pos = first; synced = true; }
     }
-    const uint32_t u = br.gr(kR);
-    adapt_krp(s, (uint64_t)u >> kR);
+    uint32_t u, pf;
+    unsigned lf;
+    if (gr_fast(br, kR, u, pf, lf)) {
+        adapt_krp_small(s, pf);
+    } else {
+        u = br.gr(kR);
+        adapt_krp(s, (uint64_t)u >> kR);
+    }
     if (run || u) {
         if (!synced) { pos = first; synced = true; }
         const uint64_t v = (uint64_t)u + (run ? 1u : 0u);
@@ -1492,6 +1655,23 @@ RAHT_API int raht_rlgr_encode_stats(const void *workspace, int64_t n, int nch, u
     const EncLayout L = enc_layout(n, nch);
     RAHT_CUDA(cudaMemcpyAsync(out5_host, (const char *)workspace + L.off_stats, 48, cudaMemcpyDeviceToHost, (cudaStream_t)stream));
     RAHT_CUDA(cudaStreamSynchronize((cudaStream_t)stream));
+    return RAHT_OK;
+}
+
+RAHT_API int raht_rlgr_build_index(const uint8_t *streams, int64_t slot_bytes, const int64_t *nbytes, int64_t n, int nch,
+                                   void *sync_index, void *stream)
+{
+    RAHT_REQUIRE(n >= 0 && n < ((int64_t)1 << 31) - 256 && nch >= 0 && nch < 65536 && slot_bytes >= 8 && (slot_bytes % 8) == 0,
+                 "raht_rlgr_build_index: bad sizes (slot_bytes must be a positive multiple of 8)");
+    if (nch == 0 || n == 0) return RAHT_OK;
+    RAHT_REQUIRE(streams && sync_index, "raht_rlgr_build_index: null pointer");
+    RAHT_REQUIRE(((uintptr_t)streams & 7) == 0 && ((uintptr_t)sync_index & 7) == 0, "raht_rlgr_build_index: pointers must be 8-byte aligned");
+    Geometry G;
+    G.n = n; G.ld = n; G.nsb = sym_blocks_of(n); G.W = chunk_slots_of(n); G.nch = nch; G.flag_signed = 0;
+    G.q = nullptr; G.lastnz = nullptr; G.vec = 0;
+    (raht_count_launches(1), rlgr_index_kernel)<<<nch, 32, 0, (cudaStream_t)stream>>>(streams, slot_bytes, nbytes, G, (uint2 *)sync_index,
+                                                                                       raht_rlgr_sync_entries(n));
+    RAHT_LAUNCH_CHECK();
     return RAHT_OK;
 }
 

@@ -70,6 +70,7 @@ SIGNATURES = {
     "raht_rlgr_encode": (_i, [_p, _i64, _i64, _i, _i, _p, _i64, _p, _p, _p, _p, _sz, _p]),
     "raht_rlgr_encode_stats": (_i, [_p, _i64, _i, C.POINTER(C.c_ulonglong), _p]),
     "raht_rlgr_decode": (_i, [_p, _i64, _p, _p, _i64, _i64, _i, _i, _p, _p]),
+    "raht_rlgr_build_index": (_i, [_p, _i64, _p, _i64, _i, _p, _p]),
     "raht_sse_workspace_bytes": (_sz, [_i64, _i]),
     "raht_sse_f64": (_i, [_p, _p, _i64, _i, _i, _i, _p, _p, _sz, _p]),
     "raht_channel_minmax_workspace_bytes": (_sz, [_i64, _i]),

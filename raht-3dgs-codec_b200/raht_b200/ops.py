@@ -507,13 +507,27 @@ def rlgr_encode(q: torch.Tensor, flag_signed=1, slot_bytes=None, with_index=True
         return out
 
 
-def rlgr_decode(streams: RlgrStreams, flag_signed=1, use_index=True) -> torch.Tensor:
-    """Chunk-parallel with the encoder's sync index, else one channel per thread (reference streams)."""
+def rlgr_build_index(streams: RlgrStreams) -> torch.Tensor:
+    """Sync index (nch, entries, 2) uint32 of streams that carry none (reference-coder streams): raht_rlgr_build_index."""
+    n, nch = streams.n, streams.nch
+    entries = lib.raht_rlgr_sync_entries(n)
+    index = torch.empty(nch, max(entries, 1), 2, dtype=torch.int32, device=streams.buf.device)
+    check(lib.raht_rlgr_build_index(ptr(streams.buf), streams.slot_bytes, ptr(streams.nbytes), n, nch, ptr(index), stream()),
+          "raht_rlgr_build_index")
+    return index[:, :entries]
+
+
+def rlgr_decode(streams: RlgrStreams, flag_signed=1, use_index=True, serial=False) -> torch.Tensor:
+    """Parallel over 256-symbol ranges through the sync index: the encoder's, or -- for streams without one (written by the
+    reference coder) or with use_index=False -- one rebuilt by a walk of the streams (rlgr_build_index).  serial=True:
+    the plain one-thread-per-channel decoder (kept as the second opinion of the tests)."""
     dev = streams.buf.device
     n, nch = streams.n, streams.nch
     ld = (n + 3) // 4 * 4
     q = torch.empty(nch, max(ld, 1), dtype=torch.int32, device=dev)
     index = streams.sync_index if use_index else None
+    if index is None and not serial and n > 0 and nch > 0:
+        index = rlgr_build_index(streams)
     check(lib.raht_rlgr_decode(ptr(streams.buf), streams.slot_bytes, ptr(streams.nbytes), ptr(index), n, max(ld, 1), nch,
                                flag_signed, ptr(q), stream()), "raht_rlgr_decode")
     return q[:, :n]

@@ -313,7 +313,8 @@ def test_rlgr_random_vs_oracle(zfrac, scale, n):
     exp, _, _, _ = orc.rlgr_encode_channels(x, 1)
     assert streams.to_bytes() == exp
     assert np.array_equal(ops.rlgr_decode(streams, 1).cpu().numpy(), x)                       # chunk-parallel, sync index
-    assert np.array_equal(ops.rlgr_decode(streams, 1, use_index=False).cpu().numpy(), x)      # channel-serial
+    assert np.array_equal(ops.rlgr_decode(streams, 1, use_index=False).cpu().numpy(), x)      # index rebuilt by a walk of the streams
+    assert np.array_equal(ops.rlgr_decode(streams, 1, use_index=False, serial=True).cpu().numpy(), x)   # channel-serial
     assert streams.stats["chunks"] == nch * ((n + 255) // 256)                                 # one sync entry per 256 symbols
     no_index = ops.rlgr_encode(cu(x), 1, with_index=False)
     assert no_index.sync_index is None and no_index.to_bytes() == exp
@@ -344,6 +345,8 @@ def test_rlgr_regime_changes_and_unsigned():
                 assert st.to_bytes() == e, (n, last, fs)
                 assert np.array_equal(ops.rlgr_decode(st, fs).cpu().numpy(), z), (n, last, fs)
                 assert np.array_equal(ops.rlgr_decode(st, fs, use_index=False).cpu().numpy(), z), (n, last, fs)
+                if n in (1, 129, 7937):
+                    assert np.array_equal(ops.rlgr_decode(st, fs, use_index=False, serial=True).cpu().numpy(), z), (n, last, fs)
 
 
 def test_rlgr_one_signed_sparse_channels_use_the_tables():

@@ -90,7 +90,18 @@ def test_reference_format_streams_without_index_decode_at_scale():
     streams = ops.rlgr_encode(torch.from_numpy(x).to(DEV), 1, with_index=False)
     assert streams.sync_index is None
     assert streams.to_bytes() == cpu_streams(x)
-    assert np.array_equal(ops.rlgr_decode(streams, 1, use_index=False).cpu().numpy(), x)
+    t0, t1, t2 = (torch.cuda.Event(enable_timing=True) for _ in range(3))
+    t0.record()
+    index = ops.rlgr_build_index(streams)                     # the serial walk (a warp per channel) ...
+    t1.record()
+    streams.sync_index = index
+    got = ops.rlgr_decode(streams, 1)                         # ... then every 256-symbol range in parallel
+    t2.record()
+    torch.cuda.synchronize()
+    assert np.array_equal(got.cpu().numpy(), x)
+    streams.sync_index = None
+    assert np.array_equal(ops.rlgr_decode(streams, 1, use_index=False, serial=True).cpu().numpy(), x)
+    print(f"index-less decode of {nch} x {n}: walk {t0.elapsed_time(t1):.2f} ms + ranges {t1.elapsed_time(t2):.2f} ms")
 
 
 def test_c1_point_cloud_frame_is_bit_exact_with_the_oracle():
