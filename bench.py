@@ -344,6 +344,8 @@ def bind_rank_to_cores(local, world):
     other.  Returns a short description for the JSON line.  N = 1: untouched (the CPU baseline wants every core)."""
     if world <= 1:
         return {"bound": False, "cores": host_cores()}
+    if os.environ.get("RAHT_BENCH_BIND", "1") == "0":
+        return {"bound": False, "cores": host_cores(), "note": "RAHT_BENCH_BIND=0"}
     try:
         allowed = sorted(os.sched_getaffinity(0))
         pools = []
@@ -436,7 +438,8 @@ def run_gpu(args):
             timers.append(tm)
         e1.record()
         barrier()
-        ms_step = max_over_ranks(e0.elapsed_time(e1)) / steps
+        ms_ranks = [round(x / steps, 4) for x in gather_ranks(e0.elapsed_time(e1))]
+        ms_step = max(ms_ranks)
         launches = (ops.lib.raht_launch_count() - launches0) // max(steps, 1)
         mem1 = torch.cuda.memory_stats(dev)
         stages, stage_max = {}, {}
@@ -444,7 +447,7 @@ def run_gpu(args):
             for k, v in tm.result().items():
                 stages[k] = stages.get(k, 0.0) + v / len(timers)
                 stage_max[k] = max(stage_max.get(k, 0.0), v)
-        return {"ms_step": ms_step, "launches": int(launches), "stages": stages, "stage_max": stage_max, "enc": enc, "Crec": Crec,
+        return {"ms_step": ms_step, "ms_ranks": ms_ranks, "launches": int(launches), "stages": stages, "stage_max": stage_max, "enc": enc, "Crec": Crec,
                 "cuda_mallocs": int(mem1.get("segment.all.allocated", 0) - mem0.get("segment.all.allocated", 0))}
 
     def per_stage_table(res, n_in, J_, peak):
@@ -621,6 +624,7 @@ def run_gpu(args):
     line = {
         "metric": METRIC, "value": round(value, 1), "unit": "Gaussians/s",
         "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": round(ms_step, 4),
+        "ms_per_step_ranks": main["ms_ranks"],
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": args.dtype, "data": "synthetic",
         "config": {"workload": desc, "n_gaussians_per_gpu": n, "nvox": nvox, "depth": J, "channels": D, "quant_step": STEP,
                    "tile_rows": args.tile_rows or ops.DEFAULT_TILE_ROWS, "payload_bytes": payload, "sync_index_bytes": index_bytes,

@@ -642,18 +642,21 @@ __device__ __forceinline__ void solve_chunk(const LaneBlock &B, bool pin, const 
 //                           [1] end states (8 x 16 bit), [2], [3] code length of the chunk on each chain (8 x 32 bit)
 // lane record  (3 x uint4): [0] the lane's 8 candidates (16 bit each), [1] code lengths of its block (8 x 16 bit),
 //                           [2].x nibble c = the lane's candidate on the chain of chunk candidate c
+//                           [3] end states of its block under each candidate (8 x 16 bit; speculation records only:
+//                               what lets a repair join the recorded chains instead of coding every block again)
 // chunk offset (u64)      : bit offset of the chunk in its stream << 3 | chosen chunk candidate
 // sync index   (uint2)    : x = bit offset (low 32), y = offset bits 32..38 | k_P << 7 | k_RP << 14 | first << 22
-constexpr int REC_WORDS = 4, LANEREC_WORDS = 3;
+constexpr int REC_WORDS = 4, LANEREC_WORDS = 4;
 
 template <int NC> __device__ __forceinline__ void finish_chunk(const ChunkSol<NC> &S, uint4 *rec, uint4 *lanerec)
 {
     const int lane = threadIdx.x & 31;
-    uint32_t in16[4] = {0, 0, 0, 0}, b16[4] = {0, 0, 0, 0};
+    uint32_t in16[4] = {0, 0, 0, 0}, b16[4] = {0, 0, 0, 0}, out16[4] = {0, 0, 0, 0};
     uint32_t cand16[4] = {~0u, ~0u, ~0u, ~0u}, end16[4] = {0, 0, 0, 0}, tot[8] = {0, 0, 0, 0, 0, 0, 0, 0};
     for (int c = 0; c < NC; ++c) {
         in16[c >> 1] |= (S.in[c] & 0xffffu) << (16 * (c & 1));
         b16[c >> 1] |= (S.bits[c] & 0xffffu) << (16 * (c & 1));
+        out16[c >> 1] |= (S.out[c] & 0xffffu) << (16 * (c & 1));
         const uint32_t l1 = __shfl_sync(~0u, S.in[c], 1);
         const uint32_t cand = (S.complete >> c & 1) ? l1 : STATE_INVALID;
         cand16[c >> 1] = (cand16[c >> 1] & ~(0xffffu << (16 * (c & 1)))) | (cand << (16 * (c & 1)));
@@ -664,6 +667,8 @@ template <int NC> __device__ __forceinline__ void finish_chunk(const ChunkSol<NC
     lr[0] = make_uint4(in16[0], in16[1], in16[2], in16[3]);
     lr[1] = make_uint4(b16[0], b16[1], b16[2], b16[3]);
     lr[2] = make_uint4(S.sel, 0u, 0u, 0u);
+    lr[3] = make_uint4(out16[0], out16[1], out16[2], out16[3]);
+    if (NC < 8) lr[3] = make_uint4(0xffffffffu, 0xffffffffu, 0xffffffffu, 0xffffffffu);      // (only the 8-candidate records are joined)
     if (lane == 0) {
         rec[0] = make_uint4(cand16[0], cand16[1], cand16[2], cand16[3]);
         rec[1] = make_uint4(end16[0], end16[1], end16[2], end16[3]);
@@ -961,20 +966,74 @@ __global__ void __launch_bounds__(32 * SPEC_WARPS) rlgr_table_lanes_kernel(Geome
 // the chunk ended up here), so a pinned fixed point would advance the true state by one lane per ROUND anyway -- 29
 // rounds of 8-candidate recodes with helper hand-overs, 0.8 ms per chunk on the 50 M-symbol position channel (97 such
 // chunks: 78 of the 105 ms of that encode) -- where the walk pays 31 single-state block codings and nothing else.
+// `stage` (shared memory, 32 x EV_BLOCK events; may be null): with one lane coding at a time, the event loads of
+// count_lane are lone 32-byte requests that each pay a full round trip (190 SM clocks per event, 0.4 ms per chunk).  All
+// lanes therefore copy their blocks into shared memory first -- together, coalesced -- and the serial pass reads them
+// from there.
 __device__ __forceinline__ void walk_chunk_exact(const LaneBlock &B, uint32_t start, uint4 *rec, uint4 *lanerec, uint32_t &end_state,
-                                                 uint32_t &total_bits)
+                                                 uint32_t &total_bits, uint2 *stage, bool use_record, int &blocks_coded)
 {
     const int lane = threadIdx.x & 31;
     const bool has = lane > 0 && (B.cnt > 0 || B.is_tail);
-    uint32_t s = start, my_in = start, my_bits = 0, total = 0;
+    const bool staged = stage != nullptr && B.sym == nullptr;          // (warp-uniform: a chunk belongs to one channel)
+    if (staged) {
+        uint4 *mine = (uint4 *)(stage + (size_t)lane * EV_BLOCK);
+        const int units = lane > 0 ? (B.cnt + EV_GROUP - 1) / EV_GROUP : 0;
+        for (int j0 = 0; j0 < EV_BLOCK / EV_GROUP; j0 += 8) {
+            uint4 a[8], b[8];
+#pragma unroll
+            for (int t = 0; t < 8; ++t)
+                if (j0 + t < units) {
+                    a[t] = __ldg(B.base + ((j0 + t) * 32 + B.slot) * 2);
+                    b[t] = __ldg(B.base + ((j0 + t) * 32 + B.slot) * 2 + 1);
+                }
+#pragma unroll
+            for (int t = 0; t < 8; ++t)
+                if (j0 + t < units) {
+                    mine[(j0 + t) * 2] = a[t];
+                    mine[(j0 + t) * 2 + 1] = b[t];
+                }
+        }
+        __syncwarp();
+    }
+    // The chunk's speculation record knows, for 8 start states of every block, where the block ends and how long its code
+    // is.  None of lane 1's candidates was the true state (that is why the chunk is here), but the true trajectory usually
+    // MERGES with a recorded one within a block or two (same class, section 4.2 of DESIGN.md): from then on every lane finds
+    // the incoming state among its candidates and answers from the record.  Only the blocks before the merge are coded.
+    uint4 *lr = lanerec + (size_t)lane * LANEREC_WORDS;
+    const uint4 r_in = lr[0], r_bits = lr[1], r_out = lr[3];
+    uint32_t s = start, my_in = start, my_bits = 0, total = 0, coded = 0;
     for (int l = 1; l < 32; ++l) {
         uint32_t out = s, b = 0;
         if (lane == l) {
             my_in = s;
-            if (has) {
+            int hit = -1;
+            if (has && use_record)
+                for (int c = 7; c >= 0; --c)
+                    if (half_of(r_in, c) == s && half_of(r_out, c) != STATE_INVALID) hit = c;
+            if (hit >= 0) {
+                out = half_of(r_out, hit);
+                b = my_bits = half_of(r_bits, hit);
+            } else if (has) {
+                ++coded;
                 State t[1] = {unpack_state(s)};
                 uint32_t bb[1];
-                count_lane<1>(B, t, bb);
+                if (staged) {
+                    const uint2 *mine = stage + (size_t)lane * EV_BLOCK;
+                    bool quirk = false;
+                    bb[0] = 0;
+                    for (int i = 0; i < B.cnt; ++i) {
+                        const uint2 e = mine[i];
+                        quirk = count_event(t[0], e.x, e.y, bb[0]);
+                    }
+                    if (B.is_tail) {
+                        CountSink k{0};
+                        code_tail(t[0], B.tail_zeros, quirk, k);
+                        bb[0] += k.bits;
+                    }
+                } else {
+                    count_lane<1>(B, t, bb);
+                }
                 out = pack_state(t[0]);
                 b = bb[0];
                 my_bits = b;
@@ -984,10 +1043,12 @@ __device__ __forceinline__ void walk_chunk_exact(const LaneBlock &B, uint32_t st
         total += __shfl_sync(~0u, b, l);
     }
     if (lane == 0) my_in = start;
-    uint4 *lr = lanerec + (size_t)lane * LANEREC_WORDS;
     lr[0] = make_uint4(my_in & 0xffffu, 0u, 0u, 0u);
     lr[1] = make_uint4(lane == 0 ? 0u : (my_bits & 0xffffu), 0u, 0u, 0u);
     lr[2] = make_uint4(0u, 0u, 0u, 0u);
+    lr[3] = make_uint4(0xffffffffu, 0xffffffffu, 0xffffffffu, 0xffffffffu);
+    for (int o = 16; o; o >>= 1) coded += __shfl_xor_sync(~0u, coded, o);
+    blocks_coded = (int)coded;
     if (lane == 0) {
         rec[0] = make_uint4((start & 0xffffu) | (STATE_INVALID << 16), ~0u, ~0u, ~0u);
         rec[1] = make_uint4(s & 0xffffu, 0u, 0u, 0u);
@@ -1013,6 +1074,7 @@ __global__ void __launch_bounds__(32 * SOLVE_WARPS) rlgr_resolve_kernel(Geometry
     const int64_t nchunks = I.nchunks;
     const bool dense = channel_is_dense(I, G);
     __shared__ Helpers helpers;                          // warps 1..7: single-state coders for the re-solves of a sparse channel
+    __shared__ uint2 walk_stage[32 * EV_BLOCK];          // the events of a chunk under repair (walk_chunk_exact)
     if (threadIdx.x >= 32) {
         if (!dense) helper_loop(&helpers, ev, G, ch, I);
         return;
@@ -1068,8 +1130,7 @@ __global__ void __launch_bounds__(32 * SOLVE_WARPS) rlgr_resolve_kernel(Geometry
                         rounds = S.rounds;
                     } else {
                         uint32_t e_x, t_x;
-                        walk_chunk_exact(B, ps, rec + ci * REC_WORDS, lr, e_x, t_x);
-                        rounds = 31;
+                        walk_chunk_exact(B, ps, rec + ci * REC_WORDS, lr, e_x, t_x, walk_stage, true, rounds);
                     }
                     __syncwarp();
                     const uint4 *rr = rec + ci * REC_WORDS;          // (written by lane 0 just above): the pinned chain is candidate 0

@@ -45,7 +45,8 @@ def oracle_front(scene, J):
 
 
 @pytest.mark.parametrize("name,n,J,seed,steps", [("c2", 1_000_000, 12, 2001, (1.0 / 64, 0.25, 2.0)),
-                                                 ("c3", 6_000_000, 16, 3001, (1.0 / 64, 0.25))])
+                                                 ("c3", 6_000_000, 16, 3001, (1.0 / 64, 0.25)),
+                                                 ("c2_rank3", 1_000_000, 12, 2004, (1.0 / 64,))])   # a replica rank's scene: 3 exact repairs in channel 0
 def test_bench_scene_is_bit_exact_with_the_oracle(name, n, J, seed, steps):
     from raht_b200 import codec, ops
     orc.set_num_threads(_cores())
