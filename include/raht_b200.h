@@ -29,7 +29,7 @@
 extern "C" {
 #endif
 
-#define RAHT_B200_ABI_VERSION 17
+#define RAHT_B200_ABI_VERSION 18
 
 enum {
     RAHT_OK = 0,
@@ -333,6 +333,38 @@ size_t raht_sse_workspace_bytes(int64_t n, int D);
  * reconstruction fp64 (the reference up-casts before subtracting, encode_3dgs.py:298).                */
 int raht_sse(const void *A, int a_dtype, const void *B, int b_dtype, int64_t n, int D, int c0, int c1,
              double *sse, void *workspace, size_t workspace_bytes, void *stream);
+
+/* ------------------------------------------------------------------------------------------------
+ * (f4) Render evaluator as CUDA compute: the reference renders original and merged / decoded Gaussians from random
+ * views with the third-party gsplat.rasterization and compares the images (python/quality_eval.py:283-353
+ * render_gaussians, :373-520 try_render_comparison).  gsplat is not vendored in the reference: these entry points
+ * restate the published 3DGS / gsplat "classic" rasterisation with gsplat's defaults (near plane 0.01, eps2d 0.3,
+ * 3-sigma extent, 16 x 16 tiles, alpha >= 1/255, alpha cap 0.999, transmittance cut 1e-4, colour =
+ * max(SH(view direction) + 0.5, 0), quaternions normalised as quality_eval.py:335 does); parity unpinned (checked
+ * against oracle/splat_oracle.py).  One view per call sequence, fp32:
+ *   raht_splat_project     camera transform, near / frustum cull, EWA projection, conic, tile rectangle and SH colour
+ *                          of every Gaussian into the workspace; *n_isect (device) = tiles touched in total.
+ *                          viewmat16_host: row-major 4x4 world-to-camera matrix (camera looks down +z), HOST memory;
+ *                          colors: (n, color_dim), coefficient-major [k][rgb] (colors.reshape(-1, K, 3), :319-321);
+ *                          sh_degree -1: the first three entries are RGB (:324-326).
+ *   raht_splat_tile_keys   key = tile << 32 | depth bits, value = Gaussian, m = *n_isect entries (the caller reads it,
+ *                          allocates, and sorts with raht_radix_sort_pairs over bits [0, 32 + tile bits))
+ *   raht_splat_tile_ranges ranges[2 t], ranges[2 t + 1] = first / one-past-last sorted entry of tile t (n_tiles pairs)
+ *   raht_splat_rasterize   front-to-back alpha blending per 16 x 16 tile over background3_host -> image (height,
+ *                          width, 3) fp32
+ * ------------------------------------------------------------------------------------------------ */
+size_t raht_splat_workspace_bytes(int64_t n);
+int raht_splat_project(const float *means, const float *quats, const float *scales, const float *opacities,
+                       const float *colors, int color_dim, int sh_degree, int64_t n,
+                       const float *viewmat16_host, float fx, float fy, float cx, float cy, int width,
+                       int height, void *workspace, size_t workspace_bytes, int64_t *n_isect, void *stream);
+int raht_splat_tile_keys(void *workspace, size_t workspace_bytes, int64_t n, int width, int height,
+                         uint64_t *keys, int32_t *vals, int64_t m, void *stream);
+int raht_splat_tile_ranges(const uint64_t *sorted_keys, int64_t m, int n_tiles, int32_t *ranges,
+                           void *stream);
+int raht_splat_rasterize(void *workspace, size_t workspace_bytes, int64_t n, const int32_t *sorted_vals,
+                         const int32_t *ranges, int width, int height, const float *background3_host,
+                         float *image, void *stream);
 
 /* ------------------------------------------------------------------------------------------------
  * (f1, f2) Container support: geometry symbols and stream packing.  The reference never serialises

@@ -86,6 +86,12 @@ SIGNATURES = {
     "raht_shard_top_cells": (_i, [_p, _p, _p, _i, _p, _i, _i, _i, _p, _p, _p]),
     "raht_ply_pack_vertices": (_i, [_p, _p, _p, _p, _p, _i, _i64, _p, _p]),
     "raht_ply_unpack_vertices": (_i, [_p, _i, _i64, _p, _p, _p, _p]),
+    "raht_splat_workspace_bytes": (_sz, [_i64]),
+    "raht_splat_project": (_i, [_p, _p, _p, _p, _p, _i, _i, _i64, C.POINTER(C.c_float), C.c_float, C.c_float, C.c_float, C.c_float,
+                                _i, _i, _p, _sz, _p, _p]),
+    "raht_splat_tile_keys": (_i, [_p, _sz, _i64, _i, _i, _p, _p, _i64, _p]),
+    "raht_splat_tile_ranges": (_i, [_p, _i64, _i, _p, _p]),
+    "raht_splat_rasterize": (_i, [_p, _sz, _i64, _p, _p, _i, _i, C.POINTER(C.c_float), _p, _p]),
     "raht_rgb_to_yuv": (_i, [_p, _i, _i64, _p, _p]),
     "raht_histogram_i64": (_i, [_p, _i64, _i, _i, _p, _p]),
     "raht_pack_rows": (_i, [_p, _i64, _p, _p, _p, _p, _p, _i, _p, _p]),

@@ -32,7 +32,7 @@ def test_ctypes_signatures_cover_header():
     assert sorted(_lib.SIGNATURES) == declared_symbols()
     import re
     header = open(os.path.join(ROOT, "include", "raht_b200.h")).read()
-    assert _lib.lib.raht_abi_version() == int(re.search(r"#define RAHT_B200_ABI_VERSION (\d+)", header).group(1)) == 17
+    assert _lib.lib.raht_abi_version() == int(re.search(r"#define RAHT_B200_ABI_VERSION (\d+)", header).group(1)) == 18
 
 
 def test_argument_validation_without_gpu():
