@@ -591,6 +591,11 @@ def run_gpu(args):
                          "unit": "Gaussians/s", "payload_bytes": r["enc"].payload_bytes(),
                          "bits_per_voxel": round(r["enc"].payload_bytes() * 8 / r["enc"].nvox, 3),
                          "rlgr_encode_ms": round(r["stages"].get("rlgr_encode", 0.0), 4), "rlgr_decode_ms": round(r["stages"].get("rlgr_decode", 0.0), 4)}
+        # render-quality evaluation (quality_eval.py:373-520): original against decoded Gaussians of the timed configuration
+        try:
+            sub["render_eval"] = render_record(devt2, codec, J, STEP)
+        except Exception as e:                                   # a reported extra, never a reason to lose the line
+            sub["render_eval"] = {"error": str(e)[:120]}
         del devt2, r
         torch.cuda.empty_cache()
         # BASELINE configs[2]: 6 M Gaussians, depth 16, fp64 bit-exact mode (the scene tests/test_gpu_scale_parity.py checks)
@@ -657,6 +662,27 @@ def run_gpu(args):
     print(json.dumps(line))
     if world > 1:
         dist.destroy_process_group()
+
+
+def render_record(scene_dev, codec, J, step):
+    """The reference's image-space check (quality_eval.try_render_comparison) on the CUDA splat rasteriser: the 1 M scene
+    against its reconstruction from the coded streams (voxel-merged, quantised at `step`, decoded), 3 views of 512 x 512.
+    The synthetic scales are shrunk so that a splat covers a few pixels, as in a trained scene."""
+    import torch
+    from raht_b200 import render_eval
+    m, q, s, o, c = scene_dev
+    orig = dict(means=m, quats=q, scales=s * 0.25, opacities=o, colors=c)
+    coords, A = codec.decode_scene(codec.encode_scene(m, q, s, o, c, J=J, step=step))
+    A = A.float()
+    dec = dict(means=A[:, 0:3].contiguous(), quats=A[:, 3:7].contiguous(), scales=A[:, 7:10].contiguous() * 0.25,
+               opacities=A[:, 10].contiguous(), colors=A[:, 11:].contiguous())
+    g = torch.Generator().manual_seed(4)
+    render_eval.try_render_comparison(orig, dec, n_views=1, image_size=512, generator=torch.Generator().manual_seed(4))   # warm-up
+    res = render_eval.try_render_comparison(orig, dec, n_views=3, image_size=512, generator=g)
+    return {"views": 3, "image": "512x512", "quant_step": step, "n_original": int(m.shape[0]), "n_decoded": int(A.shape[0]),
+            "psnr_avg_db": round(res["psnr_avg"], 3), "psnr_min_db": round(res["psnr_min"], 3),
+            "ms_per_view_original": round(res["original_render_time_ms"] / 3, 3), "ms_per_view_decoded": round(res["merged_render_time_ms"] / 3, 3),
+            "how": "raht_b200.render_eval (csrc/splat.cu): project + tile sort + rasterise per view, host-timed like the reference (quality_eval.py:421-447)"}
 
 
 def c5_record(args, dev, rank, world, barrier, max_over_ranks, tdtype):
