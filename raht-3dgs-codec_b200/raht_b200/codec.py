@@ -302,11 +302,20 @@ def decode_attributes(keys, streams, D, step, transform_dtype=torch.float64, tre
 _PINNED = {}
 
 
+_PIN_RING = 16
+
+
 def _pinned_results(device, nbytes):
+    """A small pinned host buffer for the results a scene-level call publishes (voxel count, stream lengths, status words).
+    A ring of _PIN_RING buffers per device and stream: a deferred check (`checks=` of encode_scene / decode_scene) reads
+    its buffer after later calls have been issued, so consecutive calls must not share one."""
     key = (device.index if device.index is not None else torch.cuda.current_device(), torch.cuda.current_stream(device).cuda_stream)
-    buf = _PINNED.get(key)
-    if buf is None or buf.numel() < nbytes:
-        buf = _PINNED[key] = torch.empty(max(nbytes, 4096), dtype=torch.uint8).pin_memory()
+    ring = _PINNED.get(key)
+    if ring is None or ring[0][0].numel() < nbytes:
+        ring = _PINNED[key] = ([torch.empty(max(nbytes, 4096), dtype=torch.uint8).pin_memory() for _ in range(_PIN_RING)], [0])
+    bufs, nxt = ring
+    buf = bufs[nxt[0] % _PIN_RING]
+    nxt[0] += 1
     return buf
 
 
@@ -337,7 +346,8 @@ def _tree_from_workspace(tree_ws, layout, nvox, tile_rows, plan_handle):
 
 
 @torch.no_grad()
-def _encode_scene_calls(means, quats, scales, opacities, colors, J, step, transform_dtype, tile_rows, timer, keep_packed, given=None):
+def _encode_scene_calls(means, quats, scales, opacities, colors, J, step, transform_dtype, tile_rows, timer, keep_packed, given=None,
+                        checks=None, min_slot=0):
     """encode_scene through raht_scene_front + raht_scene_encode: two host calls and one synchronisation between them (the
     voxel count sizes the second leg), one more at the end (stream lengths and status word)."""
     import ctypes as C
@@ -375,49 +385,63 @@ def _encode_scene_calls(means, quats, scales, opacities, colors, J, step, transf
                                ptr(offsets), ptr(nvox_dev), C.c_void_p(pin.data_ptr()), ptr(status), ptr(ws), ws.numel(), ev, st),
           "raht_scene_front")
     commit()
-    torch.cuda.current_stream(dev).synchronize()                      # the voxel count sizes everything that follows
-    head = pin[:24].numpy()
-    nvox = int(head[:8].view("int64")[0])
-    width_h, voxel_size_h = (float(x) for x in head[8:24].view("float64"))
-    keys = keys_all[:nvox]
-    # second leg
-    slot = (nvox * 4 + 64 + 7) // 8 * 8
-    entries = int(lib.raht_rlgr_sync_entries(nvox))
+    # Everything the second leg needs is allocated while the front runs, sized for nvox <= N: between the synchronisation
+    # below and the first kernel of the second leg the GPU idles, so that stretch holds nothing but the one host call.
+    slot = max((N * 4 + 64 + 7) // 8 * 8, int(min_slot))
     buf = torch.empty(D * slot, dtype=torch.uint8, device=dev)
     nbytes = torch.empty(D, dtype=torch.int64, device=dev)
-    index = torch.empty(D * entries, 2, dtype=torch.int32, device=dev)
-    packed = torch.empty(nvox, D, dtype=torch.float32, device=dev) if keep_packed else None
-    tree_bytes = lib.raht_scene_tree_workspace_bytes(nvox, tile_rows)
-    tree_ws = torch.empty(tree_bytes, dtype=torch.uint8, device=dev)
-    enc_bytes = lib.raht_scene_encode_workspace_bytes(nvox, D, tag, 0 if keep_packed else 1)
-    enc_ws = L.workspace_cached("scene_encode", enc_bytes, dev)
+    index_all = torch.empty(D * int(lib.raht_rlgr_sync_entries(N)), 2, dtype=torch.int32, device=dev)
+    packed_all = torch.empty(N, D, dtype=torch.float32, device=dev) if keep_packed else None
+    tree_ws = torch.empty(lib.raht_scene_tree_workspace_bytes(N, tile_rows), dtype=torch.uint8, device=dev)
+    enc_ws = L.workspace_cached("scene_encode", lib.raht_scene_encode_workspace_bytes(N, D, tag, 0 if keep_packed else 1), dev)
     layout = (C.c_int64 * 11)()
     plan = C.c_void_p()
     ev, commit = timer.handles(("merge", "raht_param", "raht", "quant_reorder", "rlgr_encode"))
-    check(lib.raht_scene_encode(ptr(idx32), ptr(offsets), nvox, ptr(means), ptr(quats), ptr(scales), ptr(opacities), ptr(colors), cd,
-                                ptr(keys), steps, tag, tile_rows, ptr(packed), ptr(buf), slot, ptr(nbytes), ptr(index), ptr(status),
-                                C.c_void_p(pin.data_ptr() + 64), C.byref(plan), layout, ptr(tree_ws), tree_ws.numel(), ptr(enc_ws),
-                                enc_ws.numel(), ev, st), "raht_scene_encode")
+    pin_enc = C.c_void_p(pin.data_ptr() + 64)
+    a = (ptr(idx32), ptr(offsets), ptr(means), ptr(quats), ptr(scales), ptr(opacities), ptr(colors), ptr(keys_all), ptr(packed_all),
+         ptr(buf), ptr(nbytes), ptr(index_all), ptr(status), ptr(tree_ws), tree_ws.numel(), ptr(enc_ws), enc_ws.numel())
+    torch.cuda.current_stream(dev).synchronize()                      # the voxel count sizes everything that follows
+    nvox = int(pin[:8].view(torch.int64)[0])
+    check(lib.raht_scene_encode(a[0], a[1], nvox, a[2], a[3], a[4], a[5], a[6], cd, a[7], steps, tag, tile_rows, a[8], a[9], slot, a[10],
+                                a[11], a[12], pin_enc, C.byref(plan), layout, a[13], a[14], a[15], a[16], ev, st), "raht_scene_encode")
     commit()
+    head = pin[:24].numpy()
+    width_h, voxel_size_h = (float(x) for x in head[8:24].view("float64"))
+    keys = keys_all[:nvox]
+    entries = int(lib.raht_rlgr_sync_entries(nvox))
+    index = index_all[:D * entries]
+    packed = packed_all[:nvox] if keep_packed else None
     tree = _tree_from_workspace(tree_ws, list(layout), nvox, tile_rows, plan)
-    torch.cuda.current_stream(dev).synchronize()                      # stream lengths and the status word
-    res = pin[64:64 + 8 * D + 4].numpy()
-    sizes = [int(x) for x in res[:8 * D].view("int64")]
-    bits = int(res[8 * D:8 * D + 4].view("int32")[0])
-    ops.raise_for_status(bits)
-    if bits & L.ST_STREAM_OVERFLOW:                                   # (more than 4 bytes per symbol: code the symbols again into wider slots)
-        lay = list(layout)
-        q = enc_ws[lay[8]:lay[8] + D * lay[9] * 4].view(torch.int32).reshape(D, lay[9])[:, :nvox]
-        streams = ops.rlgr_encode(q, 1, slot_bytes=(max(sizes) + 64 + 7) // 8 * 8)
+    streams = ops.RlgrStreams(buf, slot, nbytes, nvox, D, index)
+    enc = EncodedScene(J=J, n_in=N, nvox=nvox, D=D, step=step, vmin=params4[:3], voxel_size=voxel_size_h, width=width_h, keys=keys,
+                       streams=streams, transform_dtype=transform_dtype, tree=tree, packed=packed)
+    done = torch.cuda.Event()
+    done.record(torch.cuda.current_stream(dev))
+
+    def finish():
+        """stream lengths and the status word of this encode (published to `pin` by the call); a stream that outgrew its
+        slot (more than 4 bytes per symbol) is coded again into wider slots"""
+        done.synchronize()
+        res = pin[64:64 + 8 * D + 4].numpy()
+        sizes = [int(x) for x in res[:8 * D].view("int64")]
+        bits = int(res[8 * D:8 * D + 4].view("int32")[0])
+        ops.raise_for_status(bits)
+        if bits & L.ST_STREAM_OVERFLOW:
+            again = _encode_scene_calls(means, quats, scales, opacities, colors, J, step, transform_dtype, tile_rows, StageTimer(False),
+                                        keep_packed, given, None, (max(sizes) + 64 + 7) // 8 * 8)
+            enc.streams, enc.tree, enc.packed = again.streams, again.tree, again.packed
+        else:
+            streams._sizes = sizes
+
+    if checks is None:
+        finish()
     else:
-        streams = ops.RlgrStreams(buf, slot, nbytes, nvox, D, index)
-        streams._sizes = sizes
-    return EncodedScene(J=J, n_in=N, nvox=nvox, D=D, step=step, vmin=params4[:3], voxel_size=voxel_size_h, width=width_h, keys=keys,
-                        streams=streams, transform_dtype=transform_dtype, tree=tree, packed=packed)
+        checks.append(finish)
+    return enc
 
 
 @torch.no_grad()
-def _decode_scene_calls(enc, tile_rows, timer):
+def _decode_scene_calls(enc, tile_rows, timer, checks=None):
     """decode_scene through raht_scene_decode: one host call; the tree is rebuilt from the voxel keys."""
     import ctypes as C
     dev = enc.keys.device
@@ -439,8 +463,17 @@ def _decode_scene_calls(enc, tile_rows, timer):
                                 None, ptr(tree_ws), tree_ws.numel(), ptr(ws), ws.numel(), ev, stream()), "raht_scene_decode")
     commit()
     lib.raht_plan_destroy(plan)                                       # (host handle only; the kernels are queued with copies of it)
-    torch.cuda.current_stream(dev).synchronize()                      # the decoder's one synchronisation: were the keys a valid voxel list?
-    ops.raise_for_status(int(pin[64 + 8 * D + 8:64 + 8 * D + 12].numpy().view("int32")[0]))
+    done = torch.cuda.Event()
+    done.record(torch.cuda.current_stream(dev))
+
+    def finish():                                                     # the decoder's one synchronisation: were the keys a valid voxel list?
+        done.synchronize()
+        ops.raise_for_status(int(pin[64 + 8 * D + 8:64 + 8 * D + 12].numpy().view("int32")[0]))
+
+    if checks is None:
+        finish()
+    else:
+        checks.append(finish)
     return coords, Crec
 
 
@@ -456,11 +489,16 @@ def _plain_step(step):
 
 @torch.no_grad()
 def encode_scene(means, quats, scales, opacities, colors, J, step, transform_dtype=torch.float64, tile_rows=None,
-                 timer=None, flags=0, keep_packed=False, fused=False) -> EncodedScene:
+                 timer=None, flags=0, keep_packed=False, fused=False, checks=None) -> EncodedScene:
+    """checks: None -- the call returns when its status word and stream lengths have been read and checked (one more
+    synchronisation).  A list -- that last step is appended to it as a callable instead and the call returns with its
+    kernels queued: the caller runs the callables later (e.g. one scene behind), which raises what the call would have
+    raised and completes `streams.sizes()`; until then the GPU never waits for the host between encode and decode."""
     timer = timer or StageTimer(False)
     timer.mark("start")
     if not fused and not OVERLAP and flags == 0 and _plain_step(step) and means.shape[0] > 0:
-        return _encode_scene_calls(means, quats, scales, opacities, colors, J, step, transform_dtype, tile_rows, timer, keep_packed)
+        return _encode_scene_calls(means, quats, scales, opacities, colors, J, step, transform_dtype, tile_rows, timer, keep_packed,
+                                   checks=checks)
     status = ops._status_word(means.device)
     job = []
     on_keys = (lambda k: job.append(start_tree(k, status, tile_rows))) if OVERLAP else None
@@ -475,13 +513,13 @@ def encode_scene(means, quats, scales, opacities, colors, J, step, transform_dty
 
 
 @torch.no_grad()
-def decode_scene(enc: EncodedScene, reuse_tree=False, tile_rows=None, timer=None, flags=0, fused=False):
-    """Returns (voxel coordinates (nvox,3) fp32 integer-valued, attributes (nvox, D))."""
+def decode_scene(enc: EncodedScene, reuse_tree=False, tile_rows=None, timer=None, flags=0, fused=False, checks=None):
+    """Returns (voxel coordinates (nvox,3) fp32 integer-valued, attributes (nvox, D)).  checks: as in encode_scene."""
     timer = timer or StageTimer(False)
     timer.mark("start_dec")
     if (SCENE_CALLS and not fused and not OVERLAP and flags == 0 and not reuse_tree and enc.nvox > 0 and enc.streams.nch == enc.D
             and enc.streams.n == enc.nvox):
-        return _decode_scene_calls(enc, tile_rows, timer)
+        return _decode_scene_calls(enc, tile_rows, timer, checks)
     Crec = decode_attributes(enc.keys, enc.streams, enc.D, enc.step, enc.transform_dtype,
                              enc.tree if reuse_tree else None, tile_rows, timer, flags, fused)
     coords = torch.empty(enc.nvox, 3, dtype=torch.float32, device=enc.keys.device)

@@ -587,3 +587,32 @@ def test_scene_level_calls_match_the_operator_path(n, J, step, monkeypatch):
     _, rc = codec.decode_scene(b)                                              # streams of one path, decoder of the other
     assert torch.equal(rc, ra)
     assert torch.equal(codec.decode_scene(a, reuse_tree=True)[1], ra)
+
+
+def test_deferred_checks_give_the_same_scene_and_still_raise():
+    """encode_scene / decode_scene with checks=[...]: the calls return with their kernels queued, the callables do the
+    status / length read-back later (bench.py runs them one step behind).  Same streams and attributes as the waiting
+    calls; several scenes in flight do not disturb each other's results (ring of pinned result buffers); an invalid voxel
+    list handed to the decoder raises when its check runs, not silently never."""
+    from raht_b200 import codec
+    scenes = [[cu(a) for a in helpers.synthetic_gaussians(30000 + 7000 * k, 900 + k)] for k in range(4)]
+    eager = [codec.encode_scene(*s, J=10, step=1.0 / 16) for s in scenes]
+    eager_dec = [codec.decode_scene(e)[1] for e in eager]
+    checks, lazy, lazy_dec = [], [], []
+    for s in scenes:                                                            # four scenes queued before any check runs
+        e = codec.encode_scene(*s, J=10, step=1.0 / 16, checks=checks)
+        lazy.append(e)
+        lazy_dec.append(codec.decode_scene(e, checks=checks)[1])
+    assert len(checks) == 8 and all(e.streams._sizes is None for e in lazy)
+    for c in checks:
+        c()
+    for a, b, ra, rb in zip(eager, lazy, eager_dec, lazy_dec):
+        assert a.nvox == b.nvox and b.streams._sizes == a.streams.sizes() and a.streams.to_bytes() == b.streams.to_bytes()
+        assert torch.equal(a.keys, b.keys) and torch.equal(ra, rb)
+    bad = lazy[0]
+    bad.keys = torch.flip(bad.keys, [0]).contiguous()                           # not Morton-sorted any more
+    checks = []
+    codec.decode_scene(bad, checks=checks)
+    with pytest.raises(ValueError):
+        for c in checks:
+            c()
