@@ -385,6 +385,8 @@ def run_gpu(args):
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
     if world > 1:
+        from raht_b200 import sharded
+        sharded.tune_nccl_env()                            # point-to-point channels for the sharded sub-record's exchanges
         dist.init_process_group("nccl", device_id=dev)
     n, J, seed, desc = WORKLOADS[args.workload]
     if args.n:
@@ -815,6 +817,8 @@ def run_sharded(args):
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
     if world > 1:
+        from raht_b200 import sharded
+        sharded.tune_nccl_env()
         dist.init_process_group("nccl", device_id=dev)
 
     def barrier():
