@@ -133,7 +133,7 @@ __global__ void __launch_bounds__(OR_THREADS) order_scatter_kernel(const uint8_t
 }
 
 // ---- transform plan: one tile of one stage (plan.cuh) ------------------------------------------------
-constexpr int PB_THREADS = 256;
+constexpr int PB_THREADS = 128;
 constexpr int PB_WARPS = PB_THREADS / 32;
 
 // arrive[]: one counter per upper tile = how many of its child tiles have been planned

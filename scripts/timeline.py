@@ -8,9 +8,15 @@ from torch.profiler import profile, ProfilerActivity
 
 n = int(sys.argv[1]) if len(sys.argv) > 1 else 1_000_000
 scene = [torch.from_numpy(a).cuda() for a in synth.synthetic_gaussians(n, 2001)]
+pending = []
 def one():
-    enc = codec.encode_scene(*scene, J=12, step=1.0 / 64)
-    return codec.decode_scene(enc, reuse_tree=False)
+    mine = []
+    enc = codec.encode_scene(*scene, J=12, step=1.0 / 64, checks=mine)
+    r = codec.decode_scene(enc, reuse_tree=False, checks=mine)
+    for c in pending:
+        c()
+    pending[:] = mine
+    return r
 for _ in range(3):
     one()
 torch.cuda.synchronize()
