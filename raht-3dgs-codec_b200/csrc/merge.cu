@@ -122,8 +122,68 @@ __device__ __forceinline__ void merge_finish_group(const LaneChannel (&ch)[NS], 
     }
 }
 
+// The same for a group whose MG_UNROLL voxels all exist and have exactly ONE member (every group of a scene whose voxels
+// are finer than its Gaussians: 99.98 % of the voxels of the 1 M / 6 M bench scenes).  The arithmetic is the general
+// path's with its member loop run once -- 0 + w, 0 + x * w, the same divisions and selects -- so the results are
+// bit-identical; what goes away is the variable-trip loop, the per-voxel bounds shuffles, the kind tests of the slots
+// above the first (channels >= 32 are colours) and the divergence scaffolding around them: the general path executed
+// 170 warp instructions per voxel at 59 channels (profiles/r02_ncu_full_v1.txt: issue-bound at 68 %).
 template <typename OutT, int NS, bool SEP>
-__global__ void __launch_bounds__(32 * MG_WARPS)
+__device__ __forceinline__ void merge_finish_group_single(const LaneChannel (&ch)[NS], int64_t v0, const float (&x)[MG_UNROLL][NS], int OC,
+                                                          int color_dim, int by_opacity, float *__restrict__ m_means,
+                                                          float *__restrict__ m_quats, float *__restrict__ m_scales,
+                                                          float *__restrict__ m_opac, float *__restrict__ m_colors,
+                                                          OutT *__restrict__ packed)
+{
+    const int lane = threadIdx.x & 31;
+    const int kind0 = ch[0].kind;
+#pragma unroll
+    for (int u = 0; u < MG_UNROLL; ++u) {
+        const int64_t v = v0 + u;
+        const float o = __shfl_sync(~0u, x[u][0], 10);                   // the member's opacity
+        const float w = by_opacity ? o : 1.0f;                           // :42
+        const float wsum = __fadd_rn(0.f, w);
+        float acc[NS];
+        acc[0] = __fadd_rn(0.f, __fmul_rn(x[u][0], kind0 == CH_OPAC ? 1.0f : w));
+#pragma unroll
+        for (int k = 1; k < NS; ++k) acc[k] = __fadd_rn(0.f, __fmul_rn(x[u][k], w));
+        // quaternion norm from lanes 3..6 (:74-76)
+        const float q0 = __shfl_sync(~0u, acc[0], 3), q1 = __shfl_sync(~0u, acc[0], 4);
+        const float q2 = __shfl_sync(~0u, acc[0], 5), q3 = __shfl_sync(~0u, acc[0], 6);
+        const float qn = __fsqrt_rn(__fadd_rn(__fadd_rn(__fadd_rn(__fmul_rn(q0, q0), __fmul_rn(q1, q1)), __fmul_rn(q2, q2)),
+                                              __fmul_rn(q3, q3)));
+        const bool wpos = wsum > 0.0f;
+        OutT *prow = packed ? packed + v * OC : nullptr;
+        if (kind0 != CH_NONE) {                                          // slot 0: channels 0 .. 31, every kind
+            const float den = kind0 == CH_QUAT ? qn : ((kind0 == CH_MEAN && wsum == 0.0f) ? 1.0f : wsum);
+            float out = __fdiv_rn(acc[0], den);
+            if (kind0 == CH_QUAT && !(qn > 0.0f)) out = lane == 6 ? 1.0f : 0.0f;
+            if (kind0 == CH_COLOR && !wpos) out = 0.0f;
+            if (kind0 == CH_OPAC) out = fminf(acc[0], 1.0f);                                         // :94
+            if constexpr (SEP) {
+                const int c = lane;
+                if (c < 3) { if (m_means) m_means[v * 3 + c] = out; }
+                else if (c < 7) { if (m_quats) m_quats[v * 4 + (c - 3)] = out; }
+                else if (c < 10) { if (m_scales) m_scales[v * 3 + (c - 7)] = out; }
+                else if (c == 10) { if (m_opac) m_opac[v] = out; }
+                else { if (m_colors) m_colors[v * (int64_t)color_dim + (c - 11)] = out; }
+            }
+            if (prow) prow[lane] = (OutT)out;
+        }
+#pragma unroll
+        for (int k = 1; k < NS; ++k) {                                   // channels >= 32: colours (or nothing)
+            if (ch[k].kind == CH_NONE) continue;
+            const int c = 32 * k + lane;
+            float out = __fdiv_rn(acc[k], wsum);
+            if (!wpos) out = 0.0f;
+            if constexpr (SEP) { if (m_colors) m_colors[v * (int64_t)color_dim + (c - 11)] = out; }
+            if (prow) prow[c] = (OutT)out;
+        }
+    }
+}
+
+template <typename OutT, int NS, bool SEP>
+__global__ void __launch_bounds__(32 * MG_WARPS, NS <= 2 ? 4 : 1)
 merge_kernel(const int32_t *__restrict__ cidx, const int32_t *__restrict__ coff, int64_t nclu,
              const float *__restrict__ means, const float *__restrict__ quats, const float *__restrict__ scales,
              const float *__restrict__ opac, const float *__restrict__ colors, int color_dim, int by_opacity,
@@ -147,17 +207,28 @@ merge_kernel(const int32_t *__restrict__ cidx, const int32_t *__restrict__ coff,
         }
         const int gl = tl > sl ? cidx[sl] : -1;
         const int nv = (int)min((int64_t)32, nclu - vb);
+        // voxels of the block that exist and have exactly one member; a group of MG_UNROLL such voxels takes the lean path
+        const unsigned single = __ballot_sync(~0u, vb + lane < nclu && tl - sl == 1);
+        constexpr unsigned GROUP_MASK = (1u << MG_UNROLL) - 1u;
         float xa[MG_UNROLL][NS], xb[MG_UNROLL][NS];
         merge_load_group<NS>(ch, gl, 0, xa);
         for (int j0 = 0; j0 < nv; j0 += 2 * MG_UNROLL) {                 // warp-uniform
             const bool second = j0 + MG_UNROLL < nv;
             if (second) merge_load_group<NS>(ch, gl, j0 + MG_UNROLL, xb);
-            merge_finish_group<OutT, NS, SEP>(ch, cidx, sl, tl, j0, vb, nclu, xa, OC, color_dim, by_opacity, m_means, m_quats,
-                                              m_scales, m_opac, m_colors, packed);
+            if (((single >> j0) & GROUP_MASK) == GROUP_MASK)
+                merge_finish_group_single<OutT, NS, SEP>(ch, vb + j0, xa, OC, color_dim, by_opacity, m_means, m_quats, m_scales, m_opac,
+                                                         m_colors, packed);
+            else
+                merge_finish_group<OutT, NS, SEP>(ch, cidx, sl, tl, j0, vb, nclu, xa, OC, color_dim, by_opacity, m_means, m_quats,
+                                                  m_scales, m_opac, m_colors, packed);
             if (second) {
                 if (j0 + 2 * MG_UNROLL < nv) merge_load_group<NS>(ch, gl, j0 + 2 * MG_UNROLL, xa);
-                merge_finish_group<OutT, NS, SEP>(ch, cidx, sl, tl, j0 + MG_UNROLL, vb, nclu, xb, OC, color_dim, by_opacity, m_means,
-                                                  m_quats, m_scales, m_opac, m_colors, packed);
+                if (((single >> (j0 + MG_UNROLL)) & GROUP_MASK) == GROUP_MASK)
+                    merge_finish_group_single<OutT, NS, SEP>(ch, vb + j0 + MG_UNROLL, xb, OC, color_dim, by_opacity, m_means, m_quats,
+                                                             m_scales, m_opac, m_colors, packed);
+                else
+                    merge_finish_group<OutT, NS, SEP>(ch, cidx, sl, tl, j0 + MG_UNROLL, vb, nclu, xb, OC, color_dim, by_opacity, m_means,
+                                                      m_quats, m_scales, m_opac, m_colors, packed);
             }
         }
         // (requesting the next block's bounds and member indices a block ahead was measured: 73 registers, no gain)
