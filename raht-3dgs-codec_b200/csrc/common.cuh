@@ -115,16 +115,24 @@ __global__ void __launch_bounds__(SEL_THREADS) sel_count_kernel(int64_t n, Pred 
 }
 
 // exclusive scan of `m` counts in place by ONE block; total -> *total_out (and counts[m]).
+// A thread owns SCAN_IPT consecutive counts per sweep (8192 per sweep of the block): the 22-bucket x 489-block table of
+// order_RAGFT at 1 M rows is two sweeps (one count per thread and sweep made it eleven, four barriers each: 14 us).
+constexpr int SCAN_IPT = 8;
 static __global__ void __launch_bounds__(1024) scan_counts_kernel(unsigned long long *counts, int64_t m, int64_t *total_out)
 {
     __shared__ unsigned long long wtot[32];
     __shared__ unsigned long long carry;
     if (threadIdx.x == 0) carry = 0;
     __syncthreads();
-    for (int64_t base = 0; base < m; base += 1024) {
-        int64_t i = base + threadIdx.x;
-        unsigned long long v = (i < m) ? counts[i] : 0ull;
-        unsigned long long x = v;
+    for (int64_t base = 0; base < m; base += 1024 * SCAN_IPT) {
+        const int64_t i0 = base + (int64_t)threadIdx.x * SCAN_IPT;
+        unsigned long long v[SCAN_IPT], x = 0;
+#pragma unroll
+        for (int t = 0; t < SCAN_IPT; ++t) {
+            v[t] = (i0 + t < m) ? counts[i0 + t] : 0ull;
+            x += v[t];
+        }
+        const unsigned long long mine = x;
         for (int o = 1; o < 32; o <<= 1) {
             unsigned long long y = __shfl_up_sync(~0u, x, o);
             if ((int)lane_id() >= o) x += y;
@@ -141,10 +149,14 @@ static __global__ void __launch_bounds__(1024) scan_counts_kernel(unsigned long 
             wtot[threadIdx.x] = s - t;   // exclusive warp offsets
         }
         __syncthreads();
-        unsigned long long excl = carry + wtot[threadIdx.x >> 5] + (x - v);
-        if (i < m) counts[i] = excl;
+        unsigned long long excl = carry + wtot[threadIdx.x >> 5] + (x - mine);
+#pragma unroll
+        for (int t = 0; t < SCAN_IPT; ++t) {
+            if (i0 + t < m) counts[i0 + t] = excl;
+            excl += v[t];
+        }
         __syncthreads();
-        if (threadIdx.x == 1023) carry = excl + v;
+        if (threadIdx.x == 1023) carry = excl;
         __syncthreads();
     }
     if (threadIdx.x == 0) {

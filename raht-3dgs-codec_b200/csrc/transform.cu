@@ -116,6 +116,9 @@ __device__ __forceinline__ void stage0_tile(const PlanDev &P, int64_t tile, cons
     const int64_t base = tile * R;
 
     if (tid < (int)(sizeof(TileHdr) / 4)) ((uint32_t *)s_hdr)[tid] = ((const uint32_t *)(P.hdr + tile))[tid];
+    const bool patch = (B != nullptr) || QM == QM_FWD;       // (QM_FWD: the flags pick the rows that go to T)
+    if (patch)
+        for (int j = tid; j < R; j += TR_THREADS) s_flag[j] = 0;     // (ahead of the header barrier: the deferred list below sets them)
     __syncthreads();
     const int n_rows = s_hdr->n_rows;
     const int n_bf = s_hdr->n_bf;
@@ -154,10 +157,7 @@ __device__ __forceinline__ void stage0_tile(const PlanDev &P, int64_t tile, cons
         s_ab[2 * j] = (Tel)c.x;
         s_ab[2 * j + 1] = (Tel)c.y;
     }
-    const bool patch = (B != nullptr) || QM == QM_FWD;       // (QM_FWD: the flags pick the rows that go to T)
-    if (patch) {
-        for (int j = tid; j < n_rows; j += TR_THREADS) s_flag[j] = 0;
-        __syncthreads();
+    if (patch) {                                             // same round trip as the schedule (the flags were zeroed above)
         const int n_def = s_hdr->n_def;
         for (int j = tid; j < n_def; j += TR_THREADS) {
             const uint16_t dl = P.def_local[(size_t)tile * PLAN_DEFER_MAX + j];
@@ -358,6 +358,7 @@ __device__ __forceinline__ void upper_tile(const PlanDev &P, int stage, int64_t 
     const int tid = threadIdx.x;
     const int64_t gt = P.tile_base[stage] + tile;
     if (tid < (int)(sizeof(TileHdr) / 4)) ((uint32_t *)&s_hdr)[tid] = ((const uint32_t *)(P.hdr + gt))[tid];
+    for (int j = tid; j < PLAN_UP_CAP; j += TR_THREADS) s_flag[j] = 0;   // (ahead of the header barrier: the deferred list sets them)
     const int64_t c0 = tile * PLAN_FANIN;
     const int64_t cbase = P.tile_base[stage - 1];
     if (tid < 32) {                                          // entries per child tile: eight independent loads, one scan
@@ -380,20 +381,32 @@ __device__ __forceinline__ void upper_tile(const PlanDev &P, int stage, int64_t 
     // nothing scheduled: forward, every row stays as it is; the inverse still has to carry the tile's rows from T (or from
     // the parent's output) to C -- a forest root that became final in this tile is read from C by the child that deferred it
     if (n_bf == 0 && FWD) return;
-    for (int c = 0; c < PLAN_FANIN; ++c) {
-        const int cnt = s_off[c + 1] - s_off[c];
-        const size_t src = (size_t)(cbase + c0 + c) * PLAN_DEFER_MAX;
-        for (int j = tid; j < cnt; j += TR_THREADS) s_rowid[s_off[c] + j] = P.def_rows[src + j];
+    // the deferred lists of the children, one flat pass with every load of a thread in flight at once (a loop per child
+    // made eight dependent round trips of it: most of the ~10 us an upper tile takes whatever it holds)
+    {
+        constexpr int RB = (PLAN_UP_CAP + TR_THREADS - 1) / TR_THREADS;
+        uint32_t rid[RB];
+#pragma unroll
+        for (int u = 0; u < RB; ++u) {
+            const int j = tid + u * TR_THREADS;
+            if (j < n_rows) {
+                int c = 0;
+#pragma unroll
+                for (int k = 1; k < PLAN_FANIN; ++k) c += j >= s_off[k] ? 1 : 0;
+                rid[u] = P.def_rows[(size_t)(cbase + c0 + c) * PLAN_DEFER_MAX + (j - s_off[c])];
+            }
+        }
+#pragma unroll
+        for (int u = 0; u < RB; ++u)
+            if (tid + u * TR_THREADS < n_rows) s_rowid[tid + u * TR_THREADS] = rid[u];
     }
-    for (int j = tid; j < n_rows; j += TR_THREADS) s_flag[j] = 0;
     for (int j = tid; j < n_bf; j += TR_THREADS) {
         s_sched[j] = P.sched[bf_off + j];
         double2 c = P.ab[bf_off + j];
         s_ab[2 * j] = (Tel)c.x;
         s_ab[2 * j + 1] = (Tel)c.y;
     }
-    __syncthreads();
-    if (B) {
+    if (B) {                                                 // same round trip as the schedule (the flags were zeroed above)
         const int n_def = s_hdr.n_def;
         for (int j = tid; j < n_def; j += TR_THREADS) s_flag[P.def_local[(size_t)gt * PLAN_DEFER_MAX + j]] = 1;
     }

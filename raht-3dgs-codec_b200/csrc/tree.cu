@@ -191,12 +191,32 @@ __device__ __forceinline__ void plan_tile(const PlanDev &P, int stage, int64_t t
         }
         __syncthreads();
         n_rows = s_off[PLAN_FANIN];
-        for (int c = 0; c < PLAN_FANIN; ++c) {
-            const int cnt = s_off[c + 1] - s_off[c];
-            const size_t src = (size_t)(cbase + c0 + c) * PLAN_DEFER_MAX;
-            for (int j = tid; j < cnt; j += PB_THREADS) {
-                s_orig[s_off[c] + j] = __ldcg(P.def_rows + src + j);
-                s_lev[s_off[c] + j] = __ldcg(P.def_lev + src + j);
+        // the children's deferred lists in one flat pass, the loads of a batch in flight at once (a loop per child was eight
+        // dependent round trips); batches of 3 x 128 entries: typical upper tiles hold 70-150, and the registers of a
+        // deeper batch cost the stage-0 tiles of the same kernel their occupancy
+        constexpr int RB = 3;
+        for (int j0 = 0; j0 < n_rows; j0 += RB * PB_THREADS) {
+            uint32_t rid[RB];
+            uint8_t rlv[RB];
+#pragma unroll
+            for (int u = 0; u < RB; ++u) {
+                const int j = j0 + tid + u * PB_THREADS;
+                if (j < n_rows) {
+                    int c = 0;
+#pragma unroll
+                    for (int k = 1; k < PLAN_FANIN; ++k) c += j >= s_off[k] ? 1 : 0;
+                    const size_t src = (size_t)(cbase + c0 + c) * PLAN_DEFER_MAX + (j - s_off[c]);
+                    rid[u] = __ldcg(P.def_rows + src);
+                    rlv[u] = __ldcg(P.def_lev + src);
+                }
+            }
+#pragma unroll
+            for (int u = 0; u < RB; ++u) {
+                const int j = j0 + tid + u * PB_THREADS;
+                if (j < n_rows) {
+                    s_orig[j] = rid[u];
+                    s_lev[j] = rlv[u];
+                }
             }
         }
     }
