@@ -27,6 +27,7 @@
 #include "common.cuh"
 #include "rlgr_core.cuh"
 #include <stdlib.h>
+#include <mutex>
 
 namespace {
 
@@ -177,30 +178,40 @@ __global__ void __launch_bounds__(32 * K1_WARPS) rlgr_scatter_kernel(const int32
     uint32_t *bpos = blockpos + (size_t)ch * G.nsb;
     uint32_t e = evbase[(size_t)ch * G.nsb + blk0];
     int64_t last = blk0 ? (int64_t)lastnz[(size_t)ch * G.nsb + blk0 - 1] : -1;          // warp-uniform
-#pragma unroll 2
-    for (int b = 0; b < 32; ++b) {
-        const int64_t s0 = (blk0 + b) * SYM_BLOCK;
-        if (s0 >= G.n) break;
-        int32_t v[4];
+    // SC_BATCH blocks (4 KB of symbols per warp) are requested before the first is used: only the sparse channels come here,
+    // a few hundred warps on the whole GPU, and with two blocks in flight the pass was a chain of 16 round trips (44 us for
+    // 3 channels of 1 M symbols)
+    constexpr int SC_BATCH = 8;
+    for (int b0 = 0; b0 < 32; b0 += SC_BATCH) {
+        if ((blk0 + b0) * SYM_BLOCK >= G.n) break;
+        int32_t v[SC_BATCH][4];
 #pragma unroll
-        for (int w = 0; w < 4; ++w) {
-            const int64_t i = s0 + 32 * w + lane;
-            v[w] = i < G.n ? src[i] : 0;
+        for (int t = 0; t < SC_BATCH; ++t) {
+            const int64_t s0 = (blk0 + b0 + t) * SYM_BLOCK;
+#pragma unroll
+            for (int w = 0; w < 4; ++w) {
+                const int64_t i = s0 + 32 * w + lane;
+                v[t][w] = i < G.n ? __ldg(src + i) : 0;
+            }
         }
 #pragma unroll
-        for (int w = 0; w < 4; ++w) {
-            const unsigned m = __ballot_sync(~0u, v[w] != 0);
-            if (!m) continue;
-            const int64_t wbase = s0 + 32 * w;
-            if (v[w] != 0) {
-                const unsigned before = m & lanemask_lt();
-                const int64_t prev = before ? wbase + 31 - __clz((int)before) : last;
-                const int64_t pos = wbase + lane;
-                const uint32_t u = G.flag_signed ? s2u(v[w]) : (uint32_t)v[w];
-                store_event(evc, bpos, G.W, e + __popc(before), (uint32_t)(pos - prev - 1), u, (uint32_t)pos);
+        for (int t = 0; t < SC_BATCH; ++t) {
+            const int64_t s0 = (blk0 + b0 + t) * SYM_BLOCK;
+#pragma unroll
+            for (int w = 0; w < 4; ++w) {
+                const unsigned m = __ballot_sync(~0u, v[t][w] != 0);
+                if (!m) continue;
+                const int64_t wbase = s0 + 32 * w;
+                if (v[t][w] != 0) {
+                    const unsigned before = m & lanemask_lt();
+                    const int64_t prev = before ? wbase + 31 - __clz((int)before) : last;
+                    const int64_t pos = wbase + lane;
+                    const uint32_t u = G.flag_signed ? s2u(v[t][w]) : (uint32_t)v[t][w];
+                    store_event(evc, bpos, G.W, e + __popc(before), (uint32_t)(pos - prev - 1), u, (uint32_t)pos);
+                }
+                e += __popc(m);
+                last = wbase + 31 - __clz((int)m);
             }
-            e += __popc(m);
-            last = wbase + 31 - __clz((int)m);
         }
     }
 }
@@ -1636,6 +1647,31 @@ EncLayout enc_layout(int64_t n, int nch)
     return L;
 }
 
+// The table passes of the sparse channels (a few latency-bound warps) and the second speculation sweep (dense channels
+// only) touch disjoint records: they run side by side, the tables on a per-device side stream forked from and joined
+// back into the caller's stream by events (the pattern is legal under stream capture).  Created on first use, never
+// destroyed; the fork / join of a call is enqueued under a lock, so concurrent callers share the side stream safely.
+struct SideStream {
+    cudaStream_t s = nullptr;
+    cudaEvent_t fork = nullptr, join = nullptr;
+    bool ready = false;
+};
+std::mutex side_mutex;
+SideStream *side_stream_locked()
+{
+    static SideStream tab[64];
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return nullptr;
+    SideStream &S = tab[dev];
+    if (!S.ready) {
+        if (cudaStreamCreateWithFlags(&S.s, cudaStreamNonBlocking) != cudaSuccess) return nullptr;
+        if (cudaEventCreateWithFlags(&S.fork, cudaEventDisableTiming) != cudaSuccess) return nullptr;
+        if (cudaEventCreateWithFlags(&S.join, cudaEventDisableTiming) != cudaSuccess) return nullptr;
+        S.ready = true;
+    }
+    return &S;
+}
+
 }  // namespace
 
 RAHT_API int64_t raht_rlgr_sync_entries(int64_t n) { return n <= 0 ? 0 : (n + SYNC_RANGE - 1) >> SYNC_SHIFT; }
@@ -1692,10 +1728,28 @@ RAHT_API int raht_rlgr_encode(const int32_t *q, int64_t n, int64_t ld, int nch, 
     const dim3 cgrid((unsigned)((G.W + SPEC_WARPS - 1) / SPEC_WARPS), nch);
     const dim3 sgrid((unsigned)G.W, nch, 2);                 // z = 0: a sparse chunk per CTA; z = 1: 8 dense chunks per CTA (the rest exit)
     (raht_count_launches(1), rlgr_speculate_kernel)<<<sgrid, 32 * SOLVE_WARPS, 0, st>>>(G, info, ev, 0, nullptr, rec0, lanerec, stats);
-    (raht_count_launches(1), rlgr_speculate_kernel)<<<sgrid, 32 * SOLVE_WARPS, 0, st>>>(G, info, ev, 1, rec0, rec, lanerec, stats);
     const dim3 bgrid((unsigned)min((int64_t)192, (G.nsb + SPEC_WARPS - 1) / SPEC_WARPS), nch);    // grid-stride over the blocks
-    (raht_count_launches(1), rlgr_table_kernel)<<<bgrid, 32 * SPEC_WARPS, 0, st>>>(G, info, ev, rec, lanerec, tables, headers);
-    (raht_count_launches(1), rlgr_chunk_table_kernel)<<<cgrid, 32 * SPEC_WARPS, 0, st>>>(G, info, tables, headers, ctab);
+    static const int use_side = getenv("RAHT_RLGR_SIDE") ? atoi(getenv("RAHT_RLGR_SIDE")) : 1;      // 0: everything on the caller's stream (A/B)
+    bool forked = false;
+    if (use_side) {
+        // sweep 1 re-solves dense chunks only and copies the records of the sparse channels unchanged (rec0 -> rec), so the
+        // table passes read rec0 and may start as soon as sweep 0 is done
+        std::lock_guard<std::mutex> lock(side_mutex);
+        SideStream *S = side_stream_locked();
+        if (S && cudaEventRecord(S->fork, st) == cudaSuccess && cudaStreamWaitEvent(S->s, S->fork, 0) == cudaSuccess) {
+            (raht_count_launches(1), rlgr_table_kernel)<<<bgrid, 32 * SPEC_WARPS, 0, S->s>>>(G, info, ev, rec0, lanerec, tables, headers);
+            (raht_count_launches(1), rlgr_chunk_table_kernel)<<<cgrid, 32 * SPEC_WARPS, 0, S->s>>>(G, info, tables, headers, ctab);
+            RAHT_CUDA(cudaEventRecord(S->join, S->s));
+            (raht_count_launches(1), rlgr_speculate_kernel)<<<sgrid, 32 * SOLVE_WARPS, 0, st>>>(G, info, ev, 1, rec0, rec, lanerec, stats);
+            RAHT_CUDA(cudaStreamWaitEvent(st, S->join, 0));
+            forked = true;
+        }
+    }
+    if (!forked) {
+        (raht_count_launches(1), rlgr_speculate_kernel)<<<sgrid, 32 * SOLVE_WARPS, 0, st>>>(G, info, ev, 1, rec0, rec, lanerec, stats);
+        (raht_count_launches(1), rlgr_table_kernel)<<<bgrid, 32 * SPEC_WARPS, 0, st>>>(G, info, ev, rec, lanerec, tables, headers);
+        (raht_count_launches(1), rlgr_chunk_table_kernel)<<<cgrid, 32 * SPEC_WARPS, 0, st>>>(G, info, tables, headers, ctab);
+    }
     (raht_count_launches(1), rlgr_resolve_kernel)<<<nch, 32 * SOLVE_WARPS, 0, st>>>(G, info, ev, rec, lanerec, chunkoff, slot_bytes, nbytes,
                                                                     totals, status, stats, headers, ctab, cstart);
     (raht_count_launches(1), rlgr_table_lanes_kernel)<<<cgrid, 32 * SPEC_WARPS, 0, st>>>(G, info, tables, headers, cstart, lanerec);
