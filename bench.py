@@ -655,6 +655,9 @@ def run_gpu(args):
                    "l2": "inputs (236 MB per scene) and every intermediate exceed the 126 MB L2; no explicit flush",
                    "host_checks": "status words and stream lengths of every step are read one step behind (encode_scene / decode_scene checks=), "
                                   "all of them inside the timed region; the one synchronisation left inside a step is the voxel count",
+                   "overlap": "the tree build (levels, order, plan) runs on the library's side stream next to the merge (encoder) and next to "
+                              "the RLGR decode (decoder), RAHT_ENC_SIDE / RAHT_DEC_SIDE: in `stages`, raht_param / raht_param_dec are the part "
+                              "of the build that the other leg does not cover, and rlgr_decode holds both decoder legs",
                    "parallelism": "scene-per-GPU (no collective)" if world > 1 else "single GPU",
                    "decoder": "rebuilds the tree from the voxel keys (no encoder state reused); RLGR decode is chunk-parallel "
                               "through the encoder's sync index (side information next to the reference-format streams)"},

@@ -1,6 +1,8 @@
 // api.cu -- error reporting, version and device queries of libraht_b200.
 #include "common.cuh"
 #include <string.h>
+#include <stdlib.h>
+#include <mutex>
 
 static thread_local char g_err[512] = "";
 static long long g_launches = 0;
@@ -14,6 +16,62 @@ void raht_set_error(const char *fmt, ...)
     va_start(ap, fmt);
     vsnprintf(g_err, sizeof(g_err), fmt, ap);
     va_end(ap);
+}
+
+// ---- per-device side stream -------------------------------------------------------------------------------------------
+// Two legs of a call that touch disjoint data (the table passes of the sparse RLGR channels next to the second
+// speculation sweep; the decoder's tree next to its entropy decode) run side by side: raht_side_fork makes the device's
+// side stream wait for everything enqueued on `st` so far and returns it, raht_side_join makes `st` wait for everything
+// enqueued on the side stream so far.  Events only (legal under stream capture); stream and events are created on first
+// use and never destroyed.  Each function enqueues its record + wait pair under a lock, so host threads that share a
+// device share the side stream safely (at worst they wait for each other's side work).
+namespace {
+struct SideStream {
+    cudaStream_t s = nullptr;
+    cudaEvent_t fork = nullptr, join = nullptr;
+    bool ready = false;
+};
+std::mutex g_side_mutex;
+SideStream *side_locked()
+{
+    static SideStream tab[64];
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return nullptr;
+    SideStream &S = tab[dev];
+    if (!S.ready) {
+        // highest priority: the side legs are short, latency-bound kernels; their CTAs should take the slots the bulk kernel
+        // on the caller's stream frees instead of queueing behind its whole grid (RAHT_SIDE_PRIO=0: default priority)
+        int lo = 0, hi = 0;
+        static const int want_prio = getenv("RAHT_SIDE_PRIO") ? atoi(getenv("RAHT_SIDE_PRIO")) : 1;
+        if (cudaDeviceGetStreamPriorityRange(&lo, &hi) != cudaSuccess) { lo = hi = 0; (void)cudaGetLastError(); }
+        if (cudaStreamCreateWithPriority(&S.s, cudaStreamNonBlocking, want_prio ? hi : 0) != cudaSuccess) return nullptr;
+        if (cudaEventCreateWithFlags(&S.fork, cudaEventDisableTiming) != cudaSuccess) return nullptr;
+        if (cudaEventCreateWithFlags(&S.join, cudaEventDisableTiming) != cudaSuccess) return nullptr;
+        S.ready = true;
+    }
+    return &S;
+}
+}  // namespace
+
+cudaStream_t raht_side_fork(cudaStream_t st)
+{
+    std::lock_guard<std::mutex> lock(g_side_mutex);
+    SideStream *S = side_locked();
+    if (!S || cudaEventRecord(S->fork, st) != cudaSuccess || cudaStreamWaitEvent(S->s, S->fork, 0) != cudaSuccess) {
+        (void)cudaGetLastError();
+        return nullptr;
+    }
+    return S->s;
+}
+
+int raht_side_join(cudaStream_t st)
+{
+    std::lock_guard<std::mutex> lock(g_side_mutex);
+    SideStream *S = side_locked();
+    RAHT_REQUIRE(S != nullptr, "raht_side_join: no side stream on this device");
+    RAHT_CUDA(cudaEventRecord(S->join, S->s));
+    RAHT_CUDA(cudaStreamWaitEvent(st, S->join, 0));
+    return RAHT_OK;
 }
 
 RAHT_API int raht_abi_version(void) { return RAHT_B200_ABI_VERSION; }

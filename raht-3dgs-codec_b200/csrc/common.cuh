@@ -10,6 +10,8 @@
 
 void raht_set_error(const char *fmt, ...);
 void raht_count_launches(int n);   // bookkeeping for raht_launch_count() (bench.py reports it)
+cudaStream_t raht_side_fork(cudaStream_t st);   // api.cu: the device's side stream, waiting for what `st` holds so far (nullptr: unavailable)
+int raht_side_join(cudaStream_t st);             // `st` waits for what the side stream holds so far
 
 #define RAHT_REQUIRE(cond, ...)                                                                    \
     do {                                                                                           \
@@ -26,6 +28,12 @@ void raht_count_launches(int n);   // bookkeeping for raht_launch_count() (bench
             raht_set_error("%s:%d %s: %s", __FILE__, __LINE__, #call, cudaGetErrorString(e__));    \
             return RAHT_E_CUDA;                                                                    \
         }                                                                                          \
+    } while (0)
+
+#define RAHT_TRY(expr)                                                                             \
+    do {                                                                                           \
+        int rc_ = (expr);                                                                          \
+        if (rc_ != RAHT_OK) return rc_;                                                            \
     } while (0)
 
 #define RAHT_LAUNCH_CHECK()                                                                        \

@@ -27,7 +27,6 @@
 #include "common.cuh"
 #include "rlgr_core.cuh"
 #include <stdlib.h>
-#include <mutex>
 
 namespace {
 
@@ -1647,31 +1646,6 @@ EncLayout enc_layout(int64_t n, int nch)
     return L;
 }
 
-// The table passes of the sparse channels (a few latency-bound warps) and the second speculation sweep (dense channels
-// only) touch disjoint records: they run side by side, the tables on a per-device side stream forked from and joined
-// back into the caller's stream by events (the pattern is legal under stream capture).  Created on first use, never
-// destroyed; the fork / join of a call is enqueued under a lock, so concurrent callers share the side stream safely.
-struct SideStream {
-    cudaStream_t s = nullptr;
-    cudaEvent_t fork = nullptr, join = nullptr;
-    bool ready = false;
-};
-std::mutex side_mutex;
-SideStream *side_stream_locked()
-{
-    static SideStream tab[64];
-    int dev = 0;
-    if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return nullptr;
-    SideStream &S = tab[dev];
-    if (!S.ready) {
-        if (cudaStreamCreateWithFlags(&S.s, cudaStreamNonBlocking) != cudaSuccess) return nullptr;
-        if (cudaEventCreateWithFlags(&S.fork, cudaEventDisableTiming) != cudaSuccess) return nullptr;
-        if (cudaEventCreateWithFlags(&S.join, cudaEventDisableTiming) != cudaSuccess) return nullptr;
-        S.ready = true;
-    }
-    return &S;
-}
-
 }  // namespace
 
 RAHT_API int64_t raht_rlgr_sync_entries(int64_t n) { return n <= 0 ? 0 : (n + SYNC_RANGE - 1) >> SYNC_SHIFT; }
@@ -1732,16 +1706,15 @@ RAHT_API int raht_rlgr_encode(const int32_t *q, int64_t n, int64_t ld, int nch, 
     static const int use_side = getenv("RAHT_RLGR_SIDE") ? atoi(getenv("RAHT_RLGR_SIDE")) : 1;      // 0: everything on the caller's stream (A/B)
     bool forked = false;
     if (use_side) {
-        // sweep 1 re-solves dense chunks only and copies the records of the sparse channels unchanged (rec0 -> rec), so the
-        // table passes read rec0 and may start as soon as sweep 0 is done
-        std::lock_guard<std::mutex> lock(side_mutex);
-        SideStream *S = side_stream_locked();
-        if (S && cudaEventRecord(S->fork, st) == cudaSuccess && cudaStreamWaitEvent(S->s, S->fork, 0) == cudaSuccess) {
-            (raht_count_launches(1), rlgr_table_kernel)<<<bgrid, 32 * SPEC_WARPS, 0, S->s>>>(G, info, ev, rec0, lanerec, tables, headers);
-            (raht_count_launches(1), rlgr_chunk_table_kernel)<<<cgrid, 32 * SPEC_WARPS, 0, S->s>>>(G, info, tables, headers, ctab);
-            RAHT_CUDA(cudaEventRecord(S->join, S->s));
+        // The table passes of the sparse channels (a few latency-bound warps) and the second speculation sweep touch disjoint
+        // records -- sweep 1 re-solves dense chunks only and copies the records of the sparse channels unchanged (rec0 ->
+        // rec) -- so the tables read rec0 and run on the device's side stream next to the sweep.
+        cudaStream_t side = raht_side_fork(st);
+        if (side) {
+            (raht_count_launches(1), rlgr_table_kernel)<<<bgrid, 32 * SPEC_WARPS, 0, side>>>(G, info, ev, rec0, lanerec, tables, headers);
+            (raht_count_launches(1), rlgr_chunk_table_kernel)<<<cgrid, 32 * SPEC_WARPS, 0, side>>>(G, info, tables, headers, ctab);
             (raht_count_launches(1), rlgr_speculate_kernel)<<<sgrid, 32 * SOLVE_WARPS, 0, st>>>(G, info, ev, 1, rec0, rec, lanerec, stats);
-            RAHT_CUDA(cudaStreamWaitEvent(st, S->join, 0));
+            RAHT_TRY(raht_side_join(st));
             forked = true;
         }
     }
