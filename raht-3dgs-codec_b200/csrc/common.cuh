@@ -84,6 +84,30 @@ static inline int grid_for(int64_t work_items, int per_block, int ctas_per_sm)
     return (int)(need < cap ? need : cap);
 }
 
+// ---- programmatic dependent launch (PDL) ---------------------------------------------------------------------------------
+// A kernel launched with pdl_launch may start while the kernel before it in the stream is still running (once every CTA of
+// that kernel has executed pdl_trigger or exited): it runs its prologue -- loads of data that the predecessor does not
+// write -- and must execute pdl_wait before it touches anything the predecessor produces (the wait returns when the
+// predecessor grid has completed and its writes are visible).  Both instructions are no-ops in a plain launch.
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void pdl_trigger() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+
+template <typename... KArgs, typename... Args>
+static inline cudaError_t pdl_launch(void (*kern)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t st, Args... args)
+{
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = grid;
+    cfg.blockDim = block;
+    cfg.dynamicSmemBytes = smem;
+    cfg.stream = st;
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    at[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = at;
+    cfg.numAttrs = 1;
+    return cudaLaunchKernelEx(&cfg, kern, KArgs(args)...);
+}
+
 __device__ __forceinline__ unsigned lane_id() { return threadIdx.x & 31u; }
 __device__ __forceinline__ unsigned lanemask_lt()
 {

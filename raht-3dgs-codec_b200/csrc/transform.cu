@@ -132,6 +132,8 @@ __device__ __forceinline__ void stage0_tile(const PlanDev &P, int64_t tile, cons
         if constexpr (sizeof(Tin) == sizeof(Tel)) tma_in = QM != QM_INV && (((uintptr_t)(A + base * D)) % 16) == 0;
         tma_out = QM != QM_FWD && (((uintptr_t)(O + base * D)) % 16) == 0;
     }
+    // a programmatic dependent may read T ahead of its wait only through the bulk copy (L2); plain loads wait first
+    if constexpr (CHAIN == CHAIN_NONE && !FWD) { if (!tma_in) pdl_wait(); }
     if constexpr (QM != QM_NONE) {
         for (int c = tid; c < D; c += TR_THREADS) s_step[c] = Q.steps[c];
         for (int j = tid; j < n_rows; j += TR_THREADS) s_pos[j] = Q.pos[base + j];
@@ -184,6 +186,9 @@ __device__ __forceinline__ void stage0_tile(const PlanDev &P, int64_t tile, cons
             __syncthreads();
         }
     }
+    // (launched as a programmatic dependent of the last upper stage: header, schedule and the bulk load of T above ran under
+    // that kernel's tail; B and O are what it writes)
+    if constexpr (CHAIN == CHAIN_NONE) pdl_wait();
     if (n_patch) {
 #pragma unroll
         for (int u = 0; u < PF_ITEMS; ++u) {
@@ -328,6 +333,7 @@ __global__ void __launch_bounds__(TR_THREADS)
 transform_stage0_kernel(PlanDev P, const Tin *__restrict__ A, const Tel *B, Tel *O, int D_rt, int use_tma, QuantArgs Q)
 {
     extern __shared__ __align__(128) unsigned char tr_smem[];
+    pdl_trigger();                                           // the next stage's tiles may run their prologue under this kernel's tail
     stage0_tile<Tin, Tel, DT, FWD, QM, CHAIN_NONE>(P, (int64_t)blockIdx.x, A, B, O, D_rt, use_tma, Q, tr_smem, 0u);
 }
 
@@ -380,7 +386,12 @@ __device__ __forceinline__ void upper_tile(const PlanDev &P, int stage, int64_t 
     const size_t bf_off = s_hdr.bf_off;
     // nothing scheduled: forward, every row stays as it is; the inverse still has to carry the tile's rows from T (or from
     // the parent's output) to C -- a forest root that became final in this tile is read from C by the child that deferred it
-    if (n_bf == 0 && FWD) return;
+    // (a CTA that leaves early still waits: a dependent grid whose CTAs all returned at once would complete before the
+    // stage ahead of it, and the stage behind it -- which waits for THIS grid only -- would read rows that are not written yet)
+    if (n_bf == 0 && FWD) {
+        if constexpr (CHAIN == CHAIN_NONE) pdl_wait();
+        return;
+    }
     // the deferred lists of the children, one flat pass with every load of a thread in flight at once (a loop per child
     // made eight dependent round trips of it: most of the ~10 us an upper tile takes whatever it holds)
     {
@@ -413,6 +424,8 @@ __device__ __forceinline__ void upper_tile(const PlanDev &P, int stage, int64_t 
     __syncthreads();
 
     using AR = Arith<Tel>;
+    // everything above read the plan only; the rows are what the stage before wrote (programmatic dependent launch)
+    if constexpr (CHAIN == CHAIN_NONE) pdl_wait();
     if (cb >= ce) return;
     int DS = up_elems / n_rows;
     if (DS > ce - cb) DS = ce - cb;
@@ -474,6 +487,7 @@ __global__ void __launch_bounds__(TR_THREADS)
 transform_upper_kernel(PlanDev P, int stage, const Tel *A, const Tel *B, Tel *O, int D, int up_elems)
 {
     extern __shared__ __align__(128) unsigned char tr_smem[];
+    pdl_trigger();
     const int per = (D + (int)gridDim.y - 1) / (int)gridDim.y;            // channels of this CTA's group
     const int cb = (int)blockIdx.y * per, ce = min(D, cb + per);
     upper_tile<Tel, FWD, CHAIN_NONE>(P, stage, (int64_t)blockIdx.x, A, B, O, D, up_elems, cb, ce, tr_smem);
@@ -676,7 +690,13 @@ int launch_stage0(const raht_plan *P, const Tin *A, const Tel *B, Tel *O, int D,
         return RAHT_E_INVALID;
     }
     RAHT_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)L.total));
-    (raht_count_launches(1), kern)<<<(unsigned)P->d.tiles[0], TR_THREADS, L.total, st>>>(P->d, A, B, O, D, use_tma, QuantArgs());
+    raht_count_launches(1);
+    static const int use_pdl = getenv("RAHT_PDL") ? atoi(getenv("RAHT_PDL")) : 1;
+    // the inverse's stage 0 follows the upper stages: as their programmatic dependent its tiles load header, schedule and T
+    // rows before the last upper stage has finished (B != nullptr marks that launch)
+    if (use_pdl && !FWD && B != nullptr)
+        RAHT_CUDA(pdl_launch(kern, dim3((unsigned)P->d.tiles[0]), dim3(TR_THREADS), L.total, st, P->d, A, B, O, D, use_tma, QuantArgs()));
+    else kern<<<(unsigned)P->d.tiles[0], TR_THREADS, L.total, st>>>(P->d, A, B, O, D, use_tma, QuantArgs());
     RAHT_LAUNCH_CHECK();
     return RAHT_OK;
 }
@@ -716,7 +736,10 @@ int launch_upper(const raht_plan *P, int k, const Tel *A, const Tel *B, Tel *O, 
     if (up_elems < PLAN_UP_CAP) up_elems = PLAN_UP_CAP;                // one channel of the largest tile must fit
     const size_t smem = (size_t)(up_elems + 2 * PLAN_UP_CAP) * sizeof(Tel) + (size_t)PLAN_UP_CAP * 9 + 16;
     RAHT_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(UP_ELEMS + 2 * PLAN_UP_CAP) * (int)sizeof(Tel) + PLAN_UP_CAP * 9 + 16));
-    (raht_count_launches(1), kern)<<<dim3((unsigned)tiles, (unsigned)groups), TR_THREADS, smem, st>>>(P->d, k, A, B, O, D, up_elems);
+    raht_count_launches(1);
+    static const int use_pdl = getenv("RAHT_PDL") ? atoi(getenv("RAHT_PDL")) : 1;     // 0: plain launches (A/B)
+    if (use_pdl) RAHT_CUDA(pdl_launch(kern, dim3((unsigned)tiles, (unsigned)groups), dim3(TR_THREADS), smem, st, P->d, k, A, B, O, D, up_elems));
+    else kern<<<dim3((unsigned)tiles, (unsigned)groups), TR_THREADS, smem, st>>>(P->d, k, A, B, O, D, up_elems);
     RAHT_LAUNCH_CHECK();
     return RAHT_OK;
 }
