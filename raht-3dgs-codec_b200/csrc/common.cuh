@@ -3,6 +3,7 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 #include <stdio.h>
+#include <stdlib.h>
 #include <stdarg.h>
 #include "../../include/raht_b200.h"
 
@@ -108,6 +109,26 @@ static inline cudaError_t pdl_launch(void (*kern)(KArgs...), dim3 grid, dim3 blo
     return cudaLaunchKernelEx(&cfg, kern, KArgs(args)...);
 }
 
+// Launch-gap hiding for chains of short dependent kernels: a kernel whose first statement is pdl_enter() (trigger, then
+// wait) and that is launched with RAHT_PDL_LAUNCH becomes resident while the kernel before it in the stream drains and
+// starts the moment that one completes.  Semantics are those of a plain launch (nothing runs ahead of the wait).  Only
+// behind another KERNEL of the same stream: after a memset, a copy or an event the site uses a plain launch.
+__device__ __forceinline__ void pdl_enter() { pdl_trigger(); pdl_wait(); }
+// RAHT_PDL: bit mask of the launch groups that use it (A/B): 1 transform stages, 2 front leg (keys, sort, voxel boundaries),
+// 4 tree build, 8 RLGR encoder, 16 quantisation.
+enum { PDL_TRANSFORM = 1, PDL_FRONT = 2, PDL_TREE = 4, PDL_RLGR = 8, PDL_QUANT = 16, PDL_DEFAULT = 1 | 2 | 16 };
+static inline bool raht_use_pdl(int group)
+{
+    static const int v = getenv("RAHT_PDL") ? atoi(getenv("RAHT_PDL")) : PDL_DEFAULT;
+    return (v & group) != 0;
+}
+#define RAHT_PDL_LAUNCH(group, kern, grid, block, smem, st, ...)                                   \
+    do {                                                                                           \
+        raht_count_launches(1);                                                                    \
+        if (raht_use_pdl(group)) RAHT_CUDA(pdl_launch(kern, dim3(grid), dim3(block), (size_t)(smem), st, __VA_ARGS__)); \
+        else kern<<<grid, block, smem, st>>>(__VA_ARGS__);                                         \
+    } while (0)
+
 __device__ __forceinline__ unsigned lane_id() { return threadIdx.x & 31u; }
 __device__ __forceinline__ unsigned lanemask_lt()
 {
@@ -128,6 +149,7 @@ static inline size_t sel_workspace_bytes(int64_t n) { return align_up((sel_num_b
 template <typename Pred>
 __global__ void __launch_bounds__(SEL_THREADS) sel_count_kernel(int64_t n, Pred pred, unsigned long long *block_counts)
 {
+    pdl_enter();
     int64_t base = (int64_t)blockIdx.x * SEL_TILE;
     int cnt = 0;
 #pragma unroll
@@ -154,6 +176,7 @@ static __global__ void __launch_bounds__(1024) scan_counts_kernel(unsigned long 
 {
     __shared__ unsigned long long wtot[32];
     __shared__ unsigned long long carry;
+    pdl_enter();
     if (threadIdx.x == 0) carry = 0;
     __syncthreads();
     for (int64_t base = 0; base < m; base += 1024 * SCAN_IPT) {
@@ -201,6 +224,7 @@ template <typename Pred, typename Emit>
 __global__ void __launch_bounds__(SEL_THREADS) sel_scatter_kernel(int64_t n, Pred pred, Emit emit,
                                                                  const unsigned long long *block_offsets)
 {
+    pdl_enter();
     int64_t base = (int64_t)blockIdx.x * SEL_TILE;
     __shared__ int wsum[SEL_THREADS / 32];
     __shared__ int running;
@@ -240,9 +264,11 @@ static inline int device_select(int64_t n, Pred pred, Emit emit, int64_t *count_
         (raht_count_launches(1), scan_counts_kernel)<<<1, 1024, 0, st>>>(counts, 0, count_out);
         return 0;
     }
-    sel_count_kernel<<<(unsigned)nb, SEL_THREADS, 0, st>>>(n, pred, counts);
-    (raht_count_launches(1), scan_counts_kernel)<<<1, 1024, 0, st>>>(counts, nb, count_out);
-    sel_scatter_kernel<<<(unsigned)nb, SEL_THREADS, 0, st>>>(n, pred, emit, counts);
+    RAHT_PDL_LAUNCH(PDL_FRONT, (sel_count_kernel<Pred>), (unsigned)nb, SEL_THREADS, 0, st, n, pred, counts);
+    raht_count_launches(-1);
+    RAHT_PDL_LAUNCH(PDL_FRONT, scan_counts_kernel, 1, 1024, 0, st, counts, nb, count_out);
+    RAHT_PDL_LAUNCH(PDL_FRONT, (sel_scatter_kernel<Pred, Emit>), (unsigned)nb, SEL_THREADS, 0, st, n, pred, emit, (const unsigned long long *)counts);
+    raht_count_launches(-1);                                 // (count and scatter were counted above)
     return 0;
 }
 

@@ -35,6 +35,7 @@ quant_reorder_kernel(const Tel *__restrict__ T, int64_t n, int D, const int64_t 
                      const double *__restrict__ steps, int32_t *__restrict__ q, int64_t ld, int32_t *status)
 {
     extern __shared__ __align__(16) unsigned char qr_smem[];
+    pdl_enter();
     int32_t *s_q = (int32_t *)qr_smem;                       // [D][QR_PITCH]
     double *s_step = (double *)(s_q + (size_t)D * QR_PITCH + ((D * QR_PITCH) & 1));
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -256,7 +257,8 @@ static int quant_reorder_launch(const Tel *T, int64_t n, int D, const int64_t *o
     unsigned grid = (unsigned)((n + QR_P - 1) / QR_P);
     auto kern = D <= 32 ? quant_reorder_kernel<Tel, 1, RECIP> : D <= 64 ? quant_reorder_kernel<Tel, 2, RECIP> : quant_reorder_kernel<Tel, 0, RECIP>;
     RAHT_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    kern<<<grid, QR_THREADS, smem, st>>>(T, n, D, order, steps, q, ld, status);
+    if (raht_use_pdl(PDL_QUANT)) RAHT_CUDA(pdl_launch(kern, dim3(grid), dim3(QR_THREADS), smem, st, T, n, D, order, steps, q, ld, status));
+    else kern<<<grid, QR_THREADS, smem, st>>>(T, n, D, order, steps, q, ld, status);
     return RAHT_OK;
 }
 

@@ -29,6 +29,7 @@ __global__ void __launch_bounds__(RS_THREADS) rs_hist_kernel(const uint64_t *__r
                                                              int passes, int end_bit, unsigned long long *ghist)
 {
     __shared__ unsigned int sh[RS_MAX_PASSES * RS_RADIX];
+    pdl_trigger();
     for (int i = threadIdx.x; i < passes * RS_RADIX; i += RS_THREADS) sh[i] = 0;
     __syncthreads();
     for (int64_t i = (int64_t)blockIdx.x * RS_THREADS + threadIdx.x; i < n; i += (int64_t)gridDim.x * RS_THREADS) {
@@ -49,6 +50,7 @@ __global__ void __launch_bounds__(RS_THREADS) rs_hist_kernel(const uint64_t *__r
 __global__ void __launch_bounds__(RS_RADIX) rs_scan_kernel(unsigned long long *ghist)
 {
     __shared__ unsigned long long wt[RS_RADIX / 32];
+    pdl_enter();
     unsigned long long *h = ghist + (size_t)blockIdx.x * RS_RADIX;
     unsigned long long v = h[threadIdx.x], x = v;
     for (int o = 1; o < 32; o <<= 1) {
@@ -70,6 +72,7 @@ rs_onesweep_kernel(const uint64_t *__restrict__ keys_in, uint64_t *__restrict__ 
                    volatile uint32_t *tile_state,                                            // n_tiles x 256, zeroed
                    unsigned int *ticket, int32_t *status)
 {
+    pdl_enter();
     __shared__ uint64_t s_keys[RS_TILE];
     __shared__ uint32_t s_vals[RS_TILE];
     __shared__ uint32_t s_whist[RS_WARPS][RS_RADIX];
@@ -256,7 +259,7 @@ RAHT_API int raht_radix_sort_pairs(const uint64_t *keys_in, uint64_t *keys_out, 
     // zero histograms, tickets (one per pass) and tile states in one memset
     RAHT_CUDA(cudaMemsetAsync(ws, 0, L.off_keys, st));
     (raht_count_launches(1), rs_hist_kernel)<<<grid_for(n, RS_THREADS * 8, 4), RS_THREADS, 0, st>>>(keys_in, n, begin_bit, L.passes, end_bit, ghist);
-    (raht_count_launches(1), rs_scan_kernel)<<<L.passes, RS_RADIX, 0, st>>>(ghist);
+    RAHT_PDL_LAUNCH(PDL_FRONT, rs_scan_kernel, L.passes, RS_RADIX, 0, st, ghist);
     RAHT_LAUNCH_CHECK();
 
     // ping-pong so that the last pass lands in keys_out / vals_out
@@ -268,9 +271,9 @@ RAHT_API int raht_radix_sort_pairs(const uint64_t *keys_in, uint64_t *keys_out, 
         uint32_t *dst_v = to_out ? vals_out : tmp_vals;
         int sh = begin_bit + p * RS_BITS;
         int nb = end_bit - sh < RS_BITS ? end_bit - sh : RS_BITS;
-        (raht_count_launches(1), rs_onesweep_kernel)<<<(unsigned)L.tiles, RS_THREADS, 0, st>>>(
-            src_k, dst_k, src_v, dst_v, n, sh, (1u << nb) - 1u, ghist + (size_t)p * RS_RADIX,
-            state + (size_t)p * (size_t)L.tiles * RS_RADIX, ticket + p, status);
+        RAHT_PDL_LAUNCH(PDL_FRONT, rs_onesweep_kernel, (unsigned)L.tiles, RS_THREADS, 0, st, src_k, dst_k, src_v, dst_v, n, sh, (1u << nb) - 1u,
+                        (const unsigned long long *)(ghist + (size_t)p * RS_RADIX),
+                        (volatile uint32_t *)(state + (size_t)p * (size_t)L.tiles * RS_RADIX), ticket + p, status);
         RAHT_LAUNCH_CHECK();
         src_k = dst_k;
         src_v = dst_v;

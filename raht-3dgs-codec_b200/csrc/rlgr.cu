@@ -63,6 +63,7 @@ constexpr int K1_WARPS = 8;
 __global__ void __launch_bounds__(32 * K1_WARPS) rlgr_count_kernel(const int32_t *__restrict__ q, Geometry G,
                                                                   uint32_t *__restrict__ cnt, int32_t *__restrict__ lastnz)
 {
+    pdl_trigger();
     const int lane = threadIdx.x & 31;
     const int64_t group = (int64_t)blockIdx.x * K1_WARPS + (threadIdx.x >> 5);      // 32 symbol blocks per warp
     const int ch = blockIdx.y;
@@ -102,6 +103,7 @@ __global__ void __launch_bounds__(32 * K1_WARPS) rlgr_count_kernel(const int32_t
 __global__ void __launch_bounds__(1024) rlgr_scan_kernel(Geometry G, uint32_t *__restrict__ cnt, int32_t *__restrict__ lastnz,
                                                          ChanInfo *__restrict__ info)
 {
+    pdl_enter();
     __shared__ int32_t wmax[32];
     __shared__ uint32_t wsum[32];
     __shared__ int32_t carry_max;
@@ -167,6 +169,7 @@ __global__ void __launch_bounds__(32 * K1_WARPS) rlgr_scatter_kernel(const int32
                                                                     const int32_t *__restrict__ lastnz, uint2 *__restrict__ ev,
                                                                     uint32_t *__restrict__ blockpos, const ChanInfo *__restrict__ info)
 {
+    pdl_enter();
     const int lane = threadIdx.x & 31;
     const int64_t group = (int64_t)blockIdx.x * K1_WARPS + (threadIdx.x >> 5);
     const int ch = blockIdx.y;
@@ -791,6 +794,7 @@ __global__ void __launch_bounds__(32 * SOLVE_WARPS, 4) rlgr_speculate_kernel(Geo
                                                                          const uint4 *__restrict__ rec_prev, uint4 *__restrict__ rec,
                                                                          uint4 *__restrict__ lanerec, unsigned long long *stats)
 {
+    pdl_enter();
     __shared__ Helpers helpers;
     if (blockIdx.z == 0) speculate_chunk<8>(G, info, ev, sweep, rec_prev, rec, lanerec, stats, &helpers);
     else speculate_chunk<1>(G, info, ev, sweep, rec_prev, rec, lanerec, stats, nullptr);
@@ -866,6 +870,7 @@ __global__ void __launch_bounds__(32 * SPEC_WARPS) rlgr_table_kernel(Geometry G,
                                                                     const uint4 *__restrict__ lanerec,
                                                                     uint32_t *__restrict__ tables, uint32_t *__restrict__ headers)
 {
+    pdl_trigger();
     const int ch = blockIdx.y;
     const int lane = threadIdx.x & 31;
     const ChanInfo I = info[ch];
@@ -910,6 +915,7 @@ __global__ void __launch_bounds__(32 * SPEC_WARPS) rlgr_chunk_table_kernel(Geome
                                                                           const uint32_t *__restrict__ headers,
                                                                           uint2 *__restrict__ ctab)
 {
+    pdl_enter();
     const int ch = blockIdx.y;
     const int64_t w = (int64_t)blockIdx.x * SPEC_WARPS + (threadIdx.x >> 5);
     const int lane = threadIdx.x & 31;
@@ -946,6 +952,7 @@ __global__ void __launch_bounds__(32 * SPEC_WARPS) rlgr_table_lanes_kernel(Geome
                                                                           const uint32_t *__restrict__ headers,
                                                                           const uint32_t *__restrict__ cstart, uint4 *__restrict__ lanerec)
 {
+    pdl_enter();
     const int ch = blockIdx.y;
     const int64_t w = (int64_t)blockIdx.x * SPEC_WARPS + (threadIdx.x >> 5);
     const int lane = threadIdx.x & 31;
@@ -1078,6 +1085,7 @@ __global__ void __launch_bounds__(32 * SOLVE_WARPS) rlgr_resolve_kernel(Geometry
                                                           unsigned long long *stats, const uint32_t *__restrict__ headers,
                                                           const uint2 *__restrict__ ctab, uint32_t *__restrict__ cstart)
 {
+    pdl_trigger();
     const int ch = blockIdx.x;
     const int lane = threadIdx.x & 31;
     const ChanInfo I = info[ch];
@@ -1181,6 +1189,7 @@ __global__ void __launch_bounds__(32 * SOLVE_WARPS) rlgr_resolve_kernel(Geometry
 __global__ void __launch_bounds__(256) rlgr_zero_kernel(uint8_t *__restrict__ streams, int64_t slot_bytes,
                                                         const unsigned long long *__restrict__ totals)
 {
+    pdl_enter();
     const int ch = blockIdx.y;
     unsigned long long words = (totals[ch] + 63) >> 6;
     const unsigned long long cap = (unsigned long long)slot_bytes >> 3;
@@ -1247,6 +1256,7 @@ __global__ void __launch_bounds__(32 * SPEC_WARPS) rlgr_emit_kernel(Geometry G, 
                                                                    uint2 *__restrict__ sync_index, int64_t sync_entries,
                                                                    int32_t *status)
 {
+    pdl_enter();
     const int ch = blockIdx.y;
     const int64_t w = (int64_t)blockIdx.x * SPEC_WARPS + (threadIdx.x >> 5);
     const int lane = threadIdx.x & 31;
@@ -1697,11 +1707,13 @@ RAHT_API int raht_rlgr_encode(const int32_t *q, int64_t n, int64_t ld, int nch, 
 
     const unsigned groups = (unsigned)((G.nsb + 32 * K1_WARPS - 1) / (32 * K1_WARPS));
     (raht_count_launches(1), rlgr_count_kernel)<<<dim3(groups, nch), 32 * K1_WARPS, 0, st>>>(q, G, cnt, lastnz);
-    (raht_count_launches(1), rlgr_scan_kernel)<<<nch, 1024, 0, st>>>(G, cnt, lastnz, info);
-    (raht_count_launches(1), rlgr_scatter_kernel)<<<dim3(groups, nch), 32 * K1_WARPS, 0, st>>>(q, G, cnt, lastnz, ev, blockpos, info);
+    RAHT_PDL_LAUNCH(PDL_RLGR, rlgr_scan_kernel, nch, 1024, 0, st, G, cnt, lastnz, info);
+    RAHT_PDL_LAUNCH(PDL_RLGR, rlgr_scatter_kernel, dim3(groups, nch), 32 * K1_WARPS, 0, st, q, G, (const uint32_t *)cnt, (const int32_t *)lastnz, ev, blockpos,
+                    (const ChanInfo *)info);
     const dim3 cgrid((unsigned)((G.W + SPEC_WARPS - 1) / SPEC_WARPS), nch);
     const dim3 sgrid((unsigned)G.W, nch, 2);                 // z = 0: a sparse chunk per CTA; z = 1: 8 dense chunks per CTA (the rest exit)
-    (raht_count_launches(1), rlgr_speculate_kernel)<<<sgrid, 32 * SOLVE_WARPS, 0, st>>>(G, info, ev, 0, nullptr, rec0, lanerec, stats);
+    RAHT_PDL_LAUNCH(PDL_RLGR, rlgr_speculate_kernel, sgrid, 32 * SOLVE_WARPS, 0, st, G, (const ChanInfo *)info, (const uint2 *)ev, 0, (const uint4 *)nullptr, rec0,
+                    lanerec, stats);
     const dim3 bgrid((unsigned)min((int64_t)192, (G.nsb + SPEC_WARPS - 1) / SPEC_WARPS), nch);    // grid-stride over the blocks
     static const int use_side = getenv("RAHT_RLGR_SIDE") ? atoi(getenv("RAHT_RLGR_SIDE")) : 1;      // 0: everything on the caller's stream (A/B)
     bool forked = false;
@@ -1712,7 +1724,8 @@ RAHT_API int raht_rlgr_encode(const int32_t *q, int64_t n, int64_t ld, int nch, 
         cudaStream_t side = raht_side_fork(st);
         if (side) {
             (raht_count_launches(1), rlgr_table_kernel)<<<bgrid, 32 * SPEC_WARPS, 0, side>>>(G, info, ev, rec0, lanerec, tables, headers);
-            (raht_count_launches(1), rlgr_chunk_table_kernel)<<<cgrid, 32 * SPEC_WARPS, 0, side>>>(G, info, tables, headers, ctab);
+            RAHT_PDL_LAUNCH(PDL_RLGR, rlgr_chunk_table_kernel, cgrid, 32 * SPEC_WARPS, 0, side, G, (const ChanInfo *)info, (const uint32_t *)tables,
+                            (const uint32_t *)headers, ctab);
             (raht_count_launches(1), rlgr_speculate_kernel)<<<sgrid, 32 * SOLVE_WARPS, 0, st>>>(G, info, ev, 1, rec0, rec, lanerec, stats);
             RAHT_TRY(raht_side_join(st));
             forked = true;
@@ -1725,10 +1738,11 @@ RAHT_API int raht_rlgr_encode(const int32_t *q, int64_t n, int64_t ld, int nch, 
     }
     (raht_count_launches(1), rlgr_resolve_kernel)<<<nch, 32 * SOLVE_WARPS, 0, st>>>(G, info, ev, rec, lanerec, chunkoff, slot_bytes, nbytes,
                                                                     totals, status, stats, headers, ctab, cstart);
-    (raht_count_launches(1), rlgr_table_lanes_kernel)<<<cgrid, 32 * SPEC_WARPS, 0, st>>>(G, info, tables, headers, cstart, lanerec);
-    (raht_count_launches(1), rlgr_zero_kernel)<<<dim3(64, nch), 256, 0, st>>>(streams, slot_bytes, totals);
-    (raht_count_launches(1), rlgr_emit_kernel)<<<cgrid, 32 * SPEC_WARPS, 0, st>>>(G, info, ev, blockpos, lanerec, chunkoff, streams,
-                                                                                 slot_bytes, (uint2 *)sync_index, entries, status);
+    RAHT_PDL_LAUNCH(PDL_RLGR, rlgr_table_lanes_kernel, cgrid, 32 * SPEC_WARPS, 0, st, G, (const ChanInfo *)info, (const uint32_t *)tables, (const uint32_t *)headers,
+                    (const uint32_t *)cstart, lanerec);
+    RAHT_PDL_LAUNCH(PDL_RLGR, rlgr_zero_kernel, dim3(64, nch), 256, 0, st, streams, slot_bytes, (const unsigned long long *)totals);
+    RAHT_PDL_LAUNCH(PDL_RLGR, rlgr_emit_kernel, cgrid, 32 * SPEC_WARPS, 0, st, G, (const ChanInfo *)info, (const uint2 *)ev, (const uint32_t *)blockpos,
+                    (const uint4 *)lanerec, (const unsigned long long *)chunkoff, streams, slot_bytes, (uint2 *)sync_index, entries, status);
     RAHT_LAUNCH_CHECK();
     return RAHT_OK;
 }

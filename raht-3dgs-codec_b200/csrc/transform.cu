@@ -691,7 +691,7 @@ int launch_stage0(const raht_plan *P, const Tin *A, const Tel *B, Tel *O, int D,
     }
     RAHT_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)L.total));
     raht_count_launches(1);
-    static const int use_pdl = getenv("RAHT_PDL") ? atoi(getenv("RAHT_PDL")) : 1;
+    const bool use_pdl = raht_use_pdl(PDL_TRANSFORM);
     // the inverse's stage 0 follows the upper stages: as their programmatic dependent its tiles load header, schedule and T
     // rows before the last upper stage has finished (B != nullptr marks that launch)
     if (use_pdl && !FWD && B != nullptr)
@@ -737,7 +737,7 @@ int launch_upper(const raht_plan *P, int k, const Tel *A, const Tel *B, Tel *O, 
     const size_t smem = (size_t)(up_elems + 2 * PLAN_UP_CAP) * sizeof(Tel) + (size_t)PLAN_UP_CAP * 9 + 16;
     RAHT_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(UP_ELEMS + 2 * PLAN_UP_CAP) * (int)sizeof(Tel) + PLAN_UP_CAP * 9 + 16));
     raht_count_launches(1);
-    static const int use_pdl = getenv("RAHT_PDL") ? atoi(getenv("RAHT_PDL")) : 1;     // 0: plain launches (A/B)
+    const bool use_pdl = raht_use_pdl(PDL_TRANSFORM);
     if (use_pdl) RAHT_CUDA(pdl_launch(kern, dim3((unsigned)tiles, (unsigned)groups), dim3(TR_THREADS), smem, st, P->d, k, A, B, O, D, up_elems));
     else kern<<<dim3((unsigned)tiles, (unsigned)groups), TR_THREADS, smem, st>>>(P->d, k, A, B, O, D, up_elems);
     RAHT_LAUNCH_CHECK();

@@ -13,6 +13,7 @@ namespace {
 __global__ void __launch_bounds__(256) levels_kernel(const int64_t *__restrict__ MC, int64_t n, uint8_t *__restrict__ level,
                                                      int32_t *status)
 {
+    pdl_enter();
     bool bad = false;
     for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
         if (i == 0) { level[0] = 255; continue; }
@@ -71,6 +72,7 @@ __device__ __forceinline__ int or_bucket(int64_t, uint8_t lev) { return lev == 2
 __global__ void __launch_bounds__(OR_THREADS) order_count_kernel(const uint8_t *__restrict__ lev, int64_t n, int64_t nblocks,
                                                                 unsigned long long *counts /* [bucket][block] */)
 {
+    pdl_enter();
     __shared__ int hist[OR_BUCKETS];
     if (threadIdx.x < OR_BUCKETS) hist[threadIdx.x] = 0;
     __syncthreads();
@@ -87,6 +89,7 @@ __global__ void __launch_bounds__(OR_THREADS) order_scatter_kernel(const uint8_t
                                                                   const unsigned long long *__restrict__ offsets,
                                                                   int64_t *__restrict__ order, int32_t *__restrict__ position)
 {
+    pdl_enter();
     __shared__ int whist[OR_WARPS][OR_BUCKETS];
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     for (int i = tid; i < OR_WARPS * OR_BUCKETS; i += OR_THREADS) (&whist[0][0])[i] = 0;
@@ -139,6 +142,7 @@ constexpr int PB_WARPS = PB_THREADS / 32;
 // arrive[]: one counter per upper tile = how many of its child tiles have been planned
 __global__ void __launch_bounds__(256) plan_init_kernel(PlanDev P)
 {
+    pdl_enter();
     const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (i == 0) { *P.bump = (unsigned int)P.slots0; *P.ticket = 0u; }
     if (i < P.tiles_total) { P.arrive[i] = 0u; P.done[i] = 0u; }
@@ -369,6 +373,7 @@ __device__ __forceinline__ void plan_tile(const PlanDev &P, int stage, int64_t t
 // tiles at 1 M rows.)
 __global__ void __launch_bounds__(PB_THREADS) plan_kernel(PlanDev P, const uint8_t *__restrict__ level, double *__restrict__ w)
 {
+    pdl_enter();
     __shared__ int s_last;
     int stage = 0;
     int64_t tile = blockIdx.x;
@@ -437,7 +442,7 @@ RAHT_API int raht_tree_levels(const int64_t *MC, int64_t n, uint8_t *level, int3
 {
     RAHT_REQUIRE(n >= 0 && (n == 0 || (MC && level)), "raht_tree_levels: bad arguments");
     if (n == 0) return RAHT_OK;
-    (raht_count_launches(1), levels_kernel)<<<grid_for(n, 256, 8), 256, 0, (cudaStream_t)stream>>>(MC, n, level, status);
+    RAHT_PDL_LAUNCH(PDL_TREE, levels_kernel, grid_for(n, 256, 8), 256, 0, (cudaStream_t)stream, MC, n, level, status);
     RAHT_LAUNCH_CHECK();
     return RAHT_OK;
 }
@@ -490,9 +495,9 @@ RAHT_API int raht_order_ragft(const uint8_t *level, int64_t n, int64_t *order, i
     cudaStream_t st = (cudaStream_t)stream;
     int64_t nb = (n + OR_TILE - 1) / OR_TILE;
     unsigned long long *counts = (unsigned long long *)workspace;
-    (raht_count_launches(1), order_count_kernel)<<<(unsigned)nb, OR_THREADS, 0, st>>>(level, n, nb, counts);
-    (raht_count_launches(1), scan_counts_kernel)<<<1, 1024, 0, st>>>(counts, nb * OR_BUCKETS, nullptr);
-    (raht_count_launches(1), order_scatter_kernel)<<<(unsigned)nb, OR_THREADS, 0, st>>>(level, n, nb, counts, order, position);
+    RAHT_PDL_LAUNCH(PDL_TREE, order_count_kernel, (unsigned)nb, OR_THREADS, 0, st, level, n, nb, counts);
+    RAHT_PDL_LAUNCH(PDL_TREE, scan_counts_kernel, 1, 1024, 0, st, counts, nb * OR_BUCKETS, (int64_t *)nullptr);
+    RAHT_PDL_LAUNCH(PDL_TREE, order_scatter_kernel, (unsigned)nb, OR_THREADS, 0, st, level, n, nb, (const unsigned long long *)counts, order, position);
     RAHT_LAUNCH_CHECK();
     return RAHT_OK;
 }
@@ -539,8 +544,8 @@ RAHT_API int raht_plan_create(const uint8_t *level, int64_t n, int tile_rows, do
     P->d.ticket = (unsigned int *)(ws + L.off_bump) + 16;
     if (n > 0) {
         cudaStream_t st = (cudaStream_t)stream;
-        (raht_count_launches(1), plan_init_kernel)<<<(unsigned)((P->d.tiles_total + 255) / 256), 256, 0, st>>>(P->d);
-        (raht_count_launches(1), plan_kernel)<<<(unsigned)P->d.tiles[0], PB_THREADS, 0, st>>>(P->d, level, w);
+        RAHT_PDL_LAUNCH(PDL_TREE, plan_init_kernel, (unsigned)((P->d.tiles_total + 255) / 256), 256, 0, st, P->d);
+        RAHT_PDL_LAUNCH(PDL_TREE, plan_kernel, (unsigned)P->d.tiles[0], PB_THREADS, 0, st, P->d, level, w);
         cudaError_t e = cudaGetLastError();
         if (e != cudaSuccess) {
             raht_set_error("raht_plan_create: launch: %s", cudaGetErrorString(e));

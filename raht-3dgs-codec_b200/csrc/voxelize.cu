@@ -48,12 +48,14 @@ __device__ __forceinline__ void atomic_max_f32(float *addr, float v)
 
 __global__ void bounds_init_kernel(float *b)
 {
+    pdl_enter();
     if (threadIdx.x < 3) b[threadIdx.x] = INFINITY;
     else if (threadIdx.x < 6) b[threadIdx.x] = -INFINITY;
 }
 
 __global__ void __launch_bounds__(256) bounds3_kernel(const float *__restrict__ V, int64_t n, int64_t ld, float *bounds6)
 {
+    pdl_enter();
     float mn[3] = {INFINITY, INFINITY, INFINITY}, mx[3] = {-INFINITY, -INFINITY, -INFINITY};
     for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
         const float *p = V + i * ld;
@@ -87,7 +89,7 @@ RAHT_API int raht_bounds3_f32(const float *V, int64_t n, int64_t ld, float *boun
     RAHT_REQUIRE(bounds6 && (V || n == 0) && ld >= 3 && n >= 0, "raht_bounds3_f32: bad arguments");
     cudaStream_t st = (cudaStream_t)stream;
     (raht_count_launches(1), bounds_init_kernel)<<<1, 32, 0, st>>>(bounds6);
-    if (n) (raht_count_launches(1), bounds3_kernel)<<<grid_for(n, 256, 8), 256, 0, st>>>(V, n, ld, bounds6);
+    if (n) RAHT_PDL_LAUNCH(PDL_FRONT, bounds3_kernel, grid_for(n, 256, 8), 256, 0, st, V, n, ld, bounds6);
     RAHT_LAUNCH_CHECK();
     return RAHT_OK;
 }
@@ -97,6 +99,7 @@ struct F3 { float v[3]; };
 __global__ void voxel_params_kernel(const float *bounds6, int J, int use_vmin, F3 vmin_given, int use_width,
                                     double width_given, float *params4, double *params_d2)
 {
+    pdl_enter();
     if (threadIdx.x != 0) return;
     float vmin[3];
     for (int d = 0; d < 3; ++d) vmin[d] = use_vmin ? vmin_given.v[d] : bounds6[d];   // voxelize_pc.py:87-90
@@ -125,8 +128,7 @@ RAHT_API int raht_voxel_params(const float *bounds6, int J, int use_given_vmin, 
     RAHT_REQUIRE(!use_given_vmin || vmin_host, "raht_voxel_params: vmin_host required");
     F3 vm = {{0, 0, 0}};
     if (use_given_vmin) { vm.v[0] = vmin_host[0]; vm.v[1] = vmin_host[1]; vm.v[2] = vmin_host[2]; }
-    (raht_count_launches(1), voxel_params_kernel)<<<1, 32, 0, (cudaStream_t)stream>>>(bounds6, J, use_given_vmin, vm, use_given_width, width_host,
-                                                            params4, params_d2);
+    RAHT_PDL_LAUNCH(PDL_FRONT, voxel_params_kernel, 1, 32, 0, (cudaStream_t)stream, bounds6, J, use_given_vmin, vm, use_given_width, width_host, params4, params_d2);
     RAHT_LAUNCH_CHECK();
     return RAHT_OK;
 }
@@ -136,6 +138,7 @@ __global__ void __launch_bounds__(256) morton_f32_kernel(const float *__restrict
                                                          const float *__restrict__ params4, int J,
                                                          uint64_t *__restrict__ keys, int64_t *__restrict__ vint)
 {
+    pdl_enter();
     const float vx = params4[0], vy = params4[1], vz = params4[2], vs = params4[3];
     const int64_t hi = ((int64_t)1 << J) - 1;
     for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
@@ -158,7 +161,7 @@ RAHT_API int raht_morton_keys_f32(const float *V, int64_t n, int64_t ld, const f
     RAHT_REQUIRE(n >= 0 && ld >= 3 && J >= 1 && J <= 21 && params4 && (n == 0 || (V && keys)),
                  "raht_morton_keys_f32: bad arguments");
     if (n == 0) return RAHT_OK;
-    (raht_count_launches(1), morton_f32_kernel)<<<grid_for(n, 256, 8), 256, 0, (cudaStream_t)stream>>>(V, n, ld, params4, J, keys, vint);
+    RAHT_PDL_LAUNCH(PDL_FRONT, morton_f32_kernel, grid_for(n, 256, 8), 256, 0, (cudaStream_t)stream, V, n, ld, params4, J, keys, vint);
     RAHT_LAUNCH_CHECK();
     return RAHT_OK;
 }
@@ -251,6 +254,7 @@ struct BoundaryEmit {
 };
 __global__ void segments_tail_kernel(const int64_t *count, int64_t *nvox, int32_t *off, int64_t n)
 {
+    pdl_enter();
     int64_t c = *count;
     if (nvox) *nvox = c;
     if (off) off[c] = (int32_t)n;
@@ -273,7 +277,7 @@ RAHT_API int raht_voxel_segments(const uint64_t *sorted_keys, int64_t n, int64_t
     BoundaryPred pred{sorted_keys};
     BoundaryEmit emit{sorted_keys, voxel_indices, cluster_offsets, unique_keys};
     device_select(n, pred, emit, count, sel_ws, st);
-    (raht_count_launches(1), segments_tail_kernel)<<<1, 1, 0, st>>>(count, nvox, cluster_offsets, n);
+    RAHT_PDL_LAUNCH(PDL_FRONT, segments_tail_kernel, 1, 1, 0, st, (const int64_t *)count, nvox, cluster_offsets, n);
     RAHT_LAUNCH_CHECK();
     return RAHT_OK;
 }
