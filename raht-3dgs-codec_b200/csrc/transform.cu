@@ -712,8 +712,11 @@ int launch_stage0_d(const raht_plan *P, const Tin *A, const Tel *B, Tel *O, int 
     }
 }
 
+// head: the first kernel of a raht_inverse call.  It is a PLAIN launch: the later kernels of the call read T ahead of their
+// waits (stage 0's bulk load), which is only safe if whatever produced T -- possibly a kernel that triggers its dependents
+// early, like this library's own forward stages -- had completed before the call's first kernel started.
 template <typename Tel, bool FWD>
-int launch_upper(const raht_plan *P, int k, const Tel *A, const Tel *B, Tel *O, int D, cudaStream_t st)
+int launch_upper(const raht_plan *P, int k, const Tel *A, const Tel *B, Tel *O, int D, cudaStream_t st, bool head = false)
 {
     auto kern = transform_upper_kernel<Tel, FWD>;
     const int64_t tiles = P->d.tiles[k];
@@ -737,7 +740,7 @@ int launch_upper(const raht_plan *P, int k, const Tel *A, const Tel *B, Tel *O, 
     const size_t smem = (size_t)(up_elems + 2 * PLAN_UP_CAP) * sizeof(Tel) + (size_t)PLAN_UP_CAP * 9 + 16;
     RAHT_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(UP_ELEMS + 2 * PLAN_UP_CAP) * (int)sizeof(Tel) + PLAN_UP_CAP * 9 + 16));
     raht_count_launches(1);
-    const bool use_pdl = raht_use_pdl(PDL_TRANSFORM);
+    const bool use_pdl = raht_use_pdl(PDL_TRANSFORM) && !head;
     if (use_pdl) RAHT_CUDA(pdl_launch(kern, dim3((unsigned)tiles, (unsigned)groups), dim3(TR_THREADS), smem, st, P->d, k, A, B, O, D, up_elems));
     else kern<<<dim3((unsigned)tiles, (unsigned)groups), TR_THREADS, smem, st>>>(P->d, k, A, B, O, D, up_elems);
     RAHT_LAUNCH_CHECK();
@@ -893,7 +896,7 @@ int inverse_impl(const raht_plan *P, const Tel *T, Tel *C, int D, int use_tma, c
     int rc = RAHT_OK;
     const int S = P->d.n_stages;
     for (int k = S - 1; k >= 1 && rc == RAHT_OK; --k)
-        rc = launch_upper<Tel, false>(P, k, T, k == S - 1 ? (const Tel *)nullptr : (const Tel *)C, C, D, st);
+        rc = launch_upper<Tel, false>(P, k, T, k == S - 1 ? (const Tel *)nullptr : (const Tel *)C, C, D, st, k == S - 1);
     if (rc == RAHT_OK) rc = launch_stage0_d<Tel, Tel, false>(P, T, S > 1 ? (const Tel *)C : (const Tel *)nullptr, C, D, use_tma, st);
     return rc;
 }
@@ -922,7 +925,7 @@ int dequant_inverse_impl(const raht_plan *P, Tel *T, Tel *C, int D, int use_tma,
         deferred_rows_kernel<Tel, false><<<(unsigned)P->d.tiles[0], TR_THREADS, 0, st>>>(P->d, T, D, Q);
         RAHT_LAUNCH_CHECK();
     }
-    for (int k = S - 1; k >= 1 && rc == RAHT_OK; --k)
+    for (int k = S - 1; k >= 1 && rc == RAHT_OK; --k)                     // (the deferred-rows kernel above is the call's head)
         rc = launch_upper<Tel, false>(P, k, (const Tel *)T, k == S - 1 ? (const Tel *)nullptr : (const Tel *)C, C, D, st);
     if (rc == RAHT_OK)
         rc = launch_stage0_qd<Tel, Tel, false, QM_INV>(P, (const Tel *)T, S > 1 ? (const Tel *)C : (const Tel *)nullptr, C, D, use_tma, Q, st);
