@@ -170,6 +170,33 @@ def test_oracle_raht_pipeline(n, J, D, clustered, seed):
         assert torch.equal(ops.rlgr_decode(streams, 1, use_index=False), q)
 
 
+@pytest.mark.parametrize("n,J,seed", [(700, 6, 31), (3000, 6, 32), (9000, 8, 33)])
+def test_transform_calls_back_to_back_on_small_scenes(n, J, seed):
+    """The stages of a transform are programmatic dependent launches: the kernels of a call start while the
+    kernel before them drains, and some read their inputs ahead of their wait.  On small scenes every grid of the chain
+    fits the GPU at once, so a missing dependency shows: forward -> inverse -> forward queued without a host
+    synchronisation, many times over the same buffers, must give the oracle's bits every time."""
+    from raht_b200 import ops
+    Pts, MC = helpers.unique_sorted_voxels(n, J, seed, False)
+    N = len(MC)
+    C = np.random.default_rng(seed).normal(size=(N, 59)).astype(np.float64) * 7.0
+    t = orc.Tree(MC, J)
+    To, _ = t.forward(C)
+    Co = t.inverse(To)
+    tree = ops.tree_from_keys(cu(MC))
+    Cd = cu(C)
+    out = []
+    for _ in range(25):
+        T = ops.forward(tree, Cd, torch.float64)
+        R = ops.inverse(tree, T)
+        T2 = ops.forward(tree, R, torch.float64)
+        out.append((T, R, T2))
+    torch.cuda.synchronize()
+    To2, _ = t.forward(Co)
+    for T, R, T2 in out:
+        assert np.array_equal(T.cpu().numpy(), To) and np.array_equal(R.cpu().numpy(), Co) and np.array_equal(T2.cpu().numpy(), To2)
+
+
 def test_fp32_mode_tolerance():
     """Build-specific fp32 transform: <= 1e-5 relative error on coefficients, PSNR within 0.01 dB."""
     from raht_b200 import ops, codec
