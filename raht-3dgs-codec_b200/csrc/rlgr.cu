@@ -1777,6 +1777,9 @@ RAHT_API int raht_rlgr_build_index(const uint8_t *streams, int64_t slot_bytes, c
     return RAHT_OK;
 }
 
+static thread_local bool g_dec_share = false;
+void raht_rlgr_decode_share_gpu() { g_dec_share = true; }      // (internal, common.cuh) applies to this thread's next raht_rlgr_decode
+
 RAHT_API int raht_rlgr_decode(const uint8_t *streams, int64_t slot_bytes, const int64_t *nbytes, const void *sync_index,
                               int64_t n, int64_t ld, int nch, int flag_signed, int32_t *q, void *stream)
 {
@@ -1794,7 +1797,24 @@ RAHT_API int raht_rlgr_decode(const uint8_t *streams, int64_t slot_bytes, const 
         const int64_t entries = raht_rlgr_sync_entries(n);
         const dim3 grid((unsigned)((entries + DEC_THREADS - 1) / DEC_THREADS), nch);
         raht_count_launches(1);
-        rlgr_decode_indexed_kernel<<<grid, DEC_THREADS, 0, st>>>(streams, slot_bytes, nbytes, (const uint2 *)sync_index, entries, G, q);
+        // At most k CTAs of the decoder per SM (by dynamic shared memory it does not use) when the caller builds the tree on
+        // the side stream at the same time (raht_rlgr_decode_share_gpu, scene.cu): the decoder's grid is little more than one
+        // wave that fills every register file, and the tree's kernels found no room next to it until it drained.  9 of 10:
+        // the two decoder legs 0.465 -> 0.427 ms at 1 M (8: 0.437, 7: 0.444, 6: 0.503).  RAHT_DEC_CTAS overrides (0 = no limit).
+        static const int env_ctas = getenv("RAHT_DEC_CTAS") ? atoi(getenv("RAHT_DEC_CTAS")) : -1;
+        // (only while the grid is a few waves: a long decode leaves gaps between its waves anyway, and the 6 M scene lost
+        // 0.08 ms to the limit)
+        const bool few_waves = (int64_t)grid.x * grid.y <= (int64_t)3 * 10 * sm_count_cached();
+        const int dec_ctas = !g_dec_share ? 0 : env_ctas >= 0 ? env_ctas : (few_waves ? 9 : 0);
+        g_dec_share = false;
+        size_t pad = 0;
+        if (dec_ctas > 0) {
+            const size_t per = (size_t)227 * 1024 / (size_t)dec_ctas, fixed = sizeof(int32_t) * (DEC_THREADS / 32) * 32 * DEC_PITCH + 1024;
+            pad = per > fixed + 1024 ? per - fixed - 512 : 0;
+            if (pad > 200 * 1024) pad = 200 * 1024;
+            RAHT_CUDA(cudaFuncSetAttribute(rlgr_decode_indexed_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)pad));
+        }
+        rlgr_decode_indexed_kernel<<<grid, DEC_THREADS, pad, st>>>(streams, slot_bytes, nbytes, (const uint2 *)sync_index, entries, G, q);
     } else {
         RAHT_CUDA(cudaMemsetAsync(q, 0, ((size_t)(nch - 1) * ld + n) * 4, st));  // the serial decoder stores non-zeros only
         (raht_count_launches(1), rlgr_decode_serial_kernel)<<<nch, 32, 0, st>>>(streams, slot_bytes, nbytes, G, q);

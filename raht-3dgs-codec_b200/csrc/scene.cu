@@ -311,6 +311,7 @@ RAHT_API int raht_scene_decode(const uint64_t *keys, int64_t nvox, int J, const 
     cudaStream_t side = dec_side ? raht_side_fork(st) : nullptr;
     RAHT_TRY(build_tree(keys, nvox, tile_rows, B, status, plan, side ? side : st));
     record(events, 0, st);                                                                       // raht_param_dec
+    if (side) raht_rlgr_decode_share_gpu();
     RAHT_TRY(raht_rlgr_decode(streams, slot_bytes, nbytes, sync_index, nvox, B.ld, D, 1, B.q, st));
     if (side) RAHT_TRY(raht_side_join(st));
     record(events, 1, st);                                                                       // rlgr_decode
