@@ -483,6 +483,8 @@ def run_gpu(args):
                 rate = False
             if k == "rlgr_decode" and dec_side:
                 b += sb.get("raht_param_dec", 0)
+            if k == "merge" and enc_side:
+                b += sb.get("raht_param", 0)
             tab[k] = {"ms": round(v, 4), "max_ms": round(res["stage_max"][k], 4),
                       "GBps": round(b / (v / 1e3) / 1e9, 1) if v > 0 and rate else None,
                       "frac_of_peak": round(b / (v / 1e3) / 1e9 / peak, 4) if v > 0 and rate else None}
@@ -671,7 +673,8 @@ def run_gpu(args):
                                   "all of them inside the timed region; the one synchronisation left inside a step is the voxel count",
                    "overlap": "the tree build (levels, order, plan) runs on the library's side stream next to the merge (encoder) and next to "
                               "the RLGR decode (decoder), RAHT_ENC_SIDE / RAHT_DEC_SIDE: in `stages`, raht_param / raht_param_dec are the part "
-                              "of the build that the other leg does not cover, and rlgr_decode holds both decoder legs",
+                              "of the build that the other leg does not cover, and merge / rlgr_decode hold both legs (the merge runs as short-lived CTAs "
+                              "and the decoder with 9 CTAs per SM so that the tree's kernels find room)",
                    "parallelism": "scene-per-GPU (no collective)" if world > 1 else "single GPU",
                    "decoder": "rebuilds the tree from the voxel keys (no encoder state reused); RLGR decode is chunk-parallel "
                               "through the encoder's sync index (side information next to the reference-format streams)"},

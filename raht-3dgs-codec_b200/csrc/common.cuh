@@ -13,6 +13,7 @@ void raht_set_error(const char *fmt, ...);
 void raht_count_launches(int n);   // bookkeeping for raht_launch_count() (bench.py reports it)
 cudaStream_t raht_side_fork(cudaStream_t st);   // api.cu: the device's side stream, waiting for what `st` holds so far (nullptr: unavailable)
 int raht_side_join(cudaStream_t st);             // `st` waits for what the side stream holds so far
+void raht_merge_share_gpu();                     // merge.cu: the next raht_merge_segments of this thread runs as short-lived CTAs
 void raht_rlgr_decode_share_gpu();               // rlgr.cu: the next raht_rlgr_decode of this thread leaves room for a side-stream leg
 
 #define RAHT_REQUIRE(cond, ...)                                                                    \

@@ -9,6 +9,7 @@
 // of the inputs (the reference's --use_fast_math build is not).
 #include "common.cuh"
 #include <math.h>
+#include <stdlib.h>
 
 namespace {
 
@@ -258,6 +259,9 @@ void launch_merge(int slots, int grid, cudaStream_t st, const int32_t *ci, const
 
 }  // namespace
 
+static thread_local bool g_merge_share = false;
+void raht_merge_share_gpu() { g_merge_share = true; }          // (internal, common.cuh) applies to this thread's next raht_merge_segments
+
 RAHT_API int raht_merge_segments(const int32_t *cluster_indices, const int32_t *cluster_offsets, int64_t num_clusters,
                                  const float *means, const float *quats, const float *scales, const float *opacities,
                                  const float *colors, int color_dim, int weight_by_opacity, float *m_means,
@@ -273,7 +277,15 @@ RAHT_API int raht_merge_segments(const int32_t *cluster_indices, const int32_t *
     RAHT_REQUIRE(color_dim <= 245, "raht_merge_segments: color_dim must be <= 245");
     cudaStream_t st = (cudaStream_t)stream;
     const int slots = (11 + color_dim + 31) / 32;
-    const int grid = grid_for((num_clusters + 31) / 32, MG_WARPS, 4);                  // a warp per block of 32 voxels; 4 CTAs of 64 registers per SM
+    // One persistent wave (4 CTAs of 64 registers per SM hold every register of the GPU) is the fastest merge on its own,
+    // but nothing else gets onto an SM until it ends.  When the caller builds the tree on the side stream at the same time
+    // (raht_merge_share_gpu, scene.cu) the grid is up to 8 waves of short-lived CTAs instead, and the tree's kernels take
+    // the slots they free: merge 0.234 -> 0.303 ms, but the tree build (0.105 ms exposed before) disappears under it.
+    // RAHT_MERGE_WAVES overrides the 8.
+    static const int env_waves = getenv("RAHT_MERGE_WAVES") ? atoi(getenv("RAHT_MERGE_WAVES")) : 0;
+    const int waves = !g_merge_share ? 1 : (env_waves > 0 ? env_waves : 8);
+    g_merge_share = false;
+    const int grid = grid_for((num_clusters + 31) / 32, MG_WARPS, 4 * waves);          // a warp per block of 32 voxels
     raht_count_launches(1);
     if (packed && packed_dtype == RAHT_F64)
         launch_merge<double>(slots, grid, st, cluster_indices, cluster_offsets, num_clusters, means, quats, scales, opacities,

@@ -254,6 +254,7 @@ RAHT_API int raht_scene_encode(const uint32_t *sort_idx, const int32_t *cluster_
     // RAHT_ENC_SIDE=0: one stream.
     static const int enc_side = getenv("RAHT_ENC_SIDE") ? atoi(getenv("RAHT_ENC_SIDE")) : 1;
     cudaStream_t side = enc_side ? raht_side_fork(st) : nullptr;
+    if (side) raht_merge_share_gpu();
     RAHT_TRY(raht_merge_segments((const int32_t *)sort_idx, cluster_offsets, nvox, means, quats, scales, opacities, colors, color_dim, 1,
                                  nullptr, nullptr, nullptr, nullptr, nullptr, packed, RAHT_F32, st));
     record(events, 0, st);                                                                       // merge
