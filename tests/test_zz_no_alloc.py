@@ -20,10 +20,22 @@ def _both(T):
     ref = torch.empty(2, D, dtype=torch.float64, device=T.device)
     got = torch.full((2, D), float("nan"), dtype=torch.float64, device=T.device)
     check(lib.raht_channel_minmax(ptr(T), tag, n, D, ptr(ref), ptr(ws), ws_bytes, stream()), "raht_channel_minmax")
-    before = torch.cuda.memory_allocated(T.device)
-    check(lib.raht_channel_minmax_static(ptr(T), tag, n, D, ptr(got), stream()), "raht_channel_minmax_static")
-    assert torch.cuda.memory_allocated(T.device) == before
+    # Nothing may be allocated during the call: torch's count of allocations ever made stays put and the bytes in use do not
+    # grow.  The garbage collector is held off for the window -- after the other tests it may free cyclic garbage at any
+    # moment, which moved `memory_allocated` under an earlier form of this check (equality).
+    import gc
     torch.cuda.synchronize()
+    gc.collect()
+    gc.disable()
+    try:
+        allocs = torch.cuda.memory_stats(T.device).get("allocation.all.allocated", 0)
+        before = torch.cuda.memory_allocated(T.device)
+        check(lib.raht_channel_minmax_static(ptr(T), tag, n, D, ptr(got), stream()), "raht_channel_minmax_static")
+        torch.cuda.synchronize()
+        assert torch.cuda.memory_stats(T.device).get("allocation.all.allocated", 0) == allocs
+        assert torch.cuda.memory_allocated(T.device) <= before
+    finally:
+        gc.enable()
     return got.cpu().numpy(), ref.cpu().numpy()
 
 
