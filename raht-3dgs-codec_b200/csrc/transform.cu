@@ -117,8 +117,15 @@ __device__ __forceinline__ void stage0_tile(const PlanDev &P, int64_t tile, cons
 
     if (tid < (int)(sizeof(TileHdr) / 4)) ((uint32_t *)s_hdr)[tid] = ((const uint32_t *)(P.hdr + tile))[tid];
     const bool patch = (B != nullptr) || QM == QM_FWD;       // (QM_FWD: the flags pick the rows that go to T)
-    if (patch)
-        for (int j = tid; j < R; j += TR_THREADS) s_flag[j] = 0;     // (ahead of the header barrier: the deferred list below sets them)
+    // The tile's deferred list sits at a fixed place of the plan: it is requested together with the header (at most
+    // PLAN_DEFER_MAX entries, the count arrives with the header), so that the rows it names can be requested right behind
+    // the header barrier -- with the schedule, not a round trip after it.
+    static_assert(PLAN_DEFER_MAX <= TR_THREADS, "one deferred entry per thread");
+    uint16_t dl_pre = 0;
+    if (patch) {
+        if (tid < PLAN_DEFER_MAX) dl_pre = P.def_local[(size_t)tile * PLAN_DEFER_MAX + tid];
+        for (int j = tid; j < R; j += TR_THREADS) s_flag[j] = 0;
+    }
     __syncthreads();
     const int n_rows = s_hdr->n_rows;
     const int n_bf = s_hdr->n_bf;
@@ -152,26 +159,26 @@ __device__ __forceinline__ void stage0_tile(const PlanDev &P, int64_t tile, cons
         }
     }
 
-    // schedule and coefficients (overlaps the bulk copy)
-    for (int j = tid; j < n_bf; j += TR_THREADS) {
-        s_sched[j] = P.sched[bf_off + j];
-        double2 c = P.ab[bf_off + j];
-        s_ab[2 * j] = (Tel)c.x;
-        s_ab[2 * j + 1] = (Tel)c.y;
+    if (patch && tid < min((int)s_hdr->n_def, PLAN_DEFER_MAX)) {
+        s_flag[dl_pre] = 1;
+        s_def[tid] = dl_pre;
     }
-    if (patch) {                                             // same round trip as the schedule (the flags were zeroed above)
-        const int n_def = s_hdr->n_def;
-        for (int j = tid; j < n_def; j += TR_THREADS) {
-            const uint16_t dl = P.def_local[(size_t)tile * PLAN_DEFER_MAX + j];
-            s_flag[dl] = 1;
-            s_def[j] = dl;
-        }
-    }
-    __syncthreads();
+    // the deferred list for the row requests below, and thread 0's mbarrier initialisation for everybody's wait on it
+    // (nothing is in flight but the bulk copy: a short barrier)
+    if (patch || tma_in) __syncthreads();
 
-    // rows this tile deferred come from B: the first PF_ITEMS elements per thread are requested BEFORE the wait for the
-    // bulk copy (a dependent second round of loads after it cost ~1 us per tile), the rest (tiles that defer more than
-    // ~34 rows) afterwards
+    // schedule and coefficients: a thread's first entry is requested here, into registers (plan data: part of the prologue
+    // of a programmatic dependent launch), and stored behind the row requests below, so that neither waits for the other
+    uint32_t sched_r = 0;
+    double2 ab_r = make_double2(0.0, 0.0);
+    if (tid < n_bf) {
+        sched_r = P.sched[bf_off + tid];
+        ab_r = P.ab[bf_off + tid];
+    }
+
+    // rows this tile deferred come from B: the first PF_ITEMS elements per thread are requested BEFORE the schedule is
+    // stored and before the wait for the bulk copy (dependent rounds of loads behind either cost ~1 us per tile each), the
+    // rest (tiles that defer more than ~34 rows) afterwards
     constexpr int PF_ITEMS = 8;
     Tel pf[PF_ITEMS];
     const int n_patch = (B != nullptr) ? (int)s_hdr->n_def * D : 0;
@@ -257,6 +264,17 @@ __device__ __forceinline__ void stage0_tile(const PlanDev &P, int64_t tile, cons
             const Tel *src = B + (size_t)(base + s_def[j]) * D + c;
             s_rows[(int)s_def[j] * D + c] = CHAIN == CHAIN_INV ? ld_cg(src) : *src;
         }
+    }
+    if (tid < n_bf) {                                        // (requested behind the header barrier, with the rows)
+        s_sched[tid] = sched_r;
+        s_ab[2 * tid] = (Tel)ab_r.x;
+        s_ab[2 * tid + 1] = (Tel)ab_r.y;
+    }
+    for (int j = tid + TR_THREADS; j < n_bf; j += TR_THREADS) {        // (tiles of more than TR_THREADS rows)
+        s_sched[j] = P.sched[bf_off + j];
+        double2 c = P.ab[bf_off + j];
+        s_ab[2 * j] = (Tel)c.x;
+        s_ab[2 * j + 1] = (Tel)c.y;
     }
     __syncthreads();
 
