@@ -1111,6 +1111,9 @@ __global__ void __launch_bounds__(32 * SOLVE_WARPS) rlgr_resolve_kernel(Geometry
         const uint4 *mr = rec + cm * REC_WORDS;
         uint4 m0 = mr[0], m1 = mr[1], m2 = mr[2], m3 = mr[3];
         const int cnt = (int)min((int64_t)32, nchunks - base);
+        // sparse channel: the table window of every chunk of the batch, one load per lane (inside the serial walk below it was
+        // a dependent round trip in front of the table entry's, for every chunk that needs its table)
+        const uint32_t my_window = dense ? 0u : headers[(size_t)ch * G.nsb + (size_t)mine * CHUNK_LANES];
         uint32_t my_sel = 0, my_bits = 0, my_start = 0;              // my_start: 0 = settled by a record, else state | 1 << 16 (table)
         for (int i = 0; i < cnt; ++i) {
             int b = -1;
@@ -1125,7 +1128,7 @@ __global__ void __launch_bounds__(32 * SOLVE_WARPS) rlgr_resolve_kernel(Geometry
                 const size_t ci = (size_t)ch * G.W + w;
                 bool settled = false;
                 if (!dense) {                                        // sparse channel: the chunk's transition table
-                    const int idx = tab_index(headers[(size_t)ch * G.nsb + w * CHUNK_LANES], ps);
+                    const int idx = tab_index(__shfl_sync(~0u, my_window, i), ps);
                     uint2 te = make_uint2(TAB_DEAD, 0u);
                     if (idx >= 0) te = ctab[ci * TAB_STATES + idx];
                     if (te.x != TAB_DEAD) {
